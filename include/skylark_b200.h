@@ -1,0 +1,152 @@
+/*
+ * skylark_b200.h -- C ABI of libcskylark_b200.so, the B200-native replacement for the
+ * sketch-apply subset of libSkylark's libcskylark.so.
+ *
+ * Part 1 keeps the reference's entry points (names, argument order and meaning, error
+ * codes) so that python-skylark's lib.py / sketch.py bind to it unchanged; each
+ * declaration cites the reference declaration it replaces (paths are relative to the
+ * reference checkout).  Part 2 holds additive extensions (explicit contexts, device
+ * buffers, streams, row shards, table export for tests, launch accounting).
+ *
+ * All matrices follow the reference convention: dense = column-major with leading
+ * dimension, sparse = CSC with int32 indices; buffers are attached, never copied or
+ * owned by the wrapper.  Return value 0 = success, otherwise a code from
+ * base/exception.hpp:9-24 (100..113); sl_get_exception_info() gives the message.
+ * Every compute entry point needs a CUDA device: there is no CPU fallback.
+ */
+#ifndef SKYLARK_B200_H
+#define SKYLARK_B200_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sl_context_t sl_context_t;
+typedef struct sl_sketch_transform_t sl_sketch_transform_t;
+
+#define SL_COLUMNWISE 1 /* capi/basec.hpp:12 */
+#define SL_ROWWISE 2    /* capi/basec.hpp:13 */
+
+/* ------------------------------------------------------------------ Part 1 ---- */
+
+/* capi/basec.hpp:22, capi/csketch.cpp:74-376: space separated ("T","In","Out") tuples. */
+char *sl_supported_sketch_transforms(void);
+/* capi/basec.hpp:28 */
+const char *sl_strerror(const int errorcode);
+/* capi/basec.hpp:33-34 */
+bool sl_has_elemental(void);
+bool sl_has_combblas(void);
+
+/* capi/basec.hpp:43-44, capi/cbase.cpp:37-44 */
+int sl_create_default_context(int seed, sl_context_t **ctxt);
+/* capi/basec.hpp:52-53, capi/cbase.cpp:46-53: the communicator is ignored there too. */
+int sl_create_context(int seed, void *comm_ignored, sl_context_t **ctxt);
+/* capi/basec.hpp:58 */
+int sl_free_context(sl_context_t *ctxt);
+
+/* capi/sketchc.hpp:21-23, capi/csketch.cpp:379-545.  Variadic tail: CT `double C`;
+ * WZT `double p`; GaussianRFT / LaplacianRFT `double sigma`.  Unknown type -> 111. */
+int sl_create_sketch_transform(sl_context_t *ctxt, char *type, int n, int s,
+                               sl_sketch_transform_t **sketch, ...);
+/* capi/sketchc.hpp:29-30 */
+int sl_deserialize_sketch_transform(const char *data, sl_sketch_transform_t **sketch);
+/* capi/sketchc.hpp:36-37; *data is malloc'ed, caller frees with free(). */
+int sl_serialize_sketch_transform(const sl_sketch_transform_t *sketch, char **data);
+/* capi/sketchc.hpp:42-43 */
+int sl_free_sketch_transform(sl_sketch_transform_t *S);
+/* capi/sketchc.hpp:53-56, capi/csketch.cpp:614-1958.  input_type/output_type are
+ * "Matrix" or "SparseMatrix"; A/SA come from the sl_wrap_* functions; dim is
+ * SL_COLUMNWISE (SA = S*A) or SL_ROWWISE (SA = A*S^T).  An unsupported combination
+ * returns 109 (the reference silently returns 0, capi/csketch.cpp:1957). */
+int sl_apply_sketch_transform(sl_sketch_transform_t *S, char *input_type, void *A,
+                              char *output_type, void *SA, int dim);
+
+/* capi/basec.hpp:62-64, capi/cbase.cpp:63-75: host buffer, column-major m x n, ld = m. */
+int sl_wrap_raw_matrix(double *data, int m, int n, void **A);
+int sl_free_raw_matrix_wrap(void *A_);
+/* capi/basec.hpp:66-83, capi/cbase.cpp:77-121: host CSC, int32 indptr[n_cols+1]/indices. */
+int sl_wrap_raw_sp_matrix(int *indptr, int *ind, double *data, int nnz, int n_rows,
+                          int n_cols, void **A);
+int sl_free_raw_sp_matrix_wrap(void *A_);
+int sl_raw_sp_matrix_struct_updated(void *A_, bool *struct_updated);
+int sl_raw_sp_matrix_reset_update_flag(void *A_);
+int sl_raw_sp_matrix_nnz(void *A_, int *nnz);
+int sl_raw_sp_matrix_height(void *A_, int *height);
+int sl_raw_sp_matrix_width(void *A_, int *width);
+int sl_raw_sp_matrix_data(void *A_, int32_t *indptr, int32_t *indices, double *values);
+
+/* capi/basec.hpp:85-87; *info is malloc'ed (the reference mixes new[] with free()). */
+void sl_get_exception_info(char **info);
+void sl_print_exception_trace(void);
+
+/* ------------------------------------------------------------------ Part 2 ---- */
+
+/* context_t(seed, counter) (base/context.hpp:25-27) and its accessors (:166). */
+int sl_create_context_at(int seed, uint64_t counter, sl_context_t **ctxt);
+int sl_context_get_seed(sl_context_t *ctxt, int *seed);
+int sl_context_get_counter(sl_context_t *ctxt, uint64_t *counter);
+
+#define SL_DTYPE_F64 0
+#define SL_DTYPE_F32 1
+/* Device-resident column-major matrix (m x n, leading dimension ld, elements of dtype)
+ * on CUDA device `device`; the counterpart of sl_wrap_raw_matrix for torch tensors.
+ * Free with sl_free_raw_matrix_wrap. */
+int sl_wrap_device_matrix(void *dptr, int64_t m, int64_t n, int64_t ld, int dtype, int device,
+                          void **A);
+/* Device-resident CSC.  Free with sl_free_raw_sp_matrix_wrap. */
+int sl_wrap_device_sp_matrix(int32_t *indptr, int32_t *ind, double *data, int64_t nnz,
+                             int64_t n_rows, int64_t n_cols, int device, void **A);
+
+/* CUDA stream (cudaStream_t) used by subsequent calls of the calling thread; NULL = the
+ * legacy default stream.  Device-matrix applies are asynchronous on that stream. */
+int sl_set_stream(void *cuda_stream);
+
+/* Row-sharded apply: A holds sketched indices [index_offset, index_offset + local) of
+ * the transform's N; SA receives this shard's partial sum (to be summed across shards,
+ * cf. sketch/hash_transform_Elemental.hpp:543-561 and
+ * sketch/dense_transform_Elemental_coldist_star.hpp:200-229).  Not valid for FJLT. */
+int sl_apply_sketch_transform_shard(sl_sketch_transform_t *S, char *input_type, void *A,
+                                    char *output_type, void *SA, int dim,
+                                    int64_t index_offset);
+
+/* Options: "boost_order" = "160" (default; Boost >= 1.57 Rademacher draw order) | "155";
+ * "fjlt_fut" = "dct" (default; what the reference computes) | "wht". */
+int sl_set_option(const char *key, const char *value);
+
+/* Generated tables, copied to host memory (tests compare them bit for bit):
+ * what = "row_idx" (int64, hash), "row_value" (double, hash), "D" (double, FJLT),
+ * "samples" (int64, FJLT), "shifts" (double, RFT), "scales" (double, RFT);
+ * elements [first, first+count). */
+int sl_sketch_export(sl_sketch_transform_t *S, const char *what, int64_t first, int64_t count,
+                     void *host_out);
+/* Dense S block S[i0:i0+h, j0:j0+w], column-major doubles, to host memory
+ * (sketch/dense_transform_data.hpp:79-101). */
+int sl_sketch_export_dense(sl_sketch_transform_t *S, int64_t i0, int64_t j0, int64_t h,
+                           int64_t w, double *host_out);
+/* Raw MicroURNG draws of stream indices [base, base+count): first[i] = X1, second[i] = X0
+ * (base/randgen.hpp:109-114), generated on the device. */
+int sl_rng_export_raw(int seed, uint64_t base, int64_t count, uint64_t *first,
+                      uint64_t *second);
+
+/* Launch accounting.  Classes: 0 tables, 1 hash apply, 2 dense panel generation,
+ * 3 dense GEMM, 4 FJLT, 5 misc.  With timing enabled every launch is bracketed by CUDA
+ * events on its stream; sl_profile_read synchronises and returns the totals. */
+#define SL_KERNEL_CLASSES 6
+int sl_profile_enable(int timing_on);
+int sl_profile_reset(void);
+int sl_profile_read(unsigned long long launches[SL_KERNEL_CLASSES],
+                    double ms[SL_KERNEL_CLASSES]);
+
+/* Pinned host memory for the host-buffer path (cudaHostAlloc / cudaFreeHost). */
+int sl_host_alloc_pinned(size_t bytes, void **ptr);
+int sl_host_free_pinned(void *ptr);
+int sl_device_count(int *count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SKYLARK_B200_H */

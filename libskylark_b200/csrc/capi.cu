@@ -1,0 +1,771 @@
+// C ABI of libcskylark_b200.so (declared in include/skylark_b200.h).
+//
+// Mirrors the sketch subset of the reference's capi/{cbase,csketch}.cpp: contexts with
+// seed + counter semantics (base/context.hpp:19-183), sketch data objects whose random
+// state is a set of counter-stream bases (sketch/*_data.hpp), raw-matrix wrappers, JSON
+// (de)serialisation that replays the RNG, the error-code convention of
+// base/exception.hpp:9-24.  All arithmetic runs on the GPU; there is no CPU fallback.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/skylark_b200.h"
+#include "rng.cuh"
+#include "skb_internal.h"
+
+using namespace skb;
+
+// ---------------------------------------------------------------------------
+// process-wide state
+// ---------------------------------------------------------------------------
+static std::string g_last_error;
+static thread_local cudaStream_t g_stream = nullptr;
+static int g_boost_order = SKB_ORDER_160;
+static int g_fjlt_fut = FUT_DCT;
+
+namespace skb {
+Profiler &profiler() { static Profiler p; return p; }
+struct PendingPair { KernelClass kc; cudaEvent_t e0, e1; };
+static std::vector<PendingPair> g_pending;
+
+LaunchScope::LaunchScope(KernelClass kc_, cudaStream_t st) : kc(kc_), stream(st), timed(false) {
+    Profiler &p = profiler();
+    p.launches[kc]++;
+    if (p.enabled) {
+        if (cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess) {
+            cudaEventRecord(e0, stream);
+            timed = true;
+        }
+    }
+}
+LaunchScope::~LaunchScope() {
+    if (timed) {
+        cudaEventRecord(e1, stream);
+        g_pending.push_back({kc, e0, e1});
+    }
+}
+void profiler_collect() {
+    Profiler &p = profiler();
+    for (auto &pp : g_pending) {
+        cudaEventSynchronize(pp.e1);
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, pp.e0, pp.e1) == cudaSuccess) p.ms[pp.kc] += ms;
+        cudaEventDestroy(pp.e0);
+        cudaEventDestroy(pp.e1);
+    }
+    g_pending.clear();
+}
+}  // namespace skb
+
+static const char *const k_errmsg[] = {   // base/exception.hpp:9-24
+    "Skylark failure",
+    "Skylark failed while communicating (MPI)",
+    "Skylark failed in a call to Elemental",
+    "Skylark failed due to a unsupported matrix distribution",
+    "Skylark failed in a call to CombBLAS",
+    "Skylark failed in sketching layer",
+    "Skylark failed in nla operation",
+    "Skylark failed when allocating memory in a sketch",
+    "Skylark failed in a call into the Random123 layer",
+    "Skylark failed due to a unsupported base operation",
+    "Skylark failed in I/O calls",
+    "Skylark failed because invalid parameter was passed",
+    "Skylark failed because base classes were used incorrectly",
+    "Skylark failed in ml operation"};
+
+#define SL_TRY try {
+#define SL_CATCH                                                                   \
+    }                                                                              \
+    catch (const skb::error &e) { g_last_error = e.what(); return e.code; }        \
+    catch (const std::bad_alloc &) { g_last_error = "out of host memory"; return SKB_ERR_ALLOC; } \
+    catch (const std::exception &e) { g_last_error = e.what(); return SKB_ERR_GENERIC; } \
+    return 0;
+
+static void require_device() {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        throw error(SKB_ERR_GENERIC, "libcskylark_b200: no CUDA device available; this library has "
+                                     "no CPU path");
+    }
+}
+
+struct DeviceGuard {
+    int prev = -1; bool changed = false;
+    explicit DeviceGuard(int dev) {
+        if (dev < 0) return;
+        SKB_CUDA(cudaGetDevice(&prev));
+        if (prev != dev) { SKB_CUDA(cudaSetDevice(dev)); changed = true; }
+    }
+    ~DeviceGuard() { if (changed) cudaSetDevice(prev); }
+};
+
+// ---------------------------------------------------------------------------
+// objects
+// ---------------------------------------------------------------------------
+struct sl_context_t {
+    int seed; uint64_t counter;
+    uint64_t allocate(uint64_t size) {   // base/context.hpp:94-101, randgen.hpp:64-72
+        if (size != 0 && UINT64_MAX - counter < size - 1)
+            throw error(SKB_ERR_RANDOM123, "The random number generator stream cannot supply the "
+                                           "requested number of samples without being exhausted");
+        uint64_t b = counter; counter += size; return b;
+    }
+};
+
+enum MatKind { MK_DENSE = 0, MK_SPARSE = 1 };
+struct sl_matrix_t {
+    MatKind kind; bool on_device; int device; int dtype;
+    void *data; int64_t m, n, ld;                       // dense
+    int32_t *indptr, *indices; double *values; int64_t nnz;   // sparse (m x n CSC)
+    bool struct_updated;
+};
+
+enum TType { T_JLT, T_CT, T_CWT, T_MMT, T_WZT, T_GRFT, T_LRFT, T_FJLT };
+
+struct DevState {
+    int32_t *bucket = nullptr; double *value = nullptr;
+    std::map<std::pair<size_t, size_t>, HashPlan> plans;
+    double *shifts = nullptr, *scales = nullptr;
+    double *D = nullptr; int32_t *samples = nullptr;
+    void *ws = nullptr; size_t ws_bytes = 0;
+};
+
+struct sl_sketch_transform_t {
+    TType type; std::string name;
+    int N, S;
+    int seed; uint64_t counter0;        // creation context
+    double param = 0.0;                 // C | p | sigma
+    int order, fut;
+    // stream bases (Appendix B of SURVEY.md; *_data.hpp build() functions)
+    uint64_t base0 = 0, base1 = 0, base2 = 0;
+    double scale = 1.0, outscale = 1.0;
+    std::map<int, DevState> dev;
+
+    ~sl_sketch_transform_t() {
+        for (auto &kv : dev) {
+            int prev = -1; cudaGetDevice(&prev); cudaSetDevice(kv.first);
+            DevState &d = kv.second;
+            cudaFree(d.bucket); cudaFree(d.value); cudaFree(d.shifts); cudaFree(d.scales);
+            cudaFree(d.D); cudaFree(d.samples); cudaFree(d.ws);
+            for (auto &p : d.plans) hash_free_plan(&p.second);
+            if (prev >= 0) cudaSetDevice(prev);
+        }
+    }
+    bool is_hash() const { return type == T_CWT || type == T_MMT || type == T_WZT; }
+    bool is_dense() const { return type == T_JLT || type == T_CT; }
+    bool is_rft() const { return type == T_GRFT || type == T_LRFT; }
+};
+
+static bool str2type(const char *s, TType *t) {   // capi/csketch.cpp:48-67 (sketch subset)
+    static const struct { const char *n; TType t; } tab[] = {
+        {"JLT", T_JLT}, {"CT", T_CT}, {"CWT", T_CWT}, {"MMT", T_MMT}, {"WZT", T_WZT},
+        {"GaussianRFT", T_GRFT}, {"LaplacianRFT", T_LRFT}, {"FJLT", T_FJLT}};
+    for (auto &e : tab) if (strcmp(s, e.n) == 0) { *t = e.t; return true; }
+    return false;
+}
+
+// Builds the random state the way the reference's *_data_t constructors do and
+// advances the context (counter rules: SURVEY.md Appendix B).
+static sl_sketch_transform_t *make_transform(TType type, const char *name, int n, int s,
+                                             double param, sl_context_t &ctx) {
+    if (n <= 0 || s <= 0) throw error(SKB_ERR_INVALID_PARAM, "sketch dimensions must be positive");
+    std::unique_ptr<sl_sketch_transform_t> t(new sl_sketch_transform_t());
+    t->type = type; t->name = name; t->N = n; t->S = s;
+    t->seed = ctx.seed; t->counter0 = ctx.counter; t->param = param;
+    t->order = g_boost_order; t->fut = g_fjlt_fut;
+    const uint64_t N = (uint64_t)n, S = (uint64_t)s;
+    switch (type) {
+    case T_CWT: case T_MMT:           // hash_transform_data.hpp:64-76
+        t->base0 = ctx.allocate(N); t->base1 = ctx.allocate(N); break;
+    case T_WZT:                       // WZT_data.hpp:49-52, 110-126
+        if (param < 1 || 2 < param)
+            throw error(SKB_ERR_SKETCH, "WZT parameter p has to be in (1, 2)");
+        t->base0 = ctx.allocate(N); t->base1 = ctx.allocate(N); t->base2 = ctx.allocate(N); break;
+    case T_JLT:                       // JLT_data.hpp:27-32
+        t->scale = sqrt(1.0 / (double)s); t->base0 = ctx.allocate(N * S); break;
+    case T_CT:                        // CT_data.hpp:35-41
+        t->scale = param / (double)s; t->base0 = ctx.allocate(N * S); break;
+    case T_GRFT: case T_LRFT:         // RFT_data.hpp:71-89, 115-123
+        t->scale = 1.0 / param; t->outscale = sqrt(2.0 / s);
+        t->base0 = ctx.allocate(N * S); t->base1 = ctx.allocate(S); break;
+    case T_FJLT:                      // FJLT_data.hpp:79-86 + RFUT_data.hpp:27-31 (overlap kept)
+        t->base0 = ctx.counter; ctx.allocate(S); break;
+    }
+    return t.release();
+}
+
+static DevState &dev_state(sl_sketch_transform_t *t, int device) { return t->dev[device]; }
+
+static void ensure_ws(DevState &d, size_t bytes) {
+    if (d.ws_bytes >= bytes) return;
+    if (d.ws) { SKB_CUDA(cudaStreamSynchronize(g_stream)); cudaFree(d.ws); d.ws = nullptr; d.ws_bytes = 0; }
+    SKB_CUDA(cudaMalloc(&d.ws, bytes));
+    d.ws_bytes = bytes;
+}
+
+static void ensure_hash_tables(sl_sketch_transform_t *t, DevState &d) {
+    if (d.bucket) return;
+    SKB_CUDA(cudaMalloc(&d.bucket, (size_t)t->N * sizeof(int32_t)));
+    SKB_CUDA(cudaMalloc(&d.value, (size_t)t->N * sizeof(double)));
+    int kind = t->type == T_CWT ? HV_RADEMACHER : t->type == T_MMT ? HV_CAUCHY : HV_WZT;
+    hash_build_tables(t->seed, t->base0, t->base1, t->base2, 0, (size_t)t->N, (uint64_t)t->S, kind,
+                      t->param, t->order, d.bucket, d.value, g_stream);
+}
+
+static void ensure_rft_tables(sl_sketch_transform_t *t, DevState &d) {
+    if (d.shifts) return;
+    // shifts ~ uniform_real(0, 2*pi) (RFT_data.hpp:79-82); scales = 1 (:86).  Integer-exact
+    // arithmetic, so generating on the host and copying is identical to the device.
+    std::vector<double> sh((size_t)t->S), sc((size_t)t->S, 1.0);
+    const double pi = 3.141592653589793238462643383279502884;   // boost::math::constants::pi
+    for (int i = 0; i < t->S; i++) {
+        MicroUrng u(seed_to_key(t->seed), t->base1 + (uint64_t)i);
+        sh[i] = boost_uniform_real(u, 0.0, 2 * pi);
+    }
+    SKB_CUDA(cudaMalloc(&d.shifts, sh.size() * sizeof(double)));
+    SKB_CUDA(cudaMalloc(&d.scales, sc.size() * sizeof(double)));
+    SKB_CUDA(cudaMemcpy(d.shifts, sh.data(), sh.size() * sizeof(double), cudaMemcpyHostToDevice));
+    SKB_CUDA(cudaMemcpy(d.scales, sc.data(), sc.size() * sizeof(double), cudaMemcpyHostToDevice));
+}
+
+static void ensure_fjlt_tables(sl_sketch_transform_t *t, DevState &d) {
+    if (d.D) return;
+    SKB_CUDA(cudaMalloc(&d.D, (size_t)t->N * sizeof(double)));
+    SKB_CUDA(cudaMalloc(&d.samples, (size_t)t->S * sizeof(int32_t)));
+    fjlt_build_tables(t->seed, t->base0, (size_t)t->N, (size_t)t->S, t->order, d.D, d.samples,
+                      g_stream);
+}
+
+static DenseParams dense_params(const sl_sketch_transform_t *t) {
+    DenseParams p;
+    p.seed = t->seed; p.base = t->base0; p.scale = t->scale;
+    p.dist = (t->type == T_JLT || t->type == T_GRFT) ? DD_NORMAL : DD_CAUCHY;
+    p.N = (size_t)t->N; p.S = (size_t)t->S;
+    return p;
+}
+
+// ---------------------------------------------------------------------------
+// apply on device-resident operands
+// ---------------------------------------------------------------------------
+static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const sl_matrix_t *SA,
+                         int dim, int64_t offset, bool shard) {
+    const bool colwise = dim == SL_COLUMNWISE;
+    const int64_t sk = colwise ? A->m : A->n;        // sketched extent present in A
+    const int64_t other = colwise ? A->n : A->m;
+    if (offset < 0 || offset + sk > t->N || (!shard && sk != t->N))
+        throw error(SKB_ERR_INVALID_PARAM, "apply: sketched dimension of A does not match N");
+    if (SA->kind != MK_DENSE) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse output is not supported");
+    const int64_t sa_sk = colwise ? SA->m : SA->n, sa_other = colwise ? SA->n : SA->m;
+    if (sa_sk != t->S || sa_other != other)
+        throw error(SKB_ERR_INVALID_PARAM, "apply: SA has the wrong shape");
+    if (A->dtype != SA->dtype) throw error(SKB_ERR_INVALID_PARAM, "apply: A and SA differ in dtype");
+    const bool f32 = A->dtype == SL_DTYPE_F32;
+    if (f32 && !(t->is_dense() || t->is_rft()))
+        throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: float32 is supported for JLT/CT/RFT only");
+    DevState &d = dev_state(t, A->device);
+    cudaStream_t st = g_stream;
+    const bool layout_rows = !colwise;   // rowwise on column-major == contiguous rows per index
+
+    if (A->kind == MK_SPARSE) {
+        if (!t->is_hash()) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse input is supported for CWT/MMT/WZT only");
+        ensure_hash_tables(t, d);
+        const int32_t *b = d.bucket + offset; const double *v = d.value + offset;
+        if (colwise)
+            hash_apply_csc_columnwise(A->indptr, A->indices, A->values, (size_t)A->n, b, v,
+                                      (double *)SA->data, (size_t)SA->ld, t->S, st);
+        else
+            hash_apply_csc_rowwise(A->indptr, A->indices, A->values, (size_t)A->m, (size_t)A->n, b,
+                                   v, (double *)SA->data, (size_t)SA->ld, t->S, st);
+        return;
+    }
+    if (t->is_hash()) {
+        ensure_hash_tables(t, d);
+        if (layout_rows) {
+            auto key = std::make_pair((size_t)offset, (size_t)sk);
+            auto it = d.plans.find(key);
+            if (it == d.plans.end()) {
+                HashPlan plan;
+                hash_build_plan(d.bucket + offset, (size_t)sk, t->S, &plan, st);
+                it = d.plans.emplace(key, plan).first;
+            }
+            hash_apply_rows((const double *)A->data, (size_t)A->ld, (size_t)other, it->second,
+                            d.value + offset, (double *)SA->data, (size_t)SA->ld, t->S, st);
+        } else {
+            hash_apply_cols((const double *)A->data, (size_t)A->ld, (size_t)sk, (size_t)other,
+                            d.bucket + offset, d.value + offset, (double *)SA->data,
+                            (size_t)SA->ld, t->S, st);
+        }
+        return;
+    }
+    if (t->is_dense() || t->is_rft()) {
+        DenseParams p = dense_params(t);
+        RftEpilogue epi;
+        if (t->is_rft()) {
+            if (shard && sk != t->N)
+                throw error(SKB_ERR_INVALID_USAGE, "apply: RFT cannot be applied to a shard of the "
+                                                   "sketched dimension (the cosine is not additive)");
+            ensure_rft_tables(t, d);
+            epi.scales = d.scales; epi.shifts = d.shifts; epi.outscale = t->outscale;
+        }
+        size_t need = dense_workspace_bytes(p, (size_t)sk, layout_rows, f32, (size_t)other,
+                                            (size_t)SA->ld);
+        ensure_ws(d, need);
+        dense_apply(p, layout_rows, f32, A->data, (size_t)A->ld, (size_t)other, (size_t)offset,
+                    (size_t)sk, SA->data, (size_t)SA->ld, epi, d.ws, d.ws_bytes, st);
+        return;
+    }
+    // FJLT
+    if (shard && sk != t->N)
+        throw error(SKB_ERR_INVALID_USAGE, "apply: FJLT needs the whole sketched dimension");
+    ensure_fjlt_tables(t, d);
+    size_t need = fjlt_workspace_bytes((size_t)t->N, (size_t)other, t->fut);
+    ensure_ws(d, need);
+    fjlt_apply(t->fut, layout_rows, (const double *)A->data, (size_t)A->ld, (size_t)t->N,
+               (size_t)other, d.D, d.samples, (size_t)t->S, (double *)SA->data, (size_t)SA->ld,
+               d.ws, d.ws_bytes, st);
+}
+
+// Host operands: stage through device memory (copies inside the call, synchronous).
+static void apply_any(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA, int dim,
+                      int64_t offset, bool shard) {
+    require_device();
+    if (dim != SL_COLUMNWISE && dim != SL_ROWWISE)
+        throw error(SKB_ERR_INVALID_PARAM, "apply: dim must be SL_COLUMNWISE or SL_ROWWISE");
+    if (A->on_device != SA->on_device)
+        throw error(SKB_ERR_INVALID_USAGE, "apply: A and SA must both be host or both be device buffers");
+    if (A->on_device) {
+        if (A->device != SA->device) throw error(SKB_ERR_INVALID_USAGE, "apply: A and SA are on different devices");
+        DeviceGuard g(A->device);
+        apply_device(t, A, SA, dim, offset, shard);
+        return;
+    }
+    if (SA->kind != MK_DENSE) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse output is not supported");
+    int device = 0;
+    SKB_CUDA(cudaGetDevice(&device));
+    cudaStream_t st = g_stream;
+    sl_matrix_t dA = *A, dSA = *SA;
+    dA.on_device = dSA.on_device = true; dA.device = dSA.device = device;
+    void *bufs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    try {
+        const size_t esz = A->dtype == SL_DTYPE_F32 ? 4 : 8;
+        if (A->kind == MK_DENSE) {
+            size_t bytes = (size_t)A->ld * (size_t)A->n * esz;
+            SKB_CUDA(cudaMalloc(&bufs[0], bytes ? bytes : 16));
+            SKB_CUDA(cudaMemcpyAsync(bufs[0], A->data, bytes, cudaMemcpyHostToDevice, st));
+            dA.data = bufs[0];
+        } else {
+            size_t pb = (size_t)(A->n + 1) * 4, ib = (size_t)A->nnz * 4, vb = (size_t)A->nnz * 8;
+            SKB_CUDA(cudaMalloc(&bufs[0], pb));
+            SKB_CUDA(cudaMalloc(&bufs[1], ib ? ib : 16));
+            SKB_CUDA(cudaMalloc(&bufs[2], vb ? vb : 16));
+            SKB_CUDA(cudaMemcpyAsync(bufs[0], A->indptr, pb, cudaMemcpyHostToDevice, st));
+            SKB_CUDA(cudaMemcpyAsync(bufs[1], A->indices, ib, cudaMemcpyHostToDevice, st));
+            SKB_CUDA(cudaMemcpyAsync(bufs[2], A->values, vb, cudaMemcpyHostToDevice, st));
+            dA.indptr = (int32_t *)bufs[0]; dA.indices = (int32_t *)bufs[1]; dA.values = (double *)bufs[2];
+        }
+        size_t obytes = (size_t)SA->ld * (size_t)SA->n * (SA->dtype == SL_DTYPE_F32 ? 4 : 8);
+        SKB_CUDA(cudaMalloc(&bufs[3], obytes ? obytes : 16));
+        dSA.data = bufs[3];
+        apply_device(t, &dA, &dSA, dim, offset, shard);
+        SKB_CUDA(cudaMemcpyAsync(SA->data, bufs[3], obytes, cudaMemcpyDeviceToHost, st));
+        SKB_CUDA(cudaStreamSynchronize(st));
+    } catch (...) {
+        cudaStreamSynchronize(st);
+        for (void *b : bufs) cudaFree(b);
+        throw;
+    }
+    for (void *b : bufs) cudaFree(b);
+}
+
+// ---------------------------------------------------------------------------
+// tiny JSON (boost::property_tree::write_json style: every value is a string)
+// ---------------------------------------------------------------------------
+static void json_skip(const char *&p) { while (*p == ' ' || *p == '\n' || *p == '\t' || *p == '\r') p++; }
+static std::string json_string(const char *&p) {
+    std::string s;
+    if (*p != '"') throw error(SKB_ERR_IO, "malformed JSON: expected string");
+    p++;
+    while (*p && *p != '"') { if (*p == '\\' && p[1]) p++; s.push_back(*p++); }
+    if (*p != '"') throw error(SKB_ERR_IO, "malformed JSON: unterminated string");
+    p++;
+    return s;
+}
+static void json_object(const char *&p, const std::string &prefix, std::map<std::string, std::string> &out) {
+    json_skip(p);
+    if (*p != '{') throw error(SKB_ERR_IO, "malformed JSON: expected object");
+    p++;
+    for (;;) {
+        json_skip(p);
+        if (*p == '}') { p++; return; }
+        std::string key = json_string(p);
+        json_skip(p);
+        if (*p != ':') throw error(SKB_ERR_IO, "malformed JSON: expected ':'");
+        p++;
+        json_skip(p);
+        if (*p == '{') json_object(p, prefix + key + ".", out);
+        else if (*p == '"') out[prefix + key] = json_string(p);
+        else {
+            std::string v;
+            while (*p && *p != ',' && *p != '}' && *p != ' ' && *p != '\n' && *p != '\r' && *p != '\t') v.push_back(*p++);
+            out[prefix + key] = v;
+        }
+        json_skip(p);
+        if (*p == ',') { p++; continue; }
+        if (*p == '}') { p++; return; }
+        throw error(SKB_ERR_IO, "malformed JSON: expected ',' or '}'");
+    }
+}
+static const std::string &json_get(const std::map<std::string, std::string> &m, const char *k) {
+    auto it = m.find(k);
+    if (it == m.end()) throw error(SKB_ERR_IO, std::string("serialized sketch lacks key ") + k);
+    return it->second;
+}
+
+static char *dup_cstr(const std::string &s) {
+    char *r = (char *)malloc(s.size() + 1);
+    if (r) memcpy(r, s.c_str(), s.size() + 1);
+    return r;
+}
+
+static sl_matrix_t *as_matrix(void *p) {
+    if (!p) throw error(SKB_ERR_INVALID_PARAM, "null matrix handle");
+    return (sl_matrix_t *)p;
+}
+
+static void check_type_string(const char *s, const sl_matrix_t *M) {
+    if (!s) throw error(SKB_ERR_INVALID_PARAM, "null matrix type string");
+    bool dense = strcmp(s, "Matrix") == 0, sparse = strcmp(s, "SparseMatrix") == 0;
+    if (!dense && !sparse)
+        throw error(SKB_ERR_UNSUPPORTED_DIST, std::string("unsupported matrix type: ") + s);
+    if ((dense && M->kind != MK_DENSE) || (sparse && M->kind != MK_SPARSE))
+        throw error(SKB_ERR_INVALID_PARAM, "matrix type string does not match the wrapped object");
+}
+
+// ---------------------------------------------------------------------------
+// exported functions
+// ---------------------------------------------------------------------------
+extern "C" {
+
+char *sl_supported_sketch_transforms(void) {
+    static char s[] =
+        "(\"JLT\",\"Matrix\",\"Matrix\") "
+        "(\"CT\",\"Matrix\",\"Matrix\") "
+        "(\"FJLT\",\"Matrix\",\"Matrix\") "
+        "(\"CWT\",\"Matrix\",\"Matrix\") (\"CWT\",\"SparseMatrix\",\"Matrix\") "
+        "(\"MMT\",\"Matrix\",\"Matrix\") (\"MMT\",\"SparseMatrix\",\"Matrix\") "
+        "(\"WZT\",\"Matrix\",\"Matrix\") (\"WZT\",\"SparseMatrix\",\"Matrix\") "
+        "(\"GaussianRFT\",\"Matrix\",\"Matrix\") "
+        "(\"LaplacianRFT\",\"Matrix\",\"Matrix\") ";
+    return s;
+}
+
+const char *sl_strerror(const int errorcode) {
+    if (errorcode < 100 || errorcode > 113) return "Unknown error code";
+    return k_errmsg[errorcode - 100];
+}
+
+bool sl_has_elemental(void) { return false; }
+bool sl_has_combblas(void) { return false; }
+
+int sl_create_default_context(int seed, sl_context_t **ctxt) {
+    SL_TRY
+    *ctxt = new sl_context_t{seed, 0};
+    SL_CATCH
+}
+int sl_create_context(int seed, void *, sl_context_t **ctxt) {
+    return sl_create_default_context(seed, ctxt);
+}
+int sl_create_context_at(int seed, uint64_t counter, sl_context_t **ctxt) {
+    SL_TRY
+    *ctxt = new sl_context_t{seed, counter};
+    SL_CATCH
+}
+int sl_free_context(sl_context_t *ctxt) { delete ctxt; return 0; }
+int sl_context_get_seed(sl_context_t *ctxt, int *seed) { *seed = ctxt->seed; return 0; }
+int sl_context_get_counter(sl_context_t *ctxt, uint64_t *counter) { *counter = ctxt->counter; return 0; }
+
+int sl_create_sketch_transform(sl_context_t *ctxt, char *type_, int n, int s,
+                               sl_sketch_transform_t **sketch, ...) {
+    TType type;
+    if (!type_ || !str2type(type_, &type)) {
+        g_last_error = std::string("unknown sketch transform type: ") + (type_ ? type_ : "(null)");
+        return SKB_ERR_INVALID_PARAM;      // capi/csketch.cpp:385-386
+    }
+    double p1 = 0.0;
+    if (type == T_CT || type == T_WZT || type == T_GRFT || type == T_LRFT) {
+        va_list argp;
+        va_start(argp, sketch);
+        p1 = va_arg(argp, double);
+        va_end(argp);
+    }
+    SL_TRY
+    if (!ctxt) throw error(SKB_ERR_INVALID_PARAM, "null context");
+    *sketch = make_transform(type, type_, n, s, p1, *ctxt);
+    SL_CATCH
+}
+
+int sl_serialize_sketch_transform(const sl_sketch_transform_t *t, char **data) {
+    SL_TRY
+    char buf[1024];
+    std::string extra;
+    if (t->type == T_CT) { snprintf(buf, sizeof buf, ",\n    \"C\": \"%.17g\"", t->param); extra = buf; }
+    if (t->type == T_WZT) { snprintf(buf, sizeof buf, ",\n    \"P\": \"%.17g\"", t->param); extra = buf; }
+    if (t->is_rft()) { snprintf(buf, sizeof buf, ",\n    \"sigma\": \"%.17g\"", t->param); extra = buf; }
+    snprintf(buf, sizeof buf,
+             "{\n    \"skylark_object_type\": \"sketch\",\n    \"sketch_type\": \"%s\",\n"
+             "    \"skylark_version\": \"0.20\",\n    \"N\": \"%d\",\n    \"S\": \"%d\",\n"
+             "    \"creation_context\": {\n        \"skylark_object_type\": \"context\",\n"
+             "        \"skylark_version\": \"0.20\",\n        \"seed\": \"%d\",\n"
+             "        \"counter\": \"%llu\"\n    }%s\n}\n",
+             t->name.c_str(), t->N, t->S, t->seed, (unsigned long long)t->counter0, extra.c_str());
+    *data = dup_cstr(buf);
+    if (!*data) throw std::bad_alloc();
+    SL_CATCH
+}
+
+int sl_deserialize_sketch_transform(const char *data, sl_sketch_transform_t **sketch) {
+    SL_TRY
+    if (!data) throw error(SKB_ERR_INVALID_PARAM, "null JSON");
+    std::map<std::string, std::string> kv;
+    const char *p = data;
+    json_object(p, "", kv);
+    const std::string &name = json_get(kv, "sketch_type");
+    TType type;
+    if (!str2type(name.c_str(), &type))
+        throw error(SKB_ERR_SKETCH, "cannot deserialize sketch type " + name);   // sketch_add.hpp:15-54
+    int n = (int)strtod(json_get(kv, "N").c_str(), nullptr);
+    int s = (int)strtod(json_get(kv, "S").c_str(), nullptr);
+    sl_context_t ctx;
+    ctx.seed = (int)strtol(json_get(kv, "creation_context.seed").c_str(), nullptr, 10);
+    ctx.counter = strtoull(json_get(kv, "creation_context.counter").c_str(), nullptr, 10);
+    double p1 = 0.0;
+    if (type == T_CT) p1 = strtod(json_get(kv, "C").c_str(), nullptr);
+    if (type == T_WZT) p1 = strtod(json_get(kv, "P").c_str(), nullptr);
+    if (type == T_GRFT || type == T_LRFT) p1 = strtod(json_get(kv, "sigma").c_str(), nullptr);
+    *sketch = make_transform(type, name.c_str(), n, s, p1, ctx);   // replays the RNG (CWT_data.hpp:48-52)
+    SL_CATCH
+}
+
+int sl_free_sketch_transform(sl_sketch_transform_t *S) { delete S; return 0; }
+
+int sl_apply_sketch_transform(sl_sketch_transform_t *S, char *input_type, void *A,
+                              char *output_type, void *SA, int dim) {
+    SL_TRY
+    if (!S) throw error(SKB_ERR_INVALID_PARAM, "null sketch transform");
+    sl_matrix_t *a = as_matrix(A), *sa = as_matrix(SA);
+    check_type_string(input_type, a);
+    check_type_string(output_type, sa);
+    apply_any(S, a, sa, dim, 0, false);
+    SL_CATCH
+}
+
+int sl_apply_sketch_transform_shard(sl_sketch_transform_t *S, char *input_type, void *A,
+                                    char *output_type, void *SA, int dim, int64_t index_offset) {
+    SL_TRY
+    if (!S) throw error(SKB_ERR_INVALID_PARAM, "null sketch transform");
+    sl_matrix_t *a = as_matrix(A), *sa = as_matrix(SA);
+    check_type_string(input_type, a);
+    check_type_string(output_type, sa);
+    apply_any(S, a, sa, dim, index_offset, true);
+    SL_CATCH
+}
+
+int sl_wrap_raw_matrix(double *data, int m, int n, void **A) {
+    SL_TRY
+    sl_matrix_t *M = new sl_matrix_t();
+    M->kind = MK_DENSE; M->on_device = false; M->device = -1; M->dtype = SL_DTYPE_F64;
+    M->data = data; M->m = m; M->n = n; M->ld = m;
+    *A = M;
+    SL_CATCH
+}
+int sl_free_raw_matrix_wrap(void *A_) { delete (sl_matrix_t *)A_; return 0; }
+
+int sl_wrap_device_matrix(void *dptr, int64_t m, int64_t n, int64_t ld, int dtype, int device,
+                          void **A) {
+    SL_TRY
+    if (m < 0 || n < 0 || ld < m || (dtype != SL_DTYPE_F64 && dtype != SL_DTYPE_F32))
+        throw error(SKB_ERR_INVALID_PARAM, "sl_wrap_device_matrix: bad shape or dtype");
+    sl_matrix_t *M = new sl_matrix_t();
+    M->kind = MK_DENSE; M->on_device = true; M->device = device; M->dtype = dtype;
+    M->data = dptr; M->m = m; M->n = n; M->ld = ld;
+    *A = M;
+    SL_CATCH
+}
+
+int sl_wrap_raw_sp_matrix(int *indptr, int *ind, double *data, int nnz, int n_rows, int n_cols,
+                          void **A) {
+    SL_TRY
+    sl_matrix_t *M = new sl_matrix_t();
+    M->kind = MK_SPARSE; M->on_device = false; M->device = -1; M->dtype = SL_DTYPE_F64;
+    M->indptr = indptr; M->indices = ind; M->values = data; M->nnz = nnz; M->m = n_rows; M->n = n_cols;
+    M->struct_updated = false;
+    *A = M;
+    SL_CATCH
+}
+int sl_wrap_device_sp_matrix(int32_t *indptr, int32_t *ind, double *data, int64_t nnz,
+                             int64_t n_rows, int64_t n_cols, int device, void **A) {
+    SL_TRY
+    sl_matrix_t *M = new sl_matrix_t();
+    M->kind = MK_SPARSE; M->on_device = true; M->device = device; M->dtype = SL_DTYPE_F64;
+    M->indptr = indptr; M->indices = ind; M->values = data; M->nnz = nnz; M->m = n_rows; M->n = n_cols;
+    M->struct_updated = false;
+    *A = M;
+    SL_CATCH
+}
+int sl_free_raw_sp_matrix_wrap(void *A_) { delete (sl_matrix_t *)A_; return 0; }
+int sl_raw_sp_matrix_struct_updated(void *A_, bool *u) { *u = ((sl_matrix_t *)A_)->struct_updated; return 0; }
+int sl_raw_sp_matrix_reset_update_flag(void *A_) { ((sl_matrix_t *)A_)->struct_updated = false; return 0; }
+int sl_raw_sp_matrix_nnz(void *A_, int *nnz) { *nnz = (int)((sl_matrix_t *)A_)->nnz; return 0; }
+int sl_raw_sp_matrix_height(void *A_, int *h) { *h = (int)((sl_matrix_t *)A_)->m; return 0; }
+int sl_raw_sp_matrix_width(void *A_, int *w) { *w = (int)((sl_matrix_t *)A_)->n; return 0; }
+int sl_raw_sp_matrix_data(void *A_, int32_t *indptr, int32_t *indices, double *values) {
+    SL_TRY
+    sl_matrix_t *M = as_matrix(A_);
+    if (M->on_device) throw error(SKB_ERR_INVALID_USAGE, "sl_raw_sp_matrix_data: device matrix");
+    memcpy(indptr, M->indptr, (size_t)(M->n + 1) * sizeof(int32_t));
+    memcpy(indices, M->indices, (size_t)M->nnz * sizeof(int32_t));
+    memcpy(values, M->values, (size_t)M->nnz * sizeof(double));
+    SL_CATCH
+}
+
+void sl_get_exception_info(char **info) { *info = dup_cstr(g_last_error); }
+void sl_print_exception_trace(void) { fprintf(stderr, "%s\n", g_last_error.c_str()); }
+
+int sl_set_stream(void *cuda_stream) { g_stream = (cudaStream_t)cuda_stream; return 0; }
+
+int sl_set_option(const char *key, const char *value) {
+    SL_TRY
+    if (!key || !value) throw error(SKB_ERR_INVALID_PARAM, "null option");
+    if (strcmp(key, "boost_order") == 0) {
+        if (strcmp(value, "160") == 0) g_boost_order = SKB_ORDER_160;
+        else if (strcmp(value, "155") == 0) g_boost_order = SKB_ORDER_155;
+        else throw error(SKB_ERR_INVALID_PARAM, "boost_order must be 160 or 155");
+    } else if (strcmp(key, "fjlt_fut") == 0) {
+        if (strcmp(value, "dct") == 0) g_fjlt_fut = FUT_DCT;
+        else if (strcmp(value, "wht") == 0) g_fjlt_fut = FUT_WHT;
+        else throw error(SKB_ERR_INVALID_PARAM, "fjlt_fut must be dct or wht");
+    } else throw error(SKB_ERR_INVALID_PARAM, std::string("unknown option ") + key);
+    SL_CATCH
+}
+
+int sl_sketch_export(sl_sketch_transform_t *t, const char *what, int64_t first, int64_t count,
+                     void *host_out) {
+    SL_TRY
+    require_device();
+    if (!t || !what || first < 0 || count < 0) throw error(SKB_ERR_INVALID_PARAM, "sl_sketch_export: bad argument");
+    int device = 0;
+    SKB_CUDA(cudaGetDevice(&device));
+    DevState &d = dev_state(t, device);
+    cudaStream_t st = g_stream;
+    auto copy_f64 = [&](const double *src, int64_t limit) {
+        if (first + count > limit) throw error(SKB_ERR_RANDOM123, "Index is out of bounds");
+        SKB_CUDA(cudaMemcpyAsync(host_out, src + first, (size_t)count * 8, cudaMemcpyDeviceToHost, st));
+        SKB_CUDA(cudaStreamSynchronize(st));
+    };
+    auto copy_i32_as_i64 = [&](const int32_t *src, int64_t limit) {
+        if (first + count > limit) throw error(SKB_ERR_RANDOM123, "Index is out of bounds");
+        std::vector<int32_t> tmp((size_t)count);
+        SKB_CUDA(cudaMemcpyAsync(tmp.data(), src + first, (size_t)count * 4, cudaMemcpyDeviceToHost, st));
+        SKB_CUDA(cudaStreamSynchronize(st));
+        for (int64_t i = 0; i < count; i++) ((int64_t *)host_out)[i] = tmp[(size_t)i];
+    };
+    if (strcmp(what, "row_idx") == 0 && t->is_hash()) { ensure_hash_tables(t, d); copy_i32_as_i64(d.bucket, t->N); }
+    else if (strcmp(what, "row_value") == 0 && t->is_hash()) { ensure_hash_tables(t, d); copy_f64(d.value, t->N); }
+    else if (strcmp(what, "D") == 0 && t->type == T_FJLT) { ensure_fjlt_tables(t, d); copy_f64(d.D, t->N); }
+    else if (strcmp(what, "samples") == 0 && t->type == T_FJLT) { ensure_fjlt_tables(t, d); copy_i32_as_i64(d.samples, t->S); }
+    else if (strcmp(what, "shifts") == 0 && t->is_rft()) { ensure_rft_tables(t, d); copy_f64(d.shifts, t->S); }
+    else if (strcmp(what, "scales") == 0 && t->is_rft()) { ensure_rft_tables(t, d); copy_f64(d.scales, t->S); }
+    else throw error(SKB_ERR_INVALID_PARAM, std::string("sl_sketch_export: no table '") + what + "' for " + t->name);
+    SL_CATCH
+}
+
+int sl_sketch_export_dense(sl_sketch_transform_t *t, int64_t i0, int64_t j0, int64_t h, int64_t w,
+                           double *host_out) {
+    SL_TRY
+    require_device();
+    if (!t || !(t->is_dense() || t->is_rft())) throw error(SKB_ERR_INVALID_PARAM, "sl_sketch_export_dense: not a dense transform");
+    if (i0 < 0 || j0 < 0 || h < 0 || w < 0 || i0 + h > t->S || j0 + w > t->N)
+        throw error(SKB_ERR_RANDOM123, "Index is out of bounds");
+    double *buf = nullptr;
+    size_t bytes = (size_t)h * (size_t)w * 8;
+    SKB_CUDA(cudaMalloc(&buf, bytes ? bytes : 16));
+    try {
+        dense_export_block(dense_params(t), (size_t)i0, (size_t)j0, (size_t)h, (size_t)w, buf, g_stream);
+        SKB_CUDA(cudaMemcpyAsync(host_out, buf, bytes, cudaMemcpyDeviceToHost, g_stream));
+        SKB_CUDA(cudaStreamSynchronize(g_stream));
+    } catch (...) { cudaFree(buf); throw; }
+    cudaFree(buf);
+    SL_CATCH
+}
+
+}  // extern "C"
+
+__global__ void k_raw_draws(uint64_t key, uint64_t base, size_t count, uint64_t *first, uint64_t *second) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    MicroUrng u(key, base + t);
+    first[t] = u.next();
+    second[t] = u.next();
+}
+
+extern "C" {
+
+int sl_rng_export_raw(int seed, uint64_t base, int64_t count, uint64_t *first, uint64_t *second) {
+    SL_TRY
+    require_device();
+    if (count < 0) throw error(SKB_ERR_INVALID_PARAM, "negative count");
+    if (count == 0) return 0;
+    uint64_t *buf = nullptr;
+    SKB_CUDA(cudaMalloc(&buf, (size_t)count * 16));
+    try {
+        {
+            LaunchScope ls(KC_TABLES, g_stream);
+            k_raw_draws<<<(unsigned)((count + 255) / 256), 256, 0, g_stream>>>(
+                seed_to_key(seed), base, (size_t)count, buf, buf + count);
+        }
+        SKB_CUDA(cudaGetLastError());
+        SKB_CUDA(cudaMemcpyAsync(first, buf, (size_t)count * 8, cudaMemcpyDeviceToHost, g_stream));
+        SKB_CUDA(cudaMemcpyAsync(second, buf + count, (size_t)count * 8, cudaMemcpyDeviceToHost, g_stream));
+        SKB_CUDA(cudaStreamSynchronize(g_stream));
+    } catch (...) { cudaFree(buf); throw; }
+    cudaFree(buf);
+    SL_CATCH
+}
+
+int sl_profile_enable(int on) { profiler().enabled = on != 0; return 0; }
+int sl_profile_reset(void) {
+    profiler_collect();
+    Profiler &p = profiler();
+    for (int i = 0; i < KC_COUNT; i++) { p.launches[i] = 0; p.ms[i] = 0; }
+    return 0;
+}
+int sl_profile_read(unsigned long long launches[SL_KERNEL_CLASSES], double ms[SL_KERNEL_CLASSES]) {
+    profiler_collect();
+    Profiler &p = profiler();
+    for (int i = 0; i < KC_COUNT; i++) { launches[i] = p.launches[i]; ms[i] = p.ms[i]; }
+    return 0;
+}
+
+int sl_host_alloc_pinned(size_t bytes, void **ptr) {
+    SL_TRY
+    require_device();
+    SKB_CUDA(cudaHostAlloc(ptr, bytes ? bytes : 16, cudaHostAllocDefault));
+    SL_CATCH
+}
+int sl_host_free_pinned(void *ptr) { cudaFreeHost(ptr); return 0; }
+int sl_device_count(int *count) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }
+    *count = n;
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,431 @@
+// Dense sketches (JLT / CT) and random Fourier features (Gaussian / Laplacian RFT).
+//
+// Reference loops replaced:
+//   realize_matrix_view                 sketch/dense_transform_data.hpp:79-101
+//   local apply (Gemm)                  sketch/dense_transform_Elemental_local.hpp:79-111
+//   row-sharded inner-panel apply       sketch/dense_transform_Elemental_coldist_star.hpp:200-229
+//   RFT epilogue                        sketch/RFT_Elemental.hpp:94-117, 135-158
+//
+// B200 design.  S is never stored: entry S[i,k] = scale * sample(base + k*S + i) is
+// regenerated from the Threefry2x64-13 counter stream.  A panel of KC input indices
+// (KC*S variates, a contiguous range of the stream) is generated ONCE into an
+// L2-resident scratch buffer by k_gen_panel and consumed by a stream-K FP64 tensor
+// core GEMM (mma.sync m8n8k4 f64 = DMMA; sm_100 has no tcgen05 path for FP64).
+// Generating inside the GEMM tile loop would repeat every Box-Muller d/128 times
+// (8x at d = 1024); staging through L2 costs 16 bytes of L2 traffic per variate
+// instead and keeps the FP64 pipe for the contraction.
+//   * CTA tile 128(i) x 128(j) x 16(k), 8 warps (2 x 4), warp tile 64 x 32,
+//     accumulators in registers (64 doubles / thread), 4-stage cp.async pipeline;
+//   * shared tiles padded so that the 64-bit fragment loads are conflict free
+//     (row stride = 4 mod 16 doubles);
+//   * stream-K: the (tile, k-step) space of one launch is cut into gridDim equal
+//     contiguous ranges, one per SM, so 256 tiles on 148 SMs lose nothing to wave
+//     quantisation; partial tiles are flushed with red.global.add.f64;
+//   * the RFT epilogue outscale*cos(scale_i*acc+shift_i) is fused into the flush
+//     when a CTA owns the whole contraction of a tile (the rowwise feature-map case).
+#include <cstdio>
+
+#include "rng.cuh"
+#include "skb_internal.h"
+
+namespace skb {
+
+// ---------------------------------------------------------------------------
+// Panel generation (K5a).  P[e] = scale * sample(base + first + e), e < count.
+// ---------------------------------------------------------------------------
+template <int DIST>
+__global__ void __launch_bounds__(256)
+k_gen_panel(uint64_t key, uint64_t stream0, size_t count, double scale, double *__restrict__ P) {
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < count; e += stride) {
+        double v = DIST == DD_NORMAL ? normal_at(key, stream0 + e) : cauchy_at(key, stream0 + e);
+        P[e] = __dmul_rn(scale, v);
+    }
+}
+
+void dense_generate_panel(const DenseParams &p, size_t k0, size_t kc, double *panel,
+                          cudaStream_t st) {
+    size_t count = kc * p.S;
+    if (count == 0) return;
+    uint64_t stream0 = p.base + (uint64_t)k0 * p.S;
+    size_t blocks = (count + 255) / 256;
+    size_t cap = (size_t)148 * 16;
+    if (blocks > cap) blocks = cap;
+    LaunchScope ls(KC_GEN, st);
+    if (p.dist == DD_NORMAL)
+        k_gen_panel<DD_NORMAL><<<(unsigned)blocks, 256, 0, st>>>(seed_to_key(p.seed), stream0,
+                                                                 count, p.scale, panel);
+    else
+        k_gen_panel<DD_CAUCHY><<<(unsigned)blocks, 256, 0, st>>>(seed_to_key(p.seed), stream0,
+                                                                 count, p.scale, panel);
+    SKB_CUDA(cudaGetLastError());
+}
+
+// K0 for tests: S[i0:i0+h, j0:j0+w] column-major
+template <int DIST>
+__global__ void k_export_block(uint64_t key, uint64_t base, size_t S, double scale, size_t i0,
+                               size_t j0, size_t h, size_t w, double *__restrict__ out) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= h * w) return;
+    size_t i = t % h, j = t / h;
+    uint64_t idx = base + (uint64_t)(j0 + j) * S + (i0 + i);
+    double v = DIST == DD_NORMAL ? normal_at(key, idx) : cauchy_at(key, idx);
+    out[t] = __dmul_rn(scale, v);
+}
+
+void dense_export_block(const DenseParams &p, size_t i0, size_t j0, size_t h, size_t w,
+                        double *out, cudaStream_t st) {
+    if (h * w == 0) return;
+    unsigned blocks = (unsigned)((h * w + 255) / 256);
+    LaunchScope ls(KC_GEN, st);
+    if (p.dist == DD_NORMAL)
+        k_export_block<DD_NORMAL><<<blocks, 256, 0, st>>>(seed_to_key(p.seed), p.base, p.S,
+                                                          p.scale, i0, j0, h, w, out);
+    else
+        k_export_block<DD_CAUCHY><<<blocks, 256, 0, st>>>(seed_to_key(p.seed), p.base, p.S,
+                                                          p.scale, i0, j0, h, w, out);
+    SKB_CUDA(cudaGetLastError());
+}
+
+// ---------------------------------------------------------------------------
+// FP64 tensor-core GEMM (K5b): OUT[i,j] (+)= sum_kk P[kk*S + i] * X(kk, j)
+// ---------------------------------------------------------------------------
+static constexpr int BM = 128, BN = 128, BK = 16, STAGES = 4, NTHREADS = 256;
+static constexpr int LDP = BM + 4;   // doubles; = 4 mod 16 -> conflict-free 64-bit fragment loads
+
+template <typename TX> struct XTile;
+template <> struct XTile<double> {
+    static constexpr int LD_ROWS = BN + 4;   // Xs[kk][j]
+    static constexpr int LD_COLS = BK + 4;   // Xs[j][kk]
+};
+template <> struct XTile<float> {
+    static constexpr int LD_ROWS = BN + 8;   // = 8 mod 32 floats
+    static constexpr int LD_COLS = BK + 4;   // = 20 mod 32 floats
+};
+
+template <typename TX, bool ROWS> struct GemmSmem {
+    static constexpr int P_ELEMS = BK * LDP;
+    static constexpr int X_ELEMS = ROWS ? BK * XTile<TX>::LD_ROWS : BN * XTile<TX>::LD_COLS;
+    static constexpr size_t STAGE_BYTES = P_ELEMS * sizeof(double) +
+                                          ((X_ELEMS * sizeof(TX) + 15) / 16) * 16;
+    static constexpr size_t BYTES = STAGE_BYTES * STAGES;
+};
+
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void *smem, const void *gmem, int src_bytes) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    if (BYTES == 16)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(src_bytes));
+    else if (BYTES == 8)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(s), "l"(gmem), "r"(src_bytes));
+    else
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(s), "l"(gmem), "r"(src_bytes));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N));
+}
+
+__device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+struct GemmArgs {
+    const double *P; size_t S; size_t kc;      // panel: kc rows of S
+    const void *X; size_t ldx; size_t m;       // local input, kc sketched indices
+    void *OUT; size_t ldo;                     // TX (direct) or double (atomic) output
+    int ntm, ntn, nk;
+    int direct_ok;        // full-K segments may store (and apply the epilogue) directly
+    int whole_tiles;      // partition by whole tiles (no k split) instead of stream-K
+    int out_is_acc;       // OUT points at a double accumulation buffer (atomic path for float)
+    const double *scales, *shifts; double outscale; int has_epi;
+};
+
+// Copy `count` elements of CPB/sizeof(T) at a time; rows x cols tile from global
+// (row stride gld elements) into shared (row stride sld), zero-filling beyond
+// (row_limit, col_limit).
+template <typename T, int CPB>
+__device__ __forceinline__ void load_tile(T *smem, int sld, const T *g, size_t gld, int rows,
+                                          int cols, long long row_limit, long long col_limit) {
+    constexpr int EPC = CPB / (int)sizeof(T);          // elements per copy
+    const int cpr = cols / EPC;                        // copies per row
+    const int total = rows * cpr;
+    for (int c = threadIdx.x; c < total; c += NTHREADS) {
+        int r = c / cpr, q = (c - r * cpr) * EPC;
+        long long rem = col_limit - q;
+        int nb = 0;
+        if (r < row_limit && rem > 0) nb = rem >= EPC ? CPB : (int)rem * (int)sizeof(T);
+        const T *src = nb > 0 ? g + (size_t)r * gld + q : g;
+        cp_async<CPB>(smem + r * sld + q, src, nb);
+    }
+}
+
+template <typename TX, bool ROWS, int CPB_P, int CPB_X>
+__global__ void __launch_bounds__(NTHREADS, 1) k_dense_gemm(GemmArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    using SM = GemmSmem<TX, ROWS>;
+    constexpr int LDX = ROWS ? XTile<TX>::LD_ROWS : XTile<TX>::LD_COLS;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp & 1, wn = warp >> 1;
+    const int g = lane >> 2, t4 = lane & 3;
+
+    const long long total = (long long)a.ntm * a.ntn * a.nk;
+    long long u, u_end;
+    if (a.whole_tiles) {
+        const long long nt = (long long)a.ntm * a.ntn;
+        u = nt * blockIdx.x / gridDim.x * a.nk;
+        u_end = nt * (blockIdx.x + 1) / gridDim.x * a.nk;
+    } else {
+        u = total * blockIdx.x / gridDim.x;
+        u_end = total * (blockIdx.x + 1) / gridDim.x;
+    }
+    const TX *Xg = reinterpret_cast<const TX *>(a.X);
+
+    while (u < u_end) {
+        const int tile = (int)(u / a.nk);
+        const int ks0 = (int)(u - (long long)tile * a.nk);
+        const int ks1 = (int)min((long long)a.nk, ks0 + (u_end - u));
+        const int tm = tile / a.ntn, tn = tile - tm * a.ntn;
+        const size_t i0 = (size_t)tm * BM, j0 = (size_t)tn * BN;
+        const long long i_lim = (long long)a.S - (long long)i0;   // valid i in tile
+        const long long j_lim = (long long)a.m - (long long)j0;
+
+        double acc[8][4][2];
+#pragma unroll
+        for (int mi = 0; mi < 8; mi++)
+#pragma unroll
+            for (int ni = 0; ni < 4; ni++) { acc[mi][ni][0] = 0.0; acc[mi][ni][1] = 0.0; }
+
+        auto issue = [&](int ks, int slot) {
+            unsigned char *base = smem_raw + (size_t)slot * SM::STAGE_BYTES;
+            double *Ps = reinterpret_cast<double *>(base);
+            TX *Xs = reinterpret_cast<TX *>(base + SM::P_ELEMS * sizeof(double));
+            const long long kk0 = (long long)ks * BK;
+            const long long k_lim = (long long)a.kc - kk0;          // valid kk in this step
+            load_tile<double, CPB_P>(Ps, LDP, a.P + (size_t)kk0 * a.S + i0, a.S, BK, BM, k_lim, i_lim);
+            if (ROWS)
+                load_tile<TX, CPB_X>(Xs, LDX, Xg + (size_t)kk0 * a.ldx + j0, a.ldx, BK, BN, k_lim, j_lim);
+            else
+                load_tile<TX, CPB_X>(Xs, LDX, Xg + (size_t)j0 * a.ldx + kk0, a.ldx, BN, BK, j_lim, k_lim);
+        };
+
+        const int nsteps = ks1 - ks0;
+#pragma unroll
+        for (int s = 0; s < STAGES - 1; s++) {
+            if (s < nsteps) issue(ks0 + s, s);
+            cp_async_commit();
+        }
+        for (int it = 0; it < nsteps; it++) {
+            cp_async_wait<STAGES - 2>();
+            __syncthreads();
+            {
+                int nx = it + STAGES - 1;
+                if (nx < nsteps) issue(ks0 + nx, nx % STAGES);
+                cp_async_commit();
+            }
+            const unsigned char *base = smem_raw + (size_t)(it % STAGES) * SM::STAGE_BYTES;
+            const double *Ps = reinterpret_cast<const double *>(base);
+            const TX *Xs = reinterpret_cast<const TX *>(base + SM::P_ELEMS * sizeof(double));
+#pragma unroll
+            for (int k4 = 0; k4 < BK / 4; k4++) {
+                double af[8], bf[4];
+                const double *pa = Ps + (k4 * 4 + t4) * LDP + wm * 64 + g;
+#pragma unroll
+                for (int mi = 0; mi < 8; mi++) af[mi] = pa[mi * 8];
+#pragma unroll
+                for (int ni = 0; ni < 4; ni++) {
+                    int j = wn * 32 + ni * 8 + g;
+                    bf[ni] = ROWS ? (double)Xs[(k4 * 4 + t4) * LDX + j]
+                                  : (double)Xs[j * LDX + k4 * 4 + t4];
+                }
+#pragma unroll
+                for (int mi = 0; mi < 8; mi++)
+#pragma unroll
+                    for (int ni = 0; ni < 4; ni++)
+                        dmma884(acc[mi][ni][0], acc[mi][ni][1], af[mi], bf[ni]);
+            }
+        }
+        cp_async_wait<0>();
+        __syncthreads();
+
+        // ---- flush -----------------------------------------------------------
+        const bool full = (ks0 == 0 && ks1 == a.nk);
+        const bool direct = full && a.direct_ok;
+#pragma unroll
+        for (int mi = 0; mi < 8; mi++) {
+            const long long il = wm * 64 + mi * 8 + g;
+            if (il >= i_lim) continue;
+            const size_t i = i0 + il;
+            double sc = 1.0, sh = 0.0;
+            if (direct && a.has_epi) { sc = a.scales[i]; sh = a.shifts[i]; }
+#pragma unroll
+            for (int ni = 0; ni < 4; ni++) {
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+                    const long long jl = wn * 32 + ni * 8 + t4 * 2 + e;
+                    if (jl >= j_lim) continue;
+                    const size_t j = j0 + jl;
+                    const size_t off = ROWS ? i * a.ldo + j : i + j * a.ldo;
+                    double v = acc[mi][ni][e];
+                    if (direct) {
+                        if (a.has_epi) v = __dmul_rn(a.outscale, cos(__dadd_rn(__dmul_rn(v, sc), sh)));
+                        if (a.out_is_acc) reinterpret_cast<double *>(a.OUT)[off] = v;
+                        else reinterpret_cast<TX *>(a.OUT)[off] = (TX)v;
+                    } else {
+                        if (a.out_is_acc || sizeof(TX) == 8)
+                            atomicAdd(reinterpret_cast<double *>(a.OUT) + off, v);
+                        else
+                            atomicAdd(reinterpret_cast<float *>(a.OUT) + off, (float)v);
+                    }
+                }
+            }
+        }
+        u += nsteps;
+    }
+}
+
+// acc (double, same indexing as OUT) -> OUT with optional RFT epilogue
+template <typename TX, bool ROWS>
+__global__ void k_dense_finalize(const double *__restrict__ acc, TX *__restrict__ OUT, size_t S,
+                                 size_t m, size_t ldo, const double *scales,
+                                 const double *shifts, double outscale, int has_epi) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S * m) return;
+    size_t i, j;
+    if (ROWS) { i = t / m; j = t - i * m; } else { j = t / S; i = t - j * S; }
+    size_t off = ROWS ? i * ldo + j : i + j * ldo;
+    double v = acc[off];
+    if (has_epi) v = __dmul_rn(outscale, cos(__dadd_rn(__dmul_rn(v, scales[i]), shifts[i])));
+    OUT[off] = (TX)v;
+}
+
+static size_t panel_rows_for(size_t S) {
+    // keep panel (<= 64 MiB) + the matching slab of X inside the 126 MB L2
+    size_t kc = ((size_t)64 << 20) / (S * sizeof(double));
+    kc = kc / BK * BK;
+    if (kc < (size_t)BK) kc = BK;
+    if (kc > 8192) kc = 8192;
+    return kc;
+}
+
+size_t dense_workspace_bytes(const DenseParams &p, size_t nloc, bool layout_rows, bool f32,
+                             size_t m, size_t ldo) {
+    size_t kc = panel_rows_for(p.S);
+    if (kc > nloc) kc = (nloc + BK - 1) / BK * BK;
+    if (kc == 0) kc = BK;
+    size_t panel = ((kc * p.S * sizeof(double) + 255) / 256) * 256;
+    // double accumulation image of OUT, used only by the float atomic path
+    size_t accbuf = f32 ? (layout_rows ? p.S * ldo : m * ldo) * sizeof(double) : 0;
+    return panel + accbuf + 256;
+}
+
+template <typename TX, bool ROWS>
+static void launch_gemm(const GemmArgs &a, bool al16p, bool alx, unsigned grid, cudaStream_t st) {
+    using SM = GemmSmem<TX, ROWS>;
+    constexpr int XS = sizeof(TX) == 8 ? 8 : 4;   // small-copy size for X
+#define SKB_LAUNCH(CP, CX)                                                                       \
+    do {                                                                                         \
+        auto kern = k_dense_gemm<TX, ROWS, CP, CX>;                                              \
+        SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
+                                      (int)SM::BYTES));                                          \
+        kern<<<grid, NTHREADS, SM::BYTES, st>>>(a);                                              \
+    } while (0)
+    LaunchScope ls(KC_GEMM, st);
+    if (al16p && alx) SKB_LAUNCH(16, 16);
+    else if (al16p) SKB_LAUNCH(16, XS);
+    else if (alx) SKB_LAUNCH(8, 16);
+    else SKB_LAUNCH(8, XS);
+#undef SKB_LAUNCH
+    SKB_CUDA(cudaGetLastError());
+}
+
+template <typename TX, bool ROWS>
+static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t m, size_t koff,
+                          size_t nloc, TX *OUT, size_t ldo, const RftEpilogue &epi,
+                          void *workspace, size_t workspace_bytes, cudaStream_t st) {
+    const size_t S = p.S;
+    if (S == 0 || m == 0) return;
+    size_t kc_max = panel_rows_for(S);
+    if (kc_max > nloc) kc_max = (nloc + BK - 1) / BK * BK;
+    if (kc_max == 0) kc_max = BK;
+    const size_t panel_bytes = ((kc_max * S * sizeof(double) + 255) / 256) * 256;
+    if (workspace_bytes < panel_bytes)
+        throw error(SKB_ERR_ALLOC, "dense apply: workspace too small");
+    double *panel = reinterpret_cast<double *>(workspace);
+    double *accbuf = reinterpret_cast<double *>(reinterpret_cast<char *>(workspace) + panel_bytes);
+
+    const int ntm = (int)((S + BM - 1) / BM), ntn = (int)((m + BN - 1) / BN);
+    const long long ntiles = (long long)ntm * ntn;
+    const size_t npanels = nloc == 0 ? 0 : (nloc + kc_max - 1) / kc_max;
+    const bool has_epi = epi.shifts != nullptr;
+    const bool tile_mode = ntiles >= 4 * 148;     // enough tiles: no k split
+    const bool single = npanels == 1;
+    // direct stores (and the fused epilogue) need one CTA to own a tile's whole sum
+    const bool direct_ok = single;
+    const bool all_direct = single && tile_mode;
+    const bool use_accbuf = sizeof(TX) == 4 && !all_direct;
+    const bool need_zero = !all_direct;
+    const bool fuse_epi = has_epi && all_direct;
+
+    void *gemm_out = use_accbuf ? (void *)accbuf : (void *)OUT;
+    // accbuf is laid out exactly like OUT (same ldo) so the flush code is shared
+    if (use_accbuf && workspace_bytes < panel_bytes + (ROWS ? S * ldo : m * ldo) * sizeof(double))
+        throw error(SKB_ERR_ALLOC, "dense apply: workspace too small for accumulation buffer");
+    if (need_zero) {
+        size_t contig = ROWS ? m : S, nvec = ROWS ? S : m;
+        size_t esz = use_accbuf ? sizeof(double) : sizeof(TX);
+        if (ldo == contig) SKB_CUDA(cudaMemsetAsync(gemm_out, 0, contig * nvec * esz, st));
+        else SKB_CUDA(cudaMemset2DAsync(gemm_out, ldo * esz, 0, contig * esz, nvec, st));
+    }
+
+    const bool al16p = (S % 2 == 0);
+    const int xe = 16 / (int)sizeof(TX);
+    const bool alx = (ldx % xe == 0) && ((uintptr_t)X % 16 == 0);
+
+    for (size_t k0 = 0; k0 < nloc; k0 += kc_max) {
+        size_t kc = nloc - k0 < kc_max ? nloc - k0 : kc_max;
+        dense_generate_panel(p, koff + k0, kc, panel, st);
+        GemmArgs a;
+        a.P = panel; a.S = S; a.kc = kc;
+        a.X = ROWS ? (const void *)(X + k0 * ldx) : (const void *)(X + k0);
+        a.ldx = ldx; a.m = m; a.OUT = gemm_out; a.ldo = ldo;
+        a.ntm = ntm; a.ntn = ntn; a.nk = (int)((kc + BK - 1) / BK);
+        a.direct_ok = direct_ok ? 1 : 0;
+        a.out_is_acc = use_accbuf ? 1 : 0;
+        a.scales = epi.scales; a.shifts = epi.shifts; a.outscale = epi.outscale;
+        a.has_epi = fuse_epi ? 1 : 0;
+        if (!tile_mode && a.direct_ok) a.direct_ok = 0;   // stream-K ranges may split a tile
+        a.whole_tiles = tile_mode ? 1 : 0;
+        long long total = ntiles * a.nk;
+        unsigned grid = tile_mode ? 148u : (unsigned)(total < 148 ? total : 148);
+        // alignment of the X slab for this panel
+        bool alx_p = alx && (ROWS || (k0 % xe == 0));
+        launch_gemm<TX, ROWS>(a, al16p, alx_p, grid, st);
+    }
+    if (nloc == 0) return;   // OUT already zeroed
+    if (use_accbuf || (has_epi && !fuse_epi)) {
+        const double *src = use_accbuf ? accbuf : reinterpret_cast<const double *>(OUT);
+        size_t n = S * m;
+        LaunchScope ls(KC_MISC, st);
+        k_dense_finalize<TX, ROWS><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
+            src, OUT, S, m, ldo, epi.scales, epi.shifts, epi.outscale, has_epi ? 1 : 0);
+        SKB_CUDA(cudaGetLastError());
+    }
+}
+
+void dense_apply(const DenseParams &p, bool layout_rows, bool f32, const void *X, size_t ldx,
+                 size_t m, size_t koff, size_t nloc, void *OUT, size_t ldo,
+                 const RftEpilogue &epi, void *workspace, size_t workspace_bytes,
+                 cudaStream_t st) {
+    if (f32) {
+        if (layout_rows) dense_apply_t<float, true>(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st);
+        else dense_apply_t<float, false>(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st);
+    } else {
+        if (layout_rows) dense_apply_t<double, true>(p, (const double *)X, ldx, m, koff, nloc, (double *)OUT, ldo, epi, workspace, workspace_bytes, st);
+        else dense_apply_t<double, false>(p, (const double *)X, ldx, m, koff, nloc, (double *)OUT, ldo, epi, workspace, workspace_bytes, st);
+    }
+}
+
+}  // namespace skb

@@ -1,0 +1,468 @@
+// Hash sketches (CWT / MMT / WZT): Pi has one nonzero per input index.
+//
+// Reference loops replaced:
+//   hash_transform_data_t::build            sketch/hash_transform_data.hpp:64-76
+//   WZT_data_t::build                       sketch/WZT_data.hpp:110-126
+//   dense apply (both directions)           sketch/hash_transform_Elemental.hpp:83-123
+//   CSC -> dense apply (both directions)    sketch/hash_transform_Elemental.hpp:201-256
+//
+// B200 design (HBM-bound, no tensor cores):
+//   * bucket/value tables are produced on the device from the counter stream (K0);
+//   * for the layout in which every input index owns a contiguous row (the path a
+//     C-ordered "columnwise" sketch takes), rows are grouped by bucket once per
+//     transform (stable radix sort) so that the apply is a gather-side segmented
+//     sum: each warp streams <=32 whole rows of one bucket with 128-bit loads and
+//     writes one 64-column slice of one output row.  No atomics unless a bucket is
+//     longer than 32 rows, and rows inside a bucket are added in ascending order
+//     with separate multiply and add, i.e. the reference's own rounding sequence.
+//   * the strided layout and CSC input accumulate in shared memory per output
+//     column and dump coalesced columns.
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include "rng.cuh"
+#include "skb_internal.h"
+
+namespace skb {
+
+// ---------------------------------------------------------------------------
+// K0: tables
+// ---------------------------------------------------------------------------
+__global__ void k_hash_tables(uint64_t key, uint64_t idx_base, uint64_t val_base,
+                              uint64_t pm_base, size_t first, size_t n, uint64_t S, int kind,
+                              double p, int order, int32_t *__restrict__ bucket,
+                              double *__restrict__ value) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    size_t g = first + t;
+    {
+        MicroUrng u(key, idx_base + g);
+        bucket[t] = (int32_t)boost_uniform_int(u, S - 1);
+    }
+    MicroUrng u(key, val_base + g);
+    double v;
+    if (kind == HV_RADEMACHER) {
+        v = boost_rademacher(u, order);
+    } else if (kind == HV_CAUCHY) {
+        v = boost_cauchy(u);
+    } else {
+        double e = boost_exponential(u);
+        MicroUrng u2(key, pm_base + g);
+        double pm = boost_rademacher(u2, order);
+        v = __dmul_rn(pm, pow(__ddiv_rn(1.0, e), __ddiv_rn(1.0, p)));
+    }
+    value[t] = v;
+}
+
+void hash_build_tables(int seed, uint64_t idx_base, uint64_t val_base, uint64_t pm_base,
+                       size_t first, size_t n, uint64_t S, int kind, double p, int order,
+                       int32_t *bucket, double *value, cudaStream_t st) {
+    if (n == 0) return;
+    LaunchScope ls(KC_TABLES, st);
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    k_hash_tables<<<blocks, 256, 0, st>>>(seed_to_key(seed), idx_base, val_base, pm_base,
+                                          first, n, S, kind, p, order, bucket, value);
+    SKB_CUDA(cudaGetLastError());
+}
+
+// ---------------------------------------------------------------------------
+// Plan: rows grouped by bucket, cut in chunks of <= CHUNK rows
+// ---------------------------------------------------------------------------
+static constexpr int CHUNK = 32;
+
+__global__ void k_iota(int32_t *a, size_t n) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) a[t] = (int32_t)t;
+}
+
+__global__ void k_bucket_hist(const int32_t *__restrict__ bucket, size_t n, int32_t *hist) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) atomicAdd(&hist[bucket[t]], 1);
+}
+
+__global__ void k_chunks_per_bucket(const int32_t *__restrict__ hist, int S, int32_t *nch) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < S) nch[b] = (hist[b] + CHUNK - 1) / CHUNK;
+}
+
+// bucket_row0: exclusive scan of hist; chunk0: exclusive scan of nch
+__global__ void k_fill_chunks(const int32_t *__restrict__ hist,
+                              const int32_t *__restrict__ bucket_row0,
+                              const int32_t *__restrict__ chunk0, int S,
+                              int32_t *chunk_start, int32_t *chunk_bucket, int nchunks,
+                              int32_t n_total) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b == 0) chunk_start[nchunks] = n_total;
+    if (b >= S) return;
+    int cnt = hist[b], r0 = bucket_row0[b], c0 = chunk0[b];
+    int nc = (cnt + CHUNK - 1) / CHUNK;
+    for (int c = 0; c < nc; c++) {
+        chunk_start[c0 + c] = r0 + c * CHUNK;
+        chunk_bucket[c0 + c] = nc > 1 ? ~b : b;
+    }
+}
+
+// chunk_start[c+1] of the last chunk of a bucket must be the bucket end, which is
+// the next bucket's start: true by construction because chunks are laid out in
+// bucket order and every bucket's first chunk starts at bucket_row0.
+
+void hash_free_plan(HashPlan *plan) {
+    if (plan->rows) cudaFree(plan->rows);
+    if (plan->chunk_start) cudaFree(plan->chunk_start);
+    if (plan->chunk_bucket) cudaFree(plan->chunk_bucket);
+    *plan = HashPlan();
+}
+
+void hash_build_plan(const int32_t *bucket, size_t n, int S, HashPlan *plan, cudaStream_t st) {
+    hash_free_plan(plan);
+    plan->n = n;
+    if (n == 0) return;
+    if (n > 0x7fffffffULL) throw error(SKB_ERR_INVALID_PARAM, "hash plan: n exceeds int32");
+    int32_t *iota = nullptr, *keys_out = nullptr, *hist = nullptr, *row0 = nullptr,
+            *nch = nullptr, *chunk0 = nullptr;
+    void *tmp = nullptr;
+    try {
+        SKB_CUDA(cudaMalloc(&plan->rows, n * sizeof(int32_t)));
+        SKB_CUDA(cudaMalloc(&iota, n * sizeof(int32_t)));
+        SKB_CUDA(cudaMalloc(&keys_out, n * sizeof(int32_t)));
+        SKB_CUDA(cudaMalloc(&hist, (size_t)(S + 1) * 4 * sizeof(int32_t)));
+        row0 = hist + (S + 1); nch = row0 + (S + 1); chunk0 = nch + (S + 1);
+        SKB_CUDA(cudaMemsetAsync(hist, 0, (size_t)(S + 1) * 4 * sizeof(int32_t), st));
+        unsigned nb = (unsigned)((n + 255) / 256), sb = (unsigned)((S + 1 + 255) / 256);
+        {
+            LaunchScope ls(KC_TABLES, st);
+            k_iota<<<nb, 256, 0, st>>>(iota, n);
+        }
+        {
+            LaunchScope ls(KC_TABLES, st);
+            k_bucket_hist<<<nb, 256, 0, st>>>(bucket, n, hist);
+        }
+        int end_bit = 1;
+        while ((1LL << end_bit) < (long long)S && end_bit < 31) end_bit++;
+        size_t tmp_bytes = 0, scan_bytes = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, bucket, keys_out, iota, plan->rows,
+                                        (int)n, 0, end_bit, st);
+        cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, hist, row0, S + 1, st);
+        if (scan_bytes > tmp_bytes) tmp_bytes = scan_bytes;
+        SKB_CUDA(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 16));
+        {
+            LaunchScope ls(KC_TABLES, st);
+            SKB_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, bucket, keys_out, iota,
+                                                     plan->rows, (int)n, 0, end_bit, st));
+        }
+        {
+            LaunchScope ls(KC_TABLES, st);
+            SKB_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, hist, row0, S + 1, st));
+        }
+        {
+            LaunchScope ls(KC_TABLES, st);
+            k_chunks_per_bucket<<<sb, 256, 0, st>>>(hist, S, nch);
+        }
+        {
+            LaunchScope ls(KC_TABLES, st);
+            SKB_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, nch, chunk0, S + 1, st));
+        }
+        int32_t nchunks = 0;
+        SKB_CUDA(cudaMemcpyAsync(&nchunks, chunk0 + S, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        SKB_CUDA(cudaStreamSynchronize(st));
+        plan->nchunks = nchunks;
+        SKB_CUDA(cudaMalloc(&plan->chunk_start, (size_t)(nchunks + 1) * sizeof(int32_t)));
+        SKB_CUDA(cudaMalloc(&plan->chunk_bucket, (size_t)(nchunks + 1) * sizeof(int32_t)));
+        {
+            LaunchScope ls(KC_TABLES, st);
+            k_fill_chunks<<<sb, 256, 0, st>>>(hist, row0, chunk0, S, plan->chunk_start,
+                                              plan->chunk_bucket, nchunks, (int32_t)n);
+        }
+        SKB_CUDA(cudaGetLastError());
+        SKB_CUDA(cudaStreamSynchronize(st));
+    } catch (...) {
+        cudaFree(iota); cudaFree(keys_out); cudaFree(hist); cudaFree(tmp);
+        hash_free_plan(plan);
+        throw;
+    }
+    cudaFree(iota); cudaFree(keys_out); cudaFree(hist); cudaFree(tmp);
+}
+
+// ---------------------------------------------------------------------------
+// K1: contiguous-row layout.  One warp = one chunk (<=32 rows of one bucket) x one
+// 64-column tile; lane l keeps (row id, value) of the chunk's l-th row and
+// broadcasts them by shuffle, so the address chain has no dependent global load.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double2 ldg_stream2(const double *p) {
+    double2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0, %1}, [%2];"
+                 : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ double ldg_stream1(const double *p) {
+    double v;
+    asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+    return v;
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+k_hash_rows(const double *__restrict__ X, size_t ldx, int m,
+            const int32_t *__restrict__ rows, const int32_t *__restrict__ chunk_start,
+            const int32_t *__restrict__ chunk_bucket, const double *__restrict__ value,
+            long long nitems, int ntiles, double *__restrict__ OUT, size_t ldo) {
+    const int lane = threadIdx.x & 31;
+    long long item = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (item >= nitems) return;
+    const int chunk = (int)(item / ntiles), tile = (int)(item % ntiles);
+    const int beg = chunk_start[chunk], cnt = chunk_start[chunk + 1] - beg;
+    const int cb = chunk_bucket[chunk];
+    const bool multi = cb < 0;
+    const int b = multi ? ~cb : cb;
+
+    int myrow = 0; double myval = 0.0;
+    if (lane < cnt) { myrow = rows[beg + lane]; myval = value[myrow]; }
+
+    constexpr int TILE = 32 * VEC;
+    const int col = tile * TILE + lane * VEC;
+    const bool active = col < m;     // VEC == 2 implies m even, so col+1 < m too
+    const double *xcol = X + col;
+    double a0 = 0.0, a1 = 0.0;
+
+    constexpr int U = 8;
+    for (int r = 0; r < cnt; r += U) {
+        double2 x[U]; double v[U];
+#pragma unroll
+        for (int i = 0; i < U; i++) {
+            int k = __shfl_sync(0xffffffffu, myrow, (r + i) & 31);
+            v[i] = __shfl_sync(0xffffffffu, myval, (r + i) & 31);
+            x[i].x = 0.0; x[i].y = 0.0;
+            if (active && r + i < cnt) {
+                const double *p = xcol + (size_t)k * ldx;
+                if (VEC == 2) x[i] = ldg_stream2(p); else x[i].x = ldg_stream1(p);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < U; i++) {
+            if (r + i < cnt) {   // keep the reference's rounding: product, then sum
+                a0 = __dadd_rn(a0, __dmul_rn(v[i], x[i].x));
+                if (VEC == 2) a1 = __dadd_rn(a1, __dmul_rn(v[i], x[i].y));
+            }
+        }
+    }
+    if (!active) return;
+    double *o = OUT + (size_t)b * ldo + col;
+    if (multi) {
+        atomicAdd(o, a0);
+        if (VEC == 2) atomicAdd(o + 1, a1);
+    } else {
+        if (VEC == 2) { double2 w; w.x = a0; w.y = a1; *reinterpret_cast<double2 *>(o) = w; }
+        else *o = a0;
+    }
+}
+
+static void zero_matrix(double *OUT, size_t ld, size_t rows_contig, size_t nvec, cudaStream_t st) {
+    // nvec vectors of rows_contig contiguous doubles, stride ld
+    if (nvec == 0 || rows_contig == 0) return;
+    if (ld == rows_contig)
+        SKB_CUDA(cudaMemsetAsync(OUT, 0, rows_contig * nvec * sizeof(double), st));
+    else
+        SKB_CUDA(cudaMemset2DAsync(OUT, ld * sizeof(double), 0, rows_contig * sizeof(double),
+                                   nvec, st));
+}
+
+void hash_apply_rows(const double *X, size_t ldx, size_t m, const HashPlan &plan,
+                     const double *value, double *OUT, size_t ldo, int S, cudaStream_t st) {
+    zero_matrix(OUT, ldo, m, (size_t)S, st);
+    if (plan.nchunks == 0 || m == 0) return;
+    bool vec2 = (m % 2 == 0) && (ldx % 2 == 0) && (ldo % 2 == 0) &&
+                ((uintptr_t)X % 16 == 0) && ((uintptr_t)OUT % 16 == 0);
+    int tile = vec2 ? 64 : 32;
+    int ntiles = (int)((m + tile - 1) / tile);
+    long long nitems = (long long)plan.nchunks * ntiles;
+    long long nblocks = (nitems * 32 + 255) / 256;
+    if (nblocks > 0x7fffffffLL) throw error(SKB_ERR_INVALID_PARAM, "hash apply: grid too large");
+    LaunchScope ls(KC_HASH, st);
+    if (vec2)
+        k_hash_rows<2><<<(unsigned)nblocks, 256, 0, st>>>(X, ldx, (int)m, plan.rows,
+            plan.chunk_start, plan.chunk_bucket, value, nitems, ntiles, OUT, ldo);
+    else
+        k_hash_rows<1><<<(unsigned)nblocks, 256, 0, st>>>(X, ldx, (int)m, plan.rows,
+            plan.chunk_start, plan.chunk_bucket, value, nitems, ntiles, OUT, ldo);
+    SKB_CUDA(cudaGetLastError());
+}
+
+// ---------------------------------------------------------------------------
+// K2: strided layout (every column of X is contiguous along the sketched index).
+// A CTA owns CG columns and a slice of the sketched index; it accumulates into a
+// shared S x CG tile and flushes it (atomics only if the index is split).
+// ---------------------------------------------------------------------------
+template <int CG>
+__global__ void __launch_bounds__(256)
+k_hash_cols_smem(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
+                 const int32_t *__restrict__ bucket, const double *__restrict__ value,
+                 double *__restrict__ OUT, size_t ldo, int S, int ksplit) {
+    extern __shared__ double acc[];   // [CG][S]
+    const size_t j0 = (size_t)blockIdx.x * CG;
+    const int ncol = (int)min((size_t)CG, m - j0);
+    for (int i = threadIdx.x; i < S * CG; i += blockDim.x) acc[i] = 0.0;
+    __syncthreads();
+    const size_t per = (n + ksplit - 1) / ksplit;
+    const size_t k0 = (size_t)blockIdx.y * per;
+    const size_t k1 = min(n, k0 + per);
+    for (size_t k = k0 + threadIdx.x; k < k1; k += blockDim.x) {
+        int h = bucket[k];
+        double v = value[k];
+        double x[CG];
+#pragma unroll
+        for (int c = 0; c < CG; c++) x[c] = c < ncol ? ldg_stream1(X + k + (j0 + c) * ldx) : 0.0;
+#pragma unroll
+        for (int c = 0; c < CG; c++)
+            if (c < ncol) atomicAdd(&acc[c * S + h], __dmul_rn(v, x[c]));
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < S * ncol; i += blockDim.x) {
+        int c = i / S, h = i - c * S;
+        double a = acc[c * S + h];
+        double *o = OUT + h + (j0 + c) * ldo;
+        if (ksplit == 1) *o = a;
+        else if (a != 0.0) atomicAdd(o, a);
+    }
+}
+
+// Fallback when S is too large for shared memory: L2 atomics.
+__global__ void k_hash_cols_global(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
+                                   const int32_t *__restrict__ bucket,
+                                   const double *__restrict__ value, double *__restrict__ OUT,
+                                   size_t ldo) {
+    size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t j = blockIdx.y;
+    if (k >= n) return;
+    atomicAdd(OUT + bucket[k] + j * ldo, __dmul_rn(value[k], X[k + j * ldx]));
+}
+
+void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int32_t *bucket,
+                     const double *value, double *OUT, size_t ldo, int S, cudaStream_t st) {
+    if (m == 0) return;
+    constexpr int CG = 4;
+    size_t smem = (size_t)S * CG * sizeof(double);
+    if (smem <= 200 * 1024) {
+        unsigned gx = (unsigned)((m + CG - 1) / CG);
+        int ksplit = 1;
+        // aim for >= 2 CTAs per SM; every split costs an S x CG atomic flush
+        while ((long long)gx * ksplit < 296 && (n / (ksplit * 2)) >= 4096) ksplit *= 2;
+        if (ksplit > 1) zero_matrix(OUT, ldo, (size_t)S, m, st);
+        SKB_CUDA(cudaFuncSetAttribute(k_hash_cols_smem<CG>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        LaunchScope ls(KC_HASH, st);
+        k_hash_cols_smem<CG><<<dim3(gx, ksplit), 256, smem, st>>>(X, ldx, n, m, bucket, value,
+                                                                   OUT, ldo, S, ksplit);
+        SKB_CUDA(cudaGetLastError());
+    } else {
+        zero_matrix(OUT, ldo, (size_t)S, m, st);
+        if (n == 0) return;
+        if (m > 65535) throw error(SKB_ERR_INVALID_PARAM, "hash apply: too many columns");
+        LaunchScope ls(KC_HASH, st);
+        k_hash_cols_global<<<dim3((unsigned)((n + 255) / 256), (unsigned)m), 256, 0, st>>>(
+            X, ldx, n, m, bucket, value, OUT, ldo);
+        SKB_CUDA(cudaGetLastError());
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K3: CSC input, sketch over rows.  Persistent CTAs; each column is accumulated in
+// a shared S-vector (shared atomics), then written as one coalesced dense column
+// while the accumulator is re-zeroed.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(512)
+k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__restrict__ indices,
+                        const double *__restrict__ values, size_t ncols,
+                        const int32_t *__restrict__ bucket, const double *__restrict__ value,
+                        double *__restrict__ OUT, size_t ldo, int S) {
+    extern __shared__ double acc[];   // [S]
+    for (int i = threadIdx.x; i < S; i += blockDim.x) acc[i] = 0.0;
+    __syncthreads();
+    for (size_t col = blockIdx.x; col < ncols; col += gridDim.x) {
+        const int p0 = indptr[col], p1 = indptr[col + 1];
+        for (int p = p0 + threadIdx.x; p < p1; p += blockDim.x) {
+            int row = indices[p];
+            atomicAdd(&acc[bucket[row]], __dmul_rn(value[row], values[p]));
+        }
+        __syncthreads();
+        double *o = OUT + col * ldo;
+        for (int i = threadIdx.x; i < S; i += blockDim.x) { o[i] = acc[i]; acc[i] = 0.0; }
+        __syncthreads();
+    }
+}
+
+__global__ void k_hash_csc_colwise_global(const int32_t *__restrict__ indptr,
+                                          const int32_t *__restrict__ indices,
+                                          const double *__restrict__ values, size_t ncols,
+                                          const int32_t *__restrict__ bucket,
+                                          const double *__restrict__ value,
+                                          double *__restrict__ OUT, size_t ldo) {
+    const int lane = threadIdx.x & 31;
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    size_t nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t col = warp; col < ncols; col += nwarps) {
+        const int p0 = indptr[col], p1 = indptr[col + 1];
+        for (int p = p0 + lane; p < p1; p += 32) {
+            int row = indices[p];
+            atomicAdd(OUT + col * ldo + bucket[row], __dmul_rn(value[row], values[p]));
+        }
+    }
+}
+
+void hash_apply_csc_columnwise(const int32_t *indptr, const int32_t *indices,
+                               const double *values, size_t ncols, const int32_t *bucket,
+                               const double *value, double *OUT, size_t ldo, int S,
+                               cudaStream_t st) {
+    if (ncols == 0) return;
+    size_t smem = (size_t)S * sizeof(double);
+    if (smem <= 220 * 1024) {
+        SKB_CUDA(cudaFuncSetAttribute(k_hash_csc_colwise_smem,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = smem <= 100 * 1024 ? 2 : 1;
+        size_t grid = (size_t)148 * per_sm;
+        if (grid > ncols) grid = ncols;
+        LaunchScope ls(KC_HASH, st);
+        k_hash_csc_colwise_smem<<<(unsigned)grid, 512, smem, st>>>(indptr, indices, values, ncols,
+                                                                  bucket, value, OUT, ldo, S);
+        SKB_CUDA(cudaGetLastError());
+    } else {
+        zero_matrix(OUT, ldo, (size_t)S, ncols, st);
+        LaunchScope ls(KC_HASH, st);
+        k_hash_csc_colwise_global<<<148 * 8, 256, 0, st>>>(indptr, indices, values, ncols, bucket,
+                                                         value, OUT, ldo);
+        SKB_CUDA(cudaGetLastError());
+    }
+}
+
+// CSC input, sketch over columns: each sparse column lands in dense output column
+// h(col); several input columns share one output column, hence L2 atomics.
+__global__ void k_hash_csc_rowwise(const int32_t *__restrict__ indptr,
+                                   const int32_t *__restrict__ indices,
+                                   const double *__restrict__ values, size_t ncols,
+                                   const int32_t *__restrict__ bucket,
+                                   const double *__restrict__ value, double *__restrict__ OUT,
+                                   size_t ldo) {
+    const int lane = threadIdx.x & 31;
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    size_t nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t col = warp; col < ncols; col += nwarps) {
+        const int p0 = indptr[col], p1 = indptr[col + 1];
+        const double v = value[col];
+        double *o = OUT + (size_t)bucket[col] * ldo;
+        for (int p = p0 + lane; p < p1; p += 32)
+            atomicAdd(o + indices[p], __dmul_rn(v, values[p]));
+    }
+}
+
+void hash_apply_csc_rowwise(const int32_t *indptr, const int32_t *indices,
+                            const double *values, size_t nrows, size_t ncols,
+                            const int32_t *bucket, const double *value, double *OUT,
+                            size_t ldo, int S, cudaStream_t st) {
+    zero_matrix(OUT, ldo, nrows, (size_t)S, st);
+    if (ncols == 0) return;
+    LaunchScope ls(KC_HASH, st);
+    k_hash_csc_rowwise<<<148 * 8, 256, 0, st>>>(indptr, indices, values, ncols, bucket, value,
+                                                OUT, ldo);
+    SKB_CUDA(cudaGetLastError());
+}
+
+}  // namespace skb

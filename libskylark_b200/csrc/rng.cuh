@@ -1,0 +1,173 @@
+// Device-side counter RNG and variate generation for the sketch kernels.
+//
+// What the reference does (and what these functions reproduce bit for bit on
+// the integer side):
+//   * one sample per global stream index g = base + i: a fresh
+//     r123::MicroURNG<Threefry2x64_R<13>> with ctr = {g, 0}, key = {seed, 0}
+//     (base/randgen.hpp:27-30, 98-115);
+//   * the distribution object (Boost.Random) pulls 64-bit draws from it; block n
+//     of the MicroURNG has n in the high 32 bits of ctr[1] and hands out X1
+//     before X0.
+// Distribution semantics follow Boost 1.60 (the conda pin); the Rademacher draw
+// order of Boost <= 1.55 is selectable (SKB_ORDER_155).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace skb {
+
+#define SKB_ORDER_160 160
+#define SKB_ORDER_155 155
+
+#define SKB_BOOST_PI 3.14159265358979323846
+
+__host__ __device__ __forceinline__ uint64_t rotl64(uint64_t x, int r) {
+    return (x << r) | (x >> (64 - r));
+}
+
+// Threefry2x64, 13 rounds, key = {k0, 0}.  Fully unrolled; ks2 folds the parity
+// constant.  Returns X0 in .x and X1 in .y.
+struct u64x2 { uint64_t x, y; };
+
+__host__ __device__ __forceinline__ u64x2 threefry2x64_13(uint64_t c0, uint64_t c1,
+                                                          uint64_t k0) {
+    const uint64_t ks0 = k0, ks1 = 0, ks2 = 0x1BD11BDAA9FC1A22ULL ^ k0;
+    uint64_t x0 = c0 + ks0, x1 = c1 + ks1;
+#define SKB_MIX(R) x0 += x1; x1 = rotl64(x1, R); x1 ^= x0;
+    SKB_MIX(16) SKB_MIX(42) SKB_MIX(12) SKB_MIX(31)
+    x0 += ks1; x1 += ks2 + 1;
+    SKB_MIX(16) SKB_MIX(32) SKB_MIX(24) SKB_MIX(21)
+    x0 += ks2; x1 += ks0 + 2;
+    SKB_MIX(16) SKB_MIX(42) SKB_MIX(12) SKB_MIX(31)
+    x0 += ks0; x1 += ks1 + 3;
+    SKB_MIX(16)
+#undef SKB_MIX
+    u64x2 r; r.x = x0; r.y = x1; return r;
+}
+
+// MicroURNG over one stream index.
+struct MicroUrng {
+    uint64_t c0, k0, r0, r1;
+    uint32_t n;
+    int last;
+    __host__ __device__ __forceinline__ MicroUrng(uint64_t key, uint64_t idx)
+        : c0(idx), k0(key), r0(0), r1(0), n(0), last(0) {}
+    __host__ __device__ __forceinline__ uint64_t next() {
+        if (last == 0) {
+            u64x2 b = threefry2x64_13(c0, (uint64_t)n << 32, k0);
+            r0 = b.x; r1 = b.y; n++; last = 2;
+        }
+        --last;
+        return last == 1 ? r1 : r0;
+    }
+};
+
+__host__ __device__ __forceinline__ uint64_t seed_to_key(int seed) {
+    return (uint64_t)(int64_t)seed;   // static_cast<uint64_t>(int), randgen.hpp:37
+}
+
+// double(x) for a 64-bit unsigned x, round to nearest even, without the
+// conversion pipe: hi*2^32 and lo are exact, their sum rounds once.
+__device__ __forceinline__ double u64_to_double_rn(uint64_t x) {
+#ifdef __CUDA_ARCH__
+    double dhi = __hiloint2double(0x45300000, (int)(uint32_t)(x >> 32));   // 2^84 + hi*2^32
+    double dlo = __hiloint2double(0x43300000, (int)(uint32_t)x);           // 2^52 + lo
+    return __dadd_rn(__dsub_rn(dhi, 19342813118337666422669312.0), dlo);   // 2^84 + 2^52
+#else
+    return (double)x;
+#endif
+}
+
+__host__ __device__ __forceinline__ double u64_to_double(uint64_t x) {
+#ifdef __CUDA_ARCH__
+    return u64_to_double_rn(x);
+#else
+    return (double)x;
+#endif
+}
+
+// boost::random::uniform_01<double>
+__host__ __device__ __forceinline__ double boost_u01(MicroUrng &u) {
+    for (;;) {
+        double r = u64_to_double(u.next()) * 0x1p-64;
+        if (r < 1.0) return r;
+    }
+}
+
+// boost::random::detail::generate_uniform_int for range < 2^64-1
+__host__ __device__ __forceinline__ uint64_t boost_uniform_int(MicroUrng &u,
+                                                               uint64_t range) {
+    if (range == 0) return 0;
+    const uint64_t brange = ~(uint64_t)0;
+    uint64_t bucket = brange / (range + 1);
+    if (brange % (range + 1) == range) bucket++;
+    for (;;) {
+        uint64_t r = u.next() / bucket;
+        if (r <= range) return r;
+    }
+}
+
+// utility/distributions.hpp:40-52 (discrete_distribution{.5,0,.5} - 1)
+__host__ __device__ __forceinline__ double boost_rademacher(MicroUrng &u, int order) {
+    uint64_t r; double t;
+    if (order == SKB_ORDER_155) { t = boost_u01(u); r = boost_uniform_int(u, 2); }
+    else                        { r = boost_uniform_int(u, 2); t = boost_u01(u); }
+    // alias table [0]=(0.5,->2) [1]=(0,->0) [2]=(1,-)
+    bool minus = (r == 1) || (r == 0 && t < 0.5);
+    return minus ? -1.0 : 1.0;
+}
+
+#ifdef __CUDACC__
+// boost::random::normal_distribution (Box-Muller, cosine branch)
+__device__ __forceinline__ double boost_normal(MicroUrng &u) {
+    double r1 = boost_u01(u);
+    double r2 = boost_u01(u);
+    double rho = sqrt(__dmul_rn(-2.0, log(__dsub_rn(1.0, r2))));
+    return __dmul_rn(rho, cos(__dmul_rn(2.0 * SKB_BOOST_PI, r1)));
+}
+
+// boost::random::cauchy_distribution(0,1)
+__device__ __forceinline__ double boost_cauchy(MicroUrng &u) {
+    return tan(__dmul_rn(SKB_BOOST_PI, __dsub_rn(boost_u01(u), 0.5)));
+}
+
+// boost::random::exponential_distribution(1)
+__device__ __forceinline__ double boost_exponential(MicroUrng &u) {
+    return -log(__dsub_rn(1.0, boost_u01(u)));
+}
+
+// Fast path for the dense generators: both draws of block 0 taken directly; the
+// (probability 2^-53) rejection case falls back to the general routine.
+__device__ __forceinline__ double normal_at(uint64_t key, uint64_t idx) {
+    u64x2 b = threefry2x64_13(idx, 0, key);
+    if (b.x >= 0xFFFFFFFFFFFFFC00ULL || b.y >= 0xFFFFFFFFFFFFFC00ULL) {
+        MicroUrng u(key, idx);
+        return boost_normal(u);
+    }
+    double r1 = u64_to_double_rn(b.y) * 0x1p-64;
+    double r2 = u64_to_double_rn(b.x) * 0x1p-64;
+    double rho = sqrt(__dmul_rn(-2.0, log(__dsub_rn(1.0, r2))));
+    return __dmul_rn(rho, cos(__dmul_rn(2.0 * SKB_BOOST_PI, r1)));
+}
+
+__device__ __forceinline__ double cauchy_at(uint64_t key, uint64_t idx) {
+    MicroUrng u(key, idx);
+    return boost_cauchy(u);
+}
+#endif
+
+// boost::random::uniform_real_distribution(a,b)
+__host__ __device__ __forceinline__ double boost_uniform_real(MicroUrng &u, double a,
+                                                              double b) {
+    for (;;) {
+        double num = u64_to_double(u.next());
+#ifdef __CUDA_ARCH__
+        double r = __dadd_rn(__dmul_rn(num * 0x1p-64, b - a), a);   // no fma contraction
+#else
+        double r = num / 0x1p64 * (b - a) + a;
+#endif
+        if (r < b) return r;
+    }
+}
+
+}  // namespace skb

@@ -1,0 +1,336 @@
+"""Sketch transforms -- Python-3 counterpart of python-skylark/skylark/sketch.py.
+
+Same classes, constructor arguments, `apply(A, SA, dim)` protocol, `*` and `/` operators,
+serialisation and aliases as the reference (sketch.py:47-232, 238-620, 962-1003), for the
+transforms on the hot path: JLT, CT, FJLT, CWT, MMT, WZT, GaussianRFT, LaplacianRFT.
+Everything executes in libcskylark_b200.so on the GPU: `forceppy=True` (the reference's
+pure-Python fallback) is refused, because this package has no CPU path.
+
+Additions over the reference (all optional, existing calls keep their meaning):
+  * `context=` keyword -- or a `Context` as third positional argument -- selects an
+    explicit `lib.Context(seed, counter)` instead of the global one;
+  * torch CUDA tensors (float64; float32 for JLT/CT/RFT) and `lib.DeviceCSC` as A / SA;
+  * `apply_shard(A_local, SA, dim, index_offset)` for a row shard of the sketched
+    dimension and `apply_distributed(...)` which also sums the partial sketches over a
+    torch.distributed process group;
+  * `RFT` alias for `GaussianRFT`; table accessors used by the parity tests.
+"""
+import ctypes
+import json
+from ctypes import byref, c_char_p, c_double, c_void_p
+
+import numpy
+
+from . import errors, lib
+
+_libc = lib._libc
+
+
+def initialize(seed=-1):
+    """examples/example_sketch.py:53 calls sketch.initialize(seed); forward to lib."""
+    lib.initialize(seed)
+
+
+def finalize():
+    lib.finalize()
+
+
+def _supported():
+    raw = lib.lib.sl_supported_sketch_transforms().decode()
+    return [eval(tok) for tok in raw.split()]     # sketch.py:21
+
+
+SUPPORTED_SKETCH_TRANSFORMS = _supported()
+
+
+def deserialize_sketch(sketch_dict):
+    """Rebuild a transform from `.serialize()` output (sketch.py:33-42)."""
+    sketch_transform = c_void_p()
+    lib.callsl("sl_deserialize_sketch_transform", json.dumps(sketch_dict), byref(sketch_transform))
+    sketch_name = str(sketch_dict["sketch_type"])
+    return _map_csketch_type_to_cfun[sketch_name](sketch_dict, sketch_transform)
+
+
+def _split_context(defouttype, context):
+    """`T(n, s, context)` (third positional) is accepted next to `T(n, s, defouttype)`."""
+    if isinstance(defouttype, lib.Context):
+        if context is not None:
+            raise errors.ParameterMistmatchError("context given twice")
+        return None, defouttype
+    return defouttype, context
+
+
+class _SketchTransform(object):
+    """Base class of all sketch transforms (sketch.py:47-232)."""
+
+    def __init__(self, ttype, n, s, defouttype=None, forceppy=False, sketch_transform=None,
+                 context=None, params=()):
+        defouttype, context = _split_context(defouttype, context)
+        self._baseinit(ttype, n, s, defouttype, forceppy)
+        if sketch_transform is None:
+            sketch_transform = c_void_p()
+            ctx = lib.ctxt_obj if context is None else context._obj
+            lib.callsl("sl_create_sketch_transform", ctx, ttype, int(n), int(s),
+                       byref(sketch_transform), *[c_double(float(p)) for p in params])
+        self._obj = sketch_transform
+
+    def _baseinit(self, ttype, n, s, defouttype, forceppy):
+        if defouttype is not None and defouttype not in lib.map_to_ctor:
+            raise errors.UnsupportedError("Unsupported default output type (%s)" % defouttype)
+        if forceppy:
+            raise errors.UnsupportedError(
+                "forceppy: this package has no pure-Python / CPU implementation")
+        self._ttype = ttype
+        self._n = n
+        self._s = s
+        self._defouttype = defouttype
+        self._ppy = False
+
+    def __del__(self):
+        obj = getattr(self, "_obj", None)
+        if obj is not None and lib.lib is not None and getattr(obj, "value", obj):
+            lib.lib.sl_free_sketch_transform(obj)
+            self._obj = None
+
+    def serialize(self):
+        """Dictionary from which `deserialize_sketch` rebuilds the sketch (sketch.py:94-113)."""
+        json_data = c_char_p()
+        lib.callsl("sl_serialize_sketch_transform", self._obj, byref(json_data))
+        try:
+            return json.loads(json_data.value.decode())
+        finally:
+            _libc.free(json_data)
+
+    def __getstate__(self):
+        d = self.__dict__.copy()
+        if "_obj" in d:
+            d["_obj"] = self.serialize()
+        return d
+
+    def __setstate__(self, d):
+        self.__dict__ = d
+        sketch_transform = c_void_p()
+        lib.callsl("sl_deserialize_sketch_transform", json.dumps(d["_obj"]), byref(sketch_transform))
+        self._obj = sketch_transform
+
+    # -- apply ---------------------------------------------------------------
+    @staticmethod
+    def _normdim(dim):
+        if dim == 0 or dim == "columnwise" or dim == "left":
+            return 0
+        if dim == 1 or dim == "rowwise" or dim == "right":
+            return 1
+        raise ValueError("Dimension must be either columnwise/rowwise or left/right or 0/1")
+
+    def _prepare(self, A, SA, dim, local_n=None):
+        A = lib.adapt(A)
+        if SA is None:
+            ctor = A.getctor() if self._defouttype is None else lib.map_to_ctor[self._defouttype]
+            if dim == 0:
+                SA = ctor(self._s, A.getdim(1), A)
+            else:
+                SA = ctor(A.getdim(0), self._s, A)
+        SA = lib.adapt(SA)
+        reqcomb = (self._ttype, A.ctype(), SA.ctype())
+        if reqcomb not in SUPPORTED_SKETCH_TRANSFORMS:
+            raise errors.UnsupportedError("Unsupported transform-input-output combination: "
+                                          + str(reqcomb))
+        incomp, cinvert = A.iscompatible(SA)
+        if incomp is not None:
+            raise errors.UnsupportedError("Input and output are incompatible: " + incomp)
+        want_n = self._n if local_n is None else local_n
+        if A.getdim(dim) != want_n:
+            raise errors.DimensionMistmatchError("Sketched dimension is incorrect (input)")
+        if SA.getdim(dim) != self._s:
+            raise errors.DimensionMistmatchError("Sketched dimension is incorrect (output)")
+        if A.getdim(1 - dim) != SA.getdim(1 - dim):
+            raise errors.DimensionMistmatchError("Sketched dimension is incorrect (input != output)")
+        return A, SA, cinvert
+
+    def apply(self, A, SA=None, dim=0):
+        """Apply the transform to A along `dim` and write SA (allocated when None).
+        dim: 0 / "columnwise" / "left" gives S*A; 1 / "rowwise" / "right" gives A*S^T
+        (sketch.py:130-200)."""
+        dim = self._normdim(dim)
+        A, SA, cinvert = self._prepare(A, SA, dim)
+        self._call(A, SA, (1 - dim) if cinvert else dim, None)
+        return SA.getobj()
+
+    def apply_shard(self, A_local, SA=None, dim=0, index_offset=0):
+        """A_local holds sketched indices [index_offset, index_offset + local) of the
+        transform's input dimension; SA receives this shard's partial sketch.  Summing the
+        partial sketches of a partition of [0, n) gives `apply` of the whole matrix -- the
+        local step of sketch/hash_transform_Elemental.hpp:543-561 and
+        sketch/dense_transform_Elemental_coldist_star.hpp:200-229."""
+        dim = self._normdim(dim)
+        A = lib.adapt(A_local)
+        A, SA, cinvert = self._prepare(A, SA, dim, local_n=A.getdim(dim))
+        self._call(A, SA, (1 - dim) if cinvert else dim, int(index_offset))
+        return SA.getobj()
+
+    def _call(self, A, SA, cdim, offset):
+        if isinstance(A, (lib.TorchAdapter, lib.DeviceCSCAdapter)):
+            lib.set_stream_from_torch()
+        Aobj = A.ptr()
+        try:
+            SAobj = SA.ptr()
+            try:
+                if offset is None:
+                    lib.callsl("sl_apply_sketch_transform", self._obj, A.ctype(), Aobj,
+                               SA.ctype(), SAobj, cdim + 1)
+                else:
+                    lib.callsl("sl_apply_sketch_transform_shard", self._obj, A.ctype(), Aobj,
+                               SA.ctype(), SAobj, cdim + 1, offset)
+            finally:
+                SA.ptrcleaner()
+        finally:
+            A.ptrcleaner()
+
+    def apply_distributed(self, A_local, SA=None, dim=0, index_offset=0, group=None,
+                          reduce="allreduce", dst=0):
+        """Row-sharded sketch over a torch.distributed group: every rank sketches its shard
+        of the sketched dimension, then the partial sketches are summed.
+        reduce = "allreduce"      replicated result  (reference: -> SharedMatrix [*,*],
+                                  sketch/hash_transform_Elemental.hpp:557-561)
+                 "reduce"         result on rank `dst` (-> RootMatrix [o,o], :360-366)
+                 "reduce_scatter" each rank keeps a contiguous slice of the rows of SA's
+                                  storage (-> [VC,*]-like, El::AxpyContract at
+                                  sketch/dense_transform_Elemental_coldist_star.hpp:228)
+                 None             no collective (caller reduces)"""
+        from . import dist
+        return dist.apply_distributed(self, A_local, SA, dim, index_offset, group, reduce, dst)
+
+    def __mul__(self, A):
+        return self.apply(A, None, dim=0)
+
+    def __truediv__(self, A):
+        return self.apply(A, None, dim=1)
+
+    __div__ = __truediv__
+
+    def getindim(self):
+        return self._n
+
+    def getsketchdim(self):
+        return self._s
+
+    # -- generated state, for parity tests -------------------------------------
+    def _export(self, what, count, dtype):
+        out = numpy.empty(count, dtype=dtype)
+        lib.callsl("sl_sketch_export", self._obj, what, 0, int(count), out.ctypes.data_as(c_void_p))
+        return out
+
+    def export_dense(self, i0=0, j0=0, h=None, w=None):
+        """S[i0:i0+h, j0:j0+w] of a dense transform, generated on the device."""
+        h = self._s - i0 if h is None else h
+        w = self._n - j0 if w is None else w
+        out = numpy.empty((h, w), dtype=numpy.float64, order="F")
+        lib.callsl("sl_sketch_export_dense", self._obj, int(i0), int(j0), int(h), int(w),
+                   out.ctypes.data_as(c_void_p))
+        return out
+
+
+class JLT(_SketchTransform):
+    """Johnson-Lindenstrauss: dense i.i.d. N(0,1)/sqrt(s) map (sketch.py:238-301)."""
+
+    def __init__(self, n, s, defouttype=None, forceppy=False, sketch_transform=None, context=None):
+        super().__init__("JLT", n, s, defouttype, forceppy, sketch_transform, context)
+
+
+class CT(_SketchTransform):
+    """Cauchy transform: dense i.i.d. Cauchy * C/s (sketch.py:340-375)."""
+
+    def __init__(self, n, s, C, defouttype=None, forceppy=False, sketch_transform=None, context=None):
+        self._C = C
+        super().__init__("CT", n, s, defouttype, forceppy, sketch_transform, context, params=(C,))
+
+
+class FJLT(_SketchTransform):
+    """Fast Johnson-Lindenstrauss: sqrt(n/s) * sample(DCT-II(D x)) (sketch.py:377-407)."""
+
+    def __init__(self, n, s, defouttype=None, forceppy=False, sketch_transform=None, context=None):
+        super().__init__("FJLT", n, s, defouttype, forceppy, sketch_transform, context)
+
+    def diagonal(self):
+        return self._export("D", self._n, numpy.float64)
+
+    def samples(self):
+        return self._export("samples", self._s, numpy.int64)
+
+
+class _HashTransform(_SketchTransform):
+    def row_idx(self):
+        return self._export("row_idx", self._n, numpy.int64)
+
+    def row_value(self):
+        return self._export("row_value", self._n, numpy.float64)
+
+
+class CWT(_HashTransform):
+    """Clarkson-Woodruff (CountSketch) transform (sketch.py:409-440)."""
+
+    def __init__(self, n, s, defouttype=None, forceppy=False, sketch_transform=None, context=None):
+        super().__init__("CWT", n, s, defouttype, forceppy, sketch_transform, context)
+
+
+class MMT(_HashTransform):
+    """Meng-Mahoney transform: CountSketch with Cauchy values (sketch.py:442-471)."""
+
+    def __init__(self, n, s, defouttype=None, forceppy=False, sketch_transform=None, context=None):
+        super().__init__("MMT", n, s, defouttype, forceppy, sketch_transform, context)
+
+
+class WZT(_HashTransform):
+    """Woodruff-Zhang transform for l_p, 1 <= p <= 2 (sketch.py:473-526)."""
+
+    def __init__(self, n, s, p, defouttype=None, forceppy=False, sketch_transform=None, context=None):
+        self._p = p
+        super().__init__("WZT", n, s, defouttype, forceppy, sketch_transform, context, params=(p,))
+
+
+class _RFT(_SketchTransform):
+    def shifts(self):
+        return self._export("shifts", self._s, numpy.float64)
+
+    def scales(self):
+        return self._export("scales", self._s, numpy.float64)
+
+
+class GaussianRFT(_RFT):
+    """Random Fourier features of the Gaussian kernel (sketch.py:528-563)."""
+
+    def __init__(self, n, s, sigma=1.0, defouttype=None, forceppy=False, sketch_transform=None,
+                 context=None):
+        self._sigma = sigma
+        super().__init__("GaussianRFT", n, s, defouttype, forceppy, sketch_transform, context,
+                         params=(sigma,))
+
+
+class LaplacianRFT(_RFT):
+    """Random Fourier features of the Laplacian kernel (sketch.py:565-590)."""
+
+    def __init__(self, n, s, sigma=1.0, defouttype=None, forceppy=False, sketch_transform=None,
+                 context=None):
+        self._sigma = sigma
+        super().__init__("LaplacianRFT", n, s, defouttype, forceppy, sketch_transform, context,
+                         params=(sigma,))
+
+
+# Additional names (sketch.py:962-970); FastJLT = JLT is the reference's own aliasing.
+FastJLT = JLT
+CountSketch = CWT
+RRT = GaussianRFT
+RFT = GaussianRFT
+
+_map_csketch_type_to_cfun = {
+    "JLT": lambda sd, obj: JLT(int(sd["N"]), int(sd["S"]), None, False, obj),
+    "CT": lambda sd, obj: CT(int(sd["N"]), int(sd["S"]), float(sd["C"]), None, False, obj),
+    "FJLT": lambda sd, obj: FJLT(int(sd["N"]), int(sd["S"]), None, False, obj),
+    "CWT": lambda sd, obj: CWT(int(sd["N"]), int(sd["S"]), None, False, obj),
+    "MMT": lambda sd, obj: MMT(int(sd["N"]), int(sd["S"]), None, False, obj),
+    "WZT": lambda sd, obj: WZT(int(sd["N"]), int(sd["S"]), float(sd["P"]), None, False, obj),
+    "GaussianRFT": lambda sd, obj: GaussianRFT(int(sd["N"]), int(sd["S"]), float(sd["sigma"]),
+                                               None, False, obj),
+    "LaplacianRFT": lambda sd, obj: LaplacianRFT(int(sd["N"]), int(sd["S"]), float(sd["sigma"]),
+                                                 None, False, obj),
+}
