@@ -1,0 +1,339 @@
+#!/usr/bin/env python
+"""Benchmark of the sketch-apply hot path (contract: see the task statement / DESIGN.md).
+
+Workload (N = 1): BASELINE.json configs[1] -- JLT Gaussian columnwise sketch of a dense fp64
+1,000,000 x 1024 matrix to s = 4096 on one B200.  A "step" is one apply: 2*s*n*d flop.
+N > 1 is weak scaling: every rank holds its own 1,000,000-row shard of an (N*1e6) x 1024
+matrix, sketches it with global row indices and the 33.5 MB partial sketches are summed with
+an NCCL all-reduce inside the step (the exchange step of a row-sharded columnwise sketch).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+`--impl reference` times the reference's CPU algorithm for the same path (the oracle port:
+realise S entry by entry from the counter stream, then BLAS dgemm) on the host cores.
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_ROWS, D_COLS, S_ROWS = 1_000_000, 1024, 4096
+SKETCH_SEED = 123834      # python-skylark/skylark/examples/example_sketch.py:53
+DATA_SEED = 0
+METRIC = "JLT columnwise sketch throughput (2*s*n*d flop per apply)"
+UNIT = "TFLOP/s"
+WORKLOAD = "C2: JLT fp64 1000000x1024 -> s=4096, columnwise, row-major A"
+
+
+def flops_per_step(n_rows):
+    return 2.0 * S_ROWS * n_rows * D_COLS
+
+
+# ---------------------------------------------------------------------------
+# reference arm / cpu_baseline: the oracle port on the host cores
+# ---------------------------------------------------------------------------
+def cpu_reference_sample(n_sample, repeats=1):
+    """Times the reference's CPU path (dense_transform_data.hpp:79-101 realisation +
+    dense_transform_Elemental_local.hpp:97-111 Gemm) on the first n_sample rows."""
+    import numpy as np
+    from oracle import oracle as o
+    o.lib()
+    try:
+        import torch
+        torch.set_num_threads(os.cpu_count() or 1)
+    except Exception:
+        torch = None
+    rng = np.random.default_rng(DATA_SEED)
+    A = rng.standard_normal((n_sample, D_COLS))
+    ctx = o.Context(SKETCH_SEED)
+    t = o.JLT(N_ROWS, S_ROWS, ctx)
+    times = []
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        R = o.realize_dense(t.seed, t.base, 0, t.scale, S_ROWS, 0, 0, S_ROWS, n_sample)
+        SA = R @ A
+        times.append(time.perf_counter() - t0)
+    del SA
+    dt = statistics.median(times)
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    return {"seconds": dt, "tflops": flops_per_step(n_sample) / dt / 1e12, "cores": cores,
+            "threads": o.num_threads(),
+            "sample": "first %d of %d rows (time is linear in rows): S realised entry by entry "
+                      "(Threefry2x64-13 + Box-Muller, OpenMP) then numpy dgemm" % (n_sample, N_ROWS)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n_sample = 8192
+    for _ in range(args.warmup if args.warmup < 2 else 1):
+        cpu_reference_sample(1024)
+    res = [cpu_reference_sample(n_sample) for _ in range(max(1, min(args.steps, 3)))]
+    dt = statistics.median(r["seconds"] for r in res)
+    val = flops_per_step(n_sample) / dt / 1e12
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": len(res), "warmup": 1, "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "note": "reference CPU algorithm (oracle port; the "
+                       "Elemental/MPI build is unavailable on this box), bounded sample"},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": res[0]["cores"], "kind": "port",
+                             "sample": res[0]["sample"]},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------
+# clocks sampler
+# ---------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for name, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------
+# ours
+# ---------------------------------------------------------------------------
+def measure_fp64_gemm_peak(torch):
+    """cuBLAS DGEMM 8192^3 through torch.matmul, best of 5 -- the FP64 counterpart of the
+    driver's bf16 figure in MEASURED_PEAKS.json (which has no FP64 entry)."""
+    n = 8192
+    a = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    b = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    torch.matmul(a, b)
+    torch.cuda.synchronize()
+    best = float("inf")
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); torch.matmul(a, b); e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, b
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this package has no CPU path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    from libskylark_b200 import lib, sketch
+    from libskylark_b200.dist import reduce_partial
+
+    n_total = N_ROWS * world
+    ctx = lib.Context(SKETCH_SEED)
+    S = sketch.JLT(n_total, S_ROWS, ctx)
+    offset = rank * N_ROWS
+
+    gen = torch.Generator(device="cuda").manual_seed(DATA_SEED + rank)
+    A = torch.randn(N_ROWS, D_COLS, dtype=torch.float64, device="cuda", generator=gen)
+    SA = torch.empty(S_ROWS, D_COLS, dtype=torch.float64, device="cuda")
+
+    def step():
+        S.apply_shard(A, SA, "columnwise", offset)
+        if world > 1:
+            reduce_partial(SA, None, "allreduce")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+
+    lib.profile_reset()
+    lib.profile_enable(True)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    elapsed_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    prof = lib.profile_read()
+    lib.profile_enable(False)
+    if world > 1:
+        t = torch.tensor([elapsed_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+    ms_per_step = elapsed_ms / args.steps
+    value = flops_per_step(N_ROWS) * world / (ms_per_step * 1e-3) / 1e12
+
+    # ---- end-to-end: host buffers through the C ABI, copies inside the timed region ----
+    e2e_steps = max(1, min(args.steps, 3))
+    h2d = N_ROWS * D_COLS * 8
+    d2h = S_ROWS * D_COLS * 8
+    L = lib.lib
+    hA, hSA = ctypes.c_void_p(), ctypes.c_void_p()
+    lib.callsl("sl_host_alloc_pinned", h2d, ctypes.byref(hA))
+    lib.callsl("sl_host_alloc_pinned", d2h, ctypes.byref(hSA))
+    hA_t = torch.frombuffer((ctypes.c_char * h2d).from_address(hA.value), dtype=torch.float64)
+    hA_t.view(N_ROWS, D_COLS).copy_(A)
+    torch.cuda.synchronize()
+    Aw, SAw = ctypes.c_void_p(), ctypes.c_void_p()
+    # row-major n x d == column-major d x n: wrap the transpose, flip the direction
+    # (python-skylark/skylark/lib.py:113-123)
+    lib.callsl("sl_wrap_raw_matrix", ctypes.cast(hA, ctypes.POINTER(ctypes.c_double)), D_COLS,
+               N_ROWS, ctypes.byref(Aw))
+    lib.callsl("sl_wrap_raw_matrix", ctypes.cast(hSA, ctypes.POINTER(ctypes.c_double)), D_COLS,
+               S_ROWS, ctypes.byref(SAw))
+    lib.callsl("sl_set_stream", ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+
+    def e2e_step():
+        lib.callsl("sl_apply_sketch_transform_shard", S._obj, "Matrix", Aw, "Matrix", SAw, 2,
+                   offset)
+        if world > 1:     # partial sketches are summed on the device, result read back
+            part = torch.frombuffer((ctypes.c_char * d2h).from_address(hSA.value),
+                                    dtype=torch.float64).cuda(non_blocking=True)
+            dist.all_reduce(part)
+            part.cpu()
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_val = flops_per_step(N_ROWS) * world / e2e_s / 1e12
+    lib.callsl("sl_free_raw_matrix_wrap", Aw)
+    lib.callsl("sl_free_raw_matrix_wrap", SAw)
+    del hA_t
+    L.sl_host_free_pinned(hA)
+    L.sl_host_free_pinned(hSA)
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel (the FP64 tensor-core GEMM) ----
+    gemm_launches, gemm_ms = prof["dense_gemm"]
+    gen_launches, gen_ms = prof["dense_gen"]
+    launches = sum(v[0] for v in prof.values())
+    flops_per_launch = flops_per_step(N_ROWS) * args.steps / max(1, gemm_launches)
+    peak = measure_fp64_gemm_peak(torch)
+    achieved = flops_per_launch / (gemm_ms / max(1, gemm_launches) * 1e-3) / 1e12 if gemm_ms else None
+    roofline = {"bound": "tensor", "kernel": "k_dense_gemm (FP64 DMMA m8n8k4)",
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul fp64, best of 5, measured in "
+                               "this run (MEASURED_PEAKS.json has no FP64 entry)",
+                "flops_per_launch": flops_per_launch,
+                "kernel_ms_per_step": {"dense_gemm": gemm_ms / args.steps,
+                                       "dense_gen": gen_ms / args.steps},
+                "launches_per_step": {"dense_gemm": gemm_launches / args.steps,
+                                      "dense_gen": gen_launches / args.steps}}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        roofline["hbm_gbs_measured"] = peaks.get("hbm_gbs")
+    except Exception:
+        pass
+
+    cpu = cpu_reference_sample(8192)
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "rows_per_gpu": N_ROWS, "d": D_COLS, "s": S_ROWS,
+                       "sketch_seed": SKETCH_SEED, "partition": "row shards, allreduce of the s x d "
+                       "partial" if world > 1 else "single GPU",
+                       "l2": "inputs (8.19 GB per GPU) are larger than the 126 MB L2"},
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
+                    "path": "sl_apply_sketch_transform_shard on pinned HOST buffers (C ABI)"},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
+            "cpu_baseline": {"value": cpu["tflops"], "unit": UNIT, "cores": cpu["cores"],
+                             "kind": "port", "sample": cpu["sample"], "seconds": cpu["seconds"]}}
+    print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

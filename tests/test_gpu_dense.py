@@ -1,0 +1,110 @@
+"""JLT / CT / random Fourier features on the GPU (through the C ABI) against the oracle."""
+import numpy as np
+import pytest
+
+from util import rel_fro
+
+pytestmark = pytest.mark.gpu
+TOL64 = 1e-12   # BASELINE.json: 1e-12 relative Frobenius in fp64
+TOL32 = 1e-5    #                1e-5 in fp32
+
+
+def _ctx(sk, oracle, seed, counter=0):
+    from libskylark_b200 import lib
+    return lib.Context(seed, counter), oracle.Context(seed, counter)
+
+
+@pytest.mark.parametrize("shape", [(300, 70, 45), (128, 128, 128), (1000, 257, 3), (17, 5, 200),
+                                   (2048, 130, 131)])
+@pytest.mark.parametrize("T", ["JLT", "CT"])
+def test_numpy_both_orders_both_dims(sk, oracle, T, shape):
+    n, s, d = shape
+    c, oc = _ctx(sk, oracle, 21)
+    S, O = (sk.JLT(n, s, c), oracle.JLT(n, s, oc)) if T == "JLT" else \
+           (sk.CT(n, s, 1.5, c), oracle.CT(n, s, 1.5, oc))
+    rng = np.random.default_rng(7)
+    A = rng.standard_normal((n, d))
+    want = O.apply(A, "columnwise")
+    assert rel_fro(S.apply(A.copy(), None, "columnwise"), want) < TOL64
+    assert rel_fro(S.apply(np.asfortranarray(A), None, 0), want) < TOL64
+    B = rng.standard_normal((d, n))
+    want = O.apply(B, "rowwise")
+    assert rel_fro(S.apply(B.copy(), None, "rowwise"), want) < TOL64
+    assert rel_fro(S.apply(np.asfortranarray(B), None, 1), want) < TOL64
+
+
+def test_many_panels_and_shards(sk, oracle):
+    import torch
+    n, s, d = 20000, 48, 72      # panel cap 8192 rows -> 3 panels
+    c, oc = _ctx(sk, oracle, 5, 12345)
+    S, O = sk.JLT(n, s, c), oracle.JLT(n, s, oc)
+    A = torch.randn(n, d, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(1))
+    want = O.apply(A.cpu().numpy(), "columnwise")
+    SA = S.apply(A, None, "columnwise")
+    assert rel_fro(SA.cpu().numpy(), want) < TOL64
+    # column-major tensor takes the other kernel layout
+    SAf = S.apply(A.t().contiguous().t(), None, 0)
+    assert rel_fro(SAf.cpu().numpy(), want) < TOL64
+    # row shards with global input indices sum to the full sketch
+    parts = sum(S.apply_shard(A[o:o + k], None, 0, o) for o, k in ((0, 7001), (7001, 9999), (17000, 3000)))
+    assert rel_fro(parts.cpu().numpy(), want) < TOL64
+    # linearity
+    B = torch.randn(n, d, dtype=torch.float64, device="cuda")
+    lhs = S.apply(A + 0.5 * B, None, 0)
+    assert rel_fro(lhs.cpu().numpy(), (SA + 0.5 * S.apply(B, None, 0)).cpu().numpy()) < 1e-13
+
+
+def test_tile_mode_direct_store(sk, oracle):
+    import torch
+    n, s, m = 40, 256, 38400      # 2 x 300 output tiles >= 4*148 -> whole-tile partition
+    c, oc = _ctx(sk, oracle, 8)
+    S, O = sk.JLT(n, s, c), oracle.JLT(n, s, oc)
+    A = torch.randn(m, n, dtype=torch.float64, device="cuda")
+    got = S.apply(A, None, "rowwise")
+    assert rel_fro(got.cpu().numpy(), O.apply(A.cpu().numpy(), "rowwise")) < TOL64
+
+
+@pytest.mark.parametrize("T", ["GaussianRFT", "LaplacianRFT"])
+def test_rft_fp64(sk, oracle, T):
+    import torch
+    n, s = 60, 200
+    c, oc = _ctx(sk, oracle, 13)
+    S = getattr(sk, T)(n, s, 2.5, context=c)
+    O = getattr(oracle, T)(n, s, 2.5, oc)
+    rng = np.random.default_rng(3)
+    X = rng.uniform(0, 1, (500, n))
+    want = O.apply(X, "rowwise")
+    assert rel_fro(S.apply(X.copy(), None, "rowwise"), want) < TOL64
+    assert rel_fro(S.apply(np.asfortranarray(X), None, 1), want) < TOL64
+    Xc = rng.uniform(0, 1, (n, 33))
+    assert rel_fro(S.apply(Xc.copy(), None, "columnwise"), O.apply(Xc, "columnwise")) < TOL64
+    # feature-map shape that takes the fused-epilogue (whole tile) path
+    Xb = torch.rand(80000, n, dtype=torch.float64, device="cuda")
+    got = S.apply(Xb, None, "rowwise")
+    assert rel_fro(got.cpu().numpy(), O.apply(Xb.cpu().numpy(), "rowwise")) < TOL64
+    assert float(got.abs().max()) <= np.sqrt(2.0 / s) * (1 + 1e-15)
+    with pytest.raises(Exception):
+        S.apply_shard(Xc[:30].copy(), None, 0, 0)       # cosine is not additive over shards
+
+
+def test_fp32_tensors(sk, oracle):
+    import torch
+    n, s = 784, 512
+    c, oc = _ctx(sk, oracle, 99)
+    S, O = sk.GaussianRFT(n, s, 10.0, context=c), oracle.GaussianRFT(n, s, 10.0, oc)
+    X = torch.rand(3000, n, dtype=torch.float32, device="cuda")
+    got = S.apply(X, None, "rowwise")
+    assert got.dtype == torch.float32
+    want = O.apply(X.cpu().numpy().astype(np.float64), "rowwise")
+    assert rel_fro(got.cpu().numpy(), want) < TOL32
+    # the reference's own float path (S cast to float, sgemm, float epilogue) is no closer
+    ref32 = O.apply(X.cpu().numpy(), "rowwise", dtype=np.float32)
+    assert rel_fro(got.cpu().numpy(), ref32) < TOL32
+    Xl = torch.rand(80000, 64, dtype=torch.float32, device="cuda")    # whole-tile path, float
+    S2, O2 = sk.GaussianRFT(64, 256, 1.0, context=c), oracle.GaussianRFT(64, 256, 1.0, oc)
+    got = S2.apply(Xl, None, "rowwise")
+    assert rel_fro(got.cpu().numpy(), O2.apply(Xl.cpu().numpy().astype(np.float64), "rowwise")) < TOL32
+    J, OJ = sk.JLT(5000, 40, context=c), oracle.JLT(5000, 40, oc)
+    A = torch.randn(5000, 100, dtype=torch.float32, device="cuda")
+    got = J.apply(A, None, "columnwise")
+    assert rel_fro(got.cpu().numpy(), OJ.apply(A.cpu().numpy().astype(np.float64), "columnwise")) < TOL32

@@ -1,0 +1,47 @@
+"""FJLT on the GPU against the oracle: DCT-II mode (what the reference computes) and the
+Walsh-Hadamard mode named by BASELINE.json."""
+import numpy as np
+import pytest
+
+from util import rel_fro
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+
+
+@pytest.mark.parametrize("fut", ["dct", "wht"])
+@pytest.mark.parametrize("shape", [(64, 16, 5), (1024, 100, 33), (4096, 512, 8)])
+def test_fjlt_power_of_two(sk, oracle, fut, shape):
+    from libskylark_b200 import lib
+    n, s, d = shape
+    lib.set_option("fjlt_fut", fut)
+    try:
+        S = sk.FJLT(n, s, lib.Context(17))
+    finally:
+        lib.set_option("fjlt_fut", "dct")
+    O = oracle.FJLT(n, s, oracle.Context(17))
+    A = np.random.default_rng(5).standard_normal((n, d))
+    want = O.apply(A, "columnwise", fut=fut)
+    assert rel_fro(S.apply(np.asfortranarray(A), None, "columnwise"), want) < TOL
+    assert rel_fro(S.apply(A.copy(), None, 0), want) < TOL
+    B = np.ascontiguousarray(A.T)
+    assert rel_fro(S.apply(B, None, "rowwise"), want.T) < TOL
+
+
+def test_fjlt_general_n_dct(sk, oracle):
+    from libskylark_b200 import lib
+    n, s, d = 300, 40, 7
+    S, O = sk.FJLT(n, s, lib.Context(3)), oracle.FJLT(n, s, oracle.Context(3))
+    A = np.random.default_rng(6).standard_normal((n, d))
+    assert rel_fro(S.apply(np.asfortranarray(A), None, 0), O.apply(A, "columnwise")) < TOL
+
+
+def test_fjlt_wht_needs_power_of_two(sk):
+    from libskylark_b200 import errors, lib
+    lib.set_option("fjlt_fut", "wht")
+    try:
+        S = sk.FJLT(300, 40, lib.Context(3))
+    finally:
+        lib.set_option("fjlt_fut", "dct")
+    with pytest.raises(errors.LowerLayerError):
+        S.apply(np.zeros((300, 4), order="F"), None, 0)

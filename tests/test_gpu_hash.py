@@ -1,0 +1,160 @@
+"""CWT / MMT / WZT apply on the GPU (through the C ABI) against the oracle."""
+import ctypes
+
+import numpy as np
+import pytest
+import scipy.sparse
+
+from util import rel_fro
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12   # BASELINE.json: SA within 1e-12 relative Frobenius error in fp64
+
+
+def _pair(sk, oracle, T, n, s, seed=11):
+    from libskylark_b200 import lib
+    c, oc = lib.Context(seed), oracle.Context(seed)
+    if T == "CWT":
+        return sk.CWT(n, s, c), oracle.CWT(n, s, oc)
+    if T == "MMT":
+        return sk.MMT(n, s, c), oracle.MMT(n, s, oc)
+    return sk.WZT(n, s, 1.5, c), oracle.WZT(n, s, 1.5, oc)
+
+
+@pytest.mark.parametrize("T", ["CWT", "MMT", "WZT"])
+@pytest.mark.parametrize("shape", [(1000, 37, 64), (257, 8, 1), (5000, 7, 130), (300, 1000, 17),
+                                   (4000, 7000, 5)])
+def test_numpy_both_orders_both_dims(sk, oracle, T, shape):
+    n, s, d = shape
+    S, O = _pair(sk, oracle, T, n, s)
+    rng = np.random.default_rng(1)
+    A = rng.standard_normal((n, d))
+    want = O.apply(A, "columnwise")
+    assert rel_fro(S.apply(A.copy(), None, "columnwise"), want) < TOL          # C order
+    assert rel_fro(S.apply(np.asfortranarray(A), None, 0), want) < TOL         # F order
+    assert rel_fro(S * A.copy(), want) < TOL
+    B = rng.standard_normal((d, n))
+    want = O.apply(B, "rowwise")
+    assert rel_fro(S.apply(B.copy(), None, "rowwise"), want) < TOL
+    assert rel_fro(S.apply(np.asfortranarray(B), None, 1), want) < TOL
+    assert rel_fro(S / B.copy(), want) < TOL
+
+
+def test_cwt_rows_layout_is_bit_exact_when_buckets_are_short(sk, oracle):
+    # every bucket <= 32 rows -> no atomics, rows added in ascending order with separate
+    # multiply and add: the reference loop's exact result (hash_transform_Elemental.hpp:106-123)
+    n, s, d = 20000, 4000, 96
+    S, O = _pair(sk, oracle, "CWT", n, s, seed=3)
+    assert np.bincount(O.row_idx.astype(int), minlength=s).max() <= 32
+    A = np.random.default_rng(2).standard_normal((n, d))
+    got = S.apply(A.copy(), None, "columnwise")
+    assert np.array_equal(got, O.apply(A, "columnwise"))
+    S2, O2 = _pair(sk, oracle, "MMT", n, s, seed=3)
+    got, want = S2.apply(A.copy(), None, 0), O2.apply(A, "columnwise")
+    assert rel_fro(got, want) < 1e-15     # values differ by <= 2 ulp, sums follow
+
+
+@pytest.mark.parametrize("fmt", ["csc", "csr"])
+@pytest.mark.parametrize("T", ["CWT", "MMT"])
+def test_scipy_sparse_input(sk, oracle, T, fmt):
+    n, s, d = 3000, 64, 41
+    S, O = _pair(sk, oracle, T, n, s)
+    A = scipy.sparse.random(n, d, 0.05, format=fmt, random_state=3, dtype=np.float64)
+    want = O.apply(A.toarray(), "columnwise")
+    got = S.apply(A, None, "columnwise")
+    assert isinstance(got, np.ndarray) and got.shape == (s, d)
+    assert rel_fro(got, want) < TOL
+    B = scipy.sparse.random(d, n, 0.05, format=fmt, random_state=4, dtype=np.float64)
+    assert rel_fro(S.apply(B, None, "rowwise"), O.apply(B.toarray(), "rowwise")) < TOL
+    # empty matrix and empty columns
+    E = scipy.sparse.csc_matrix((n, 5)) if fmt == "csc" else scipy.sparse.csr_matrix((n, 5))
+    assert np.count_nonzero(S.apply(E, None, 0)) == 0
+
+
+def test_sparse_large_sketch_uses_global_path(sk, oracle):
+    n, s, d = 2000, 40000, 9           # S*8 > shared memory
+    S, O = _pair(sk, oracle, "CWT", n, s)
+    A = scipy.sparse.random(n, d, 0.1, format="csc", random_state=5, dtype=np.float64)
+    assert rel_fro(S.apply(A, None, 0), O.apply(A.toarray(), "columnwise")) < TOL
+
+
+def test_torch_tensors_and_views(sk, oracle):
+    import torch
+    n, s, d = 6000, 100, 250
+    S, O = _pair(sk, oracle, "CWT", n, s)
+    A = torch.randn(n, d, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(0))
+    want = O.apply(A.cpu().numpy(), "columnwise")
+    got = S.apply(A, None, "columnwise")
+    assert got.is_cuda and got.shape == (s, d) and got.is_contiguous()
+    assert rel_fro(got.cpu().numpy(), want) < TOL
+    At = A.t().contiguous().t()                     # column-major tensor
+    got = S.apply(At, None, 0)
+    assert got.stride(0) == 1
+    assert rel_fro(got.cpu().numpy(), want) < TOL
+    # strided view (leading dimension > width) and preallocated output
+    big = torch.zeros(n, d + 6, dtype=torch.float64, device="cuda")
+    big[:, :d] = A
+    out = torch.empty(s, d, dtype=torch.float64, device="cuda")
+    S.apply(big[:, :d], out, 0)
+    assert rel_fro(out.cpu().numpy(), want) < TOL
+    B = A.t().contiguous()                          # d x n row-major, rowwise
+    assert rel_fro(S.apply(B, None, "rowwise").cpu().numpy(), want.T) < TOL
+
+
+def test_device_csc(sk, oracle):
+    import torch
+    from libskylark_b200 import lib
+    n, s, d = 5000, 300, 77
+    S, O = _pair(sk, oracle, "MMT", n, s)
+    A = scipy.sparse.random(n, d, 0.02, format="csc", random_state=6, dtype=np.float64)
+    dev = lib.DeviceCSC(torch.tensor(A.indptr, dtype=torch.int32, device="cuda"),
+                        torch.tensor(A.indices, dtype=torch.int32, device="cuda"),
+                        torch.tensor(A.data, dtype=torch.float64, device="cuda"), A.shape)
+    got = S.apply(dev, None, "columnwise")
+    assert got.shape == (s, d) and got.stride(0) == 1
+    assert rel_fro(got.cpu().numpy(), O.apply(A.toarray(), "columnwise")) < TOL
+
+
+def test_config1_full_size_parity_and_properties(sk, oracle):
+    # BASELINE.json configs[0]: CWT columnwise, dense fp64 100k x 500 -> s = 2000
+    import torch
+    n, d, s = 100000, 500, 2000
+    S, O = _pair(sk, oracle, "CWT", n, s, seed=123834)
+    A = torch.randn(n, d, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(0))
+    SA = S.apply(A, None, "columnwise")
+    assert rel_fro(SA.cpu().numpy(), O.apply(A.cpu().numpy(), "columnwise")) < TOL
+    # size-independent properties: column sums are preserved up to sign pattern ...
+    signs = torch.tensor(O.row_value, device="cuda")
+    assert torch.allclose(SA.sum(0), (signs[:, None] * A).sum(0), rtol=1e-9, atol=1e-9)
+    # ... linearity, and shard additivity
+    B = torch.randn(n, d, dtype=torch.float64, device="cuda")
+    lhs = S.apply(2.0 * A - 3.0 * B, None, 0)
+    rhs = 2.0 * SA - 3.0 * S.apply(B, None, 0)
+    assert rel_fro(lhs.cpu().numpy(), rhs.cpu().numpy()) < 1e-13
+    parts = sum(S.apply_shard(A[o:o + c], None, 0, o) for o, c in ((0, 33333), (33333, 40000), (73333, 26667)))
+    assert rel_fro(parts.cpu().numpy(), SA.cpu().numpy()) < 1e-13
+    # apply twice -> identical bits (idempotent state: tables and plan are cached)
+    assert torch.equal(S.apply(A, None, 0), SA)
+
+
+def test_raw_c_abi_call(sk, oracle):
+    """The same entry points the reference's lib.py binds, called with bare ctypes."""
+    from libskylark_b200 import _build
+    L = ctypes.CDLL(_build.SO)
+    ctx = ctypes.c_void_p(); S = ctypes.c_void_p(); Aw = ctypes.c_void_p(); SAw = ctypes.c_void_p()
+    assert L.sl_create_default_context(42, ctypes.byref(ctx)) == 0
+    assert L.sl_create_sketch_transform(ctx, b"CWT", 500, 20, ctypes.byref(S)) == 0
+    A = np.asfortranarray(np.random.default_rng(0).standard_normal((500, 30)))
+    SA = np.empty((20, 30), order="F")
+    dp = ctypes.POINTER(ctypes.c_double)
+    assert L.sl_wrap_raw_matrix(A.ctypes.data_as(dp), 500, 30, ctypes.byref(Aw)) == 0
+    assert L.sl_wrap_raw_matrix(SA.ctypes.data_as(dp), 20, 30, ctypes.byref(SAw)) == 0
+    assert L.sl_apply_sketch_transform(S, b"Matrix", Aw, b"Matrix", SAw, 1) == 0
+    want = oracle.CWT(500, 20, oracle.Context(42)).apply(A, "columnwise")
+    assert rel_fro(SA, want) < TOL
+    assert L.sl_apply_sketch_transform(S, b"DistMatrix", Aw, b"Matrix", SAw, 1) == 103
+    assert L.sl_apply_sketch_transform(S, b"Matrix", Aw, b"Matrix", SAw, 7) == 111
+    for w in (Aw, SAw):
+        L.sl_free_raw_matrix_wrap(w)
+    L.sl_free_sketch_transform(S)
+    L.sl_free_context(ctx)

@@ -1,0 +1,112 @@
+"""Device RNG and generated tables against the oracle: raw Random123 draws, hash buckets and
++-1 signs bit for bit; Gaussian / Cauchy variates within 2 ulp (BASELINE.json north_star)."""
+import ctypes
+import json
+import os
+
+import numpy as np
+import pytest
+
+from util import ulp_diff
+
+pytestmark = pytest.mark.gpu
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "golden.json")))
+
+
+def _raw(seed, base, count):
+    from libskylark_b200 import lib
+    a = np.empty(count, dtype=np.uint64)
+    b = np.empty(count, dtype=np.uint64)
+    lib.callsl("sl_rng_export_raw", int(seed), int(base), int(count),
+               a.ctypes.data_as(ctypes.c_void_p), b.ctypes.data_as(ctypes.c_void_p))
+    return a, b
+
+
+def test_raw_draws_bit_exact(sk, oracle):
+    for seed in (0, 123834, -7, 2**31 - 1):
+        for base in (0, 999983, 2**40 + 17, 2**64 - 5000):
+            a, b = _raw(seed, base, 4096)
+            oa, ob = oracle.raw_draws(seed, base, 4096)
+            assert np.array_equal(a, oa) and np.array_equal(b, ob)
+    for c in GOLDEN["streams"]:
+        a, b = _raw(c["seed"], c["base"], 8)
+        assert ["%016x" % int(x) for x in a] == c["first"]
+        assert ["%016x" % int(x) for x in b] == c["second"]
+
+
+@pytest.mark.parametrize("order", [160, 155])
+def test_cwt_tables_bit_exact(sk, oracle, order):
+    from libskylark_b200 import lib
+    lib.set_option("boost_order", order)
+    try:
+        n, s = 100000, 2000
+        S = sk.CWT(n, s, lib.Context(123834))
+        o = oracle.CWT(n, s, oracle.Context(123834), order=order)
+        assert np.array_equal(S.row_idx(), o.row_idx.astype(np.int64))
+        assert np.array_equal(S.row_value(), o.row_value)
+    finally:
+        lib.set_option("boost_order", 160)
+
+
+def test_golden_transform_sequence(sk):
+    from libskylark_b200 import lib
+    for g in GOLDEN["transforms_in_sequence"]:
+        c = lib.Context(g["seed"])
+        t = sk.CWT(10, 6, c); m = sk.MMT(7, 3, c); w = sk.WZT(5, 4, 1.5, c)
+        j = sk.JLT(4, 3, c); r = sk.GaussianRFT(3, 5, 2.0, c); f = sk.FJLT(16, 4, c)
+        assert c.counter == g["counter_after"]
+        assert t.row_idx().tolist() == g["cwt_row_idx"]
+        assert t.row_value().tolist() == g["cwt_row_value"]
+        assert m.row_idx().tolist() == g["mmt_row_idx"]
+        assert ulp_diff(m.row_value(), [float.fromhex(x) for x in g["mmt_row_value"]]).max() <= 2
+        assert ulp_diff(w.row_value(), [float.fromhex(x) for x in g["wzt_row_value"]]).max() <= 4
+        got = j.export_dense().ravel(order="F")
+        assert ulp_diff(got, [float.fromhex(x) for x in g["jlt_S"]]).max() <= 2
+        assert r.shifts().tolist() == [float.fromhex(x) for x in g["rft_shifts"]]
+        assert f.diagonal().tolist() == g["fjlt_D"]
+        assert f.samples().tolist() == g["fjlt_samples"]
+
+
+def test_mmt_wzt_values(sk, oracle):
+    from libskylark_b200 import lib
+    n, s = 50000, 777
+    m = sk.MMT(n, s, lib.Context(5))
+    om = oracle.MMT(n, s, oracle.Context(5))
+    assert np.array_equal(m.row_idx(), om.row_idx.astype(np.int64))
+    assert ulp_diff(m.row_value(), om.row_value).max() <= 2
+    for p in (1.0, 1.5, 2.0):
+        w = sk.WZT(n, s, p, lib.Context(6))
+        ow = oracle.WZT(n, s, p, oracle.Context(6))
+        assert np.array_equal(w.row_idx(), ow.row_idx.astype(np.int64))
+        assert np.array_equal(np.sign(w.row_value()), np.sign(ow.row_value))
+        assert ulp_diff(w.row_value(), ow.row_value).max() <= 4   # log, divide and pow chained
+
+
+def test_dense_entries_within_2ulp(sk, oracle):
+    from libskylark_b200 import lib
+    n, s = 1500, 300
+    j = sk.JLT(n, s, lib.Context(123834, 17))
+    oj = oracle.JLT(n, s, oracle.Context(123834, 17))
+    d = ulp_diff(j.export_dense(), oj.realize())
+    assert d.max() <= 2, int(d.max())
+    # sub-block addressing S[i0:i0+h, j0:j0+w]
+    assert np.array_equal(j.export_dense(7, 11, 20, 30), j.export_dense()[7:27, 11:41])
+    c = sk.CT(n, s, 2.0, lib.Context(9))
+    oc = oracle.CT(n, s, 2.0, oracle.Context(9))
+    d = ulp_diff(c.export_dense(), oc.realize())
+    assert d.max() <= 2, int(d.max())
+    r = sk.GaussianRFT(64, 128, 3.0, lib.Context(4))
+    orr = oracle.GaussianRFT(64, 128, 3.0, oracle.Context(4))
+    assert np.array_equal(r.shifts(), orr.shifts)
+    assert np.array_equal(r.scales(), orr.scales)
+    assert ulp_diff(r.export_dense(), orr.realize()).max() <= 2
+
+
+def test_fjlt_tables_and_overlap(sk, oracle):
+    from libskylark_b200 import lib
+    c = lib.Context(31, 1000)
+    f = sk.FJLT(4096, 500, c)
+    assert c.counter == 1500
+    of = oracle.FJLT(4096, 500, oracle.Context(31, 1000))
+    assert np.array_equal(f.diagonal(), of.D)
+    assert np.array_equal(f.samples(), of.samples.astype(np.int64))

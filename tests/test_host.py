@@ -1,0 +1,148 @@
+"""Host-side logic that needs no GPU: the C-ABI library loads and exports every declared
+symbol, contexts / counters / JSON follow the reference's rules, errors use its codes."""
+import ctypes
+import json
+import os
+import pickle
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "golden.json")))
+
+
+def test_library_exports_every_declared_symbol():
+    from libskylark_b200 import _build
+    hdr = open(os.path.join(ROOT, "include", "skylark_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(sl_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 40
+    L = ctypes.CDLL(_build.SO)
+    missing = [n for n in sorted(names) if not hasattr(L, n)]
+    assert not missing, missing
+
+
+def test_supported_list_is_evaluable(sk):
+    combos = sk.SUPPORTED_SKETCH_TRANSFORMS
+    assert ("CWT", "Matrix", "Matrix") in combos and ("CWT", "SparseMatrix", "Matrix") in combos
+    assert ("JLT", "Matrix", "Matrix") in combos and ("FJLT", "Matrix", "Matrix") in combos
+    assert all(len(c) == 3 for c in combos)
+
+
+def test_global_context_counter_rules(sk):
+    from libskylark_b200 import lib
+    sk.initialize(3)
+    assert lib.global_counter() == 0
+    sk.CWT(10, 6); assert lib.global_counter() == 20
+    sk.MMT(7, 3); assert lib.global_counter() == 34
+    sk.WZT(5, 4, 1.5); assert lib.global_counter() == 49
+    sk.JLT(4, 3); assert lib.global_counter() == 61
+    sk.CT(4, 3, 2.0); assert lib.global_counter() == 73
+    sk.GaussianRFT(3, 5, 2.0); assert lib.global_counter() == 93
+    sk.FJLT(16, 4); assert lib.global_counter() == 97      # advances by S only
+    sk.LaplacianRFT(3, 5, 2.0); assert lib.global_counter() == 117
+
+
+def test_explicit_context_and_positional_form(sk):
+    from libskylark_b200 import lib
+    c = lib.Context(7, 100)
+    assert (c.seed, c.counter) == (7, 100)
+    S = sk.CWT(10, 6, c)                  # BASELINE.json form: T(n, s, context)
+    assert c.counter == 120
+    d = S.serialize()
+    assert d["creation_context"]["seed"] == "7" and d["creation_context"]["counter"] == "100"
+    sk.JLT(4, 3, context=c)
+    assert c.counter == 132
+    assert sk.RFT is sk.GaussianRFT and sk.FastJLT is sk.JLT and sk.CountSketch is sk.CWT
+
+
+def test_serialize_roundtrip_and_pickle(sk):
+    for make in (lambda: sk.CWT(10, 6), lambda: sk.MMT(10, 6), lambda: sk.WZT(10, 6, 1.25),
+                 lambda: sk.JLT(10, 6), lambda: sk.CT(10, 6, 2.5), lambda: sk.FJLT(16, 6),
+                 lambda: sk.GaussianRFT(10, 6, 3.0), lambda: sk.LaplacianRFT(10, 6, 0.5)):
+        S = make()
+        d = S.serialize()
+        assert d["skylark_object_type"] == "sketch" and d["skylark_version"] == "0.20"
+        S2 = sk.deserialize_sketch(d)
+        assert type(S2) is type(S)
+        assert S2.serialize() == d
+        S3 = pickle.loads(pickle.dumps(S))
+        assert S3.serialize() == d
+        assert (S3.getindim(), S3.getsketchdim()) == (S.getindim(), S.getsketchdim())
+    # numbers instead of boost's strings are accepted too
+    d = sk.CT(10, 6, 2.5).serialize()
+    d2 = dict(d, N=10, S=6, C=2.5, creation_context=dict(d["creation_context"], seed=123834, counter=int(d["creation_context"]["counter"])))
+    assert sk.deserialize_sketch(d2).serialize() == d
+
+
+def test_error_codes(sk):
+    from libskylark_b200 import errors, lib
+    with pytest.raises(errors.LowerLayerError) as e:
+        sk._SketchTransform("NoSuchTransform", 4, 2)
+    assert e.value.code == 111                      # capi/csketch.cpp:385-386
+    with pytest.raises(errors.LowerLayerError) as e:
+        sk.WZT(10, 5, 3.0)
+    assert e.value.code == 105                      # WZT_data.hpp:49-52 sketch_exception
+    with pytest.raises(errors.LowerLayerError) as e:
+        sk.CWT(0, 5)
+    assert e.value.code == 111
+    assert lib.lib.sl_strerror(108).decode() == "Skylark failed in a call into the Random123 layer"
+    with pytest.raises(errors.UnsupportedError):
+        sk.CWT(10, 5, forceppy=True)
+    with pytest.raises(errors.UnsupportedError):
+        sk.CWT(10, 5, defouttype="NoSuchType")
+    c = lib.Context(1, 2**64 - 5)
+    with pytest.raises(errors.LowerLayerError) as e:
+        sk.CWT(10, 5, c)
+    assert e.value.code == 108                      # stream exhausted, randgen.hpp:64-72
+
+
+def test_adapter_checks(sk):
+    from libskylark_b200 import errors
+    S = sk.CWT(10, 5)
+    with pytest.raises(errors.UnsupportedError):
+        S.apply(np.zeros((10, 3), dtype=np.float32), None, 0)
+    with pytest.raises(errors.UnsupportedError):
+        S.apply(np.zeros((20, 3))[::2], None, 0)       # views refused, lib.py:103-104
+    with pytest.raises(errors.DimensionMistmatchError):
+        S.apply(np.zeros((11, 3)), None, 0)
+    with pytest.raises(errors.DimensionMistmatchError):
+        S.apply(np.zeros((10, 3)), np.zeros((4, 3)), 0)
+    with pytest.raises(errors.UnsupportedError):
+        S.apply(np.zeros((10, 3)), np.zeros((5, 3), order="F"), 0)
+    with pytest.raises(ValueError):
+        S.apply(np.zeros((10, 3)), None, "diagonal")
+    with pytest.raises(errors.InvalidObjectError):
+        S.apply([[1.0]], None, 0)
+
+
+def test_compute_fails_loudly_without_gpu(sk):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from libskylark_b200 import errors
+    S = sk.CWT(10, 5)
+    with pytest.raises(errors.LowerLayerError, match="no CUDA device"):
+        S.apply(np.zeros((10, 3)), None, 0)
+    with pytest.raises(errors.LowerLayerError, match="no CUDA device"):
+        S.row_idx()
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "libskylark_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src.lower(), os.path.join(dirpath, f)
+
+
+def test_shard_range():
+    from libskylark_b200.dist import shard_range
+    for n, w in ((10, 3), (8, 8), (5, 8), (1000003, 8)):
+        parts = [shard_range(n, r, w) for r in range(w)]
+        assert parts[0][0] == 0 and sum(c for _, c in parts) == n
+        for (o1, c1), (o2, _) in zip(parts, parts[1:]):
+            assert o1 + c1 == o2
