@@ -74,14 +74,18 @@ def test_rft_fp64(sk, oracle, T):
     rng = np.random.default_rng(3)
     X = rng.uniform(0, 1, (500, n))
     want = O.apply(X, "rowwise")
-    assert rel_fro(S.apply(X.copy(), None, "rowwise"), want) < TOL64
-    assert rel_fro(S.apply(np.asfortranarray(X), None, 1), want) < TOL64
+    # Laplacian features take cos() of Cauchy-weighted sums whose magnitude reaches 1e4..1e5:
+    # the summation order alone (numpy's blocked dgemm vs any other order) moves the argument
+    # by eps*|arg|, so the features are only defined to ~1e-11 there.  Gaussian: 1e-12.
+    tol = TOL64 if T == "GaussianRFT" else 1e-10
+    assert rel_fro(S.apply(X.copy(), None, "rowwise"), want) < tol
+    assert rel_fro(S.apply(np.asfortranarray(X), None, 1), want) < tol
     Xc = rng.uniform(0, 1, (n, 33))
-    assert rel_fro(S.apply(Xc.copy(), None, "columnwise"), O.apply(Xc, "columnwise")) < TOL64
+    assert rel_fro(S.apply(Xc.copy(), None, "columnwise"), O.apply(Xc, "columnwise")) < tol
     # feature-map shape that takes the fused-epilogue (whole tile) path
     Xb = torch.rand(80000, n, dtype=torch.float64, device="cuda")
     got = S.apply(Xb, None, "rowwise")
-    assert rel_fro(got.cpu().numpy(), O.apply(Xb.cpu().numpy(), "rowwise")) < TOL64
+    assert rel_fro(got.cpu().numpy(), O.apply(Xb.cpu().numpy(), "rowwise")) < tol
     assert float(got.abs().max()) <= np.sqrt(2.0 / s) * (1 + 1e-15)
     with pytest.raises(Exception):
         S.apply_shard(Xc[:30].copy(), None, 0, 0)       # cosine is not additive over shards
