@@ -24,6 +24,7 @@
 //   * the RFT epilogue outscale*cos(scale_i*acc+shift_i) is fused into the flush
 //     when a CTA owns the whole contraction of a tile (the rowwise feature-map case).
 #include <cstdio>
+#include <cstdlib>
 
 #include "rng.cuh"
 #include "skb_internal.h"
@@ -33,11 +34,21 @@ namespace skb {
 // ---------------------------------------------------------------------------
 // Panel generation (K5a).  P[e] = scale * sample(base + first + e), e < count.
 // ---------------------------------------------------------------------------
+// 128-thread blocks with <= 80 registers: one such block fits beside the resident GEMM CTA
+// of an SM (which holds 256 x 212 registers), so generation of panel p+1 overlaps GEMM p.
 template <int DIST>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 k_gen_panel(uint64_t key, uint64_t stream0, size_t count, double scale, double *__restrict__ P) {
-    size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < count; e += stride) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; e + stride < count; e += 2 * stride) {       // two independent variates in flight
+        double v0 = DIST == DD_NORMAL ? normal_at(key, stream0 + e) : cauchy_at(key, stream0 + e);
+        double v1 = DIST == DD_NORMAL ? normal_at(key, stream0 + e + stride)
+                                      : cauchy_at(key, stream0 + e + stride);
+        P[e] = __dmul_rn(scale, v0);
+        P[e + stride] = __dmul_rn(scale, v1);
+    }
+    if (e < count) {
         double v = DIST == DD_NORMAL ? normal_at(key, stream0 + e) : cauchy_at(key, stream0 + e);
         P[e] = __dmul_rn(scale, v);
     }
@@ -49,14 +60,14 @@ void dense_generate_panel(const DenseParams &p, size_t k0, size_t kc, double *pa
     if (count == 0) return;
     uint64_t stream0 = p.base + (uint64_t)k0 * p.S;
     size_t blocks = (count + 255) / 256;
-    size_t cap = (size_t)148 * 16;
+    size_t cap = (size_t)148 * 64;
     if (blocks > cap) blocks = cap;
     LaunchScope ls(KC_GEN, st);
     if (p.dist == DD_NORMAL)
-        k_gen_panel<DD_NORMAL><<<(unsigned)blocks, 256, 0, st>>>(seed_to_key(p.seed), stream0,
+        k_gen_panel<DD_NORMAL><<<(unsigned)blocks, 128, 0, st>>>(seed_to_key(p.seed), stream0,
                                                                  count, p.scale, panel);
     else
-        k_gen_panel<DD_CAUCHY><<<(unsigned)blocks, 256, 0, st>>>(seed_to_key(p.seed), stream0,
+        k_gen_panel<DD_CAUCHY><<<(unsigned)blocks, 128, 0, st>>>(seed_to_key(p.seed), stream0,
                                                                  count, p.scale, panel);
     SKB_CUDA(cudaGetLastError());
 }
@@ -127,7 +138,7 @@ template <int N> __device__ __forceinline__ void cp_async_wait() {
 }
 
 __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                  : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
@@ -301,12 +312,21 @@ __global__ void k_dense_finalize(const double *__restrict__ acc, TX *__restrict_
     OUT[off] = (TX)v;
 }
 
+static size_t panel_mib() {
+    static size_t v = 0;
+    if (v == 0) {
+        const char *e = getenv("SKB_PANEL_MIB");   // tuning knob; default chosen by measurement
+        long x = e ? atol(e) : 0;
+        v = x > 0 ? (size_t)x : 256;
+    }
+    return v;
+}
+
 static size_t panel_rows_for(size_t S) {
-    // keep panel (<= 64 MiB) + the matching slab of X inside the 126 MB L2
-    size_t kc = ((size_t)64 << 20) / (S * sizeof(double));
+    size_t kc = (panel_mib() << 20) / (S * sizeof(double));
     kc = kc / BK * BK;
     if (kc < (size_t)BK) kc = BK;
-    if (kc > 8192) kc = 8192;
+    if (kc > 32768) kc = 32768;
     return kc;
 }
 
@@ -316,9 +336,10 @@ size_t dense_workspace_bytes(const DenseParams &p, size_t nloc, bool layout_rows
     if (kc > nloc) kc = (nloc + BK - 1) / BK * BK;
     if (kc == 0) kc = BK;
     size_t panel = ((kc * p.S * sizeof(double) + 255) / 256) * 256;
+    size_t npanels = nloc == 0 ? 0 : (nloc + kc - 1) / kc;
     // double accumulation image of OUT, used only by the float atomic path
     size_t accbuf = f32 ? (layout_rows ? p.S * ldo : m * ldo) * sizeof(double) : 0;
-    return panel + accbuf + 256;
+    return panel * (npanels > 1 ? 2 : 1) + accbuf + 256;
 }
 
 template <typename TX, bool ROWS>
@@ -341,6 +362,32 @@ static void launch_gemm(const GemmArgs &a, bool al16p, bool alx, unsigned grid, 
     SKB_CUDA(cudaGetLastError());
 }
 
+// Two internal streams per device: the GEMMs run on a high-priority stream, the panel
+// generator on a low-priority one, so that generation of panel p+1 fills the FP64-pipe
+// bubbles (and the idle integer pipe) of GEMM p instead of running ahead of it.
+struct SideStreams {
+    cudaStream_t gemm = nullptr, gen = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr, gen_done[2] = {nullptr, nullptr},
+                gemm_done[2] = {nullptr, nullptr};
+};
+static SideStreams &side_streams() {
+    static SideStreams per_dev[64];
+    int dev = 0;
+    SKB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) throw error(SKB_ERR_GENERIC, "device index out of range");
+    SideStreams &s = per_dev[dev];
+    if (!s.gemm) {
+        int least = 0, greatest = 0;
+        SKB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        SKB_CUDA(cudaStreamCreateWithPriority(&s.gemm, cudaStreamNonBlocking, greatest));
+        SKB_CUDA(cudaStreamCreateWithPriority(&s.gen, cudaStreamNonBlocking, least));
+        cudaEvent_t *evs[] = {&s.fork, &s.join, &s.gen_done[0], &s.gen_done[1], &s.gemm_done[0],
+                              &s.gemm_done[1]};
+        for (cudaEvent_t *e : evs) SKB_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    }
+    return s;
+}
+
 template <typename TX, bool ROWS>
 static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t m, size_t koff,
                           size_t nloc, TX *OUT, size_t ldo, const RftEpilogue &epi,
@@ -353,12 +400,18 @@ static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t 
     const size_t panel_bytes = ((kc_max * S * sizeof(double) + 255) / 256) * 256;
     if (workspace_bytes < panel_bytes)
         throw error(SKB_ERR_ALLOC, "dense apply: workspace too small");
-    double *panel = reinterpret_cast<double *>(workspace);
-    double *accbuf = reinterpret_cast<double *>(reinterpret_cast<char *>(workspace) + panel_bytes);
+    const size_t npanels = nloc == 0 ? 0 : (nloc + kc_max - 1) / kc_max;
+    const size_t nbuf = npanels > 1 ? 2 : 1;
+    if (workspace_bytes < panel_bytes * nbuf)
+        throw error(SKB_ERR_ALLOC, "dense apply: workspace too small");
+    double *panels[2] = {reinterpret_cast<double *>(workspace),
+                         reinterpret_cast<double *>(reinterpret_cast<char *>(workspace) +
+                                                    panel_bytes * (nbuf - 1))};
+    double *accbuf = reinterpret_cast<double *>(reinterpret_cast<char *>(workspace) +
+                                                panel_bytes * nbuf);
 
     const int ntm = (int)((S + BM - 1) / BM), ntn = (int)((m + BN - 1) / BN);
     const long long ntiles = (long long)ntm * ntn;
-    const size_t npanels = nloc == 0 ? 0 : (nloc + kc_max - 1) / kc_max;
     const bool has_epi = epi.shifts != nullptr;
     const bool tile_mode = ntiles >= 4 * 148;     // enough tiles: no k split
     const bool single = npanels == 1;
@@ -371,24 +424,46 @@ static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t 
 
     void *gemm_out = use_accbuf ? (void *)accbuf : (void *)OUT;
     // accbuf is laid out exactly like OUT (same ldo) so the flush code is shared
-    if (use_accbuf && workspace_bytes < panel_bytes + (ROWS ? S * ldo : m * ldo) * sizeof(double))
+    if (use_accbuf && workspace_bytes < panel_bytes * nbuf + (ROWS ? S * ldo : m * ldo) * sizeof(double))
         throw error(SKB_ERR_ALLOC, "dense apply: workspace too small for accumulation buffer");
+    // With several panels the work is forked onto the two internal streams and joined back.
+    const bool forked = npanels > 1;
+    cudaStream_t st_gemm = st, st_gen = st;
+    SideStreams *ss = nullptr;
+    if (forked) {
+        ss = &side_streams();
+        st_gemm = ss->gemm; st_gen = ss->gen;
+        SKB_CUDA(cudaEventRecord(ss->fork, st));
+        SKB_CUDA(cudaStreamWaitEvent(st_gemm, ss->fork, 0));
+        SKB_CUDA(cudaStreamWaitEvent(st_gen, ss->fork, 0));
+    }
     if (need_zero) {
         size_t contig = ROWS ? m : S, nvec = ROWS ? S : m;
         size_t esz = use_accbuf ? sizeof(double) : sizeof(TX);
-        if (ldo == contig) SKB_CUDA(cudaMemsetAsync(gemm_out, 0, contig * nvec * esz, st));
-        else SKB_CUDA(cudaMemset2DAsync(gemm_out, ldo * esz, 0, contig * esz, nvec, st));
+        if (ldo == contig) SKB_CUDA(cudaMemsetAsync(gemm_out, 0, contig * nvec * esz, st_gemm));
+        else SKB_CUDA(cudaMemset2DAsync(gemm_out, ldo * esz, 0, contig * esz, nvec, st_gemm));
     }
 
     const bool al16p = (S % 2 == 0);
     const int xe = 16 / (int)sizeof(TX);
     const bool alx = (ldx % xe == 0) && ((uintptr_t)X % 16 == 0);
 
-    for (size_t k0 = 0; k0 < nloc; k0 += kc_max) {
+    auto gen_panel = [&](size_t pi) {
+        size_t k0 = pi * kc_max;
         size_t kc = nloc - k0 < kc_max ? nloc - k0 : kc_max;
-        dense_generate_panel(p, koff + k0, kc, panel, st);
+        if (forked && pi >= 2)    // buffer pi%2 was last read by GEMM pi-2
+            SKB_CUDA(cudaStreamWaitEvent(st_gen, ss->gemm_done[pi % 2], 0));
+        dense_generate_panel(p, koff + k0, kc, panels[pi % 2], st_gen);
+        if (forked) SKB_CUDA(cudaEventRecord(ss->gen_done[pi % 2], st_gen));
+    };
+    if (npanels > 0) gen_panel(0);
+    for (size_t pi = 0; pi < npanels; pi++) {
+        const size_t k0 = pi * kc_max;
+        size_t kc = nloc - k0 < kc_max ? nloc - k0 : kc_max;
+        if (pi + 1 < npanels) gen_panel(pi + 1);
+        if (forked) SKB_CUDA(cudaStreamWaitEvent(st_gemm, ss->gen_done[pi % 2], 0));
         GemmArgs a;
-        a.P = panel; a.S = S; a.kc = kc;
+        a.P = panels[pi % 2]; a.S = S; a.kc = kc;
         a.X = ROWS ? (const void *)(X + k0 * ldx) : (const void *)(X + k0);
         a.ldx = ldx; a.m = m; a.OUT = gemm_out; a.ldo = ldo;
         a.ntm = ntm; a.ntn = ntn; a.nk = (int)((kc + BK - 1) / BK);
@@ -402,16 +477,20 @@ static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t 
         unsigned grid = tile_mode ? 148u : (unsigned)(total < 148 ? total : 148);
         // alignment of the X slab for this panel
         bool alx_p = alx && (ROWS || (k0 % xe == 0));
-        launch_gemm<TX, ROWS>(a, al16p, alx_p, grid, st);
+        launch_gemm<TX, ROWS>(a, al16p, alx_p, grid, st_gemm);
+        if (forked) SKB_CUDA(cudaEventRecord(ss->gemm_done[pi % 2], st_gemm));
     }
-    if (nloc == 0) return;   // OUT already zeroed
-    if (use_accbuf || (has_epi && !fuse_epi)) {
+    if (nloc != 0 && (use_accbuf || (has_epi && !fuse_epi))) {
         const double *src = use_accbuf ? accbuf : reinterpret_cast<const double *>(OUT);
         size_t n = S * m;
-        LaunchScope ls(KC_MISC, st);
-        k_dense_finalize<TX, ROWS><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
+        LaunchScope ls(KC_MISC, st_gemm);
+        k_dense_finalize<TX, ROWS><<<(unsigned)((n + 255) / 256), 256, 0, st_gemm>>>(
             src, OUT, S, m, ldo, epi.scales, epi.shifts, epi.outscale, has_epi ? 1 : 0);
         SKB_CUDA(cudaGetLastError());
+    }
+    if (forked) {
+        SKB_CUDA(cudaEventRecord(ss->join, st_gemm));
+        SKB_CUDA(cudaStreamWaitEvent(st, ss->join, 0));
     }
 }
 

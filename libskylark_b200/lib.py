@@ -137,9 +137,12 @@ class Context:
         callsl("sl_create_context_at", int(seed), int(counter), byref(self._obj))
 
     def __del__(self):
-        if lib is not None and getattr(self, "_obj", None) is not None and self._obj.value:
-            lib.sl_free_context(self._obj)
-            self._obj = None
+        try:
+            if lib is not None and getattr(self, "_obj", None) is not None and self._obj.value:
+                lib.sl_free_context(self._obj)
+                self._obj = None
+        except Exception:
+            pass
 
     @property
     def seed(self):

@@ -87,10 +87,13 @@ class _SketchTransform(object):
         self._ppy = False
 
     def __del__(self):
-        obj = getattr(self, "_obj", None)
-        if obj is not None and lib.lib is not None and getattr(obj, "value", obj):
-            lib.lib.sl_free_sketch_transform(obj)
-            self._obj = None
+        try:    # module globals may already be gone at interpreter shutdown
+            obj = getattr(self, "_obj", None)
+            if obj is not None and lib.lib is not None and getattr(obj, "value", obj):
+                lib.lib.sl_free_sketch_transform(obj)
+                self._obj = None
+        except Exception:
+            pass
 
     def serialize(self):
         """Dictionary from which `deserialize_sketch` rebuilds the sketch (sketch.py:94-113)."""
