@@ -5,7 +5,7 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SO = os.path.join(HERE, "libcskylark_b200.so")
+SO = os.environ.get("SKB_SO") or os.path.join(HERE, "libcskylark_b200.so")   # SKB_SO: A/B builds
 SOURCES = ["capi.cu", "hash.cu", "dense.cu", "fjlt.cu"]
 HEADERS = ["rng.cuh", "skb_internal.h", os.path.join("..", "..", "include", "skylark_b200.h")]
 

@@ -134,7 +134,7 @@ struct DevState {
     int32_t *bucket = nullptr; double *value = nullptr;
     std::map<std::pair<size_t, size_t>, HashPlan> plans;
     double *shifts = nullptr, *scales = nullptr;
-    double *D = nullptr; int32_t *samples = nullptr;
+    double *D = nullptr; int32_t *samples = nullptr; uint32_t *Dbits = nullptr;
     void *ws = nullptr; size_t ws_bytes = 0;
 };
 
@@ -154,7 +154,7 @@ struct sl_sketch_transform_t {
             int prev = -1; cudaGetDevice(&prev); cudaSetDevice(kv.first);
             DevState &d = kv.second;
             cudaFree(d.bucket); cudaFree(d.value); cudaFree(d.shifts); cudaFree(d.scales);
-            cudaFree(d.D); cudaFree(d.samples); cudaFree(d.ws);
+            cudaFree(d.D); cudaFree(d.samples); cudaFree(d.Dbits); cudaFree(d.ws);
             for (auto &p : d.plans) hash_free_plan(&p.second);
             if (prev >= 0) cudaSetDevice(prev);
         }
@@ -240,8 +240,9 @@ static void ensure_fjlt_tables(sl_sketch_transform_t *t, DevState &d) {
     if (d.D) return;
     SKB_CUDA(cudaMalloc(&d.D, (size_t)t->N * sizeof(double)));
     SKB_CUDA(cudaMalloc(&d.samples, (size_t)t->S * sizeof(int32_t)));
+    SKB_CUDA(cudaMalloc(&d.Dbits, ((size_t)t->N / 32 + 1) * sizeof(uint32_t)));
     fjlt_build_tables(t->seed, t->base0, (size_t)t->N, (size_t)t->S, t->order, d.D, d.samples,
-                      g_stream);
+                      d.Dbits, g_stream);
 }
 
 static DenseParams dense_params(const sl_sketch_transform_t *t) {
@@ -326,10 +327,10 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
     if (shard && sk != t->N)
         throw error(SKB_ERR_INVALID_USAGE, "apply: FJLT needs the whole sketched dimension");
     ensure_fjlt_tables(t, d);
-    size_t need = fjlt_workspace_bytes((size_t)t->N, (size_t)other, t->fut);
+    size_t need = fjlt_workspace_bytes((size_t)t->N, (size_t)other, t->fut, layout_rows, (size_t)t->S);
     ensure_ws(d, need);
     fjlt_apply(t->fut, layout_rows, (const double *)A->data, (size_t)A->ld, (size_t)t->N,
-               (size_t)other, d.D, d.samples, (size_t)t->S, (double *)SA->data, (size_t)SA->ld,
+               (size_t)other, d.D, d.Dbits, d.samples, (size_t)t->S, (double *)SA->data, (size_t)SA->ld,
                d.ws, d.ws_bytes, st);
 }
 

@@ -101,7 +101,13 @@ void dense_export_block(const DenseParams &p, size_t i0, size_t j0, size_t h, si
 // ---------------------------------------------------------------------------
 // FP64 tensor-core GEMM (K5b): OUT[i,j] (+)= sum_kk P[kk*S + i] * X(kk, j)
 // ---------------------------------------------------------------------------
-static constexpr int BM = 128, BN = 128, BK = 16, STAGES = 4, NTHREADS = 256;
+#ifndef SKB_BK
+#define SKB_BK 16
+#endif
+#ifndef SKB_STAGES
+#define SKB_STAGES 4
+#endif
+static constexpr int BM = 128, BN = 128, BK = SKB_BK, STAGES = SKB_STAGES, NTHREADS = 256;
 static constexpr int LDP = BM + 4;   // doubles; = 4 mod 16 -> conflict-free 64-bit fragment loads
 
 template <typename TX> struct XTile;

@@ -16,12 +16,18 @@
 namespace skb {
 
 __global__ void k_fjlt_tables(uint64_t key, uint64_t base, size_t N, size_t S, int order,
-                              double *__restrict__ D, int32_t *__restrict__ samples) {
+                              double *__restrict__ D, int32_t *__restrict__ samples,
+                              uint32_t *__restrict__ Dbits) {
     size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool neg = false;
     if (t < N) {
         MicroUrng u(key, base + t);
-        D[t] = boost_rademacher(u, order);
+        double d = boost_rademacher(u, order);
+        D[t] = d;
+        neg = d < 0.0;
     }
+    unsigned word = __ballot_sync(0xffffffffu, neg);     // bit l of word t/32 = sign of D[t]
+    if ((threadIdx.x & 31) == 0 && t < ((N + 31) / 32) * 32) Dbits[t >> 5] = word;
     if (t < S) {
         MicroUrng u(key, base + t);
         samples[t] = (int32_t)boost_uniform_int(u, (uint64_t)N - 1);
@@ -29,12 +35,12 @@ __global__ void k_fjlt_tables(uint64_t key, uint64_t base, size_t N, size_t S, i
 }
 
 void fjlt_build_tables(int seed, uint64_t base, size_t N, size_t S, int order, double *D,
-                       int32_t *samples, cudaStream_t st) {
+                       int32_t *samples, uint32_t *Dbits, cudaStream_t st) {
     size_t n = N > S ? N : S;
     if (n == 0) return;
     LaunchScope ls(KC_TABLES, st);
     k_fjlt_tables<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(seed_to_key(seed), base, N, S,
-                                                               order, D, samples);
+                                                               order, D, samples, Dbits);
     SKB_CUDA(cudaGetLastError());
 }
 
@@ -78,19 +84,461 @@ k_fjlt_direct(const double *__restrict__ X, size_t sk, size_t sj, size_t N, size
     }
 }
 
-size_t fjlt_workspace_bytes(size_t N, size_t m, int fut) {
-    (void)m;
-    return fut == FUT_DCT ? 4 * N * sizeof(double) + 256 : 256;
+
+// ---------------------------------------------------------------------------
+// WHT mode, N = 2^p >= 8192, every column contiguous (K7).
+// H_N = H_{N/SEG} (x) H_SEG in natural order, so a column is streamed ONCE through shared
+// memory in SEG = 8192-element segments (64 KB, double buffered with cp.async): each
+// segment gets its 13 butterfly levels on chip (4 in registers, 5 by warp shuffle, 4 after
+// one shared-memory exchange) and only the S sampled outputs are kept: sample r = (k1, k2)
+// accumulates (-1)^popc(k1 & n1) * seg[k2] over the segments n1, in registers.  HBM
+// traffic is exactly the algorithmic n*d*8 + s*d*8 bytes; no scratch, no atomics.
+// ---------------------------------------------------------------------------
+static constexpr int WSEG_LOG = 13, WSEG = 1 << WSEG_LOG, WTHREADS = 512, WSPT = 16;
+
+__device__ __forceinline__ void cp_async16(void *smem, const void *g) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(g));
+}
+__device__ __forceinline__ void cp_async8(void *smem, const void *g) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(g));
+}
+
+__device__ __forceinline__ double shfl_xor_f64(double v, int m) {
+    return __shfl_xor_sync(0xffffffffu, v, m);
+}
+
+template <bool AL16>
+__global__ void __launch_bounds__(WTHREADS, 1)
+k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
+                const uint32_t *__restrict__ Dbits, const int32_t *__restrict__ samples,
+                size_t S, size_t s_first, double inscale, double outscale,
+                double *__restrict__ OUT, size_t oi, size_t oj) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *buf0 = reinterpret_cast<double *>(smem_raw);
+    double *buf1 = buf0 + WSEG;
+    int32_t *smp = reinterpret_cast<int32_t *>(buf1 + WSEG);      // [WTHREADS * WSPT]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t nseg = N >> WSEG_LOG;
+    const size_t s_cnt = min((size_t)WTHREADS * WSPT, S - s_first);
+
+    for (int q = 0; q < WSPT; q++) {
+        size_t i = (size_t)q * WTHREADS + tid;
+        smp[i] = i < s_cnt ? samples[s_first + i] : -1;
+    }
+    __syncthreads();
+
+    auto prefetch = [&](const double *col, size_t seg, double *dst) {
+        const double *g = col + (seg << WSEG_LOG);
+        if (AL16) {
+#pragma unroll
+            for (int c = 0; c < WSEG / 2 / WTHREADS; c++) {
+                int e = (c * WTHREADS + tid) * 2;
+                cp_async16(dst + e, g + e);
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < WSEG / WTHREADS; c++) {
+                int e = c * WTHREADS + tid;
+                cp_async8(dst + e, g + e);
+            }
+        }
+        asm volatile("cp.async.commit_group;");
+    };
+
+    for (size_t j = blockIdx.x; j < m; j += gridDim.x) {
+        const double *col = X + j * ldx;
+        double acc[WSPT];
+#pragma unroll
+        for (int q = 0; q < WSPT; q++) acc[q] = 0.0;
+        prefetch(col, 0, buf0);
+        for (size_t n1 = 0; n1 < nseg; n1++) {
+            double *buf = (n1 & 1) ? buf1 : buf0;
+            if (n1 + 1 < nseg) {
+                prefetch(col, n1 + 1, (n1 & 1) ? buf0 : buf1);
+                asm volatile("cp.async.wait_group 1;");
+            } else {
+                asm volatile("cp.async.wait_group 0;");
+            }
+            __syncthreads();
+            // ---- phase 1: element e = c*1024 + tid*2 + b, c < 8, b < 2 (16 per thread)
+            double v[16];
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                double2 x = *reinterpret_cast<const double2 *>(buf + c * 1024 + tid * 2);
+                // sign bits: global index n1*8192 + c*1024 + tid*2 + b
+                uint32_t w = Dbits[(n1 << (WSEG_LOG - 5)) + c * 32 + (tid >> 4)];
+                int bit = (tid & 15) * 2;
+                v[2 * c] = __dmul_rn((w >> bit) & 1 ? -inscale : inscale, x.x);
+                v[2 * c + 1] = __dmul_rn((w >> (bit + 1)) & 1 ? -inscale : inscale, x.y);
+            }
+            // register levels: index bit 0 (b) and bits 10..12 (c)
+#pragma unroll
+            for (int h = 1; h < 16; h <<= 1)
+#pragma unroll
+                for (int i = 0; i < 16; i++)
+                    if (!(i & h)) { double a = v[i], b = v[i + h]; v[i] = a + b; v[i + h] = a - b; }
+            // lane levels: index bits 1..5
+#pragma unroll
+            for (int mk = 1; mk < 32; mk <<= 1) {
+                const bool up = lane & mk;
+#pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    double o = shfl_xor_f64(v[i], mk);
+                    v[i] = up ? o - v[i] : v[i] + o;
+                }
+            }
+            __syncthreads();          // everyone has read its inputs: reuse buf for the exchange
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                double2 x; x.x = v[2 * c]; x.y = v[2 * c + 1];
+                *reinterpret_cast<double2 *>(buf + c * 1024 + tid * 2) = x;
+            }
+            __syncthreads();
+            // ---- phase 2: warp bits 6..9 of the index; thread t = (c, l, b) holds w = 0..15
+            {
+                const int base = (tid >> 6) * 1024 + (tid & 63);
+#pragma unroll
+                for (int w = 0; w < 16; w++) v[w] = buf[base + w * 64];
+#pragma unroll
+                for (int h = 1; h < 16; h <<= 1)
+#pragma unroll
+                    for (int i = 0; i < 16; i++)
+                        if (!(i & h)) { double a = v[i], b = v[i + h]; v[i] = a + b; v[i + h] = a - b; }
+#pragma unroll
+                for (int w = 0; w < 16; w++) buf[base + w * 64] = v[w];
+            }
+            __syncthreads();
+            // ---- sampled accumulate
+#pragma unroll
+            for (int q = 0; q < WSPT; q++) {
+                int r = smp[q * WTHREADS + tid];
+                if (r >= 0) {
+                    double x = buf[r & (WSEG - 1)];
+                    bool neg = __popcll((unsigned long long)(r >> WSEG_LOG) & n1) & 1;
+                    acc[q] += neg ? -x : x;
+                }
+            }
+            __syncthreads();          // buf may be overwritten by the prefetch two segments on
+        }
+#pragma unroll
+        for (int q = 0; q < WSPT; q++) {
+            size_t i = (size_t)q * WTHREADS + tid;
+            if (i < s_cnt) OUT[(s_first + i) * oi + j * oj] = outscale * acc[q];
+        }
+    }
+}
+
+// Tiled transpose: T[k + j*N] = X[k*ldx + j]  (rows layout -> contiguous columns)
+__global__ void k_transpose_to_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
+                                    double *__restrict__ T) {
+    __shared__ double tile[32][33];
+    size_t j0 = (size_t)blockIdx.x * 32, k0 = (size_t)blockIdx.y * 32;
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        size_t k = k0 + r, j = j0 + threadIdx.x;
+        tile[r][threadIdx.x] = (k < N && j < m) ? X[k * ldx + j] : 0.0;
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        size_t j = j0 + r, k = k0 + threadIdx.x;
+        if (k < N && j < m) T[k + j * N] = tile[threadIdx.x][r];
+    }
+}
+
+
+// ---------------------------------------------------------------------------
+// DCT-II mode (what the reference computes), N = 2^p >= 1024, contiguous columns (K8).
+//   v = Makhoul permutation of x' = scale * D .* x;   z[n] = v[2n] + i v[2n+1]  (N' = N/2)
+//   Z = DFT_N'(z) by a two-pass Cooley-Tukey split N' = N1 * N2 (n = n1 + N1 n2,
+//   k = N2 k1 + k2): pass 1 = length-N2 FFTs over the strided index + twiddle W_N'^(n1 k2),
+//   pass 2 = length-N1 FFTs over contiguous rows; both are radix-4/2 Stockham FFTs in
+//   shared memory.  Only the S sampled bins are finished:
+//   V[k] = E[k] + W_N^k O[k] (real-input split of Z), Y[k] = 2 Re(W_4N^k V[k]).
+// Columns are processed in batches small enough that the N*8-byte intermediate of every
+// column in flight stays in the 126 MB L2, so HBM sees each input element once.
+// FP64 FFT arithmetic (~40 flop per element) is comparable to the HBM time of the element
+// on this part, so this mode is compute/shared-memory bound, not HBM bound.
+// ---------------------------------------------------------------------------
+struct cplx { double x, y; };
+__device__ __forceinline__ cplx cmul(cplx a, cplx b) {
+    cplx r; r.x = a.x * b.x - a.y * b.y; r.y = a.x * b.y + a.y * b.x; return r;
+}
+__device__ __forceinline__ cplx cadd(cplx a, cplx b) { cplx r; r.x = a.x + b.x; r.y = a.y + b.y; return r; }
+__device__ __forceinline__ cplx csub(cplx a, cplx b) { cplx r; r.x = a.x - b.x; r.y = a.y - b.y; return r; }
+
+struct DctPlan {
+    size_t N, Np, N1, N2;     // Np = N/2 = N1*N2
+    int lo_bits;              // twiddle exponent split: e = hi << lo_bits | lo
+    cplx *W1, *W2;            // W_N2[m], W_N1[m]
+    cplx *Tlo, *Thi;          // W_Np^(lo), W_Np^(hi << lo_bits)
+    cplx *post;               // per sample: W_N^k, W_4N^k
+    size_t G;                 // sequences per CTA
+};
+
+__global__ void k_dct_tables(DctPlan pl, const int32_t *__restrict__ samples, size_t S) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    double sn, cs;
+    if (t < pl.N2) { sincospi(-2.0 * (double)t / (double)pl.N2, &sn, &cs); pl.W1[t].x = cs; pl.W1[t].y = sn; }
+    if (t < pl.N1) { sincospi(-2.0 * (double)t / (double)pl.N1, &sn, &cs); pl.W2[t].x = cs; pl.W2[t].y = sn; }
+    size_t nlo = (size_t)1 << pl.lo_bits;
+    if (t < nlo) { sincospi(-2.0 * (double)t / (double)pl.Np, &sn, &cs); pl.Tlo[t].x = cs; pl.Tlo[t].y = sn; }
+    size_t nhi = (pl.Np + nlo - 1) / nlo;
+    if (t < nhi) {
+        sincospi(-2.0 * (double)(t << pl.lo_bits) / (double)pl.Np, &sn, &cs);
+        pl.Thi[t].x = cs; pl.Thi[t].y = sn;
+    }
+    if (t < S) {
+        double k = (double)samples[t];
+        sincospi(-2.0 * k / (double)pl.N, &sn, &cs); pl.post[2 * t].x = cs; pl.post[2 * t].y = sn;
+        sincospi(-0.5 * k / (double)pl.N, &sn, &cs); pl.post[2 * t + 1].x = cs; pl.post[2 * t + 1].y = sn;
+    }
+}
+
+// One radix-R Stockham pass over G sequences of length L held in shared memory.
+template <int R>
+__device__ __forceinline__ void stockham_pass(const cplx *in, cplx *out, int L, int Ns, int G,
+                                              const cplx *__restrict__ W) {
+    const int per = L / R, units = G * per, step = L / (Ns * R);
+    for (int u = threadIdx.x; u < units; u += blockDim.x) {
+        const int g = u / per, j = u - g * per, k = j & (Ns - 1);
+        const cplx *src = in + g * L + j;
+        cplx a[R];
+#pragma unroll
+        for (int t = 0; t < R; t++) a[t] = src[t * per];
+        if (Ns > 1) {
+#pragma unroll
+            for (int t = 1; t < R; t++) a[t] = cmul(a[t], W[t * k * step]);
+        }
+        cplx *dst = out + g * L + (j - k) * R + k;
+        if (R == 2) {
+            dst[0] = cadd(a[0], a[1]);
+            dst[Ns] = csub(a[0], a[1]);
+        } else {
+            cplx b0 = cadd(a[0], a[2]), b1 = csub(a[0], a[2]), b2 = cadd(a[1], a[3]);
+            cplx d = csub(a[1], a[3]);
+            cplx b3; b3.x = d.y; b3.y = -d.x;               // -i * (a1 - a3)
+            dst[0] = cadd(b0, b2);
+            dst[Ns] = cadd(b1, b3);
+            dst[2 * Ns] = csub(b0, b2);
+            dst[3 * Ns] = csub(b1, b3);
+        }
+    }
+}
+
+// Full FFT of G sequences of length L (power of two) in shared memory; returns the buffer
+// that holds the result (ping-pong between a and b).
+__device__ __forceinline__ cplx *smem_fft(cplx *a, cplx *b, int L, int G, const cplx *__restrict__ W) {
+    int Ns = 1;
+    cplx *in = a, *out = b;
+    int logL = 31 - __clz(L);
+    if (logL & 1) {
+        stockham_pass<2>(in, out, L, Ns, G, W);
+        __syncthreads();
+        Ns = 2; cplx *t = in; in = out; out = t;
+    }
+    for (; Ns < L; Ns *= 4) {
+        stockham_pass<4>(in, out, L, Ns, G, W);
+        __syncthreads();
+        cplx *t = in; in = out; out = t;
+    }
+    return in;
+}
+
+__device__ __forceinline__ double dct_xprime(const double *__restrict__ col,
+                                             const uint32_t *__restrict__ Dbits, size_t q,
+                                             double inscale) {
+    uint32_t w = Dbits[q >> 5];
+    return __dmul_rn((w >> (q & 31)) & 1 ? -inscale : inscale, col[q]);
+}
+
+// pass 1: grid (N1/G, columns in batch)
+__global__ void __launch_bounds__(1024)
+k_dct_pass1(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan pl,
+            const uint32_t *__restrict__ Dbits, double inscale, cplx *__restrict__ H) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int G = (int)pl.G, N2 = (int)pl.N2;
+    const size_t N = pl.N, N1 = pl.N1;
+    cplx *a = reinterpret_cast<cplx *>(smem_raw), *b = a + (size_t)G * N2;
+    const size_t n1_0 = (size_t)blockIdx.x * G;
+    const double *col = X + (col0 + blockIdx.y) * ldx;
+    cplx *Hc = H + (size_t)blockIdx.y * pl.Np;
+    for (int idx = threadIdx.x; idx < G * N2; idx += blockDim.x) {
+        const int g = idx % G, n2 = idx / G;
+        const size_t n = n1_0 + g + N1 * (size_t)n2;
+        cplx z;
+        if (4 * n < N) { z.x = dct_xprime(col, Dbits, 4 * n, inscale); z.y = dct_xprime(col, Dbits, 4 * n + 2, inscale); }
+        else { z.x = dct_xprime(col, Dbits, 2 * N - 4 * n - 1, inscale); z.y = dct_xprime(col, Dbits, 2 * N - 4 * n - 3, inscale); }
+        a[g * N2 + n2] = z;
+    }
+    __syncthreads();
+    cplx *res = smem_fft(a, b, N2, G, pl.W1);
+    const size_t lo_mask = ((size_t)1 << pl.lo_bits) - 1;
+    for (int idx = threadIdx.x; idx < G * N2; idx += blockDim.x) {
+        const int g = idx % G, k2 = idx / G;
+        const size_t n1 = n1_0 + g, e = n1 * (size_t)k2;       // < Np
+        cplx tw = cmul(pl.Thi[e >> pl.lo_bits], pl.Tlo[e & lo_mask]);
+        Hc[(size_t)k2 * N1 + n1] = cmul(res[g * N2 + k2], tw);
+    }
+}
+
+// pass 2: grid (N2/G, columns in batch); rows of H are contiguous; in place
+__global__ void __launch_bounds__(1024)
+k_dct_pass2(DctPlan pl, cplx *__restrict__ H) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int G = (int)pl.G, N1 = (int)pl.N1;
+    cplx *a = reinterpret_cast<cplx *>(smem_raw), *b = a + (size_t)G * N1;
+    cplx *rows = H + (size_t)blockIdx.y * pl.Np + (size_t)blockIdx.x * G * N1;
+    for (int idx = threadIdx.x; idx < G * N1; idx += blockDim.x) a[idx] = rows[idx];
+    __syncthreads();
+    cplx *res = smem_fft(a, b, N1, G, pl.W2);
+    for (int idx = threadIdx.x; idx < G * N1; idx += blockDim.x) rows[idx] = res[idx];
+}
+
+// sampled bins -> DCT values -> OUT
+__global__ void k_dct_post(DctPlan pl, const cplx *__restrict__ H, const int32_t *__restrict__ samples,
+                           size_t S, size_t col0, size_t ncols, double outscale,
+                           double *__restrict__ OUT, size_t oi, size_t oj) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S * ncols) return;
+    const size_t i = t % S, c = t / S;
+    const size_t k = (size_t)samples[i], kp = k & (pl.Np - 1), km = (pl.Np - kp) & (pl.Np - 1);
+    const cplx *Z = H + c * pl.Np;
+    const cplx za = Z[(kp & (pl.N2 - 1)) * pl.N1 + kp / pl.N2];
+    const cplx zb = Z[(km & (pl.N2 - 1)) * pl.N1 + km / pl.N2];
+    cplx E, O;
+    E.x = 0.5 * (za.x + zb.x); E.y = 0.5 * (za.y - zb.y);
+    O.x = 0.5 * (za.y + zb.y); O.y = -0.5 * (za.x - zb.x);
+    cplx V = cadd(E, cmul(pl.post[2 * i], O));
+    cplx Yc = cmul(pl.post[2 * i + 1], V);
+    OUT[i * oi + (col0 + c) * oj] = outscale * (2.0 * Yc.x);
+}
+
+static bool dct_fast_ok(size_t N) { return N >= 1024 && (N & (N - 1)) == 0 && N <= ((size_t)1 << 25); }
+
+static size_t dct_batch_cols(size_t N, size_t m) {
+    size_t b = ((size_t)48 << 20) / (N * sizeof(double));
+    if (b < 1) b = 1;
+    if (b > m) b = m;
+    return b;
+}
+
+static size_t dct_table_bytes(size_t N, size_t S) {
+    return (N + 4096 + 2 * S + 1024) * sizeof(cplx);     // generous upper bound
+}
+
+static bool wht_fast_ok(size_t N) { return N >= (size_t)WSEG && (N & (N - 1)) == 0; }
+
+size_t fjlt_workspace_bytes(size_t N, size_t m, int fut, bool layout_rows, size_t S) {
+    if (fut == FUT_DCT && dct_fast_ok(N))
+        return (layout_rows ? N * m * sizeof(double) : 0) + dct_batch_cols(N, m) * N * sizeof(double) +
+               dct_table_bytes(N, S) + 1024;
+    if (fut == FUT_DCT) return 4 * N * sizeof(double) + 256;
+    if (wht_fast_ok(N) && layout_rows) return N * m * sizeof(double) + 256;   // transposed copy
+    return 256;
 }
 
 void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N, size_t m,
-                const double *D, const int32_t *samples, size_t S, double *OUT, size_t ldo,
-                void *workspace, size_t workspace_bytes, cudaStream_t st) {
+                const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
+                double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
+                cudaStream_t st) {
     if (S == 0 || m == 0) return;
     if (fut == FUT_WHT && (N & (N - 1)) != 0)
         throw error(SKB_ERR_INVALID_PARAM, "FJLT (WHT mode): N must be a power of two");
-    if (workspace_bytes < fjlt_workspace_bytes(N, m, fut))
+    if (workspace_bytes < fjlt_workspace_bytes(N, m, fut, layout_rows, S))
         throw error(SKB_ERR_ALLOC, "fjlt apply: workspace too small");
+    if (fut == FUT_DCT && dct_fast_ok(N)) {
+        char *ws = reinterpret_cast<char *>(workspace);
+        const double *Xc = X;
+        size_t ldc = ldx;
+        if (layout_rows) {      // the reference also transposes for this direction
+            double *T = reinterpret_cast<double *>(ws);
+            ws += ((N * m * sizeof(double) + 255) / 256) * 256;
+            LaunchScope ls(KC_FJLT, st);
+            dim3 grid((unsigned)((m + 31) / 32), (unsigned)((N + 31) / 32));
+            k_transpose_to_cols<<<grid, dim3(32, 8), 0, st>>>(X, ldx, N, m, T);
+            SKB_CUDA(cudaGetLastError());
+            Xc = T; ldc = N;
+        }
+        DctPlan pl;
+        pl.N = N; pl.Np = N / 2;
+        int lg = 0; while (((size_t)1 << lg) < pl.Np) lg++;
+        pl.N1 = (size_t)1 << (lg / 2); pl.N2 = pl.Np / pl.N1;
+        pl.lo_bits = 10;
+        const size_t B = dct_batch_cols(N, m);
+        cplx *H = reinterpret_cast<cplx *>(ws);
+        cplx *tab = H + B * pl.Np;
+        pl.W1 = tab; tab += pl.N2;
+        pl.W2 = tab; tab += pl.N1;
+        pl.Tlo = tab; tab += (size_t)1 << pl.lo_bits;
+        pl.Thi = tab; tab += (pl.Np >> pl.lo_bits) + 1;
+        pl.post = tab;
+        // sequences per CTA: two ping-pong buffers of G*L complex doubles within ~128 KB
+        size_t Lmax = pl.N2;
+        pl.G = 4096 / Lmax; if (pl.G < 1) pl.G = 1; if (pl.G > 8) pl.G = 8;
+        while (pl.G > 1 && (pl.N1 % pl.G || pl.N2 % pl.G)) pl.G /= 2;
+        const size_t smem1 = 2 * pl.G * pl.N2 * sizeof(cplx), smem2 = 2 * pl.G * pl.N1 * sizeof(cplx);
+        SKB_CUDA(cudaFuncSetAttribute(k_dct_pass1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+        SKB_CUDA(cudaFuncSetAttribute(k_dct_pass2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+        {
+            size_t nt = pl.N2 > S ? pl.N2 : S;
+            if (nt < 1024) nt = 1024;
+            if (nt < (pl.Np >> pl.lo_bits) + 1) nt = (pl.Np >> pl.lo_bits) + 1;
+            LaunchScope ls(KC_FJLT, st);
+            k_dct_tables<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(pl, samples, S);
+            SKB_CUDA(cudaGetLastError());
+        }
+        const size_t oi = layout_rows ? ldo : 1, oj = layout_rows ? 1 : ldo;
+        const double inscale = 1.0 / sqrt(2.0 * (double)N), outscale = sqrt((double)N / (double)S);
+        // one radix-4 unit per thread per pass where possible (latency hiding by occupancy)
+        auto threads_for = [](size_t units) { size_t t = 128; while (t < units && t < 1024) t *= 2; return (unsigned)t; };
+        const unsigned thr1 = threads_for(pl.G * pl.N2 / 4), thr2 = threads_for(pl.G * pl.N1 / 4);
+        for (size_t c0 = 0; c0 < m; c0 += B) {
+            const size_t nb = m - c0 < B ? m - c0 : B;
+            {
+                LaunchScope ls(KC_FJLT, st);
+                k_dct_pass1<<<dim3((unsigned)(pl.N1 / pl.G), (unsigned)nb), thr1, smem1, st>>>(
+                    Xc, ldc, c0, pl, Dbits, inscale, H);
+            }
+            {
+                LaunchScope ls(KC_FJLT, st);
+                k_dct_pass2<<<dim3((unsigned)(pl.N2 / pl.G), (unsigned)nb), thr2, smem2, st>>>(pl, H);
+            }
+            {
+                LaunchScope ls(KC_FJLT, st);
+                k_dct_post<<<(unsigned)((S * nb + 255) / 256), 256, 0, st>>>(
+                    pl, H, samples, S, c0, nb, outscale, OUT, oi, oj);
+            }
+            SKB_CUDA(cudaGetLastError());
+        }
+        return;
+    }
+    if (fut == FUT_WHT && wht_fast_ok(N)) {
+        const double *Xc = X;
+        size_t ldc = ldx;
+        if (layout_rows) {      // the reference also transposes for this direction
+            double *T = reinterpret_cast<double *>(workspace);
+            LaunchScope ls(KC_FJLT, st);
+            dim3 grid((unsigned)((m + 31) / 32), (unsigned)((N + 31) / 32));
+            k_transpose_to_cols<<<grid, dim3(32, 8), 0, st>>>(X, ldx, N, m, T);
+            SKB_CUDA(cudaGetLastError());
+            Xc = T; ldc = N;
+        }
+        const size_t oi = layout_rows ? ldo : 1, oj = layout_rows ? 1 : ldo;
+        const double inscale = 1.0 / sqrt((double)N), outscale = sqrt((double)N / (double)S);
+        const size_t smem = 2 * WSEG * sizeof(double) + (size_t)WTHREADS * WSPT * sizeof(int32_t);
+        const bool al16 = (ldc % 2 == 0) && ((uintptr_t)Xc % 16 == 0);
+        auto kern = al16 ? k_fjlt_wht_cols<true> : k_fjlt_wht_cols<false>;
+        SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        unsigned grid = (unsigned)(m < 148 ? m : 148);
+        for (size_t s0 = 0; s0 < S; s0 += (size_t)WTHREADS * WSPT) {    // 8192 samples per pass
+            LaunchScope ls(KC_FJLT, st);
+            kern<<<grid, WTHREADS, smem, st>>>(Xc, ldc, N, m, Dbits, samples, S, s0, inscale,
+                                               outscale, OUT, oi, oj);
+            SKB_CUDA(cudaGetLastError());
+        }
+        return;
+    }
     if (S > 0x7fffffffULL || m > 65535)
         throw error(SKB_ERR_INVALID_PARAM, "fjlt apply (general path): shape too large");
     const size_t sk = layout_rows ? ldx : 1, sj = layout_rows ? 1 : ldx;

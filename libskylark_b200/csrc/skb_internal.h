@@ -120,11 +120,12 @@ void dense_export_block(const DenseParams &p, size_t i0, size_t j0, size_t h, si
 // ---- FJLT (fjlt.cu) ----------------------------------------------------------
 enum FutKind { FUT_DCT = 0, FUT_WHT = 1 };
 void fjlt_build_tables(int seed, uint64_t base, size_t N, size_t S, int order, double *D,
-                       int32_t *samples, cudaStream_t st);
-size_t fjlt_workspace_bytes(size_t N, size_t m, int fut);
+                       int32_t *samples, uint32_t *Dbits, cudaStream_t st);
+size_t fjlt_workspace_bytes(size_t N, size_t m, int fut, bool layout_rows, size_t S);
 // layout_rows as above.  OUT[i, j] = sqrt(N/S) * FUT(scale * D .* X[:, j])[samples[i]]
 void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N, size_t m,
-                const double *D, const int32_t *samples, size_t S, double *OUT, size_t ldo,
-                void *workspace, size_t workspace_bytes, cudaStream_t st);
+                const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
+                double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
+                cudaStream_t st);
 
 }  // namespace skb

@@ -10,7 +10,8 @@ TOL = 1e-12
 
 
 @pytest.mark.parametrize("fut", ["dct", "wht"])
-@pytest.mark.parametrize("shape", [(64, 16, 5), (1024, 100, 33), (4096, 512, 8)])
+@pytest.mark.parametrize("shape", [(64, 16, 5), (1024, 100, 33), (4096, 512, 8), (16384, 300, 9),
+                                   (65536, 9000, 5), (2048, 64, 150)])
 def test_fjlt_power_of_two(sk, oracle, fut, shape):
     from libskylark_b200 import lib
     n, s, d = shape
