@@ -141,6 +141,36 @@ int sl_profile_reset(void);
 int sl_profile_read(unsigned long long launches[SL_KERNEL_CLASSES],
                     double ms[SL_KERNEL_CLASSES]);
 
+/* Dense sketch (JLT / CT arithmetic) that allocates nothing.  No counterpart in the
+ * reference.  It exists for callers that must not allocate device memory at the moment they
+ * sketch: a step that is being captured into a CUDA graph, a latency-critical loop, a
+ * process whose GPU memory is handed out up front by another allocator, or a host
+ * application that forbids cudaMalloc once it is running.  sl_apply_sketch_transform keeps
+ * a cudaMalloc'ed, growing workspace per transform; this call instead stages the generated
+ * panel of S in a fixed 32 MiB array that is part of the library image on every GPU that
+ * loads it (held until the process exits), and makes no cudaMalloc / cudaFree / stream or
+ * event creation of its own.
+ *   SA = scale * G * A        (dim = SL_COLUMNWISE; A is n x m, SA is s x m)
+ *   SA = scale * A * G^T      (dim = SL_ROWWISE;    A is m x n, SA is m x s)
+ * with G[i,k] = sample(counter_base + k*s + i), dist 0 = normal, 1 = Cauchy -- i.e. the S of
+ * a JLT created from a context at `counter_base` with scale sqrt(1/s), or a CT with C/s.
+ * A_dev / SA_dev are column-major fp64 device buffers with leading dimensions lda / ldsa;
+ * the work is queued on `cuda_stream` (NULL = default stream) and the call returns without
+ * synchronising.
+ * Limits and rules:
+ *   - s must be at most 262144 (16 panel rows have to fit in the 4 Mi-double array); larger s
+ *     is refused with code 111 and a message.  n and m are not limited.
+ *   - The first call on each device looks up the array's device address (and loads the
+ *     kernels); make that first call outside any stream capture.
+ *   - All calls on a device share the one array.  Nothing in it needs clearing between
+ *     calls (each call rewrites what it reads; SA is zeroed by the call itself), but two
+ *     calls that run on the GPU at the same time -- different streams, or different host
+ *     threads -- overwrite each other's panel and give wrong results.  Serialise them. */
+int sl_dense_sketch_apply_noalloc(int seed, uint64_t counter_base, int dist, double scale,
+                                  int64_t n, int64_t s, const double *A_dev, int64_t lda,
+                                  int64_t m, double *SA_dev, int64_t ldsa, int dim,
+                                  void *cuda_stream);
+
 /* Pinned host memory for the host-buffer path (cudaHostAlloc / cudaFreeHost). */
 int sl_host_alloc_pinned(size_t bytes, void **ptr);
 int sl_host_free_pinned(void *ptr);

@@ -30,6 +30,7 @@ static int g_boost_order = SKB_ORDER_160;
 static int g_fjlt_fut = FUT_DCT;
 
 namespace skb {
+void set_last_error(const std::string &msg) { g_last_error = msg; }
 Profiler &profiler() { static Profiler p; return p; }
 struct PendingPair { KernelClass kc; cudaEvent_t e0, e1; };
 static std::vector<PendingPair> g_pending;

@@ -513,4 +513,131 @@ void dense_apply(const DenseParams &p, bool layout_rows, bool f32, const void *X
     }
 }
 
+
+// ---------------------------------------------------------------------------
+// Allocation-free dense sketch (sl_dense_sketch_apply_noalloc, include/skylark_b200.h).
+//
+// For callers that are not allowed to allocate device memory while they run -- code
+// inside a CUDA-graph capture or a real-time loop, a process whose memory pool is owned by
+// another runtime and sized up front, a plugin host that forbids cudaMalloc after start-up.
+// The generated panel of S lives in a fixed file-scope device array instead of a
+// cudaMalloc'ed workspace.  Every GPU that loads this library carries these 32 MiB until
+// the process exits.
+// ---------------------------------------------------------------------------
+static constexpr size_t NOALLOC_PANEL_DOUBLES = (size_t)4 << 20;        // 32 MiB
+static __device__ __align__(256) double g_noalloc_panel[NOALLOC_PANEL_DOUBLES];
+
+// In host code `g_noalloc_panel` is only a handle for the runtime, not a device address;
+// the address each device gave the array is looked up once per device and kept here.
+static double *g_noalloc_panel_addr[64] = {nullptr};
+
+static double *noalloc_panel_for_current_device() {
+    int dev = 0;
+    SKB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) throw error(SKB_ERR_GENERIC, "device index out of range");
+    if (!g_noalloc_panel_addr[dev]) {
+        double *ptr = nullptr;
+        SKB_CUDA(cudaGetSymbolAddress((void **)&ptr, g_noalloc_panel));
+        g_noalloc_panel_addr[dev] = ptr;
+    }
+    return g_noalloc_panel_addr[dev];
+}
+
+template <bool ROWS>
+static void noalloc_apply(const DenseParams &p, const double *X, size_t ldx, size_t m, double *OUT,
+                          size_t ldo, cudaStream_t st) {
+    const size_t S = p.S, N = p.N;
+    if (S == 0 || m == 0) return;
+    size_t kc_max = NOALLOC_PANEL_DOUBLES / S / BK * BK;
+    if (kc_max == 0)
+        throw error(SKB_ERR_INVALID_PARAM,
+                    "sl_dense_sketch_apply_noalloc: s = " + std::to_string(S) + " exceeds the "
+                    "built-in panel (" + std::to_string(NOALLOC_PANEL_DOUBLES / BK) +
+                    " is the largest sketch size it can hold); use sl_apply_sketch_transform");
+    double *panel = noalloc_panel_for_current_device();
+    // The panel keeps whatever the previous call left in it: every element the GEMM reads
+    // (rows < kc) is rewritten by the generator first, rows beyond kc are never read.  The
+    // output is accumulated with atomics, so it is the one thing that must start at zero.
+    {
+        size_t contig = ROWS ? m : S, nvec = ROWS ? S : m;
+        if (ldo == contig) SKB_CUDA(cudaMemsetAsync(OUT, 0, contig * nvec * sizeof(double), st));
+        else SKB_CUDA(cudaMemset2DAsync(OUT, ldo * sizeof(double), 0, contig * sizeof(double), nvec, st));
+    }
+    const int ntm = (int)((S + BM - 1) / BM), ntn = (int)((m + BN - 1) / BN);
+    const long long ntiles = (long long)ntm * ntn;
+    const bool al16p = (S % 2 == 0);
+    const bool alx = (ldx % 2 == 0) && ((uintptr_t)X % 16 == 0);
+    const uint64_t key = seed_to_key(p.seed);
+    for (size_t k0 = 0; k0 < N; k0 += kc_max) {
+        const size_t kc = N - k0 < kc_max ? N - k0 : kc_max;
+        const size_t count = kc * S;
+        size_t blocks = (count + 255) / 256;
+        if (blocks > (size_t)148 * 64) blocks = (size_t)148 * 64;
+        profiler().launches[KC_GEN]++;
+        if (p.dist == DD_NORMAL)
+            k_gen_panel<DD_NORMAL><<<(unsigned)blocks, 128, 0, st>>>(key, p.base + (uint64_t)k0 * S, count, p.scale, panel);
+        else
+            k_gen_panel<DD_CAUCHY><<<(unsigned)blocks, 128, 0, st>>>(key, p.base + (uint64_t)k0 * S, count, p.scale, panel);
+        SKB_CUDA(cudaGetLastError());
+        GemmArgs a;
+        a.P = panel; a.S = S; a.kc = kc;
+        a.X = ROWS ? (const void *)(X + k0 * ldx) : (const void *)(X + k0);
+        a.ldx = ldx; a.m = m; a.OUT = OUT; a.ldo = ldo;
+        a.ntm = ntm; a.ntn = ntn; a.nk = (int)((kc + BK - 1) / BK);
+        a.direct_ok = 0; a.whole_tiles = 0; a.out_is_acc = 0;
+        a.scales = nullptr; a.shifts = nullptr; a.outscale = 1.0; a.has_epi = 0;
+        const long long total = ntiles * a.nk;
+        const unsigned grid = (unsigned)(total < 148 ? total : 148);
+        const bool alx_p = alx && (ROWS || (k0 % 2 == 0));
+        using SM = GemmSmem<double, ROWS>;
+        profiler().launches[KC_GEMM]++;
+#define SKB_NA_LAUNCH(CP, CX)                                                                      \
+        do {                                                                                       \
+            auto kern = k_dense_gemm<double, ROWS, CP, CX>;                                        \
+            SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
+                                          (int)SM::BYTES));                                        \
+            kern<<<grid, NTHREADS, SM::BYTES, st>>>(a);                                            \
+        } while (0)
+        if (al16p && alx_p) SKB_NA_LAUNCH(16, 16);
+        else if (al16p) SKB_NA_LAUNCH(16, 8);
+        else if (alx_p) SKB_NA_LAUNCH(8, 16);
+        else SKB_NA_LAUNCH(8, 8);
+#undef SKB_NA_LAUNCH
+        SKB_CUDA(cudaGetLastError());
+    }
+}
+
 }  // namespace skb
+
+extern "C" {
+
+// See include/skylark_b200.h for the contract.
+int sl_dense_sketch_apply_noalloc(int seed, uint64_t counter_base, int dist, double scale,
+                                  int64_t n, int64_t s, const double *A_dev, int64_t lda, int64_t m,
+                                  double *SA_dev, int64_t ldsa, int dim, void *cuda_stream) {
+    try {
+        if (n <= 0 || s <= 0 || m < 0 || !A_dev || !SA_dev || (dist != 0 && dist != 1))
+            throw skb::error(skb::SKB_ERR_INVALID_PARAM, "sl_dense_sketch_apply_noalloc: bad argument");
+        if (dim != 1 && dim != 2)
+            throw skb::error(skb::SKB_ERR_INVALID_PARAM, "sl_dense_sketch_apply_noalloc: dim must be 1 or 2");
+        // column-major operands, as everywhere in this ABI
+        const int64_t a_rows = dim == 1 ? n : m, sa_rows = dim == 1 ? s : m;
+        if (lda < a_rows || ldsa < sa_rows)
+            throw skb::error(skb::SKB_ERR_INVALID_PARAM, "sl_dense_sketch_apply_noalloc: leading dimension too small");
+        skb::DenseParams p;
+        p.seed = seed; p.base = counter_base; p.dist = dist; p.scale = scale;
+        p.N = (size_t)n; p.S = (size_t)s;
+        cudaStream_t st = (cudaStream_t)cuda_stream;
+        if (dim == 2) skb::noalloc_apply<true>(p, A_dev, (size_t)lda, (size_t)m, SA_dev, (size_t)ldsa, st);
+        else skb::noalloc_apply<false>(p, A_dev, (size_t)lda, (size_t)m, SA_dev, (size_t)ldsa, st);
+    } catch (const skb::error &e) {
+        skb::set_last_error(e.what());
+        return e.code;
+    } catch (const std::exception &e) {
+        skb::set_last_error(e.what());
+        return skb::SKB_ERR_GENERIC;
+    }
+    return 0;
+}
+
+}  // extern "C"

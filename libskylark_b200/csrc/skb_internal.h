@@ -52,6 +52,7 @@ struct LaunchScope {
     KernelClass kc; cudaStream_t stream; cudaEvent_t e0, e1; bool timed;
 };
 void profiler_collect();   // synchronises and folds pending event pairs into ms[]
+void set_last_error(const std::string &msg);   // message returned by sl_get_exception_info
 
 // ---- hash transforms (hash.cu) ---------------------------------------------
 enum HashValueKind { HV_RADEMACHER = 0, HV_CAUCHY = 1, HV_WZT = 2 };
