@@ -143,9 +143,9 @@ int sl_profile_read(unsigned long long launches[SL_KERNEL_CLASSES],
 
 /* Dense sketch (JLT / CT arithmetic) that allocates nothing.  No counterpart in the
  * reference.  It exists for callers that must not allocate device memory at the moment they
- * sketch: a step that is being captured into a CUDA graph, a latency-critical loop, a
- * process whose GPU memory is handed out up front by another allocator, or a host
- * application that forbids cudaMalloc once it is running.  sl_apply_sketch_transform keeps
+ * sketch: a latency-critical loop that cannot afford an allocator call, a process whose
+ * GPU memory is handed out up front by another allocator (so a later cudaMalloc may simply
+ * fail), or a host application that forbids cudaMalloc once it is running.  sl_apply_sketch_transform keeps
  * a cudaMalloc'ed, growing workspace per transform; this call instead stages the generated
  * panel of S in a fixed 32 MiB array that is part of the library image on every GPU that
  * loads it (held until the process exits), and makes no cudaMalloc / cudaFree / stream or

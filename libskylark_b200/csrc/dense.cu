@@ -517,9 +517,10 @@ void dense_apply(const DenseParams &p, bool layout_rows, bool f32, const void *X
 // ---------------------------------------------------------------------------
 // Allocation-free dense sketch (sl_dense_sketch_apply_noalloc, include/skylark_b200.h).
 //
-// For callers that are not allowed to allocate device memory while they run -- code
-// inside a CUDA-graph capture or a real-time loop, a process whose memory pool is owned by
-// another runtime and sized up front, a plugin host that forbids cudaMalloc after start-up.
+// For callers that are not allowed to allocate device memory while they run -- a
+// real-time loop, a process whose memory pool is owned by another runtime and sized up
+// front (a late cudaMalloc may fail there), a plugin host that forbids cudaMalloc after
+// start-up.
 // The generated panel of S lives in a fixed file-scope device array instead of a
 // cudaMalloc'ed workspace.  Every GPU that loads this library carries these 32 MiB until
 // the process exits.

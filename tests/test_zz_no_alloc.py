@@ -1,6 +1,6 @@
 """sl_dense_sketch_apply_noalloc: the dense sketch for callers that may not allocate GPU
-memory while they run (graph capture, real-time loops, processes whose memory pool belongs
-to someone else).  It must give what sl_apply_sketch_transform gives, call after call,
+memory while they run (real-time loops, processes whose memory pool belongs to someone
+else, hosts that forbid cudaMalloc after start-up).  It must give what sl_apply_sketch_transform gives, call after call,
 although every call reuses the same built-in scratch array.  Collected last on purpose."""
 import ctypes
 import math
