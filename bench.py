@@ -165,6 +165,103 @@ def measure_fp64_gemm_peak(torch):
     return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
+def _time_apply(torch, S, A, SA, dim, reps, flush):
+    S.apply(A, SA, dim)
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(reps):
+        if flush is not None:
+            flush.zero_()            # evict L2 between timed runs
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); S.apply(A, SA, dim); e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return statistics.median(ts)
+
+
+def other_configs(torch, lib, sketch, hbm_gbs, fp64_peak):
+    """The remaining BASELINE.json configs on one GPU (device-resident, CUDA events, median of
+    5, L2 flushed between runs); reported beside the main line, not as the bench value."""
+    out = {}
+    dev = "cuda"
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def guarded(name, fn):
+        try:
+            out[name] = fn()
+        except Exception as e:      # never lose the main line
+            out[name] = {"error": str(e)[:200]}
+        torch.cuda.empty_cache()
+
+    def c1(order):
+        n, d, s = 100_000, 500, 2000
+        A = torch.randn(n, d, dtype=torch.float64, device=dev)
+        if order == "F":
+            A = A.t().contiguous().t()
+        S = sketch.CWT(n, s, lib.Context(SKETCH_SEED))
+        SA = S.apply(A, None, "columnwise")
+        ms = _time_apply(torch, S, A, SA, "columnwise", 5, flush)
+        gbs = (n * d * 8 + s * d * 8) / (ms * 1e-3) / 1e9
+        return {"workload": "C1: CWT fp64 100000x500 -> 2000, %s-major A" % ("row" if order == "C" else "column"),
+                "ms": ms, "value": gbs, "unit": "GB/s", "frac_of_measured_hbm": gbs / hbm_gbs}
+
+    def c3(fut, d):
+        n, s = 2 ** 20, 8192
+        lib.set_option("fjlt_fut", fut)
+        try:
+            S = sketch.FJLT(n, s, lib.Context(SKETCH_SEED))
+        finally:
+            lib.set_option("fjlt_fut", "dct")
+        A = torch.randn(d, n, dtype=torch.float64, device=dev).t()     # column-major n x d
+        SA = S.apply(A, None, "columnwise")
+        ms = _time_apply(torch, S, A, SA, "columnwise", 3, None)
+        gbs = (n * d * 8 + s * d * 8) / (ms * 1e-3) / 1e9
+        return {"workload": "C3: FJLT(%s) fp64 2^20x%d -> 8192, column-major A, 1 GPU" % (fut, d),
+                "ms": ms, "value": gbs, "unit": "GB/s", "frac_of_measured_hbm": gbs / hbm_gbs}
+
+    def c4():
+        # one GPU's shard of the 8-GPU config: 1.25e6 of the 1e7 rows, 1e5 columns, 1.25e8 nnz
+        n_total, n_loc, d, s, nnz_col = 10_000_000, 1_250_000, 100_000, 20_000, 1250
+        g = torch.Generator(device=dev).manual_seed(DATA_SEED)
+        indptr = (torch.arange(d + 1, device=dev, dtype=torch.int64) * nnz_col).to(torch.int32)
+        indices = torch.randint(0, n_loc, (d * nnz_col,), device=dev, dtype=torch.int32, generator=g)
+        values = torch.randn(d * nnz_col, dtype=torch.float64, device=dev, generator=g)
+        A = lib.DeviceCSC(indptr, indices, values, (n_loc, d))
+        S = sketch.CWT(n_total, s, lib.Context(SKETCH_SEED))
+        SA = torch.empty(d, s, dtype=torch.float64, device=dev).t()     # column-major s x d, 16 GB
+        S.apply_shard(A, SA, "columnwise", 0)
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); S.apply_shard(A, SA, "columnwise", 0); e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        ms = statistics.median(ts)
+        nbytes = d * nnz_col * 12 + (d + 1) * 4 + s * d * 8
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        return {"workload": "C4 shard: CWT CSC 1.25e6(of 1e7)x1e5, 1.25e8 nnz -> 20000 (dense 16 GB partial)",
+                "ms": ms, "value": gbs, "unit": "GB/s", "frac_of_measured_hbm": gbs / hbm_gbs}
+
+    def c5():
+        m, n, s = 500_000, 784, 16384      # one GPU's share of the 4M points
+        S = sketch.GaussianRFT(n, s, 10.0, context=lib.Context(SKETCH_SEED))
+        A = torch.rand(m, n, dtype=torch.float32, device=dev)
+        SA = torch.empty(m, s, dtype=torch.float32, device=dev)          # 32.8 GB
+        ms = _time_apply(torch, S, A, SA, "rowwise", 2, None)
+        tf = 2.0 * m * n * s / (ms * 1e-3) / 1e12
+        return {"workload": "C5 shard: GaussianRFT fp32 500000x784 -> 16384 rowwise, fused cos",
+                "ms": ms, "value": tf, "unit": "TFLOP/s", "frac_of_measured_fp64_gemm": tf / fp64_peak}
+
+    guarded("c1_cwt_rowmajor", lambda: c1("C"))
+    guarded("c1_cwt_colmajor", lambda: c1("F"))
+    guarded("c3_fjlt_wht", lambda: c3("wht", 2048))
+    guarded("c3_fjlt_dct", lambda: c3("dct", 2048))
+    guarded("c4_cwt_csc_shard", c4)
+    guarded("c5_rft_shard", c5)
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -302,7 +399,12 @@ def run_ours(args):
     except Exception:
         pass
 
-    cpu = cpu_reference_sample(8192)
+    cpu = cpu_reference_sample(8192) if world == 1 else None
+    extra = None
+    if world == 1:
+        del A, SA, S
+        torch.cuda.empty_cache()
+        extra = other_configs(torch, lib, sketch, roofline.get("hbm_gbs_measured") or 6533.5, peak)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -313,9 +415,12 @@ def run_ours(args):
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
                     "path": "sl_apply_sketch_transform_shard on pinned HOST buffers (C ABI)"},
-            "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
-            "cpu_baseline": {"value": cpu["tflops"], "unit": UNIT, "cores": cpu["cores"],
-                             "kind": "port", "sample": cpu["sample"], "seconds": cpu["seconds"]}}
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline}
+    if cpu is not None:
+        line["cpu_baseline"] = {"value": cpu["tflops"], "unit": UNIT, "cores": cpu["cores"],
+                                "kind": "port", "sample": cpu["sample"], "seconds": cpu["seconds"]}
+    if extra is not None:
+        line["other_configs"] = extra
     print(json.dumps(line))
     if world > 1:
         dist.barrier()

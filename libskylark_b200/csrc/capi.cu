@@ -258,7 +258,7 @@ static DenseParams dense_params(const sl_sketch_transform_t *t) {
 // apply on device-resident operands
 // ---------------------------------------------------------------------------
 static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const sl_matrix_t *SA,
-                         int dim, int64_t offset, bool shard) {
+                         int dim, int64_t offset, bool shard, bool accumulate = false) {
     const bool colwise = dim == SL_COLUMNWISE;
     const int64_t sk = colwise ? A->m : A->n;        // sketched extent present in A
     const int64_t other = colwise ? A->n : A->m;
@@ -276,6 +276,8 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
     cudaStream_t st = g_stream;
     const bool layout_rows = !colwise;   // rowwise on column-major == contiguous rows per index
 
+    if (accumulate && !t->is_dense())
+        throw error(SKB_ERR_INVALID_USAGE, "apply: accumulation is implemented for JLT/CT only");
     if (A->kind == MK_SPARSE) {
         if (!t->is_hash()) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse input is supported for CWT/MMT/WZT only");
         ensure_hash_tables(t, d);
@@ -321,7 +323,7 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
                                             (size_t)SA->ld);
         ensure_ws(d, need);
         dense_apply(p, layout_rows, f32, A->data, (size_t)A->ld, (size_t)other, (size_t)offset,
-                    (size_t)sk, SA->data, (size_t)SA->ld, epi, d.ws, d.ws_bytes, st);
+                    (size_t)sk, SA->data, (size_t)SA->ld, epi, d.ws, d.ws_bytes, st, accumulate);
         return;
     }
     // FJLT
@@ -333,6 +335,90 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
     fjlt_apply(t->fut, layout_rows, (const double *)A->data, (size_t)A->ld, (size_t)t->N,
                (size_t)other, d.D, d.Dbits, d.samples, (size_t)t->S, (double *)SA->data, (size_t)SA->ld,
                d.ws, d.ws_bytes, st);
+}
+
+// Host operands of a dense sketch: the sketched dimension is cut in chunks; chunk c+1 is
+// copied to the device (second stream, double-buffered staging) while chunk c is sketched
+// into the device-resident SA with global input indices -- the same additivity the
+// row-sharded multi-GPU path uses.  Staging buffers persist per device (grow-only).
+struct HostStage {
+    void *buf[2] = {nullptr, nullptr}; size_t cap = 0;
+    void *out = nullptr; size_t out_cap = 0;
+    cudaStream_t copy = nullptr;
+    cudaEvent_t copied[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr}, start = nullptr;
+};
+static HostStage &host_stage(int dev) {
+    static HostStage per_dev[64];
+    if (dev < 0 || dev >= 64) throw error(SKB_ERR_GENERIC, "device index out of range");
+    HostStage &h = per_dev[dev];
+    if (!h.copy) {
+        SKB_CUDA(cudaStreamCreateWithFlags(&h.copy, cudaStreamNonBlocking));
+        cudaEvent_t *evs[] = {&h.copied[0], &h.copied[1], &h.consumed[0], &h.consumed[1], &h.start};
+        for (cudaEvent_t *e : evs) SKB_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    }
+    return h;
+}
+
+static void apply_host_dense_pipelined(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA,
+                                       int dim, int64_t offset, bool shard, int device) {
+    const bool colwise = dim == SL_COLUMNWISE;
+    const int64_t sk = colwise ? A->m : A->n, other = colwise ? A->n : A->m;
+    if (offset < 0 || offset + sk > t->N || (!shard && sk != t->N))
+        throw error(SKB_ERR_INVALID_PARAM, "apply: sketched dimension of A does not match N");
+    const int64_t sa_sk = colwise ? SA->m : SA->n, sa_other = colwise ? SA->n : SA->m;
+    if (sa_sk != t->S || sa_other != other) throw error(SKB_ERR_INVALID_PARAM, "apply: SA has the wrong shape");
+    cudaStream_t st = g_stream;
+    HostStage &h = host_stage(device);
+    const size_t chunk_bytes_target = (size_t)256 << 20;
+    int64_t krows = (int64_t)(chunk_bytes_target / ((size_t)other * 8));
+    krows = krows / 16 * 16;
+    if (krows < 16) krows = 16;
+    if (krows > sk) krows = sk;
+    const size_t need = (size_t)krows * (size_t)other * 8;
+    if (h.cap < need) {
+        SKB_CUDA(cudaStreamSynchronize(st));
+        SKB_CUDA(cudaStreamSynchronize(h.copy));
+        for (int b = 0; b < 2; b++) { cudaFree(h.buf[b]); h.buf[b] = nullptr; }
+        h.cap = 0;
+        for (int b = 0; b < 2; b++) SKB_CUDA(cudaMalloc(&h.buf[b], need));
+        h.cap = need;
+    }
+    const size_t obytes = (size_t)SA->ld * (size_t)SA->n * 8;
+    if (h.out_cap < obytes) {
+        SKB_CUDA(cudaStreamSynchronize(st));
+        cudaFree(h.out); h.out = nullptr; h.out_cap = 0;
+        SKB_CUDA(cudaMalloc(&h.out, obytes ? obytes : 16));
+        h.out_cap = obytes;
+    }
+    sl_matrix_t dSA = *SA;
+    dSA.on_device = true; dSA.device = device; dSA.data = h.out;
+    SKB_CUDA(cudaMemsetAsync(h.out, 0, obytes, st));
+    SKB_CUDA(cudaEventRecord(h.start, st));
+    SKB_CUDA(cudaStreamWaitEvent(h.copy, h.start, 0));
+    int c = 0;
+    for (int64_t k0 = 0; k0 < sk; k0 += krows, c++) {
+        const int64_t kc = sk - k0 < krows ? sk - k0 : krows;
+        const int b = c & 1;
+        if (c >= 2) SKB_CUDA(cudaStreamWaitEvent(h.copy, h.consumed[b], 0));
+        sl_matrix_t dA = *A;
+        dA.on_device = true; dA.device = device; dA.data = h.buf[b];
+        if (colwise) {     // A is sk x other column-major: rows [k0, k0+kc) of every column
+            dA.m = kc; dA.n = other; dA.ld = kc;
+            SKB_CUDA(cudaMemcpy2DAsync(h.buf[b], (size_t)kc * 8, (const double *)A->data + k0,
+                                       (size_t)A->ld * 8, (size_t)kc * 8, (size_t)other,
+                                       cudaMemcpyHostToDevice, h.copy));
+        } else {           // A is other x sk column-major: columns [k0, k0+kc) are contiguous
+            dA.m = other; dA.n = kc; dA.ld = A->ld;
+            SKB_CUDA(cudaMemcpyAsync(h.buf[b], (const double *)A->data + (size_t)k0 * A->ld,
+                                     (size_t)kc * (size_t)A->ld * 8, cudaMemcpyHostToDevice, h.copy));
+        }
+        SKB_CUDA(cudaEventRecord(h.copied[b], h.copy));
+        SKB_CUDA(cudaStreamWaitEvent(st, h.copied[b], 0));
+        apply_device(t, &dA, &dSA, dim, offset + k0, true, true);
+        SKB_CUDA(cudaEventRecord(h.consumed[b], st));
+    }
+    SKB_CUDA(cudaMemcpyAsync(SA->data, h.out, obytes, cudaMemcpyDeviceToHost, st));
+    SKB_CUDA(cudaStreamSynchronize(st));
 }
 
 // Host operands: stage through device memory (copies inside the call, synchronous).
@@ -353,6 +439,11 @@ static void apply_any(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA,
     int device = 0;
     SKB_CUDA(cudaGetDevice(&device));
     cudaStream_t st = g_stream;
+    if (t->is_dense() && A->kind == MK_DENSE && A->dtype == SL_DTYPE_F64 && SA->dtype == SL_DTYPE_F64 &&
+        (size_t)A->m * (size_t)A->n * 8 > ((size_t)64 << 20)) {
+        apply_host_dense_pipelined(t, A, SA, dim, offset, shard, device);
+        return;
+    }
     sl_matrix_t dA = *A, dSA = *SA;
     dA.on_device = dSA.on_device = true; dA.device = dSA.device = device;
     void *bufs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};

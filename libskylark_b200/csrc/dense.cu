@@ -397,8 +397,11 @@ static SideStreams &side_streams() {
 template <typename TX, bool ROWS>
 static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t m, size_t koff,
                           size_t nloc, TX *OUT, size_t ldo, const RftEpilogue &epi,
-                          void *workspace, size_t workspace_bytes, cudaStream_t st) {
+                          void *workspace, size_t workspace_bytes, cudaStream_t st,
+                          bool accumulate) {
     const size_t S = p.S;
+    if (accumulate && (sizeof(TX) != 8 || epi.shifts != nullptr))
+        throw error(SKB_ERR_INVALID_USAGE, "dense apply: accumulation needs fp64 and no epilogue");
     if (S == 0 || m == 0) return;
     size_t kc_max = panel_rows_for(S);
     if (kc_max > nloc) kc_max = (nloc + BK - 1) / BK * BK;
@@ -420,12 +423,12 @@ static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t 
     const long long ntiles = (long long)ntm * ntn;
     const bool has_epi = epi.shifts != nullptr;
     const bool tile_mode = ntiles >= 4 * 148;     // enough tiles: no k split
-    const bool single = npanels == 1;
+    const bool single = npanels == 1 && !accumulate;
     // direct stores (and the fused epilogue) need one CTA to own a tile's whole sum
     const bool direct_ok = single;
     const bool all_direct = single && tile_mode;
     const bool use_accbuf = sizeof(TX) == 4 && !all_direct;
-    const bool need_zero = !all_direct;
+    const bool need_zero = !all_direct && !accumulate;
     const bool fuse_epi = has_epi && all_direct;
 
     void *gemm_out = use_accbuf ? (void *)accbuf : (void *)OUT;
@@ -503,13 +506,13 @@ static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t 
 void dense_apply(const DenseParams &p, bool layout_rows, bool f32, const void *X, size_t ldx,
                  size_t m, size_t koff, size_t nloc, void *OUT, size_t ldo,
                  const RftEpilogue &epi, void *workspace, size_t workspace_bytes,
-                 cudaStream_t st) {
+                 cudaStream_t st, bool accumulate) {
     if (f32) {
-        if (layout_rows) dense_apply_t<float, true>(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st);
-        else dense_apply_t<float, false>(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st);
+        if (layout_rows) dense_apply_t<float, true>(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st, accumulate);
+        else dense_apply_t<float, false>(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st, accumulate);
     } else {
-        if (layout_rows) dense_apply_t<double, true>(p, (const double *)X, ldx, m, koff, nloc, (double *)OUT, ldo, epi, workspace, workspace_bytes, st);
-        else dense_apply_t<double, false>(p, (const double *)X, ldx, m, koff, nloc, (double *)OUT, ldo, epi, workspace, workspace_bytes, st);
+        if (layout_rows) dense_apply_t<double, true>(p, (const double *)X, ldx, m, koff, nloc, (double *)OUT, ldo, epi, workspace, workspace_bytes, st, accumulate);
+        else dense_apply_t<double, false>(p, (const double *)X, ldx, m, koff, nloc, (double *)OUT, ldo, epi, workspace, workspace_bytes, st, accumulate);
     }
 }
 

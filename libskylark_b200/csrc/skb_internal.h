@@ -113,7 +113,7 @@ size_t dense_workspace_bytes(const DenseParams &p, size_t nloc, bool layout_rows
 void dense_apply(const DenseParams &p, bool layout_rows, bool f32, const void *X, size_t ldx,
                  size_t m, size_t koff, size_t nloc, void *OUT, size_t ldo,
                  const RftEpilogue &epi, void *workspace, size_t workspace_bytes,
-                 cudaStream_t st);
+                 cudaStream_t st, bool accumulate = false);   // accumulate: OUT += (fp64, no epilogue)
 // K0 for tests: dense block S[i0:i0+h, j0:j0+w] column-major into out
 void dense_export_block(const DenseParams &p, size_t i0, size_t j0, size_t h, size_t w,
                         double *out, cudaStream_t st);

@@ -112,3 +112,19 @@ def test_fp32_tensors(sk, oracle):
     A = torch.randn(5000, 100, dtype=torch.float32, device="cuda")
     got = J.apply(A, None, "columnwise")
     assert rel_fro(got.cpu().numpy(), OJ.apply(A.cpu().numpy().astype(np.float64), "columnwise")) < TOL32
+
+
+def test_large_host_arrays_take_the_pipelined_path(sk, oracle):
+    """numpy operands above 64 MB are staged chunk by chunk (copy overlapped with compute)."""
+    n, s, d = 70000, 48, 160        # 89.6 MB
+    c, oc = _ctx(sk, oracle, 77)
+    S, O = sk.JLT(n, s, c), oracle.JLT(n, s, oc)
+    A = np.random.default_rng(9).standard_normal((n, d))
+    want = O.apply(A, "columnwise")
+    assert rel_fro(S.apply(A.copy(), None, "columnwise"), want) < TOL64          # C order
+    assert rel_fro(S.apply(np.asfortranarray(A), None, "columnwise"), want) < TOL64   # F order
+    B = np.ascontiguousarray(A.T)
+    assert rel_fro(S.apply(B, None, "rowwise"), want.T) < TOL64
+    half = n // 2
+    part = S.apply_shard(A[:half].copy(), None, 0, 0) + S.apply_shard(A[half:].copy(), None, 0, half)
+    assert rel_fro(part, want) < TOL64
