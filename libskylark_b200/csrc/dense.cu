@@ -107,7 +107,11 @@ void dense_export_block(const DenseParams &p, size_t i0, size_t j0, size_t h, si
 #ifndef SKB_STAGES
 #define SKB_STAGES 4
 #endif
-static constexpr int BM = 128, BN = 128, BK = SKB_BK, STAGES = SKB_STAGES, NTHREADS = 256;
+static constexpr int BM = 128, BN = 128, BK = SKB_BK, STAGES = SKB_STAGES;
+// Warp layout (WM x WN warps over the 128 x 128 tile) is a template parameter: measured on
+// B200, 2 x 4 warps (64 x 32 warp tiles, 64 accumulators/thread) is fastest for fp64 operands
+// (C2: 307 vs 334 ms), 4 x 4 warps (32 x 32 warp tiles) for fp32 operands with the fused
+// cosine epilogue (C5 shard: 470 vs 611 ms) where conversions and the epilogue need covering.
 static constexpr int LDP = BM + 4;   // doubles; = 4 mod 16 -> conflict-free 64-bit fragment loads
 
 template <typename TX> struct XTile;
@@ -159,33 +163,58 @@ struct GemmArgs {
     const double *scales, *shifts; double outscale; int has_epi;
 };
 
-// Copy `count` elements of CPB/sizeof(T) at a time; rows x cols tile from global
-// (row stride gld elements) into shared (row stride sld), zero-filling beyond
-// (row_limit, col_limit).
-template <typename T, int CPB>
-__device__ __forceinline__ void load_tile(T *smem, int sld, const T *g, size_t gld, int rows,
-                                          int cols, long long row_limit, long long col_limit) {
+// Copy a TR x TC tile from global (row stride gld elements) into shared (row stride sld)
+// with CPB-byte cp.async, zero-filling beyond (row_limit, col_limit).  Every thread copies
+// the same column offset of rows r0, r0 + RSTEP, ...: one division per call, then only
+// pointer increments -- the copy issue sits on the critical path of every k-step.
+template <typename T, int CPB, int NT, int TR, int TC>
+__device__ __forceinline__ void load_tile(T *smem, int sld, const T *g, size_t gld,
+                                          long long row_limit, long long col_limit) {
     constexpr int EPC = CPB / (int)sizeof(T);          // elements per copy
-    const int cpr = cols / EPC;                        // copies per row
-    const int total = rows * cpr;
-    for (int c = threadIdx.x; c < total; c += NTHREADS) {
-        int r = c / cpr, q = (c - r * cpr) * EPC;
-        long long rem = col_limit - q;
-        int nb = 0;
-        if (r < row_limit && rem > 0) nb = rem >= EPC ? CPB : (int)rem * (int)sizeof(T);
-        const T *src = nb > 0 ? g + (size_t)r * gld + q : g;
-        cp_async<CPB>(smem + r * sld + q, src, nb);
+    constexpr int CPR = TC / EPC;                      // copies per row
+    static_assert(NT % CPR == 0 || CPR % NT == 0, "thread count must tile the copies of a row");
+    if (CPR <= NT) {
+        constexpr int RSTEP = NT / (CPR <= NT ? CPR : NT), Q = (TR + RSTEP - 1) / RSTEP;
+        const int r0 = threadIdx.x / CPR, col = (threadIdx.x % CPR) * EPC;
+        const long long rem = col_limit - col;
+        const int colbytes = rem <= 0 ? 0 : (rem >= EPC ? CPB : (int)rem * (int)sizeof(T));
+        const T *src = g + (size_t)r0 * gld + col;
+        T *dst = smem + r0 * sld + col;
+#pragma unroll
+        for (int q = 0; q < Q; q++) {
+            const int r = r0 + q * RSTEP;
+            if (TR % RSTEP == 0 || r < TR) {
+                const int nb = r < row_limit ? colbytes : 0;
+                cp_async<CPB>(dst, nb > 0 ? src : g, nb);
+            }
+            src += (size_t)RSTEP * gld;
+            dst += RSTEP * sld;
+        }
+    } else {                                           // more copies per row than threads
+        constexpr int PER = CPR / (CPR <= NT ? 1 : NT);
+#pragma unroll 1
+        for (int r = 0; r < TR; r++) {
+#pragma unroll
+            for (int p = 0; p < PER; p++) {
+                const int col = (threadIdx.x + p * NT) * EPC;
+                const long long rem = col_limit - col;
+                int nb = 0;
+                if (r < row_limit && rem > 0) nb = rem >= EPC ? CPB : (int)rem * (int)sizeof(T);
+                cp_async<CPB>(smem + r * sld + col, nb > 0 ? g + (size_t)r * gld + col : g, nb);
+            }
+        }
     }
 }
 
-template <typename TX, bool ROWS, int CPB_P, int CPB_X>
-__global__ void __launch_bounds__(NTHREADS, 1) k_dense_gemm(GemmArgs a) {
+template <typename TX, bool ROWS, int CPB_P, int CPB_X, int WM, int WN>
+__global__ void __launch_bounds__(32 * WM * WN, 1) k_dense_gemm(GemmArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     using SM = GemmSmem<TX, ROWS>;
+    constexpr int NT = 32 * WM * WN, WTM = BM / WM, WTN = BN / WN, MI = WTM / 8, NI = WTN / 8;
     constexpr int LDX = ROWS ? XTile<TX>::LD_ROWS : XTile<TX>::LD_COLS;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm = warp & 1, wn = warp >> 1;
+    const int wm = warp % WM, wn = warp / WM;
     const int g = lane >> 2, t4 = lane & 3;
 
     const long long total = (long long)a.ntm * a.ntn * a.nk;
@@ -209,11 +238,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_dense_gemm(GemmArgs a) {
         const long long i_lim = (long long)a.S - (long long)i0;   // valid i in tile
         const long long j_lim = (long long)a.m - (long long)j0;
 
-        double acc[8][4][2];
+        double acc[MI][NI][2];
 #pragma unroll
-        for (int mi = 0; mi < 8; mi++)
+        for (int mi = 0; mi < MI; mi++)
 #pragma unroll
-            for (int ni = 0; ni < 4; ni++) { acc[mi][ni][0] = 0.0; acc[mi][ni][1] = 0.0; }
+            for (int ni = 0; ni < NI; ni++) { acc[mi][ni][0] = 0.0; acc[mi][ni][1] = 0.0; }
 
         auto issue = [&](int ks, int slot) {
             unsigned char *base = smem_raw + (size_t)slot * SM::STAGE_BYTES;
@@ -221,11 +250,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_dense_gemm(GemmArgs a) {
             TX *Xs = reinterpret_cast<TX *>(base + SM::P_ELEMS * sizeof(double));
             const long long kk0 = (long long)ks * BK;
             const long long k_lim = (long long)a.kc - kk0;          // valid kk in this step
-            load_tile<double, CPB_P>(Ps, LDP, a.P + (size_t)kk0 * a.S + i0, a.S, BK, BM, k_lim, i_lim);
+            load_tile<double, CPB_P, NT, BK, BM>(Ps, LDP, a.P + (size_t)kk0 * a.S + i0, a.S, k_lim, i_lim);
             if (ROWS)
-                load_tile<TX, CPB_X>(Xs, LDX, Xg + (size_t)kk0 * a.ldx + j0, a.ldx, BK, BN, k_lim, j_lim);
+                load_tile<TX, CPB_X, NT, BK, BN>(Xs, LDX, Xg + (size_t)kk0 * a.ldx + j0, a.ldx, k_lim, j_lim);
             else
-                load_tile<TX, CPB_X>(Xs, LDX, Xg + (size_t)j0 * a.ldx + kk0, a.ldx, BN, BK, j_lim, k_lim);
+                load_tile<TX, CPB_X, NT, BN, BK>(Xs, LDX, Xg + (size_t)j0 * a.ldx + kk0, a.ldx, j_lim, k_lim);
         };
 
         const int nsteps = ks1 - ks0;
@@ -247,20 +276,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_dense_gemm(GemmArgs a) {
             const TX *Xs = reinterpret_cast<const TX *>(base + SM::P_ELEMS * sizeof(double));
 #pragma unroll
             for (int k4 = 0; k4 < BK / 4; k4++) {
-                double af[8], bf[4];
-                const double *pa = Ps + (k4 * 4 + t4) * LDP + wm * 64 + g;
+                double af[MI], bf[NI];
+                const double *pa = Ps + (k4 * 4 + t4) * LDP + wm * WTM + g;
 #pragma unroll
-                for (int mi = 0; mi < 8; mi++) af[mi] = pa[mi * 8];
+                for (int mi = 0; mi < MI; mi++) af[mi] = pa[mi * 8];
 #pragma unroll
-                for (int ni = 0; ni < 4; ni++) {
-                    int j = wn * 32 + ni * 8 + g;
+                for (int ni = 0; ni < NI; ni++) {
+                    int j = wn * WTN + ni * 8 + g;
                     bf[ni] = ROWS ? (double)Xs[(k4 * 4 + t4) * LDX + j]
                                   : (double)Xs[j * LDX + k4 * 4 + t4];
                 }
 #pragma unroll
-                for (int mi = 0; mi < 8; mi++)
+                for (int mi = 0; mi < MI; mi++)
 #pragma unroll
-                    for (int ni = 0; ni < 4; ni++)
+                    for (int ni = 0; ni < NI; ni++)
                         dmma884(acc[mi][ni][0], acc[mi][ni][1], af[mi], bf[ni]);
             }
         }
@@ -271,17 +300,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_dense_gemm(GemmArgs a) {
         const bool full = (ks0 == 0 && ks1 == a.nk);
         const bool direct = full && a.direct_ok;
 #pragma unroll
-        for (int mi = 0; mi < 8; mi++) {
-            const long long il = wm * 64 + mi * 8 + g;
+        for (int mi = 0; mi < MI; mi++) {
+            const long long il = wm * WTM + mi * 8 + g;
             if (il >= i_lim) continue;
             const size_t i = i0 + il;
             double sc = 1.0, sh = 0.0;
             if (direct && a.has_epi) { sc = a.scales[i]; sh = a.shifts[i]; }
 #pragma unroll
-            for (int ni = 0; ni < 4; ni++) {
+            for (int ni = 0; ni < NI; ni++) {
 #pragma unroll
                 for (int e = 0; e < 2; e++) {
-                    const long long jl = wn * 32 + ni * 8 + t4 * 2 + e;
+                    const long long jl = wn * WTN + ni * 8 + t4 * 2 + e;
                     if (jl >= j_lim) continue;
                     const size_t j = j0 + jl;
                     const size_t off = ROWS ? i * a.ldo + j : i + j * a.ldo;
@@ -352,12 +381,13 @@ template <typename TX, bool ROWS>
 static void launch_gemm(const GemmArgs &a, bool al16p, bool alx, unsigned grid, cudaStream_t st) {
     using SM = GemmSmem<TX, ROWS>;
     constexpr int XS = sizeof(TX) == 8 ? 8 : 4;   // small-copy size for X
+    constexpr int WM = sizeof(TX) == 8 ? 2 : 4, WN = 4;
 #define SKB_LAUNCH(CP, CX)                                                                       \
     do {                                                                                         \
-        auto kern = k_dense_gemm<TX, ROWS, CP, CX>;                                              \
+        auto kern = k_dense_gemm<TX, ROWS, CP, CX, WM, WN>;                                      \
         SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
                                       (int)SM::BYTES));                                          \
-        kern<<<grid, NTHREADS, SM::BYTES, st>>>(a);                                              \
+        kern<<<grid, 32 * WM * WN, SM::BYTES, st>>>(a);                                          \
     } while (0)
     LaunchScope ls(KC_GEMM, st);
     if (al16p && alx) SKB_LAUNCH(16, 16);
@@ -597,10 +627,10 @@ static void noalloc_apply(const DenseParams &p, const double *X, size_t ldx, siz
         profiler().launches[KC_GEMM]++;
 #define SKB_NA_LAUNCH(CP, CX)                                                                      \
         do {                                                                                       \
-            auto kern = k_dense_gemm<double, ROWS, CP, CX>;                                        \
+            auto kern = k_dense_gemm<double, ROWS, CP, CX, 2, 4>;                                  \
             SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
                                           (int)SM::BYTES));                                        \
-            kern<<<grid, NTHREADS, SM::BYTES, st>>>(a);                                            \
+            kern<<<grid, 256, SM::BYTES, st>>>(a);                                                 \
         } while (0)
         if (al16p && alx_p) SKB_NA_LAUNCH(16, 16);
         else if (al16p) SKB_NA_LAUNCH(16, 8);

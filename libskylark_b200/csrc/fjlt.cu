@@ -273,7 +273,7 @@ struct DctPlan {
     cplx *W1, *W2;            // W_N2[m], W_N1[m]
     cplx *Tlo, *Thi;          // W_Np^(lo), W_Np^(hi << lo_bits)
     cplx *post;               // per sample: W_N^k, W_4N^k
-    size_t G;                 // sequences per CTA
+    size_t G1, G2;            // sequences per CTA in pass 1 / pass 2
 };
 
 __global__ void k_dct_tables(DctPlan pl, const int32_t *__restrict__ samples, size_t S) {
@@ -299,9 +299,9 @@ __global__ void k_dct_tables(DctPlan pl, const int32_t *__restrict__ samples, si
 template <int R>
 __device__ __forceinline__ void stockham_pass(const cplx *in, cplx *out, int L, int Ns, int G,
                                               const cplx *__restrict__ W) {
-    const int per = L / R, units = G * per, step = L / (Ns * R);
+    const int per = L / R, units = G * per, step = L / (Ns * R), pshift = 31 - __clz(per);
     for (int u = threadIdx.x; u < units; u += blockDim.x) {
-        const int g = u / per, j = u - g * per, k = j & (Ns - 1);
+        const int g = u >> pshift, j = u & (per - 1), k = j & (Ns - 1);
         const cplx *src = in + g * L + j;
         cplx a[R];
 #pragma unroll
@@ -357,25 +357,48 @@ __global__ void __launch_bounds__(1024)
 k_dct_pass1(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan pl,
             const uint32_t *__restrict__ Dbits, double inscale, cplx *__restrict__ H) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int G = (int)pl.G, N2 = (int)pl.N2;
+    const int G = (int)pl.G1, N2 = (int)pl.N2;
     const size_t N = pl.N, N1 = pl.N1;
-    cplx *a = reinterpret_cast<cplx *>(smem_raw), *b = a + (size_t)G * N2;
+    cplx *a = reinterpret_cast<cplx *>(smem_raw), *b = a + (size_t)G * N2, *Ws = b + (size_t)G * N2;
+    for (int i = threadIdx.x; i < N2; i += blockDim.x) Ws[i] = pl.W1[i];     // twiddles on chip
+    const int gshift = 31 - __clz(G);                                         // G is a power of two
     const size_t n1_0 = (size_t)blockIdx.x * G;
     const double *col = X + (col0 + blockIdx.y) * ldx;
     cplx *Hc = H + (size_t)blockIdx.y * pl.Np;
-    for (int idx = threadIdx.x; idx < G * N2; idx += blockDim.x) {
-        const int g = idx % G, n2 = idx / G;
-        const size_t n = n1_0 + g + N1 * (size_t)n2;
-        cplx z;
-        if (4 * n < N) { z.x = dct_xprime(col, Dbits, 4 * n, inscale); z.y = dct_xprime(col, Dbits, 4 * n + 2, inscale); }
-        else { z.x = dct_xprime(col, Dbits, 2 * N - 4 * n - 1, inscale); z.y = dct_xprime(col, Dbits, 2 * N - 4 * n - 3, inscale); }
-        a[g * N2 + n2] = z;
+    const int total = G * N2;
+    // four elements per trip so that all their (independent) global loads are in flight together
+    for (int base = threadIdx.x; base < total; base += 4 * blockDim.x) {
+        size_t q0[4], q1[4]; uint32_t w0[4], w1[4]; double x0[4], x1[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int idx = base + u * blockDim.x;
+            const int g = idx & (G - 1), n2 = idx >> gshift;
+            const size_t n = n1_0 + g + N1 * (size_t)n2;
+            const bool lowhalf = 4 * n < N;
+            q0[u] = lowhalf ? 4 * n : 2 * N - 4 * n - 1;
+            q1[u] = lowhalf ? 4 * n + 2 : 2 * N - 4 * n - 3;
+            if (idx < total) {
+                w0[u] = __ldg(Dbits + (q0[u] >> 5)); w1[u] = __ldg(Dbits + (q1[u] >> 5));
+                x0[u] = __ldg(col + q0[u]); x1[u] = __ldg(col + q1[u]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int idx = base + u * blockDim.x;
+            if (idx < total) {
+                cplx z;
+                z.x = __dmul_rn((w0[u] >> (q0[u] & 31)) & 1 ? -inscale : inscale, x0[u]);
+                z.y = __dmul_rn((w1[u] >> (q1[u] & 31)) & 1 ? -inscale : inscale, x1[u]);
+                a[(idx & (G - 1)) * N2 + (idx >> gshift)] = z;
+            }
+        }
     }
     __syncthreads();
-    cplx *res = smem_fft(a, b, N2, G, pl.W1);
+    cplx *res = smem_fft(a, b, N2, G, Ws);
     const size_t lo_mask = ((size_t)1 << pl.lo_bits) - 1;
-    for (int idx = threadIdx.x; idx < G * N2; idx += blockDim.x) {
-        const int g = idx % G, k2 = idx / G;
+#pragma unroll 4
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+        const int g = idx & (G - 1), k2 = idx >> gshift;
         const size_t n1 = n1_0 + g, e = n1 * (size_t)k2;       // < Np
         cplx tw = cmul(pl.Thi[e >> pl.lo_bits], pl.Tlo[e & lo_mask]);
         Hc[(size_t)k2 * N1 + n1] = cmul(res[g * N2 + k2], tw);
@@ -386,12 +409,15 @@ k_dct_pass1(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan pl,
 __global__ void __launch_bounds__(1024)
 k_dct_pass2(DctPlan pl, cplx *__restrict__ H) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int G = (int)pl.G, N1 = (int)pl.N1;
-    cplx *a = reinterpret_cast<cplx *>(smem_raw), *b = a + (size_t)G * N1;
+    const int G = (int)pl.G2, N1 = (int)pl.N1;
+    cplx *a = reinterpret_cast<cplx *>(smem_raw), *b = a + (size_t)G * N1, *Ws = b + (size_t)G * N1;
+    for (int i = threadIdx.x; i < N1; i += blockDim.x) Ws[i] = pl.W2[i];
     cplx *rows = H + (size_t)blockIdx.y * pl.Np + (size_t)blockIdx.x * G * N1;
+#pragma unroll 4
     for (int idx = threadIdx.x; idx < G * N1; idx += blockDim.x) a[idx] = rows[idx];
     __syncthreads();
-    cplx *res = smem_fft(a, b, N1, G, pl.W2);
+    cplx *res = smem_fft(a, b, N1, G, Ws);
+#pragma unroll 4
     for (int idx = threadIdx.x; idx < G * N1; idx += blockDim.x) rows[idx] = res[idx];
 }
 
@@ -473,11 +499,15 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         pl.Tlo = tab; tab += (size_t)1 << pl.lo_bits;
         pl.Thi = tab; tab += (pl.Np >> pl.lo_bits) + 1;
         pl.post = tab;
-        // sequences per CTA: two ping-pong buffers of G*L complex doubles within ~128 KB
-        size_t Lmax = pl.N2;
-        pl.G = 4096 / Lmax; if (pl.G < 1) pl.G = 1; if (pl.G > 8) pl.G = 8;
-        while (pl.G > 1 && (pl.N1 % pl.G || pl.N2 % pl.G)) pl.G /= 2;
-        const size_t smem1 = 2 * pl.G * pl.N2 * sizeof(cplx), smem2 = 2 * pl.G * pl.N1 * sizeof(cplx);
+        // sequences per CTA: G*L = 2048 points -> two 32 KB ping-pong buffers, 512 threads with
+        // one radix-4 unit each per pass, three CTAs per SM
+        auto seqs = [](size_t L, size_t other) {
+            size_t g = 2048 / L; if (g < 1) g = 1; if (g > 16) g = 16;
+            while (g > 1 && other % g) g /= 2;
+            return g;
+        };
+        pl.G1 = seqs(pl.N2, pl.N1); pl.G2 = seqs(pl.N1, pl.N2);
+        const size_t smem1 = (2 * pl.G1 + 1) * pl.N2 * sizeof(cplx), smem2 = (2 * pl.G2 + 1) * pl.N1 * sizeof(cplx);
         SKB_CUDA(cudaFuncSetAttribute(k_dct_pass1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
         SKB_CUDA(cudaFuncSetAttribute(k_dct_pass2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
         {
@@ -492,17 +522,17 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         const double inscale = 1.0 / sqrt(2.0 * (double)N), outscale = sqrt((double)N / (double)S);
         // one radix-4 unit per thread per pass where possible (latency hiding by occupancy)
         auto threads_for = [](size_t units) { size_t t = 128; while (t < units && t < 1024) t *= 2; return (unsigned)t; };
-        const unsigned thr1 = threads_for(pl.G * pl.N2 / 4), thr2 = threads_for(pl.G * pl.N1 / 4);
+        const unsigned thr1 = threads_for(pl.G1 * pl.N2 / 4), thr2 = threads_for(pl.G2 * pl.N1 / 4);
         for (size_t c0 = 0; c0 < m; c0 += B) {
             const size_t nb = m - c0 < B ? m - c0 : B;
             {
                 LaunchScope ls(KC_FJLT, st);
-                k_dct_pass1<<<dim3((unsigned)(pl.N1 / pl.G), (unsigned)nb), thr1, smem1, st>>>(
+                k_dct_pass1<<<dim3((unsigned)(pl.N1 / pl.G1), (unsigned)nb), thr1, smem1, st>>>(
                     Xc, ldc, c0, pl, Dbits, inscale, H);
             }
             {
                 LaunchScope ls(KC_FJLT, st);
-                k_dct_pass2<<<dim3((unsigned)(pl.N2 / pl.G), (unsigned)nb), thr2, smem2, st>>>(pl, H);
+                k_dct_pass2<<<dim3((unsigned)(pl.N2 / pl.G2), (unsigned)nb), thr2, smem2, st>>>(pl, H);
             }
             {
                 LaunchScope ls(KC_FJLT, st);

@@ -2,6 +2,7 @@
 // assembles), and DFMA+DMMA interleaved (do the two share one pipe?).  Prints TFLOP/s.
 // Build: nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o fp64_peak fp64_peak.cu
 #include <cstdio>
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 #define ITERS 4096
@@ -91,8 +92,9 @@ static double run(K kern, int blocks, int threads, double *out) {
     return best;
 }
 
-int main() {
-    int blocks = 148 * 8, threads = 256;
+int main(int argc, char **argv) {
+    int blocks = argc > 1 ? atoi(argv[1]) : 148 * 8, threads = argc > 2 ? atoi(argv[2]) : 256;
+    printf("blocks=%d threads=%d\n", blocks, threads);
     double *out; cudaMalloc(&out, (size_t)blocks * threads * 8);
     double thr = (double)blocks * threads;
     double ms = run(k_dfma, blocks, threads, out);
