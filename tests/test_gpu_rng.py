@@ -88,11 +88,11 @@ def test_dense_entries_within_2ulp(sk, oracle):
     j = sk.JLT(n, s, lib.Context(123834, 17))
     oj = oracle.JLT(n, s, oracle.Context(123834, 17))
     d = ulp_diff(j.export_dense(), oj.realize())
-    # Target (BASELINE.json): 2 ulp.  Measured on B200 (profiles/r01_c2_jlt_v1.txt): 99.8 % of
-    # the Gaussians are within 2 ulp of the glibc-based oracle, 0.2 % are at 3 ulp, max 5:
-    # libdevice log/cos and glibc log/cos are each faithful to 1-2 ulp, not correctly rounded,
-    # and sqrt(-2 log) * cos chains three roundings.  Asserted: what holds.
-    assert (d <= 2).mean() >= 0.995 and d.max() <= 6, (float((d <= 2).mean()), int(d.max()))
+    # Target (BASELINE.json): 2 ulp.  Measured on B200 over 2e6 Gaussians with the in-house
+    # 0.6-ulp cosine (rng.cuh: cos_0_2pi): 97.5 % bit-identical to the glibc-based oracle,
+    # 99.987 % within 2 ulp, 0.013 % at 3 ulp, one sample at 5.  The rest comes from log():
+    # libdevice's (1 ulp) and glibc's (0.52 ulp) are both faithful, neither correctly rounded.
+    assert (d <= 2).mean() >= 0.9995 and d.max() <= 6, (float((d <= 2).mean()), int(d.max()))
     # sub-block addressing S[i0:i0+h, j0:j0+w]
     assert np.array_equal(j.export_dense(7, 11, 20, 30), j.export_dense()[7:27, 11:41])
     c = sk.CT(n, s, 2.0, lib.Context(9))
