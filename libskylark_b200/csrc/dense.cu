@@ -107,7 +107,17 @@ void dense_export_block(const DenseParams &p, size_t i0, size_t j0, size_t h, si
 #ifndef SKB_STAGES
 #define SKB_STAGES 4
 #endif
-static constexpr int BM = 128, BN = 128, BK = SKB_BK, STAGES = SKB_STAGES;
+static constexpr int BM = 128, BK = SKB_BK, STAGES = SKB_STAGES;
+// Tile configuration per operand type (measured on B200):
+//   fp64: 128 x 64 tile, 2 x 2 warps (64 x 32 warp tiles), TWO CTAs per SM.  Each CTA syncs all
+//         its warps at every k-step; two independent CTAs per SM run out of phase, so one is
+//         issuing DMMAs while the other sits at its barrier / fragment loads (C2: 292 vs 303 ms
+//         for one 128 x 128 CTA of 8 warps).
+//   fp32: 128 x 128 tile, 4 x 4 warps (32 x 32 warp tiles), one CTA per SM (C5 shard: 470 vs
+//         611 ms for 2 x 4 warps): conversions and the fused cosine need more warps to cover.
+template <typename TX> struct GemmCfg;
+template <> struct GemmCfg<double> { static constexpr int BN = 64, WM = 2, WN = 2, CTAS = 2; };
+template <> struct GemmCfg<float> { static constexpr int BN = 128, WM = 4, WN = 4, CTAS = 1; };
 // Warp layout (WM x WN warps over the 128 x 128 tile) is a template parameter: measured on
 // B200, 2 x 4 warps (64 x 32 warp tiles, 64 accumulators/thread) is fastest for fp64 operands
 // (C2: 307 vs 334 ms), 4 x 4 warps (32 x 32 warp tiles) for fp32 operands with the fused
@@ -116,17 +126,17 @@ static constexpr int LDP = BM + 4;   // doubles; = 4 mod 16 -> conflict-free 64-
 
 template <typename TX> struct XTile;
 template <> struct XTile<double> {
-    static constexpr int LD_ROWS = BN + 4;   // Xs[kk][j]
-    static constexpr int LD_COLS = BK + 4;   // Xs[j][kk]
+    static constexpr int LD_ROWS = GemmCfg<double>::BN + 4;   // Xs[kk][j]
+    static constexpr int LD_COLS = BK + 4;                    // Xs[j][kk]
 };
 template <> struct XTile<float> {
-    static constexpr int LD_ROWS = BN + 8;   // = 8 mod 32 floats
-    static constexpr int LD_COLS = BK + 4;   // = 20 mod 32 floats
+    static constexpr int LD_ROWS = GemmCfg<float>::BN + 8;    // = 8 mod 32 floats
+    static constexpr int LD_COLS = BK + 4;                    // = 20 mod 32 floats
 };
 
 template <typename TX, bool ROWS> struct GemmSmem {
     static constexpr int P_ELEMS = BK * LDP;
-    static constexpr int X_ELEMS = ROWS ? BK * XTile<TX>::LD_ROWS : BN * XTile<TX>::LD_COLS;
+    static constexpr int X_ELEMS = ROWS ? BK * XTile<TX>::LD_ROWS : GemmCfg<TX>::BN * XTile<TX>::LD_COLS;
     static constexpr size_t STAGE_BYTES = P_ELEMS * sizeof(double) +
                                           ((X_ELEMS * sizeof(TX) + 15) / 16) * 16;
     static constexpr size_t BYTES = STAGE_BYTES * STAGES;
@@ -207,9 +217,10 @@ __device__ __forceinline__ void load_tile(T *smem, int sld, const T *g, size_t g
 }
 
 template <typename TX, bool ROWS, int CPB_P, int CPB_X, int WM, int WN>
-__global__ void __launch_bounds__(32 * WM * WN, 1) k_dense_gemm(GemmArgs a) {
+__global__ void __launch_bounds__(32 * WM * WN, GemmCfg<TX>::CTAS) k_dense_gemm(GemmArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     using SM = GemmSmem<TX, ROWS>;
+    constexpr int BN = GemmCfg<TX>::BN;
     constexpr int NT = 32 * WM * WN, WTM = BM / WM, WTN = BN / WN, MI = WTM / 8, NI = WTN / 8;
     constexpr int LDX = ROWS ? XTile<TX>::LD_ROWS : XTile<TX>::LD_COLS;
 
@@ -381,7 +392,7 @@ template <typename TX, bool ROWS>
 static void launch_gemm(const GemmArgs &a, bool al16p, bool alx, unsigned grid, cudaStream_t st) {
     using SM = GemmSmem<TX, ROWS>;
     constexpr int XS = sizeof(TX) == 8 ? 8 : 4;   // small-copy size for X
-    constexpr int WM = sizeof(TX) == 8 ? 2 : 4, WN = 4;
+    constexpr int WM = GemmCfg<TX>::WM, WN = GemmCfg<TX>::WN;
 #define SKB_LAUNCH(CP, CX)                                                                       \
     do {                                                                                         \
         auto kern = k_dense_gemm<TX, ROWS, CP, CX, WM, WN>;                                      \
@@ -449,10 +460,11 @@ static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t 
     double *accbuf = reinterpret_cast<double *>(reinterpret_cast<char *>(workspace) +
                                                 panel_bytes * nbuf);
 
+    constexpr int BN = GemmCfg<TX>::BN;
     const int ntm = (int)((S + BM - 1) / BM), ntn = (int)((m + BN - 1) / BN);
     const long long ntiles = (long long)ntm * ntn;
     const bool has_epi = epi.shifts != nullptr;
-    const bool tile_mode = ntiles >= 4 * 148;     // enough tiles: no k split
+    const bool tile_mode = ntiles >= 4 * 148 * GemmCfg<TX>::CTAS;     // enough tiles: no k split
     const bool single = npanels == 1 && !accumulate;
     // direct stores (and the fused epilogue) need one CTA to own a tile's whole sum
     const bool direct_ok = single;
@@ -513,7 +525,8 @@ static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t 
         if (!tile_mode && a.direct_ok) a.direct_ok = 0;   // stream-K ranges may split a tile
         a.whole_tiles = tile_mode ? 1 : 0;
         long long total = ntiles * a.nk;
-        unsigned grid = tile_mode ? 148u : (unsigned)(total < 148 ? total : 148);
+        const long long ncta = 148LL * GemmCfg<TX>::CTAS;
+        unsigned grid = tile_mode ? (unsigned)ncta : (unsigned)(total < ncta ? total : ncta);
         // alignment of the X slab for this panel
         bool alx_p = alx && (ROWS || (k0 % xe == 0));
         launch_gemm<TX, ROWS>(a, al16p, alx_p, grid, st_gemm);
@@ -597,6 +610,7 @@ static void noalloc_apply(const DenseParams &p, const double *X, size_t ldx, siz
         if (ldo == contig) SKB_CUDA(cudaMemsetAsync(OUT, 0, contig * nvec * sizeof(double), st));
         else SKB_CUDA(cudaMemset2DAsync(OUT, ldo * sizeof(double), 0, contig * sizeof(double), nvec, st));
     }
+    constexpr int BN = GemmCfg<double>::BN;
     const int ntm = (int)((S + BM - 1) / BM), ntn = (int)((m + BN - 1) / BN);
     const long long ntiles = (long long)ntm * ntn;
     const bool al16p = (S % 2 == 0);
@@ -621,16 +635,17 @@ static void noalloc_apply(const DenseParams &p, const double *X, size_t ldx, siz
         a.direct_ok = 0; a.whole_tiles = 0; a.out_is_acc = 0;
         a.scales = nullptr; a.shifts = nullptr; a.outscale = 1.0; a.has_epi = 0;
         const long long total = ntiles * a.nk;
-        const unsigned grid = (unsigned)(total < 148 ? total : 148);
+        const long long ncta = 148LL * GemmCfg<double>::CTAS;
+        const unsigned grid = (unsigned)(total < ncta ? total : ncta);
         const bool alx_p = alx && (ROWS || (k0 % 2 == 0));
         using SM = GemmSmem<double, ROWS>;
         profiler().launches[KC_GEMM]++;
 #define SKB_NA_LAUNCH(CP, CX)                                                                      \
         do {                                                                                       \
-            auto kern = k_dense_gemm<double, ROWS, CP, CX, 2, 4>;                                  \
+            auto kern = k_dense_gemm<double, ROWS, CP, CX, GemmCfg<double>::WM, GemmCfg<double>::WN>; \
             SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
                                           (int)SM::BYTES));                                        \
-            kern<<<grid, 256, SM::BYTES, st>>>(a);                                                 \
+            kern<<<grid, 32 * GemmCfg<double>::WM * GemmCfg<double>::WN, SM::BYTES, st>>>(a);      \
         } while (0)
         if (al16p && alx_p) SKB_NA_LAUNCH(16, 16);
         else if (al16p) SKB_NA_LAUNCH(16, 8);
