@@ -58,16 +58,21 @@ void dense_generate_panel(const DenseParams &p, size_t k0, size_t kc, double *pa
                           cudaStream_t st) {
     size_t count = kc * p.S;
     if (count == 0) return;
+    static int skip_gen = -1;      // timing experiments only (results are garbage when set)
+    if (skip_gen < 0) skip_gen = getenv("SKB_DEBUG_SKIP_GEN") ? 1 : 0;
+    if (skip_gen) return;
     uint64_t stream0 = p.base + (uint64_t)k0 * p.S;
-    size_t blocks = (count + 255) / 256;
-    size_t cap = (size_t)148 * 64;
+    static int gen_threads = 0;
+    if (!gen_threads) { const char *e = getenv("SKB_GEN_THREADS"); gen_threads = e ? atoi(e) : 128; }
+    size_t blocks = (count + 2 * gen_threads - 1) / (2 * gen_threads);
+    size_t cap = (size_t)148 * 64 * (128 / gen_threads > 0 ? 128 / gen_threads : 1);
     if (blocks > cap) blocks = cap;
     LaunchScope ls(KC_GEN, st);
     if (p.dist == DD_NORMAL)
-        k_gen_panel<DD_NORMAL><<<(unsigned)blocks, 128, 0, st>>>(seed_to_key(p.seed), stream0,
+        k_gen_panel<DD_NORMAL><<<(unsigned)blocks, gen_threads, 0, st>>>(seed_to_key(p.seed), stream0,
                                                                  count, p.scale, panel);
     else
-        k_gen_panel<DD_CAUCHY><<<(unsigned)blocks, 128, 0, st>>>(seed_to_key(p.seed), stream0,
+        k_gen_panel<DD_CAUCHY><<<(unsigned)blocks, gen_threads, 0, st>>>(seed_to_key(p.seed), stream0,
                                                                  count, p.scale, panel);
     SKB_CUDA(cudaGetLastError());
 }
@@ -478,7 +483,9 @@ static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t 
     if (use_accbuf && workspace_bytes < panel_bytes * nbuf + (ROWS ? S * ldo : m * ldo) * sizeof(double))
         throw error(SKB_ERR_ALLOC, "dense apply: workspace too small for accumulation buffer");
     // With several panels the work is forked onto the two internal streams and joined back.
-    const bool forked = npanels > 1;
+    static int no_fork = -1;
+    if (no_fork < 0) no_fork = getenv("SKB_DEBUG_NO_FORK") ? 1 : 0;
+    const bool forked = npanels > 1 && !no_fork;
     cudaStream_t st_gemm = st, st_gen = st;
     SideStreams *ss = nullptr;
     if (forked) {
