@@ -260,7 +260,7 @@ __global__ void k_transpose_to_cols(const double *__restrict__ X, size_t ldx, si
 // FP64 FFT arithmetic (~40 flop per element) is comparable to the HBM time of the element
 // on this part, so this mode is compute/shared-memory bound, not HBM bound.
 // ---------------------------------------------------------------------------
-struct cplx { double x, y; };
+struct __align__(16) cplx { double x, y; };
 __device__ __forceinline__ cplx cmul(cplx a, cplx b) {
     cplx r; r.x = a.x * b.x - a.y * b.y; r.y = a.x * b.y + a.y * b.x; return r;
 }
@@ -295,6 +295,11 @@ __global__ void k_dct_tables(DctPlan pl, const int32_t *__restrict__ samples, si
     }
 }
 
+// Shared-memory FFT buffers are addressed through pad(): one spare element after every 8,
+// which spreads the power-of-two strides of the Stockham scatter over the banks.
+__device__ __forceinline__ int pad(int i) { return i + (i >> 3); }
+__host__ __device__ constexpr size_t padded(size_t n) { return n + (n >> 3) + 8; }
+
 // One radix-R Stockham pass over G sequences of length L held in shared memory.
 template <int R>
 __device__ __forceinline__ void stockham_pass(const cplx *in, cplx *out, int L, int Ns, int G,
@@ -302,26 +307,26 @@ __device__ __forceinline__ void stockham_pass(const cplx *in, cplx *out, int L, 
     const int per = L / R, units = G * per, step = L / (Ns * R), pshift = 31 - __clz(per);
     for (int u = threadIdx.x; u < units; u += blockDim.x) {
         const int g = u >> pshift, j = u & (per - 1), k = j & (Ns - 1);
-        const cplx *src = in + g * L + j;
+        const int sbase = g * L + j;
         cplx a[R];
 #pragma unroll
-        for (int t = 0; t < R; t++) a[t] = src[t * per];
+        for (int t = 0; t < R; t++) a[t] = in[pad(sbase + t * per)];
         if (Ns > 1) {
 #pragma unroll
             for (int t = 1; t < R; t++) a[t] = cmul(a[t], W[t * k * step]);
         }
-        cplx *dst = out + g * L + (j - k) * R + k;
+        const int dbase = g * L + (j - k) * R + k;
         if (R == 2) {
-            dst[0] = cadd(a[0], a[1]);
-            dst[Ns] = csub(a[0], a[1]);
+            out[pad(dbase)] = cadd(a[0], a[1]);
+            out[pad(dbase + Ns)] = csub(a[0], a[1]);
         } else {
             cplx b0 = cadd(a[0], a[2]), b1 = csub(a[0], a[2]), b2 = cadd(a[1], a[3]);
             cplx d = csub(a[1], a[3]);
             cplx b3; b3.x = d.y; b3.y = -d.x;               // -i * (a1 - a3)
-            dst[0] = cadd(b0, b2);
-            dst[Ns] = cadd(b1, b3);
-            dst[2 * Ns] = csub(b0, b2);
-            dst[3 * Ns] = csub(b1, b3);
+            out[pad(dbase)] = cadd(b0, b2);
+            out[pad(dbase + Ns)] = cadd(b1, b3);
+            out[pad(dbase + 2 * Ns)] = csub(b0, b2);
+            out[pad(dbase + 3 * Ns)] = csub(b1, b3);
         }
     }
 }
@@ -359,7 +364,7 @@ k_dct_pass1(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan pl,
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int G = (int)pl.G1, N2 = (int)pl.N2;
     const size_t N = pl.N, N1 = pl.N1;
-    cplx *a = reinterpret_cast<cplx *>(smem_raw), *b = a + (size_t)G * N2, *Ws = b + (size_t)G * N2;
+    cplx *a = reinterpret_cast<cplx *>(smem_raw), *b = a + padded((size_t)G * N2), *Ws = b + padded((size_t)G * N2);
     for (int i = threadIdx.x; i < N2; i += blockDim.x) Ws[i] = pl.W1[i];     // twiddles on chip
     const int gshift = 31 - __clz(G);                                         // G is a power of two
     const size_t n1_0 = (size_t)blockIdx.x * G;
@@ -389,7 +394,7 @@ k_dct_pass1(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan pl,
                 cplx z;
                 z.x = __dmul_rn((w0[u] >> (q0[u] & 31)) & 1 ? -inscale : inscale, x0[u]);
                 z.y = __dmul_rn((w1[u] >> (q1[u] & 31)) & 1 ? -inscale : inscale, x1[u]);
-                a[(idx & (G - 1)) * N2 + (idx >> gshift)] = z;
+                a[pad((idx & (G - 1)) * N2 + (idx >> gshift))] = z;
             }
         }
     }
@@ -401,7 +406,7 @@ k_dct_pass1(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan pl,
         const int g = idx & (G - 1), k2 = idx >> gshift;
         const size_t n1 = n1_0 + g, e = n1 * (size_t)k2;       // < Np
         cplx tw = cmul(pl.Thi[e >> pl.lo_bits], pl.Tlo[e & lo_mask]);
-        Hc[(size_t)k2 * N1 + n1] = cmul(res[g * N2 + k2], tw);
+        Hc[(size_t)k2 * N1 + n1] = cmul(res[pad(g * N2 + k2)], tw);
     }
 }
 
@@ -410,15 +415,15 @@ __global__ void __launch_bounds__(1024)
 k_dct_pass2(DctPlan pl, cplx *__restrict__ H) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int G = (int)pl.G2, N1 = (int)pl.N1;
-    cplx *a = reinterpret_cast<cplx *>(smem_raw), *b = a + (size_t)G * N1, *Ws = b + (size_t)G * N1;
+    cplx *a = reinterpret_cast<cplx *>(smem_raw), *b = a + padded((size_t)G * N1), *Ws = b + padded((size_t)G * N1);
     for (int i = threadIdx.x; i < N1; i += blockDim.x) Ws[i] = pl.W2[i];
     cplx *rows = H + (size_t)blockIdx.y * pl.Np + (size_t)blockIdx.x * G * N1;
 #pragma unroll 4
-    for (int idx = threadIdx.x; idx < G * N1; idx += blockDim.x) a[idx] = rows[idx];
+    for (int idx = threadIdx.x; idx < G * N1; idx += blockDim.x) a[pad(idx)] = rows[idx];
     __syncthreads();
     cplx *res = smem_fft(a, b, N1, G, Ws);
 #pragma unroll 4
-    for (int idx = threadIdx.x; idx < G * N1; idx += blockDim.x) rows[idx] = res[idx];
+    for (int idx = threadIdx.x; idx < G * N1; idx += blockDim.x) rows[idx] = res[pad(idx)];
 }
 
 // sampled bins -> DCT values -> OUT
@@ -507,7 +512,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
             return g;
         };
         pl.G1 = seqs(pl.N2, pl.N1); pl.G2 = seqs(pl.N1, pl.N2);
-        const size_t smem1 = (2 * pl.G1 + 1) * pl.N2 * sizeof(cplx), smem2 = (2 * pl.G2 + 1) * pl.N1 * sizeof(cplx);
+        const size_t smem1 = (2 * padded(pl.G1 * pl.N2) + pl.N2) * sizeof(cplx), smem2 = (2 * padded(pl.G2 * pl.N1) + pl.N1) * sizeof(cplx);
         SKB_CUDA(cudaFuncSetAttribute(k_dct_pass1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
         SKB_CUDA(cudaFuncSetAttribute(k_dct_pass2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
         {
