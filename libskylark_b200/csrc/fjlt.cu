@@ -94,7 +94,7 @@ k_fjlt_direct(const double *__restrict__ X, size_t sk, size_t sj, size_t N, size
 // accumulates (-1)^popc(k1 & n1) * seg[k2] over the segments n1, in registers.  HBM
 // traffic is exactly the algorithmic n*d*8 + s*d*8 bytes; no scratch, no atomics.
 // ---------------------------------------------------------------------------
-static constexpr int WSEG_LOG = 13, WSEG = 1 << WSEG_LOG, WTHREADS = 512, WSPT = 16;
+static constexpr int WSEG_LOG = 13, WSEG = 1 << WSEG_LOG, WTHREADS = 256, WSPT = 32;
 
 __device__ __forceinline__ void cp_async16(void *smem, const void *g) {
     unsigned s = (unsigned)__cvta_generic_to_shared(smem);
@@ -105,8 +105,19 @@ __device__ __forceinline__ void cp_async8(void *smem, const void *g) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(g));
 }
 
-__device__ __forceinline__ double shfl_xor_f64(double v, int m) {
-    return __shfl_xor_sync(0xffffffffu, v, m);
+// Segment element e lives at shared word swz(e): index bits 6..9 are XORed into bits 1..4, so
+// that the three register phases below (which hold bits {0,9..12}, {1..5}, {6..8} of the index
+// per thread) all read and write shared memory without bank conflicts; bit 0 is untouched, so
+// 16-byte pairs stay pairs.
+__device__ __forceinline__ int swz(int e) { return e ^ (((e >> 6) & 15) << 1); }
+
+template <int LEVELS, int STRIDE>
+__device__ __forceinline__ void wht_regs(double *v) {      // butterflies over register index bits
+#pragma unroll
+    for (int h = STRIDE; h < (STRIDE << LEVELS); h <<= 1)
+#pragma unroll
+        for (int i = 0; i < 32; i++)
+            if (!(i & h) && i + h < 32) { double a = v[i], b = v[i + h]; v[i] = a + b; v[i + h] = a - b; }
 }
 
 template <bool AL16>
@@ -119,13 +130,19 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
     double *buf0 = reinterpret_cast<double *>(smem_raw);
     double *buf1 = buf0 + WSEG;
     int32_t *smp = reinterpret_cast<int32_t *>(buf1 + WSEG);      // [WTHREADS * WSPT]
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x;
     const size_t nseg = N >> WSEG_LOG;
     const size_t s_cnt = min((size_t)WTHREADS * WSPT, S - s_first);
 
+    // sample r = k1 * 8192 + k2 is kept as (k1 << 16) | swz(k2); -1 = no sample
     for (int q = 0; q < WSPT; q++) {
         size_t i = (size_t)q * WTHREADS + tid;
-        smp[i] = i < s_cnt ? samples[s_first + i] : -1;
+        int packed = -1;
+        if (i < s_cnt) {
+            int r = samples[s_first + i];
+            packed = ((r >> WSEG_LOG) << 16) | swz(r & (WSEG - 1));
+        }
+        smp[i] = packed;
     }
     __syncthreads();
 
@@ -135,13 +152,13 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
 #pragma unroll
             for (int c = 0; c < WSEG / 2 / WTHREADS; c++) {
                 int e = (c * WTHREADS + tid) * 2;
-                cp_async16(dst + e, g + e);
+                cp_async16(dst + swz(e), g + e);
             }
         } else {
 #pragma unroll
             for (int c = 0; c < WSEG / WTHREADS; c++) {
                 int e = c * WTHREADS + tid;
-                cp_async8(dst + e, g + e);
+                cp_async8(dst + swz(e), g + e);
             }
         }
         asm volatile("cp.async.commit_group;");
@@ -162,61 +179,62 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
                 asm volatile("cp.async.wait_group 0;");
             }
             __syncthreads();
-            // ---- phase 1: element e = c*1024 + tid*2 + b, c < 8, b < 2 (16 per thread)
-            double v[16];
+            double v[32];
+            // ---- phase A: e = c*512 + tid*2 + b; registers hold index bits {0, 9..12}
 #pragma unroll
-            for (int c = 0; c < 8; c++) {
-                double2 x = *reinterpret_cast<const double2 *>(buf + c * 1024 + tid * 2);
-                // sign bits: global index n1*8192 + c*1024 + tid*2 + b
-                uint32_t w = Dbits[(n1 << (WSEG_LOG - 5)) + c * 32 + (tid >> 4)];
-                int bit = (tid & 15) * 2;
+            for (int c = 0; c < 16; c++) {
+                const int e = c * 512 + tid * 2;
+                double2 x = *reinterpret_cast<const double2 *>(buf + swz(e));
+                uint32_t w = Dbits[(n1 << (WSEG_LOG - 5)) + c * 16 + (tid >> 4)];
+                const int bit = (tid & 15) * 2;
                 v[2 * c] = __dmul_rn((w >> bit) & 1 ? -inscale : inscale, x.x);
                 v[2 * c + 1] = __dmul_rn((w >> (bit + 1)) & 1 ? -inscale : inscale, x.y);
             }
-            // register levels: index bit 0 (b) and bits 10..12 (c)
+            wht_regs<5, 1>(v);
 #pragma unroll
-            for (int h = 1; h < 16; h <<= 1)
-#pragma unroll
-                for (int i = 0; i < 16; i++)
-                    if (!(i & h)) { double a = v[i], b = v[i + h]; v[i] = a + b; v[i + h] = a - b; }
-            // lane levels: index bits 1..5
-#pragma unroll
-            for (int mk = 1; mk < 32; mk <<= 1) {
-                const bool up = lane & mk;
-#pragma unroll
-                for (int i = 0; i < 16; i++) {
-                    double o = shfl_xor_f64(v[i], mk);
-                    v[i] = up ? o - v[i] : v[i] + o;
-                }
-            }
-            __syncthreads();          // everyone has read its inputs: reuse buf for the exchange
-#pragma unroll
-            for (int c = 0; c < 8; c++) {
+            for (int c = 0; c < 16; c++) {
                 double2 x; x.x = v[2 * c]; x.y = v[2 * c + 1];
-                *reinterpret_cast<double2 *>(buf + c * 1024 + tid * 2) = x;
+                *reinterpret_cast<double2 *>(buf + swz(c * 512 + tid * 2)) = x;
             }
             __syncthreads();
-            // ---- phase 2: warp bits 6..9 of the index; thread t = (c, l, b) holds w = 0..15
+            // ---- phase B: registers hold index bits 1..5; thread = (b, bits 6..9, bits 10..12)
             {
-                const int base = (tid >> 6) * 1024 + (tid & 63);
+                const int u = (tid >> 1) & 15;
+                const int base = (tid & 1) + (u << 6) + ((tid >> 5) << 10);
 #pragma unroll
-                for (int w = 0; w < 16; w++) v[w] = buf[base + w * 64];
+                for (int r = 0; r < 32; r++) v[r] = buf[base + ((((r & 15) ^ u) << 1) | ((r >> 4) << 5))];
+                wht_regs<5, 1>(v);
 #pragma unroll
-                for (int h = 1; h < 16; h <<= 1)
+                for (int r = 0; r < 32; r++) buf[base + ((((r & 15) ^ u) << 1) | ((r >> 4) << 5))] = v[r];
+            }
+            __syncthreads();
+            // ---- phase C: registers hold index bits 6..8 (x4 groups over bits 9,10);
+            //      thread = (bits 0..5, bits 11..12)
+            {
+                const int low = tid & 63, base = low + ((tid >> 6) << 11);
+                // swizzle: bits 1..4 ^= (bits 6..9) = r3 | (it & 1) << 3
 #pragma unroll
-                    for (int i = 0; i < 16; i++)
-                        if (!(i & h)) { double a = v[i], b = v[i + h]; v[i] = a + b; v[i + h] = a - b; }
+                for (int r = 0; r < 32; r++) {
+                    const int r3 = r & 7, it = r >> 3;
+                    const int x = r3 | ((it & 1) << 3);
+                    v[r] = buf[(base ^ (x << 1)) + (r3 << 6) + (it << 9)];
+                }
+                wht_regs<3, 1>(v);          // register bits 0..2 = index bits 6..8
 #pragma unroll
-                for (int w = 0; w < 16; w++) buf[base + w * 64] = v[w];
+                for (int r = 0; r < 32; r++) {
+                    const int r3 = r & 7, it = r >> 3;
+                    const int x = r3 | ((it & 1) << 3);
+                    buf[(base ^ (x << 1)) + (r3 << 6) + (it << 9)] = v[r];
+                }
             }
             __syncthreads();
             // ---- sampled accumulate
 #pragma unroll
             for (int q = 0; q < WSPT; q++) {
-                int r = smp[q * WTHREADS + tid];
-                if (r >= 0) {
-                    double x = buf[r & (WSEG - 1)];
-                    bool neg = __popcll((unsigned long long)(r >> WSEG_LOG) & n1) & 1;
+                const int p = smp[q * WTHREADS + tid];
+                if (p >= 0) {
+                    const double x = buf[p & 0xffff];
+                    const bool neg = __popc((unsigned)(p >> 16) & (unsigned)n1) & 1;
                     acc[q] += neg ? -x : x;
                 }
             }
@@ -458,7 +476,7 @@ static size_t dct_table_bytes(size_t N, size_t S) {
     return (N + 4096 + 2 * S + 1024) * sizeof(cplx);     // generous upper bound
 }
 
-static bool wht_fast_ok(size_t N) { return N >= (size_t)WSEG && (N & (N - 1)) == 0; }
+static bool wht_fast_ok(size_t N) { return N >= (size_t)WSEG && (N & (N - 1)) == 0 && N <= ((size_t)1 << 28); }
 
 size_t fjlt_workspace_bytes(size_t N, size_t m, int fut, bool layout_rows, size_t S) {
     if (fut == FUT_DCT && dct_fast_ok(N))

@@ -325,6 +325,7 @@ k_hash_cols_smem(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
     }
 }
 
+
 // Fallback when S is too large for shared memory: L2 atomics.
 __global__ void k_hash_cols_global(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
                                    const int32_t *__restrict__ bucket,

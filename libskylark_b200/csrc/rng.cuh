@@ -66,6 +66,17 @@ __host__ __device__ __forceinline__ uint64_t seed_to_key(int seed) {
     return (uint64_t)(int64_t)seed;   // static_cast<uint64_t>(int), randgen.hpp:37
 }
 
+// u01 of a draw without the conversion pipe and without the final multiply: the two halves
+// are planted in doubles whose exponents already carry the 2^-64 factor,
+//   dhi = 2^20 + hi*2^-32,  dlo = 2^-12 + lo*2^-64,  result = (dhi - (2^20 + 2^-12)) + dlo,
+// every step exact except the last add, which rounds hi*2^-32 + lo*2^-64 = x*2^-64 once
+// (to nearest even) -- bit-identical to double(x) * 2^-64.
+__device__ __forceinline__ double u64_to_u01_rn(uint64_t x) {
+    double dhi = __hiloint2double(0x41300000, (int)(uint32_t)(x >> 32));   // 2^20 + hi*2^-32
+    double dlo = __hiloint2double(0x3F300000, (int)(uint32_t)x);           // 2^-12 + lo*2^-64
+    return __dadd_rn(__dsub_rn(dhi, 1048576.000244140625), dlo);           // 2^20 + 2^-12
+}
+
 // double(x) for a 64-bit unsigned x, round to nearest even, without the
 // conversion pipe: hi*2^32 and lo are exact, their sum rounds once.
 __device__ __forceinline__ double u64_to_double_rn(uint64_t x) {
@@ -207,8 +218,8 @@ __device__ __forceinline__ double normal_at(uint64_t key, uint64_t idx) {
         MicroUrng u(key, idx);
         return boost_normal(u);
     }
-    double r1 = u64_to_double_rn(b.y) * 0x1p-64;
-    double r2 = u64_to_double_rn(b.x) * 0x1p-64;
+    double r1 = u64_to_u01_rn(b.y);
+    double r2 = u64_to_u01_rn(b.x);
     double rho = sqrt(__dmul_rn(-2.0, log(__dsub_rn(1.0, r2))));
     return __dmul_rn(rho, cos_0_2pi(__dmul_rn(2.0 * SKB_BOOST_PI, r1)));
 }

@@ -204,15 +204,32 @@ class NumpyAdapter:
     def getobj(self):
         return self._A
 
+    def orders(self):
+        """Element orders this array satisfies; degenerate shapes (one row / one column /
+        empty) are both C- and F-contiguous, which lib.py:137-141 resolves to 'F' blindly."""
+        o = set()
+        if self._A.flags.f_contiguous:
+            o.add("F")
+        if self._A.flags.c_contiguous:
+            o.add("C")
+        return o
+
     def getorder(self):
+        if getattr(self, "_order", None):
+            return self._order
         return "F" if self._A.flags.f_contiguous else "C"
 
     def iscompatible(self, B):
-        if isinstance(B, (NumpyAdapter, ScipyAdapter)) and self.getorder() != B.getorder():
-            return "sketching numpy array to numpy/scipy array requires same element ordering", None
         if not isinstance(B, (NumpyAdapter, ScipyAdapter)):
             return "numpy input needs numpy output", None
-        return None, self.getorder() == "C"
+        common = self.orders() & B.orders()
+        if not common:
+            return "sketching numpy array to numpy/scipy array requires same element ordering", None
+        # agree on one order for both operands (matters only for degenerate shapes)
+        order = "F" if "F" in common else "C"
+        self._order = order
+        B._order = order
+        return None, order == "C"
 
     def getctor(self):
         return NumpyAdapter.ctor
@@ -267,14 +284,18 @@ class ScipyAdapter:
     def getobj(self):
         return self._A
 
+    def orders(self):
+        return {self.getorder()}
+
     def getorder(self):
         return "C" if isinstance(self._A, scipy.sparse.csr_matrix) else "F"
 
     def iscompatible(self, B):
-        if isinstance(B, (NumpyAdapter, ScipyAdapter)) and self.getorder() != B.getorder():
-            return "sketching scipy matrix to numpy/scipy matrix requires same format", None
         if not isinstance(B, (NumpyAdapter, ScipyAdapter)):
             return "scipy input needs numpy output", None
+        if self.getorder() not in B.orders():
+            return "sketching scipy matrix to numpy/scipy matrix requires same format", None
+        B._order = self.getorder()
         return None, self.getorder() == "C"
 
     def getctor(self):

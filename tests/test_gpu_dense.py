@@ -128,3 +128,16 @@ def test_large_host_arrays_take_the_pipelined_path(sk, oracle):
     half = n // 2
     part = S.apply_shard(A[:half].copy(), None, 0, 0) + S.apply_shard(A[half:].copy(), None, 0, half)
     assert rel_fro(part, want) < TOL64
+
+
+def test_edge_shapes(sk, oracle):
+    c, oc = _ctx(sk, oracle, 3)
+    J, OJ = sk.JLT(37, 1, c), oracle.JLT(37, 1, oc)              # one sketch row
+    A = np.random.default_rng(0).standard_normal((37, 9))
+    assert rel_fro(J.apply(A.copy(), None, 0), OJ.apply(A, "columnwise")) < TOL64
+    assert J.apply(np.zeros((37, 0)), None, 0).shape == (1, 0)   # no columns
+    J1, OJ1 = sk.JLT(1, 5, c), oracle.JLT(1, 5, oc)              # one input row
+    a = np.array([[1.5, -2.0]])
+    assert rel_fro(J1.apply(a.copy(), None, 0), OJ1.apply(a, "columnwise")) < TOL64
+    v = np.random.default_rng(1).standard_normal((37, 1))        # a single vector
+    assert rel_fro(J.apply(v.copy(), None, 0), OJ.apply(v, "columnwise")) < TOL64

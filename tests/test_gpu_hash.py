@@ -158,3 +158,31 @@ def test_raw_c_abi_call(sk, oracle):
         L.sl_free_raw_matrix_wrap(w)
     L.sl_free_sketch_transform(S)
     L.sl_free_context(ctx)
+
+
+def test_edge_shapes(sk, oracle):
+    """Empty and degenerate operands: no columns, one row, one bucket, more buckets than rows."""
+    import torch
+    S, O = _pair(sk, oracle, "CWT", 50, 7)
+    out = S.apply(np.zeros((50, 0)), None, "columnwise")
+    assert out.shape == (7, 0)
+    out = S.apply(np.zeros((0, 50)), None, "rowwise")
+    assert out.shape == (0, 7)
+    S1, O1 = _pair(sk, oracle, "MMT", 1, 5)
+    a = np.array([[2.5, -1.0, 0.0]])
+    assert rel_fro(S1.apply(a.copy(), None, 0), O1.apply(a, "columnwise")) < TOL
+    S2, O2 = _pair(sk, oracle, "CWT", 500, 1)          # everything lands in one bucket
+    A = np.random.default_rng(0).standard_normal((500, 33))
+    assert rel_fro(S2.apply(A.copy(), None, 0), O2.apply(A, "columnwise")) < TOL
+    assert rel_fro(S2.apply(np.asfortranarray(A), None, 0), O2.apply(A, "columnwise")) < TOL
+    S3, O3 = _pair(sk, oracle, "WZT", 40, 3000)        # mostly empty buckets
+    B = np.random.default_rng(1).standard_normal((40, 5))
+    got = S3.apply(B.copy(), None, 0)
+    assert rel_fro(got, O3.apply(B, "columnwise")) < TOL
+    assert np.count_nonzero(got.any(axis=1)) <= 40
+    # a single column vector, both as (n,1) numpy and as a torch tensor
+    S4, O4 = _pair(sk, oracle, "CWT", 3000, 64)
+    v = np.random.default_rng(2).standard_normal((3000, 1))
+    assert rel_fro(S4.apply(v.copy(), None, 0), O4.apply(v, "columnwise")) < TOL
+    tv = torch.tensor(v, device="cuda")
+    assert rel_fro(S4.apply(tv, None, 0).cpu().numpy(), O4.apply(v, "columnwise")) < TOL
