@@ -136,6 +136,7 @@ struct DevState {
     std::map<std::pair<size_t, size_t>, HashPlan> plans;
     double *shifts = nullptr, *scales = nullptr;
     double *D = nullptr; int32_t *samples = nullptr; uint32_t *Dbits = nullptr;
+    int32_t *wht_slot_sample = nullptr, *wht_slot_out = nullptr;
     void *ws = nullptr; size_t ws_bytes = 0;
 };
 
@@ -155,7 +156,8 @@ struct sl_sketch_transform_t {
             int prev = -1; cudaGetDevice(&prev); cudaSetDevice(kv.first);
             DevState &d = kv.second;
             cudaFree(d.bucket); cudaFree(d.value); cudaFree(d.shifts); cudaFree(d.scales);
-            cudaFree(d.D); cudaFree(d.samples); cudaFree(d.Dbits); cudaFree(d.ws);
+            cudaFree(d.D); cudaFree(d.samples); cudaFree(d.Dbits); cudaFree(d.wht_slot_sample);
+            cudaFree(d.wht_slot_out); cudaFree(d.ws);
             for (auto &p : d.plans) hash_free_plan(&p.second);
             if (prev >= 0) cudaSetDevice(prev);
         }
@@ -244,6 +246,19 @@ static void ensure_fjlt_tables(sl_sketch_transform_t *t, DevState &d) {
     SKB_CUDA(cudaMalloc(&d.Dbits, ((size_t)t->N / 32 + 1) * sizeof(uint32_t)));
     fjlt_build_tables(t->seed, t->base0, (size_t)t->N, (size_t)t->S, t->order, d.D, d.samples,
                       d.Dbits, g_stream);
+    if (t->fut == FUT_WHT) {     // gather layout of the WHT kernel, computed once from the samples
+        std::vector<int32_t> hs((size_t)t->S), slot_sample, slot_out;
+        SKB_CUDA(cudaMemcpyAsync(hs.data(), d.samples, hs.size() * sizeof(int32_t),
+                                 cudaMemcpyDeviceToHost, g_stream));
+        SKB_CUDA(cudaStreamSynchronize(g_stream));
+        fjlt_build_wht_slots(hs.data(), hs.size(), slot_sample, slot_out);
+        SKB_CUDA(cudaMalloc(&d.wht_slot_sample, slot_sample.size() * sizeof(int32_t) + 16));
+        SKB_CUDA(cudaMalloc(&d.wht_slot_out, slot_out.size() * sizeof(int32_t) + 16));
+        SKB_CUDA(cudaMemcpy(d.wht_slot_sample, slot_sample.data(), slot_sample.size() * sizeof(int32_t),
+                            cudaMemcpyHostToDevice));
+        SKB_CUDA(cudaMemcpy(d.wht_slot_out, slot_out.data(), slot_out.size() * sizeof(int32_t),
+                            cudaMemcpyHostToDevice));
+    }
 }
 
 static DenseParams dense_params(const sl_sketch_transform_t *t) {
@@ -333,7 +348,8 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
     size_t need = fjlt_workspace_bytes((size_t)t->N, (size_t)other, t->fut, layout_rows, (size_t)t->S);
     ensure_ws(d, need);
     fjlt_apply(t->fut, layout_rows, (const double *)A->data, (size_t)A->ld, (size_t)t->N,
-               (size_t)other, d.D, d.Dbits, d.samples, (size_t)t->S, (double *)SA->data, (size_t)SA->ld,
+               (size_t)other, d.D, d.Dbits, d.samples, (size_t)t->S, d.wht_slot_sample, d.wht_slot_out,
+               (double *)SA->data, (size_t)SA->ld,
                d.ws, d.ws_bytes, st);
 }
 

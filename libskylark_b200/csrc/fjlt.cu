@@ -10,6 +10,9 @@
 //
 // The counter overlap of the reference is kept: D uses stream [c, c+N), the sample
 // indices use [c, c+S) of the same stream.
+#include <algorithm>
+#include <vector>
+
 #include "rng.cuh"
 #include "skb_internal.h"
 
@@ -94,7 +97,8 @@ k_fjlt_direct(const double *__restrict__ X, size_t sk, size_t sj, size_t N, size
 // accumulates (-1)^popc(k1 & n1) * seg[k2] over the segments n1, in registers.  HBM
 // traffic is exactly the algorithmic n*d*8 + s*d*8 bytes; no scratch, no atomics.
 // ---------------------------------------------------------------------------
-static constexpr int WSEG_LOG = 13, WSEG = 1 << WSEG_LOG, WTHREADS = 256, WSPT = 32;
+static constexpr int WSEG_LOG = 13, WSEG = 1 << WSEG_LOG, WTHREADS = 512, WSPT = 16;
+static constexpr int WFOLD = 9;      // index bit whose butterfly level is folded into the gather
 
 __device__ __forceinline__ void cp_async16(void *smem, const void *g) {
     unsigned s = (unsigned)__cvta_generic_to_shared(smem);
@@ -105,26 +109,28 @@ __device__ __forceinline__ void cp_async8(void *smem, const void *g) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(g));
 }
 
-// Segment element e lives at shared word swz(e): index bits 6..9 are XORed into bits 1..4, so
-// that the three register phases below (which hold bits {0,9..12}, {1..5}, {6..8} of the index
-// per thread) all read and write shared memory without bank conflicts; bit 0 is untouched, so
-// 16-byte pairs stay pairs.
-__device__ __forceinline__ int swz(int e) { return e ^ (((e >> 6) & 15) << 1); }
+// Segment element e lives at shared word swz(e): index bits 5..8 are XORed into bits 1..4, which
+// makes all three register phases below conflict-free (they keep index bits {0,10,11,12},
+// {1..4} and {5..8} per thread); bit 0 is untouched, so 16-byte pairs stay pairs.
+__device__ __forceinline__ int swz(int e) { return e ^ (((e >> 5) & 15) << 1); }
 
-template <int LEVELS, int STRIDE>
-__device__ __forceinline__ void wht_regs(double *v) {      // butterflies over register index bits
+__device__ __forceinline__ void wht16(double *v) {      // 4 butterfly levels over 16 registers
 #pragma unroll
-    for (int h = STRIDE; h < (STRIDE << LEVELS); h <<= 1)
+    for (int h = 1; h < 16; h <<= 1)
 #pragma unroll
-        for (int i = 0; i < 32; i++)
-            if (!(i & h) && i + h < 32) { double a = v[i], b = v[i + h]; v[i] = a + b; v[i + h] = a - b; }
+        for (int i = 0; i < 16; i++)
+            if (!(i & h)) { double a = v[i], b = v[i + h]; v[i] = a + b; v[i + h] = a - b; }
+}
+
+__device__ __forceinline__ double flip_sign(double x, unsigned neg) {   // neg in {0, 1}
+    return __hiloint2double(__double2hiint(x) ^ (int)(neg << 31), __double2loint(x));
 }
 
 template <bool AL16>
 __global__ void __launch_bounds__(WTHREADS, 1)
 k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
-                const uint32_t *__restrict__ Dbits, const int32_t *__restrict__ samples,
-                size_t S, size_t s_first, double inscale, double outscale,
+                const uint32_t *__restrict__ Dbits, const int32_t *__restrict__ slot_sample,
+                const int32_t *__restrict__ slot_out, double inscale, double outscale,
                 double *__restrict__ OUT, size_t oi, size_t oj) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double *buf0 = reinterpret_cast<double *>(smem_raw);
@@ -132,18 +138,11 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
     int32_t *smp = reinterpret_cast<int32_t *>(buf1 + WSEG);      // [WTHREADS * WSPT]
     const int tid = threadIdx.x;
     const size_t nseg = N >> WSEG_LOG;
-    const size_t s_cnt = min((size_t)WTHREADS * WSPT, S - s_first);
 
-    // sample r = k1 * 8192 + k2 is kept as (k1 << 16) | swz(k2); -1 = no sample
-    for (int q = 0; q < WSPT; q++) {
-        size_t i = (size_t)q * WTHREADS + tid;
-        int packed = -1;
-        if (i < s_cnt) {
-            int r = samples[s_first + i];
-            packed = ((r >> WSEG_LOG) << 16) | swz(r & (WSEG - 1));
-        }
-        smp[i] = packed;
-    }
+    // slot tables (fjlt_build_wht_slots): sample r = k1 * 8192 + k2 packed as (k1 << 16) | k2,
+    // bit 31 set = empty slot; slots are ordered so that the 16 lanes of a half warp read 16
+    // different bank pairs in the gather below.
+    for (int q = 0; q < WSPT; q++) smp[q * WTHREADS + tid] = slot_sample[q * WTHREADS + tid];
     __syncthreads();
 
     auto prefetch = [&](const double *col, size_t seg, double *dst) {
@@ -164,6 +163,9 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
         asm volatile("cp.async.commit_group;");
     };
 
+    // The two scale factors commute with the transform; they are applied once to the sampled sums.
+    const double scale = inscale * outscale;
+
     for (size_t j = blockIdx.x; j < m; j += gridDim.x) {
         const double *col = X + j * ldx;
         double acc[WSPT];
@@ -179,72 +181,94 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
                 asm volatile("cp.async.wait_group 0;");
             }
             __syncthreads();
-            double v[32];
-            // ---- phase A: e = c*512 + tid*2 + b; registers hold index bits {0, 9..12}
+            double v[16];
+            // ---- phase A: e = c*1024 + tid*2 + b; registers hold index bits {0, 10, 11, 12}
 #pragma unroll
-            for (int c = 0; c < 16; c++) {
-                const int e = c * 512 + tid * 2;
-                double2 x = *reinterpret_cast<const double2 *>(buf + swz(e));
-                uint32_t w = Dbits[(n1 << (WSEG_LOG - 5)) + c * 16 + (tid >> 4)];
-                const int bit = (tid & 15) * 2;
-                v[2 * c] = __dmul_rn((w >> bit) & 1 ? -inscale : inscale, x.x);
-                v[2 * c + 1] = __dmul_rn((w >> (bit + 1)) & 1 ? -inscale : inscale, x.y);
+            for (int c = 0; c < 8; c++) {
+                double2 x = *reinterpret_cast<const double2 *>(buf + swz(c * 1024 + tid * 2));
+                const uint32_t w = Dbits[(n1 << (WSEG_LOG - 5)) + c * 32 + (tid >> 4)] >> ((tid & 15) * 2);
+                v[2 * c] = flip_sign(x.x, w & 1);
+                v[2 * c + 1] = flip_sign(x.y, (w >> 1) & 1);
             }
-            wht_regs<5, 1>(v);
+            wht16(v);
 #pragma unroll
-            for (int c = 0; c < 16; c++) {
+            for (int c = 0; c < 8; c++) {
                 double2 x; x.x = v[2 * c]; x.y = v[2 * c + 1];
-                *reinterpret_cast<double2 *>(buf + swz(c * 512 + tid * 2)) = x;
+                *reinterpret_cast<double2 *>(buf + swz(c * 1024 + tid * 2)) = x;
             }
             __syncthreads();
-            // ---- phase B: registers hold index bits 1..5; thread = (b, bits 6..9, bits 10..12)
+            // ---- phase B: registers hold index bits 1..4; thread = (bit 0, bits 5..12)
             {
-                const int u = (tid >> 1) & 15;
-                const int base = (tid & 1) + (u << 6) + ((tid >> 5) << 10);
+                const int u = (tid >> 1) & 15;                       // index bits 5..8
+                const int base = (tid & 1) + ((tid >> 1) << 5);
 #pragma unroll
-                for (int r = 0; r < 32; r++) v[r] = buf[base + ((((r & 15) ^ u) << 1) | ((r >> 4) << 5))];
-                wht_regs<5, 1>(v);
+                for (int r = 0; r < 16; r++) v[r] = buf[base + ((r ^ u) << 1)];
+                wht16(v);
 #pragma unroll
-                for (int r = 0; r < 32; r++) buf[base + ((((r & 15) ^ u) << 1) | ((r >> 4) << 5))] = v[r];
+                for (int r = 0; r < 16; r++) buf[base + ((r ^ u) << 1)] = v[r];
             }
             __syncthreads();
-            // ---- phase C: registers hold index bits 6..8 (x4 groups over bits 9,10);
-            //      thread = (bits 0..5, bits 11..12)
+            // ---- phase C: registers hold index bits 5..8; thread = (bits 0..4, bits 9..12)
             {
-                const int low = tid & 63, base = low + ((tid >> 6) << 11);
-                // swizzle: bits 1..4 ^= (bits 6..9) = r3 | (it & 1) << 3
+                const int base = (tid & 31) + ((tid >> 5) << 9);
 #pragma unroll
-                for (int r = 0; r < 32; r++) {
-                    const int r3 = r & 7, it = r >> 3;
-                    const int x = r3 | ((it & 1) << 3);
-                    v[r] = buf[(base ^ (x << 1)) + (r3 << 6) + (it << 9)];
-                }
-                wht_regs<3, 1>(v);          // register bits 0..2 = index bits 6..8
+                for (int r = 0; r < 16; r++) v[r] = buf[(base ^ (r << 1)) + (r << 5)];
+                wht16(v);
 #pragma unroll
-                for (int r = 0; r < 32; r++) {
-                    const int r3 = r & 7, it = r >> 3;
-                    const int x = r3 | ((it & 1) << 3);
-                    buf[(base ^ (x << 1)) + (r3 << 6) + (it << 9)] = v[r];
-                }
+                for (int r = 0; r < 16; r++) buf[(base ^ (r << 1)) + (r << 5)] = v[r];
             }
             __syncthreads();
-            // ---- sampled accumulate
+            // ---- sampled accumulate; the level of index bit 9 is done here, on two reads
 #pragma unroll
             for (int q = 0; q < WSPT; q++) {
                 const int p = smp[q * WTHREADS + tid];
-                if (p >= 0) {
-                    const double x = buf[p & 0xffff];
-                    const bool neg = __popc((unsigned)(p >> 16) & (unsigned)n1) & 1;
-                    acc[q] += neg ? -x : x;
-                }
+                const int k2 = p & (WSEG - 1);
+                const double lo = buf[swz(k2 & ~(1 << WFOLD))], hi = buf[swz(k2 | (1 << WFOLD))];
+                const unsigned par = __popc((unsigned)(p >> 16) & (unsigned)n1) & 1;
+                const double y = lo + flip_sign(hi, (k2 >> WFOLD) & 1);
+                if (p >= 0) acc[q] += flip_sign(y, par);
             }
             __syncthreads();          // buf may be overwritten by the prefetch two segments on
         }
 #pragma unroll
         for (int q = 0; q < WSPT; q++) {
-            size_t i = (size_t)q * WTHREADS + tid;
-            if (i < s_cnt) OUT[(s_first + i) * oi + j * oj] = outscale * acc[q];
+            const int i = slot_out[q * WTHREADS + tid];
+            if (i >= 0) OUT[(size_t)i * oi + j * oj] = scale * acc[q];
         }
+    }
+}
+
+// Host side of the gather layout: distributes the samples of one pass (<= 8192) over the
+// [WSPT][WTHREADS] slots so that each aligned group of 16 slots (= the lanes of a half warp in
+// one gather step) holds samples from 16 different shared-memory bank pairs wherever the
+// sample set allows it.  slot_sample / slot_out get npasses * WSPT * WTHREADS entries.
+void fjlt_build_wht_slots(const int32_t *samples, size_t S, std::vector<int32_t> &slot_sample,
+                          std::vector<int32_t> &slot_out) {
+    const size_t per_pass = (size_t)WTHREADS * WSPT;
+    const size_t npass = S == 0 ? 0 : (S + per_pass - 1) / per_pass;
+    slot_sample.assign(npass * per_pass, (int32_t)0x80000000);
+    slot_out.assign(npass * per_pass, -1);
+    auto host_swz = [](int e) { return e ^ (((e >> 5) & 15) << 1); };
+    for (size_t p = 0; p < npass; p++) {
+        const size_t s0 = p * per_pass, s1 = std::min(S, s0 + per_pass);
+        std::vector<std::vector<int32_t>> q(16);
+        for (size_t i = s0; i < s1; i++) q[host_swz(samples[i] & (WSEG - 1)) & 15].push_back((int32_t)i);
+        std::vector<int32_t> leftovers;
+        int32_t *ss = slot_sample.data() + p * per_pass, *so = slot_out.data() + p * per_pass;
+        const size_t ngroups = per_pass / 16;
+        std::vector<size_t> holes;
+        for (size_t g = 0; g < ngroups; g++)
+            for (int b = 0; b < 16; b++) {
+                if (!q[b].empty()) { so[g * 16 + b] = q[b].back(); q[b].pop_back(); }
+                else holes.push_back(g * 16 + b);
+            }
+        for (int b = 0; b < 16; b++) for (int32_t i : q[b]) leftovers.push_back(i);
+        for (size_t h = 0; h < holes.size() && h < leftovers.size(); h++) so[holes[h]] = leftovers[h];
+        for (size_t t = 0; t < per_pass; t++)
+            if (so[t] >= 0) {
+                const int32_t r = samples[so[t]];
+                ss[t] = ((r >> WSEG_LOG) << 16) | (r & (WSEG - 1));
+            }
     }
 }
 
@@ -489,6 +513,7 @@ size_t fjlt_workspace_bytes(size_t N, size_t m, int fut, bool layout_rows, size_
 
 void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N, size_t m,
                 const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
+                const int32_t *wht_slot_sample, const int32_t *wht_slot_out,
                 double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
                 cudaStream_t st) {
     if (S == 0 || m == 0) return;
@@ -584,10 +609,12 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         auto kern = al16 ? k_fjlt_wht_cols<true> : k_fjlt_wht_cols<false>;
         SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         unsigned grid = (unsigned)(m < 148 ? m : 148);
-        for (size_t s0 = 0; s0 < S; s0 += (size_t)WTHREADS * WSPT) {    // 8192 samples per pass
+        const size_t per_pass = (size_t)WTHREADS * WSPT;                 // 8192 samples per pass
+        for (size_t s0 = 0, p = 0; s0 < S; s0 += per_pass, p++) {
             LaunchScope ls(KC_FJLT, st);
-            kern<<<grid, WTHREADS, smem, st>>>(Xc, ldc, N, m, Dbits, samples, S, s0, inscale,
-                                               outscale, OUT, oi, oj);
+            kern<<<grid, WTHREADS, smem, st>>>(Xc, ldc, N, m, Dbits, wht_slot_sample + p * per_pass,
+                                               wht_slot_out + p * per_pass, inscale, outscale, OUT,
+                                               oi, oj);
             SKB_CUDA(cudaGetLastError());
         }
         return;

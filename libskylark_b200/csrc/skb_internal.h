@@ -6,6 +6,7 @@
 #include <cstdint>
 #include <stdexcept>
 #include <string>
+#include <vector>
 #include <cuda_runtime.h>
 
 namespace skb {
@@ -126,7 +127,11 @@ size_t fjlt_workspace_bytes(size_t N, size_t m, int fut, bool layout_rows, size_
 // layout_rows as above.  OUT[i, j] = sqrt(N/S) * FUT(scale * D .* X[:, j])[samples[i]]
 void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N, size_t m,
                 const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
+                const int32_t *wht_slot_sample, const int32_t *wht_slot_out,
                 double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
                 cudaStream_t st);
+// Host-side layout of the sampled gather of the WHT kernel (see fjlt.cu).
+void fjlt_build_wht_slots(const int32_t *samples, size_t S, std::vector<int32_t> &slot_sample,
+                          std::vector<int32_t> &slot_out);
 
 }  // namespace skb
