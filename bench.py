@@ -262,6 +262,98 @@ def other_configs(torch, lib, sketch, hbm_gbs, fp64_peak):
     return out
 
 
+def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
+    """BASELINE.json configs 3-5 on `world` GPUs (all ranks run this in lockstep; device time via
+    CUDA events, max over ranks).  C3: strong scaling of the fixed 2^20 x 2048 problem, row
+    shards + all-reduce of the 134 MB sketch.  C4: 1.25e6 rows per rank of a (1.25e6*world) x 1e5
+    CSC matrix + reduce-scatter of the 16 GB dense partial.  C5: 5e5 points per rank, no
+    collective."""
+    from libskylark_b200.dist import reduce_partial
+    dev = "cuda"
+    out = {}
+
+    def timed(fn, reps):
+        fn()
+        torch.cuda.synchronize(); dist.barrier()
+        ts = []
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ts.append(float(t.item()))
+            dist.barrier()
+        return statistics.median(ts)
+
+    # ---- C3 (Walsh-Hadamard mode; the DCT does not split over row shards)
+    n, d, s = 2 ** 20, 2048, 8192
+    if n % (8192 * world) == 0:
+        lib.set_option("fjlt_fut", "wht")
+        try:
+            S = sketch.FJLT(n, s, lib.Context(SKETCH_SEED))
+        finally:
+            lib.set_option("fjlt_fut", "dct")
+        nloc = n // world
+        A = torch.randn(d, nloc, dtype=torch.float64, device=dev).t()       # column-major shard
+        SA = torch.empty(d, s, dtype=torch.float64, device=dev).t()
+
+        def c3():
+            S.apply_shard(A, SA, "columnwise", rank * nloc)
+            reduce_partial(SA, None, "allreduce")
+        ms = timed(c3, 3)
+        gbs = (n * d * 8 + s * d * 8) / (ms * 1e-3) / 1e9
+        out["c3_fjlt_wht"] = {"workload": "C3: FJLT(wht) fp64 2^20x2048 -> 8192 row-sharded over %d GPUs, "
+                              "all-reduce of the 134 MB sketch (strong scaling)" % world,
+                              "ms": ms, "value": gbs, "unit": "GB/s", "scaling": "strong"}
+        del A, SA, S
+        torch.cuda.empty_cache()
+
+    # ---- C4
+    n_loc, d, s, nnz_col = 1_250_000, 100_000, 20_000, 1250
+    if d % world == 0:
+        g = torch.Generator(device=dev).manual_seed(DATA_SEED + rank)
+        indptr = (torch.arange(d + 1, device=dev, dtype=torch.int64) * nnz_col).to(torch.int32)
+        indices = torch.randint(0, n_loc, (d * nnz_col,), device=dev, dtype=torch.int32, generator=g)
+        values = torch.randn(d * nnz_col, dtype=torch.float64, device=dev, generator=g)
+        A = lib.DeviceCSC(indptr, indices, values, (n_loc, d))
+        S = sketch.CWT(n_loc * world, s, lib.Context(SKETCH_SEED))
+        SA = torch.empty(d, s, dtype=torch.float64, device=dev).t()          # column-major s x d
+        kernel_ms = []
+
+        def c4():
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            S.apply_shard(A, SA, "columnwise", rank * n_loc)
+            e1.record()
+            res = reduce_partial(SA, None, "reduce_scatter")     # each rank keeps d/world columns
+            torch.cuda.synchronize()
+            kernel_ms.append(e0.elapsed_time(e1))
+            return res
+        ms = timed(c4, 2)
+        nbytes = world * (d * nnz_col * 12 + (d + 1) * 4 + s * d * 8)
+        out["c4_cwt_csc"] = {"workload": "C4: CWT CSC %dx100000, %.2e nnz -> 20000 row-sharded over %d GPUs, "
+                             "reduce-scatter of the 16 GB partials" % (n_loc * world, 1.25e8 * world, world),
+                             "ms": ms, "kernel_ms_rank0": statistics.median(kernel_ms),
+                             "value": nbytes / (ms * 1e-3) / 1e9, "unit": "GB/s (all GPUs, kernel bytes / "
+                             "end-to-end time incl. collective)", "scaling": "weak"}
+        del A, SA, S, indptr, indices, values
+        torch.cuda.empty_cache()
+
+    # ---- C5
+    m, n, s = 500_000, 784, 16384
+    S = sketch.GaussianRFT(n, s, 10.0, context=lib.Context(SKETCH_SEED))
+    A = torch.rand(m, n, dtype=torch.float32, device=dev)
+    SA = torch.empty(m, s, dtype=torch.float32, device=dev)
+    ms = timed(lambda: S.apply(A, SA, "rowwise"), 2)
+    out["c5_rft"] = {"workload": "C5: GaussianRFT fp32 %dx784 -> 16384 rowwise, %d points per GPU, no collective"
+                     % (m * world, m), "ms": ms, "value": 2.0 * m * world * n * s / (ms * 1e-3) / 1e12,
+                     "unit": "TFLOP/s", "scaling": "weak"}
+    del A, SA, S
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -370,6 +462,14 @@ def run_ours(args):
     L.sl_host_free_pinned(hA)
     L.sl_host_free_pinned(hSA)
 
+    multi = None
+    if world > 1:
+        del A, SA
+        torch.cuda.empty_cache()
+        try:
+            multi = multi_gpu_configs(torch, dist, lib, sketch, rank, world, 6533.5)
+        except Exception as e:      # keep the main line
+            multi = {"error": str(e)[:300]}
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -425,6 +525,8 @@ def run_ours(args):
                                 "kind": "port", "sample": cpu["sample"], "seconds": cpu["seconds"]}
     if extra is not None:
         line["other_configs"] = extra
+    if multi is not None:
+        line["other_configs"] = multi
     print(json.dumps(line))
     if world > 1:
         dist.barrier()

@@ -108,7 +108,10 @@ int sl_set_stream(void *cuda_stream);
 /* Row-sharded apply: A holds sketched indices [index_offset, index_offset + local) of
  * the transform's N; SA receives this shard's partial sum (to be summed across shards,
  * cf. sketch/hash_transform_Elemental.hpp:543-561 and
- * sketch/dense_transform_Elemental_coldist_star.hpp:200-229).  Not valid for FJLT. */
+ * sketch/dense_transform_Elemental_coldist_star.hpp:200-229).  RFT cannot be sharded this
+ * way (the cosine is not additive); FJLT can in the Walsh-Hadamard mode only, with N a power
+ * of two >= 8192 and 8192-aligned shards (in DCT mode shard the other dimension, as the
+ * reference re-distributes to, sketch/FJLT_Elemental.hpp:149-150). */
 int sl_apply_sketch_transform_shard(sl_sketch_transform_t *S, char *input_type, void *A,
                                     char *output_type, void *SA, int dim,
                                     int64_t index_offset);

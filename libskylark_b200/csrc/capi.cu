@@ -341,16 +341,20 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
                     (size_t)sk, SA->data, (size_t)SA->ld, epi, d.ws, d.ws_bytes, st, accumulate);
         return;
     }
-    // FJLT
-    if (shard && sk != t->N)
-        throw error(SKB_ERR_INVALID_USAGE, "apply: FJLT needs the whole sketched dimension");
+    // FJLT.  Row shards are possible in the Walsh-Hadamard mode only (H_N = H_P (x) H_{N/P}:
+    // the partial sketches of whole 8192-row segments add up); the DCT does not split that way
+    // (the reference re-distributes instead, FJLT_Elemental.hpp:149-150) -- shard its columns.
+    if (sk != t->N && !fjlt_shard_ok(t->fut, (size_t)t->N, (size_t)offset, (size_t)sk))
+        throw error(SKB_ERR_INVALID_USAGE,
+                    "apply: FJLT over a shard of the sketched dimension needs fjlt_fut=wht, N a power of "
+                    "two >= 8192 and 8192-aligned shards; in DCT mode shard the other dimension");
     ensure_fjlt_tables(t, d);
     size_t need = fjlt_workspace_bytes((size_t)t->N, (size_t)other, t->fut, layout_rows, (size_t)t->S);
     ensure_ws(d, need);
     fjlt_apply(t->fut, layout_rows, (const double *)A->data, (size_t)A->ld, (size_t)t->N,
                (size_t)other, d.D, d.Dbits, d.samples, (size_t)t->S, d.wht_slot_sample, d.wht_slot_out,
                (double *)SA->data, (size_t)SA->ld,
-               d.ws, d.ws_bytes, st);
+               d.ws, d.ws_bytes, st, (size_t)offset, (size_t)sk);
 }
 
 // Host operands of a dense sketch: the sketched dimension is cut in chunks; chunk c+1 is

@@ -130,14 +130,14 @@ template <bool AL16>
 __global__ void __launch_bounds__(WTHREADS, 1)
 k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
                 const uint32_t *__restrict__ Dbits, const int32_t *__restrict__ slot_sample,
-                const int32_t *__restrict__ slot_out, double inscale, double outscale,
+                const int32_t *__restrict__ slot_out, size_t seg0, double inscale, double outscale,
                 double *__restrict__ OUT, size_t oi, size_t oj) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double *buf0 = reinterpret_cast<double *>(smem_raw);
     double *buf1 = buf0 + WSEG;
     int32_t *smp = reinterpret_cast<int32_t *>(buf1 + WSEG);      // [WTHREADS * WSPT]
     const int tid = threadIdx.x;
-    const size_t nseg = N >> WSEG_LOG;
+    const size_t nseg = N >> WSEG_LOG;      // segments present in X (a row shard starts at seg0)
 
     // slot tables (fjlt_build_wht_slots): sample r = k1 * 8192 + k2 packed as (k1 << 16) | k2,
     // bit 31 set = empty slot; slots are ordered so that the 16 lanes of a half warp read 16
@@ -186,7 +186,7 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
 #pragma unroll
             for (int c = 0; c < 8; c++) {
                 double2 x = *reinterpret_cast<const double2 *>(buf + swz(c * 1024 + tid * 2));
-                const uint32_t w = Dbits[(n1 << (WSEG_LOG - 5)) + c * 32 + (tid >> 4)] >> ((tid & 15) * 2);
+                const uint32_t w = Dbits[((seg0 + n1) << (WSEG_LOG - 5)) + c * 32 + (tid >> 4)] >> ((tid & 15) * 2);
                 v[2 * c] = flip_sign(x.x, w & 1);
                 v[2 * c + 1] = flip_sign(x.y, (w >> 1) & 1);
             }
@@ -224,7 +224,7 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
                 const int p = smp[q * WTHREADS + tid];
                 const int k2 = p & (WSEG - 1);
                 const double lo = buf[swz(k2 & ~(1 << WFOLD))], hi = buf[swz(k2 | (1 << WFOLD))];
-                const unsigned par = __popc((unsigned)(p >> 16) & (unsigned)n1) & 1;
+                const unsigned par = __popc((unsigned)(p >> 16) & (unsigned)(seg0 + n1)) & 1;
                 const double y = lo + flip_sign(hi, (k2 >> WFOLD) & 1);
                 if (p >= 0) acc[q] += flip_sign(y, par);
             }
@@ -511,12 +511,21 @@ size_t fjlt_workspace_bytes(size_t N, size_t m, int fut, bool layout_rows, size_
     return 256;
 }
 
+bool fjlt_shard_ok(int fut, size_t N, size_t offset, size_t nloc) {
+    return fut == FUT_WHT && N >= (size_t)WSEG && (N & (N - 1)) == 0 && N <= ((size_t)1 << 28) &&
+           offset % WSEG == 0 && nloc % WSEG == 0 && nloc > 0;
+}
+
 void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N, size_t m,
                 const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
                 const int32_t *wht_slot_sample, const int32_t *wht_slot_out,
                 double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
-                cudaStream_t st) {
+                cudaStream_t st, size_t offset, size_t nloc) {
     if (S == 0 || m == 0) return;
+    if (nloc != N && !fjlt_shard_ok(fut, N, offset, nloc))
+        throw error(SKB_ERR_INVALID_USAGE,
+                    "FJLT: a shard of the sketched dimension needs the Walsh-Hadamard mode, N a power "
+                    "of two >= 8192, and shard offset and length that are multiples of 8192");
     if (fut == FUT_WHT && (N & (N - 1)) != 0)
         throw error(SKB_ERR_INVALID_PARAM, "FJLT (WHT mode): N must be a power of two");
     if (workspace_bytes < fjlt_workspace_bytes(N, m, fut, layout_rows, S))
@@ -597,10 +606,10 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         if (layout_rows) {      // the reference also transposes for this direction
             double *T = reinterpret_cast<double *>(workspace);
             LaunchScope ls(KC_FJLT, st);
-            dim3 grid((unsigned)((m + 31) / 32), (unsigned)((N + 31) / 32));
-            k_transpose_to_cols<<<grid, dim3(32, 8), 0, st>>>(X, ldx, N, m, T);
+            dim3 grid((unsigned)((m + 31) / 32), (unsigned)((nloc + 31) / 32));
+            k_transpose_to_cols<<<grid, dim3(32, 8), 0, st>>>(X, ldx, nloc, m, T);
             SKB_CUDA(cudaGetLastError());
-            Xc = T; ldc = N;
+            Xc = T; ldc = nloc;
         }
         const size_t oi = layout_rows ? ldo : 1, oj = layout_rows ? 1 : ldo;
         const double inscale = 1.0 / sqrt((double)N), outscale = sqrt((double)N / (double)S);
@@ -612,9 +621,9 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         const size_t per_pass = (size_t)WTHREADS * WSPT;                 // 8192 samples per pass
         for (size_t s0 = 0, p = 0; s0 < S; s0 += per_pass, p++) {
             LaunchScope ls(KC_FJLT, st);
-            kern<<<grid, WTHREADS, smem, st>>>(Xc, ldc, N, m, Dbits, wht_slot_sample + p * per_pass,
-                                               wht_slot_out + p * per_pass, inscale, outscale, OUT,
-                                               oi, oj);
+            kern<<<grid, WTHREADS, smem, st>>>(Xc, ldc, nloc, m, Dbits, wht_slot_sample + p * per_pass,
+                                               wht_slot_out + p * per_pass, offset >> WSEG_LOG,
+                                               inscale, outscale, OUT, oi, oj);
             SKB_CUDA(cudaGetLastError());
         }
         return;

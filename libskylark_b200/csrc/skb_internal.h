@@ -129,7 +129,8 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
                 const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
                 const int32_t *wht_slot_sample, const int32_t *wht_slot_out,
                 double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
-                cudaStream_t st);
+                cudaStream_t st, size_t offset, size_t nloc);   // X holds rows [offset, offset+nloc)
+bool fjlt_shard_ok(int fut, size_t N, size_t offset, size_t nloc);
 // Host-side layout of the sampled gather of the WHT kernel (see fjlt.cu).
 void fjlt_build_wht_slots(const int32_t *samples, size_t S, std::vector<int32_t> &slot_sample,
                           std::vector<int32_t> &slot_out);

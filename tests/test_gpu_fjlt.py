@@ -46,3 +46,32 @@ def test_fjlt_wht_needs_power_of_two(sk):
         lib.set_option("fjlt_fut", "dct")
     with pytest.raises(errors.LowerLayerError):
         S.apply(np.zeros((300, 4), order="F"), None, 0)
+
+
+def test_wht_row_shards_add_up(sk, oracle):
+    """H_N = H_P (x) H_{N/P}: partial sketches of 8192-aligned row blocks sum to the full one
+    (BASELINE.json config 3: FJLT row-sharded over GPUs with a reduce)."""
+    import torch
+    from libskylark_b200 import errors, lib
+    n, s, d = 65536, 700, 24
+    lib.set_option("fjlt_fut", "wht")
+    try:
+        S = sk.FJLT(n, s, lib.Context(5))
+    finally:
+        lib.set_option("fjlt_fut", "dct")
+    O = oracle.FJLT(n, s, oracle.Context(5))
+    A = torch.randn(d, n, dtype=torch.float64, device="cuda").t()        # column-major n x d
+    want = O.apply(A.cpu().numpy(), "columnwise", fut="wht")
+    full = S.apply(A, None, "columnwise")
+    assert rel_fro(full.cpu().numpy(), want) < TOL
+    for cuts in ((0, 32768, 65536), (0, 8192, 24576, 57344, 65536)):
+        parts = sum(S.apply_shard(A[a:b], None, 0, a) for a, b in zip(cuts, cuts[1:]))
+        assert rel_fro(parts.cpu().numpy(), want) < TOL
+    Ar = A.contiguous()                                                   # row-major: transposed path
+    parts = sum(S.apply_shard(Ar[a:b], None, 0, a) for a, b in ((0, 16384), (16384, 65536)))
+    assert rel_fro(parts.cpu().numpy(), want) < TOL
+    with pytest.raises(errors.LowerLayerError):
+        S.apply_shard(A[:1000], None, 0, 0)                               # not 8192-aligned
+    Sd = sk.FJLT(n, s, lib.Context(5))                                    # DCT mode cannot
+    with pytest.raises(errors.LowerLayerError):
+        Sd.apply_shard(A[:32768], None, 0, 0)
