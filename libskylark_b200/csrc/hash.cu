@@ -17,6 +17,7 @@
 //     with separate multiply and add, i.e. the reference's own rounding sequence.
 //   * the strided layout and CSC input accumulate in shared memory per output
 //     column and dump coalesced columns.
+#include <cstdlib>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
@@ -370,6 +371,7 @@ void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int3
 // a shared S-vector (shared atomics), then written as one coalesced dense column
 // while the accumulator is re-zeroed.
 // ---------------------------------------------------------------------------
+template <bool VEC2>
 __global__ void __launch_bounds__(512)
 k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__restrict__ indices,
                         const double *__restrict__ values, size_t ncols,
@@ -378,15 +380,51 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
     extern __shared__ double acc[];   // [S]
     for (int i = threadIdx.x; i < S; i += blockDim.x) acc[i] = 0.0;
     __syncthreads();
-    for (size_t col = blockIdx.x; col < ncols; col += gridDim.x) {
+    // Software pipeline over the columns this CTA owns: the nonzeros of the NEXT column (index ->
+    // bucket/value gathers, two dependent trips to L2/HBM) are fetched into registers while the
+    // CURRENT column's dense S-vector is being written out, so the gather latency hides behind
+    // the 8*S-byte dump instead of adding to it.
+    constexpr int PRE = 4;            // nonzeros per thread held in registers (4 * 512 per column)
+    int h[PRE]; double v[PRE];
+    auto fetch = [&](size_t col) {
+#pragma unroll
+        for (int i = 0; i < PRE; i++) { h[i] = -1; v[i] = 0.0; }
+        if (col >= ncols) return;
         const int p0 = indptr[col], p1 = indptr[col + 1];
-        for (int p = p0 + threadIdx.x; p < p1; p += blockDim.x) {
-            int row = indices[p];
-            atomicAdd(&acc[bucket[row]], __dmul_rn(value[row], values[p]));
+#pragma unroll
+        for (int i = 0; i < PRE; i++) {
+            const int p = p0 + (int)threadIdx.x + i * (int)blockDim.x;
+            if (p < p1) {
+                const int row = indices[p];
+                h[i] = bucket[row];
+                v[i] = __dmul_rn(value[row], values[p]);
+            }
         }
+    };
+    fetch(blockIdx.x);
+    for (size_t col = blockIdx.x; col < ncols; col += gridDim.x) {
+#pragma unroll
+        for (int i = 0; i < PRE; i++)
+            if (h[i] >= 0) atomicAdd(&acc[h[i]], v[i]);
+        {   // columns with more than PRE * blockDim nonzeros
+            const int p0 = indptr[col], p1 = indptr[col + 1];
+            for (int p = p0 + PRE * (int)blockDim.x + (int)threadIdx.x; p < p1; p += blockDim.x) {
+                const int row = indices[p];
+                atomicAdd(&acc[bucket[row]], __dmul_rn(value[row], values[p]));
+            }
+        }
+        fetch(col + gridDim.x);       // in flight during the dump below
         __syncthreads();
         double *o = OUT + col * ldo;
-        for (int i = threadIdx.x; i < S; i += blockDim.x) { o[i] = acc[i]; acc[i] = 0.0; }
+        if (VEC2) {
+            double2 *o2 = reinterpret_cast<double2 *>(o);
+            double2 *a2 = reinterpret_cast<double2 *>(acc);
+            const double2 z = make_double2(0.0, 0.0);
+            for (int i = threadIdx.x; i < S / 2; i += blockDim.x) { o2[i] = a2[i]; a2[i] = z; }
+            if ((S & 1) && threadIdx.x == 0) { o[S - 1] = acc[S - 1]; acc[S - 1] = 0.0; }
+        } else {
+            for (int i = threadIdx.x; i < S; i += blockDim.x) { o[i] = acc[i]; acc[i] = 0.0; }
+        }
         __syncthreads();
     }
 }
@@ -415,15 +453,18 @@ void hash_apply_csc_columnwise(const int32_t *indptr, const int32_t *indices,
                                cudaStream_t st) {
     if (ncols == 0) return;
     size_t smem = (size_t)S * sizeof(double);
-    if (smem <= 220 * 1024) {
-        SKB_CUDA(cudaFuncSetAttribute(k_hash_csc_colwise_smem,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    static int force_global = -1;
+    if (force_global < 0) force_global = getenv("SKB_DEBUG_CSC_GLOBAL") ? 1 : 0;
+    if (smem <= 220 * 1024 && !force_global) {
+        const bool vec2 = (ldo % 2 == 0) && ((uintptr_t)OUT % 16 == 0);
+        auto kern = vec2 ? k_hash_csc_colwise_smem<true> : k_hash_csc_colwise_smem<false>;
+        SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int per_sm = smem <= 100 * 1024 ? 2 : 1;
         size_t grid = (size_t)148 * per_sm;
         if (grid > ncols) grid = ncols;
         LaunchScope ls(KC_HASH, st);
-        k_hash_csc_colwise_smem<<<(unsigned)grid, 512, smem, st>>>(indptr, indices, values, ncols,
-                                                                  bucket, value, OUT, ldo, S);
+        kern<<<(unsigned)grid, 512, smem, st>>>(indptr, indices, values, ncols, bucket, value, OUT,
+                                                ldo, S);
         SKB_CUDA(cudaGetLastError());
     } else {
         zero_matrix(OUT, ldo, (size_t)S, ncols, st);
