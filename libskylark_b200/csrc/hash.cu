@@ -380,32 +380,42 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
     extern __shared__ double acc[];   // [S]
     for (int i = threadIdx.x; i < S; i += blockDim.x) acc[i] = 0.0;
     __syncthreads();
-    // Software pipeline over the columns this CTA owns: the nonzeros of the NEXT column (index ->
-    // bucket/value gathers, two dependent trips to L2/HBM) are fetched into registers while the
-    // CURRENT column's dense S-vector is being written out, so the gather latency hides behind
-    // the 8*S-byte dump instead of adding to it.
+    // Three-deep software pipeline over the columns this CTA owns.  A nonzero needs three
+    // dependent trips to L2/HBM (indptr -> index/value -> bucket/value tables); each trip of a
+    // LATER column is issued before the current column's dense S-vector is written out and its
+    // result is only touched one iteration later, so the whole chain hides behind the dumps.
     constexpr int PRE = 4;            // nonzeros per thread held in registers (4 * 512 per column)
-    int h[PRE]; double v[PRE];
-    auto fetch = [&](size_t col) {
-#pragma unroll
-        for (int i = 0; i < PRE; i++) { h[i] = -1; v[i] = 0.0; }
-        if (col >= ncols) return;
-        const int p0 = indptr[col], p1 = indptr[col + 1];
+    const size_t stride = gridDim.x;
+    int hC[PRE]; double wC[PRE], xC[PRE];          // current column: bucket, table value, entry
+    int rN[PRE]; double xN[PRE];                   // next column: row index, entry
+    int q0 = 0, q1 = 0;                            // column after next: its indptr pair
+    auto load_ptr = [&](size_t col) {
+        q0 = q1 = 0;
+        if (col < ncols) { q0 = indptr[col]; q1 = indptr[col + 1]; }
+    };
+    auto load_entries = [&]() {                    // uses q0/q1
 #pragma unroll
         for (int i = 0; i < PRE; i++) {
-            const int p = p0 + (int)threadIdx.x + i * (int)blockDim.x;
-            if (p < p1) {
-                const int row = indices[p];
-                h[i] = bucket[row];
-                v[i] = __dmul_rn(value[row], values[p]);
-            }
+            const int p = q0 + (int)threadIdx.x + i * (int)blockDim.x;
+            rN[i] = -1; xN[i] = 0.0;
+            if (p < q1) { rN[i] = indices[p]; xN[i] = values[p]; }
         }
     };
-    fetch(blockIdx.x);
-    for (size_t col = blockIdx.x; col < ncols; col += gridDim.x) {
+    auto load_tables = [&]() {                     // uses rN/xN, fills hC/wC/xC
+#pragma unroll
+        for (int i = 0; i < PRE; i++) {
+            hC[i] = -1; wC[i] = 0.0; xC[i] = xN[i];
+            if (rN[i] >= 0) { hC[i] = bucket[rN[i]]; wC[i] = value[rN[i]]; }
+        }
+    };
+    // prologue: column c fully staged, column c+stride at the entry stage, c+2*stride at indptr
+    load_ptr(blockIdx.x); load_entries(); load_tables();
+    load_ptr(blockIdx.x + stride); load_entries();
+    load_ptr(blockIdx.x + 2 * stride);
+    for (size_t col = blockIdx.x; col < ncols; col += stride) {
 #pragma unroll
         for (int i = 0; i < PRE; i++)
-            if (h[i] >= 0) atomicAdd(&acc[h[i]], v[i]);
+            if (hC[i] >= 0) atomicAdd(&acc[hC[i]], __dmul_rn(wC[i], xC[i]));
         {   // columns with more than PRE * blockDim nonzeros
             const int p0 = indptr[col], p1 = indptr[col + 1];
             for (int p = p0 + PRE * (int)blockDim.x + (int)threadIdx.x; p < p1; p += blockDim.x) {
@@ -413,7 +423,9 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
                 atomicAdd(&acc[bucket[row]], __dmul_rn(value[row], values[p]));
             }
         }
-        fetch(col + gridDim.x);       // in flight during the dump below
+        load_tables();                 // column col + stride   (rows arrived an iteration ago)
+        load_entries();                // column col + 2*stride (indptr arrived an iteration ago)
+        load_ptr(col + 3 * stride);
         __syncthreads();
         double *o = OUT + col * ldo;
         if (VEC2) {
