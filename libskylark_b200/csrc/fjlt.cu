@@ -11,6 +11,7 @@
 // The counter overlap of the reference is kept: D uses stream [c, c+N), the sample
 // indices use [c, c+S) of the same stream.
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 #include "rng.cuh"
@@ -468,6 +469,186 @@ k_dct_pass2(DctPlan pl, cplx *__restrict__ H) {
     for (int idx = threadIdx.x; idx < G * N1; idx += blockDim.x) rows[idx] = res[pad(idx)];
 }
 
+
+// ---------------------------------------------------------------------------
+// Register-blocked FFT engine used for N >= 8192: a CTA of 256 threads transforms 4096 complex
+// points (G sequences of length L = 4096 / G) IN PLACE in shared memory.  Every thread holds 16
+// points per pass and does a radix-16 butterfly in registers (radix 8 / 4 / 2 for the last
+// pass), so a 1024-point transform is 3 passes (16 * 16 * 4) instead of 5 radix-4 ones, with
+// 16 independent loads, twiddles and stores per thread in flight.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ int pad16(int i) { return i + (i >> 4); }
+constexpr size_t FFT_POINTS = 4096, FFT_THREADS = 256;
+constexpr size_t FFT_SMEM = (FFT_POINTS + (FFT_POINTS >> 4) + 16) * sizeof(cplx);
+
+__device__ __forceinline__ cplx ldg_cplx(const cplx *p) {
+    double2 v = __ldg(reinterpret_cast<const double2 *>(p));
+    cplx r; r.x = v.x; r.y = v.y; return r;
+}
+__device__ __forceinline__ cplx mul_mi(cplx a) { cplx r; r.x = a.y; r.y = -a.x; return r; }   // * (-i)
+
+__device__ __forceinline__ void dft4(cplx &x0, cplx &x1, cplx &x2, cplx &x3) {
+    cplx t0 = cadd(x0, x2), t1 = csub(x0, x2), t2 = cadd(x1, x3), t3 = mul_mi(csub(x1, x3));
+    x0 = cadd(t0, t2); x1 = cadd(t1, t3); x2 = csub(t0, t2); x3 = csub(t1, t3);
+}
+
+template <int M> __device__ __forceinline__ cplx mul_w16(cplx a) {      // a * exp(-2 pi i M / 16)
+    const double c = 0.92387953251128673848, s = 0.38268343236508978178, h = 0.70710678118654752440;
+    cplx r;
+    if (M == 0) return a;
+    if (M == 1) { r.x = a.x * c + a.y * s; r.y = a.y * c - a.x * s; }
+    if (M == 2) { r.x = h * (a.x + a.y); r.y = h * (a.y - a.x); }
+    if (M == 3) { r.x = a.x * s + a.y * c; r.y = a.y * s - a.x * c; }
+    if (M == 4) { r.x = a.y; r.y = -a.x; }
+    if (M == 6) { r.x = h * (a.y - a.x); r.y = -h * (a.x + a.y); }
+    if (M == 9) { r.x = -(a.x * c + a.y * s); r.y = -(a.y * c - a.x * s); }
+    return r;
+}
+
+template <int R> __device__ __forceinline__ void butterfly(cplx *a);
+template <> __device__ __forceinline__ void butterfly<2>(cplx *a) {
+    cplx t = cadd(a[0], a[1]); a[1] = csub(a[0], a[1]); a[0] = t;
+}
+template <> __device__ __forceinline__ void butterfly<4>(cplx *a) { dft4(a[0], a[1], a[2], a[3]); }
+template <> __device__ __forceinline__ void butterfly<8>(cplx *a) {
+    cplx e0 = a[0], e1 = a[2], e2 = a[4], e3 = a[6], o0 = a[1], o1 = a[3], o2 = a[5], o3 = a[7];
+    dft4(e0, e1, e2, e3);
+    dft4(o0, o1, o2, o3);
+    o1 = mul_w16<2>(o1); o2 = mul_w16<4>(o2); o3 = mul_w16<6>(o3);
+    a[0] = cadd(e0, o0); a[4] = csub(e0, o0);
+    a[1] = cadd(e1, o1); a[5] = csub(e1, o1);
+    a[2] = cadd(e2, o2); a[6] = csub(e2, o2);
+    a[3] = cadd(e3, o3); a[7] = csub(e3, o3);
+}
+template <> __device__ __forceinline__ void butterfly<16>(cplx *a) {
+    // n = 4 n1 + n2, k = k1 + 4 k2:  B[n2][k1] = DFT4_n1 a[4 n1 + n2];  B *= W16^(n2 k1);
+    // X[k1 + 4 k2] = DFT4_n2 B[n2][k1]
+    dft4(a[0], a[4], a[8], a[12]);      // n2 = 0: a[4 k1 + 0] now holds B[0][k1]
+    dft4(a[1], a[5], a[9], a[13]);
+    dft4(a[2], a[6], a[10], a[14]);
+    dft4(a[3], a[7], a[11], a[15]);
+    a[5] = mul_w16<1>(a[5]);  a[9] = mul_w16<2>(a[9]);   a[13] = mul_w16<3>(a[13]);   // n2 = 1
+    a[6] = mul_w16<2>(a[6]);  a[10] = mul_w16<4>(a[10]); a[14] = mul_w16<6>(a[14]);   // n2 = 2
+    a[7] = mul_w16<3>(a[7]);  a[11] = mul_w16<6>(a[11]); a[15] = mul_w16<9>(a[15]);   // n2 = 3
+    // now a[4 k1 + n2] = B'[n2][k1]; transform over n2 and place X[k1 + 4 k2]
+    cplx x[16];
+#pragma unroll
+    for (int k1 = 0; k1 < 4; k1++) {
+        cplx b0 = a[4 * k1], b1 = a[4 * k1 + 1], b2 = a[4 * k1 + 2], b3 = a[4 * k1 + 3];
+        dft4(b0, b1, b2, b3);
+        x[k1] = b0; x[k1 + 4] = b1; x[k1 + 8] = b2; x[k1 + 12] = b3;
+    }
+#pragma unroll
+    for (int i = 0; i < 16; i++) a[i] = x[i];
+}
+
+template <int R>
+__device__ __forceinline__ void inplace_pass(cplx *buf, int L, int Ns, const cplx *__restrict__ W) {
+    constexpr int U = 16 / R;            // butterflies per thread
+    const int per = L / R, pshift = 31 - __clz(per), step = L / (Ns * R);
+    cplx a[U][R];
+    int dbase[U];
+#pragma unroll
+    for (int uu = 0; uu < U; uu++) {
+        const int u = (int)threadIdx.x + uu * (int)FFT_THREADS;
+        const int g = u >> pshift, j = u & (per - 1), k = j & (Ns - 1);
+        const int sbase = g * L + j;
+#pragma unroll
+        for (int t = 0; t < R; t++) a[uu][t] = buf[pad16(sbase + t * per)];
+        if (Ns > 1) {
+#pragma unroll
+            for (int t = 1; t < R; t++) a[uu][t] = cmul(a[uu][t], ldg_cplx(W + t * k * step));
+        }
+        dbase[uu] = g * L + (j - k) * R + k;
+    }
+    __syncthreads();                     // every input is in registers: the buffer may be overwritten
+#pragma unroll
+    for (int uu = 0; uu < U; uu++) {
+        butterfly<R>(a[uu]);
+#pragma unroll
+        for (int q = 0; q < R; q++) buf[pad16(dbase[uu] + q * Ns)] = a[uu][q];
+    }
+    __syncthreads();
+}
+
+// In-place FFT of 4096 / L sequences of length L (16 <= L <= 4096, power of two); W = W_L table.
+__device__ __forceinline__ void smem_fft16(cplx *buf, int L, const cplx *__restrict__ W) {
+    int Ns = 1;
+    for (; L / Ns >= 16; Ns *= 16) inplace_pass<16>(buf, L, Ns, W);
+    const int rem = L / Ns;
+    if (rem == 8) inplace_pass<8>(buf, L, Ns, W);
+    else if (rem == 4) inplace_pass<4>(buf, L, Ns, W);
+    else if (rem == 2) inplace_pass<2>(buf, L, Ns, W);
+}
+
+// pass 1 (register-blocked engine): grid (N1 / G, columns in batch), G = 4096 / N2
+__global__ void __launch_bounds__(FFT_THREADS, 2)
+k_dct_pass1_r16(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan pl,
+                const uint32_t *__restrict__ Dbits, double inscale, cplx *__restrict__ H) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cplx *buf = reinterpret_cast<cplx *>(smem_raw);
+    const int N2 = (int)pl.N2, G = (int)(FFT_POINTS / pl.N2), gshift = 31 - __clz(G);
+    const size_t N = pl.N, N1 = pl.N1;
+    const size_t n1_0 = (size_t)blockIdx.x * G;
+    const double *col = X + (col0 + blockIdx.y) * ldx;
+    cplx *Hc = H + (size_t)blockIdx.y * pl.Np;
+    // 16 elements per thread, four at a time so that their global loads are in flight together
+#pragma unroll
+    for (int b4 = 0; b4 < 4; b4++) {
+        size_t q0[4], q1[4]; uint32_t w0[4], w1[4]; double x0[4], x1[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int idx = (int)threadIdx.x + (b4 * 4 + u) * (int)FFT_THREADS;
+            const int g = idx & (G - 1), n2 = idx >> gshift;
+            const size_t n = n1_0 + g + N1 * (size_t)n2;
+            const bool lowhalf = 4 * n < N;
+            q0[u] = lowhalf ? 4 * n : 2 * N - 4 * n - 1;
+            q1[u] = lowhalf ? 4 * n + 2 : 2 * N - 4 * n - 3;
+            w0[u] = __ldg(Dbits + (q0[u] >> 5)); w1[u] = __ldg(Dbits + (q1[u] >> 5));
+            x0[u] = __ldg(col + q0[u]); x1[u] = __ldg(col + q1[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int idx = (int)threadIdx.x + (b4 * 4 + u) * (int)FFT_THREADS;
+            cplx z;
+            z.x = __dmul_rn((w0[u] >> (q0[u] & 31)) & 1 ? -inscale : inscale, x0[u]);
+            z.y = __dmul_rn((w1[u] >> (q1[u] & 31)) & 1 ? -inscale : inscale, x1[u]);
+            buf[pad16((idx & (G - 1)) * N2 + (idx >> gshift))] = z;
+        }
+    }
+    __syncthreads();
+    smem_fft16(buf, N2, pl.W1);
+    const size_t lo_mask = ((size_t)1 << pl.lo_bits) - 1;
+#pragma unroll 4
+    for (int it = 0; it < 16; it++) {
+        const int idx = (int)threadIdx.x + it * (int)FFT_THREADS;
+        const int g = idx & (G - 1), k2 = idx >> gshift;
+        const size_t n1 = n1_0 + g, e = n1 * (size_t)k2;       // < Np
+        cplx tw = cmul(ldg_cplx(pl.Thi + (e >> pl.lo_bits)), ldg_cplx(pl.Tlo + (e & lo_mask)));
+        Hc[(size_t)k2 * N1 + n1] = cmul(buf[pad16(g * N2 + k2)], tw);
+    }
+}
+
+// pass 2 (register-blocked engine): grid (N2 / G, columns in batch), G = 4096 / N1; in place
+__global__ void __launch_bounds__(FFT_THREADS, 2)
+k_dct_pass2_r16(DctPlan pl, cplx *__restrict__ H) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cplx *buf = reinterpret_cast<cplx *>(smem_raw);
+    cplx *rows = H + (size_t)blockIdx.y * pl.Np + (size_t)blockIdx.x * FFT_POINTS;
+#pragma unroll
+    for (int it = 0; it < 16; it++) {
+        const int idx = (int)threadIdx.x + it * (int)FFT_THREADS;
+        buf[pad16(idx)] = rows[idx];
+    }
+    __syncthreads();
+    smem_fft16(buf, (int)pl.N1, pl.W2);
+#pragma unroll
+    for (int it = 0; it < 16; it++) {
+        const int idx = (int)threadIdx.x + it * (int)FFT_THREADS;
+        rows[idx] = buf[pad16(idx)];
+    }
+}
+
 // sampled bins -> DCT values -> OUT
 __global__ void k_dct_post(DctPlan pl, const cplx *__restrict__ H, const int32_t *__restrict__ samples,
                            size_t S, size_t col0, size_t ncols, double outscale,
@@ -490,7 +671,9 @@ __global__ void k_dct_post(DctPlan pl, const cplx *__restrict__ H, const int32_t
 static bool dct_fast_ok(size_t N) { return N >= 1024 && (N & (N - 1)) == 0 && N <= ((size_t)1 << 25); }
 
 static size_t dct_batch_cols(size_t N, size_t m) {
-    size_t b = ((size_t)48 << 20) / (N * sizeof(double));
+    static size_t mb = 0;
+    if (!mb) { const char *e = getenv("SKB_DCT_BATCH_MB"); mb = e && atol(e) > 0 ? (size_t)atol(e) : 512; }
+    size_t b = (mb << 20) / (N * sizeof(double));
     if (b < 1) b = 1;
     if (b > m) b = m;
     return b;
@@ -580,8 +763,27 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         // one radix-4 unit per thread per pass where possible (latency hiding by occupancy)
         auto threads_for = [](size_t units) { size_t t = 128; while (t < units && t < 1024) t *= 2; return (unsigned)t; };
         const unsigned thr1 = threads_for(pl.G1 * pl.N2 / 4), thr2 = threads_for(pl.G2 * pl.N1 / 4);
+        // register-blocked radix-16 engine when a CTA's 4096 points hold whole sequences
+        const bool r16 = pl.N1 >= 16 && pl.N2 >= 16 && pl.N1 <= FFT_POINTS && pl.N2 <= FFT_POINTS &&
+                         pl.N1 * pl.N2 >= FFT_POINTS;
+        if (r16) {
+            SKB_CUDA(cudaFuncSetAttribute(k_dct_pass1_r16, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFT_SMEM));
+            SKB_CUDA(cudaFuncSetAttribute(k_dct_pass2_r16, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFT_SMEM));
+        }
         for (size_t c0 = 0; c0 < m; c0 += B) {
             const size_t nb = m - c0 < B ? m - c0 : B;
+            if (r16) {
+                {
+                    LaunchScope ls(KC_FJLT, st);
+                    k_dct_pass1_r16<<<dim3((unsigned)(pl.N1 * pl.N2 / FFT_POINTS), (unsigned)nb),
+                                      FFT_THREADS, FFT_SMEM, st>>>(Xc, ldc, c0, pl, Dbits, inscale, H);
+                }
+                {
+                    LaunchScope ls(KC_FJLT, st);
+                    k_dct_pass2_r16<<<dim3((unsigned)(pl.N1 * pl.N2 / FFT_POINTS), (unsigned)nb),
+                                      FFT_THREADS, FFT_SMEM, st>>>(pl, H);
+                }
+            } else {
             {
                 LaunchScope ls(KC_FJLT, st);
                 k_dct_pass1<<<dim3((unsigned)(pl.N1 / pl.G1), (unsigned)nb), thr1, smem1, st>>>(
@@ -590,6 +792,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
             {
                 LaunchScope ls(KC_FJLT, st);
                 k_dct_pass2<<<dim3((unsigned)(pl.N2 / pl.G2), (unsigned)nb), thr2, smem2, st>>>(pl, H);
+            }
             }
             {
                 LaunchScope ls(KC_FJLT, st);
