@@ -201,8 +201,9 @@ __device__ __forceinline__ double ldg_stream1(const double *p) {
     return v;
 }
 
+// 64 registers -> 4 CTAs (32 warps) per SM: measured 75% of HBM at C1 against 72% at 79 registers
 template <int VEC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 k_hash_rows(const double *__restrict__ X, size_t ldx, int m,
             const int32_t *__restrict__ rows, const int32_t *__restrict__ chunk_start,
             const int32_t *__restrict__ chunk_bucket, const double *__restrict__ value,
