@@ -179,6 +179,60 @@ def _time_apply(torch, S, A, SA, dim, reps, flush):
     return statistics.median(ts)
 
 
+def cpu_other_configs():
+    """The reference's CPU algorithm (oracle port) for configs 1, 3, 4, 5 on bounded samples, so
+    that every GPU number in `other_configs` has the CPU path timed beside it."""
+    import numpy as np
+    import scipy.sparse
+    from oracle import oracle as o
+    out = {}
+    rng = np.random.default_rng(DATA_SEED)
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+    def best(fn, reps=2):
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter(); fn(); ts.append(time.perf_counter() - t0)
+        return min(ts)
+
+    # C1 at full size: the serial scatter loop of hash_transform_Elemental.hpp:106-123
+    n, d, s = 100_000, 500, 2000
+    t = o.CWT(n, s, o.Context(SKETCH_SEED))
+    A = rng.standard_normal((n, d))
+    # a C-ordered n x d array reaches the reference as the column-major d x n matrix with the
+    # direction flipped (lib.py:113-123): the rowwise loop, which walks memory contiguously
+    dt = best(lambda: t.apply(A.T, "rowwise"))
+    out["c1_cwt"] = {"seconds": dt, "value": (n * d * 8 + s * d * 8) / dt / 1e9, "unit": "GB/s", "cores": 1,
+                     "sample": "full size (100000x500 -> 2000), the reference's serial rowwise loop on "
+                               "the transposed view"}
+    # C3: sign-scale + per-column DCT-II (scipy/pocketfft = REDFT10) + gather on 16 of the 2048 columns
+    n, s, dc = 2 ** 20, 8192, 16
+    f = o.FJLT(n, s, o.Context(SKETCH_SEED))
+    A = rng.standard_normal((n, dc))
+    dt = best(lambda: f.apply(A, "columnwise", fut="dct"), 1)
+    out["c3_fjlt_dct"] = {"seconds": dt, "value": (n * dc * 8 + s * dc * 8) / dt / 1e9, "unit": "GB/s",
+                          "cores": 1, "sample": "16 of 2048 columns (time is linear in columns)"}
+    # C4: CSC scatter loop (OpenMP over columns) on 2000 of the 100000 columns of one shard
+    n_loc, dcols, s, nnz_col = 1_250_000, 2000, 20_000, 1250
+    t = o.CWT(n_loc, s, o.Context(SKETCH_SEED))
+    indptr = (np.arange(dcols + 1, dtype=np.int64) * nnz_col).astype(np.int32)
+    indices = rng.integers(0, n_loc, dcols * nnz_col, dtype=np.int32)
+    values = rng.standard_normal(dcols * nnz_col)
+    dt = best(lambda: t.apply_csc(indptr, indices, values, (n_loc, dcols), "columnwise"))
+    out["c4_cwt_csc"] = {"seconds": dt, "value": (dcols * nnz_col * 12 + s * dcols * 8) / dt / 1e9,
+                         "unit": "GB/s", "cores": o.num_threads(),
+                         "sample": "2000 of 100000 columns of one shard (time is linear in columns)"}
+    # C5: realise W in double, cast to float, sgemm, float cosine pass on 2048 of the 500000 points
+    m, n, s = 2048, 784, 16384
+    r = o.GaussianRFT(n, s, 10.0, o.Context(SKETCH_SEED))
+    X = rng.random((m, n), dtype=np.float32)
+    dt = best(lambda: r.apply(X, "rowwise", dtype=np.float32), 1)
+    out["c5_rft"] = {"seconds": dt, "value": 2.0 * m * n * s / dt / 1e12, "unit": "TFLOP/s", "cores": cores,
+                     "sample": "2048 of 500000 points; includes realising the 784x16384 W, as every "
+                               "reference apply does (dense_transform_Elemental_local.hpp:101-102)"}
+    return out
+
+
 def other_configs(torch, lib, sketch, hbm_gbs, fp64_peak):
     """The remaining BASELINE.json configs on one GPU (device-resident, CUDA events, median of
     5, L2 flushed between runs); reported beside the main line, not as the bench value."""
@@ -259,6 +313,10 @@ def other_configs(torch, lib, sketch, hbm_gbs, fp64_peak):
     guarded("c3_fjlt_dct", lambda: c3("dct", 2048))
     guarded("c4_cwt_csc_shard", c4)
     guarded("c5_rft_shard", c5)
+    try:
+        out["cpu_baseline"] = cpu_other_configs()
+    except Exception as e:
+        out["cpu_baseline"] = {"error": str(e)[:200]}
     return out
 
 
