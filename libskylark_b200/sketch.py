@@ -319,7 +319,37 @@ class LaplacianRFT(_RFT):
                          params=(sigma,))
 
 
+def _outside_hot_path(name, where):
+    """Reference transforms that are not part of the accelerated path keep their names, so that
+    code importing them fails with a clear message instead of an AttributeError."""
+    class _Unsupported(object):
+        def __init__(self, *args, **kwargs):
+            raise errors.UnsupportedError(
+                "%s (%s) is outside the GPU sketch-apply path of this package; see DESIGN.md "
+                "section 7" % (name, where))
+    _Unsupported.__name__ = name
+    return _Unsupported
+
+
+SJLT = _outside_hot_path("SJLT", "sketch.py:303-338, pure Python in the reference")
+MaternRFT = _outside_hot_path("MaternRFT", "sketch.py:592-619")
+GaussianQRFT = _outside_hot_path("GaussianQRFT", "sketch.py:621-648")
+LaplacianQRFT = _outside_hot_path("LaplacianQRFT", "sketch.py:650-677")
+FastGaussianRFT = _outside_hot_path("FastGaussianRFT", "sketch.py:679-741")
+FastMaternRFT = _outside_hot_path("FastMaternRFT", "sketch.py:743-772")
+ExpSemigroupRLT = _outside_hot_path("ExpSemigroupRLT", "sketch.py:774-800")
+ExpSemigroupQRLT = _outside_hot_path("ExpSemigroupQRLT", "sketch.py:802-827")
+PPT = _outside_hot_path("PPT", "sketch.py:829-881")
+URST = _outside_hot_path("URST", "sketch.py:883-904, pure Python in the reference")
+NURST = _outside_hot_path("NURST", "sketch.py:906-931, pure Python in the reference")
+
 # Additional names (sketch.py:962-970); FastJLT = JLT is the reference's own aliasing.
+SparseJLT = SJLT
+Fastfood = FastGaussianRFT
+MaternFastfood = FastMaternRFT
+TensorSketch = PPT
+UniformSampler = URST
+NonUniformSampler = NURST
 FastJLT = JLT
 CountSketch = CWT
 RRT = GaussianRFT

@@ -186,3 +186,28 @@ def test_edge_shapes(sk, oracle):
     assert rel_fro(S4.apply(v.copy(), None, 0), O4.apply(v, "columnwise")) < TOL
     tv = torch.tensor(v, device="cuda")
     assert rel_fro(S4.apply(tv, None, 0).cpu().numpy(), O4.apply(v, "columnwise")) < TOL
+
+
+def test_serialized_sketch_replays_identically(sk, oracle):
+    """serialize -> deserialize (and pickle) rebuilds the same random state: identical sketch
+    bits (the reference's SerializationTest.cpp:13-87 round-trip check)."""
+    import pickle
+    import torch
+    from libskylark_b200 import lib
+    c = lib.Context(2024, 77)
+    A = torch.randn(3000, 40, dtype=torch.float64, device="cuda")
+    for make in (lambda: sk.CWT(3000, 4000, c), lambda: sk.MMT(3000, 4000, c),
+                 lambda: sk.WZT(3000, 4000, 1.5, c)):
+        S = make()
+        want = S.apply(A, None, 0)
+        S2 = sk.deserialize_sketch(S.serialize())
+        S3 = pickle.loads(pickle.dumps(S))
+        assert torch.equal(S2.apply(A, None, 0), want)      # buckets <= 32 rows: no atomics
+        assert torch.equal(S3.apply(A, None, 0), want)
+        assert np.array_equal(S2.row_idx(), S.row_idx()) and np.array_equal(S2.row_value(), S.row_value())
+    J = sk.JLT(3000, 64, c)
+    J2 = sk.deserialize_sketch(J.serialize())
+    assert np.array_equal(J2.export_dense(0, 0, 64, 50), J.export_dense(0, 0, 64, 50))
+    F = sk.FJLT(4096, 100, c)
+    F2 = pickle.loads(pickle.dumps(F))
+    assert np.array_equal(F2.samples(), F.samples()) and np.array_equal(F2.diagonal(), F.diagonal())

@@ -99,6 +99,14 @@ def test_error_codes(sk):
     assert e.value.code == 108                      # stream exhausted, randgen.hpp:64-72
 
 
+def test_reference_names_outside_the_path_fail_clearly(sk):
+    from libskylark_b200 import errors
+    for name in ("SJLT", "SparseJLT", "PPT", "TensorSketch", "FastGaussianRFT", "Fastfood", "MaternRFT",
+                 "URST", "UniformSampler", "NURST", "GaussianQRFT", "ExpSemigroupRLT"):
+        with pytest.raises(errors.UnsupportedError, match="outside the GPU sketch-apply path"):
+            getattr(sk, name)(10, 5)
+
+
 def test_adapter_checks(sk):
     from libskylark_b200 import errors
     S = sk.CWT(10, 5)
