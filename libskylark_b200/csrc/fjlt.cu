@@ -478,7 +478,14 @@ k_dct_pass2(DctPlan pl, cplx *__restrict__ H) {
 // 16 independent loads, twiddles and stores per thread in flight.
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ int pad16(int i) { return i + (i >> 4); }
-constexpr size_t FFT_POINTS = 4096, FFT_THREADS = 256;
+#ifndef SKB_FFT_PPT
+#define SKB_FFT_PPT 16          // points a thread holds per pass (16: radix-16 passes, 8: radix-8)
+#endif
+#ifndef SKB_FFT_MINB
+#define SKB_FFT_MINB 2
+#endif
+constexpr int FFT_PPT = SKB_FFT_PPT;
+constexpr size_t FFT_POINTS = 4096, FFT_THREADS = FFT_POINTS / FFT_PPT;
 constexpr size_t FFT_SMEM = (FFT_POINTS + (FFT_POINTS >> 4) + 16) * sizeof(cplx);
 
 __device__ __forceinline__ cplx ldg_cplx(const cplx *p) {
@@ -544,7 +551,7 @@ template <> __device__ __forceinline__ void butterfly<16>(cplx *a) {
 
 template <int R>
 __device__ __forceinline__ void inplace_pass(cplx *buf, int L, int Ns, const cplx *__restrict__ W) {
-    constexpr int U = 16 / R;            // butterflies per thread
+    constexpr int U = FFT_PPT / R;       // butterflies per thread
     const int per = L / R, pshift = 31 - __clz(per), step = L / (Ns * R);
     cplx a[U][R];
     int dbase[U];
@@ -574,15 +581,15 @@ __device__ __forceinline__ void inplace_pass(cplx *buf, int L, int Ns, const cpl
 // In-place FFT of 4096 / L sequences of length L (16 <= L <= 4096, power of two); W = W_L table.
 __device__ __forceinline__ void smem_fft16(cplx *buf, int L, const cplx *__restrict__ W) {
     int Ns = 1;
-    for (; L / Ns >= 16; Ns *= 16) inplace_pass<16>(buf, L, Ns, W);
+    for (; L / Ns >= FFT_PPT; Ns *= FFT_PPT) inplace_pass<FFT_PPT>(buf, L, Ns, W);
     const int rem = L / Ns;
-    if (rem == 8) inplace_pass<8>(buf, L, Ns, W);
+    if (FFT_PPT > 8 && rem == 8) inplace_pass<(FFT_PPT > 8 ? 8 : 2)>(buf, L, Ns, W);
     else if (rem == 4) inplace_pass<4>(buf, L, Ns, W);
     else if (rem == 2) inplace_pass<2>(buf, L, Ns, W);
 }
 
 // pass 1 (register-blocked engine): grid (N1 / G, columns in batch), G = 4096 / N2
-__global__ void __launch_bounds__(FFT_THREADS, 2)
+__global__ void __launch_bounds__(FFT_THREADS, SKB_FFT_MINB)
 k_dct_pass1_r16(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan pl,
                 const uint32_t *__restrict__ Dbits, double inscale, cplx *__restrict__ H) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -592,9 +599,9 @@ k_dct_pass1_r16(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan p
     const size_t n1_0 = (size_t)blockIdx.x * G;
     const double *col = X + (col0 + blockIdx.y) * ldx;
     cplx *Hc = H + (size_t)blockIdx.y * pl.Np;
-    // 16 elements per thread, four at a time so that their global loads are in flight together
+    // FFT_PPT elements per thread, four at a time so that their global loads are in flight together
 #pragma unroll
-    for (int b4 = 0; b4 < 4; b4++) {
+    for (int b4 = 0; b4 < FFT_PPT / 4; b4++) {
         size_t q0[4], q1[4]; uint32_t w0[4], w1[4]; double x0[4], x1[4];
 #pragma unroll
         for (int u = 0; u < 4; u++) {
@@ -620,7 +627,7 @@ k_dct_pass1_r16(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan p
     smem_fft16(buf, N2, pl.W1);
     const size_t lo_mask = ((size_t)1 << pl.lo_bits) - 1;
 #pragma unroll 4
-    for (int it = 0; it < 16; it++) {
+    for (int it = 0; it < FFT_PPT; it++) {
         const int idx = (int)threadIdx.x + it * (int)FFT_THREADS;
         const int g = idx & (G - 1), k2 = idx >> gshift;
         const size_t n1 = n1_0 + g, e = n1 * (size_t)k2;       // < Np
@@ -630,20 +637,20 @@ k_dct_pass1_r16(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan p
 }
 
 // pass 2 (register-blocked engine): grid (N2 / G, columns in batch), G = 4096 / N1; in place
-__global__ void __launch_bounds__(FFT_THREADS, 2)
+__global__ void __launch_bounds__(FFT_THREADS, SKB_FFT_MINB)
 k_dct_pass2_r16(DctPlan pl, cplx *__restrict__ H) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     cplx *buf = reinterpret_cast<cplx *>(smem_raw);
     cplx *rows = H + (size_t)blockIdx.y * pl.Np + (size_t)blockIdx.x * FFT_POINTS;
 #pragma unroll
-    for (int it = 0; it < 16; it++) {
+    for (int it = 0; it < FFT_PPT; it++) {
         const int idx = (int)threadIdx.x + it * (int)FFT_THREADS;
         buf[pad16(idx)] = rows[idx];
     }
     __syncthreads();
     smem_fft16(buf, (int)pl.N1, pl.W2);
 #pragma unroll
-    for (int it = 0; it < 16; it++) {
+    for (int it = 0; it < FFT_PPT; it++) {
         const int idx = (int)threadIdx.x + it * (int)FFT_THREADS;
         rows[idx] = buf[pad16(idx)];
     }
@@ -764,7 +771,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         auto threads_for = [](size_t units) { size_t t = 128; while (t < units && t < 1024) t *= 2; return (unsigned)t; };
         const unsigned thr1 = threads_for(pl.G1 * pl.N2 / 4), thr2 = threads_for(pl.G2 * pl.N1 / 4);
         // register-blocked radix-16 engine when a CTA's 4096 points hold whole sequences
-        const bool r16 = pl.N1 >= 16 && pl.N2 >= 16 && pl.N1 <= FFT_POINTS && pl.N2 <= FFT_POINTS &&
+        const bool r16 = pl.N1 >= (size_t)FFT_PPT && pl.N2 >= (size_t)FFT_PPT && pl.N1 <= FFT_POINTS && pl.N2 <= FFT_POINTS &&
                          pl.N1 * pl.N2 >= FFT_POINTS;
         if (r16) {
             SKB_CUDA(cudaFuncSetAttribute(k_dct_pass1_r16, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFT_SMEM));
