@@ -68,7 +68,12 @@ int sl_apply_sketch_transform(sl_sketch_transform_t *S, char *input_type, void *
 /* capi/basec.hpp:62-64, capi/cbase.cpp:63-75: host buffer, column-major m x n, ld = m. */
 int sl_wrap_raw_matrix(double *data, int m, int n, void **A);
 int sl_free_raw_matrix_wrap(void *A_);
-/* capi/basec.hpp:66-83, capi/cbase.cpp:77-121: host CSC, int32 indptr[n_cols+1]/indices. */
+/* capi/basec.hpp:66-83, capi/cbase.cpp:77-121: host CSC, int32 indptr[n_cols+1]/indices.
+ * When a wrapper is the SA of a sparse -> sparse CWT/MMT/WZT apply
+ * (sketch/hash_transform_local_sparse.hpp:88-223) the library attaches new arrays it owns and
+ * raises struct_updated; read nnz/height/width, then copy out with sl_raw_sp_matrix_data before
+ * freeing the wrapper.  For device wrappers (sl_wrap_device_sp_matrix) the three destinations
+ * of sl_raw_sp_matrix_data are device pointers. */
 int sl_wrap_raw_sp_matrix(int *indptr, int *ind, double *data, int nnz, int n_rows,
                           int n_cols, void **A);
 int sl_free_raw_sp_matrix_wrap(void *A_);

@@ -127,6 +127,21 @@ struct sl_matrix_t {
     void *data; int64_t m, n, ld;                       // dense
     int32_t *indptr, *indices; double *values; int64_t nnz;   // sparse (m x n CSC)
     bool struct_updated;
+    struct SpOwned *own = nullptr;   // arrays a sparse result was attached with (wrapper-owned)
+};
+// Storage behind a sparse SA after an apply replaced its structure (the reference's
+// sparse_matrix_t::attach(..., ownership=true), base/sparse_matrix.hpp); freed with the wrapper.
+struct SpOwned {
+    std::vector<int32_t> h_indptr, h_indices; std::vector<double> h_values;
+    int32_t *d_indptr = nullptr, *d_indices = nullptr; double *d_values = nullptr; int device = -1;
+    void release_device() {
+        if (!d_indptr && !d_indices && !d_values) return;
+        int prev = -1; cudaGetDevice(&prev); if (device >= 0) cudaSetDevice(device);
+        cudaFree(d_indptr); cudaFree(d_indices); cudaFree(d_values);
+        d_indptr = d_indices = nullptr; d_values = nullptr;
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+    ~SpOwned() { release_device(); }
 };
 
 enum TType { T_JLT, T_CT, T_CWT, T_MMT, T_WZT, T_GRFT, T_LRFT, T_FJLT };
@@ -279,7 +294,7 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
     const int64_t other = colwise ? A->n : A->m;
     if (offset < 0 || offset + sk > t->N || (!shard && sk != t->N))
         throw error(SKB_ERR_INVALID_PARAM, "apply: sketched dimension of A does not match N");
-    if (SA->kind != MK_DENSE) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse output is not supported");
+    if (SA->kind != MK_DENSE) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse output goes through apply_sparse_out");
     const int64_t sa_sk = colwise ? SA->m : SA->n, sa_other = colwise ? SA->n : SA->m;
     if (sa_sk != t->S || sa_other != other)
         throw error(SKB_ERR_INVALID_PARAM, "apply: SA has the wrong shape");
@@ -355,6 +370,46 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
                (size_t)other, d.D, d.Dbits, d.samples, (size_t)t->S, d.wht_slot_sample, d.wht_slot_out,
                (double *)SA->data, (size_t)SA->ld,
                d.ws, d.ws_bytes, st, (size_t)offset, (size_t)sk);
+}
+
+// Sparse in, sparse out (CWT/MMT/WZT; sketch/hash_transform_local_sparse.hpp:88-223).  A is
+// device resident; the result replaces SA's structure, on the device for device wrappers and
+// in wrapper-owned host arrays otherwise (read back through sl_raw_sp_matrix_*).
+static void apply_sparse_out(sl_sketch_transform_t *t, const sl_matrix_t *A, sl_matrix_t *SA,
+                             int dim, int64_t offset, bool shard, int device) {
+    const bool colwise = dim == SL_COLUMNWISE;
+    if (!t->is_hash() || A->kind != MK_SPARSE)
+        throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse output needs CWT/MMT/WZT and a sparse input");
+    const int64_t sk = colwise ? A->m : A->n;
+    if (offset < 0 || offset + sk > t->N || (!shard && sk != t->N))
+        throw error(SKB_ERR_INVALID_PARAM, "apply: sketched dimension of A does not match N");
+    DevState &d = dev_state(t, device);
+    ensure_hash_tables(t, d);
+    int32_t *oi = nullptr, *ox = nullptr; double *ov = nullptr; size_t onnz = 0;
+    hash_apply_csc_sparse(A->indptr, A->indices, A->values, (size_t)A->m, (size_t)A->n,
+                          (size_t)A->nnz, !colwise, d.bucket + offset, d.value + offset, t->S,
+                          &oi, &ox, &ov, &onnz, &d.ws, &d.ws_bytes, g_stream);
+    if (!SA->own) SA->own = new SpOwned();
+    SpOwned &o = *SA->own;
+    o.release_device();
+    const int64_t om = colwise ? t->S : A->m, on = colwise ? A->n : t->S;
+    if (SA->on_device) {
+        o.d_indptr = oi; o.d_indices = ox; o.d_values = ov; o.device = device;
+        SA->indptr = oi; SA->indices = ox; SA->values = ov;
+    } else {
+        try {
+            o.h_indptr.resize((size_t)on + 1); o.h_indices.resize(onnz); o.h_values.resize(onnz);
+            SKB_CUDA(cudaMemcpyAsync(o.h_indptr.data(), oi, ((size_t)on + 1) * 4, cudaMemcpyDeviceToHost, g_stream));
+            if (onnz) {
+                SKB_CUDA(cudaMemcpyAsync(o.h_indices.data(), ox, onnz * 4, cudaMemcpyDeviceToHost, g_stream));
+                SKB_CUDA(cudaMemcpyAsync(o.h_values.data(), ov, onnz * 8, cudaMemcpyDeviceToHost, g_stream));
+            }
+            SKB_CUDA(cudaStreamSynchronize(g_stream));
+        } catch (...) { cudaFree(oi); cudaFree(ox); cudaFree(ov); throw; }
+        cudaFree(oi); cudaFree(ox); cudaFree(ov);
+        SA->indptr = o.h_indptr.data(); SA->indices = o.h_indices.data(); SA->values = o.h_values.data();
+    }
+    SA->m = om; SA->n = on; SA->nnz = (int64_t)onnz; SA->struct_updated = true;
 }
 
 // Host operands of a dense sketch: the sketched dimension is cut in chunks; chunk c+1 is
@@ -452,10 +507,12 @@ static void apply_any(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA,
     if (A->on_device) {
         if (A->device != SA->device) throw error(SKB_ERR_INVALID_USAGE, "apply: A and SA are on different devices");
         DeviceGuard g(A->device);
-        apply_device(t, A, SA, dim, offset, shard);
+        if (SA->kind == MK_SPARSE) apply_sparse_out(t, A, SA, dim, offset, shard, A->device);
+        else apply_device(t, A, SA, dim, offset, shard);
         return;
     }
-    if (SA->kind != MK_DENSE) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse output is not supported");
+    if (SA->kind == MK_SPARSE && A->kind != MK_SPARSE)
+        throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse output needs CWT/MMT/WZT and a sparse input");
     int device = 0;
     SKB_CUDA(cudaGetDevice(&device));
     cudaStream_t st = g_stream;
@@ -483,6 +540,11 @@ static void apply_any(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA,
             SKB_CUDA(cudaMemcpyAsync(bufs[1], A->indices, ib, cudaMemcpyHostToDevice, st));
             SKB_CUDA(cudaMemcpyAsync(bufs[2], A->values, vb, cudaMemcpyHostToDevice, st));
             dA.indptr = (int32_t *)bufs[0]; dA.indices = (int32_t *)bufs[1]; dA.values = (double *)bufs[2];
+        }
+        if (SA->kind == MK_SPARSE) {
+            apply_sparse_out(t, &dA, SA, dim, offset, shard, device);
+            for (void *b : bufs) cudaFree(b);
+            return;
         }
         size_t obytes = (size_t)SA->ld * (size_t)SA->n * (SA->dtype == SL_DTYPE_F32 ? 4 : 8);
         SKB_CUDA(cudaMalloc(&bufs[3], obytes ? obytes : 16));
@@ -573,8 +635,11 @@ char *sl_supported_sketch_transforms(void) {
         "(\"CT\",\"Matrix\",\"Matrix\") "
         "(\"FJLT\",\"Matrix\",\"Matrix\") "
         "(\"CWT\",\"Matrix\",\"Matrix\") (\"CWT\",\"SparseMatrix\",\"Matrix\") "
+        "(\"CWT\",\"SparseMatrix\",\"SparseMatrix\") "
         "(\"MMT\",\"Matrix\",\"Matrix\") (\"MMT\",\"SparseMatrix\",\"Matrix\") "
+        "(\"MMT\",\"SparseMatrix\",\"SparseMatrix\") "
         "(\"WZT\",\"Matrix\",\"Matrix\") (\"WZT\",\"SparseMatrix\",\"Matrix\") "
+        "(\"WZT\",\"SparseMatrix\",\"SparseMatrix\") "
         "(\"GaussianRFT\",\"Matrix\",\"Matrix\") "
         "(\"LaplacianRFT\",\"Matrix\",\"Matrix\") ";
     return s;
@@ -733,7 +798,12 @@ int sl_wrap_device_sp_matrix(int32_t *indptr, int32_t *ind, double *data, int64_
     *A = M;
     SL_CATCH
 }
-int sl_free_raw_sp_matrix_wrap(void *A_) { delete (sl_matrix_t *)A_; return 0; }
+int sl_free_raw_sp_matrix_wrap(void *A_) {
+    sl_matrix_t *M = (sl_matrix_t *)A_;
+    if (M) delete M->own;
+    delete M;
+    return 0;
+}
 int sl_raw_sp_matrix_struct_updated(void *A_, bool *u) { *u = ((sl_matrix_t *)A_)->struct_updated; return 0; }
 int sl_raw_sp_matrix_reset_update_flag(void *A_) { ((sl_matrix_t *)A_)->struct_updated = false; return 0; }
 int sl_raw_sp_matrix_nnz(void *A_, int *nnz) { *nnz = (int)((sl_matrix_t *)A_)->nnz; return 0; }
@@ -742,7 +812,14 @@ int sl_raw_sp_matrix_width(void *A_, int *w) { *w = (int)((sl_matrix_t *)A_)->n;
 int sl_raw_sp_matrix_data(void *A_, int32_t *indptr, int32_t *indices, double *values) {
     SL_TRY
     sl_matrix_t *M = as_matrix(A_);
-    if (M->on_device) throw error(SKB_ERR_INVALID_USAGE, "sl_raw_sp_matrix_data: device matrix");
+    if (M->on_device) {     // device wrapper: the three destinations are device pointers too
+        DeviceGuard g(M->device);
+        SKB_CUDA(cudaMemcpyAsync(indptr, M->indptr, (size_t)(M->n + 1) * sizeof(int32_t), cudaMemcpyDeviceToDevice, g_stream));
+        SKB_CUDA(cudaMemcpyAsync(indices, M->indices, (size_t)M->nnz * sizeof(int32_t), cudaMemcpyDeviceToDevice, g_stream));
+        SKB_CUDA(cudaMemcpyAsync(values, M->values, (size_t)M->nnz * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+        SKB_CUDA(cudaStreamSynchronize(g_stream));
+        return 0;
+    }
     memcpy(indptr, M->indptr, (size_t)(M->n + 1) * sizeof(int32_t));
     memcpy(indices, M->indices, (size_t)M->nnz * sizeof(int32_t));
     memcpy(values, M->values, (size_t)M->nnz * sizeof(double));

@@ -17,6 +17,7 @@
 //     with separate multiply and add, i.e. the reference's own rounding sequence.
 //   * the strided layout and CSC input accumulate in shared memory per output
 //     column and dump coalesced columns.
+#include <algorithm>
 #include <cstdlib>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -518,6 +519,165 @@ void hash_apply_csc_rowwise(const int32_t *indptr, const int32_t *indices,
     k_hash_csc_rowwise<<<148 * 8, 256, 0, st>>>(indptr, indices, values, ncols, bucket, value,
                                                 OUT, ldo);
     SKB_CUDA(cudaGetLastError());
+}
+
+// ---------------------------------------------------------------------------
+// K2s: sparse -> sparse (hash_transform_local_sparse.hpp:88-223).  Every stored entry becomes
+// a (target column, target row) key and a scaled value; a stable radix sort groups equal
+// keys while keeping the input order inside a group -- the order in which the reference
+// accumulates -- and one thread per group adds its run left to right, so the sums round
+// exactly as the reference's do.  Output columns come out row-sorted (the reference leaves
+// them in first-touch order; same matrix).  Cancelled sums stay stored, as in the reference.
+// ---------------------------------------------------------------------------
+__global__ void k_sp_expand(const int32_t *__restrict__ indptr, const int32_t *__restrict__ indices,
+                            const double *__restrict__ values, int ncols, int nnz, int rowwise,
+                            const int32_t *__restrict__ bucket, const double *__restrict__ value,
+                            uint64_t *__restrict__ keys, double *__restrict__ vals) {
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += gridDim.x * blockDim.x) {
+        int lo = 0, hi = ncols;                  // column of entry e: last c with indptr[c] <= e
+        while (hi - lo > 1) {
+            int mid = (lo + hi) >> 1;
+            if (indptr[mid] <= e) lo = mid; else hi = mid;
+        }
+        const int col = lo, row = indices[e];
+        const int k = rowwise ? col : row;       // sketched index
+        const uint32_t ocol = rowwise ? (uint32_t)bucket[k] : (uint32_t)col;
+        const uint32_t orow = rowwise ? (uint32_t)row : (uint32_t)bucket[k];
+        keys[e] = ((uint64_t)ocol << 32) | orow;
+        vals[e] = __dmul_rn(values[e], value[k]);
+    }
+}
+
+__global__ void k_sp_heads(const uint64_t *__restrict__ keys, int nnz, int32_t *__restrict__ head) {
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += gridDim.x * blockDim.x)
+        head[e] = (e == 0 || keys[e] != keys[e - 1]) ? 1 : 0;
+}
+
+__global__ void k_sp_reduce(const uint64_t *__restrict__ keys, const double *__restrict__ vals,
+                            const int32_t *__restrict__ pos, int nnz,
+                            uint64_t *__restrict__ ukeys, int32_t *__restrict__ out_indices,
+                            double *__restrict__ out_values) {
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += gridDim.x * blockDim.x) {
+        const int r = pos[e] - 1;
+        if (e != 0 && pos[e - 1] == pos[e]) continue;      // not the head of its run
+        const uint64_t k = keys[e];
+        double acc = vals[e];
+        for (int q = e + 1; q < nnz && keys[q] == k; q++) acc = __dadd_rn(acc, vals[q]);
+        ukeys[r] = k;
+        out_indices[r] = (int32_t)(uint32_t)k;
+        out_values[r] = acc;
+    }
+}
+
+__global__ void k_sp_indptr(const uint64_t *__restrict__ ukeys, int nout, int ncols_out,
+                            int32_t *__restrict__ out_indptr) {
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c <= ncols_out; c += gridDim.x * blockDim.x) {
+        const uint64_t target = (uint64_t)(uint32_t)c << 32;
+        int lo = 0, hi = nout;                    // first entry with key >= target
+        while (lo < hi) {
+            int mid = (lo + hi) >> 1;
+            if (ukeys[mid] < target) lo = mid + 1; else hi = mid;
+        }
+        out_indptr[c] = lo;
+    }
+}
+
+void hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices, const double *values,
+                           size_t nrows, size_t ncols, size_t nnz, bool rowwise,
+                           const int32_t *bucket, const double *value, int S,
+                           int32_t **out_indptr, int32_t **out_indices, double **out_values,
+                           size_t *out_nnz, void **ws, size_t *ws_bytes, cudaStream_t st) {
+    const size_t ncols_out = rowwise ? (size_t)S : ncols;
+    const size_t nrows_out = rowwise ? nrows : (size_t)S;
+    *out_indptr = nullptr; *out_indices = nullptr; *out_values = nullptr; *out_nnz = 0;
+    if (nnz > 0x7fffffffULL || ncols > 0x7ffffffeULL || nrows > 0x7fffffffULL)
+        throw error(SKB_ERR_INVALID_PARAM, "sparse apply: sizes exceed int32");
+    // temporaries live in the caller's grow-only workspace (no allocation in steady state)
+    auto al = [](size_t b) { return (b + 255) / 256 * 256; };
+    size_t sort_bytes = 0, scan_bytes = 0;
+    if (nnz) {
+        cub::DoubleBuffer<uint64_t> kq(nullptr, nullptr);
+        cub::DoubleBuffer<double> vq(nullptr, nullptr);
+        cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, kq, vq, (int)nnz, 0, 64, st);
+        cub::DeviceScan::InclusiveSum(nullptr, scan_bytes, (int32_t *)nullptr, (int32_t *)nullptr,
+                                      (int)nnz, st);
+    }
+    const size_t tmp_bytes = al(std::max(sort_bytes, scan_bytes));
+    const size_t need = 4 * al(nnz * 8) + 2 * al(nnz * 4) + tmp_bytes + 256;
+    if (*ws_bytes < need) {
+        SKB_CUDA(cudaStreamSynchronize(st));
+        cudaFree(*ws); *ws = nullptr; *ws_bytes = 0;
+        SKB_CUDA(cudaMalloc(ws, need));
+        *ws_bytes = need;
+    }
+    char *w = (char *)*ws;
+    uint64_t *keys = (uint64_t *)w;  w += al(nnz * 8);
+    uint64_t *keys2 = (uint64_t *)w; w += al(nnz * 8);
+    double *vals = (double *)w;      w += al(nnz * 8);
+    double *vals2 = (double *)w;     w += al(nnz * 8);
+    int32_t *head = (int32_t *)w;    w += al(nnz * 4);
+    int32_t *pos = (int32_t *)w;     w += al(nnz * 4);
+    void *tmp = w;
+    try {
+        SKB_CUDA(cudaMalloc(out_indptr, (ncols_out + 1) * sizeof(int32_t)));
+        if (nnz == 0) {
+            SKB_CUDA(cudaMemsetAsync(*out_indptr, 0, (ncols_out + 1) * sizeof(int32_t), st));
+            SKB_CUDA(cudaMalloc(out_indices, 16));
+            SKB_CUDA(cudaMalloc(out_values, 16));
+            return;
+        }
+        const int n = (int)nnz;
+        const unsigned nb = (unsigned)std::min<size_t>((nnz + 255) / 256, 148 * 32);
+        {
+            LaunchScope ls(KC_HASH, st);
+            k_sp_expand<<<nb, 256, 0, st>>>(indptr, indices, values, (int)ncols, n, rowwise ? 1 : 0,
+                                            bucket, value, keys, vals);
+        }
+        int row_bits = 1, col_bits = 1;
+        while ((1ULL << row_bits) < nrows_out && row_bits < 32) row_bits++;
+        while ((1ULL << col_bits) < ncols_out && col_bits < 32) col_bits++;
+        // rows occupy the low word: sort its used bits, then the used bits of the high word
+        cub::DoubleBuffer<uint64_t> kb(keys, keys2);
+        cub::DoubleBuffer<double> vb(vals, vals2);
+        {
+            LaunchScope ls(KC_HASH, st);
+            SKB_CUDA(cub::DeviceRadixSort::SortPairs(tmp, sort_bytes, kb, vb, n, 0, row_bits, st));
+        }
+        {
+            LaunchScope ls(KC_HASH, st);
+            SKB_CUDA(cub::DeviceRadixSort::SortPairs(tmp, sort_bytes, kb, vb, n, 32, 32 + col_bits, st));
+        }
+        {
+            LaunchScope ls(KC_HASH, st);
+            k_sp_heads<<<nb, 256, 0, st>>>(kb.Current(), n, head);
+        }
+        {
+            LaunchScope ls(KC_HASH, st);
+            SKB_CUDA(cub::DeviceScan::InclusiveSum(tmp, scan_bytes, head, pos, n, st));
+        }
+        int32_t nout = 0;
+        SKB_CUDA(cudaMemcpyAsync(&nout, pos + (n - 1), sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        SKB_CUDA(cudaStreamSynchronize(st));
+        SKB_CUDA(cudaMalloc(out_indices, (size_t)nout * 4));
+        SKB_CUDA(cudaMalloc(out_values, (size_t)nout * 8));
+        uint64_t *ukeys = kb.Alternate();       // the other sort buffer is free by now
+        {
+            LaunchScope ls(KC_HASH, st);
+            k_sp_reduce<<<nb, 256, 0, st>>>(kb.Current(), vb.Current(), pos, n, ukeys, *out_indices,
+                                            *out_values);
+        }
+        {
+            LaunchScope ls(KC_HASH, st);
+            const unsigned cb = (unsigned)std::min<size_t>((ncols_out + 1 + 255) / 256, 148 * 32);
+            k_sp_indptr<<<cb, 256, 0, st>>>(ukeys, nout, (int)ncols_out, *out_indptr);
+        }
+        SKB_CUDA(cudaGetLastError());
+        *out_nnz = (size_t)nout;
+    } catch (...) {
+        cudaFree(*out_indptr); cudaFree(*out_indices); cudaFree(*out_values);
+        *out_indptr = nullptr; *out_indices = nullptr; *out_values = nullptr;
+        throw;
+    }
 }
 
 }  // namespace skb

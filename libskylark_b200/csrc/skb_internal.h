@@ -92,6 +92,16 @@ void hash_apply_csc_rowwise(const int32_t *indptr, const int32_t *indices,
                             const int32_t *bucket, const double *value, double *OUT,
                             size_t ldo, int S, cudaStream_t st);
 
+// CSC input -> CSC output (device arrays allocated here with cudaMalloc, owned by the caller):
+// columnwise gives S x ncols, rowwise nrows x S; rows inside a column come out sorted.
+// Temporaries live in the grow-only workspace (*ws, *ws_bytes).  Stream-ordered: the result
+// arrays are complete once work queued on st so far has finished.
+void hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices, const double *values,
+                           size_t nrows, size_t ncols, size_t nnz, bool rowwise,
+                           const int32_t *bucket, const double *value, int S,
+                           int32_t **out_indptr, int32_t **out_indices, double **out_values,
+                           size_t *out_nnz, void **ws, size_t *ws_bytes, cudaStream_t st);
+
 // ---- dense transforms (dense.cu) -------------------------------------------
 enum DenseDist { DD_NORMAL = 0, DD_CAUCHY = 1 };
 struct DenseParams {

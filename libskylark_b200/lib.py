@@ -275,8 +275,27 @@ class ScipyAdapter:
         return data
 
     def ptrcleaner(self):
-        callsl("sl_free_raw_sp_matrix_wrap", self._ptr)
-        self._keep = None
+        # A sparse result replaces the wrapped structure inside the library; fetch it before
+        # the wrapper goes away (same protocol as the reference's ScipyAdapter, lib.py:200-231).
+        try:
+            updated = ctypes.c_bool()
+            callsl("sl_raw_sp_matrix_struct_updated", self._ptr, byref(updated))
+            if updated.value:
+                nnz, h, w = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+                callsl("sl_raw_sp_matrix_nnz", self._ptr, byref(nnz))
+                callsl("sl_raw_sp_matrix_height", self._ptr, byref(h))
+                callsl("sl_raw_sp_matrix_width", self._ptr, byref(w))
+                indptr = numpy.zeros(w.value + 1, dtype=numpy.int32)
+                indices = numpy.zeros(nnz.value, dtype=numpy.int32)
+                values = numpy.zeros(nnz.value, dtype=numpy.float64)
+                callsl("sl_raw_sp_matrix_data", self._ptr, indptr.ctypes.data_as(c_void_p),
+                       indices.ctypes.data_as(c_void_p), values.ctypes.data_as(c_void_p))
+                A = self._A
+                A._shape = (h.value, w.value) if self.getorder() == "F" else (w.value, h.value)
+                A.indptr, A.indices, A.data = indptr, indices, values
+        finally:
+            callsl("sl_free_raw_sp_matrix_wrap", self._ptr)
+            self._keep = None
 
     def getdim(self, dim):
         return self._A.shape[dim]
@@ -299,9 +318,9 @@ class ScipyAdapter:
         return None, self.getorder() == "C"
 
     def getctor(self):
-        # the reference would build a sparse output (lib.py:257-266); this library only
-        # produces dense sketches, so the default output of a sparse input is dense.
-        return NumpyAdapter.ctor
+        # sparse in -> sparse out by default, as in the reference (lib.py:257-266); pass a numpy
+        # SA or defouttype="LocalMatrix" for a dense sketch of a sparse input.
+        return ScipyAdapter.ctor
 
     @staticmethod
     def ctor(m, n, B):
@@ -403,6 +422,20 @@ class DeviceCSC:
         self.device = values.device
         self.dtype = values.dtype
 
+    @classmethod
+    def empty(cls, shape, format="csc", device="cuda"):
+        """All-zero matrix; an output operand for sparse -> sparse CWT/MMT/WZT."""
+        torch = _torch()
+        nptr = (shape[1] if format == "csc" else shape[0]) + 1
+        return cls(torch.zeros(nptr, dtype=torch.int32, device=device),
+                   torch.zeros(0, dtype=torch.int32, device=device),
+                   torch.zeros(0, dtype=torch.float64, device=device), shape, format)
+
+    def to_scipy(self):
+        ctor = scipy.sparse.csc_matrix if self.format == "csc" else scipy.sparse.csr_matrix
+        return ctor((self.values.cpu().numpy(), self.indices.cpu().numpy(),
+                     self.indptr.cpu().numpy()), shape=self.shape)
+
 
 class DeviceCSCAdapter:
     def __init__(self, A):
@@ -427,7 +460,25 @@ class DeviceCSCAdapter:
         return data
 
     def ptrcleaner(self):
-        callsl("sl_free_raw_sp_matrix_wrap", self._ptr)
+        try:
+            updated = ctypes.c_bool()
+            callsl("sl_raw_sp_matrix_struct_updated", self._ptr, byref(updated))
+            if updated.value:     # sparse result: copy it into tensors torch owns
+                torch = _torch()
+                nnz, h, w = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+                callsl("sl_raw_sp_matrix_nnz", self._ptr, byref(nnz))
+                callsl("sl_raw_sp_matrix_height", self._ptr, byref(h))
+                callsl("sl_raw_sp_matrix_width", self._ptr, byref(w))
+                A = self._A
+                dev = A.values.device
+                A.indptr = torch.empty(w.value + 1, dtype=torch.int32, device=dev)
+                A.indices = torch.empty(nnz.value, dtype=torch.int32, device=dev)
+                A.values = torch.empty(nnz.value, dtype=torch.float64, device=dev)
+                callsl("sl_raw_sp_matrix_data", self._ptr, c_void_p(A.indptr.data_ptr()),
+                       c_void_p(A.indices.data_ptr()), c_void_p(A.values.data_ptr()))
+                A.shape = (h.value, w.value) if A.format == "csc" else (w.value, h.value)
+        finally:
+            callsl("sl_free_raw_sp_matrix_wrap", self._ptr)
 
     def getdim(self, dim):
         return self._A.shape[dim]
@@ -439,6 +490,10 @@ class DeviceCSCAdapter:
         return "F" if self._A.format == "csc" else "C"
 
     def iscompatible(self, B):
+        if isinstance(B, DeviceCSCAdapter):
+            if self.getorder() != B.getorder():
+                return "sketching device CSC to device CSC requires the same format", None
+            return None, self.getorder() == "C"
         if not isinstance(B, TorchAdapter):
             return "device sparse input needs a device (torch CUDA) output", None
         if self.getorder() != B.getorder():
@@ -447,6 +502,12 @@ class DeviceCSCAdapter:
 
     def getctor(self):
         return TorchAdapter.ctor
+
+    @staticmethod
+    def ctor(m, n, B):
+        A = B.getobj() if isinstance(B, (TorchAdapter, DeviceCSCAdapter)) else None
+        fmt = "csr" if (A is not None and B.getorder() == "C") else "csc"
+        return DeviceCSC.empty((m, n), fmt, A.device if A is not None else "cuda")
 
 
 def adapt(obj):
@@ -472,6 +533,7 @@ map_to_ctor = {}
 map_to_ctor["LocalMatrix"] = NumpyAdapter.ctor
 map_to_ctor["LocalSpMatrix"] = ScipyAdapter.ctor
 map_to_ctor["DeviceMatrix"] = TorchAdapter.ctor
+map_to_ctor["DeviceSpMatrix"] = DeviceCSCAdapter.ctor
 
 
 def set_stream_from_torch():

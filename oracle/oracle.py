@@ -56,6 +56,7 @@ def lib():
         _lib = ctypes.CDLL(_SO)
         _lib.sko_random_int.restype = ctypes.c_int
         _lib.sko_num_threads.restype = ctypes.c_int
+        _lib.sko_hash_apply_csc_sparse.restype = ctypes.c_size_t
     return _lib
 
 
@@ -268,6 +269,25 @@ class _Hash(_Transform):
                                          _p(self.row_value), _p(SA), _sz(self.S),
                                          _sz(h))
         return SA
+
+    def apply_csc_sparse(self, A_csc, dim="columnwise"):
+        """sparse -> sparse (hash_transform_local_sparse.hpp:88-223); returns scipy CSC."""
+        import scipy.sparse
+        A = scipy.sparse.csc_matrix(A_csc)
+        indptr = np.ascontiguousarray(A.indptr, dtype=np.int32)
+        indices = np.ascontiguousarray(A.indices, dtype=np.int32)
+        values = np.ascontiguousarray(A.data, dtype=np.float64)
+        h, w = A.shape
+        rowwise = 0 if dim == "columnwise" else 1
+        ncols_out = w if not rowwise else self.S
+        oi = np.zeros(ncols_out + 1, dtype=np.int32)
+        ox = np.zeros(max(1, len(indices)), dtype=np.int32)
+        ov = np.zeros(max(1, len(indices)), dtype=np.float64)
+        nnz = lib().sko_hash_apply_csc_sparse(_p(indptr), _p(indices), _p(values), _sz(h), _sz(w),
+                                              _int(rowwise), _p(self.row_idx), _p(self.row_value),
+                                              _sz(self.S), _p(oi), _p(ox), _p(ov))
+        shape = (self.S, w) if not rowwise else (h, self.S)
+        return scipy.sparse.csc_matrix((ov[:nnz], ox[:nnz], oi), shape=shape)
 
     def explicit(self):
         """The S x N matrix Pi (one nonzero per column)."""

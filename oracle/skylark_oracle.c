@@ -333,6 +333,66 @@ void sko_hash_apply_csc_rowwise(const int32_t *indptr, const int32_t *indices,
     }
 }
 
+/* hash_transform_t<sparse_matrix_t,sparse_matrix_t>::apply_impl
+ * (sketch/hash_transform_local_sparse.hpp:88-223), both directions.  Output arrays must hold
+ * nnz(A) entries; returns the number of stored entries.  Rows inside an output column appear in
+ * first-touch order and cancelled sums stay stored, as in the reference. */
+size_t sko_hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices,
+                                 const double *values, size_t h, size_t w, int rowwise,
+                                 const uint64_t *row_idx, const double *row_value, size_t S,
+                                 int32_t *out_indptr, int32_t *out_indices, double *out_values) {
+    size_t nnz = 0;
+    out_indptr[0] = 0;
+    if (!rowwise) {
+        long *idx_map = (long *)malloc(S * sizeof(long));
+        for (size_t i = 0; i < S; i++) idx_map[i] = -1;
+        for (size_t col = 0; col < w; col++) {
+            for (int32_t idx = indptr[col]; idx < indptr[col + 1]; idx++) {
+                size_t row = (size_t)indices[idx];
+                double val = values[idx] * row_value[row];
+                row = (size_t)row_idx[row];
+                if (idx_map[row] == -1) {
+                    idx_map[row] = (long)nnz; out_indices[nnz] = (int32_t)row; out_values[nnz] = val; nnz++;
+                } else {
+                    out_values[idx_map[row]] += val;
+                }
+            }
+            out_indptr[col + 1] = (int32_t)nnz;
+            for (size_t i = (size_t)out_indptr[col]; i < nnz; i++) idx_map[out_indices[i]] = -1;
+        }
+        free(idx_map);
+    } else {
+        /* inv_mapping: input columns of each target column, in ascending order */
+        size_t *cnt = (size_t *)calloc(S + 1, sizeof(size_t));
+        for (size_t c = 0; c < w; c++) cnt[row_idx[c] + 1]++;
+        for (size_t b = 0; b < S; b++) cnt[b + 1] += cnt[b];
+        size_t *fill = (size_t *)malloc(S * sizeof(size_t));
+        size_t *cols = (size_t *)malloc((w ? w : 1) * sizeof(size_t));
+        for (size_t b = 0; b < S; b++) fill[b] = cnt[b];
+        for (size_t c = 0; c < w; c++) cols[fill[row_idx[c]]++] = c;
+        long *idx_map = (long *)malloc((h ? h : 1) * sizeof(long));
+        for (size_t i = 0; i < h; i++) idx_map[i] = -1;
+        for (size_t b = 0; b < S; b++) {
+            for (size_t q = cnt[b]; q < cnt[b + 1]; q++) {
+                size_t col = cols[q];
+                for (int32_t idx = indptr[col]; idx < indptr[col + 1]; idx++) {
+                    size_t row = (size_t)indices[idx];
+                    double val = values[idx] * row_value[col];
+                    if (idx_map[row] == -1) {
+                        idx_map[row] = (long)nnz; out_indices[nnz] = (int32_t)row; out_values[nnz] = val; nnz++;
+                    } else {
+                        out_values[idx_map[row]] += val;
+                    }
+                }
+            }
+            out_indptr[b + 1] = (int32_t)nnz;
+            for (size_t i = (size_t)out_indptr[b]; i < nnz; i++) idx_map[out_indices[i]] = -1;
+        }
+        free(cnt); free(fill); free(cols); free(idx_map);
+    }
+    return nnz;
+}
+
 /* ------------------------------------------------------------------------ */
 /* Dense transforms                                                         */
 /* ------------------------------------------------------------------------ */

@@ -60,22 +60,83 @@ def test_scipy_sparse_input(sk, oracle, T, fmt):
     n, s, d = 3000, 64, 41
     S, O = _pair(sk, oracle, T, n, s)
     A = scipy.sparse.random(n, d, 0.05, format=fmt, random_state=3, dtype=np.float64)
+    order = "F" if fmt == "csc" else "C"
     want = O.apply(A.toarray(), "columnwise")
-    got = S.apply(A, None, "columnwise")
+    got = S.apply(A, np.empty((s, d), order=order), "columnwise")     # sparse in, dense out
     assert isinstance(got, np.ndarray) and got.shape == (s, d)
     assert rel_fro(got, want) < TOL
     B = scipy.sparse.random(d, n, 0.05, format=fmt, random_state=4, dtype=np.float64)
-    assert rel_fro(S.apply(B, None, "rowwise"), O.apply(B.toarray(), "rowwise")) < TOL
+    assert rel_fro(S.apply(B, np.empty((d, s), order=order), "rowwise"),
+                   O.apply(B.toarray(), "rowwise")) < TOL
     # empty matrix and empty columns
     E = scipy.sparse.csc_matrix((n, 5)) if fmt == "csc" else scipy.sparse.csr_matrix((n, 5))
-    assert np.count_nonzero(S.apply(E, None, 0)) == 0
+    assert np.count_nonzero(S.apply(E, np.empty((s, 5), order=order), 0)) == 0
+
+
+def _canon(M):
+    M = scipy.sparse.csc_matrix(M).copy()
+    M.sort_indices()
+    return M
+
+
+@pytest.mark.parametrize("fmt", ["csc", "csr"])
+@pytest.mark.parametrize("T", ["CWT", "MMT", "WZT"])
+@pytest.mark.parametrize("shape", [(3000, 64, 41, 0.05), (500, 3, 200, 0.3), (40, 1, 7, 0.9),
+                                   (2000, 5000, 30, 0.02)])
+def test_scipy_sparse_to_sparse_is_the_reference_result(sk, oracle, T, fmt, shape):
+    # sparse -> sparse is the default for scipy inputs, as in the reference (lib.py:257-266).
+    # Entries of one output slot are added in input order on both sides, so values are
+    # compared exactly (CWT) / to the 2-ulp value tolerance (MMT, WZT); the stored pattern,
+    # including sums that cancel to zero, is identical after sorting rows inside columns.
+    n, s, d, dens = shape
+    S, O = _pair(sk, oracle, T, n, s)
+    A = scipy.sparse.random(n, d, dens, format=fmt, random_state=3, dtype=np.float64)
+    if dens > 0.2:                       # force cancellations: +-1 entries only
+        A.data[:] = 1.0
+    got = S.apply(A, None, "columnwise")
+    assert scipy.sparse.issparse(got) and got.format == fmt and got.shape == (s, d)
+    want = _canon(O.apply_csc_sparse(A, "columnwise"))
+    g = _canon(got)
+    assert np.array_equal(g.indptr, want.indptr) and np.array_equal(g.indices, want.indices)
+    if T == "CWT":
+        assert np.array_equal(g.data, want.data)
+    else:
+        assert np.allclose(g.data, want.data, rtol=1e-13, atol=1e-13 * np.abs(want.data).max())
+    B = scipy.sparse.random(d, n, dens, format=fmt, random_state=4, dtype=np.float64)
+    got = S.apply(B, None, "rowwise")
+    assert got.format == fmt and got.shape == (d, s)
+    want = _canon(O.apply_csc_sparse(B, "rowwise"))
+    g = _canon(got)
+    assert np.array_equal(g.indptr, want.indptr) and np.array_equal(g.indices, want.indices)
+    if T == "CWT":
+        assert np.array_equal(g.data, want.data)
+    else:
+        assert np.allclose(g.data, want.data, rtol=1e-13, atol=1e-13 * np.abs(want.data).max())
+    # operators and an all-zero input
+    assert rel_fro((S * A).toarray(), O.apply(A.toarray(), "columnwise")) < TOL
+    E = scipy.sparse.csc_matrix((n, 5)) if fmt == "csc" else scipy.sparse.csr_matrix((n, 5))
+    Z = S.apply(E, None, 0)
+    assert Z.shape == (s, 5) and Z.nnz == 0
+    # a preallocated sparse SA is overwritten in place
+    out = scipy.sparse.csc_matrix((s, d)) if fmt == "csc" else scipy.sparse.csr_matrix((s, d))
+    ret = S.apply(A, out, 0)
+    assert ret is out and rel_fro(out.toarray(), O.apply(A.toarray(), "columnwise")) < TOL
+
+
+def test_sparse_to_sparse_rejects_other_transforms(sk):
+    from libskylark_b200 import errors
+    A = scipy.sparse.random(100, 5, 0.1, format="csc", dtype=np.float64)
+    with pytest.raises(errors.UnsupportedError):
+        sk.JLT(100, 10).apply(A, None, 0)
+    with pytest.raises(errors.UnsupportedError):      # dense in, sparse out
+        sk.CWT(100, 10).apply(np.zeros((100, 5), order="F"), scipy.sparse.csc_matrix((10, 5)), 0)
 
 
 def test_sparse_large_sketch_uses_global_path(sk, oracle):
     n, s, d = 2000, 40000, 9           # S*8 > shared memory
     S, O = _pair(sk, oracle, "CWT", n, s)
     A = scipy.sparse.random(n, d, 0.1, format="csc", random_state=5, dtype=np.float64)
-    assert rel_fro(S.apply(A, None, 0), O.apply(A.toarray(), "columnwise")) < TOL
+    assert rel_fro(S.apply(A, np.empty((s, d), order="F"), 0), O.apply(A.toarray(), "columnwise")) < TOL
 
 
 def test_torch_tensors_and_views(sk, oracle):
@@ -113,6 +174,15 @@ def test_device_csc(sk, oracle):
     got = S.apply(dev, None, "columnwise")
     assert got.shape == (s, d) and got.stride(0) == 1
     assert rel_fro(got.cpu().numpy(), O.apply(A.toarray(), "columnwise")) < TOL
+    # device sparse -> device sparse
+    out = S.apply(dev, lib.DeviceCSC.empty((s, d)), "columnwise")
+    assert out.values.is_cuda and out.shape == (s, d)
+    want = _canon(O.apply_csc_sparse(A, "columnwise"))
+    g = out.to_scipy()
+    assert np.array_equal(g.indptr, want.indptr) and np.array_equal(g.indices, want.indices)
+    assert np.allclose(g.data, want.data, rtol=1e-13, atol=1e-13 * np.abs(want.data).max())
+    S2 = sk.MMT(n, s, context=lib.Context(11), defouttype="DeviceSpMatrix")
+    assert np.array_equal(S2.apply(dev, None, 0).to_scipy().indices, want.indices)
 
 
 def test_config1_full_size_parity_and_properties(sk, oracle):
