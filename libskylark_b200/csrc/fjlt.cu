@@ -91,169 +91,217 @@ k_fjlt_direct(const double *__restrict__ X, size_t sk, size_t sj, size_t N, size
 
 // ---------------------------------------------------------------------------
 // WHT mode, N = 2^p >= 8192, every column contiguous (K7).
-// H_N = H_{N/SEG} (x) H_SEG in natural order, so a column is streamed ONCE through shared
-// memory in SEG = 8192-element segments (64 KB, double buffered with cp.async): each
-// segment gets its 13 butterfly levels on chip (4 in registers, 5 by warp shuffle, 4 after
-// one shared-memory exchange) and only the S sampled outputs are kept: sample r = (k1, k2)
-// accumulates (-1)^popc(k1 & n1) * seg[k2] over the segments n1, in registers.  HBM
-// traffic is exactly the algorithmic n*d*8 + s*d*8 bytes; no scratch, no atomics.
+// H_N = H_{N/SEG} (x) H_SEG in natural order, so a column is streamed ONCE in SEG = 8192-element
+// segments (64 KB) and only the S sampled outputs are kept: sample r = (k1, k2) accumulates
+// (-1)^popc(k1 & n1) * H_SEG(seg_n1)[k2] over the segments n1, in registers.  HBM traffic is the
+// algorithmic n*d*8 + s*d*8 bytes; no scratch, no atomics.
+//
+// One CTA per SM, two roles (warp specialised, named barriers):
+//  * 4 butterfly warps: thread t loads its 64 values of a segment straight from global memory
+//    into registers (32 coalesced 16-byte loads: index bits {0, 8..12}), flips signs from a
+//    per-thread 64-bit word of D, does 6 butterfly levels in registers, exchanges through
+//    shared memory ONCE, does the 6 levels of index bits 1..6 and leaves the segment in shared
+//    memory.  12 of the 13 levels cost two shared-memory passes in total.
+//  * 8 gather warps hold the S sample accumulators (32 per thread).  Per segment each sample
+//    reads two values (the level of index bit 7 is folded in here), applies the cross-segment
+//    sign and adds.  They work on segment i while the butterfly warps are already loading
+//    and transforming segment i+1 (two shared buffers), and one of them keeps an L2 prefetch
+//    two segments ahead of the butterfly warps' loads.
 // ---------------------------------------------------------------------------
-static constexpr int WSEG_LOG = 13, WSEG = 1 << WSEG_LOG, WTHREADS = 512, WSPT = 16;
-static constexpr int WFOLD = 9;      // index bit whose butterfly level is folded into the gather
+static constexpr int WSEG_LOG = 13, WSEG = 1 << WSEG_LOG;
+static constexpr int WB_THREADS = 128, WG_THREADS = 256, WTHREADS = WB_THREADS + WG_THREADS;
+static constexpr int WSPT = 32;      // sample slots per gather thread (WG_THREADS * WSPT = 8192 per pass)
+static constexpr int WFOLD = 7;      // index bit whose butterfly level is folded into the gather
+static constexpr int WBUF_BYTES = WSEG * 8;
+enum { WBAR_FULL = 1, WBAR_EMPTY = 3, WBAR_INNER = 5 };   // FULL/EMPTY use two ids each (buffer 0/1)
 
-__device__ __forceinline__ void cp_async16(void *smem, const void *g) {
-    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(g));
+// Segment element e lives at shared word swz(e): index bits 7..9 are XORed into bits 1..3.  The
+// exchange store (16-byte pairs, consecutive lanes), the phase-B accesses (a half warp varies
+// index bits {0, 7, 8, 9}) and the gather (slots arranged by the host) are all conflict-free.
+__host__ __device__ __forceinline__ int swz(int e) { return e ^ (((e >> 7) & 7) << 1); }
+
+__device__ __forceinline__ void bar_sync(int id, int n) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
 }
-__device__ __forceinline__ void cp_async8(void *smem, const void *g) {
-    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(g));
+__device__ __forceinline__ void bar_arrive(int id, int n) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+__device__ __forceinline__ double2 ldg_stream2(const double *p) {
+    double2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ double ldg_stream1(const double *p) {
+    double v;
+    asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts_f64(unsigned addr, double v) {
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+__device__ __forceinline__ void sts_v2f64(unsigned addr, double a, double b) {
+    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(a), "d"(b) : "memory");
+}
+__device__ __forceinline__ double xor_sign(double x, unsigned mask) {   // mask = 0 or 0x80000000
+    return __hiloint2double(__double2hiint(x) ^ (int)mask, __double2loint(x));
 }
 
-// Segment element e lives at shared word swz(e): index bits 5..8 are XORed into bits 1..4, which
-// makes all three register phases below conflict-free (they keep index bits {0,10,11,12},
-// {1..4} and {5..8} per thread); bit 0 is untouched, so 16-byte pairs stay pairs.
-__device__ __forceinline__ int swz(int e) { return e ^ (((e >> 5) & 15) << 1); }
-
-__device__ __forceinline__ void wht16(double *v) {      // 4 butterfly levels over 16 registers
+__device__ __forceinline__ void wht64(double (&v)[64]) {      // 6 butterfly levels over 64 registers
 #pragma unroll
-    for (int h = 1; h < 16; h <<= 1)
+    for (int h = 1; h < 64; h <<= 1)
 #pragma unroll
-        for (int i = 0; i < 16; i++)
+        for (int i = 0; i < 64; i++)
             if (!(i & h)) { double a = v[i], b = v[i + h]; v[i] = a + b; v[i + h] = a - b; }
 }
 
-__device__ __forceinline__ double flip_sign(double x, unsigned neg) {   // neg in {0, 1}
-    return __hiloint2double(__double2hiint(x) ^ (int)(neg << 31), __double2loint(x));
+// Per-thread sign words of the butterfly warps: bit (2*j + b) of Dwht[seg*128 + t] is the sign
+// bit of D at element seg*8192 + j*256 + t*2 + b.
+__global__ void k_wht_sign_words(const uint32_t *__restrict__ Dbits, size_t nwords, uint64_t *__restrict__ Dwht) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nwords) return;
+    const size_t seg = i >> 7; const int t = (int)(i & 127);
+    uint64_t w = 0;
+    for (int j = 0; j < 32; j++) {
+        const size_t e = (seg << WSEG_LOG) + (size_t)j * 256 + (size_t)t * 2;
+        const uint64_t two = (Dbits[e >> 5] >> (e & 31)) & 3u;
+        w |= two << (2 * j);
+    }
+    Dwht[i] = w;
 }
 
 template <bool AL16>
 __global__ void __launch_bounds__(WTHREADS, 1)
 k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
-                const uint32_t *__restrict__ Dbits, const int32_t *__restrict__ slot_sample,
+                const uint64_t *__restrict__ Dwht, const int32_t *__restrict__ slot_sample,
                 const int32_t *__restrict__ slot_out, size_t seg0, double inscale, double outscale,
                 double *__restrict__ OUT, size_t oi, size_t oj) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double *buf0 = reinterpret_cast<double *>(smem_raw);
-    double *buf1 = buf0 + WSEG;
-    int32_t *smp = reinterpret_cast<int32_t *>(buf1 + WSEG);      // [WTHREADS * WSPT]
+    const unsigned sbase = (unsigned)__cvta_generic_to_shared(smem_raw);
     const int tid = threadIdx.x;
     const size_t nseg = N >> WSEG_LOG;      // segments present in X (a row shard starts at seg0)
+    const size_t ncols = (m - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    const size_t total = ncols * nseg;      // (column, segment) items of this CTA, in order
 
-    // slot tables (fjlt_build_wht_slots): sample r = k1 * 8192 + k2 packed as (k1 << 16) | k2,
-    // bit 31 set = empty slot; slots are ordered so that the 16 lanes of a half warp read 16
-    // different bank pairs in the gather below.
-    for (int q = 0; q < WSPT; q++) smp[q * WTHREADS + tid] = slot_sample[q * WTHREADS + tid];
-    __syncthreads();
-
-    auto prefetch = [&](const double *col, size_t seg, double *dst) {
-        const double *g = col + (seg << WSEG_LOG);
-        if (AL16) {
+    if (tid < WB_THREADS) {
+        // ================= butterfly warps =================
+        const int t = tid;
+        // exchange store: element pair e = j*256 + t*2 -> swz(e) = j*256 + ((t*2) ^ (c << 1)),
+        // c = index bits 7..9 = (t >> 6) | ((j & 3) << 1)
+        unsigned offA[4];
 #pragma unroll
-            for (int c = 0; c < WSEG / 2 / WTHREADS; c++) {
-                int e = (c * WTHREADS + tid) * 2;
-                cp_async16(dst + swz(e), g + e);
-            }
-        } else {
+        for (int c = 0; c < 4; c++) offA[c] = (unsigned)(((t * 2) ^ ((((t >> 6) & 1) | (c << 1)) << 1)) * 8);
+        // phase B: thread = (index bit 0, index bits 7..12), registers = index bits 1..6
+        const int b0 = t & 1, hi = t >> 1, h3 = hi & 7;
+        unsigned offB[8];
 #pragma unroll
-            for (int c = 0; c < WSEG / WTHREADS; c++) {
-                int e = c * WTHREADS + tid;
-                cp_async8(dst + swz(e), g + e);
+        for (int rl = 0; rl < 8; rl++) offB[rl] = (unsigned)((hi * 128 + b0 + ((rl ^ h3) << 1)) * 8);
+        size_t it = 0;
+        for (size_t j = blockIdx.x; j < m; j += gridDim.x) {
+            const double *col = X + j * ldx;
+            for (size_t n1 = 0; n1 < nseg; n1++, it++) {
+                const double *g = col + (n1 << WSEG_LOG) + t * 2;
+                const uint64_t w = Dwht[((seg0 + n1) << 7) + t];
+                double v[64];
+#pragma unroll
+                for (int jj = 0; jj < 32; jj++) {
+                    if (AL16) {
+                        double2 x = ldg_stream2(g + jj * 256);
+                        v[2 * jj] = x.x; v[2 * jj + 1] = x.y;
+                    } else {
+                        v[2 * jj] = ldg_stream1(g + jj * 256);
+                        v[2 * jj + 1] = ldg_stream1(g + jj * 256 + 1);
+                    }
+                }
+                const unsigned wlo = (unsigned)w, whi = (unsigned)(w >> 32);
+#pragma unroll
+                for (int i = 0; i < 32; i++) {
+                    v[i] = xor_sign(v[i], (wlo << (31 - i)) & 0x80000000u);
+                    v[32 + i] = xor_sign(v[32 + i], (whi << (31 - i)) & 0x80000000u);
+                }
+                wht64(v);                                   // index bits {0, 8..12}
+                const int b = (int)(it & 1);
+                const unsigned buf = sbase + (unsigned)b * WBUF_BYTES;
+                if (it >= 2) bar_sync(WBAR_EMPTY + b, WTHREADS);      // gather of item it-2 is done
+#pragma unroll
+                for (int jj = 0; jj < 32; jj++)
+                    sts_v2f64(buf + offA[jj & 3] + jj * 2048, v[2 * jj], v[2 * jj + 1]);
+                bar_sync(WBAR_INNER, WB_THREADS);
+#pragma unroll
+                for (int r = 0; r < 64; r++) v[r] = lds_f64(buf + offB[r & 7] + (r >> 3) * 128);
+                wht64(v);                                   // index bits 1..6
+#pragma unroll
+                for (int r = 0; r < 64; r++) sts_f64(buf + offB[r & 7] + (r >> 3) * 128, v[r]);
+                __threadfence_block();
+                bar_arrive(WBAR_FULL + b, WTHREADS);
             }
         }
-        asm volatile("cp.async.commit_group;");
-    };
-
-    // The two scale factors commute with the transform; they are applied once to the sampled sums.
-    const double scale = inscale * outscale;
-
-    for (size_t j = blockIdx.x; j < m; j += gridDim.x) {
-        const double *col = X + j * ldx;
-        double acc[WSPT];
+    } else {
+        // ================= gather warps =================
+        const int g = tid - WB_THREADS;
+        // slot tables (fjlt_build_wht_slots): bits 0..15 byte offset of the sample's first value,
+        // bits 16..30 k1, bit 31 the sign of the folded level; empty slots read slot 0 and are
+        // never written out.
+        int p[WSPT];
 #pragma unroll
-        for (int q = 0; q < WSPT; q++) acc[q] = 0.0;
-        prefetch(col, 0, buf0);
-        for (size_t n1 = 0; n1 < nseg; n1++) {
-            double *buf = (n1 & 1) ? buf1 : buf0;
-            if (n1 + 1 < nseg) {
-                prefetch(col, n1 + 1, (n1 & 1) ? buf0 : buf1);
-                asm volatile("cp.async.wait_group 1;");
-            } else {
-                asm volatile("cp.async.wait_group 0;");
+        for (int q = 0; q < WSPT; q++) p[q] = slot_sample[q * WG_THREADS + g];
+        const double scale = inscale * outscale;   // both commute with the transform
+        size_t it = 0;
+        for (size_t j = blockIdx.x; j < m; j += gridDim.x) {
+            double acc[WSPT];
+#pragma unroll
+            for (int q = 0; q < WSPT; q++) acc[q] = 0.0;
+            for (size_t n1 = 0; n1 < nseg; n1++, it++) {
+                if (AL16 && g == 0) {           // keep L2 two items ahead of the butterfly warps
+                    size_t jp = j, np = n1 + 2;
+                    while (np >= nseg) { np -= nseg; jp += gridDim.x; }
+                    if (jp < m) {
+                        const double *nx = X + jp * ldx + (np << WSEG_LOG);
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nx), "r"(WBUF_BYTES));
+                    }
+                }
+                const int b = (int)(it & 1);
+                const unsigned buf = sbase + (unsigned)b * WBUF_BYTES;
+                const unsigned n1g = (unsigned)(seg0 + n1);
+                bar_sync(WBAR_FULL + b, WTHREADS);
+#pragma unroll
+                for (int q = 0; q < WSPT; q++) {
+                    const unsigned a0 = (unsigned)p[q] & 0xFFFFu;
+                    const double lo = lds_f64(buf + a0), hi = lds_f64(buf + (a0 ^ 1040u));
+                    const double y = lo + xor_sign(hi, (unsigned)p[q] & 0x80000000u);
+                    const unsigned par = (unsigned)__popc(((unsigned)p[q] >> 16) & n1g) << 31;
+                    acc[q] += xor_sign(y, par);
+                }
+                if (it + 2 < total) bar_arrive(WBAR_EMPTY + b, WTHREADS);
             }
-            __syncthreads();
-            double v[16];
-            // ---- phase A: e = c*1024 + tid*2 + b; registers hold index bits {0, 10, 11, 12}
-#pragma unroll
-            for (int c = 0; c < 8; c++) {
-                double2 x = *reinterpret_cast<const double2 *>(buf + swz(c * 1024 + tid * 2));
-                const uint32_t w = Dbits[((seg0 + n1) << (WSEG_LOG - 5)) + c * 32 + (tid >> 4)] >> ((tid & 15) * 2);
-                v[2 * c] = flip_sign(x.x, w & 1);
-                v[2 * c + 1] = flip_sign(x.y, (w >> 1) & 1);
-            }
-            wht16(v);
-#pragma unroll
-            for (int c = 0; c < 8; c++) {
-                double2 x; x.x = v[2 * c]; x.y = v[2 * c + 1];
-                *reinterpret_cast<double2 *>(buf + swz(c * 1024 + tid * 2)) = x;
-            }
-            __syncthreads();
-            // ---- phase B: registers hold index bits 1..4; thread = (bit 0, bits 5..12)
-            {
-                const int u = (tid >> 1) & 15;                       // index bits 5..8
-                const int base = (tid & 1) + ((tid >> 1) << 5);
-#pragma unroll
-                for (int r = 0; r < 16; r++) v[r] = buf[base + ((r ^ u) << 1)];
-                wht16(v);
-#pragma unroll
-                for (int r = 0; r < 16; r++) buf[base + ((r ^ u) << 1)] = v[r];
-            }
-            __syncthreads();
-            // ---- phase C: registers hold index bits 5..8; thread = (bits 0..4, bits 9..12)
-            {
-                const int base = (tid & 31) + ((tid >> 5) << 9);
-#pragma unroll
-                for (int r = 0; r < 16; r++) v[r] = buf[(base ^ (r << 1)) + (r << 5)];
-                wht16(v);
-#pragma unroll
-                for (int r = 0; r < 16; r++) buf[(base ^ (r << 1)) + (r << 5)] = v[r];
-            }
-            __syncthreads();
-            // ---- sampled accumulate; the level of index bit 9 is done here, on two reads
 #pragma unroll
             for (int q = 0; q < WSPT; q++) {
-                const int p = smp[q * WTHREADS + tid];
-                const int k2 = p & (WSEG - 1);
-                const double lo = buf[swz(k2 & ~(1 << WFOLD))], hi = buf[swz(k2 | (1 << WFOLD))];
-                const unsigned par = __popc((unsigned)(p >> 16) & (unsigned)(seg0 + n1)) & 1;
-                const double y = lo + flip_sign(hi, (k2 >> WFOLD) & 1);
-                if (p >= 0) acc[q] += flip_sign(y, par);
+                const int i = slot_out[q * WG_THREADS + g];
+                if (i >= 0) OUT[(size_t)i * oi + j * oj] = scale * acc[q];
             }
-            __syncthreads();          // buf may be overwritten by the prefetch two segments on
-        }
-#pragma unroll
-        for (int q = 0; q < WSPT; q++) {
-            const int i = slot_out[q * WTHREADS + tid];
-            if (i >= 0) OUT[(size_t)i * oi + j * oj] = scale * acc[q];
         }
     }
 }
 
 // Host side of the gather layout: distributes the samples of one pass (<= 8192) over the
-// [WSPT][WTHREADS] slots so that each aligned group of 16 slots (= the lanes of a half warp in
+// [WSPT][WG_THREADS] slots so that each aligned group of 16 slots (= the lanes of a half warp in
 // one gather step) holds samples from 16 different shared-memory bank pairs wherever the
-// sample set allows it.  slot_sample / slot_out get npasses * WSPT * WTHREADS entries.
+// sample set allows it.  slot_sample / slot_out get npasses * WSPT * WG_THREADS entries.
 void fjlt_build_wht_slots(const int32_t *samples, size_t S, std::vector<int32_t> &slot_sample,
                           std::vector<int32_t> &slot_out) {
-    const size_t per_pass = (size_t)WTHREADS * WSPT;
+    const size_t per_pass = (size_t)WG_THREADS * WSPT;
     const size_t npass = S == 0 ? 0 : (S + per_pass - 1) / per_pass;
-    slot_sample.assign(npass * per_pass, (int32_t)0x80000000);
+    slot_sample.assign(npass * per_pass, 0);
     slot_out.assign(npass * per_pass, -1);
-    auto host_swz = [](int e) { return e ^ (((e >> 5) & 15) << 1); };
+    auto first_word = [](int32_t r) { return swz((r & (WSEG - 1)) & ~(1 << WFOLD)); };
     for (size_t p = 0; p < npass; p++) {
         const size_t s0 = p * per_pass, s1 = std::min(S, s0 + per_pass);
         std::vector<std::vector<int32_t>> q(16);
-        for (size_t i = s0; i < s1; i++) q[host_swz(samples[i] & (WSEG - 1)) & 15].push_back((int32_t)i);
+        for (size_t i = s0; i < s1; i++) q[first_word(samples[i]) & 15].push_back((int32_t)i);
         std::vector<int32_t> leftovers;
         int32_t *ss = slot_sample.data() + p * per_pass, *so = slot_out.data() + p * per_pass;
         const size_t ngroups = per_pass / 16;
@@ -268,7 +316,8 @@ void fjlt_build_wht_slots(const int32_t *samples, size_t S, std::vector<int32_t>
         for (size_t t = 0; t < per_pass; t++)
             if (so[t] >= 0) {
                 const int32_t r = samples[so[t]];
-                ss[t] = ((r >> WSEG_LOG) << 16) | (r & (WSEG - 1));
+                const uint32_t k1 = (uint32_t)(r >> WSEG_LOG), fold = ((uint32_t)r >> WFOLD) & 1u;
+                ss[t] = (int32_t)((fold << 31) | (k1 << 16) | (uint32_t)(first_word(r) * 8));
             }
     }
 }
@@ -697,7 +746,8 @@ size_t fjlt_workspace_bytes(size_t N, size_t m, int fut, bool layout_rows, size_
         return (layout_rows ? N * m * sizeof(double) : 0) + dct_batch_cols(N, m) * N * sizeof(double) +
                dct_table_bytes(N, S) + 1024;
     if (fut == FUT_DCT) return 4 * N * sizeof(double) + 256;
-    if (wht_fast_ok(N) && layout_rows) return N * m * sizeof(double) + 256;   // transposed copy
+    if (fut == FUT_WHT && wht_fast_ok(N))         // sign words (+ transposed copy)
+        return (layout_rows ? (N * m * sizeof(double) + 255) / 256 * 256 : 0) + N / 8 + 256;
     return 256;
 }
 
@@ -813,25 +863,34 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
     if (fut == FUT_WHT && wht_fast_ok(N)) {
         const double *Xc = X;
         size_t ldc = ldx;
+        char *ws = reinterpret_cast<char *>(workspace);
         if (layout_rows) {      // the reference also transposes for this direction
-            double *T = reinterpret_cast<double *>(workspace);
+            double *T = reinterpret_cast<double *>(ws);
+            ws += (nloc * m * sizeof(double) + 255) / 256 * 256;
             LaunchScope ls(KC_FJLT, st);
             dim3 grid((unsigned)((m + 31) / 32), (unsigned)((nloc + 31) / 32));
             k_transpose_to_cols<<<grid, dim3(32, 8), 0, st>>>(X, ldx, nloc, m, T);
             SKB_CUDA(cudaGetLastError());
             Xc = T; ldc = nloc;
         }
+        uint64_t *Dwht = reinterpret_cast<uint64_t *>(ws);      // N/64 words, rebuilt per apply (~2 us)
+        {
+            LaunchScope ls(KC_FJLT, st);
+            const size_t nwords = N >> 6;
+            k_wht_sign_words<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(Dbits, nwords, Dwht);
+            SKB_CUDA(cudaGetLastError());
+        }
         const size_t oi = layout_rows ? ldo : 1, oj = layout_rows ? 1 : ldo;
         const double inscale = 1.0 / sqrt((double)N), outscale = sqrt((double)N / (double)S);
-        const size_t smem = 2 * WSEG * sizeof(double) + (size_t)WTHREADS * WSPT * sizeof(int32_t);
+        const size_t smem = 2 * (size_t)WBUF_BYTES;
         const bool al16 = (ldc % 2 == 0) && ((uintptr_t)Xc % 16 == 0);
         auto kern = al16 ? k_fjlt_wht_cols<true> : k_fjlt_wht_cols<false>;
         SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         unsigned grid = (unsigned)(m < 148 ? m : 148);
-        const size_t per_pass = (size_t)WTHREADS * WSPT;                 // 8192 samples per pass
+        const size_t per_pass = (size_t)WG_THREADS * WSPT;               // 8192 samples per pass
         for (size_t s0 = 0, p = 0; s0 < S; s0 += per_pass, p++) {
             LaunchScope ls(KC_FJLT, st);
-            kern<<<grid, WTHREADS, smem, st>>>(Xc, ldc, nloc, m, Dbits, wht_slot_sample + p * per_pass,
+            kern<<<grid, WTHREADS, smem, st>>>(Xc, ldc, nloc, m, Dwht, wht_slot_sample + p * per_pass,
                                                wht_slot_out + p * per_pass, offset >> WSEG_LOG,
                                                inscale, outscale, OUT, oi, oj);
             SKB_CUDA(cudaGetLastError());
