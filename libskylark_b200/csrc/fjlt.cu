@@ -99,26 +99,30 @@ k_fjlt_direct(const double *__restrict__ X, size_t sk, size_t sj, size_t N, size
 // One CTA per SM, two roles (warp specialised, named barriers):
 //  * 4 butterfly warps: thread t loads its 64 values of a segment straight from global memory
 //    into registers (32 coalesced 16-byte loads: index bits {0, 8..12}), flips signs from a
-//    per-thread 64-bit word of D, does 6 butterfly levels in registers, exchanges through
-//    shared memory ONCE, does the 6 levels of index bits 1..6 and leaves the segment in shared
-//    memory.  12 of the 13 levels cost two shared-memory passes in total.
+//    per-thread 64-bit word of D, does 6 butterfly levels in registers and the level of index
+//    bit 1 with its neighbour lane (shuffle), exchanges through shared memory ONCE, does the 6
+//    levels of index bits 2..7 and leaves the segment in shared memory.  Two groups of 4 warps
+//    take alternate segments, so one computes while the other waits for its loads.
 //  * 8 gather warps hold the S sample accumulators (32 per thread).  Per segment each sample
-//    reads two values (the level of index bit 7 is folded in here), applies the cross-segment
-//    sign and adds.  They work on segment i while the butterfly warps are already loading
-//    and transforming segment i+1 (two shared buffers), and one of them keeps an L2 prefetch
-//    two segments ahead of the butterfly warps' loads.
+//    reads its value, applies the cross-segment sign and adds.  They work on segment i while
+//    the butterfly warps are already on segments i+1 and i+2 (ring of three shared buffers),
+//    and one of them keeps an L2 prefetch ahead of the butterfly warps' loads.
+//  Registers are split with setmaxnreg: 168 per butterfly thread, 88 per gather thread.
 // ---------------------------------------------------------------------------
 static constexpr int WSEG_LOG = 13, WSEG = 1 << WSEG_LOG;
-static constexpr int WB_THREADS = 128, WG_THREADS = 256, WTHREADS = WB_THREADS + WG_THREADS;
+static constexpr int WB_THREADS = 128;               // one butterfly group (there are two)
+static constexpr int WG_THREADS = 256, WTHREADS = 2 * WB_THREADS + WG_THREADS;
 static constexpr int WSPT = 32;      // sample slots per gather thread (WG_THREADS * WSPT = 8192 per pass)
-static constexpr int WFOLD = 7;      // index bit whose butterfly level is folded into the gather
-static constexpr int WBUF_BYTES = WSEG * 8;
-enum { WBAR_FULL = 1, WBAR_EMPTY = 3, WBAR_INNER = 5 };   // FULL/EMPTY use two ids each (buffer 0/1)
+static constexpr int WBUF_BYTES = WSEG * 8, WNBUF = 3;
+static constexpr int WSMEM_BYTES = WNBUF * WBUF_BYTES + WG_THREADS * WSPT * 4;
+// named barriers: FULL/EMPTY one id per ring buffer, INNER one per butterfly group
+enum { WBAR_FULL = 1, WBAR_EMPTY = 4, WBAR_INNER = 7 };
+static constexpr int WREG_B = 168, WREG_G = 88;      // 256*168 + 256*88 = the whole register file
 
-// Segment element e lives at shared word swz(e): index bits 7..9 are XORed into bits 1..3.  The
+// Segment element e lives at shared word swz(e): index bits 8..9 are XORed into bits 2..3.  The
 // exchange store (16-byte pairs, consecutive lanes), the phase-B accesses (a half warp varies
-// index bits {0, 7, 8, 9}) and the gather (slots arranged by the host) are all conflict-free.
-__host__ __device__ __forceinline__ int swz(int e) { return e ^ (((e >> 7) & 7) << 1); }
+// index bits {0, 1, 8, 9}) and the gather (slots arranged by the host) are all conflict-free.
+__host__ __device__ __forceinline__ int swz(int e) { return e ^ (((e >> 8) & 3) << 2); }
 
 __device__ __forceinline__ void bar_sync(int id, int n) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
@@ -185,25 +189,30 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
     const int tid = threadIdx.x;
     const size_t nseg = N >> WSEG_LOG;      // segments present in X (a row shard starts at seg0)
     const size_t ncols = (m - blockIdx.x + gridDim.x - 1) / gridDim.x;
-    const size_t total = ncols * nseg;      // (column, segment) items of this CTA, in order
+    const size_t total = ncols * nseg;      // (column, segment) items of this CTA, in order;
+                                            // item it lives in ring buffer it % 3
 
-    if (tid < WB_THREADS) {
-        // ================= butterfly warps =================
-        const int t = tid;
-        // exchange store: element pair e = j*256 + t*2 -> swz(e) = j*256 + ((t*2) ^ (c << 1)),
-        // c = index bits 7..9 = (t >> 6) | ((j & 3) << 1)
+    if (tid < 2 * WB_THREADS) {
+        // ================= butterfly warps: group s takes the items with it % 2 == s =================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(WREG_B));
+        const int s = tid >> 7, t = tid & (WB_THREADS - 1);
+        // exchange store: element pair e = j*256 + t*2 -> swz(e) = j*256 + ((t*2) ^ (c << 2)),
+        // c = index bits 8..9 = j & 3
         unsigned offA[4];
 #pragma unroll
-        for (int c = 0; c < 4; c++) offA[c] = (unsigned)(((t * 2) ^ ((((t >> 6) & 1) | (c << 1)) << 1)) * 8);
-        // phase B: thread = (index bit 0, index bits 7..12), registers = index bits 1..6
-        const int b0 = t & 1, hi = t >> 1, h3 = hi & 7;
-        unsigned offB[8];
+        for (int c = 0; c < 4; c++) offA[c] = (unsigned)(((t * 2) ^ (c << 2)) * 8);
+        // phase B: thread = (index bits 0..1, index bits 8..12), registers = index bits 2..7
+        const int lo2 = t & 3, hi = t >> 2, h2 = hi & 3;
+        unsigned offB[4];
 #pragma unroll
-        for (int rl = 0; rl < 8; rl++) offB[rl] = (unsigned)((hi * 128 + b0 + ((rl ^ h3) << 1)) * 8);
+        for (int rl = 0; rl < 4; rl++) offB[rl] = (unsigned)((hi * 256 + lo2 + ((rl ^ h2) << 2)) * 8);
+        const unsigned odd = (unsigned)(t & 1) << 31;     // index bit 1 of this thread's phase-A elements
         size_t it = 0;
+        int b = 0;                                  // it % 3
         for (size_t j = blockIdx.x; j < m; j += gridDim.x) {
             const double *col = X + j * ldx;
-            for (size_t n1 = 0; n1 < nseg; n1++, it++) {
+            for (size_t n1 = 0; n1 < nseg; n1++, it++, b = (b == WNBUF - 1) ? 0 : b + 1) {
+                if ((int)(it & 1) != s) continue;
                 const double *g = col + (n1 << WSEG_LOG) + t * 2;
                 const uint64_t w = Dwht[((seg0 + n1) << 7) + t];
                 double v[64];
@@ -224,59 +233,77 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
                     v[32 + i] = xor_sign(v[32 + i], (whi << (31 - i)) & 0x80000000u);
                 }
                 wht64(v);                                   // index bits {0, 8..12}
-                const int b = (int)(it & 1);
+#pragma unroll
+                for (int i = 0; i < 64; i++) {              // index bit 1: the partner is the next lane
+                    const double o = __shfl_xor_sync(0xffffffffu, v[i], 1);
+                    v[i] = o + xor_sign(v[i], odd);
+                }
                 const unsigned buf = sbase + (unsigned)b * WBUF_BYTES;
-                if (it >= 2) bar_sync(WBAR_EMPTY + b, WTHREADS);      // gather of item it-2 is done
+                if (it >= WNBUF) bar_sync(WBAR_EMPTY + b, WB_THREADS + WG_THREADS);   // gather of item it-3 is done
 #pragma unroll
                 for (int jj = 0; jj < 32; jj++)
                     sts_v2f64(buf + offA[jj & 3] + jj * 2048, v[2 * jj], v[2 * jj + 1]);
-                bar_sync(WBAR_INNER, WB_THREADS);
+                bar_sync(WBAR_INNER + s, WB_THREADS);
 #pragma unroll
-                for (int r = 0; r < 64; r++) v[r] = lds_f64(buf + offB[r & 7] + (r >> 3) * 128);
-                wht64(v);                                   // index bits 1..6
+                for (int r = 0; r < 64; r++) v[r] = lds_f64(buf + offB[r & 3] + (r >> 2) * 128);
+                wht64(v);                                   // index bits 2..7
 #pragma unroll
-                for (int r = 0; r < 64; r++) sts_f64(buf + offB[r & 7] + (r >> 3) * 128, v[r]);
+                for (int r = 0; r < 64; r++) sts_f64(buf + offB[r & 3] + (r >> 2) * 128, v[r]);
                 __threadfence_block();
-                bar_arrive(WBAR_FULL + b, WTHREADS);
+                bar_arrive(WBAR_FULL + b, WB_THREADS + WG_THREADS);
             }
         }
     } else {
         // ================= gather warps =================
-        const int g = tid - WB_THREADS;
-        // slot tables (fjlt_build_wht_slots): bits 0..15 byte offset of the sample's first value,
-        // bits 16..30 k1, bit 31 the sign of the folded level; empty slots read slot 0 and are
-        // never written out.
-        int p[WSPT];
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(WREG_G));
+        const int g = tid - 2 * WB_THREADS;
+        // slot table (fjlt_build_wht_slots): bits 0..15 byte offset of the sample's value, bits
+        // 16..30 k1; empty slots read offset 0 and are never written out.  Kept in shared memory as [WSPT/4][WG_THREADS] int4 (the registers
+        // belong to the accumulators).
+        const unsigned ptab = sbase + WNBUF * WBUF_BYTES + (unsigned)g * 16;
 #pragma unroll
-        for (int q = 0; q < WSPT; q++) p[q] = slot_sample[q * WG_THREADS + g];
+        for (int q4 = 0; q4 < WSPT / 4; q4++) {
+            int4 pp;
+            pp.x = slot_sample[(q4 * 4 + 0) * WG_THREADS + g];
+            pp.y = slot_sample[(q4 * 4 + 1) * WG_THREADS + g];
+            pp.z = slot_sample[(q4 * 4 + 2) * WG_THREADS + g];
+            pp.w = slot_sample[(q4 * 4 + 3) * WG_THREADS + g];
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(ptab + q4 * WG_THREADS * 16),
+                         "r"(pp.x), "r"(pp.y), "r"(pp.z), "r"(pp.w) : "memory");
+        }
         const double scale = inscale * outscale;   // both commute with the transform
         size_t it = 0;
+        int b = 0;
         for (size_t j = blockIdx.x; j < m; j += gridDim.x) {
             double acc[WSPT];
 #pragma unroll
             for (int q = 0; q < WSPT; q++) acc[q] = 0.0;
-            for (size_t n1 = 0; n1 < nseg; n1++, it++) {
-                if (AL16 && g == 0) {           // keep L2 two items ahead of the butterfly warps
-                    size_t jp = j, np = n1 + 2;
+            for (size_t n1 = 0; n1 < nseg; n1++, it++, b = (b == WNBUF - 1) ? 0 : b + 1) {
+                if (AL16 && g == 0) {           // keep L2 ahead of the butterfly warps' loads
+                    size_t jp = j, np = n1 + 4;
                     while (np >= nseg) { np -= nseg; jp += gridDim.x; }
                     if (jp < m) {
                         const double *nx = X + jp * ldx + (np << WSEG_LOG);
                         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nx), "r"(WBUF_BYTES));
                     }
                 }
-                const int b = (int)(it & 1);
                 const unsigned buf = sbase + (unsigned)b * WBUF_BYTES;
                 const unsigned n1g = (unsigned)(seg0 + n1);
-                bar_sync(WBAR_FULL + b, WTHREADS);
+                bar_sync(WBAR_FULL + b, WB_THREADS + WG_THREADS);
 #pragma unroll
-                for (int q = 0; q < WSPT; q++) {
-                    const unsigned a0 = (unsigned)p[q] & 0xFFFFu;
-                    const double lo = lds_f64(buf + a0), hi = lds_f64(buf + (a0 ^ 1040u));
-                    const double y = lo + xor_sign(hi, (unsigned)p[q] & 0x80000000u);
-                    const unsigned par = (unsigned)__popc(((unsigned)p[q] >> 16) & n1g) << 31;
-                    acc[q] += xor_sign(y, par);
+                for (int q4 = 0; q4 < WSPT / 4; q4++) {
+                    int pq[4];
+                    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                                 : "=r"(pq[0]), "=r"(pq[1]), "=r"(pq[2]), "=r"(pq[3])
+                                 : "r"(ptab + q4 * WG_THREADS * 16));
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const double y = lds_f64(buf + ((unsigned)pq[k] & 0xFFFFu));
+                        const unsigned par = (unsigned)__popc(((unsigned)pq[k] >> 16) & n1g) << 31;
+                        acc[q4 * 4 + k] += xor_sign(y, par);
+                    }
                 }
-                if (it + 2 < total) bar_arrive(WBAR_EMPTY + b, WTHREADS);
+                if (it + WNBUF < total) bar_arrive(WBAR_EMPTY + b, WB_THREADS + WG_THREADS);
             }
 #pragma unroll
             for (int q = 0; q < WSPT; q++) {
@@ -297,7 +324,7 @@ void fjlt_build_wht_slots(const int32_t *samples, size_t S, std::vector<int32_t>
     const size_t npass = S == 0 ? 0 : (S + per_pass - 1) / per_pass;
     slot_sample.assign(npass * per_pass, 0);
     slot_out.assign(npass * per_pass, -1);
-    auto first_word = [](int32_t r) { return swz((r & (WSEG - 1)) & ~(1 << WFOLD)); };
+    auto first_word = [](int32_t r) { return swz(r & (WSEG - 1)); };
     for (size_t p = 0; p < npass; p++) {
         const size_t s0 = p * per_pass, s1 = std::min(S, s0 + per_pass);
         std::vector<std::vector<int32_t>> q(16);
@@ -316,8 +343,8 @@ void fjlt_build_wht_slots(const int32_t *samples, size_t S, std::vector<int32_t>
         for (size_t t = 0; t < per_pass; t++)
             if (so[t] >= 0) {
                 const int32_t r = samples[so[t]];
-                const uint32_t k1 = (uint32_t)(r >> WSEG_LOG), fold = ((uint32_t)r >> WFOLD) & 1u;
-                ss[t] = (int32_t)((fold << 31) | (k1 << 16) | (uint32_t)(first_word(r) * 8));
+                const uint32_t k1 = (uint32_t)(r >> WSEG_LOG);
+                ss[t] = (int32_t)((k1 << 16) | (uint32_t)(first_word(r) * 8));
             }
     }
 }
@@ -882,7 +909,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         }
         const size_t oi = layout_rows ? ldo : 1, oj = layout_rows ? 1 : ldo;
         const double inscale = 1.0 / sqrt((double)N), outscale = sqrt((double)N / (double)S);
-        const size_t smem = 2 * (size_t)WBUF_BYTES;
+        const size_t smem = (size_t)WSMEM_BYTES;
         const bool al16 = (ldc % 2 == 0) && ((uintptr_t)Xc % 16 == 0);
         auto kern = al16 ? k_fjlt_wht_cols<true> : k_fjlt_wht_cols<false>;
         SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
