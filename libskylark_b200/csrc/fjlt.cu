@@ -115,9 +115,14 @@ static constexpr int WG_THREADS = 256, WTHREADS = 2 * WB_THREADS + WG_THREADS;
 static constexpr int WSPT = 32;      // sample slots per gather thread (WG_THREADS * WSPT = 8192 per pass)
 static constexpr int WBUF_BYTES = WSEG * 8, WNBUF = 3;
 static constexpr int WSMEM_BYTES = WNBUF * WBUF_BYTES + WG_THREADS * WSPT * 4;
-// named barriers: FULL/EMPTY one id per ring buffer, INNER one per butterfly group
-enum { WBAR_FULL = 1, WBAR_EMPTY = 4, WBAR_INNER = 7 };
+// named barriers: FULL one id per ring buffer; EMPTY one id per (ring buffer, butterfly group
+// that will refill it) -- with a shared id the other group, running ahead, could complete the
+// barrier in place of the group it was meant for; INNER one per butterfly group
+enum { WBAR_FULL = 1, WBAR_EMPTY = 4, WBAR_INNER = 10 };
 static constexpr int WREG_B = 168, WREG_G = 88;      // 256*168 + 256*88 = the whole register file
+#ifndef SKB_WHT_PF
+#define SKB_WHT_PF 4                 // L2 prefetch distance in segments (0 = off)
+#endif
 
 // Segment element e lives at shared word swz(e): index bits 8..9 are XORed into bits 2..3.  The
 // exchange store (16-byte pairs, consecutive lanes), the phase-B accesses (a half warp varies
@@ -239,7 +244,7 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
                     v[i] = o + xor_sign(v[i], odd);
                 }
                 const unsigned buf = sbase + (unsigned)b * WBUF_BYTES;
-                if (it >= WNBUF) bar_sync(WBAR_EMPTY + b, WB_THREADS + WG_THREADS);   // gather of item it-3 is done
+                if (it >= WNBUF) bar_sync(WBAR_EMPTY + 2 * b + s, WB_THREADS + WG_THREADS);   // gather of item it-3 is done
 #pragma unroll
                 for (int jj = 0; jj < 32; jj++)
                     sts_v2f64(buf + offA[jj & 3] + jj * 2048, v[2 * jj], v[2 * jj + 1]);
@@ -279,8 +284,8 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
 #pragma unroll
             for (int q = 0; q < WSPT; q++) acc[q] = 0.0;
             for (size_t n1 = 0; n1 < nseg; n1++, it++, b = (b == WNBUF - 1) ? 0 : b + 1) {
-                if (AL16 && g == 0) {           // keep L2 ahead of the butterfly warps' loads
-                    size_t jp = j, np = n1 + 4;
+                if (AL16 && SKB_WHT_PF > 0 && g == 0) {   // keep L2 ahead of the butterfly warps' loads
+                    size_t jp = j, np = n1 + SKB_WHT_PF;
                     while (np >= nseg) { np -= nseg; jp += gridDim.x; }
                     if (jp < m) {
                         const double *nx = X + jp * ldx + (np << WSEG_LOG);
@@ -303,7 +308,8 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
                         acc[q4 * 4 + k] += xor_sign(y, par);
                     }
                 }
-                if (it + WNBUF < total) bar_arrive(WBAR_EMPTY + b, WB_THREADS + WG_THREADS);
+                if (it + WNBUF < total)           // item it+3 (other parity) refills this buffer
+                    bar_arrive(WBAR_EMPTY + 2 * b + (int)((it + 1) & 1), WB_THREADS + WG_THREADS);
             }
 #pragma unroll
             for (int q = 0; q < WSPT; q++) {

@@ -29,6 +29,29 @@ def test_fjlt_power_of_two(sk, oracle, fut, shape):
     assert rel_fro(S.apply(B, None, "rowwise"), want.T) < TOL
 
 
+@pytest.mark.parametrize("shape", [(8192, 700, 1000), (32768, 9000, 450), (16384, 100, 149)])
+def test_wht_many_columns_per_cta(sk, oracle, shape):
+    # more columns than SMs: every CTA of the streaming kernel walks several columns, so its
+    # ring of shared buffers and both butterfly groups wrap across column boundaries
+    # (n = 8192: one segment per column, the groups alternate columns)
+    from libskylark_b200 import lib
+    n, s, d = shape
+    lib.set_option("fjlt_fut", "wht")
+    try:
+        S = sk.FJLT(n, s, lib.Context(23))
+    finally:
+        lib.set_option("fjlt_fut", "dct")
+    O = oracle.FJLT(n, s, oracle.Context(23))
+    A = np.asfortranarray(np.random.default_rng(8).standard_normal((n, d)))
+    want = O.apply(A, "columnwise", fut="wht")
+    for _ in range(3):            # repeated: the hand-off between warps is timing dependent
+        assert rel_fro(S.apply(A, None, "columnwise"), want) < TOL
+    import torch
+    odd = torch.zeros(d, n + 1, dtype=torch.float64, device="cuda").t()[1:, :]   # columns only 8-byte aligned
+    odd.copy_(torch.from_numpy(A))
+    assert rel_fro(S.apply(odd, None, "columnwise").cpu().numpy(), want) < TOL
+
+
 def test_fjlt_general_n_dct(sk, oracle):
     from libskylark_b200 import lib
     n, s, d = 300, 40, 7
