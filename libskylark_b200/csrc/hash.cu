@@ -295,7 +295,7 @@ void hash_apply_rows(const double *X, size_t ldx, size_t m, const HashPlan &plan
 // A CTA owns CG columns and a slice of the sketched index; it accumulates into a
 // shared S x CG tile and flushes it (atomics only if the index is split).
 // ---------------------------------------------------------------------------
-template <int CG>
+template <int CG, int KU>
 __global__ void __launch_bounds__(256)
 k_hash_cols_smem(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
                  const int32_t *__restrict__ bucket, const double *__restrict__ value,
@@ -308,15 +308,26 @@ k_hash_cols_smem(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
     const size_t per = (n + ksplit - 1) / ksplit;
     const size_t k0 = (size_t)blockIdx.y * per;
     const size_t k1 = min(n, k0 + per);
-    for (size_t k = k0 + threadIdx.x; k < k1; k += blockDim.x) {
-        int h = bucket[k];
-        double v = value[k];
-        double x[CG];
+    // KU index steps per trip: KU*CG independent loads in flight per thread before the atomics
+    for (size_t kb = k0 + threadIdx.x; kb < k1; kb += (size_t)blockDim.x * KU) {
+        int h[KU]; double v[KU]; double x[KU][CG];
 #pragma unroll
-        for (int c = 0; c < CG; c++) x[c] = c < ncol ? ldg_stream1(X + k + (j0 + c) * ldx) : 0.0;
+        for (int u = 0; u < KU; u++) {
+            const size_t k = kb + (size_t)u * blockDim.x;
+            const bool on = k < k1;
+            h[u] = on ? bucket[k] : 0;
+            v[u] = on ? value[k] : 0.0;
 #pragma unroll
-        for (int c = 0; c < CG; c++)
-            if (c < ncol) atomicAdd(&acc[c * S + h], __dmul_rn(v, x[c]));
+            for (int c = 0; c < CG; c++) x[u][c] = (on && c < ncol) ? ldg_stream1(X + k + (j0 + c) * ldx) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < KU; u++) {
+            if (kb + (size_t)u * blockDim.x < k1) {
+#pragma unroll
+                for (int c = 0; c < CG; c++)
+                    if (c < ncol) atomicAdd(&acc[c * S + h[u]], __dmul_rn(v[u], x[u][c]));
+            }
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < S * ncol; i += blockDim.x) {
@@ -343,18 +354,22 @@ __global__ void k_hash_cols_global(const double *__restrict__ X, size_t ldx, siz
 void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int32_t *bucket,
                      const double *value, double *OUT, size_t ldo, int S, cudaStream_t st) {
     if (m == 0) return;
-    constexpr int CG = 4;
+    constexpr int CG = 4, KU = 4;
     size_t smem = (size_t)S * CG * sizeof(double);
     if (smem <= 200 * 1024) {
         unsigned gx = (unsigned)((m + CG - 1) / CG);
         int ksplit = 1;
-        // aim for >= 2 CTAs per SM; every split costs an S x CG atomic flush
-        while ((long long)gx * ksplit < 296 && (n / (ksplit * 2)) >= 4096) ksplit *= 2;
+        // aim for the CTAs that fit per SM (by shared memory, <= 4); every split costs an
+        // S x CG atomic flush
+        long long per_sm = (long long)((220 * 1024) / (smem ? smem : 1));
+        if (per_sm > 4) per_sm = 4;
+        if (per_sm < 1) per_sm = 1;
+        while ((long long)gx * ksplit < 148 * per_sm && (n / (ksplit * 2)) >= 4096) ksplit *= 2;
         if (ksplit > 1) zero_matrix(OUT, ldo, (size_t)S, m, st);
-        SKB_CUDA(cudaFuncSetAttribute(k_hash_cols_smem<CG>,
+        SKB_CUDA(cudaFuncSetAttribute(k_hash_cols_smem<CG, KU>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         LaunchScope ls(KC_HASH, st);
-        k_hash_cols_smem<CG><<<dim3(gx, ksplit), 256, smem, st>>>(X, ldx, n, m, bucket, value,
+        k_hash_cols_smem<CG, KU><<<dim3(gx, ksplit), 256, smem, st>>>(X, ldx, n, m, bucket, value,
                                                                    OUT, ldo, S, ksplit);
         SKB_CUDA(cudaGetLastError());
     } else {

@@ -54,6 +54,20 @@ def test_cwt_rows_layout_is_bit_exact_when_buckets_are_short(sk, oracle):
     assert rel_fro(got, want) < 1e-15     # values differ by <= 2 ulp, sums follow
 
 
+@pytest.mark.parametrize("shape", [(3000, 50, 40), (4000, 3, 333), (70, 64, 9), (3500, 2000, 20),
+                                   (50000, 2000, 6)])
+def test_cwt_strided_layout(sk, oracle, shape):
+    # column-major operand (sketched index contiguous) and its twin, a row-major operand sketched
+    # rowwise: shared-memory accumulation, rows of a bucket arrive in no fixed order
+    n, s, d = shape
+    S, O = _pair(sk, oracle, "CWT", n, s, seed=5)
+    A = np.random.default_rng(4).standard_normal((n, d))
+    want = O.apply(A, "columnwise")
+    assert rel_fro(S.apply(np.asfortranarray(A), None, "columnwise"), want) < 1e-14
+    B = np.ascontiguousarray(A.T)
+    assert rel_fro(S.apply(B, None, "rowwise"), want.T) < 1e-14
+
+
 @pytest.mark.parametrize("fmt", ["csc", "csr"])
 @pytest.mark.parametrize("T", ["CWT", "MMT"])
 def test_scipy_sparse_input(sk, oracle, T, fmt):
