@@ -33,6 +33,9 @@ UNIT = "TFLOP/s"
 WORKLOAD = "C2: JLT fp64 1000000x1024 -> s=4096, columnwise, row-major A"
 
 
+CPU_SAMPLE_ROWS = 48 * 8192   # ~10-15 s of host work on the 16-core box (0.3 TFLOP/s measured)
+
+
 def flops_per_step(n_rows):
     return 2.0 * S_ROWS * n_rows * D_COLS
 
@@ -56,10 +59,15 @@ def cpu_reference_sample(n_sample, repeats=1):
     ctx = o.Context(SKETCH_SEED)
     t = o.JLT(N_ROWS, S_ROWS, ctx)
     times = []
+    panel = 8192        # rows of A per panel, so S is never materialised whole (the reference
+                        # blocks the same way, dense_transform_Elemental_coldist_star.hpp:200-229)
     for _ in range(repeats):
         t0 = time.perf_counter()
-        R = o.realize_dense(t.seed, t.base, 0, t.scale, S_ROWS, 0, 0, S_ROWS, n_sample)
-        SA = R @ A
+        SA = np.zeros((S_ROWS, D_COLS))
+        for k0 in range(0, n_sample, panel):
+            kc = min(panel, n_sample - k0)
+            R = o.realize_dense(t.seed, t.base, 0, t.scale, S_ROWS, 0, k0, S_ROWS, kc)
+            SA += R @ A[k0:k0 + kc]
         times.append(time.perf_counter() - t0)
     del SA
     dt = statistics.median(times)
@@ -74,7 +82,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    n_sample = 8192
+    n_sample = CPU_SAMPLE_ROWS
     for _ in range(args.warmup if args.warmup < 2 else 1):
         cpu_reference_sample(1024)
     res = [cpu_reference_sample(n_sample) for _ in range(max(1, min(args.steps, 3)))]
@@ -561,7 +569,7 @@ def run_ours(args):
     except Exception:
         pass
 
-    cpu = cpu_reference_sample(8192) if world == 1 else None
+    cpu = cpu_reference_sample(CPU_SAMPLE_ROWS) if world == 1 else None
     extra = None
     if world == 1:
         del A, SA, S
