@@ -566,6 +566,9 @@ __device__ __forceinline__ int pad16(int i) { return i + (i >> 4); }
 #ifndef SKB_FFT_MINB
 #define SKB_FFT_MINB 2
 #endif
+#ifndef SKB_FFT_TWPOW
+#define SKB_FFT_TWPOW 1         // twiddles of a butterfly as powers of one table entry
+#endif
 constexpr int FFT_PPT = SKB_FFT_PPT;
 constexpr size_t FFT_POINTS = 4096, FFT_THREADS = FFT_POINTS / FFT_PPT;
 constexpr size_t FFT_SMEM = (FFT_POINTS + (FFT_POINTS >> 4) + 16) * sizeof(cplx);
@@ -645,8 +648,19 @@ __device__ __forceinline__ void inplace_pass(cplx *buf, int L, int Ns, const cpl
 #pragma unroll
         for (int t = 0; t < R; t++) a[uu][t] = buf[pad16(sbase + t * per)];
         if (Ns > 1) {
+#if SKB_FFT_TWPOW
+            // one table read per butterfly; the other R-2 twiddles are its powers (product tree of
+            // depth <= 4, a few ulp): the FP64 pipe is idle here, the load latency is not
+            cplx wp[R];
+            wp[1] = ldg_cplx(W + k * step);
+#pragma unroll
+            for (int t = 2; t < R; t++) wp[t] = (t & 1) ? cmul(wp[t - 1], wp[1]) : cmul(wp[t / 2], wp[t / 2]);
+#pragma unroll
+            for (int t = 1; t < R; t++) a[uu][t] = cmul(a[uu][t], wp[t]);
+#else
 #pragma unroll
             for (int t = 1; t < R; t++) a[uu][t] = cmul(a[uu][t], ldg_cplx(W + t * k * step));
+#endif
         }
         dbase[uu] = g * L + (j - k) * R + k;
     }
@@ -819,7 +833,12 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         DctPlan pl;
         pl.N = N; pl.Np = N / 2;
         int lg = 0; while (((size_t)1 << lg) < pl.Np) lg++;
-        pl.N1 = (size_t)1 << (lg / 2); pl.N2 = pl.Np / pl.N1;
+        pl.N1 = (size_t)1 << (lg / 2);
+        {   // debug knob: log2 of the contiguous (pass 2) FFT length
+            static const char *e = getenv("SKB_DCT_N1LOG");
+            if (e && atoi(e) > 0 && atoi(e) < lg) pl.N1 = (size_t)1 << atoi(e);
+        }
+        pl.N2 = pl.Np / pl.N1;
         pl.lo_bits = 10;
         const size_t B = dct_batch_cols(N, m);
         cplx *H = reinterpret_cast<cplx *>(ws);
@@ -842,6 +861,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         SKB_CUDA(cudaFuncSetAttribute(k_dct_pass2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
         {
             size_t nt = pl.N2 > S ? pl.N2 : S;
+            if (nt < pl.N1) nt = pl.N1;
             if (nt < 1024) nt = 1024;
             if (nt < (pl.Np >> pl.lo_bits) + 1) nt = (pl.Np >> pl.lo_bits) + 1;
             LaunchScope ls(KC_FJLT, st);
