@@ -399,7 +399,46 @@ struct DctPlan {
     cplx *Tlo, *Thi;          // W_Np^(lo), W_Np^(hi << lo_bits)
     cplx *post;               // per sample: W_N^k, W_4N^k
     size_t G1, G2;            // sequences per CTA in pass 1 / pass 2
+    // register-blocked engine only: pass 2 keeps just the bins the samples need.  need = bitmap
+    // over positions of H (k2*N1 + k1), rank = number of needed positions before each word,
+    // Zc = per column the needed bins in position order (stride zc_ld)
+    uint32_t *need, *rank;
+    cplx *Zc; size_t zc_ld;
 };
+
+__device__ __forceinline__ size_t dct_pos(const DctPlan &pl, size_t k) {     // bin k -> position in H
+    return (k & (pl.N2 - 1)) * pl.N1 + k / pl.N2;
+}
+__global__ void k_dct_mark(DctPlan pl, const int32_t *__restrict__ samples, size_t S) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S) return;
+    const size_t k = (size_t)samples[t], kp = k & (pl.Np - 1), km = (pl.Np - kp) & (pl.Np - 1);
+    const size_t pa = dct_pos(pl, kp), pb = dct_pos(pl, km);
+    atomicOr(pl.need + (pa >> 5), 1u << (pa & 31));
+    atomicOr(pl.need + (pb >> 5), 1u << (pb & 31));
+}
+// exclusive prefix of the popcounts of `need` (one 1024-thread block)
+__global__ void __launch_bounds__(1024) k_dct_rank(DctPlan pl) {
+    __shared__ uint32_t part[1024];
+    const size_t nwords = pl.Np >> 5, per = (nwords + 1023) / 1024;
+    const size_t w0 = (size_t)threadIdx.x * per, w1 = w0 + per < nwords ? w0 + per : nwords;
+    uint32_t c = 0;
+    for (size_t w = w0; w < w1; w++) c += __popc(pl.need[w]);
+    part[threadIdx.x] = c;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {
+        uint32_t v = threadIdx.x >= (unsigned)off ? part[threadIdx.x - off] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    uint32_t run = part[threadIdx.x] - c;
+    for (size_t w = w0; w < w1; w++) { pl.rank[w] = run; run += __popc(pl.need[w]); }
+}
+__device__ __forceinline__ uint32_t dct_rank_of(const DctPlan &pl, size_t p) {
+    const uint32_t w = __ldg(pl.need + (p >> 5));
+    return __ldg(pl.rank + (p >> 5)) + __popc(w & ((1u << (p & 31)) - 1u));
+}
 
 __global__ void k_dct_tables(DctPlan pl, const int32_t *__restrict__ samples, size_t S) {
     size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -757,12 +796,14 @@ k_dct_pass1_r16(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan p
     }
 }
 
-// pass 2 (register-blocked engine): grid (N2 / G, columns in batch), G = 4096 / N1; in place
+// pass 2 (register-blocked engine): grid (N2 / G, columns in batch), G = 4096 / N1 contiguous rows per CTA,
+// keeping only the bins the samples need (see DctPlan::need)
 __global__ void __launch_bounds__(FFT_THREADS, SKB_FFT_MINB)
-k_dct_pass2_r16(DctPlan pl, cplx *__restrict__ H) {
+k_dct_pass2_r16_sel(DctPlan pl, const cplx *__restrict__ H) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     cplx *buf = reinterpret_cast<cplx *>(smem_raw);
-    cplx *rows = H + (size_t)blockIdx.y * pl.Np + (size_t)blockIdx.x * FFT_POINTS;
+    const size_t base = (size_t)blockIdx.x * FFT_POINTS;
+    const cplx *rows = H + (size_t)blockIdx.y * pl.Np + base;
 #pragma unroll
     for (int it = 0; it < FFT_PPT; it++) {
         const int idx = (int)threadIdx.x + it * (int)FFT_THREADS;
@@ -770,11 +811,33 @@ k_dct_pass2_r16(DctPlan pl, cplx *__restrict__ H) {
     }
     __syncthreads();
     smem_fft16(buf, (int)pl.N1, pl.W2);
+    cplx *zc = pl.Zc + (size_t)blockIdx.y * pl.zc_ld;
 #pragma unroll
     for (int it = 0; it < FFT_PPT; it++) {
         const int idx = (int)threadIdx.x + it * (int)FFT_THREADS;
-        rows[idx] = buf[pad16(idx)];
+        const size_t p = base + idx;
+        const uint32_t w = __ldg(pl.need + (p >> 5));
+        if ((w >> (p & 31)) & 1u)
+            zc[__ldg(pl.rank + (p >> 5)) + __popc(w & ((1u << (p & 31)) - 1u))] = buf[pad16(idx)];
     }
+}
+
+__global__ void k_dct_post_sel(DctPlan pl, const int32_t *__restrict__ samples,
+                               size_t S, size_t col0, size_t ncols, double outscale,
+                               double *__restrict__ OUT, size_t oi, size_t oj) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S * ncols) return;
+    const size_t i = t % S, c = t / S;
+    const size_t k = (size_t)samples[i], kp = k & (pl.Np - 1), km = (pl.Np - kp) & (pl.Np - 1);
+    const cplx *Z = pl.Zc + c * pl.zc_ld;
+    const cplx za = Z[dct_rank_of(pl, dct_pos(pl, kp))];
+    const cplx zb = Z[dct_rank_of(pl, dct_pos(pl, km))];
+    cplx E, O;
+    E.x = 0.5 * (za.x + zb.x); E.y = 0.5 * (za.y - zb.y);
+    O.x = 0.5 * (za.y + zb.y); O.y = -0.5 * (za.x - zb.x);
+    cplx V = cadd(E, cmul(pl.post[2 * i], O));
+    cplx Yc = cmul(pl.post[2 * i + 1], V);
+    OUT[i * oi + (col0 + c) * oj] = outscale * (2.0 * Yc.x);
 }
 
 // sampled bins -> DCT values -> OUT
@@ -810,13 +873,16 @@ static size_t dct_batch_cols(size_t N, size_t m) {
 static size_t dct_table_bytes(size_t N, size_t S) {
     return (N + 4096 + 2 * S + 1024) * sizeof(cplx);     // generous upper bound
 }
+static size_t dct_sel_bytes(size_t N, size_t S, size_t B) {     // need bitmap, ranks, kept bins
+    return (N / 2 / 32 + 64) * 2 * sizeof(uint32_t) + (B * 2 * S + 64) * sizeof(cplx) + 512;
+}
 
 static bool wht_fast_ok(size_t N) { return N >= (size_t)WSEG && (N & (N - 1)) == 0 && N <= ((size_t)1 << 28); }
 
 size_t fjlt_workspace_bytes(size_t N, size_t m, int fut, bool layout_rows, size_t S) {
     if (fut == FUT_DCT && dct_fast_ok(N))
         return (layout_rows ? N * m * sizeof(double) : 0) + dct_batch_cols(N, m) * N * sizeof(double) +
-               dct_table_bytes(N, S) + 1024;
+               dct_table_bytes(N, S) + dct_sel_bytes(N, S, dct_batch_cols(N, m)) + 1024;
     if (fut == FUT_DCT) return 4 * N * sizeof(double) + 256;
     if (fut == FUT_WHT && wht_fast_ok(N))         // sign words (+ transposed copy)
         return (layout_rows ? (N * m * sizeof(double) + 255) / 256 * 256 : 0) + N / 8 + 256;
@@ -876,7 +942,11 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         pl.W2 = tab; tab += pl.N1;
         pl.Tlo = tab; tab += (size_t)1 << pl.lo_bits;
         pl.Thi = tab; tab += (pl.Np >> pl.lo_bits) + 1;
-        pl.post = tab;
+        pl.post = tab; tab += 2 * S;
+        pl.need = reinterpret_cast<uint32_t *>(tab);
+        pl.rank = pl.need + (pl.Np / 32 + 64);
+        pl.Zc = reinterpret_cast<cplx *>((reinterpret_cast<uintptr_t>(pl.rank + (pl.Np / 32 + 64)) + 255) / 256 * 256);
+        pl.zc_ld = 2 * S;
         // sequences per CTA: G*L = 2048 points -> two 32 KB ping-pong buffers, 512 threads with
         // one radix-4 unit each per pass, three CTAs per SM
         auto seqs = [](size_t L, size_t other) {
@@ -908,7 +978,16 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         if (r16) {
             SKB_CUDA(cudaFuncSetAttribute(k_dct_pass1_r16<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFT_SMEM));
             SKB_CUDA(cudaFuncSetAttribute(k_dct_pass1_r16<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFT_SMEM));
-            SKB_CUDA(cudaFuncSetAttribute(k_dct_pass2_r16, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFT_SMEM));
+            SKB_CUDA(cudaFuncSetAttribute(k_dct_pass2_r16_sel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFT_SMEM));
+            SKB_CUDA(cudaMemsetAsync(pl.need, 0, (pl.Np / 32) * sizeof(uint32_t), st));
+            {
+                LaunchScope ls(KC_FJLT, st);
+                k_dct_mark<<<(unsigned)((S + 255) / 256), 256, 0, st>>>(pl, samples, S);
+            }
+            {
+                LaunchScope ls(KC_FJLT, st);
+                k_dct_rank<<<1, 1024, 0, st>>>(pl);
+            }
         }
         for (size_t c0 = 0; c0 < m; c0 += B) {
             const size_t nb = m - c0 < B ? m - c0 : B;
@@ -922,9 +1001,16 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
                 }
                 {
                     LaunchScope ls(KC_FJLT, st);
-                    k_dct_pass2_r16<<<dim3((unsigned)(pl.N1 * pl.N2 / FFT_POINTS), (unsigned)nb),
-                                      FFT_THREADS, FFT_SMEM, st>>>(pl, H);
+                    k_dct_pass2_r16_sel<<<dim3((unsigned)(pl.N1 * pl.N2 / FFT_POINTS), (unsigned)nb),
+                                          FFT_THREADS, FFT_SMEM, st>>>(pl, H);
                 }
+                {
+                    LaunchScope ls(KC_FJLT, st);
+                    k_dct_post_sel<<<(unsigned)((S * nb + 255) / 256), 256, 0, st>>>(
+                        pl, samples, S, c0, nb, outscale, OUT, oi, oj);
+                }
+                SKB_CUDA(cudaGetLastError());
+                continue;
             } else {
             {
                 LaunchScope ls(KC_FJLT, st);
