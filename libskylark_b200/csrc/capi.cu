@@ -137,7 +137,7 @@ struct SpOwned {
     void release_device() {
         if (!d_indptr && !d_indices && !d_values) return;
         int prev = -1; cudaGetDevice(&prev); if (device >= 0) cudaSetDevice(device);
-        cudaFree(d_indptr); cudaFree(d_indices); cudaFree(d_values);
+        cudaFree(d_indptr); cudaFree(d_indices); cudaFree(d_values);   // pool memory: goes back to the pool
         d_indptr = d_indices = nullptr; d_values = nullptr;
         if (prev >= 0) cudaSetDevice(prev);
     }
@@ -405,8 +405,8 @@ static void apply_sparse_out(sl_sketch_transform_t *t, const sl_matrix_t *A, sl_
                 SKB_CUDA(cudaMemcpyAsync(o.h_values.data(), ov, onnz * 8, cudaMemcpyDeviceToHost, g_stream));
             }
             SKB_CUDA(cudaStreamSynchronize(g_stream));
-        } catch (...) { cudaFree(oi); cudaFree(ox); cudaFree(ov); throw; }
-        cudaFree(oi); cudaFree(ox); cudaFree(ov);
+        } catch (...) { hash_sparse_free(oi, g_stream); hash_sparse_free(ox, g_stream); hash_sparse_free(ov, g_stream); throw; }
+        hash_sparse_free(oi, g_stream); hash_sparse_free(ox, g_stream); hash_sparse_free(ov, g_stream);
         SA->indptr = o.h_indptr.data(); SA->indices = o.h_indices.data(); SA->values = o.h_values.data();
     }
     SA->m = om; SA->n = on; SA->nnz = (int64_t)onnz; SA->struct_updated = true;

@@ -19,6 +19,8 @@
 //     column and dump coalesced columns.
 #include <algorithm>
 #include <cstdlib>
+#include <cub/block/block_radix_sort.cuh>
+#include <cub/block/block_scan.cuh>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
@@ -597,6 +599,181 @@ __global__ void k_sp_indptr(const uint64_t *__restrict__ ukeys, int nout, int nc
     }
 }
 
+// Result arrays of the sparse path come from the device's stream-ordered pool (kept cached:
+// no release threshold), so a steady stream of applies does not pay cudaMalloc/cudaFree.
+template <class T>
+static void sp_alloc(T **p, size_t bytes, cudaStream_t st) {
+    static bool tuned[64] = {false};
+    int dev = 0;
+    SKB_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !tuned[dev]) {
+        cudaMemPool_t pool;
+        SKB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+        unsigned long long keep = ~0ULL;
+        SKB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+        tuned[dev] = true;
+    }
+    SKB_CUDA(cudaMallocAsync((void **)p, bytes ? bytes : 16, st));
+}
+// cudaFree accepts pool allocations (no implicit synchronisation: callers are done with p)
+void hash_sparse_free(void *p, cudaStream_t st) { if (p) { cudaStreamSynchronize(st); cudaFree(p); } }
+
+// K2s fast path (columnwise, every column <= 2048 entries): one CTA sorts a column at a
+// time in shared memory.  Key = bucket << PB | position in the column, so a keys-only block
+// radix sort is stable by construction and the values are fetched through the position.  Equal
+// buckets are then added left to right (input order, as the reference does) by the thread that
+// holds the head of the run.  Results go to scratch at the column's input offset; a second
+// kernel packs the columns once the output offsets are known.
+static constexpr int SPC_THREADS = 256;
+
+template <int ITEMS>
+__global__ void __launch_bounds__(SPC_THREADS)
+k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ indices,
+              const double *__restrict__ values, int ncols, const int32_t *__restrict__ bucket,
+              const double *__restrict__ value, int pos_bits, int key_bits,
+              int32_t *__restrict__ tmp_idx, double *__restrict__ tmp_val, int32_t *__restrict__ cnt) {
+    constexpr int CAP = SPC_THREADS * ITEMS;
+    using Sort = cub::BlockRadixSort<uint32_t, SPC_THREADS, ITEMS>;
+    using Scan = cub::BlockScan<int, SPC_THREADS>;
+    __shared__ union { typename Sort::TempStorage sort; typename Scan::TempStorage scan; } tmp;
+    __shared__ uint32_t skeys[CAP + 1];
+    __shared__ double svals[CAP];
+    const uint32_t pmask = (1u << pos_bits) - 1u;
+    for (int col = blockIdx.x; col < ncols; col += gridDim.x) {
+        const int c0 = indptr[col], cn = indptr[col + 1] - c0;
+        uint32_t keys[ITEMS];
+#pragma unroll
+        for (int t = 0; t < ITEMS; t++) {
+            const int i = threadIdx.x + t * SPC_THREADS;
+            keys[t] = 0xffffffffu;
+            if (i < cn) {
+                const int row = indices[c0 + i];
+                keys[t] = ((uint32_t)bucket[row] << pos_bits) | (uint32_t)i;
+                svals[i] = __dmul_rn(values[c0 + i], value[row]);
+            }
+        }
+        Sort(tmp.sort).Sort(keys, 0, key_bits);        // blocked output: thread holds ITEMS consecutive keys
+#pragma unroll
+        for (int t = 0; t < ITEMS; t++) skeys[threadIdx.x * ITEMS + t] = keys[t];
+        if (threadIdx.x == 0) skeys[CAP] = 0xffffffffu;
+        __syncthreads();
+        int nhead = 0;
+        bool head[ITEMS];
+#pragma unroll
+        for (int t = 0; t < ITEMS; t++) {
+            const int i = threadIdx.x * ITEMS + t;
+            head[t] = i < cn && (i == 0 || (skeys[i - 1] >> pos_bits) != (keys[t] >> pos_bits));
+            nhead += head[t];
+        }
+        int off, total;
+        Scan(tmp.scan).ExclusiveSum(nhead, off, total);
+#pragma unroll
+        for (int t = 0; t < ITEMS; t++) {
+            if (head[t]) {
+                const uint32_t b = keys[t] >> pos_bits;
+                double acc = svals[keys[t] & pmask];
+                for (int q = threadIdx.x * ITEMS + t + 1; (skeys[q] >> pos_bits) == b && q < cn; q++)
+                    acc = __dadd_rn(acc, svals[skeys[q] & pmask]);
+                tmp_idx[c0 + off] = (int32_t)b;
+                tmp_val[c0 + off] = acc;
+                off++;
+            }
+        }
+        if (threadIdx.x == 0) cnt[col] = total;
+        __syncthreads();                               // shared arrays are reused by the next column
+    }
+}
+
+__global__ void k_sp_col_pack(const int32_t *__restrict__ indptr, const int32_t *__restrict__ out_indptr,
+                              int ncols, const int32_t *__restrict__ tmp_idx,
+                              const double *__restrict__ tmp_val, int32_t *__restrict__ out_indices,
+                              double *__restrict__ out_values) {
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int col = warp; col < ncols; col += nwarps) {
+        const int src = indptr[col], dst = out_indptr[col], n = out_indptr[col + 1] - dst;
+        for (int i = lane; i < n; i += 32) {
+            out_indices[dst + i] = tmp_idx[src + i];
+            out_values[dst + i] = tmp_val[src + i];
+        }
+    }
+}
+
+__global__ void k_sp_max_col(const int32_t *__restrict__ indptr, int ncols, int32_t *out) {
+    int m = 0;
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < ncols; c += gridDim.x * blockDim.x)
+        m = max(m, indptr[c + 1] - indptr[c]);
+    m = __reduce_max_sync(0xffffffffu, m);
+    if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
+}
+
+// Returns false (nothing done) when the shape does not qualify.
+static bool sparse_columnwise_fast(const int32_t *indptr, const int32_t *indices, const double *values,
+                                   size_t ncols, size_t nnz, const int32_t *bucket, const double *value,
+                                   int S, int32_t **out_indptr, int32_t **out_indices,
+                                   double **out_values, size_t *out_nnz, void **ws, size_t *ws_bytes,
+                                   cudaStream_t st) {
+    static const bool off = getenv("SKB_DEBUG_SP_GENERIC") != nullptr;
+    if (off || nnz == 0 || ncols == 0 || nnz / ncols < 256) return false;   // short columns: the global sort wins
+    auto al = [](size_t b) { return (b + 255) / 256 * 256; };
+    size_t scan_bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (int32_t *)nullptr, (int32_t *)nullptr, (int)ncols + 1, st);
+    const size_t need = al(nnz * 4) + al(nnz * 8) + al((ncols + 1) * 4) + al(scan_bytes) + 512;
+    if (*ws_bytes < need) {
+        SKB_CUDA(cudaStreamSynchronize(st));
+        cudaFree(*ws); *ws = nullptr; *ws_bytes = 0;
+        SKB_CUDA(cudaMalloc(ws, need));
+        *ws_bytes = need;
+    }
+    char *w = (char *)*ws;
+    int32_t *tmp_idx = (int32_t *)w; w += al(nnz * 4);
+    double *tmp_val = (double *)w;   w += al(nnz * 8);
+    int32_t *cnt = (int32_t *)w;     w += al((ncols + 1) * 4);
+    void *scan_tmp = w;              w += al(scan_bytes);
+    int32_t *dmax = (int32_t *)w;
+    SKB_CUDA(cudaMemsetAsync(dmax, 0, sizeof(int32_t), st));
+    {
+        LaunchScope ls(KC_HASH, st);
+        k_sp_max_col<<<(unsigned)std::min<size_t>((ncols + 255) / 256, 1184), 256, 0, st>>>(indptr, (int)ncols, dmax);
+    }
+    int32_t maxc = 0;
+    SKB_CUDA(cudaMemcpyAsync(&maxc, dmax, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    SKB_CUDA(cudaStreamSynchronize(st));
+    int items = maxc <= SPC_THREADS * 2 ? 2 : maxc <= SPC_THREADS * 4 ? 4 : maxc <= SPC_THREADS * 8 ? 8 : 0;
+    int pos_bits = 1, bucket_bits = 1;
+    while ((1 << pos_bits) < SPC_THREADS * (items ? items : 1)) pos_bits++;
+    while ((1LL << bucket_bits) < (long long)S) bucket_bits++;
+    if (!items || pos_bits + bucket_bits > 32) return false;
+    sp_alloc(out_indptr, (ncols + 1) * sizeof(int32_t), st);
+    SKB_CUDA(cudaMemsetAsync(cnt + ncols, 0, sizeof(int32_t), st));
+    const unsigned grid = (unsigned)std::min<size_t>(ncols, 148 * 4);
+    {
+        LaunchScope ls(KC_HASH, st);
+        const int kb = pos_bits + bucket_bits;
+        if (items == 2) k_sp_col_sort<2><<<grid, SPC_THREADS, 0, st>>>(indptr, indices, values, (int)ncols, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt);
+        else if (items == 4) k_sp_col_sort<4><<<grid, SPC_THREADS, 0, st>>>(indptr, indices, values, (int)ncols, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt);
+        else k_sp_col_sort<8><<<grid, SPC_THREADS, 0, st>>>(indptr, indices, values, (int)ncols, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt);
+        SKB_CUDA(cudaGetLastError());
+    }
+    {
+        LaunchScope ls(KC_HASH, st);
+        SKB_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, cnt, *out_indptr, (int)ncols + 1, st));
+    }
+    int32_t nout = 0;
+    SKB_CUDA(cudaMemcpyAsync(&nout, *out_indptr + ncols, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    SKB_CUDA(cudaStreamSynchronize(st));
+    sp_alloc(out_indices, (size_t)nout * 4, st);
+    sp_alloc(out_values, (size_t)nout * 8, st);
+    {
+        LaunchScope ls(KC_HASH, st);
+        k_sp_col_pack<<<148 * 8, 256, 0, st>>>(indptr, *out_indptr, (int)ncols, tmp_idx, tmp_val,
+                                               *out_indices, *out_values);
+        SKB_CUDA(cudaGetLastError());
+    }
+    *out_nnz = (size_t)nout;
+    return true;
+}
+
 void hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices, const double *values,
                            size_t nrows, size_t ncols, size_t nnz, bool rowwise,
                            const int32_t *bucket, const double *value, int S,
@@ -607,6 +784,17 @@ void hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices, const 
     *out_indptr = nullptr; *out_indices = nullptr; *out_values = nullptr; *out_nnz = 0;
     if (nnz > 0x7fffffffULL || ncols > 0x7ffffffeULL || nrows > 0x7fffffffULL)
         throw error(SKB_ERR_INVALID_PARAM, "sparse apply: sizes exceed int32");
+    if (!rowwise) {
+        try {
+            if (sparse_columnwise_fast(indptr, indices, values, ncols, nnz, bucket, value, S, out_indptr,
+                                       out_indices, out_values, out_nnz, ws, ws_bytes, st))
+                return;
+        } catch (...) {
+            hash_sparse_free(*out_indptr, st); hash_sparse_free(*out_indices, st); hash_sparse_free(*out_values, st);
+            *out_indptr = nullptr; *out_indices = nullptr; *out_values = nullptr;
+            throw;
+        }
+    }
     // temporaries live in the caller's grow-only workspace (no allocation in steady state)
     auto al = [](size_t b) { return (b + 255) / 256 * 256; };
     size_t sort_bytes = 0, scan_bytes = 0;
@@ -634,11 +822,11 @@ void hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices, const 
     int32_t *pos = (int32_t *)w;     w += al(nnz * 4);
     void *tmp = w;
     try {
-        SKB_CUDA(cudaMalloc(out_indptr, (ncols_out + 1) * sizeof(int32_t)));
+        sp_alloc(out_indptr, (ncols_out + 1) * sizeof(int32_t), st);
         if (nnz == 0) {
             SKB_CUDA(cudaMemsetAsync(*out_indptr, 0, (ncols_out + 1) * sizeof(int32_t), st));
-            SKB_CUDA(cudaMalloc(out_indices, 16));
-            SKB_CUDA(cudaMalloc(out_values, 16));
+            sp_alloc(out_indices, 16, st);
+            sp_alloc(out_values, 16, st);
             return;
         }
         const int n = (int)nnz;
@@ -673,8 +861,8 @@ void hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices, const 
         int32_t nout = 0;
         SKB_CUDA(cudaMemcpyAsync(&nout, pos + (n - 1), sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         SKB_CUDA(cudaStreamSynchronize(st));
-        SKB_CUDA(cudaMalloc(out_indices, (size_t)nout * 4));
-        SKB_CUDA(cudaMalloc(out_values, (size_t)nout * 8));
+        sp_alloc(out_indices, (size_t)nout * 4, st);
+        sp_alloc(out_values, (size_t)nout * 8, st);
         uint64_t *ukeys = kb.Alternate();       // the other sort buffer is free by now
         {
             LaunchScope ls(KC_HASH, st);
@@ -689,7 +877,7 @@ void hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices, const 
         SKB_CUDA(cudaGetLastError());
         *out_nnz = (size_t)nout;
     } catch (...) {
-        cudaFree(*out_indptr); cudaFree(*out_indices); cudaFree(*out_values);
+        hash_sparse_free(*out_indptr, st); hash_sparse_free(*out_indices, st); hash_sparse_free(*out_values, st);
         *out_indptr = nullptr; *out_indices = nullptr; *out_values = nullptr;
         throw;
     }

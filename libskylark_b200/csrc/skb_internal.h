@@ -92,7 +92,8 @@ void hash_apply_csc_rowwise(const int32_t *indptr, const int32_t *indices,
                             const int32_t *bucket, const double *value, double *OUT,
                             size_t ldo, int S, cudaStream_t st);
 
-// CSC input -> CSC output (device arrays allocated here with cudaMalloc, owned by the caller):
+// CSC input -> CSC output (device arrays allocated here from the stream-ordered pool, owned by
+// the caller, released with hash_sparse_free):
 // columnwise gives S x ncols, rowwise nrows x S; rows inside a column come out sorted.
 // Temporaries live in the grow-only workspace (*ws, *ws_bytes).  Stream-ordered: the result
 // arrays are complete once work queued on st so far has finished.
@@ -101,6 +102,7 @@ void hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices, const 
                            const int32_t *bucket, const double *value, int S,
                            int32_t **out_indptr, int32_t **out_indices, double **out_values,
                            size_t *out_nnz, void **ws, size_t *ws_bytes, cudaStream_t st);
+void hash_sparse_free(void *p, cudaStream_t st);
 
 // ---- dense transforms (dense.cu) -------------------------------------------
 enum DenseDist { DD_NORMAL = 0, DD_CAUCHY = 1 };
