@@ -403,7 +403,25 @@ def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
                              "ms": ms, "kernel_ms_rank0": statistics.median(kernel_ms),
                              "value": nbytes / (ms * 1e-3) / 1e9, "unit": "GB/s (all GPUs, kernel bytes / "
                              "end-to-end time incl. collective)", "scaling": "weak"}
-        del A, SA, S, indptr, indices, values
+        del SA
+        torch.cuda.empty_cache()
+        # the same sketch with sparse partials: column-block all-to-all of ~1.5 GB per GPU instead of
+        # the 16 GB dense reduce-scatter; every rank ends with its d/world columns as CSC
+        from libskylark_b200.dist import apply_distributed_sparse
+        try:
+            def c4s():
+                res = apply_distributed_sparse(S, A, rank * n_loc, None)
+                torch.cuda.synchronize()
+                return res
+            ms = timed(c4s, 2)
+            out["c4_cwt_csc_sparse_exchange"] = {
+                "workload": "C4: same matrix, sparse partial sketches (CSC -> CSC), column-block all-to-all, "
+                            "merge on the device; result = d/world columns per GPU as CSC",
+                "ms": ms, "value": world * (d * nnz_col * 12 + (d + 1) * 4) / (ms * 1e-3) / 1e9,
+                "unit": "GB/s (all GPUs, input bytes / end-to-end time incl. exchange and merge)", "scaling": "weak"}
+        except Exception as e:      # keep the bench line if this optional leg fails
+            out["c4_cwt_csc_sparse_exchange"] = {"error": repr(e)[:300]}
+        del A, S, indptr, indices, values
         torch.cuda.empty_cache()
 
     # ---- C5

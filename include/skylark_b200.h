@@ -183,6 +183,11 @@ int sl_dense_sketch_apply_noalloc(int seed, uint64_t counter_base, int dist, dou
 int sl_host_alloc_pinned(size_t bytes, void **ptr);
 int sl_host_free_pinned(void *ptr);
 int sl_device_count(int *count);
+/* No counterpart in the reference (its distributed hash apply reduces dense partials,
+ * sketch/hash_transform_Elemental.hpp:543-561).  A, SA: device sparse wrappers.  SA receives
+ * A with entries of equal (row, column) added in storage order and the rows of every column
+ * sorted -- the merge step after ranks have exchanged sparse partial sketches. */
+int sl_sp_matrix_coalesce(void *A, void *SA);
 
 #ifdef __cplusplus
 }

@@ -372,27 +372,13 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
                d.ws, d.ws_bytes, st, (size_t)offset, (size_t)sk);
 }
 
-// Sparse in, sparse out (CWT/MMT/WZT; sketch/hash_transform_local_sparse.hpp:88-223).  A is
-// device resident; the result replaces SA's structure, on the device for device wrappers and
-// in wrapper-owned host arrays otherwise (read back through sl_raw_sp_matrix_*).
-static void apply_sparse_out(sl_sketch_transform_t *t, const sl_matrix_t *A, sl_matrix_t *SA,
-                             int dim, int64_t offset, bool shard, int device) {
-    const bool colwise = dim == SL_COLUMNWISE;
-    if (!t->is_hash() || A->kind != MK_SPARSE)
-        throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse output needs CWT/MMT/WZT and a sparse input");
-    const int64_t sk = colwise ? A->m : A->n;
-    if (offset < 0 || offset + sk > t->N || (!shard && sk != t->N))
-        throw error(SKB_ERR_INVALID_PARAM, "apply: sketched dimension of A does not match N");
-    DevState &d = dev_state(t, device);
-    ensure_hash_tables(t, d);
-    int32_t *oi = nullptr, *ox = nullptr; double *ov = nullptr; size_t onnz = 0;
-    hash_apply_csc_sparse(A->indptr, A->indices, A->values, (size_t)A->m, (size_t)A->n,
-                          (size_t)A->nnz, !colwise, d.bucket + offset, d.value + offset, t->S,
-                          &oi, &ox, &ov, &onnz, &d.ws, &d.ws_bytes, g_stream);
+// Hands a freshly computed device CSC to the wrapper SA: kept on the device for device wrappers,
+// copied into wrapper-owned host arrays otherwise.
+static void attach_sparse_result(sl_matrix_t *SA, int32_t *oi, int32_t *ox, double *ov, size_t onnz,
+                                 int64_t om, int64_t on, int device) {
     if (!SA->own) SA->own = new SpOwned();
     SpOwned &o = *SA->own;
     o.release_device();
-    const int64_t om = colwise ? t->S : A->m, on = colwise ? A->n : t->S;
     if (SA->on_device) {
         o.d_indptr = oi; o.d_indices = ox; o.d_values = ov; o.device = device;
         SA->indptr = oi; SA->indices = ox; SA->values = ov;
@@ -410,6 +396,26 @@ static void apply_sparse_out(sl_sketch_transform_t *t, const sl_matrix_t *A, sl_
         SA->indptr = o.h_indptr.data(); SA->indices = o.h_indices.data(); SA->values = o.h_values.data();
     }
     SA->m = om; SA->n = on; SA->nnz = (int64_t)onnz; SA->struct_updated = true;
+}
+
+// Sparse in, sparse out (CWT/MMT/WZT; sketch/hash_transform_local_sparse.hpp:88-223).  A is
+// device resident; the result replaces SA's structure, on the device for device wrappers and
+// in wrapper-owned host arrays otherwise (read back through sl_raw_sp_matrix_*).
+static void apply_sparse_out(sl_sketch_transform_t *t, const sl_matrix_t *A, sl_matrix_t *SA,
+                             int dim, int64_t offset, bool shard, int device) {
+    const bool colwise = dim == SL_COLUMNWISE;
+    if (!t->is_hash() || A->kind != MK_SPARSE)
+        throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse output needs CWT/MMT/WZT and a sparse input");
+    const int64_t sk = colwise ? A->m : A->n;
+    if (offset < 0 || offset + sk > t->N || (!shard && sk != t->N))
+        throw error(SKB_ERR_INVALID_PARAM, "apply: sketched dimension of A does not match N");
+    DevState &d = dev_state(t, device);
+    ensure_hash_tables(t, d);
+    int32_t *oi = nullptr, *ox = nullptr; double *ov = nullptr; size_t onnz = 0;
+    hash_apply_csc_sparse(A->indptr, A->indices, A->values, (size_t)A->m, (size_t)A->n,
+                          (size_t)A->nnz, !colwise, d.bucket + offset, d.value + offset, t->S,
+                          &oi, &ox, &ov, &onnz, &d.ws, &d.ws_bytes, g_stream);
+    attach_sparse_result(SA, oi, ox, ov, onnz, colwise ? t->S : A->m, colwise ? A->n : t->S, device);
 }
 
 // Host operands of a dense sketch: the sketched dimension is cut in chunks; chunk c+1 is
@@ -951,6 +957,35 @@ int sl_host_alloc_pinned(size_t bytes, void **ptr) {
     SL_CATCH
 }
 int sl_host_free_pinned(void *ptr) { cudaFreeHost(ptr); return 0; }
+// Sums entries of a device CSC that share (row, column), in storage order, and sorts the rows of
+// every column: the merge step after sparse partial sketches have been exchanged between ranks.
+__global__ void k_iota_ones(int32_t *idx, double *one, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { idx[i] = (int32_t)i; one[i] = 1.0; }
+}
+int sl_sp_matrix_coalesce(void *A_, void *SA_) {
+    SL_TRY
+    require_device();
+    sl_matrix_t *A = as_matrix(A_), *SA = as_matrix(SA_);
+    if (A->kind != MK_SPARSE || SA->kind != MK_SPARSE || !A->on_device || !SA->on_device)
+        throw error(SKB_ERR_INVALID_USAGE, "sl_sp_matrix_coalesce: both operands must be device sparse matrices");
+    DeviceGuard g(A->device);
+    static std::map<int, std::pair<void *, size_t>> ws_per_dev;      // grow-only scratch per device
+    auto &ws = ws_per_dev[A->device];
+    int32_t *idx = nullptr; double *one = nullptr;
+    const size_t m = (size_t)A->m;
+    SKB_CUDA(cudaMallocAsync((void **)&idx, (m + 1) * sizeof(int32_t), g_stream));
+    SKB_CUDA(cudaMallocAsync((void **)&one, (m + 1) * sizeof(double), g_stream));
+    int32_t *oi = nullptr, *ox = nullptr; double *ov = nullptr; size_t onnz = 0;
+    try {
+        if (m) k_iota_ones<<<(unsigned)((m + 255) / 256), 256, 0, g_stream>>>(idx, one, m);
+        hash_apply_csc_sparse(A->indptr, A->indices, A->values, m, (size_t)A->n, (size_t)A->nnz, false,
+                              idx, one, (int)(m ? m : 1), &oi, &ox, &ov, &onnz, &ws.first, &ws.second, g_stream);
+    } catch (...) { cudaFreeAsync(idx, g_stream); cudaFreeAsync(one, g_stream); throw; }
+    cudaFreeAsync(idx, g_stream); cudaFreeAsync(one, g_stream);
+    attach_sparse_result(SA, oi, ox, ov, onnz, A->m, A->n, A->device);
+    SL_CATCH
+}
 int sl_device_count(int *count) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }

@@ -619,8 +619,8 @@ static void sp_alloc(T **p, size_t bytes, cudaStream_t st) {
 void hash_sparse_free(void *p, cudaStream_t st) { if (p) { cudaStreamSynchronize(st); cudaFree(p); } }
 
 // K2s fast path (columnwise, every column <= 2048 entries): one CTA sorts a column at a
-// time in shared memory.  Key = bucket << PB | position in the column, so a keys-only block
-// radix sort is stable by construction and the values are fetched through the position.  Equal
+// time in shared memory.  Key = bucket << PB | position in the column; a keys-only stable block
+// radix sort over the bucket bits groups the buckets and the values are fetched through the position.  Equal
 // buckets are then added left to right (input order, as the reference does) by the thread that
 // holds the head of the run.  Results go to scratch at the column's input offset; a second
 // kernel packs the columns once the output offsets are known.
@@ -633,7 +633,10 @@ k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ in
               const double *__restrict__ value, int pos_bits, int key_bits,
               int32_t *__restrict__ tmp_idx, double *__restrict__ tmp_val, int32_t *__restrict__ cnt) {
     constexpr int CAP = SPC_THREADS * ITEMS;
-    using Sort = cub::BlockRadixSort<uint32_t, SPC_THREADS, ITEMS>;
+#ifndef SKB_SPC_RADIX
+#define SKB_SPC_RADIX 4
+#endif
+    using Sort = cub::BlockRadixSort<uint32_t, SPC_THREADS, ITEMS, cub::NullType, SKB_SPC_RADIX>;
     using Scan = cub::BlockScan<int, SPC_THREADS>;
     __shared__ union { typename Sort::TempStorage sort; typename Scan::TempStorage scan; } tmp;
     __shared__ uint32_t skeys[CAP + 1];
@@ -643,8 +646,8 @@ k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ in
         const int c0 = indptr[col], cn = indptr[col + 1] - c0;
         uint32_t keys[ITEMS];
 #pragma unroll
-        for (int t = 0; t < ITEMS; t++) {
-            const int i = threadIdx.x + t * SPC_THREADS;
+        for (int t = 0; t < ITEMS; t++) {                // blocked: thread holds ITEMS consecutive entries
+            const int i = threadIdx.x * ITEMS + t;
             keys[t] = 0xffffffffu;
             if (i < cn) {
                 const int row = indices[c0 + i];
@@ -652,7 +655,9 @@ k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ in
                 svals[i] = __dmul_rn(values[c0 + i], value[row]);
             }
         }
-        Sort(tmp.sort).Sort(keys, 0, key_bits);        // blocked output: thread holds ITEMS consecutive keys
+        // the radix sort is stable and the entries start in column order, so only the bucket
+        // bits need sorting (padding keys are all ones and stay behind)
+        Sort(tmp.sort).Sort(keys, pos_bits, key_bits);   // blocked output
 #pragma unroll
         for (int t = 0; t < ITEMS; t++) skeys[threadIdx.x * ITEMS + t] = keys[t];
         if (threadIdx.x == 0) skeys[CAP] = 0xffffffffu;

@@ -79,3 +79,68 @@ def apply_distributed(S, A_local, SA=None, dim=0, index_offset=0, group=None,
     """Partial sketch of this rank's shard, then the collective (see reduce_partial)."""
     SA = S.apply_shard(A_local, SA, dim, index_offset)
     return reduce_partial(SA, group, reduce, dst)
+
+
+def exchange_sparse_partials(indptr, indices, values, group=None):
+    """Column-block all-to-all of sparse partial sketches (the sparse form of the reduce-scatter
+    above).  Every rank passes its partial s x d sketch as CSC tensors (int32 indptr/indices,
+    float64 values; CUDA with NCCL, CPU with gloo).  Rank r receives, for its block of columns
+    `shard_range(d, r, world)`, the entries of all ranks, stored per column in rank order --
+    the order of the global input index when rank r holds the r-th block of rows, so adding
+    equal (row, column) entries left to right reproduces the single-process sum.  Returns
+    (indptr, indices, values, (first_column, columns)); equal (row, column) entries are NOT yet
+    added (see sketch.coalesce / sl_sp_matrix_coalesce)."""
+    import torch
+    import torch.distributed as dist
+    d = indptr.numel() - 1
+    if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return indptr, indices, values, (0, d)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = indptr.device
+    blocks = [shard_range(d, r, world) for r in range(world)]
+    col0, ncols = blocks[rank]
+    ip = indptr.to(torch.int64)
+    edges = torch.tensor([b[0] for b in blocks] + [d], device=dev)
+    send_entries = (ip[edges[1:]] - ip[edges[:-1]]).tolist()            # entries per destination
+    counts = (ip[1:] - ip[:-1]).to(torch.int32).contiguous()            # entries per column
+    recv_counts = torch.empty(world * ncols, dtype=torch.int32, device=dev)
+    dist.all_to_all_single(recv_counts, counts, output_split_sizes=[ncols] * world,
+                           input_split_sizes=[b[1] for b in blocks], group=group)
+    C = recv_counts.view(world, ncols).to(torch.int64)                  # C[s, j]: entries of column j from rank s
+    recv_entries = C.sum(dim=1).tolist()
+    total = int(sum(recv_entries))
+    ridx = torch.empty(total, dtype=indices.dtype, device=dev)
+    rval = torch.empty(total, dtype=values.dtype, device=dev)
+    dist.all_to_all_single(ridx, indices.contiguous(), output_split_sizes=recv_entries,
+                           input_split_sizes=send_entries, group=group)
+    dist.all_to_all_single(rval, values.contiguous(), output_split_sizes=recv_entries,
+                           input_split_sizes=send_entries, group=group)
+    # received order is (rank, column); wanted order is (column, rank)
+    per_col = C.sum(dim=0)
+    out_indptr = torch.zeros(ncols + 1, dtype=torch.int64, device=dev)
+    out_indptr[1:] = torch.cumsum(per_col, 0)
+    flat = C.reshape(-1)
+    src_start = torch.cumsum(flat, 0) - flat
+    dst_start = (out_indptr[:-1].unsqueeze(0) + torch.cumsum(C, 0) - C).reshape(-1)
+    seg = torch.repeat_interleave(torch.arange(flat.numel(), device=dev), flat)
+    dest = dst_start[seg] + (torch.arange(total, device=dev) - src_start[seg])
+    oidx = torch.empty_like(ridx)
+    oval = torch.empty_like(rval)
+    oidx[dest] = ridx
+    oval[dest] = rval
+    return out_indptr.to(torch.int32), oidx, oval, (col0, ncols)
+
+
+def apply_distributed_sparse(S, A_local, index_offset=0, group=None):
+    """Columnwise CWT/MMT/WZT of a row-sharded device CSC matrix with a SPARSE exchange: every
+    rank sketches its rows into a sparse partial (lib.DeviceCSC, format "csc"), the partials
+    are exchanged by column block (exchange_sparse_partials) and merged on the device.
+    Returns (lib.DeviceCSC of shape s x columns_of_this_rank, (first_column, columns)).  For
+    sketches much sparser than s x d this moves nnz*12 bytes instead of the s*d*8 bytes of the
+    dense reduce-scatter (config C4: 1.5 GB instead of 16 GB per GPU)."""
+    from . import lib, sketch
+    part = S.apply_shard(A_local, lib.DeviceCSC.empty((S.getsketchdim(), A_local.shape[1]), "csc",
+                                                       A_local.values.device), 0, index_offset)
+    ip, ix, vv, (c0, nc) = exchange_sparse_partials(part.indptr, part.indices, part.values, group)
+    merged = lib.DeviceCSC(ip, ix, vv, (S.getsketchdim(), nc), "csc")
+    return sketch.coalesce(merged), (c0, nc)

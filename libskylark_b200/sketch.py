@@ -43,6 +43,24 @@ def _supported():
 SUPPORTED_SKETCH_TRANSFORMS = _supported()
 
 
+def coalesce(A):
+    """Adds entries of a lib.DeviceCSC that share (row, column), in storage order, and sorts the
+    rows of every column (sl_sp_matrix_coalesce).  Returns a new lib.DeviceCSC."""
+    out = lib.DeviceCSC.empty(A.shape, A.format, A.values.device)
+    a, o = lib.DeviceCSCAdapter(A), lib.DeviceCSCAdapter(out)
+    lib.set_stream_from_torch()
+    ap = a.ptr()
+    try:
+        op = o.ptr()
+        try:
+            lib.callsl("sl_sp_matrix_coalesce", ap, op)
+        finally:
+            o.ptrcleaner()
+    finally:
+        a.ptrcleaner()
+    return out
+
+
 def deserialize_sketch(sketch_dict):
     """Rebuild a transform from `.serialize()` output (sketch.py:33-42)."""
     sketch_transform = c_void_p()

@@ -63,3 +63,43 @@ def test_row_sharded_sum_world2(tmp_path, mode):
     port = _free_port()
     mp.spawn(_worker, args=(2, port, mode, str(tmp_path)), nprocs=2, join=True)
     assert os.path.exists(tmp_path / "ok0") and os.path.exists(tmp_path / "ok1")
+
+
+def _sparse_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import scipy.sparse
+    from libskylark_b200.dist import exchange_sparse_partials, shard_range
+    from oracle import oracle as o
+    n, d, s = 300, 11, 7                      # s small: many equal (row, column) entries to merge
+    A = scipy.sparse.random(n, d, 0.3, format="csc", random_state=5, dtype=np.float64)
+    t = o.CWT(n, s, o.Context(41))
+    full = t.apply_csc_sparse(A, "columnwise")
+    off, cnt = shard_range(n, rank, world)
+    # this rank's rows only (global row ids kept) -> its sparse partial sketch
+    mask = (A.indices >= off) & (A.indices < off + cnt)
+    colid = np.repeat(np.arange(d), np.diff(A.indptr))
+    Ash = scipy.sparse.csc_matrix((A.data[mask], (A.indices[mask], colid[mask])), shape=(n, d))
+    part = t.apply_csc_sparse(Ash, "columnwise")
+    part.sort_indices()
+    ip, ix, vv, (c0, nc) = exchange_sparse_partials(
+        torch.from_numpy(part.indptr.astype(np.int32)), torch.from_numpy(part.indices.astype(np.int32)),
+        torch.from_numpy(part.data.copy()), None)
+    assert (c0, nc) == shard_range(d, rank, world)
+    assert int(ip[-1]) == ix.numel() == vv.numel()
+    # entries of one column arrive in rank order: rank 0's rows first
+    merged = scipy.sparse.csc_matrix((vv.numpy().copy(), ix.numpy().copy(), ip.numpy().copy()), shape=(s, nc))
+    merged.sum_duplicates()
+    want = full[:, c0:c0 + nc]
+    np.testing.assert_allclose(merged.toarray(), want.toarray(), rtol=1e-13, atol=1e-13)
+    dist.barrier()
+    dist.destroy_process_group()
+    open(os.path.join(out_dir, "ok%d" % rank), "w").write("ok")
+
+
+def test_sparse_partials_exchange_world2(tmp_path):
+    # the sparse form of the reduce-scatter: column-block all-to-all of CSC partial sketches
+    port = _free_port()
+    mp.spawn(_sparse_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    assert os.path.exists(tmp_path / "ok0") and os.path.exists(tmp_path / "ok1")

@@ -96,7 +96,9 @@ def _canon(M):
 @pytest.mark.parametrize("fmt", ["csc", "csr"])
 @pytest.mark.parametrize("T", ["CWT", "MMT", "WZT"])
 @pytest.mark.parametrize("shape", [(3000, 64, 41, 0.05), (500, 3, 200, 0.3), (40, 1, 7, 0.9),
-                                   (2000, 5000, 30, 0.02)])
+                                   (2000, 5000, 30, 0.02),
+                                   # >= 256 entries per column: the per-column shared-memory sort
+                                   (6000, 64, 12, 0.2), (20000, 5000, 8, 0.09), (2100, 7, 5, 0.95)])
 def test_scipy_sparse_to_sparse_is_the_reference_result(sk, oracle, T, fmt, shape):
     # sparse -> sparse is the default for scipy inputs, as in the reference (lib.py:257-266).
     # Entries of one output slot are added in input order on both sides, so values are
@@ -135,6 +137,31 @@ def test_scipy_sparse_to_sparse_is_the_reference_result(sk, oracle, T, fmt, shap
     out = scipy.sparse.csc_matrix((s, d)) if fmt == "csc" else scipy.sparse.csr_matrix((s, d))
     ret = S.apply(A, out, 0)
     assert ret is out and rel_fro(out.toarray(), O.apply(A.toarray(), "columnwise")) < TOL
+
+
+def test_device_coalesce(sk):
+    # merge step of the sparse exchange: equal (row, column) entries added in storage order
+    import torch
+    from libskylark_b200 import lib
+    rng = np.random.default_rng(9)
+    s, d, per = 50, 37, 400                       # 400 entries per column over 50 rows: long runs
+    rows = rng.integers(0, s, size=(d, per)).astype(np.int32)
+    vals = rng.standard_normal((d, per))
+    indptr = np.arange(0, d * per + 1, per, dtype=np.int32)
+    A = lib.DeviceCSC(torch.tensor(indptr, device="cuda"), torch.tensor(rows.reshape(-1), device="cuda"),
+                      torch.tensor(vals.reshape(-1), device="cuda"), (s, d))
+    got = sk.coalesce(A).to_scipy()
+    want = np.zeros((s, d))
+    for j in range(d):                            # left-to-right sums, as the kernel promises
+        for r, v in zip(rows[j], vals[j]):
+            want[r, j] += v
+    assert got.has_sorted_indices or np.all(np.diff(got.indices[got.indptr[0]:got.indptr[1]]) > 0)
+    assert np.array_equal(got.toarray(), want)
+    short = lib.DeviceCSC(torch.tensor([0, 2, 2, 5], dtype=torch.int32, device="cuda"),
+                          torch.tensor([3, 3, 0, 4, 0], dtype=torch.int32, device="cuda"),
+                          torch.tensor([1.0, 2.0, 5.0, 7.0, -5.0], device="cuda", dtype=torch.float64), (6, 3))
+    g = sk.coalesce(short).to_scipy()
+    assert g.nnz == 3 and g[3, 0] == 3.0 and g[4, 2] == 7.0 and g[0, 2] == 0.0
 
 
 def test_sparse_to_sparse_rejects_other_transforms(sk):
