@@ -288,7 +288,90 @@ static DenseParams dense_params(const sl_sketch_transform_t *t) {
 // apply on device-resident operands
 // ---------------------------------------------------------------------------
 static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const sl_matrix_t *SA,
-                         int dim, int64_t offset, bool shard, bool accumulate = false) {
+                         int dim, int64_t offset, bool shard, bool accumulate);
+
+// Dense transform (JLT / CT / RFT) of a CSC operand -- the (T, SparseMatrix, Matrix) combinations of
+// capi/csketch.cpp:80,100,177,197.  Blocks of the sketched index are expanded to dense panels in
+// scratch and go through the dense kernels, panel results accumulating in SA; the work is that of
+// the dense sketch of the same shape (the reference realises all of S and multiplies, also O(s)
+// per stored entry plus the generation of S).
+__global__ void k_csc_expand_rows(const int32_t *__restrict__ indptr, const int32_t *__restrict__ indices,
+                                  const double *__restrict__ values, size_t ncols, int64_t k0, int64_t kc,
+                                  double *__restrict__ X) {       // X[(row-k0) + col*kc]
+    const int lane = threadIdx.x & 31;
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t j = warp; j < ncols; j += nwarps)
+        for (int p = indptr[j] + lane; p < indptr[j + 1]; p += 32) {
+            const int64_t r = indices[p];
+            if (r >= k0 && r < k0 + kc) atomicAdd(X + (r - k0) + j * kc, values[p]);
+        }
+}
+__global__ void k_csc_expand_cols(const int32_t *__restrict__ indptr, const int32_t *__restrict__ indices,
+                                  const double *__restrict__ values, int64_t k0, int64_t kc, size_t ld,
+                                  double *__restrict__ X) {       // X[(col-k0)*ld + row]
+    const int lane = threadIdx.x & 31;
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t kk = warp; kk < (size_t)kc; kk += nwarps)
+        for (int p = indptr[k0 + kk] + lane; p < indptr[k0 + kk + 1]; p += 32)
+            atomicAdd(X + kk * ld + indices[p], values[p]);
+}
+
+static void apply_dense_on_sparse(sl_sketch_transform_t *t, const sl_matrix_t *A, const sl_matrix_t *SA,
+                                  int dim, int64_t offset, bool shard) {
+    const bool colwise = dim == SL_COLUMNWISE, rft = t->is_rft();
+    const int64_t sk = colwise ? A->m : A->n, other = colwise ? A->n : A->m;
+    if (offset < 0 || offset + sk > t->N || (!shard && sk != t->N))
+        throw error(SKB_ERR_INVALID_PARAM, "apply: sketched dimension of A does not match N");
+    if (SA->kind != MK_DENSE || SA->dtype != SL_DTYPE_F64)
+        throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: a dense transform of a sparse matrix needs a float64 dense SA");
+    const int64_t sa_sk = colwise ? SA->m : SA->n, sa_other = colwise ? SA->n : SA->m;
+    if (sa_sk != t->S || sa_other != other) throw error(SKB_ERR_INVALID_PARAM, "apply: SA has the wrong shape");
+    if (sk == 0 || other == 0) return;
+    cudaStream_t st = g_stream;
+    static std::map<int, std::pair<void *, size_t>> scratch_per_dev;      // grow-only dense panel per device
+    auto &sc = scratch_per_dev[A->device];
+    const size_t budget = (size_t)1 << 30;
+    int64_t kc = (int64_t)(budget / ((size_t)other * 8)) / 16 * 16;
+    if (kc < 16) kc = 16;
+    if (kc > sk) kc = sk;
+    if (rft) {      // the cosine is not additive over panels: one panel or nothing
+        if ((size_t)sk * (size_t)other * 8 > ((size_t)16 << 30))
+            throw error(SKB_ERR_ALLOC, "apply: RFT of a sparse matrix expands it to dense; this one is too large");
+        kc = sk;
+    }
+    const size_t need = (size_t)kc * (size_t)other * 8;
+    if (sc.second < need) {
+        SKB_CUDA(cudaStreamSynchronize(st));
+        cudaFree(sc.first); sc.first = nullptr; sc.second = 0;
+        SKB_CUDA(cudaMalloc(&sc.first, need));
+        sc.second = need;
+    }
+    if (!rft)       // panels accumulate
+        SKB_CUDA(cudaMemset2DAsync(SA->data, (size_t)SA->ld * 8, 0, (size_t)SA->m * 8, (size_t)SA->n, st));
+    for (int64_t k0 = 0; k0 < sk; k0 += kc) {
+        const int64_t kn = sk - k0 < kc ? sk - k0 : kc;
+        SKB_CUDA(cudaMemsetAsync(sc.first, 0, (size_t)kn * (size_t)other * 8, st));
+        sl_matrix_t dA = *A;
+        dA.kind = MK_DENSE; dA.data = sc.first; dA.dtype = SL_DTYPE_F64;
+        {
+            LaunchScope ls(KC_MISC, st);
+            if (colwise) {
+                dA.m = kn; dA.n = other; dA.ld = kn;
+                k_csc_expand_rows<<<148 * 8, 256, 0, st>>>(A->indptr, A->indices, A->values, (size_t)A->n, k0, kn,
+                                                           (double *)sc.first);
+            } else {
+                dA.m = other; dA.n = kn; dA.ld = other;
+                k_csc_expand_cols<<<148 * 8, 256, 0, st>>>(A->indptr, A->indices, A->values, k0, kn, (size_t)other,
+                                                           (double *)sc.first);
+            }
+            SKB_CUDA(cudaGetLastError());
+        }
+        apply_device(t, &dA, SA, dim, offset + k0, true, !rft);
+    }
+}
+
+static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const sl_matrix_t *SA,
+                         int dim, int64_t offset, bool shard, bool accumulate) {
     const bool colwise = dim == SL_COLUMNWISE;
     const int64_t sk = colwise ? A->m : A->n;        // sketched extent present in A
     const int64_t other = colwise ? A->n : A->m;
@@ -309,7 +392,8 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
     if (accumulate && !t->is_dense())
         throw error(SKB_ERR_INVALID_USAGE, "apply: accumulation is implemented for JLT/CT only");
     if (A->kind == MK_SPARSE) {
-        if (!t->is_hash()) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: sparse input is supported for CWT/MMT/WZT only");
+        if (t->is_dense() || t->is_rft()) { apply_dense_on_sparse(t, A, SA, dim, offset, shard); return; }
+        if (!t->is_hash()) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: FJLT takes dense operands only");
         ensure_hash_tables(t, d);
         const int32_t *b = d.bucket + offset; const double *v = d.value + offset;
         if (colwise)
@@ -514,7 +598,7 @@ static void apply_any(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA,
         if (A->device != SA->device) throw error(SKB_ERR_INVALID_USAGE, "apply: A and SA are on different devices");
         DeviceGuard g(A->device);
         if (SA->kind == MK_SPARSE) apply_sparse_out(t, A, SA, dim, offset, shard, A->device);
-        else apply_device(t, A, SA, dim, offset, shard);
+        else apply_device(t, A, SA, dim, offset, shard, false);
         return;
     }
     if (SA->kind == MK_SPARSE && A->kind != MK_SPARSE)
@@ -555,7 +639,7 @@ static void apply_any(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA,
         size_t obytes = (size_t)SA->ld * (size_t)SA->n * (SA->dtype == SL_DTYPE_F32 ? 4 : 8);
         SKB_CUDA(cudaMalloc(&bufs[3], obytes ? obytes : 16));
         dSA.data = bufs[3];
-        apply_device(t, &dA, &dSA, dim, offset, shard);
+        apply_device(t, &dA, &dSA, dim, offset, shard, false);
         SKB_CUDA(cudaMemcpyAsync(SA->data, bufs[3], obytes, cudaMemcpyDeviceToHost, st));
         SKB_CUDA(cudaStreamSynchronize(st));
     } catch (...) {
@@ -637,8 +721,8 @@ extern "C" {
 
 char *sl_supported_sketch_transforms(void) {
     static char s[] =
-        "(\"JLT\",\"Matrix\",\"Matrix\") "
-        "(\"CT\",\"Matrix\",\"Matrix\") "
+        "(\"JLT\",\"Matrix\",\"Matrix\") (\"JLT\",\"SparseMatrix\",\"Matrix\") "
+        "(\"CT\",\"Matrix\",\"Matrix\") (\"CT\",\"SparseMatrix\",\"Matrix\") "
         "(\"FJLT\",\"Matrix\",\"Matrix\") "
         "(\"CWT\",\"Matrix\",\"Matrix\") (\"CWT\",\"SparseMatrix\",\"Matrix\") "
         "(\"CWT\",\"SparseMatrix\",\"SparseMatrix\") "
@@ -646,8 +730,8 @@ char *sl_supported_sketch_transforms(void) {
         "(\"MMT\",\"SparseMatrix\",\"SparseMatrix\") "
         "(\"WZT\",\"Matrix\",\"Matrix\") (\"WZT\",\"SparseMatrix\",\"Matrix\") "
         "(\"WZT\",\"SparseMatrix\",\"SparseMatrix\") "
-        "(\"GaussianRFT\",\"Matrix\",\"Matrix\") "
-        "(\"LaplacianRFT\",\"Matrix\",\"Matrix\") ";
+        "(\"GaussianRFT\",\"Matrix\",\"Matrix\") (\"GaussianRFT\",\"SparseMatrix\",\"Matrix\") "
+        "(\"LaplacianRFT\",\"Matrix\",\"Matrix\") (\"LaplacianRFT\",\"SparseMatrix\",\"Matrix\") ";
     return s;
 }
 

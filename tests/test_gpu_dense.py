@@ -141,3 +141,29 @@ def test_edge_shapes(sk, oracle):
     assert rel_fro(J1.apply(a.copy(), None, 0), OJ1.apply(a, "columnwise")) < TOL64
     v = np.random.default_rng(1).standard_normal((37, 1))        # a single vector
     assert rel_fro(J.apply(v.copy(), None, 0), OJ.apply(v, "columnwise")) < TOL64
+
+
+@pytest.mark.parametrize("fmt", ["csc", "csr"])
+@pytest.mark.parametrize("T", ["JLT", "CT", "GaussianRFT", "LaplacianRFT"])
+def test_dense_transform_of_sparse_operand(sk, oracle, T, fmt):
+    # (T, SparseMatrix, Matrix) of capi/csketch.cpp:80,100,177,197: same result as for the dense
+    # matrix with the same entries
+    import scipy.sparse
+    from libskylark_b200 import lib
+    n, s, d = 700, 48, 23
+    mk = {"JLT": lambda m, c: m.JLT(n, s, c), "CT": lambda m, c: m.CT(n, s, 2.5, c),
+          "GaussianRFT": lambda m, c: m.GaussianRFT(n, s, 3.0, c),
+          "LaplacianRFT": lambda m, c: m.LaplacianRFT(n, s, 3.0, c)}[T]
+    S, O = mk(sk, lib.Context(31)), mk(oracle, oracle.Context(31))
+    tol = 1e-10 if T == "LaplacianRFT" else 1e-12
+    order = "F" if fmt == "csc" else "C"
+    A = scipy.sparse.random(n, d, 0.1, format=fmt, random_state=2, dtype=np.float64)
+    got = S.apply(A, np.empty((s, d), order=order), "columnwise")
+    assert rel_fro(got, O.apply(A.toarray(), "columnwise")) < tol
+    B = scipy.sparse.random(d, n, 0.1, format=fmt, random_state=3, dtype=np.float64)
+    got = S.apply(B, np.empty((d, s), order=order), "rowwise")
+    assert rel_fro(got, O.apply(B.toarray(), "rowwise")) < tol
+    params = {"JLT": (), "CT": (2.5,), "GaussianRFT": (3.0,), "LaplacianRFT": (3.0,)}[T]
+    S2 = getattr(sk, T)(n, s, *params, defouttype="LocalMatrix", context=lib.Context(31))
+    got = S2.apply(A, None, 0)                          # the reference's way to ask for a dense result
+    assert isinstance(got, np.ndarray) and rel_fro(got, O.apply(A.toarray(), "columnwise")) < tol
