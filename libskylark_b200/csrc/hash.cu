@@ -618,29 +618,37 @@ static void sp_alloc(T **p, size_t bytes, cudaStream_t st) {
 // cudaFree accepts pool allocations (no implicit synchronisation: callers are done with p)
 void hash_sparse_free(void *p, cudaStream_t st) { if (p) { cudaStreamSynchronize(st); cudaFree(p); } }
 
-// K2s fast path (columnwise, every column <= 2048 entries): one CTA sorts a column at a
+// K2s fast path (columnwise, every column <= 10240 entries): one CTA sorts a column at a
 // time in shared memory.  Key = bucket << PB | position in the column; a keys-only stable block
 // radix sort over the bucket bits groups the buckets and the values are fetched through the position.  Equal
 // buckets are then added left to right (input order, as the reference does) by the thread that
 // holds the head of the run.  Results go to scratch at the column's input offset; a second
 // kernel packs the columns once the output offsets are known.
-static constexpr int SPC_THREADS = 256;
+#ifndef SKB_SPC_RADIX
+#define SKB_SPC_RADIX 4
+#endif
+template <int THREADS, int ITEMS>
+struct SpcTypes {
+    static constexpr int CAP = THREADS * ITEMS;
+    using Sort = cub::BlockRadixSort<uint32_t, THREADS, ITEMS, cub::NullType, SKB_SPC_RADIX>;
+    using Scan = cub::BlockScan<int, THREADS>;
+    union Tmp { typename Sort::TempStorage sort; typename Scan::TempStorage scan; };
+    static constexpr size_t tmp_bytes = (sizeof(Tmp) + 15) / 16 * 16;
+    static constexpr size_t smem_bytes = tmp_bytes + (size_t)CAP * 8 + ((size_t)CAP + 4) * 4;
+};
 
-template <int ITEMS>
-__global__ void __launch_bounds__(SPC_THREADS)
+template <int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS)
 k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ indices,
               const double *__restrict__ values, int ncols, const int32_t *__restrict__ bucket,
               const double *__restrict__ value, int pos_bits, int key_bits,
               int32_t *__restrict__ tmp_idx, double *__restrict__ tmp_val, int32_t *__restrict__ cnt) {
-    constexpr int CAP = SPC_THREADS * ITEMS;
-#ifndef SKB_SPC_RADIX
-#define SKB_SPC_RADIX 4
-#endif
-    using Sort = cub::BlockRadixSort<uint32_t, SPC_THREADS, ITEMS, cub::NullType, SKB_SPC_RADIX>;
-    using Scan = cub::BlockScan<int, SPC_THREADS>;
-    __shared__ union { typename Sort::TempStorage sort; typename Scan::TempStorage scan; } tmp;
-    __shared__ uint32_t skeys[CAP + 1];
-    __shared__ double svals[CAP];
+    using T = SpcTypes<THREADS, ITEMS>;
+    constexpr int CAP = T::CAP;
+    extern __shared__ __align__(16) unsigned char spc_smem[];
+    typename T::Tmp &tmp = *reinterpret_cast<typename T::Tmp *>(spc_smem);
+    double *svals = reinterpret_cast<double *>(spc_smem + T::tmp_bytes);
+    uint32_t *skeys = reinterpret_cast<uint32_t *>(svals + CAP);
     const uint32_t pmask = (1u << pos_bits) - 1u;
     for (int col = blockIdx.x; col < ncols; col += gridDim.x) {
         const int c0 = indptr[col], cn = indptr[col + 1] - c0;
@@ -657,7 +665,7 @@ k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ in
         }
         // the radix sort is stable and the entries start in column order, so only the bucket
         // bits need sorting (padding keys are all ones and stay behind)
-        Sort(tmp.sort).Sort(keys, pos_bits, key_bits);   // blocked output
+        typename T::Sort(tmp.sort).Sort(keys, pos_bits, key_bits);   // blocked output
 #pragma unroll
         for (int t = 0; t < ITEMS; t++) skeys[threadIdx.x * ITEMS + t] = keys[t];
         if (threadIdx.x == 0) skeys[CAP] = 0xffffffffu;
@@ -671,7 +679,7 @@ k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ in
             nhead += head[t];
         }
         int off, total;
-        Scan(tmp.scan).ExclusiveSum(nhead, off, total);
+        typename T::Scan(tmp.scan).ExclusiveSum(nhead, off, total);
 #pragma unroll
         for (int t = 0; t < ITEMS; t++) {
             if (head[t]) {
@@ -687,6 +695,22 @@ k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ in
         if (threadIdx.x == 0) cnt[col] = total;
         __syncthreads();                               // shared arrays are reused by the next column
     }
+}
+
+template <int THREADS, int ITEMS>
+static void launch_sp_col_sort(const int32_t *indptr, const int32_t *indices, const double *values,
+                               int ncols, const int32_t *bucket, const double *value, int pos_bits,
+                               int key_bits, int32_t *tmp_idx, double *tmp_val, int32_t *cnt, cudaStream_t st) {
+    using T = SpcTypes<THREADS, ITEMS>;
+    auto kern = k_sp_col_sort<THREADS, ITEMS>;
+    SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::smem_bytes));
+    size_t per_sm = (size_t)(220 * 1024) / T::smem_bytes;
+    if (per_sm * THREADS > 2048) per_sm = 2048 / THREADS;
+    if (per_sm < 1) per_sm = 1;
+    const unsigned grid = (unsigned)std::min<size_t>((size_t)ncols, 148 * per_sm);
+    kern<<<grid, THREADS, T::smem_bytes, st>>>(indptr, indices, values, ncols, bucket, value, pos_bits,
+                                               key_bits, tmp_idx, tmp_val, cnt);
+    SKB_CUDA(cudaGetLastError());
 }
 
 __global__ void k_sp_col_pack(const int32_t *__restrict__ indptr, const int32_t *__restrict__ out_indptr,
@@ -744,21 +768,23 @@ static bool sparse_columnwise_fast(const int32_t *indptr, const int32_t *indices
     int32_t maxc = 0;
     SKB_CUDA(cudaMemcpyAsync(&maxc, dmax, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     SKB_CUDA(cudaStreamSynchronize(st));
-    int items = maxc <= SPC_THREADS * 2 ? 2 : maxc <= SPC_THREADS * 4 ? 4 : maxc <= SPC_THREADS * 8 ? 8 : 0;
+    // capacity classes: (threads, entries per thread)
+    const int cap = maxc <= 512 ? 512 : maxc <= 1024 ? 1024 : maxc <= 2048 ? 2048 : maxc <= 5120 ? 5120 :
+                    maxc <= 10240 ? 10240 : 0;
     int pos_bits = 1, bucket_bits = 1;
-    while ((1 << pos_bits) < SPC_THREADS * (items ? items : 1)) pos_bits++;
+    while ((1 << pos_bits) < (cap ? cap : 1)) pos_bits++;
     while ((1LL << bucket_bits) < (long long)S) bucket_bits++;
-    if (!items || pos_bits + bucket_bits > 32) return false;
+    if (!cap || pos_bits + bucket_bits > 32) return false;
     sp_alloc(out_indptr, (ncols + 1) * sizeof(int32_t), st);
     SKB_CUDA(cudaMemsetAsync(cnt + ncols, 0, sizeof(int32_t), st));
-    const unsigned grid = (unsigned)std::min<size_t>(ncols, 148 * 4);
     {
         LaunchScope ls(KC_HASH, st);
-        const int kb = pos_bits + bucket_bits;
-        if (items == 2) k_sp_col_sort<2><<<grid, SPC_THREADS, 0, st>>>(indptr, indices, values, (int)ncols, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt);
-        else if (items == 4) k_sp_col_sort<4><<<grid, SPC_THREADS, 0, st>>>(indptr, indices, values, (int)ncols, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt);
-        else k_sp_col_sort<8><<<grid, SPC_THREADS, 0, st>>>(indptr, indices, values, (int)ncols, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt);
-        SKB_CUDA(cudaGetLastError());
+        const int kb = pos_bits + bucket_bits, nc = (int)ncols;
+        if (cap == 512) launch_sp_col_sort<256, 2>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st);
+        else if (cap == 1024) launch_sp_col_sort<256, 4>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st);
+        else if (cap == 2048) launch_sp_col_sort<256, 8>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st);
+        else if (cap == 5120) launch_sp_col_sort<512, 10>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st);
+        else launch_sp_col_sort<512, 20>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st);
     }
     {
         LaunchScope ls(KC_HASH, st);

@@ -98,7 +98,8 @@ def _canon(M):
 @pytest.mark.parametrize("shape", [(3000, 64, 41, 0.05), (500, 3, 200, 0.3), (40, 1, 7, 0.9),
                                    (2000, 5000, 30, 0.02),
                                    # >= 256 entries per column: the per-column shared-memory sort
-                                   (6000, 64, 12, 0.2), (20000, 5000, 8, 0.09), (2100, 7, 5, 0.95)])
+                                   (6000, 64, 12, 0.2), (20000, 5000, 8, 0.09), (2100, 7, 5, 0.95),
+                                   (30000, 900, 3, 0.15), (12000, 20000, 4, 0.8)])     # 4500 / 9600 per column
 def test_scipy_sparse_to_sparse_is_the_reference_result(sk, oracle, T, fmt, shape):
     # sparse -> sparse is the default for scipy inputs, as in the reference (lib.py:257-266).
     # Entries of one output slot are added in input order on both sides, so values are
