@@ -423,6 +423,28 @@ def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
             out["c4_cwt_csc_sparse_exchange"] = {"error": repr(e)[:300]}
         del A, S, indptr, indices, values
         torch.cuda.empty_cache()
+        # the partition that needs no exchange at all: shard the COLUMNS of A (every GPU holds all
+        # 1e7 rows of d/world columns, the same 1.25e8 nnz) -> each GPU owns its columns of SA outright
+        try:
+            dc, nnz_c = d // world, nnz_col * world
+            n_all = n_loc * world
+            g = torch.Generator(device=dev).manual_seed(DATA_SEED + 100 + rank)
+            indptr = (torch.arange(dc + 1, device=dev, dtype=torch.int64) * nnz_c).to(torch.int32)
+            indices = torch.randint(0, n_all, (dc * nnz_c,), device=dev, dtype=torch.int32, generator=g)
+            values = torch.randn(dc * nnz_c, dtype=torch.float64, device=dev, generator=g)
+            A = lib.DeviceCSC(indptr, indices, values, (n_all, dc))
+            S = sketch.CWT(n_all, s, lib.Context(SKETCH_SEED))
+            SA = torch.empty(dc, s, dtype=torch.float64, device=dev).t()
+            ms = timed(lambda: S.apply(A, SA, "columnwise"), 3)
+            out["c4_cwt_csc_column_sharded"] = {
+                "workload": "C4: same 1e7 x 1e5 matrix, COLUMNS sharded over %d GPUs (all rows of %d columns each): "
+                            "no collective, each GPU owns its %d columns of SA (dense)" % (world, dc, dc),
+                "ms": ms, "value": world * (dc * nnz_c * 12 + (dc + 1) * 4 + s * dc * 8) / (ms * 1e-3) / 1e9,
+                "unit": "GB/s (all GPUs)", "scaling": "strong"}
+            del A, S, SA, indptr, indices, values
+        except Exception as e:
+            out["c4_cwt_csc_column_sharded"] = {"error": repr(e)[:300]}
+        torch.cuda.empty_cache()
 
     # ---- C5
     m, n, s = 500_000, 784, 16384
