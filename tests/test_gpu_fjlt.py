@@ -29,7 +29,8 @@ def test_fjlt_power_of_two(sk, oracle, fut, shape):
     assert rel_fro(S.apply(B, None, "rowwise"), want.T) < TOL
 
 
-@pytest.mark.parametrize("shape", [(8192, 700, 1000), (32768, 9000, 450), (16384, 100, 149)])
+@pytest.mark.parametrize("shape", [(8192, 700, 1000), (32768, 9000, 450), (16384, 100, 149),
+                                   (8192, 50, 1), (16384, 50, 2), (65536, 8192, 3)])
 def test_wht_many_columns_per_cta(sk, oracle, shape):
     # more columns than SMs: every CTA of the streaming kernel walks several columns, so its
     # ring of shared buffers and both butterfly groups wrap across column boundaries
