@@ -69,6 +69,34 @@ def main():
                    "fjlt_D": f.D.tolist(), "fjlt_samples": [int(x) for x in f.samples],
                    "counter_after": c.counter})
     g["transforms_in_sequence"] = tr
+    # end results on a fixed small input: A[i, j] = ((7 i + 3 j) mod 11 - 5) / 4 (exact in binary)
+    n, d = 64, 3
+    A = (((7 * np.arange(n)[:, None] + 3 * np.arange(d)[None, :]) % 11) - 5) / 4.0
+    Asp = A * (((np.arange(n)[:, None] + 2 * np.arange(d)[None, :]) % 3) == 0)       # about a third kept
+    ap = {"n": n, "d": d, "seed": 123834, "input": "A[i,j] = ((7i+3j) mod 11 - 5)/4; sparse: kept where (i+2j) mod 3 == 0"}
+
+    def hx(M):
+        return [x.hex() for x in np.asarray(M, dtype=np.float64).ravel(order="F").tolist()]
+    import scipy.sparse
+    c = o.Context(123834)
+    cw = o.CWT(n, 5, c)
+    ap["cwt_columnwise"] = hx(cw.apply(A, "columnwise"))
+    ap["cwt_rowwise_of_transpose"] = hx(cw.apply(np.ascontiguousarray(A.T), "rowwise"))
+    sp = cw.apply_csc_sparse(scipy.sparse.csc_matrix(Asp), "columnwise")
+    sp.sort_indices()
+    ap["cwt_sparse_columnwise"] = {"indptr": sp.indptr.tolist(), "indices": sp.indices.tolist(),
+                                   "data": [x.hex() for x in sp.data.tolist()]}
+    ap["mmt_columnwise"] = hx(o.MMT(n, 4, c).apply(A, "columnwise"))
+    ap["wzt_columnwise"] = hx(o.WZT(n, 4, 1.5, c).apply(A, "columnwise"))
+    ap["jlt_columnwise"] = hx(o.JLT(n, 6, c).apply(A, "columnwise"))
+    ap["ct_columnwise"] = hx(o.CT(n, 6, 2.0, c).apply(A, "columnwise"))
+    ap["gaussian_rft_columnwise"] = hx(o.GaussianRFT(n, 7, 3.0, c).apply(A, "columnwise"))
+    ap["laplacian_rft_columnwise"] = hx(o.LaplacianRFT(n, 7, 3.0, c).apply(A, "columnwise"))
+    fj = o.FJLT(n, 8, c)
+    ap["fjlt_dct_columnwise"] = hx(fj.apply(A, "columnwise", fut="dct"))
+    ap["fjlt_wht_columnwise"] = hx(fj.apply(A, "columnwise", fut="wht"))
+    ap["counter_after"] = c.counter
+    g["applies"] = ap
     with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden.json"), "w") as fh:
         json.dump(g, fh, indent=1)
     print("wrote golden.json")

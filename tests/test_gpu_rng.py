@@ -114,3 +114,41 @@ def test_fjlt_tables_and_overlap(sk, oracle):
     of = oracle.FJLT(4096, 500, oracle.Context(31, 1000))
     assert np.array_equal(f.diagonal(), of.D)
     assert np.array_equal(f.samples(), of.samples.astype(np.int64))
+
+
+def test_golden_applies_on_the_gpu(sk):
+    # same sequence of transforms from one context as tests/golden/make_golden.py, end results
+    # against the committed fixture (no oracle involved at run time)
+    import scipy.sparse
+    from libskylark_b200 import lib
+    from util import golden_input, unhex, rel_fro
+    g = GOLDEN["applies"]
+    n, d = g["n"], g["d"]
+    A, Asp = golden_input(n, d)
+    AF = np.asfortranarray(A)
+    c = lib.Context(g["seed"])
+    cw = sk.CWT(n, 5, c)
+    assert np.array_equal(cw.apply(AF, None, "columnwise"), unhex(g["cwt_columnwise"], (5, d)))
+    assert np.array_equal(cw.apply(np.ascontiguousarray(A.T), None, "rowwise"),
+                          unhex(g["cwt_rowwise_of_transpose"], (d, 5)))
+    sp = cw.apply(scipy.sparse.csc_matrix(Asp), None, "columnwise")
+    sp.sort_indices()
+    assert sp.indptr.tolist() == g["cwt_sparse_columnwise"]["indptr"]
+    assert sp.indices.tolist() == g["cwt_sparse_columnwise"]["indices"]
+    assert [x.hex() for x in sp.data.tolist()] == g["cwt_sparse_columnwise"]["data"]
+    seq = [("mmt_columnwise", sk.MMT(n, 4, c), 4, 1e-12), ("wzt_columnwise", sk.WZT(n, 4, 1.5, c), 4, 1e-12),
+           ("jlt_columnwise", sk.JLT(n, 6, c), 6, 1e-12), ("ct_columnwise", sk.CT(n, 6, 2.0, c), 6, 1e-12),
+           ("gaussian_rft_columnwise", sk.GaussianRFT(n, 7, 3.0, c), 7, 1e-12),
+           ("laplacian_rft_columnwise", sk.LaplacianRFT(n, 7, 3.0, c), 7, 1e-10)]
+    for key, t, s, tol in seq:
+        assert rel_fro(t.apply(AF, None, "columnwise"), unhex(g[key], (s, d))) < tol, key
+    base = c.counter                                   # where the fixture created its FJLT
+    for fut in ("dct", "wht"):
+        lib.set_option("fjlt_fut", fut)
+        try:
+            cf = lib.Context(g["seed"], base)
+            fj = sk.FJLT(n, 8, cf)
+        finally:
+            lib.set_option("fjlt_fut", "dct")
+        assert rel_fro(fj.apply(AF, None, "columnwise"), unhex(g["fjlt_%s_columnwise" % fut], (8, d))) < 1e-12
+        assert cf.counter == g["counter_after"]

@@ -151,3 +151,31 @@ def test_wht(oracle):
     x = np.arange(8.0)
     H = np.array([[(-1) ** bin(i & j).count("1") for j in range(8)] for i in range(8)], float)
     np.testing.assert_allclose(oracle.wht(x), H @ x)
+
+
+def test_golden_applies(oracle):
+    # end results of every transform on the fixed input, created in one sequence from one context
+    import scipy.sparse
+    from util import golden_input, unhex, rel_fro
+    g = GOLDEN["applies"]
+    n, d = g["n"], g["d"]
+    A, Asp = golden_input(n, d)
+    c = oracle.Context(g["seed"])
+    cw = oracle.CWT(n, 5, c)
+    assert np.array_equal(cw.apply(A, "columnwise"), unhex(g["cwt_columnwise"], (5, d)))
+    assert np.array_equal(cw.apply(np.ascontiguousarray(A.T), "rowwise"), unhex(g["cwt_rowwise_of_transpose"], (d, 5)))
+    sp = cw.apply_csc_sparse(scipy.sparse.csc_matrix(Asp), "columnwise")
+    sp.sort_indices()
+    assert sp.indptr.tolist() == g["cwt_sparse_columnwise"]["indptr"]
+    assert sp.indices.tolist() == g["cwt_sparse_columnwise"]["indices"]
+    assert [x.hex() for x in sp.data.tolist()] == g["cwt_sparse_columnwise"]["data"]
+    rest = [("mmt_columnwise", oracle.MMT(n, 4, c), 4, {}), ("wzt_columnwise", oracle.WZT(n, 4, 1.5, c), 4, {}),
+            ("jlt_columnwise", oracle.JLT(n, 6, c), 6, {}), ("ct_columnwise", oracle.CT(n, 6, 2.0, c), 6, {}),
+            ("gaussian_rft_columnwise", oracle.GaussianRFT(n, 7, 3.0, c), 7, {}),
+            ("laplacian_rft_columnwise", oracle.LaplacianRFT(n, 7, 3.0, c), 7, {})]
+    for key, t, s, kw in rest:
+        assert rel_fro(t.apply(A, "columnwise", **kw), unhex(g[key], (s, d))) < 1e-13, key
+    fj = oracle.FJLT(n, 8, c)
+    assert rel_fro(fj.apply(A, "columnwise", fut="dct"), unhex(g["fjlt_dct_columnwise"], (8, d))) < 1e-13
+    assert rel_fro(fj.apply(A, "columnwise", fut="wht"), unhex(g["fjlt_wht_columnwise"], (8, d))) < 1e-13
+    assert c.counter == g["counter_after"]
