@@ -553,11 +553,191 @@ static void dense_apply_t(const DenseParams &p, const TX *X, size_t ldx, size_t 
     }
 }
 
+// ---------------------------------------------------------------------------
+// K5c: fp32 operands in the strided layout with the whole contraction in one panel -- the
+// rowwise feature map of C5 (4M x 784 fp32 -> 16384).  The reference computes this case in
+// single precision (W is cast to float, then sgemm: dense_transform_data.hpp:90-99); FP64 DMMA
+// is far more precise than the 1e-5 bar asks and 10x slower than the fp32-class tensor path.
+// Here every fp32 operand is split into two TF32 numbers (hi + lo, 21 mantissa bits together)
+// and a product is three mma.sync.m16n8k8.tf32 (lo*hi, hi*lo, hi*hi) accumulated in fp32
+// ("3xTF32"), which keeps fp32-level accuracy; the cosine epilogue stays in fp64 and is fused.
+//   OUT[i + j*ldo] = f( sum_k Pf[k*S + i] * X[k + j*ldx] ),  i < S (features), j < m (points)
+// CTA tile 128(i) x 128(j) x 32(k), 8 warps (2 x 4, warp tile 64 x 32), 3-stage cp.async
+// pipeline, two CTAs per SM so that one CTA's cosines overlap the other's MMAs.
+// ---------------------------------------------------------------------------
+namespace tf32 {
+constexpr int TBM = 128, TBN = 128, TBK = 32, TSTAGES = 3, TNT = 256;
+constexpr int LDA = TBM + 8;      // floats, As[k][i]: = 8 mod 32 -> a fragment's 4 k-rows x 8 i hit 32 banks
+constexpr int LDB = TBK + 4;      // floats, Bs[j][k]: = 4 mod 32 -> 8 j-rows x 4 k hit 32 banks
+constexpr int STAGE_FLOATS = TBK * LDA + TBN * LDB;
+constexpr size_t SMEM = (size_t)TSTAGES * STAGE_FLOATS * sizeof(float);
+}  // namespace tf32
+
+struct Tf32Args {
+    const float *P; const float *X; float *OUT;
+    size_t S, m, K, ldx, ldo;
+    const double *scales, *shifts; double outscale; int has_epi;
+    int ntm; long long ntiles;
+};
+
+__global__ void k_panel_to_f32(const double *__restrict__ P, float *__restrict__ Pf, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) Pf[i] = (float)P[i];          // round to nearest, the reference's cast
+}
+
+__device__ __forceinline__ void split_tf32(float x, unsigned &hi, unsigned &lo) {
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+    const float r = x - __uint_as_float(hi);
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const unsigned (&a)[4], const unsigned (&b)[2]) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+__global__ void __launch_bounds__(tf32::TNT, 2) k_dense_gemm_tf32x3(Tf32Args a) {
+    using namespace tf32;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float *sm = reinterpret_cast<float *>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp & 1, wn = warp >> 1;              // 2 x 4 warps
+    const int g = lane >> 2, t = lane & 3;
+    const long long tile = blockIdx.x;
+    const size_t i0 = (size_t)(tile % a.ntm) * TBM, j0 = (size_t)(tile / a.ntm) * TBN;   // i fastest: the X tile stays in L2
+    const int nk = (int)((a.K + TBK - 1) / TBK);
+
+    auto load_stage = [&](int st, int kb) {
+        float *As = sm + (size_t)st * STAGE_FLOATS, *Bs = As + TBK * LDA;
+        const size_t k0 = (size_t)kb * TBK;
+#pragma unroll
+        for (int c = 0; c < (TBK * TBM / 4) / TNT; c++) {          // 4 chunks of 16 B per thread
+            const int q = tid + c * TNT, kk = q >> 5, ci = (q & 31) * 4;
+            const bool ok = k0 + kk < a.K && i0 + ci < a.S;        // S, K are multiples of 4 here
+            const float *src = ok ? a.P + (k0 + kk) * a.S + i0 + ci : a.P;
+            cp_async<16>(As + kk * LDA + ci, src, ok ? 16 : 0);
+        }
+#pragma unroll
+        for (int c = 0; c < (TBN * TBK / 4) / TNT; c++) {
+            const int q = tid + c * TNT, jj = q >> 3, ck = (q & 7) * 4;
+            const bool ok = j0 + jj < a.m && k0 + ck < a.K;
+            const float *src = ok ? a.X + (j0 + jj) * a.ldx + k0 + ck : a.X;
+            cp_async<16>(Bs + jj * LDB + ck, src, ok ? 16 : 0);
+        }
+        asm volatile("cp.async.commit_group;");
+    };
+
+    float acc[4][4][4];
+#pragma unroll
+    for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+        for (int ni = 0; ni < 4; ni++)
+#pragma unroll
+            for (int e = 0; e < 4; e++) acc[mi][ni][e] = 0.f;
+
+#pragma unroll
+    for (int s = 0; s < TSTAGES - 1; s++) {
+        if (s < nk) load_stage(s, s); else asm volatile("cp.async.commit_group;");
+    }
+    for (int kb = 0; kb < nk; kb++) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(TSTAGES - 2));
+        __syncthreads();
+        if (kb + TSTAGES - 1 < nk) load_stage((kb + TSTAGES - 1) % TSTAGES, kb + TSTAGES - 1);
+        else asm volatile("cp.async.commit_group;");
+        const float *As = sm + (size_t)(kb % TSTAGES) * STAGE_FLOATS, *Bs = As + TBK * LDA;
+#pragma unroll
+        for (int ks = 0; ks < TBK / 8; ks++) {
+            unsigned bh[4][2], bl[4][2];
+#pragma unroll
+            for (int ni = 0; ni < 4; ni++) {
+                const float *bp = Bs + (wn * 32 + ni * 8 + g) * LDB + ks * 8 + t;
+                split_tf32(bp[0], bh[ni][0], bl[ni][0]);
+                split_tf32(bp[4], bh[ni][1], bl[ni][1]);
+            }
+#pragma unroll
+            for (int mi = 0; mi < 4; mi++) {
+                const float *ap = As + (ks * 8 + t) * LDA + wm * 64 + mi * 16 + g;
+                unsigned ah[4], al[4];
+                split_tf32(ap[0], ah[0], al[0]);
+                split_tf32(ap[8], ah[1], al[1]);
+                split_tf32(ap[4 * LDA], ah[2], al[2]);
+                split_tf32(ap[4 * LDA + 8], ah[3], al[3]);
+#pragma unroll
+                for (int ni = 0; ni < 4; ni++) {       // small terms first
+                    mma_tf32(acc[mi][ni], al, bh[ni]);
+                    mma_tf32(acc[mi][ni], ah, bl[ni]);
+                    mma_tf32(acc[mi][ni], ah, bh[ni]);
+                }
+            }
+        }
+    }
+    asm volatile("cp.async.wait_group 0;");
+    // epilogue: c0 (g, 2t) c1 (g, 2t+1) c2 (g+8, 2t) c3 (g+8, 2t+1) of every 16 x 8 block
+#pragma unroll
+    for (int mi = 0; mi < 4; mi++) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const size_t i = i0 + wm * 64 + mi * 16 + g + h * 8;
+            if (i >= a.S) continue;
+            double sc = 1.0, sh = 0.0;
+            if (a.has_epi) { sc = a.scales[i]; sh = a.shifts[i]; }
+#pragma unroll
+            for (int ni = 0; ni < 4; ni++) {
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+                    const size_t j = j0 + wn * 32 + ni * 8 + 2 * t + e;
+                    if (j >= a.m) continue;
+                    double v = (double)acc[mi][ni][h * 2 + e];
+                    if (a.has_epi) v = __dmul_rn(a.outscale, cos(__dadd_rn(__dmul_rn(v, sc), sh)));
+                    a.OUT[i + j * a.ldo] = (float)v;
+                }
+            }
+        }
+    }
+}
+
+// Returns false when the shape does not qualify for the 3xTF32 path.
+static bool dense_apply_tf32x3(const DenseParams &p, const float *X, size_t ldx, size_t m, size_t koff,
+                               size_t nloc, float *OUT, size_t ldo, const RftEpilogue &epi,
+                               void *workspace, size_t workspace_bytes, cudaStream_t st) {
+    static const bool off = getenv("SKB_DEBUG_NO_TF32") != nullptr;
+    const size_t S = p.S;
+    if (off || S == 0 || m == 0 || nloc == 0) return false;
+    if (S % 4 || nloc % 4 || ldx % 4 || ((uintptr_t)X % 16)) return false;
+    const size_t pbytes = ((nloc * S * sizeof(double) + 255) / 256) * 256;
+    const size_t fbytes = ((nloc * S * sizeof(float) + 255) / 256) * 256;
+    if (nloc > panel_rows_for(S) || workspace_bytes < pbytes + fbytes) return false;
+    const long long ntm = (long long)((S + tf32::TBM - 1) / tf32::TBM), ntn = (long long)((m + tf32::TBN - 1) / tf32::TBN);
+    if (ntm * ntn > 0x7fffffffLL) return false;
+    double *P = reinterpret_cast<double *>(workspace);
+    float *Pf = reinterpret_cast<float *>(reinterpret_cast<char *>(workspace) + pbytes);
+    dense_generate_panel(p, koff, nloc, P, st);
+    {
+        LaunchScope ls(KC_GEN, st);
+        const size_t n = nloc * S;
+        k_panel_to_f32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(P, Pf, n);
+        SKB_CUDA(cudaGetLastError());
+    }
+    Tf32Args a;
+    a.P = Pf; a.X = X; a.OUT = OUT; a.S = S; a.m = m; a.K = nloc; a.ldx = ldx; a.ldo = ldo;
+    a.scales = epi.scales; a.shifts = epi.shifts; a.outscale = epi.outscale;
+    a.has_epi = epi.shifts != nullptr ? 1 : 0;
+    a.ntm = (int)ntm; a.ntiles = ntm * ntn;
+    SKB_CUDA(cudaFuncSetAttribute(k_dense_gemm_tf32x3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tf32::SMEM));
+    LaunchScope ls(KC_GEMM, st);
+    k_dense_gemm_tf32x3<<<(unsigned)a.ntiles, tf32::TNT, tf32::SMEM, st>>>(a);
+    SKB_CUDA(cudaGetLastError());
+    return true;
+}
+
 void dense_apply(const DenseParams &p, bool layout_rows, bool f32, const void *X, size_t ldx,
                  size_t m, size_t koff, size_t nloc, void *OUT, size_t ldo,
                  const RftEpilogue &epi, void *workspace, size_t workspace_bytes,
                  cudaStream_t st, bool accumulate) {
     if (f32) {
+        if (!layout_rows && !accumulate &&
+            dense_apply_tf32x3(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st))
+            return;
         if (layout_rows) dense_apply_t<float, true>(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st, accumulate);
         else dense_apply_t<float, false>(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st, accumulate);
     } else {
