@@ -591,9 +591,14 @@ __device__ __forceinline__ void split_tf32(float x, unsigned &hi, unsigned &lo) 
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
 }
 __device__ __forceinline__ void mma_tf32(float (&c)[4], const unsigned (&a)[4], const unsigned (&b)[2]) {
-    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+    asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+__device__ __forceinline__ void mma_tf32_zero(float (&d)[4], const unsigned (&a)[4], const unsigned (&b)[2]) {
+    asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+        : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]), "f"(0.f));
 }
 
 // The tensor core adds into its accumulator with truncation, so a long chain of accumulating
@@ -668,8 +673,8 @@ __global__ void __launch_bounds__(tf32::TNT, 2) k_dense_gemm_tf32x3(Tf32Args a) 
                 split_tf32(ap[4 * LDA + 8], ah[3], al[3]);
 #pragma unroll
                 for (int ni = 0; ni < 4; ni++) {
-                    float tmp[4] = {0.f, 0.f, 0.f, 0.f};
-                    mma_tf32(tmp, al, bh[ni]);         // small terms first
+                    float tmp[4];
+                    mma_tf32_zero(tmp, al, bh[ni]);    // small terms first
                     mma_tf32(tmp, ah, bl[ni]);
                     mma_tf32(tmp, ah, bh[ni]);
 #pragma unroll
