@@ -585,10 +585,12 @@ __global__ void k_panel_to_f32(const double *__restrict__ P, float *__restrict__
     if (i < n) Pf[i] = (float)P[i];          // round to nearest, the reference's cast
 }
 
+// hi = x with the 13 low mantissa bits cleared (a TF32 number), lo = x - hi (exact in fp32).
+// lo is passed as it is: the tensor core reads only the TF32 part of an operand, i.e. drops
+// lo's own low bits (2^-21 relative to x).  Two instructions per element.
 __device__ __forceinline__ void split_tf32(float x, unsigned &hi, unsigned &lo) {
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
-    const float r = x - __uint_as_float(hi);
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+    hi = __float_as_uint(x) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi));
 }
 __device__ __forceinline__ void mma_tf32(float (&c)[4], const unsigned (&a)[4], const unsigned (&b)[2]) {
     asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
