@@ -716,19 +716,30 @@ __global__ void __launch_bounds__(tf32::TNT, 2) k_dense_gemm_tf32x3(Tf32Args a) 
     }
 }
 
-// Returns false when the shape does not qualify for the 3xTF32 path.
-static bool dense_apply_tf32x3(const DenseParams &p, const float *X, size_t ldx, size_t m, size_t koff,
-                               size_t nloc, float *OUT, size_t ldo, const RftEpilogue &epi,
-                               void *workspace, size_t workspace_bytes, cudaStream_t st) {
+// Shapes the 3xTF32 path takes (fp32 operands, strided layout, no accumulation).
+bool dense_tf32_path_ok(const DenseParams &p, const void *X, size_t ldx, size_t m, size_t nloc) {
     static const bool off = getenv("SKB_DEBUG_NO_TF32") != nullptr;
     const size_t S = p.S;
     if (off || S == 0 || m == 0 || nloc == 0) return false;
     if (S % 4 || nloc % 4 || ldx % 4 || ((uintptr_t)X % 16)) return false;
+    if (nloc > panel_rows_for(S)) return false;
+    const long long ntm = (long long)((S + tf32::TBM - 1) / tf32::TBM), ntn = (long long)((m + tf32::TBN - 1) / tf32::TBN);
+    return ntm * ntn <= 0x7fffffffLL;
+}
+size_t dense_tf32_workspace_bytes(const DenseParams &p, size_t nloc) {
+    return ((nloc * p.S * sizeof(double) + 255) / 256) * 256 + ((nloc * p.S * sizeof(float) + 255) / 256) * 256 + 256;
+}
+
+// Returns false when the shape does not qualify for the 3xTF32 path.
+static bool dense_apply_tf32x3(const DenseParams &p, const float *X, size_t ldx, size_t m, size_t koff,
+                               size_t nloc, float *OUT, size_t ldo, const RftEpilogue &epi,
+                               void *workspace, size_t workspace_bytes, cudaStream_t st) {
+    const size_t S = p.S;
+    if (!dense_tf32_path_ok(p, X, ldx, m, nloc)) return false;
     const size_t pbytes = ((nloc * S * sizeof(double) + 255) / 256) * 256;
     const size_t fbytes = ((nloc * S * sizeof(float) + 255) / 256) * 256;
-    if (nloc > panel_rows_for(S) || workspace_bytes < pbytes + fbytes) return false;
+    if (workspace_bytes < pbytes + fbytes) return false;
     const long long ntm = (long long)((S + tf32::TBM - 1) / tf32::TBM), ntn = (long long)((m + tf32::TBN - 1) / tf32::TBN);
-    if (ntm * ntn > 0x7fffffffLL) return false;
     double *P = reinterpret_cast<double *>(workspace);
     float *Pf = reinterpret_cast<float *>(reinterpret_cast<char *>(workspace) + pbytes);
     dense_generate_panel(p, koff, nloc, P, st);
