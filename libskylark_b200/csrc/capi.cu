@@ -436,7 +436,7 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
         size_t need;
         if (f32 && !layout_rows && !accumulate &&
             dense_tf32_path_ok(p, A->data, (size_t)A->ld, (size_t)other, (size_t)sk))
-            need = dense_tf32_workspace_bytes(p, (size_t)sk);      // no fp64 image of SA needed
+            need = dense_tf32_workspace_bytes(p, (size_t)sk, (size_t)other);      // no fp64 image of SA needed
         else
             need = dense_workspace_bytes(p, (size_t)sk, layout_rows, f32, (size_t)other, (size_t)SA->ld);
         ensure_ws(d, need);

@@ -23,6 +23,7 @@
 //     quantisation; partial tiles are flushed with red.global.add.f64;
 //   * the RFT epilogue outscale*cos(scale_i*acc+shift_i) is fused into the flush
 //     when a CTA owns the whole contraction of a tile (the rowwise feature-map case).
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 
@@ -716,6 +717,211 @@ __global__ void __launch_bounds__(tf32::TNT, 2) k_dense_gemm_tf32x3(Tf32Args a) 
     }
 }
 
+// ---------------------------------------------------------------------------
+// K5d: the same 3xTF32 product on the 5th-generation tensor cores (tcgen05.mma.kind::tf32,
+// accumulators in TMEM).  The tensor core reads shared memory itself, so operands are split
+// BEFORE they get there: a pre-pass writes hi / lo copies of the panel (transposed to K-major)
+// and of X, padded with zeros to a multiple of 16 in k.  A CTA owns a 128(i) x 128(j) tile:
+// 4 producer warps fill a 3-stage ring with cp.async in the no-swizzle K-major core-matrix
+// layout (element (r,k) at (r/8)*512 + (k/4)*128 + (r%8)*16 + (k%4)*4), one thread issues the
+// MMAs -- hi*hi into one TMEM accumulator, lo*hi and hi*lo into a second one, so the long
+// truncating chain carries only the large term once -- and the producer warps, done loading,
+// read both accumulators back (tcgen05.ld), add them and apply the epilogue.  Two CTAs fit an
+// SM (96 KB of shared memory, 256 TMEM columns each): one's epilogue overlaps the other's MMAs.
+// Measured accumulator behaviour (tools/tcgen05_probe.cu): operands are truncated to TF32,
+// a chain of 100 accumulating MMAs loses 1.6e-6 (relative, Frobenius), 32 lose 2.3e-7.
+// ---------------------------------------------------------------------------
+namespace tc {
+constexpr int TM = 128, TN = 128, TK = 16, NSTAGE = 3;
+constexpr int PRODUCERS = 128, THREADS = PRODUCERS + 32;
+constexpr uint32_t LBO = 128, SBO = (TK / 4) * 128;            // bytes
+constexpr uint32_t TILE_BYTES = TM * TK * 4;                   // 8 KB
+constexpr uint32_t STAGE_BYTES = 4 * TILE_BYTES;               // P_hi, P_lo, X_hi, X_lo
+constexpr size_t SMEM = (size_t)NSTAGE * STAGE_BYTES + 256;    // + barriers, TMEM base
+constexpr uint32_t TMEM_COLS = 256;                            // main, cross
+}  // namespace tc
+
+// panel P[k*S + i] (fp64) -> Pt_hi / Pt_lo [i*Kp + k] (fp32 split, zero padded in k)
+__global__ void k_tc_split_panel(const double *__restrict__ P, size_t S, size_t K, size_t Kp,
+                                 float *__restrict__ hi, float *__restrict__ lo) {
+    __shared__ float tile[32][33];
+    const size_t i0 = (size_t)blockIdx.x * 32, k0 = (size_t)blockIdx.y * 32;
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {          // r = k, x = i (coalesced read)
+        const size_t k = k0 + r, i = i0 + threadIdx.x;
+        tile[r][threadIdx.x] = (k < K && i < S) ? (float)P[k * S + i] : 0.f;
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {          // r = i, x = k (coalesced write)
+        const size_t i = i0 + r, k = k0 + threadIdx.x;
+        if (i < S && k < Kp) {
+            const float x = tile[threadIdx.x][r];
+            const float h = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+            hi[i * Kp + k] = h;
+            lo[i * Kp + k] = x - h;
+        }
+    }
+}
+// X[j*ldx + k] (fp32) -> X_hi / X_lo [j*Kp + k]
+__global__ void k_tc_split_x(const float *__restrict__ X, size_t ldx, size_t m, size_t K, size_t Kp,
+                             float *__restrict__ hi, float *__restrict__ lo) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= m * Kp) return;
+    const size_t j = t / Kp, k = t - j * Kp;
+    const float x = k < K ? X[j * ldx + k] : 0.f;
+    const float h = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+    hi[t] = h;
+    lo[t] = x - h;
+}
+
+__device__ __forceinline__ uint64_t tc_desc(uint32_t saddr) {
+    return (uint64_t)((saddr >> 4) & 0x3fff) | ((uint64_t)(tc::LBO >> 4) << 16) |
+           ((uint64_t)(tc::SBO >> 4) << 32) | ((uint64_t)1 << 46);      // version 1, no swizzle
+}
+__device__ __forceinline__ void tc_mma(uint32_t tmem, uint64_t ad, uint64_t bd, uint32_t idesc, uint32_t accum) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem), "l"(ad), "l"(bd), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+struct TcArgs {
+    const float *Phi, *Plo, *Xhi, *Xlo; float *OUT;
+    size_t S, m, Kp, ldo;
+    const double *scales, *shifts; double outscale; int has_epi;
+    int ntm;
+};
+
+__global__ void __launch_bounds__(tc::THREADS, 2) k_dense_gemm_tc_tf32x3(TcArgs a) {
+    using namespace tc;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem_raw);
+    const uint32_t bars = sbase + NSTAGE * STAGE_BYTES;        // full[3], empty[3], accfull: 8 B each
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem_raw + NSTAGE * STAGE_BYTES + 64);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const size_t i0 = (size_t)(blockIdx.x % a.ntm) * TM, j0 = (size_t)(blockIdx.x / a.ntm) * TN;
+    const int nk = (int)(a.Kp / TK);
+    auto full_bar = [&](int s) { return bars + 8u * s; };
+    auto empty_bar = [&](int s) { return bars + 8u * (NSTAGE + s); };
+    const uint32_t acc_bar = bars + 8u * (2 * NSTAGE);
+
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; s++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full_bar(s)), "r"(PRODUCERS));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(empty_bar(s)));
+        }
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(acc_bar));
+        asm volatile("fence.mbarrier_init.release.cluster;");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(tmem_slot)), "n"(TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp < 4) {
+        // ===== producers: thread t loads row t of each of the four tiles (64 contiguous bytes) =====
+        const int r = tid;
+        const uint32_t drow = (uint32_t)(r >> 3) * SBO + (uint32_t)(r & 7) * 16;
+        const bool okp = i0 + r < a.S, okx = j0 + r < a.m;
+        const float *srcs[4] = {a.Phi + (okp ? (i0 + r) * a.Kp : 0), a.Plo + (okp ? (i0 + r) * a.Kp : 0),
+                                a.Xhi + (okx ? (j0 + r) * a.Kp : 0), a.Xlo + (okx ? (j0 + r) * a.Kp : 0)};
+        const int nbytes[4] = {okp ? 16 : 0, okp ? 16 : 0, okx ? 16 : 0, okx ? 16 : 0};
+        auto signal = [&](int kb) {            // this thread's loads of k-block kb have landed
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(full_bar(kb % NSTAGE));
+        };
+        for (int kb = 0; kb < nk; kb++) {
+            const int s = kb % NSTAGE;
+            if (kb >= NSTAGE) mbar_wait(empty_bar(s), (uint32_t)((kb / NSTAGE - 1) & 1));
+            const uint32_t dst = sbase + (uint32_t)s * STAGE_BYTES + drow;
+#pragma unroll
+            for (int tl = 0; tl < 4; tl++)
+#pragma unroll
+                for (int kc = 0; kc < TK / 4; kc++)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + tl * TILE_BYTES + kc * LBO),
+                                 "l"(srcs[tl] + (size_t)kb * TK + kc * 4), "r"(nbytes[tl]) : "memory");
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            if (kb >= 2) { asm volatile("cp.async.wait_group 2;" ::: "memory"); signal(kb - 2); }
+        }
+        if (nk >= 2) { asm volatile("cp.async.wait_group 1;" ::: "memory"); signal(nk - 2); }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        signal(nk - 1);
+        // ===== epilogue: warp w owns TMEM lanes [32w, 32w+32) = rows i, columns = j =====
+        mbar_wait(acc_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        const size_t i = i0 + (size_t)tid;
+        double sc = 1.0, sh = 0.0;
+        if (a.has_epi && i < a.S) { sc = a.scales[i]; sh = a.shifts[i]; }
+        for (int c0 = 0; c0 < TN; c0 += 8) {
+            uint32_t mn[8], cr[8];
+            const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(mn[0]), "=r"(mn[1]), "=r"(mn[2]), "=r"(mn[3]), "=r"(mn[4]), "=r"(mn[5]), "=r"(mn[6]), "=r"(mn[7])
+                         : "r"(taddr));
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(cr[0]), "=r"(cr[1]), "=r"(cr[2]), "=r"(cr[3]), "=r"(cr[4]), "=r"(cr[5]), "=r"(cr[6]), "=r"(cr[7])
+                         : "r"(taddr + (uint32_t)TN));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (i < a.S) {
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                    const size_t j = j0 + c0 + e;
+                    if (j >= a.m) break;
+                    float v = __uint_as_float(mn[e]) + __uint_as_float(cr[e]);
+                    if (a.has_epi) {
+                        const double arg = fma((double)v, sc, sh);
+                        const double q = rint(arg * 0.15915494309189535);
+                        const double rr = fma(q, -6.283185307179586, arg);
+                        v = (float)(a.outscale * (double)cosf((float)rr));
+                    }
+                    a.OUT[i + j * a.ldo] = v;
+                }
+            }
+        }
+    } else if (lane == 0) {
+        // ===== MMA issuer =====
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+        const uint32_t t_main = tmem, t_cross = tmem + (uint32_t)TN;
+        for (int kb = 0; kb < nk; kb++) {
+            const int s = kb % NSTAGE;
+            mbar_wait(full_bar(s), (uint32_t)((kb / NSTAGE) & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;");
+            const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+#pragma unroll
+            for (int ks = 0; ks < TK / 8; ks++) {
+                const uint32_t ko = (uint32_t)ks * 2 * LBO;
+                const uint64_t phi = tc_desc(st0 + ko), plo = tc_desc(st0 + TILE_BYTES + ko);
+                const uint64_t xhi = tc_desc(st0 + 2 * TILE_BYTES + ko), xlo = tc_desc(st0 + 3 * TILE_BYTES + ko);
+                const uint32_t first = (kb | ks) == 0 ? 0u : 1u;
+                tc_mma(t_cross, plo, xhi, idesc, first);
+                tc_mma(t_cross, phi, xlo, idesc, 1u);
+                tc_mma(t_main, phi, xhi, idesc, first);
+            }
+            tc_commit(empty_bar(s));          // frees the stage once these MMAs have read it
+        }
+        tc_commit(acc_bar);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    __syncwarp();
+    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(tc::TMEM_COLS));
+}
+
 // Shapes the 3xTF32 path takes (fp32 operands, strided layout, no accumulation).
 bool dense_tf32_path_ok(const DenseParams &p, const void *X, size_t ldx, size_t m, size_t nloc) {
     static const bool off = getenv("SKB_DEBUG_NO_TF32") != nullptr;
@@ -726,8 +932,12 @@ bool dense_tf32_path_ok(const DenseParams &p, const void *X, size_t ldx, size_t 
     const long long ntm = (long long)((S + tf32::TBM - 1) / tf32::TBM), ntn = (long long)((m + tf32::TBN - 1) / tf32::TBN);
     return ntm * ntn <= 0x7fffffffLL;
 }
-size_t dense_tf32_workspace_bytes(const DenseParams &p, size_t nloc) {
-    return ((nloc * p.S * sizeof(double) + 255) / 256) * 256 + ((nloc * p.S * sizeof(float) + 255) / 256) * 256 + 256;
+static size_t tc_workspace_bytes(const DenseParams &p, size_t nloc, size_t m);
+static bool tc_enabled();
+size_t dense_tf32_workspace_bytes(const DenseParams &p, size_t nloc, size_t m) {
+    size_t need = ((nloc * p.S * sizeof(double) + 255) / 256) * 256 + ((nloc * p.S * sizeof(float) + 255) / 256) * 256 + 256;
+    if (tc_enabled()) need = std::max(need, tc_workspace_bytes(p, nloc, m));
+    return need;
 }
 
 // Returns false when the shape does not qualify for the 3xTF32 path.
@@ -761,11 +971,65 @@ static bool dense_apply_tf32x3(const DenseParams &p, const float *X, size_t ldx,
     return true;
 }
 
+static bool tc_enabled() {
+    static const bool on = getenv("SKB_TF32_TCGEN05") != nullptr;
+    return on;
+}
+static size_t tc_kp(size_t K) { return (K + tc::TK - 1) / tc::TK * tc::TK; }
+static size_t tc_workspace_bytes(const DenseParams &p, size_t nloc, size_t m) {
+    auto al = [](size_t b) { return (b + 255) / 256 * 256; };
+    const size_t Kp = tc_kp(nloc);
+    return al(nloc * p.S * sizeof(double)) + 2 * al(p.S * Kp * 4) + 2 * al(m * Kp * 4) + 256;
+}
+
+static bool dense_apply_tc_tf32x3(const DenseParams &p, const float *X, size_t ldx, size_t m, size_t koff,
+                                  size_t nloc, float *OUT, size_t ldo, const RftEpilogue &epi,
+                                  void *workspace, size_t workspace_bytes, cudaStream_t st) {
+    if (!tc_enabled() || !dense_tf32_path_ok(p, X, ldx, m, nloc)) return false;
+    if (workspace_bytes < tc_workspace_bytes(p, nloc, m)) return false;
+    auto al = [](size_t b) { return (b + 255) / 256 * 256; };
+    const size_t S = p.S, Kp = tc_kp(nloc);
+    char *w = reinterpret_cast<char *>(workspace);
+    double *P = reinterpret_cast<double *>(w); w += al(nloc * S * sizeof(double));
+    float *Phi = reinterpret_cast<float *>(w); w += al(S * Kp * 4);
+    float *Plo = reinterpret_cast<float *>(w); w += al(S * Kp * 4);
+    float *Xhi = reinterpret_cast<float *>(w); w += al(m * Kp * 4);
+    float *Xlo = reinterpret_cast<float *>(w);
+    dense_generate_panel(p, koff, nloc, P, st);
+    {
+        LaunchScope ls(KC_GEN, st);
+        dim3 grid((unsigned)((S + 31) / 32), (unsigned)((Kp + 31) / 32));
+        k_tc_split_panel<<<grid, dim3(32, 8), 0, st>>>(P, S, nloc, Kp, Phi, Plo);
+        SKB_CUDA(cudaGetLastError());
+    }
+    {
+        LaunchScope ls(KC_MISC, st);
+        const size_t n = m * Kp;
+        k_tc_split_x<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(X, ldx, m, nloc, Kp, Xhi, Xlo);
+        SKB_CUDA(cudaGetLastError());
+    }
+    TcArgs a;
+    a.Phi = Phi; a.Plo = Plo; a.Xhi = Xhi; a.Xlo = Xlo; a.OUT = OUT;
+    a.S = S; a.m = m; a.Kp = Kp; a.ldo = ldo;
+    a.scales = epi.scales; a.shifts = epi.shifts; a.outscale = epi.outscale;
+    a.has_epi = epi.shifts != nullptr ? 1 : 0;
+    const long long ntm = (long long)((S + tc::TM - 1) / tc::TM), ntn = (long long)((m + tc::TN - 1) / tc::TN);
+    a.ntm = (int)ntm;
+    SKB_CUDA(cudaFuncSetAttribute(k_dense_gemm_tc_tf32x3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM));
+    LaunchScope ls(KC_GEMM, st);
+    k_dense_gemm_tc_tf32x3<<<(unsigned)(ntm * ntn), tc::THREADS, tc::SMEM, st>>>(a);
+    SKB_CUDA(cudaGetLastError());
+    return true;
+}
+
 void dense_apply(const DenseParams &p, bool layout_rows, bool f32, const void *X, size_t ldx,
                  size_t m, size_t koff, size_t nloc, void *OUT, size_t ldo,
                  const RftEpilogue &epi, void *workspace, size_t workspace_bytes,
                  cudaStream_t st, bool accumulate) {
     if (f32) {
+        if (!layout_rows && !accumulate &&
+            dense_apply_tc_tf32x3(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st))
+            return;
         if (!layout_rows && !accumulate &&
             dense_apply_tf32x3(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st))
             return;

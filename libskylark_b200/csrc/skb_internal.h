@@ -122,7 +122,7 @@ size_t dense_workspace_bytes(const DenseParams &p, size_t nloc, bool layout_rows
 // fp32 operands in the strided layout whose contraction fits one panel take the 3xTF32 kernel,
 // which needs only the panel (fp64 + fp32 copy) as workspace.
 bool dense_tf32_path_ok(const DenseParams &p, const void *X, size_t ldx, size_t m, size_t nloc);
-size_t dense_tf32_workspace_bytes(const DenseParams &p, size_t nloc);
+size_t dense_tf32_workspace_bytes(const DenseParams &p, size_t nloc, size_t m);
 // layout_rows = true : X[k*ldx + j] (k-th input index is a contiguous row of m), OUT[i*ldo + j]
 // layout_rows = false: X[k + j*ldx],                                             OUT[i + j*ldo]
 // Sketches input indices [koff, koff+nloc) of the transform (row shard); accumulate=false
