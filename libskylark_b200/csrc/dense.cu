@@ -799,7 +799,7 @@ struct TcArgs {
     const float *Phi, *Plo, *Xhi, *Xlo; float *OUT;
     size_t S, m, Kp, ldo;
     const double *scales, *shifts; double outscale; int has_epi;
-    int ntm;
+    int ntm, ntn;
 };
 
 __global__ void __launch_bounds__(tc::THREADS, 2) k_dense_gemm_tc_tf32x3(TcArgs a) {
@@ -809,7 +809,16 @@ __global__ void __launch_bounds__(tc::THREADS, 2) k_dense_gemm_tc_tf32x3(TcArgs 
     const uint32_t bars = sbase + NSTAGE * STAGE_BYTES;        // full[3], empty[3], accfull: 8 B each
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem_raw + NSTAGE * STAGE_BYTES + 64);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const size_t i0 = (size_t)(blockIdx.x % a.ntm) * TM, j0 = (size_t)(blockIdx.x / a.ntm) * TN;
+    // tile order: groups of GI i-tiles, inside a group j outer / i inner, so the CTAs in flight share
+    // GI panel tiles and a few X tiles (L2 working set of tens of MB instead of the whole panel)
+    size_t ti, tj;
+    {
+        constexpr int GI = 16;
+        const long long t = blockIdx.x, per = (long long)GI * a.ntn, grp = t / per, tp = t - grp * per;
+        const int gi = (int)min((long long)GI, (long long)a.ntm - grp * GI);
+        tj = (size_t)(tp / gi); ti = (size_t)(grp * GI + tp % gi);
+    }
+    const size_t i0 = ti * TM, j0 = tj * TN;
     const int nk = (int)(a.Kp / TK);
     auto full_bar = [&](int s) { return bars + 8u * s; };
     auto empty_bar = [&](int s) { return bars + 8u * (NSTAGE + s); };
@@ -834,33 +843,33 @@ __global__ void __launch_bounds__(tc::THREADS, 2) k_dense_gemm_tc_tf32x3(TcArgs 
     const uint32_t tmem = *tmem_slot;
 
     if (warp < 4) {
-        // ===== producers: thread t loads row t of each of the four tiles (64 contiguous bytes) =====
-        const int r = tid;
-        const uint32_t drow = (uint32_t)(r >> 3) * SBO + (uint32_t)(r & 7) * 16;
-        const bool okp = i0 + r < a.S, okx = j0 + r < a.m;
-        const float *srcs[4] = {a.Phi + (okp ? (i0 + r) * a.Kp : 0), a.Plo + (okp ? (i0 + r) * a.Kp : 0),
-                                a.Xhi + (okx ? (j0 + r) * a.Kp : 0), a.Xlo + (okx ? (j0 + r) * a.Kp : 0)};
-        const int nbytes[4] = {okp ? 16 : 0, okp ? 16 : 0, okx ? 16 : 0, okx ? 16 : 0};
-        auto signal = [&](int kb) {            // this thread's loads of k-block kb have landed
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            mbar_arrive(full_bar(kb % NSTAGE));
-        };
+        // ===== producers: a warp instruction reads 8 rows x 64 contiguous bytes (whole sectors):
+        // lane -> (row = 8*warp-step + lane/4, 16-byte chunk = lane%4); 4 steps cover 128 rows =====
+        const int kc = tid & 3;
+        uint32_t drow[4]; size_t prow[4], xrow[4]; int pb[4], xb[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const int r = (tid >> 2) + 32 * c;
+            drow[c] = (uint32_t)(r >> 3) * SBO + (uint32_t)(r & 7) * 16 + (uint32_t)kc * LBO;
+            const bool okp = i0 + r < a.S, okx = j0 + r < a.m;
+            prow[c] = (okp ? (i0 + r) * a.Kp : 0) + kc * 4; pb[c] = okp ? 16 : 0;
+            xrow[c] = (okx ? (j0 + r) * a.Kp : 0) + kc * 4; xb[c] = okx ? 16 : 0;
+        }
         for (int kb = 0; kb < nk; kb++) {
             const int s = kb % NSTAGE;
             if (kb >= NSTAGE) mbar_wait(empty_bar(s), (uint32_t)((kb / NSTAGE - 1) & 1));
-            const uint32_t dst = sbase + (uint32_t)s * STAGE_BYTES + drow;
+            const uint32_t dst = sbase + (uint32_t)s * STAGE_BYTES;
+            const size_t kof = (size_t)kb * TK;
 #pragma unroll
-            for (int tl = 0; tl < 4; tl++)
-#pragma unroll
-                for (int kc = 0; kc < TK / 4; kc++)
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + tl * TILE_BYTES + kc * LBO),
-                                 "l"(srcs[tl] + (size_t)kb * TK + kc * 4), "r"(nbytes[tl]) : "memory");
-            asm volatile("cp.async.commit_group;" ::: "memory");
-            if (kb >= 2) { asm volatile("cp.async.wait_group 2;" ::: "memory"); signal(kb - 2); }
+            for (int c = 0; c < 4; c++) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + drow[c]), "l"(a.Phi + prow[c] + kof), "r"(pb[c]) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + TILE_BYTES + drow[c]), "l"(a.Plo + prow[c] + kof), "r"(pb[c]) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + 2 * TILE_BYTES + drow[c]), "l"(a.Xhi + xrow[c] + kof), "r"(xb[c]) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + 3 * TILE_BYTES + drow[c]), "l"(a.Xlo + xrow[c] + kof), "r"(xb[c]) : "memory");
+            }
+            // the barrier receives this thread's arrival when the copies above have landed
+            asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(full_bar(s)) : "memory");
         }
-        if (nk >= 2) { asm volatile("cp.async.wait_group 1;" ::: "memory"); signal(nk - 2); }
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        signal(nk - 1);
         // ===== epilogue: warp w owns TMEM lanes [32w, 32w+32) = rows i, columns = j =====
         mbar_wait(acc_bar, 0);
         asm volatile("tcgen05.fence::after_thread_sync;");
@@ -900,6 +909,7 @@ __global__ void __launch_bounds__(tc::THREADS, 2) k_dense_gemm_tc_tf32x3(TcArgs 
         for (int kb = 0; kb < nk; kb++) {
             const int s = kb % NSTAGE;
             mbar_wait(full_bar(s), (uint32_t)((kb / NSTAGE) & 1));
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // cp.async wrote through the generic proxy
             asm volatile("tcgen05.fence::after_thread_sync;");
             const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
 #pragma unroll
@@ -1014,7 +1024,7 @@ static bool dense_apply_tc_tf32x3(const DenseParams &p, const float *X, size_t l
     a.scales = epi.scales; a.shifts = epi.shifts; a.outscale = epi.outscale;
     a.has_epi = epi.shifts != nullptr ? 1 : 0;
     const long long ntm = (long long)((S + tc::TM - 1) / tc::TM), ntn = (long long)((m + tc::TN - 1) / tc::TN);
-    a.ntm = (int)ntm;
+    a.ntm = (int)ntm; a.ntn = (int)ntn;
     SKB_CUDA(cudaFuncSetAttribute(k_dense_gemm_tc_tf32x3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM));
     LaunchScope ls(KC_GEMM, st);
     k_dense_gemm_tc_tf32x3<<<(unsigned)(ntm * ntn), tc::THREADS, tc::SMEM, st>>>(a);
