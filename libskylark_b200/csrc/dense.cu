@@ -741,9 +741,9 @@ constexpr size_t SMEM = (size_t)NSTAGE * STAGE_BYTES + 256;    // + barriers, TM
 constexpr uint32_t TMEM_COLS = 256;                            // main, cross
 }  // namespace tc
 
-// panel P[k*S + i] (fp64) -> Pt_hi / Pt_lo [i*Kp + k] (fp32 split, zero padded in k)
-__global__ void k_tc_split_panel(const double *__restrict__ P, size_t S, size_t K, size_t Kp,
-                                 float *__restrict__ hi, float *__restrict__ lo) {
+// panel P[k*S + i] (fp64) -> Pt[i*Kp + k] (fp32, the reference's cast; K-major, zero padded in k)
+__global__ void k_tc_transpose_panel(const double *__restrict__ P, size_t S, size_t K, size_t Kp,
+                                     float *__restrict__ Pt) {
     __shared__ float tile[32][33];
     const size_t i0 = (size_t)blockIdx.x * 32, k0 = (size_t)blockIdx.y * 32;
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {          // r = k, x = i (coalesced read)
@@ -753,24 +753,8 @@ __global__ void k_tc_split_panel(const double *__restrict__ P, size_t S, size_t 
     __syncthreads();
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {          // r = i, x = k (coalesced write)
         const size_t i = i0 + r, k = k0 + threadIdx.x;
-        if (i < S && k < Kp) {
-            const float x = tile[threadIdx.x][r];
-            const float h = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
-            hi[i * Kp + k] = h;
-            lo[i * Kp + k] = x - h;
-        }
+        if (i < S && k < Kp) Pt[i * Kp + k] = tile[threadIdx.x][r];
     }
-}
-// X[j*ldx + k] (fp32) -> X_hi / X_lo [j*Kp + k]
-__global__ void k_tc_split_x(const float *__restrict__ X, size_t ldx, size_t m, size_t K, size_t Kp,
-                             float *__restrict__ hi, float *__restrict__ lo) {
-    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= m * Kp) return;
-    const size_t j = t / Kp, k = t - j * Kp;
-    const float x = k < K ? X[j * ldx + k] : 0.f;
-    const float h = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
-    hi[t] = h;
-    lo[t] = x - h;
 }
 
 __device__ __forceinline__ uint64_t tc_desc(uint32_t saddr) {
@@ -796,8 +780,8 @@ __device__ __forceinline__ void tc_commit(uint32_t bar) {
 }
 
 struct TcArgs {
-    const float *Phi, *Plo, *Xhi, *Xlo; float *OUT;
-    size_t S, m, Kp, ldo;
+    const float *Pt, *X; float *OUT;          // Pt[i*Kp + k] (panel, transposed, zero padded), X[j*ldx + k]
+    size_t S, m, K, Kp, ldx, ldo;
     const double *scales, *shifts; double outscale; int has_epi;
     int ntm, ntn;
 };
@@ -843,32 +827,55 @@ __global__ void __launch_bounds__(tc::THREADS, 2) k_dense_gemm_tc_tf32x3(TcArgs 
     const uint32_t tmem = *tmem_slot;
 
     if (warp < 4) {
-        // ===== producers: a warp instruction reads 8 rows x 64 contiguous bytes (whole sectors):
-        // lane -> (row = 8*warp-step + lane/4, 16-byte chunk = lane%4); 4 steps cover 128 rows =====
+        // ===== producers: load raw fp32 once, split into hi / lo in registers, store both tiles.
+        // A warp instruction reads 8 rows x 64 contiguous bytes (whole sectors): lane -> (row =
+        // lane/4 + 8*warp + 32*c, 16-byte chunk = lane%4); the loads of k-block kb+1 are in flight
+        // while k-block kb is split and stored =====
         const int kc = tid & 3;
-        uint32_t drow[4]; size_t prow[4], xrow[4]; int pb[4], xb[4];
+        uint32_t drow[4]; const float *prow[4], *xrow[4]; bool okp[4], okx[4];
 #pragma unroll
         for (int c = 0; c < 4; c++) {
             const int r = (tid >> 2) + 32 * c;
             drow[c] = (uint32_t)(r >> 3) * SBO + (uint32_t)(r & 7) * 16 + (uint32_t)kc * LBO;
-            const bool okp = i0 + r < a.S, okx = j0 + r < a.m;
-            prow[c] = (okp ? (i0 + r) * a.Kp : 0) + kc * 4; pb[c] = okp ? 16 : 0;
-            xrow[c] = (okx ? (j0 + r) * a.Kp : 0) + kc * 4; xb[c] = okx ? 16 : 0;
+            okp[c] = i0 + r < a.S; okx[c] = j0 + r < a.m;
+            prow[c] = a.Pt + (okp[c] ? (i0 + r) * a.Kp : 0) + kc * 4;
+            xrow[c] = a.X + (okx[c] ? (j0 + r) * a.ldx : 0) + kc * 4;
         }
-        for (int kb = 0; kb < nk; kb++) {
-            const int s = kb % NSTAGE;
-            if (kb >= NSTAGE) mbar_wait(empty_bar(s), (uint32_t)((kb / NSTAGE - 1) & 1));
-            const uint32_t dst = sbase + (uint32_t)s * STAGE_BYTES;
+        float4 pv[4], xv[4];
+        auto fetch = [&](int kb) {
             const size_t kof = (size_t)kb * TK;
+            const bool kin = kof + kc * 4 < a.K;          // K is a multiple of 4: a chunk is inside or outside
 #pragma unroll
             for (int c = 0; c < 4; c++) {
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + drow[c]), "l"(a.Phi + prow[c] + kof), "r"(pb[c]) : "memory");
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + TILE_BYTES + drow[c]), "l"(a.Plo + prow[c] + kof), "r"(pb[c]) : "memory");
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + 2 * TILE_BYTES + drow[c]), "l"(a.Xhi + xrow[c] + kof), "r"(xb[c]) : "memory");
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + 3 * TILE_BYTES + drow[c]), "l"(a.Xlo + xrow[c] + kof), "r"(xb[c]) : "memory");
+                pv[c] = okp[c] ? __ldg(reinterpret_cast<const float4 *>(prow[c] + kof)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                xv[c] = (okx[c] && kin) ? __ldg(reinterpret_cast<const float4 *>(xrow[c] + kof)) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
-            // the barrier receives this thread's arrival when the copies above have landed
-            asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(full_bar(s)) : "memory");
+        };
+        auto put = [&](uint32_t addr_hi, uint32_t addr_lo, float4 v) {
+            float4 h, l;
+            h.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u); l.x = v.x - h.x;
+            h.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u); l.y = v.y - h.y;
+            h.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u); l.z = v.z - h.z;
+            h.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u); l.w = v.w - h.w;
+            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr_hi), "f"(h.x), "f"(h.y), "f"(h.z), "f"(h.w) : "memory");
+            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr_lo), "f"(l.x), "f"(l.y), "f"(l.z), "f"(l.w) : "memory");
+        };
+        fetch(0);
+        for (int kb = 0; kb < nk; kb++) {
+            const int s = kb % NSTAGE;
+            float4 pc[4], xc[4];
+#pragma unroll
+            for (int c = 0; c < 4; c++) { pc[c] = pv[c]; xc[c] = xv[c]; }
+            if (kb + 1 < nk) fetch(kb + 1);
+            if (kb >= NSTAGE) mbar_wait(empty_bar(s), (uint32_t)((kb / NSTAGE - 1) & 1));
+            const uint32_t dst = sbase + (uint32_t)s * STAGE_BYTES;
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                put(dst + drow[c], dst + TILE_BYTES + drow[c], pc[c]);
+                put(dst + 2 * TILE_BYTES + drow[c], dst + 3 * TILE_BYTES + drow[c], xc[c]);
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> tensor core
+            mbar_arrive(full_bar(s));
         }
         // ===== epilogue: warp w owns TMEM lanes [32w, 32w+32) = rows i, columns = j =====
         mbar_wait(acc_bar, 0);
@@ -909,7 +916,6 @@ __global__ void __launch_bounds__(tc::THREADS, 2) k_dense_gemm_tc_tf32x3(TcArgs 
         for (int kb = 0; kb < nk; kb++) {
             const int s = kb % NSTAGE;
             mbar_wait(full_bar(s), (uint32_t)((kb / NSTAGE) & 1));
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // cp.async wrote through the generic proxy
             asm volatile("tcgen05.fence::after_thread_sync;");
             const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
 #pragma unroll
@@ -988,8 +994,8 @@ static bool tc_enabled() {
 static size_t tc_kp(size_t K) { return (K + tc::TK - 1) / tc::TK * tc::TK; }
 static size_t tc_workspace_bytes(const DenseParams &p, size_t nloc, size_t m) {
     auto al = [](size_t b) { return (b + 255) / 256 * 256; };
-    const size_t Kp = tc_kp(nloc);
-    return al(nloc * p.S * sizeof(double)) + 2 * al(p.S * Kp * 4) + 2 * al(m * Kp * 4) + 256;
+    (void)m;
+    return al(nloc * p.S * sizeof(double)) + al(p.S * tc_kp(nloc) * 4) + 256;
 }
 
 static bool dense_apply_tc_tf32x3(const DenseParams &p, const float *X, size_t ldx, size_t m, size_t koff,
@@ -1001,26 +1007,17 @@ static bool dense_apply_tc_tf32x3(const DenseParams &p, const float *X, size_t l
     const size_t S = p.S, Kp = tc_kp(nloc);
     char *w = reinterpret_cast<char *>(workspace);
     double *P = reinterpret_cast<double *>(w); w += al(nloc * S * sizeof(double));
-    float *Phi = reinterpret_cast<float *>(w); w += al(S * Kp * 4);
-    float *Plo = reinterpret_cast<float *>(w); w += al(S * Kp * 4);
-    float *Xhi = reinterpret_cast<float *>(w); w += al(m * Kp * 4);
-    float *Xlo = reinterpret_cast<float *>(w);
+    float *Pt = reinterpret_cast<float *>(w);
     dense_generate_panel(p, koff, nloc, P, st);
     {
         LaunchScope ls(KC_GEN, st);
         dim3 grid((unsigned)((S + 31) / 32), (unsigned)((Kp + 31) / 32));
-        k_tc_split_panel<<<grid, dim3(32, 8), 0, st>>>(P, S, nloc, Kp, Phi, Plo);
-        SKB_CUDA(cudaGetLastError());
-    }
-    {
-        LaunchScope ls(KC_MISC, st);
-        const size_t n = m * Kp;
-        k_tc_split_x<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(X, ldx, m, nloc, Kp, Xhi, Xlo);
+        k_tc_transpose_panel<<<grid, dim3(32, 8), 0, st>>>(P, S, nloc, Kp, Pt);
         SKB_CUDA(cudaGetLastError());
     }
     TcArgs a;
-    a.Phi = Phi; a.Plo = Plo; a.Xhi = Xhi; a.Xlo = Xlo; a.OUT = OUT;
-    a.S = S; a.m = m; a.Kp = Kp; a.ldo = ldo;
+    a.Pt = Pt; a.X = X; a.OUT = OUT;
+    a.S = S; a.m = m; a.K = nloc; a.Kp = Kp; a.ldx = ldx; a.ldo = ldo;
     a.scales = epi.scales; a.shifts = epi.shifts; a.outscale = epi.outscale;
     a.has_epi = epi.shifts != nullptr ? 1 : 0;
     const long long ntm = (long long)((S + tc::TM - 1) / tc::TM), ntn = (long long)((m + tc::TN - 1) / tc::TN);
