@@ -829,20 +829,21 @@ __global__ void __launch_bounds__(tc::THREADS, 2) k_dense_gemm_tc_tf32x3(TcArgs 
     if (warp < 4) {
         // ===== producers: load raw fp32 once, split into hi / lo in registers, store both tiles.
         // A warp instruction reads 8 rows x 64 contiguous bytes (whole sectors): lane -> (row =
-        // lane/4 + 8*warp + 32*c, 16-byte chunk = lane%4); the loads of k-block kb+1 are in flight
+        // lane%8 + 8*warp + 32*c, 16-byte chunk = lane/8); the loads of k-block kb+1 are in flight
         // while k-block kb is split and stored =====
-        const int kc = tid & 3;
+        // (8 lanes of a quarter warp = 8 consecutive rows of one chunk: their 16-byte stores fill one
+        // 128-byte core matrix, conflict-free; the warp as a whole still reads 8 rows x 64 bytes)
+        const int kc = lane >> 3;
         uint32_t drow[4]; const float *prow[4], *xrow[4]; bool okp[4], okx[4];
 #pragma unroll
         for (int c = 0; c < 4; c++) {
-            const int r = (tid >> 2) + 32 * c;
+            const int r = warp * 8 + (lane & 7) + 32 * c;
             drow[c] = (uint32_t)(r >> 3) * SBO + (uint32_t)(r & 7) * 16 + (uint32_t)kc * LBO;
             okp[c] = i0 + r < a.S; okx[c] = j0 + r < a.m;
             prow[c] = a.Pt + (okp[c] ? (i0 + r) * a.Kp : 0) + kc * 4;
             xrow[c] = a.X + (okx[c] ? (j0 + r) * a.ldx : 0) + kc * 4;
         }
-        float4 pv[4], xv[4];
-        auto fetch = [&](int kb) {
+        auto fetch = [&](int kb, float4 (&pv)[4], float4 (&xv)[4]) {
             const size_t kof = (size_t)kb * TK;
             const bool kin = kof + kc * 4 < a.K;          // K is a multiple of 4: a chunk is inside or outside
 #pragma unroll
@@ -860,25 +861,36 @@ __global__ void __launch_bounds__(tc::THREADS, 2) k_dense_gemm_tc_tf32x3(TcArgs 
             asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr_hi), "f"(h.x), "f"(h.y), "f"(h.z), "f"(h.w) : "memory");
             asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr_lo), "f"(l.x), "f"(l.y), "f"(l.z), "f"(l.w) : "memory");
         };
-        fetch(0);
-        for (int kb = 0; kb < nk; kb++) {
+        auto stage_out = [&](int kb, float4 (&pv)[4], float4 (&xv)[4]) {
             const int s = kb % NSTAGE;
-            float4 pc[4], xc[4];
-#pragma unroll
-            for (int c = 0; c < 4; c++) { pc[c] = pv[c]; xc[c] = xv[c]; }
-            if (kb + 1 < nk) fetch(kb + 1);
-            if (kb >= NSTAGE) mbar_wait(empty_bar(s), (uint32_t)((kb / NSTAGE - 1) & 1));
+            if (kb >= NSTAGE) {          // one lane polls, the warp follows (the barrier unit is shared with the stores)
+                if (lane == 0) mbar_wait(empty_bar(s), (uint32_t)((kb / NSTAGE - 1) & 1));
+                __syncwarp();
+            }
             const uint32_t dst = sbase + (uint32_t)s * STAGE_BYTES;
 #pragma unroll
             for (int c = 0; c < 4; c++) {
-                put(dst + drow[c], dst + TILE_BYTES + drow[c], pc[c]);
-                put(dst + 2 * TILE_BYTES + drow[c], dst + 3 * TILE_BYTES + drow[c], xc[c]);
+                put(dst + drow[c], dst + TILE_BYTES + drow[c], pv[c]);
+                put(dst + 2 * TILE_BYTES + drow[c], dst + 3 * TILE_BYTES + drow[c], xv[c]);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> tensor core
             mbar_arrive(full_bar(s));
+        };
+        // two register sets: the loads of k-blocks kb+1 and kb+2 are in flight while kb is split and stored
+        float4 pa[4], xa[4], pb[4], xb[4];
+        fetch(0, pa, xa);
+        if (nk > 1) fetch(1, pb, xb);
+        for (int kb = 0; kb < nk; kb += 2) {
+            stage_out(kb, pa, xa);
+            if (kb + 2 < nk) fetch(kb + 2, pa, xa);
+            if (kb + 1 < nk) {
+                stage_out(kb + 1, pb, xb);
+                if (kb + 3 < nk) fetch(kb + 3, pb, xb);
+            }
         }
         // ===== epilogue: warp w owns TMEM lanes [32w, 32w+32) = rows i, columns = j =====
-        mbar_wait(acc_bar, 0);
+        if (lane == 0) mbar_wait(acc_bar, 0);
+        __syncwarp();
         asm volatile("tcgen05.fence::after_thread_sync;");
         const size_t i = i0 + (size_t)tid;
         double sc = 1.0, sh = 0.0;
