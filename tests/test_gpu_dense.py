@@ -169,11 +169,14 @@ def test_dense_transform_of_sparse_operand(sk, oracle, T, fmt):
     assert isinstance(got, np.ndarray) and rel_fro(got, O.apply(A.toarray(), "columnwise")) < tol
 
 
-@pytest.mark.parametrize("shape", [(784, 16384, 700), (100, 520, 133), (36, 12, 5)])
+@pytest.mark.parametrize("shape", [(784, 16384, 700), (100, 520, 133), (36, 12, 5), (16, 4, 1), (1028, 260, 300),
+                                   (2000, 128, 129)])      # the last two: k > 1024 -> mma.sync kernel
 def test_fp32_feature_map_keeps_fp32_accuracy(sk, oracle, shape):
-    # the strided fp32 case runs on the TF32 tensor pipe with operand splitting; a plain
-    # accumulating MMA chain would sit at ~9e-6 (tensor-core accumulation truncates), the
-    # zero-start + FADD scheme at < 1e-6 -- asserted well inside the 1e-5 bar, edge tiles included
+    # the strided fp32 case runs on the TF32 tensor cores with operand splitting.  Tensor-core
+    # accumulation truncates, so one chain over all three products would sit at ~9e-6; the
+    # tcgen05 kernel keeps the large term in its own accumulator (3.4e-6 at k = 784), the
+    # mma.sync kernel restarts its accumulator every 8 (6.5e-7) -- asserted inside the 1e-5 bar,
+    # edge tiles included
     import torch
     n, s, m = shape
     c, oc = _ctx(sk, oracle, 7)
@@ -181,7 +184,7 @@ def test_fp32_feature_map_keeps_fp32_accuracy(sk, oracle, shape):
     X = torch.rand(m, n, dtype=torch.float32, device="cuda", generator=torch.Generator("cuda").manual_seed(1))
     got = S.apply(X, None, "rowwise").cpu().numpy()
     want = O.apply(X.cpu().numpy().astype(np.float64), "rowwise")
-    assert rel_fro(got, want) < 2e-6
+    assert rel_fro(got, want) < 5e-6
     J, OJ = sk.JLT(n, s, context=c), oracle.JLT(n, s, oc)        # no epilogue, same kernel
     got = J.apply(X, None, "rowwise").cpu().numpy()
-    assert rel_fro(got, OJ.apply(X.cpu().numpy().astype(np.float64), "rowwise")) < 2e-6
+    assert rel_fro(got, OJ.apply(X.cpu().numpy().astype(np.float64), "rowwise")) < 5e-6
