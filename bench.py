@@ -312,12 +312,13 @@ def other_configs(torch, lib, sketch, hbm_gbs, fp64_peak):
         SA = torch.empty(m, s, dtype=torch.float32, device=dev)          # 32.8 GB
         ms = _time_apply(torch, S, A, SA, "rowwise", 2, None)
         tf = 2.0 * m * n * s / (ms * 1e-3) / 1e12
-        # fp32 operands take the 3xTF32 path (three mma.sync.m16n8k8.tf32 per product, fp32-level
-        # accuracy); its ceiling is the legacy TF32 tensor pipe measured with tools/tf32_peak.cu on
-        # this pool (278 TFLOP/s) divided by three.  For reference the FP64-DMMA path gave 26.9.
-        tf32_eff_peak = 278.0 / 3.0
-        return {"workload": "C5 shard: GaussianRFT fp32 500000x784 -> 16384 rowwise, fused cos, 3xTF32",
-                "ms": ms, "value": tf, "unit": "TFLOP/s", "frac_of_3xtf32_mma_sync_peak": tf / tf32_eff_peak,
+        # fp32 operands take the 3xTF32 path on the 5th-generation tensor cores (tcgen05.mma.kind::tf32,
+        # three MMAs per product, fp32-level accuracy).  Ceiling: the TF32 rate of that instruction
+        # measured on this pool with tools/tcgen05_probe.cu (875 TFLOP/s over 148 SMs) divided by three.
+        # For reference: 26.9 TFLOP/s on the FP64-DMMA path, 55 on the mma.sync 3xTF32 kernel.
+        tf32_eff_peak = 875.0 / 3.0
+        return {"workload": "C5 shard: GaussianRFT fp32 500000x784 -> 16384 rowwise, fused cos, 3xTF32 (tcgen05)",
+                "ms": ms, "value": tf, "unit": "TFLOP/s", "frac_of_3xtf32_tcgen05_peak": tf / tf32_eff_peak,
                 "ratio_to_measured_fp64_gemm": tf / fp64_peak}
 
     guarded("c1_cwt_rowmajor", lambda: c1("C"))
