@@ -27,6 +27,8 @@
 #include <cstdio>
 #include <cstdlib>
 
+#include <cuda.h>          // CUtensorMap and its enums (the encoder itself is fetched at run time)
+
 #include "rng.cuh"
 #include "skb_internal.h"
 
@@ -1003,6 +1005,213 @@ static bool dense_apply_tf32x3(const DenseParams &p, const float *X, size_t ldx,
     return true;
 }
 
+// ---------------------------------------------------------------------------
+// K5e: K5d with TMA.  The hardware truncates fp32 operands to TF32 (tools/tcgen05_probe.cu:
+// 3.5e-8 against truncated operands, 2.9e-4 against rounded ones), so a raw fp32 tile IS the hi
+// operand: one thread issues two cp.async.bulk.tensor loads per stage (16 x 128 boxes of the
+// transposed panel and of X, 64-byte swizzle = the canonical K-major SWIZZLE_64B layout of the
+// MMA), out-of-range rows and the k tail arrive as zeros.  The producer warps only compute the lo
+// tiles (lo = x - trunc(x), element by element in the same swizzled positions): per stage 16 KB
+// read and 16 KB written through the LSU instead of 16 KB of scattered global loads and 32 KB of
+// stores.  Everything else (two TMEM accumulators, commit-based stage release, epilogue) as K5d.
+// ---------------------------------------------------------------------------
+typedef CUresult (*skb_encode_tiled_t)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                       const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                       CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                       CUtensorMapFloatOOBfill);
+static skb_encode_tiled_t tma_encoder() {
+    static skb_encode_tiled_t fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<skb_encode_tiled_t>(p);
+        cudaGetLastError();
+    }
+    return fn;
+}
+// rows x cols fp32 matrix with row stride ld (elements), boxes of 16 columns x 128 rows
+static bool tma_make_map(CUtensorMap *map, const float *base, size_t rows, size_t cols, size_t ld) {
+    skb_encode_tiled_t enc = tma_encoder();
+    if (!enc) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
+    const cuuint32_t box[2] = {16, 128}, estr[2] = {1, 1};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+namespace tm {
+constexpr int TM = 128, TN = 128, TK = 16, NSTAGE = 3;
+constexpr int PRODUCERS = 128, THREADS = PRODUCERS + 64;     // + MMA warp + TMA warp
+constexpr uint32_t SBO = 8 * 64;                               // 8 rows of 64 bytes
+constexpr uint32_t TILE_BYTES = TM * TK * 4;                   // 8 KB
+constexpr uint32_t STAGE_BYTES = 4 * TILE_BYTES;               // P raw, P lo, X raw, X lo
+constexpr size_t SMEM = (size_t)NSTAGE * STAGE_BYTES + 1024 + 256;   // + alignment slack + barriers
+constexpr uint32_t TMEM_COLS = 256;
+}  // namespace tm
+
+__device__ __forceinline__ uint64_t tm_desc(uint32_t saddr) {       // K-major, SWIZZLE_64B
+    return (uint64_t)((saddr >> 4) & 0x3fff) | ((uint64_t)1 << 16) | ((uint64_t)(tm::SBO >> 4) << 32) |
+           ((uint64_t)1 << 46) | ((uint64_t)4 << 61);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+
+struct TmArgs {
+    float *OUT; size_t S, m, ldo;
+    const double *scales, *shifts; double outscale; int has_epi;
+    int ntm, ntn, nk;
+};
+
+__global__ void __launch_bounds__(tm::THREADS, 2)
+k_dense_gemm_tc_tma(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmX, TmArgs a) {
+    using namespace tm;
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t sbase = ((uint32_t)__cvta_generic_to_shared(smem_raw) + 1023u) & ~1023u;   // swizzle atoms want aligned tiles
+    const uint32_t bars = sbase + NSTAGE * STAGE_BYTES;        // tma[3], full[3], empty[3], acc: 8 B each
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    size_t ti, tj;
+    {
+        constexpr int GI = 16;
+        const long long t = blockIdx.x, per = (long long)GI * a.ntn, grp = t / per, tp = t - grp * per;
+        const int gi = (int)min((long long)GI, (long long)a.ntm - grp * GI);
+        tj = (size_t)(tp / gi); ti = (size_t)(grp * GI + tp % gi);
+    }
+    const size_t i0 = ti * TM, j0 = tj * TN;
+    const int nk = a.nk;
+    auto tma_bar = [&](int s) { return bars + 8u * s; };
+    auto full_bar = [&](int s) { return bars + 8u * (NSTAGE + s); };
+    auto empty_bar = [&](int s) { return bars + 8u * (2 * NSTAGE + s); };
+    const uint32_t acc_bar = bars + 8u * (3 * NSTAGE);
+
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; s++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tma_bar(s)));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full_bar(s)), "r"(PRODUCERS));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(empty_bar(s)));
+        }
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(acc_bar));
+        asm volatile("fence.mbarrier_init.release.cluster;");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(&tmem_slot)), "n"(TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem = tmem_slot;
+
+    if (warp == 5) {
+        if (lane == 0) {
+            // ===== TMA issuer =====
+            for (int kb = 0; kb < nk; kb++) {
+                const int s = kb % NSTAGE;
+                if (kb >= NSTAGE) mbar_wait(empty_bar(s), (uint32_t)((kb / NSTAGE - 1) & 1));
+                const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tma_bar(s)), "r"(2 * TILE_BYTES) : "memory");
+                tma_load_2d(st0, &tmP, kb * TK, (int)i0, tma_bar(s));
+                tma_load_2d(st0 + 2 * TILE_BYTES, &tmX, kb * TK, (int)j0, tma_bar(s));
+            }
+        }
+    } else if (warp == 4) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+            const uint32_t t_main = tmem, t_cross = tmem + (uint32_t)TN;
+            for (int kb = 0; kb < nk; kb++) {
+                const int s = kb % NSTAGE;
+                mbar_wait(full_bar(s), (uint32_t)((kb / NSTAGE) & 1));
+                asm volatile("tcgen05.fence::after_thread_sync;");
+                const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+#pragma unroll
+                for (int ks = 0; ks < TK / 8; ks++) {
+                    const uint32_t ko = (uint32_t)ks * 32;          // 8 floats inside the 64-byte swizzle row
+                    const uint64_t phi = tm_desc(st0 + ko), plo = tm_desc(st0 + TILE_BYTES + ko);
+                    const uint64_t xhi = tm_desc(st0 + 2 * TILE_BYTES + ko), xlo = tm_desc(st0 + 3 * TILE_BYTES + ko);
+                    const uint32_t first = (kb | ks) == 0 ? 0u : 1u;
+                    tc_mma(t_cross, plo, xhi, idesc, first);
+                    tc_mma(t_cross, phi, xlo, idesc, 1u);
+                    tc_mma(t_main, phi, xhi, idesc, first);
+                }
+                tc_commit(empty_bar(s));
+            }
+            tc_commit(acc_bar);
+        }
+    } else {
+        // ===== lo producers: lo = x - trunc(x), same (swizzled) position in the lo tile =====
+        for (int kb = 0; kb < nk; kb++) {
+            const int s = kb % NSTAGE;
+            if (lane == 0) mbar_wait(tma_bar(s), (uint32_t)((kb / NSTAGE) & 1));
+            __syncwarp();
+            const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+#pragma unroll
+            for (int tl = 0; tl < 2; tl++) {
+                const uint32_t raw = st0 + (uint32_t)tl * 2 * TILE_BYTES, lo = raw + TILE_BYTES;
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const uint32_t off = (uint32_t)(tid + c * PRODUCERS) * 16;
+                    float4 v, l;
+                    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(raw + off));
+                    l.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
+                    l.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
+                    l.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
+                    l.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
+                    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(lo + off), "f"(l.x), "f"(l.y), "f"(l.z), "f"(l.w) : "memory");
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(full_bar(s));
+        }
+        // ===== epilogue: warp w owns TMEM lanes [32w, 32w+32) = rows i, columns = j =====
+        if (lane == 0) mbar_wait(acc_bar, 0);
+        __syncwarp();
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        const size_t i = i0 + (size_t)tid;
+        double sc = 1.0, sh = 0.0;
+        if (a.has_epi && i < a.S) { sc = a.scales[i]; sh = a.shifts[i]; }
+        const float osc = (float)a.outscale;
+        for (int c0 = 0; c0 < TN; c0 += 8) {
+            uint32_t mn[8], cr[8];
+            const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(mn[0]), "=r"(mn[1]), "=r"(mn[2]), "=r"(mn[3]), "=r"(mn[4]), "=r"(mn[5]), "=r"(mn[6]), "=r"(mn[7])
+                         : "r"(taddr));
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(cr[0]), "=r"(cr[1]), "=r"(cr[2]), "=r"(cr[3]), "=r"(cr[4]), "=r"(cr[5]), "=r"(cr[6]), "=r"(cr[7])
+                         : "r"(taddr + (uint32_t)TN));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (i < a.S) {
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                    const size_t j = j0 + c0 + e;
+                    if (j >= a.m) break;
+                    float v = __uint_as_float(mn[e]) + __uint_as_float(cr[e]);
+                    if (a.has_epi) {
+                        const double arg = fma((double)v, sc, sh);
+                        const double q = rint(arg * 0.15915494309189535);
+                        v = osc * cosf((float)fma(q, -6.283185307179586, arg));
+                    }
+                    a.OUT[i + j * a.ldo] = v;
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    __syncwarp();
+    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(tm::TMEM_COLS));
+}
+
 static bool tc_enabled() {      // SKB_DEBUG_NO_TCGEN05=1 falls back to the mma.sync kernel
     static const bool on = getenv("SKB_DEBUG_NO_TCGEN05") == nullptr;
     return on;
@@ -1047,11 +1256,47 @@ static bool dense_apply_tc_tf32x3(const DenseParams &p, const float *X, size_t l
     return true;
 }
 
+static bool dense_apply_tc_tma(const DenseParams &p, const float *X, size_t ldx, size_t m, size_t koff,
+                               size_t nloc, float *OUT, size_t ldo, const RftEpilogue &epi,
+                               void *workspace, size_t workspace_bytes, cudaStream_t st) {
+    static const bool off = getenv("SKB_DEBUG_NO_TMA") != nullptr;
+    if (off || !tc_enabled() || nloc > 1024 || !dense_tf32_path_ok(p, X, ldx, m, nloc)) return false;
+    if (workspace_bytes < tc_workspace_bytes(p, nloc, m) || !tma_encoder()) return false;
+    auto al = [](size_t b) { return (b + 255) / 256 * 256; };
+    const size_t S = p.S, Kp = tc_kp(nloc);
+    char *w = reinterpret_cast<char *>(workspace);
+    double *P = reinterpret_cast<double *>(w); w += al(nloc * S * sizeof(double));
+    float *Pt = reinterpret_cast<float *>(w);
+    CUtensorMap tmP, tmX;
+    if (!tma_make_map(&tmP, Pt, S, Kp, Kp) || !tma_make_map(&tmX, X, m, nloc, ldx)) return false;
+    dense_generate_panel(p, koff, nloc, P, st);
+    {
+        LaunchScope ls(KC_GEN, st);
+        dim3 grid((unsigned)((S + 31) / 32), (unsigned)((Kp + 31) / 32));
+        k_tc_transpose_panel<<<grid, dim3(32, 8), 0, st>>>(P, S, nloc, Kp, Pt);
+        SKB_CUDA(cudaGetLastError());
+    }
+    TmArgs a;
+    a.OUT = OUT; a.S = S; a.m = m; a.ldo = ldo;
+    a.scales = epi.scales; a.shifts = epi.shifts; a.outscale = epi.outscale;
+    a.has_epi = epi.shifts != nullptr ? 1 : 0;
+    const long long ntm = (long long)((S + tm::TM - 1) / tm::TM), ntn = (long long)((m + tm::TN - 1) / tm::TN);
+    a.ntm = (int)ntm; a.ntn = (int)ntn; a.nk = (int)(Kp / tm::TK);
+    SKB_CUDA(cudaFuncSetAttribute(k_dense_gemm_tc_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tm::SMEM));
+    LaunchScope ls(KC_GEMM, st);
+    k_dense_gemm_tc_tma<<<(unsigned)(ntm * ntn), tm::THREADS, tm::SMEM, st>>>(tmP, tmX, a);
+    SKB_CUDA(cudaGetLastError());
+    return true;
+}
+
 void dense_apply(const DenseParams &p, bool layout_rows, bool f32, const void *X, size_t ldx,
                  size_t m, size_t koff, size_t nloc, void *OUT, size_t ldo,
                  const RftEpilogue &epi, void *workspace, size_t workspace_bytes,
                  cudaStream_t st, bool accumulate) {
     if (f32) {
+        if (!layout_rows && !accumulate &&
+            dense_apply_tc_tma(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st))
+            return;
         if (!layout_rows && !accumulate &&
             dense_apply_tc_tf32x3(p, (const float *)X, ldx, m, koff, nloc, (float *)OUT, ldo, epi, workspace, workspace_bytes, st))
             return;
