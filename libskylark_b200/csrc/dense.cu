@@ -1199,7 +1199,7 @@ k_dense_gemm_tc_tma(const __grid_constant__ CUtensorMap tmP, const __grid_consta
                     if (a.has_epi) {
                         const double arg = fma((double)v, sc, sh);
                         const double q = rint(arg * 0.15915494309189535);
-                        v = osc * cosf((float)fma(q, -6.283185307179586, arg));
+                        v = osc * __cosf((float)fma(q, -6.283185307179586, arg));     // |r| <= pi: MUFU.COS is good to 4e-7 there
                     }
                     a.OUT[i + j * a.ldo] = v;
                 }
