@@ -317,7 +317,7 @@ def other_configs(torch, lib, sketch, hbm_gbs, fp64_peak):
         # measured on this pool with tools/tcgen05_probe.cu (875 TFLOP/s over 148 SMs) divided by three.
         # For reference: 26.9 TFLOP/s on the FP64-DMMA path, 55 on the mma.sync 3xTF32 kernel.
         tf32_eff_peak = 875.0 / 3.0
-        return {"workload": "C5 shard: GaussianRFT fp32 500000x784 -> 16384 rowwise, fused cos, 3xTF32 (tcgen05)",
+        return {"workload": "C5 shard: GaussianRFT fp32 500000x784 -> 16384 rowwise, fused cos, 3xTF32 (tcgen05 + TMA)",
                 "ms": ms, "value": tf, "unit": "TFLOP/s", "frac_of_3xtf32_tcgen05_peak": tf / tf32_eff_peak,
                 "ratio_to_measured_fp64_gemm": tf / fp64_peak}
 
