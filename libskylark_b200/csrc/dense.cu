@@ -1212,6 +1212,188 @@ k_dense_gemm_tc_tma(const __grid_constant__ CUtensorMap tmP, const __grid_consta
     if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(tm::TMEM_COLS));
 }
 
+// ---------------------------------------------------------------------------
+// K5d, persistent form: one CTA per SM walks the tile list.  Roles: warps 0-3 epilogue, warps
+// 4-7 lo producers, warp 8 MMA issuer, warp 9 TMA issuer.  The operand ring (6 stages) runs
+// across tile boundaries and TMEM holds two accumulator pairs, so the MMAs of tile t+1 start
+// while the epilogue warps drain tile t.
+// ---------------------------------------------------------------------------
+namespace tp {
+constexpr int TM = 128, TN = 128, TK = 16, NSTAGE = 6;
+constexpr int EPI = 128, PRODUCERS = 128, THREADS = EPI + PRODUCERS + 64;
+constexpr uint32_t TILE_BYTES = TM * TK * 4, STAGE_BYTES = 4 * TILE_BYTES;
+constexpr size_t SMEM = (size_t)NSTAGE * STAGE_BYTES + 1024 + 256;
+constexpr uint32_t TMEM_COLS = 512;            // 2 x (main 128 + cross 128)
+}  // namespace tp
+
+__device__ __forceinline__ void tp_tile(const TmArgs &a, long long t, size_t &i0, size_t &j0) {
+    constexpr int GI = 16;
+    const long long per = (long long)GI * a.ntn, grp = t / per, tp_ = t - grp * per;
+    const int gi = (int)min((long long)GI, (long long)a.ntm - grp * GI);
+    j0 = (size_t)(tp_ / gi) * tp::TN; i0 = (size_t)(grp * GI + tp_ % gi) * tp::TM;
+}
+
+__global__ void __launch_bounds__(tp::THREADS, 1)
+k_dense_gemm_tc_tma_p(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmX, TmArgs a,
+                      long long ntiles) {
+    using namespace tp;
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t sbase = ((uint32_t)__cvta_generic_to_shared(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = sbase + NSTAGE * STAGE_BYTES;   // tma[6], full[6], empty[6], accfull[2], accempty[2]
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nk = a.nk;
+    auto tma_bar = [&](int s) { return bars + 8u * s; };
+    auto full_bar = [&](int s) { return bars + 8u * (NSTAGE + s); };
+    auto empty_bar = [&](int s) { return bars + 8u * (2 * NSTAGE + s); };
+    auto accfull_bar = [&](int b) { return bars + 8u * (3 * NSTAGE + b); };
+    auto accempty_bar = [&](int b) { return bars + 8u * (3 * NSTAGE + 2 + b); };
+
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; s++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tma_bar(s)));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full_bar(s)), "r"(PRODUCERS));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(empty_bar(s)));
+        }
+        for (int b = 0; b < 2; b++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(accfull_bar(b)));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(accempty_bar(b)), "r"(EPI));
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;");
+    }
+    if (warp == 8) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(&tmem_slot)), "n"(TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem = tmem_slot;
+
+    if (warp == 9) {
+        if (lane == 0) {
+            // ===== TMA issuer: g counts stages over all tiles of this CTA =====
+            long long g = 0;
+            for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+                size_t i0, j0; tp_tile(a, t, i0, j0);
+                for (int kb = 0; kb < nk; kb++, g++) {
+                    const int s = (int)(g % NSTAGE);
+                    if (g >= NSTAGE) mbar_wait(empty_bar(s), (uint32_t)((g / NSTAGE - 1) & 1));
+                    const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tma_bar(s)), "r"(2 * TILE_BYTES) : "memory");
+                    tma_load_2d(st0, &tmP, kb * TK, (int)i0, tma_bar(s));
+                    tma_load_2d(st0 + 2 * TILE_BYTES, &tmX, kb * TK, (int)j0, tma_bar(s));
+                }
+            }
+        }
+    } else if (warp == 8) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+            long long g = 0; int it = 0;
+            for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
+                const int buf = it & 1;
+                if (it >= 2) mbar_wait(accempty_bar(buf), (uint32_t)(((it >> 1) - 1) & 1));   // epilogue drained this pair
+                asm volatile("tcgen05.fence::after_thread_sync;");
+                const uint32_t t_main = tmem + (uint32_t)buf * 256, t_cross = t_main + (uint32_t)TN;
+                for (int kb = 0; kb < nk; kb++, g++) {
+                    const int s = (int)(g % NSTAGE);
+                    mbar_wait(full_bar(s), (uint32_t)((g / NSTAGE) & 1));
+                    asm volatile("tcgen05.fence::after_thread_sync;");
+                    const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+#pragma unroll
+                    for (int ks = 0; ks < TK / 8; ks++) {
+                        const uint32_t ko = (uint32_t)ks * 32;
+                        const uint64_t phi = tm_desc(st0 + ko), plo = tm_desc(st0 + TILE_BYTES + ko);
+                        const uint64_t xhi = tm_desc(st0 + 2 * TILE_BYTES + ko), xlo = tm_desc(st0 + 3 * TILE_BYTES + ko);
+                        const uint32_t first = (kb | ks) == 0 ? 0u : 1u;
+                        tc_mma(t_cross, plo, xhi, idesc, first);
+                        tc_mma(t_cross, phi, xlo, idesc, 1u);
+                        tc_mma(t_main, phi, xhi, idesc, first);
+                    }
+                    tc_commit(empty_bar(s));
+                }
+                tc_commit(accfull_bar(buf));
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== lo producers (warps 4-7) =====
+        const int pt = tid - EPI;
+        long long g = 0;
+        for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+            for (int kb = 0; kb < nk; kb++, g++) {
+                const int s = (int)(g % NSTAGE);
+                if (lane == 0) mbar_wait(tma_bar(s), (uint32_t)((g / NSTAGE) & 1));
+                __syncwarp();
+                const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+#pragma unroll
+                for (int tl = 0; tl < 2; tl++) {
+                    const uint32_t raw = st0 + (uint32_t)tl * 2 * TILE_BYTES, lo = raw + TILE_BYTES;
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const uint32_t off = (uint32_t)(pt + c * PRODUCERS) * 16;
+                        float4 v, l;
+                        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(raw + off));
+                        l.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
+                        l.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
+                        l.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
+                        l.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
+                        asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(lo + off), "f"(l.x), "f"(l.y), "f"(l.z), "f"(l.w) : "memory");
+                    }
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(full_bar(s));
+            }
+        }
+    } else {
+        // ===== epilogue (warps 0-3): warp w owns TMEM lanes [32w, 32w+32) = rows i =====
+        const float osc = (float)a.outscale;
+        int it = 0;
+        for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
+            size_t i0, j0; tp_tile(a, t, i0, j0);
+            const int buf = it & 1;
+            if (lane == 0) mbar_wait(accfull_bar(buf), (uint32_t)((it >> 1) & 1));
+            __syncwarp();
+            asm volatile("tcgen05.fence::after_thread_sync;");
+            const size_t i = i0 + (size_t)tid;
+            double sc = 1.0, sh = 0.0;
+            if (a.has_epi && i < a.S) { sc = a.scales[i]; sh = a.shifts[i]; }
+            const uint32_t tb = tmem + (uint32_t)buf * 256 + ((uint32_t)(warp * 32) << 16);
+            for (int c0 = 0; c0 < TN; c0 += 8) {
+                uint32_t mn[8], cr[8];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                             : "=r"(mn[0]), "=r"(mn[1]), "=r"(mn[2]), "=r"(mn[3]), "=r"(mn[4]), "=r"(mn[5]), "=r"(mn[6]), "=r"(mn[7])
+                             : "r"(tb + (uint32_t)c0));
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                             : "=r"(cr[0]), "=r"(cr[1]), "=r"(cr[2]), "=r"(cr[3]), "=r"(cr[4]), "=r"(cr[5]), "=r"(cr[6]), "=r"(cr[7])
+                             : "r"(tb + (uint32_t)TN + (uint32_t)c0));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (i < a.S) {
+#pragma unroll
+                    for (int e = 0; e < 8; e++) {
+                        const size_t j = j0 + c0 + e;
+                        if (j >= a.m) break;
+                        float v = __uint_as_float(mn[e]) + __uint_as_float(cr[e]);
+                        if (a.has_epi) {
+                            const double arg = fma((double)v, sc, sh);
+                            const double q = rint(arg * 0.15915494309189535);
+                            v = osc * __cosf((float)fma(q, -6.283185307179586, arg));
+                        }
+                        a.OUT[i + j * a.ldo] = v;
+                    }
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;");
+            mbar_arrive(accempty_bar(buf));             // this accumulator pair may be overwritten
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    __syncwarp();
+    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(tp::TMEM_COLS));
+}
+
 static bool tc_enabled() {      // SKB_DEBUG_NO_TCGEN05=1 falls back to the mma.sync kernel
     static const bool on = getenv("SKB_DEBUG_NO_TCGEN05") == nullptr;
     return on;
@@ -1282,9 +1464,16 @@ static bool dense_apply_tc_tma(const DenseParams &p, const float *X, size_t ldx,
     a.has_epi = epi.shifts != nullptr ? 1 : 0;
     const long long ntm = (long long)((S + tm::TM - 1) / tm::TM), ntn = (long long)((m + tm::TN - 1) / tm::TN);
     a.ntm = (int)ntm; a.ntn = (int)ntn; a.nk = (int)(Kp / tm::TK);
-    SKB_CUDA(cudaFuncSetAttribute(k_dense_gemm_tc_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tm::SMEM));
+    static const bool persist = getenv("SKB_DEBUG_NO_PERSIST") == nullptr;
     LaunchScope ls(KC_GEMM, st);
-    k_dense_gemm_tc_tma<<<(unsigned)(ntm * ntn), tm::THREADS, tm::SMEM, st>>>(tmP, tmX, a);
+    if (persist) {
+        SKB_CUDA(cudaFuncSetAttribute(k_dense_gemm_tc_tma_p, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tp::SMEM));
+        const long long ntiles = ntm * ntn;
+        k_dense_gemm_tc_tma_p<<<(unsigned)std::min<long long>(ntiles, 148), tp::THREADS, tp::SMEM, st>>>(tmP, tmX, a, ntiles);
+    } else {
+        SKB_CUDA(cudaFuncSetAttribute(k_dense_gemm_tc_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tm::SMEM));
+        k_dense_gemm_tc_tma<<<(unsigned)(ntm * ntn), tm::THREADS, tm::SMEM, st>>>(tmP, tmX, a);
+    }
     SKB_CUDA(cudaGetLastError());
     return true;
 }
