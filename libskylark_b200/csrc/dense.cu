@@ -745,7 +745,7 @@ constexpr uint32_t TMEM_COLS = 256;                            // main, cross
 
 // panel P[k*S + i] (fp64) -> Pt[i*Kp + k] (fp32, the reference's cast; K-major, zero padded in k)
 __global__ void k_tc_transpose_panel(const double *__restrict__ P, size_t S, size_t K, size_t Kp,
-                                     float *__restrict__ Pt) {
+                                     float *__restrict__ Pt, float *__restrict__ Pt_lo = nullptr) {
     __shared__ float tile[32][33];
     const size_t i0 = (size_t)blockIdx.x * 32, k0 = (size_t)blockIdx.y * 32;
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {          // r = k, x = i (coalesced read)
@@ -755,7 +755,11 @@ __global__ void k_tc_transpose_panel(const double *__restrict__ P, size_t S, siz
     __syncthreads();
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {          // r = i, x = k (coalesced write)
         const size_t i = i0 + r, k = k0 + threadIdx.x;
-        if (i < S && k < Kp) Pt[i * Kp + k] = tile[threadIdx.x][r];
+        if (i < S && k < Kp) {
+            const float x = tile[threadIdx.x][r];
+            Pt[i * Kp + k] = x;
+            if (Pt_lo) Pt_lo[i * Kp + k] = x - __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+        }
     }
 }
 
@@ -1034,12 +1038,13 @@ static skb_encode_tiled_t tma_encoder() {
     return fn;
 }
 // rows x cols fp32 matrix with row stride ld (elements), boxes of 16 columns x 128 rows
-static bool tma_make_map(CUtensorMap *map, const float *base, size_t rows, size_t cols, size_t ld) {
+static bool tma_make_map(CUtensorMap *map, const float *base, size_t rows, size_t cols, size_t ld,
+                         unsigned box_rows = 128) {
     skb_encode_tiled_t enc = tma_encoder();
     if (!enc) return false;
     const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
     const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
-    const cuuint32_t box[2] = {16, 128}, estr[2] = {1, 1};
+    const cuuint32_t box[2] = {16, box_rows}, estr[2] = {1, 1};
     return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -1394,6 +1399,193 @@ k_dense_gemm_tc_tma_p(const __grid_constant__ CUtensorMap tmP, const __grid_cons
     if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(tp::TMEM_COLS));
 }
 
+// ---------------------------------------------------------------------------
+// K5d, wide form (the default): 128(i) x 256(j) tiles.  Shared-memory bandwidth is what bounds
+// the 128 x 128 forms: three MMAs per k8 each read both operands again (48 KB per k-block of 16)
+// on top of the TMA writes (16 KB) and the lo pass (32 KB): 200 bytes per clock wanted, 128
+// available.  With N = 256 a panel tile serves twice the work, the panel's lo tile comes
+// precomputed through TMA (the panel is small and shared by every point tile), and the producer
+// warps compute only X's lo tile: about 140 bytes per clock at the full MMA rate.  TMEM holds one
+// accumulator pair (main 256 + cross 256 columns), so the epilogue of a tile is not overlapped
+// (about a tenth of the tile time).  Stage = P raw 8 KB, P lo 8 KB, X raw 16 KB, X lo 16 KB; ring of 4.
+// ---------------------------------------------------------------------------
+namespace tw {
+constexpr int TM = 128, TN = 256, TK = 16, NSTAGE = 4;
+constexpr int EPI = 128, PRODUCERS = 128, THREADS = EPI + PRODUCERS + 64;
+constexpr uint32_t PT_BYTES = TM * TK * 4, XT_BYTES = TN * TK * 4;     // 8 KB, 16 KB
+constexpr uint32_t STAGE_BYTES = 2 * PT_BYTES + 2 * XT_BYTES;          // 48 KB
+constexpr uint32_t OFF_PLO = PT_BYTES, OFF_X = 2 * PT_BYTES, OFF_XLO = 2 * PT_BYTES + XT_BYTES;
+constexpr size_t SMEM = (size_t)NSTAGE * STAGE_BYTES + 1024 + 256;
+constexpr uint32_t TMEM_COLS = 512;            // main 256 + cross 256
+}  // namespace tw
+
+__device__ __forceinline__ void tw_tile(const TmArgs &a, long long t, size_t &i0, size_t &j0) {
+    constexpr int GI = 16;
+    const long long per = (long long)GI * a.ntn, grp = t / per, tp_ = t - grp * per;
+    const int gi = (int)min((long long)GI, (long long)a.ntm - grp * GI);
+    j0 = (size_t)(tp_ / gi) * tw::TN; i0 = (size_t)(grp * GI + tp_ % gi) * tw::TM;
+}
+
+__global__ void __launch_bounds__(tw::THREADS, 1)
+k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmPlo,
+                      const __grid_constant__ CUtensorMap tmX, TmArgs a,
+                      long long ntiles) {
+    using namespace tw;
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t sbase = ((uint32_t)__cvta_generic_to_shared(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = sbase + NSTAGE * STAGE_BYTES;   // tma[6], full[6], empty[6], accfull[2], accempty[2]
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nk = a.nk;
+    auto tma_bar = [&](int s) { return bars + 8u * s; };
+    auto full_bar = [&](int s) { return bars + 8u * (NSTAGE + s); };
+    auto empty_bar = [&](int s) { return bars + 8u * (2 * NSTAGE + s); };
+    auto accfull_bar = [&](int b) { return bars + 8u * (3 * NSTAGE + b); };
+    auto accempty_bar = [&](int b) { return bars + 8u * (3 * NSTAGE + 2 + b); };
+
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; s++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tma_bar(s)));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full_bar(s)), "r"(PRODUCERS));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(empty_bar(s)));
+        }
+        for (int b = 0; b < 2; b++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(accfull_bar(b)));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(accempty_bar(b)), "r"(EPI));
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;");
+    }
+    if (warp == 8) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(&tmem_slot)), "n"(TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem = tmem_slot;
+
+    if (warp == 9) {
+        if (lane == 0) {
+            // ===== TMA issuer: g counts stages over all tiles of this CTA =====
+            long long g = 0;
+            for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+                size_t i0, j0; tw_tile(a, t, i0, j0);
+                for (int kb = 0; kb < nk; kb++, g++) {
+                    const int s = (int)(g % NSTAGE);
+                    if (g >= NSTAGE) mbar_wait(empty_bar(s), (uint32_t)((g / NSTAGE - 1) & 1));
+                    const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tma_bar(s)), "r"(2 * PT_BYTES + XT_BYTES) : "memory");
+                    tma_load_2d(st0, &tmP, kb * TK, (int)i0, tma_bar(s));
+                    tma_load_2d(st0 + OFF_PLO, &tmPlo, kb * TK, (int)i0, tma_bar(s));
+                    tma_load_2d(st0 + OFF_X, &tmX, kb * TK, (int)j0, tma_bar(s));
+                }
+            }
+        }
+    } else if (warp == 8) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+            long long g = 0; int it = 0;
+            for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
+                const int buf = 0;
+                if (it >= 1) mbar_wait(accempty_bar(buf), (uint32_t)((it - 1) & 1));          // epilogue drained the accumulators
+                asm volatile("tcgen05.fence::after_thread_sync;");
+                const uint32_t t_main = tmem, t_cross = tmem + (uint32_t)TN;
+                for (int kb = 0; kb < nk; kb++, g++) {
+                    const int s = (int)(g % NSTAGE);
+                    mbar_wait(full_bar(s), (uint32_t)((g / NSTAGE) & 1));
+                    asm volatile("tcgen05.fence::after_thread_sync;");
+                    const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+#pragma unroll
+                    for (int ks = 0; ks < TK / 8; ks++) {
+                        const uint32_t ko = (uint32_t)ks * 32;
+                        const uint64_t phi = tm_desc(st0 + ko), plo = tm_desc(st0 + OFF_PLO + ko);
+                        const uint64_t xhi = tm_desc(st0 + OFF_X + ko), xlo = tm_desc(st0 + OFF_XLO + ko);
+                        const uint32_t first = (kb | ks) == 0 ? 0u : 1u;
+                        tc_mma(t_cross, plo, xhi, idesc, first);
+                        tc_mma(t_cross, phi, xlo, idesc, 1u);
+                        tc_mma(t_main, phi, xhi, idesc, first);
+                    }
+                    tc_commit(empty_bar(s));
+                }
+                tc_commit(accfull_bar(buf));
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== lo producers (warps 4-7) =====
+        const int pt = tid - EPI;
+        long long g = 0;
+        for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+            for (int kb = 0; kb < nk; kb++, g++) {
+                const int s = (int)(g % NSTAGE);
+                if (lane == 0) mbar_wait(tma_bar(s), (uint32_t)((g / NSTAGE) & 1));
+                __syncwarp();
+                const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+                const uint32_t raw = st0 + OFF_X, lo = st0 + OFF_XLO;
+#pragma unroll
+                for (int c = 0; c < (int)(XT_BYTES / 16) / PRODUCERS; c++) {
+                    const uint32_t off = (uint32_t)(pt + c * PRODUCERS) * 16;
+                    float4 v, l;
+                    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(raw + off));
+                    l.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
+                    l.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
+                    l.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
+                    l.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
+                    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(lo + off), "f"(l.x), "f"(l.y), "f"(l.z), "f"(l.w) : "memory");
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(full_bar(s));
+            }
+        }
+    } else {
+        // ===== epilogue (warps 0-3): warp w owns TMEM lanes [32w, 32w+32) = rows i =====
+        const float osc = (float)a.outscale;
+        int it = 0;
+        for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
+            size_t i0, j0; tw_tile(a, t, i0, j0);
+            const int buf = 0;
+            if (lane == 0) mbar_wait(accfull_bar(buf), (uint32_t)(it & 1));
+            __syncwarp();
+            asm volatile("tcgen05.fence::after_thread_sync;");
+            const size_t i = i0 + (size_t)tid;
+            double sc = 1.0, sh = 0.0;
+            if (a.has_epi && i < a.S) { sc = a.scales[i]; sh = a.shifts[i]; }
+            const uint32_t tb = tmem + ((uint32_t)(warp * 32) << 16);
+            for (int c0 = 0; c0 < TN; c0 += 8) {
+                uint32_t mn[8], cr[8];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                             : "=r"(mn[0]), "=r"(mn[1]), "=r"(mn[2]), "=r"(mn[3]), "=r"(mn[4]), "=r"(mn[5]), "=r"(mn[6]), "=r"(mn[7])
+                             : "r"(tb + (uint32_t)c0));
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                             : "=r"(cr[0]), "=r"(cr[1]), "=r"(cr[2]), "=r"(cr[3]), "=r"(cr[4]), "=r"(cr[5]), "=r"(cr[6]), "=r"(cr[7])
+                             : "r"(tb + (uint32_t)TN + (uint32_t)c0));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (i < a.S) {
+#pragma unroll
+                    for (int e = 0; e < 8; e++) {
+                        const size_t j = j0 + c0 + e;
+                        if (j >= a.m) break;
+                        float v = __uint_as_float(mn[e]) + __uint_as_float(cr[e]);
+                        if (a.has_epi) {
+                            const double arg = fma((double)v, sc, sh);
+                            const double q = rint(arg * 0.15915494309189535);
+                            v = osc * __cosf((float)fma(q, -6.283185307179586, arg));
+                        }
+                        a.OUT[i + j * a.ldo] = v;
+                    }
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;");
+            mbar_arrive(accempty_bar(buf));             // this accumulator pair may be overwritten
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    __syncwarp();
+    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(tw::TMEM_COLS));
+}
+
 static bool tc_enabled() {      // SKB_DEBUG_NO_TCGEN05=1 falls back to the mma.sync kernel
     static const bool on = getenv("SKB_DEBUG_NO_TCGEN05") == nullptr;
     return on;
@@ -1402,7 +1594,7 @@ static size_t tc_kp(size_t K) { return (K + tc::TK - 1) / tc::TK * tc::TK; }
 static size_t tc_workspace_bytes(const DenseParams &p, size_t nloc, size_t m) {
     auto al = [](size_t b) { return (b + 255) / 256 * 256; };
     (void)m;
-    return al(nloc * p.S * sizeof(double)) + al(p.S * tc_kp(nloc) * 4) + 256;
+    return al(nloc * p.S * sizeof(double)) + 2 * al(p.S * tc_kp(nloc) * 4) + 256;     // panel, Pt, Pt_lo
 }
 
 static bool dense_apply_tc_tf32x3(const DenseParams &p, const float *X, size_t ldx, size_t m, size_t koff,
@@ -1448,31 +1640,40 @@ static bool dense_apply_tc_tma(const DenseParams &p, const float *X, size_t ldx,
     const size_t S = p.S, Kp = tc_kp(nloc);
     char *w = reinterpret_cast<char *>(workspace);
     double *P = reinterpret_cast<double *>(w); w += al(nloc * S * sizeof(double));
-    float *Pt = reinterpret_cast<float *>(w);
-    CUtensorMap tmP, tmX;
-    if (!tma_make_map(&tmP, Pt, S, Kp, Kp) || !tma_make_map(&tmX, X, m, nloc, ldx)) return false;
+    float *Pt = reinterpret_cast<float *>(w); w += al(S * Kp * 4);
+    float *Pt_lo = reinterpret_cast<float *>(w);
+    // form: wide = 128 x 256 tiles (default), persist / plain = the 128 x 128 kernels
+    static const char *form_env = getenv("SKB_TC_FORM");
+    const bool wide = !form_env || form_env[0] == 'w';
+    static const bool persist = !form_env || form_env[0] != 'n';      // "nonpersistent"
+    CUtensorMap tmP, tmPlo, tmX;
+    if (!tma_make_map(&tmP, Pt, S, Kp, Kp) || !tma_make_map(&tmPlo, Pt_lo, S, Kp, Kp) ||
+        !tma_make_map(&tmX, X, m, nloc, ldx, wide ? 256 : 128)) return false;
     dense_generate_panel(p, koff, nloc, P, st);
     {
         LaunchScope ls(KC_GEN, st);
         dim3 grid((unsigned)((S + 31) / 32), (unsigned)((Kp + 31) / 32));
-        k_tc_transpose_panel<<<grid, dim3(32, 8), 0, st>>>(P, S, nloc, Kp, Pt);
+        k_tc_transpose_panel<<<grid, dim3(32, 8), 0, st>>>(P, S, nloc, Kp, Pt, wide ? Pt_lo : nullptr);
         SKB_CUDA(cudaGetLastError());
     }
     TmArgs a;
     a.OUT = OUT; a.S = S; a.m = m; a.ldo = ldo;
     a.scales = epi.scales; a.shifts = epi.shifts; a.outscale = epi.outscale;
     a.has_epi = epi.shifts != nullptr ? 1 : 0;
-    const long long ntm = (long long)((S + tm::TM - 1) / tm::TM), ntn = (long long)((m + tm::TN - 1) / tm::TN);
+    const int tn = wide ? tw::TN : tm::TN;
+    const long long ntm = (long long)((S + tm::TM - 1) / tm::TM), ntn = (long long)((m + tn - 1) / tn);
     a.ntm = (int)ntm; a.ntn = (int)ntn; a.nk = (int)(Kp / tm::TK);
-    static const bool persist = getenv("SKB_DEBUG_NO_PERSIST") == nullptr;
+    const long long ntiles = ntm * ntn;
     LaunchScope ls(KC_GEMM, st);
-    if (persist) {
+    if (wide) {
+        SKB_CUDA(cudaFuncSetAttribute(k_dense_gemm_tc_tma_w, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tw::SMEM));
+        k_dense_gemm_tc_tma_w<<<(unsigned)std::min<long long>(ntiles, 148), tw::THREADS, tw::SMEM, st>>>(tmP, tmPlo, tmX, a, ntiles);
+    } else if (persist) {
         SKB_CUDA(cudaFuncSetAttribute(k_dense_gemm_tc_tma_p, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tp::SMEM));
-        const long long ntiles = ntm * ntn;
         k_dense_gemm_tc_tma_p<<<(unsigned)std::min<long long>(ntiles, 148), tp::THREADS, tp::SMEM, st>>>(tmP, tmX, a, ntiles);
     } else {
         SKB_CUDA(cudaFuncSetAttribute(k_dense_gemm_tc_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tm::SMEM));
-        k_dense_gemm_tc_tma<<<(unsigned)(ntm * ntn), tm::THREADS, tm::SMEM, st>>>(tmP, tmX, a);
+        k_dense_gemm_tc_tma<<<(unsigned)ntiles, tm::THREADS, tm::SMEM, st>>>(tmP, tmX, a);
     }
     SKB_CUDA(cudaGetLastError());
     return true;
