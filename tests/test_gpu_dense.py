@@ -188,3 +188,18 @@ def test_fp32_feature_map_keeps_fp32_accuracy(sk, oracle, shape):
     J, OJ = sk.JLT(n, s, context=c), oracle.JLT(n, s, oc)        # no epilogue, same kernel
     got = J.apply(X, None, "rowwise").cpu().numpy()
     assert rel_fro(got, OJ.apply(X.cpu().numpy().astype(np.float64), "rowwise")) < 5e-6
+
+
+@pytest.mark.parametrize("env", [{"SKB_TC_FORM": "persist"}, {"SKB_TC_FORM": "nonpersistent"},
+                                 {"SKB_DEBUG_NO_TMA": "1"}, {"SKB_DEBUG_NO_TCGEN05": "1"}, {"SKB_DEBUG_NO_TF32": "1"}])
+def test_fp32_feature_map_fallback_forms(env):
+    # the other forms of the fp32 feature-map kernel (128 x 128 persistent / per-tile tcgen05 kernels, the
+    # tcgen05 kernel without TMA, the mma.sync kernel, FP64 DMMA) are selected by environment variables that
+    # the library reads once, so each runs in its own process
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    e = dict(os.environ); e.update(env)
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_dense.py"), "-x", "-q",
+                        "-k", "fp32_feature_map_keeps or fp32_tensors"], env=e, cwd=root, capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-500:]
