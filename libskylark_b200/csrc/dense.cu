@@ -1411,7 +1411,11 @@ k_dense_gemm_tc_tma_p(const __grid_constant__ CUtensorMap tmP, const __grid_cons
 // ---------------------------------------------------------------------------
 namespace tw {
 constexpr int TM = 128, TN = 256, TK = 16, NSTAGE = 4;
-constexpr int EPI = 128, PRODUCERS = 128, THREADS = EPI + PRODUCERS + 64;
+#ifndef SKB_TW_PRODUCERS
+#define SKB_TW_PRODUCERS 128
+#endif
+constexpr int EPI = 128, PRODUCERS = SKB_TW_PRODUCERS, THREADS = EPI + PRODUCERS + 64;
+constexpr int WARP_MMA = (EPI + PRODUCERS) / 32, WARP_TMA = WARP_MMA + 1;
 constexpr uint32_t PT_BYTES = TM * TK * 4, XT_BYTES = TN * TK * 4;     // 8 KB, 16 KB
 constexpr uint32_t STAGE_BYTES = 2 * PT_BYTES + 2 * XT_BYTES;          // 48 KB
 constexpr uint32_t OFF_PLO = PT_BYTES, OFF_X = 2 * PT_BYTES, OFF_XLO = 2 * PT_BYTES + XT_BYTES;
@@ -1455,7 +1459,7 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
         }
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
-    if (warp == 8) {
+    if (warp == WARP_MMA) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
                      ::"r"((uint32_t)__cvta_generic_to_shared(&tmem_slot)), "n"(TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
@@ -1465,7 +1469,7 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
     asm volatile("tcgen05.fence::after_thread_sync;");
     const uint32_t tmem = tmem_slot;
 
-    if (warp == 9) {
+    if (warp == WARP_TMA) {
         if (lane == 0) {
             // ===== TMA issuer: g counts stages over all tiles of this CTA =====
             long long g = 0;
@@ -1482,7 +1486,7 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
                 }
             }
         }
-    } else if (warp == 8) {
+    } else if (warp == WARP_MMA) {
         if (lane == 0) {
             // ===== MMA issuer =====
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
@@ -1513,7 +1517,7 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
             }
         }
     } else if (warp >= 4) {
-        // ===== lo producers (warps 4-7) =====
+        // ===== lo producers (warps 4 .. WARP_MMA-1) =====
         const int pt = tid - EPI;
         long long g = 0;
         for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
@@ -1583,7 +1587,7 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
     __syncwarp();
-    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(tw::TMEM_COLS));
+    if (warp == WARP_MMA) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(tw::TMEM_COLS));
 }
 
 static bool tc_enabled() {      // SKB_DEBUG_NO_TCGEN05=1 falls back to the mma.sync kernel
