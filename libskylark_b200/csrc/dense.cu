@@ -1229,6 +1229,7 @@ constexpr int EPI = 128, PRODUCERS = 128, THREADS = EPI + PRODUCERS + 64;
 constexpr uint32_t TILE_BYTES = TM * TK * 4, STAGE_BYTES = 4 * TILE_BYTES;
 constexpr size_t SMEM = (size_t)NSTAGE * STAGE_BYTES + 1024 + 256;
 constexpr uint32_t TMEM_COLS = 512;            // 2 x (main 128 + cross 128)
+constexpr int CHUNK = 16;                      // k-blocks per accumulation chunk: the truncating chain stays at 32 MMAs
 }  // namespace tp
 
 __device__ __forceinline__ void tp_tile(const TmArgs &a, long long t, size_t &i0, size_t &j0) {
@@ -1296,30 +1297,33 @@ k_dense_gemm_tc_tma_p(const __grid_constant__ CUtensorMap tmP, const __grid_cons
         if (lane == 0) {
             // ===== MMA issuer =====
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
-            long long g = 0; int it = 0;
-            for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
-                const int buf = it & 1;
-                if (it >= 2) mbar_wait(accempty_bar(buf), (uint32_t)(((it >> 1) - 1) & 1));   // epilogue drained this pair
-                asm volatile("tcgen05.fence::after_thread_sync;");
-                const uint32_t t_main = tmem + (uint32_t)buf * 256, t_cross = t_main + (uint32_t)TN;
-                for (int kb = 0; kb < nk; kb++, g++) {
-                    const int s = (int)(g % NSTAGE);
-                    mbar_wait(full_bar(s), (uint32_t)((g / NSTAGE) & 1));
+            long long g = 0; int u = 0;                 // u counts (tile, chunk) units; accumulator pair = u & 1
+            for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+                for (int k0 = 0; k0 < nk; k0 += CHUNK, u++) {
+                    const int buf = u & 1;
+                    if (u >= 2) mbar_wait(accempty_bar(buf), (uint32_t)(((u >> 1) - 1) & 1));   // epilogue drained this pair
                     asm volatile("tcgen05.fence::after_thread_sync;");
-                    const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
+                    const uint32_t t_main = tmem + (uint32_t)buf * 256, t_cross = t_main + (uint32_t)TN;
+                    const int k1 = min(nk, k0 + CHUNK);
+                    for (int kb = k0; kb < k1; kb++, g++) {
+                        const int s = (int)(g % NSTAGE);
+                        mbar_wait(full_bar(s), (uint32_t)((g / NSTAGE) & 1));
+                        asm volatile("tcgen05.fence::after_thread_sync;");
+                        const uint32_t st0 = sbase + (uint32_t)s * STAGE_BYTES;
 #pragma unroll
-                    for (int ks = 0; ks < TK / 8; ks++) {
-                        const uint32_t ko = (uint32_t)ks * 32;
-                        const uint64_t phi = tm_desc(st0 + ko), plo = tm_desc(st0 + TILE_BYTES + ko);
-                        const uint64_t xhi = tm_desc(st0 + 2 * TILE_BYTES + ko), xlo = tm_desc(st0 + 3 * TILE_BYTES + ko);
-                        const uint32_t first = (kb | ks) == 0 ? 0u : 1u;
-                        tc_mma(t_cross, plo, xhi, idesc, first);
-                        tc_mma(t_cross, phi, xlo, idesc, 1u);
-                        tc_mma(t_main, phi, xhi, idesc, first);
+                        for (int ks = 0; ks < TK / 8; ks++) {
+                            const uint32_t ko = (uint32_t)ks * 32;
+                            const uint64_t phi = tm_desc(st0 + ko), plo = tm_desc(st0 + TILE_BYTES + ko);
+                            const uint64_t xhi = tm_desc(st0 + 2 * TILE_BYTES + ko), xlo = tm_desc(st0 + 3 * TILE_BYTES + ko);
+                            const uint32_t first = (kb == k0 && ks == 0) ? 0u : 1u;
+                            tc_mma(t_cross, plo, xhi, idesc, first);
+                            tc_mma(t_cross, phi, xlo, idesc, 1u);
+                            tc_mma(t_main, phi, xhi, idesc, first);
+                        }
+                        tc_commit(empty_bar(s));
                     }
-                    tc_commit(empty_bar(s));
+                    tc_commit(accfull_bar(buf));
                 }
-                tc_commit(accfull_bar(buf));
             }
         }
     } else if (warp >= 4) {
@@ -1354,32 +1358,43 @@ k_dense_gemm_tc_tma_p(const __grid_constant__ CUtensorMap tmP, const __grid_cons
     } else {
         // ===== epilogue (warps 0-3): warp w owns TMEM lanes [32w, 32w+32) = rows i =====
         const float osc = (float)a.outscale;
-        int it = 0;
-        for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
+        int u = 0;
+        for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
             size_t i0, j0; tp_tile(a, t, i0, j0);
-            const int buf = it & 1;
-            if (lane == 0) mbar_wait(accfull_bar(buf), (uint32_t)((it >> 1) & 1));
-            __syncwarp();
-            asm volatile("tcgen05.fence::after_thread_sync;");
-            const size_t i = i0 + (size_t)tid;
-            double sc = 1.0, sh = 0.0;
-            if (a.has_epi && i < a.S) { sc = a.scales[i]; sh = a.shifts[i]; }
-            const uint32_t tb = tmem + (uint32_t)buf * 256 + ((uint32_t)(warp * 32) << 16);
-            for (int c0 = 0; c0 < TN; c0 += 8) {
-                uint32_t mn[8], cr[8];
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                             : "=r"(mn[0]), "=r"(mn[1]), "=r"(mn[2]), "=r"(mn[3]), "=r"(mn[4]), "=r"(mn[5]), "=r"(mn[6]), "=r"(mn[7])
-                             : "r"(tb + (uint32_t)c0));
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                             : "=r"(cr[0]), "=r"(cr[1]), "=r"(cr[2]), "=r"(cr[3]), "=r"(cr[4]), "=r"(cr[5]), "=r"(cr[6]), "=r"(cr[7])
-                             : "r"(tb + (uint32_t)TN + (uint32_t)c0));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (i < a.S) {
+            float acc[TN];                      // running sums in registers, added with round-to-nearest
 #pragma unroll
-                    for (int e = 0; e < 8; e++) {
-                        const size_t j = j0 + c0 + e;
-                        if (j >= a.m) break;
-                        float v = __uint_as_float(mn[e]) + __uint_as_float(cr[e]);
+            for (int c = 0; c < TN; c++) acc[c] = 0.f;
+            for (int k0 = 0; k0 < nk; k0 += CHUNK, u++) {
+                const int buf = u & 1;
+                if (lane == 0) mbar_wait(accfull_bar(buf), (uint32_t)((u >> 1) & 1));
+                __syncwarp();
+                asm volatile("tcgen05.fence::after_thread_sync;");
+                const uint32_t tb = tmem + (uint32_t)buf * 256 + ((uint32_t)(warp * 32) << 16);
+#pragma unroll
+                for (int c0 = 0; c0 < TN; c0 += 8) {
+                    uint32_t mn[8], cr[8];
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(mn[0]), "=r"(mn[1]), "=r"(mn[2]), "=r"(mn[3]), "=r"(mn[4]), "=r"(mn[5]), "=r"(mn[6]), "=r"(mn[7])
+                                 : "r"(tb + (uint32_t)c0));
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(cr[0]), "=r"(cr[1]), "=r"(cr[2]), "=r"(cr[3]), "=r"(cr[4]), "=r"(cr[5]), "=r"(cr[6]), "=r"(cr[7])
+                                 : "r"(tb + (uint32_t)TN + (uint32_t)c0));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                    for (int e = 0; e < 8; e++) acc[c0 + e] += __uint_as_float(mn[e]) + __uint_as_float(cr[e]);
+                }
+                asm volatile("tcgen05.fence::before_thread_sync;");
+                mbar_arrive(accempty_bar(buf));             // this accumulator pair may be overwritten
+            }
+            const size_t i = i0 + (size_t)tid;
+            if (i < a.S) {
+                double sc = 1.0, sh = 0.0;
+                if (a.has_epi) { sc = a.scales[i]; sh = a.shifts[i]; }
+#pragma unroll
+                for (int c = 0; c < TN; c++) {
+                    const size_t j = j0 + c;
+                    if (j < a.m) {
+                        float v = acc[c];
                         if (a.has_epi) {
                             const double arg = fma((double)v, sc, sh);
                             const double q = rint(arg * 0.15915494309189535);
@@ -1389,8 +1404,6 @@ k_dense_gemm_tc_tma_p(const __grid_constant__ CUtensorMap tmP, const __grid_cons
                     }
                 }
             }
-            asm volatile("tcgen05.fence::before_thread_sync;");
-            mbar_arrive(accempty_bar(buf));             // this accumulator pair may be overwritten
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;");
@@ -1638,7 +1651,7 @@ static bool dense_apply_tc_tma(const DenseParams &p, const float *X, size_t ldx,
                                size_t nloc, float *OUT, size_t ldo, const RftEpilogue &epi,
                                void *workspace, size_t workspace_bytes, cudaStream_t st) {
     static const bool off = getenv("SKB_DEBUG_NO_TMA") != nullptr;
-    if (off || !tc_enabled() || nloc > 1024 || !dense_tf32_path_ok(p, X, ldx, m, nloc)) return false;
+    if (off || !tc_enabled() || !dense_tf32_path_ok(p, X, ldx, m, nloc)) return false;
     if (workspace_bytes < tc_workspace_bytes(p, nloc, m) || !tma_encoder()) return false;
     auto al = [](size_t b) { return (b + 255) / 256 * 256; };
     const size_t S = p.S, Kp = tc_kp(nloc);
@@ -1647,9 +1660,12 @@ static bool dense_apply_tc_tma(const DenseParams &p, const float *X, size_t ldx,
     float *Pt = reinterpret_cast<float *>(w); w += al(S * Kp * 4);
     float *Pt_lo = reinterpret_cast<float *>(w);
     // form: wide = 128 x 256 tiles (default), persist / plain = the 128 x 128 kernels
+    // the wide form keeps one accumulation chain per tile (error grows with k: 3.4e-6 at k = 784), the
+    // persistent form drains its accumulators every 16 k-blocks (1.4e-6, independent of k): short
+    // contractions take the faster one, long ones the chunked one
     static const char *form_env = getenv("SKB_TC_FORM");
-    const bool wide = !form_env || form_env[0] == 'w';
-    static const bool persist = !form_env || form_env[0] != 'n';      // "nonpersistent"
+    const bool wide = nloc <= 1024 && (!form_env || form_env[0] == 'w');
+    const bool persist = nloc > 1024 || !form_env || form_env[0] != 'n';      // "nonpersistent"
     CUtensorMap tmP, tmPlo, tmX;
     if (!tma_make_map(&tmP, Pt, S, Kp, Kp) || !tma_make_map(&tmPlo, Pt_lo, S, Kp, Kp) ||
         !tma_make_map(&tmX, X, m, nloc, ldx, wide ? 256 : 128)) return false;
