@@ -170,13 +170,13 @@ def test_dense_transform_of_sparse_operand(sk, oracle, T, fmt):
 
 
 @pytest.mark.parametrize("shape", [(784, 16384, 700), (100, 520, 133), (36, 12, 5), (16, 4, 1), (1028, 260, 300),
-                                   (2000, 128, 129)])      # the last two: k > 1024 -> mma.sync kernel
+                                   (2000, 128, 129)])      # the last two: k > 1024 -> the draining form
 def test_fp32_feature_map_keeps_fp32_accuracy(sk, oracle, shape):
     # the strided fp32 case runs on the TF32 tensor cores with operand splitting.  Tensor-core
     # accumulation truncates, so one chain over all three products would sit at ~9e-6; the
-    # tcgen05 kernel keeps the large term in its own accumulator (3.4e-6 at k = 784), the
-    # mma.sync kernel restarts its accumulator every 8 (6.5e-7) -- asserted inside the 1e-5 bar,
-    # edge tiles included
+    # tcgen05 kernel keeps the large term in its own accumulator (3.4e-6 at k = 784) and, for
+    # k > 1024, drains it every 32 MMAs (1.4e-6); the mma.sync kernel restarts its accumulator
+    # every 8 (6.5e-7) -- asserted inside the 1e-5 bar, edge tiles included
     import torch
     n, s, m = shape
     c, oc = _ctx(sk, oracle, 7)
