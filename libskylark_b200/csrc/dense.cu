@@ -1468,7 +1468,7 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
         }
         for (int b = 0; b < 2; b++) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(accfull_bar(b)));
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(accempty_bar(b)), "r"(EPI));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(accempty_bar(b)), "r"(EPI + PRODUCERS));
         }
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
@@ -1481,6 +1481,45 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;");
     const uint32_t tmem = tmem_slot;
+
+    // epilogue of one tile for 128 of its 256 columns; warp w reads TMEM lanes [32(w%4), +32) = rows i
+    auto drain = [&](long long t, int it, int cbeg) {
+        const float osc = (float)a.outscale;
+        size_t i0, j0; tw_tile(a, t, i0, j0);
+        if (lane == 0) mbar_wait(accfull_bar(0), (uint32_t)(it & 1));
+        __syncwarp();
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        const size_t i = i0 + (size_t)((warp & 3) * 32 + lane);
+        double sc = 1.0, sh = 0.0;
+        if (a.has_epi && i < a.S) { sc = a.scales[i]; sh = a.shifts[i]; }
+        const uint32_t tb = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+        for (int c0 = cbeg; c0 < cbeg + 128; c0 += 8) {
+            uint32_t mn[8], cr[8];
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(mn[0]), "=r"(mn[1]), "=r"(mn[2]), "=r"(mn[3]), "=r"(mn[4]), "=r"(mn[5]), "=r"(mn[6]), "=r"(mn[7])
+                         : "r"(tb + (uint32_t)c0));
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(cr[0]), "=r"(cr[1]), "=r"(cr[2]), "=r"(cr[3]), "=r"(cr[4]), "=r"(cr[5]), "=r"(cr[6]), "=r"(cr[7])
+                         : "r"(tb + (uint32_t)TN + (uint32_t)c0));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (i < a.S) {
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                    const size_t j = j0 + c0 + e;
+                    if (j >= a.m) break;
+                    float v = __uint_as_float(mn[e]) + __uint_as_float(cr[e]);
+                    if (a.has_epi) {
+                        const double arg = fma((double)v, sc, sh);
+                        const double q = rint(arg * 0.15915494309189535);
+                        v = osc * __cosf((float)fma(q, -6.283185307179586, arg));
+                    }
+                    a.OUT[i + j * a.ldo] = v;
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;");
+        mbar_arrive(accempty_bar(0));             // the accumulators may be overwritten once all 256 arrive
+    };
 
     if (warp == WARP_TMA) {
         if (lane == 0) {
@@ -1532,8 +1571,8 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
     } else if (warp >= 4) {
         // ===== lo producers (warps 4 .. WARP_MMA-1) =====
         const int pt = tid - EPI;
-        long long g = 0;
-        for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        long long g = 0; int pit = 0;
+        for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, pit++) {
             for (int kb = 0; kb < nk; kb++, g++) {
                 const int s = (int)(g % NSTAGE);
                 if (lane == 0) mbar_wait(tma_bar(s), (uint32_t)((g / NSTAGE) & 1));
@@ -1554,48 +1593,12 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_arrive(full_bar(s));
             }
+            drain(t, pit, 128);          // the MMAs of the next tile cannot start before the epilogue anyway
         }
     } else {
-        // ===== epilogue (warps 0-3): warp w owns TMEM lanes [32w, 32w+32) = rows i =====
-        const float osc = (float)a.outscale;
+        // ===== epilogue (warps 0-3): columns [0, 128) of every tile; the lo producers take [128, 256) =====
         int it = 0;
-        for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
-            size_t i0, j0; tw_tile(a, t, i0, j0);
-            const int buf = 0;
-            if (lane == 0) mbar_wait(accfull_bar(buf), (uint32_t)(it & 1));
-            __syncwarp();
-            asm volatile("tcgen05.fence::after_thread_sync;");
-            const size_t i = i0 + (size_t)tid;
-            double sc = 1.0, sh = 0.0;
-            if (a.has_epi && i < a.S) { sc = a.scales[i]; sh = a.shifts[i]; }
-            const uint32_t tb = tmem + ((uint32_t)(warp * 32) << 16);
-            for (int c0 = 0; c0 < TN; c0 += 8) {
-                uint32_t mn[8], cr[8];
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                             : "=r"(mn[0]), "=r"(mn[1]), "=r"(mn[2]), "=r"(mn[3]), "=r"(mn[4]), "=r"(mn[5]), "=r"(mn[6]), "=r"(mn[7])
-                             : "r"(tb + (uint32_t)c0));
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                             : "=r"(cr[0]), "=r"(cr[1]), "=r"(cr[2]), "=r"(cr[3]), "=r"(cr[4]), "=r"(cr[5]), "=r"(cr[6]), "=r"(cr[7])
-                             : "r"(tb + (uint32_t)TN + (uint32_t)c0));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (i < a.S) {
-#pragma unroll
-                    for (int e = 0; e < 8; e++) {
-                        const size_t j = j0 + c0 + e;
-                        if (j >= a.m) break;
-                        float v = __uint_as_float(mn[e]) + __uint_as_float(cr[e]);
-                        if (a.has_epi) {
-                            const double arg = fma((double)v, sc, sh);
-                            const double q = rint(arg * 0.15915494309189535);
-                            v = osc * __cosf((float)fma(q, -6.283185307179586, arg));
-                        }
-                        a.OUT[i + j * a.ldo] = v;
-                    }
-                }
-            }
-            asm volatile("tcgen05.fence::before_thread_sync;");
-            mbar_arrive(accempty_bar(buf));             // this accumulator pair may be overwritten
-        }
+        for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, it++) drain(t, it, 0);
     }
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
