@@ -1490,8 +1490,8 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
         __syncwarp();
         asm volatile("tcgen05.fence::after_thread_sync;");
         const size_t i = i0 + (size_t)((warp & 3) * 32 + lane);
-        double sc = 1.0, sh = 0.0;
-        if (a.has_epi && i < a.S) { sc = a.scales[i]; sh = a.shifts[i]; }
+        float scf = 1.f, shf = 0.f;
+        if (a.has_epi && i < a.S) { scf = (float)a.scales[i]; shf = (float)a.shifts[i]; }
         const uint32_t tb = tmem + ((uint32_t)((warp & 3) * 32) << 16);
         for (int c0 = cbeg; c0 < cbeg + 128; c0 += 8) {
             uint32_t mn[8], cr[8];
@@ -1508,10 +1508,12 @@ k_dense_gemm_tc_tma_w(const __grid_constant__ CUtensorMap tmP, const __grid_cons
                     const size_t j = j0 + c0 + e;
                     if (j >= a.m) break;
                     float v = __uint_as_float(mn[e]) + __uint_as_float(cr[e]);
-                    if (a.has_epi) {
-                        const double arg = fma((double)v, sc, sh);
-                        const double q = rint(arg * 0.15915494309189535);
-                        v = osc * __cosf((float)fma(q, -6.283185307179586, arg));
+                    if (a.has_epi) {       // fp32 throughout, like the accumulator: two-constant reduction to [-pi, pi]
+                        const float arg = fmaf(v, scf, shf);
+                        const float q = rintf(arg * 0.15915494f);
+                        float r = fmaf(q, -6.2831855f, arg);
+                        r = fmaf(q, 1.7484555e-7f, r);            // 2*pi = 6.2831855f - 1.7484555e-7
+                        v = osc * __cosf(r);
                     }
                     a.OUT[i + j * a.ldo] = v;
                 }
