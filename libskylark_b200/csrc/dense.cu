@@ -720,16 +720,18 @@ __global__ void __launch_bounds__(tf32::TNT, 2) k_dense_gemm_tf32x3(Tf32Args a) 
 }
 
 // ---------------------------------------------------------------------------
-// K5d: the same 3xTF32 product on the 5th-generation tensor cores (tcgen05.mma.kind::tf32,
-// accumulators in TMEM).  The tensor core reads shared memory itself, so operands are split
-// BEFORE they get there: a pre-pass writes hi / lo copies of the panel (transposed to K-major)
-// and of X, padded with zeros to a multiple of 16 in k.  A CTA owns a 128(i) x 128(j) tile:
-// 4 producer warps fill a 3-stage ring with cp.async in the no-swizzle K-major core-matrix
-// layout (element (r,k) at (r/8)*512 + (k/4)*128 + (r%8)*16 + (k%4)*4), one thread issues the
-// MMAs -- hi*hi into one TMEM accumulator, lo*hi and hi*lo into a second one, so the long
-// truncating chain carries only the large term once -- and the producer warps, done loading,
-// read both accumulators back (tcgen05.ld), add them and apply the epilogue.  Two CTAs fit an
-// SM (96 KB of shared memory, 256 TMEM columns each): one's epilogue overlaps the other's MMAs.
+// K5d (form without TMA; the fallback when the driver offers no tensor-map encoder): the same
+// 3xTF32 product on the 5th-generation tensor cores (tcgen05.mma.kind::tf32, accumulators in
+// TMEM).  The tensor core reads shared memory itself, so operands are split BEFORE they get
+// there.  A CTA owns a 128(i) x 128(j) tile: 4 producer warps load the raw fp32 rows (panel
+// transposed to K-major by a pre-pass and padded with zeros to a multiple of 16 in k; X from the
+// caller's buffer), split them in registers and store hi and lo tiles in the no-swizzle K-major
+// core-matrix layout (element (r,k) at (r/8)*512 + (k/4)*128 + (r%8)*16 + (k%4)*4) of a 3-stage
+// ring; one thread issues the MMAs -- hi*hi into one TMEM accumulator, lo*hi and hi*lo into a
+// second one, so the long truncating chain carries only the large term once -- and the producer
+// warps, done loading, read both accumulators back (tcgen05.ld), add them and apply the epilogue.
+// Two CTAs fit an SM (96 KB of shared memory, 256 TMEM columns each): one's epilogue overlaps the
+// other's MMAs.  The TMA forms further down are the ones normally used.
 // Measured accumulator behaviour (tools/tcgen05_probe.cu): operands are truncated to TF32,
 // a chain of 100 accumulating MMAs loses 1.6e-6 (relative, Frobenius), 32 lose 2.3e-7.
 // ---------------------------------------------------------------------------
