@@ -775,14 +775,12 @@ __device__ __forceinline__ void tc_mma(uint32_t tmem, uint64_t ad, uint64_t bd, 
                  ::"r"(tmem), "l"(ad), "l"(bd), "r"(idesc), "r"(accum) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    // try_wait goes through the same pipe as the shared-memory stores: back off between polls
+    // only single threads and elected lanes wait here, so a plain try_wait loop (which suspends in
+    // hardware for a bounded time) costs nothing elsewhere and adds no wake-up latency
     uint32_t done = 0;
-    for (;;) {
+    while (!done)
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
                      "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-        if (done) break;
-        __nanosleep(32);
-    }
 }
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
