@@ -51,9 +51,13 @@ def cpu_reference_sample(n_sample, repeats=1):
     o.lib()
     try:
         import torch
-        torch.set_num_threads(os.cpu_count() or 1)
+        torch.set_num_threads(_host_cores())
     except Exception:
         torch = None
+    try:
+        o.lib().sko_set_num_threads(_host_cores())
+    except Exception:
+        pass
     rng = np.random.default_rng(DATA_SEED)
     A = rng.standard_normal((n_sample, D_COLS))
     ctx = o.Context(SKETCH_SEED)
@@ -71,7 +75,7 @@ def cpu_reference_sample(n_sample, repeats=1):
         times.append(time.perf_counter() - t0)
     del SA
     dt = statistics.median(times)
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = _host_cores()
     return {"seconds": dt, "tflops": flops_per_step(n_sample) / dt / 1e12, "cores": cores,
             "threads": o.num_threads(),
             "sample": "first %d of %d rows (time is linear in rows): S realised entry by entry "
@@ -93,8 +97,9 @@ def run_reference(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "note": "reference CPU algorithm (oracle port; the "
                        "Elemental/MPI build is unavailable on this box), bounded sample"},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": res[0]["cores"], "kind": "port",
-                             "sample": res[0]["sample"]},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": res[0]["cores"],
+                             "threads": res[0]["threads"], "kind": "port", "sample": res[0]["sample"]},
+            "threads": res[0]["threads"],
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
     return 0
@@ -155,6 +160,27 @@ class ClockSampler:
 # ---------------------------------------------------------------------------
 # ours
 # ---------------------------------------------------------------------------
+def measured_hbm_gbs():
+    """(GB/s, source): the driver-measured copy bandwidth of this pool's B200s, else the
+    fallback the profiling recipe states."""
+    try:
+        v = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+        return v, "MEASURED_PEAKS.json hbm_gbs (driver-measured copy, read+write)"
+    except Exception:
+        return 6500.0, "fallback: MEASURED_PEAKS.json absent"
+
+
+def committed_dram_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed
+    summary of an `ncu --set full` capture of this bench command (profiles/dram_traffic.json,
+    written by tools/ncu_summary.py); None when no capture of the current kernel is committed."""
+    try:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json")))[kernel]
+        return rec["dram_bytes_per_launch"], rec.get("source")
+    except Exception:
+        return None, None
+
+
 def measure_fp64_gemm_peak(torch):
     """cuBLAS DGEMM 8192^3 through torch.matmul, best of 5 -- the FP64 counterpart of the
     driver's bf16 figure in MEASURED_PEAKS.json (which has no FP64 entry)."""
@@ -249,10 +275,13 @@ def other_configs(torch, lib, sketch, hbm_gbs, fp64_peak):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     def guarded(name, fn):
+        sampler = ClockSampler(torch.cuda.current_device())
+        sampler.start()
         try:
             out[name] = fn()
         except Exception as e:      # never lose the main line
             out[name] = {"error": str(e)[:200]}
+        out[name]["clocks"] = sampler.stop()
         torch.cuda.empty_cache()
 
     def c1(order):
@@ -579,7 +608,7 @@ def run_ours(args):
         del A, SA
         torch.cuda.empty_cache()
         try:
-            multi = multi_gpu_configs(torch, dist, lib, sketch, rank, world, 6533.5)
+            multi = multi_gpu_configs(torch, dist, lib, sketch, rank, world, measured_hbm_gbs()[0])
         except Exception as e:      # keep the main line
             multi = {"error": str(e)[:300]}
     if rank != 0:
@@ -594,14 +623,14 @@ def run_ours(args):
     launches = sum(v[0] for v in prof.values())
     flops_per_launch = flops_per_step(N_ROWS) * args.steps / max(1, gemm_launches)
     peak = measure_fp64_gemm_peak(torch)
+    traffic, traffic_src = committed_dram_traffic("k_dense_gemm")
     achieved = flops_per_launch / (gemm_ms / max(1, gemm_launches) * 1e-3) / 1e12 if gemm_ms else None
     roofline = {"bound": "tensor", "kernel": "k_dense_gemm (FP64 DMMA m8n8k4)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                 "frac": (achieved / peak) if achieved else None,
-                # dram__bytes_read.sum + dram__bytes_write.sum of one GEMM launch (8192-row panel)
-                # from the ncu --set full capture summarised in profiles/r01_kernels_v2.txt
-                "traffic": 2.77e9, "traffic_unit": "bytes per launch (algorithmic operand bytes: "
-                "panel 268 MB + X slab 67 MB + SA 34 MB)",
+                "traffic": traffic, "traffic_unit": "DRAM bytes per launch (dram__bytes_read.sum + "
+                "dram__bytes_write.sum, ncu --set full): " + str(traffic_src),
+                "algorithmic_operand_bytes_per_launch": 8192 * S_ROWS * 8 + 8192 * D_COLS * 8 + S_ROWS * D_COLS * 8,
                 "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul fp64, best of 5, measured in "
                                "this run (MEASURED_PEAKS.json has no FP64 entry)",
                 "flops_per_launch": flops_per_launch,
@@ -609,18 +638,14 @@ def run_ours(args):
                                        "dense_gen": gen_ms / args.steps},
                 "launches_per_step": {"dense_gemm": gemm_launches / args.steps,
                                       "dense_gen": gen_launches / args.steps}}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        roofline["hbm_gbs_measured"] = peaks.get("hbm_gbs")
-    except Exception:
-        pass
+    roofline["hbm_gbs_measured"], roofline["hbm_gbs_source"] = measured_hbm_gbs()
 
     cpu = cpu_reference_sample(CPU_SAMPLE_ROWS) if world == 1 else None
     extra = None
     if world == 1:
         del A, SA, S
         torch.cuda.empty_cache()
-        extra = other_configs(torch, lib, sketch, roofline.get("hbm_gbs_measured") or 6533.5, peak)
+        extra = other_configs(torch, lib, sketch, roofline["hbm_gbs_measured"], peak)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -646,6 +671,20 @@ def run_ours(args):
     return 0
 
 
+def _host_cores():
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
+def _pin_cpu_threads():
+    """The CPU legs use every host core this process may run on.  torchrun exports
+    OMP_NUM_THREADS=1 to its workers, which would time the reference arm on one core: set the
+    OpenMP / BLAS thread counts explicitly, before numpy or the oracle library are loaded."""
+    n = str(_host_cores())
+    for k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[k] = n
+    return int(n)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -654,7 +693,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
     if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:
+            return 0
+        _pin_cpu_threads()
         return run_reference(args)
+    if int(os.environ.get("WORLD_SIZE", "1")) == 1:
+        _pin_cpu_threads()          # cpu_baseline legs run on rank 0 of a single-GPU run only
     return run_ours(args)
 
 

@@ -168,6 +168,8 @@ int sl_profile_read(unsigned long long launches[SL_KERNEL_CLASSES],
  * Limits and rules:
  *   - s must be at most 262144 (16 panel rows have to fit in the 4 Mi-double array); larger s
  *     is refused with code 111 and a message.  n and m are not limited.
+ *   - The array used is the one of the CURRENT device: A_dev, SA_dev and the stream must belong
+ *     to it (operands of another device are refused with code 112).
  *   - The first call on each device looks up the array's device address (and loads the
  *     kernels); make that first call outside any stream capture.
  *   - All calls on a device share the one array.  Nothing in it needs clearing between

@@ -229,13 +229,21 @@ static void ensure_ws(DevState &d, size_t bytes) {
     d.ws_bytes = bytes;
 }
 
+// Device tables are cached per (transform, device).  They are built on the calling thread's
+// stream and the build is waited for once, so that a later apply on ANY stream may read them; the
+// DevState pointers are published only after every allocation and launch has succeeded.
 static void ensure_hash_tables(sl_sketch_transform_t *t, DevState &d) {
     if (d.bucket) return;
-    SKB_CUDA(cudaMalloc(&d.bucket, (size_t)t->N * sizeof(int32_t)));
-    SKB_CUDA(cudaMalloc(&d.value, (size_t)t->N * sizeof(double)));
-    int kind = t->type == T_CWT ? HV_RADEMACHER : t->type == T_MMT ? HV_CAUCHY : HV_WZT;
-    hash_build_tables(t->seed, t->base0, t->base1, t->base2, 0, (size_t)t->N, (uint64_t)t->S, kind,
-                      t->param, t->order, d.bucket, d.value, g_stream);
+    int32_t *bucket = nullptr; double *value = nullptr;
+    try {
+        SKB_CUDA(cudaMalloc(&bucket, (size_t)t->N * sizeof(int32_t)));
+        SKB_CUDA(cudaMalloc(&value, (size_t)t->N * sizeof(double)));
+        int kind = t->type == T_CWT ? HV_RADEMACHER : t->type == T_MMT ? HV_CAUCHY : HV_WZT;
+        hash_build_tables(t->seed, t->base0, t->base1, t->base2, 0, (size_t)t->N, (uint64_t)t->S, kind,
+                          t->param, t->order, bucket, value, g_stream);
+        SKB_CUDA(cudaStreamSynchronize(g_stream));
+    } catch (...) { cudaFree(bucket); cudaFree(value); throw; }
+    d.value = value; d.bucket = bucket;
 }
 
 static void ensure_rft_tables(sl_sketch_transform_t *t, DevState &d) {
@@ -256,24 +264,24 @@ static void ensure_rft_tables(sl_sketch_transform_t *t, DevState &d) {
 
 static void ensure_fjlt_tables(sl_sketch_transform_t *t, DevState &d) {
     if (d.D) return;
-    SKB_CUDA(cudaMalloc(&d.D, (size_t)t->N * sizeof(double)));
-    SKB_CUDA(cudaMalloc(&d.samples, (size_t)t->S * sizeof(int32_t)));
-    SKB_CUDA(cudaMalloc(&d.Dbits, ((size_t)t->N / 32 + 1) * sizeof(uint32_t)));
-    fjlt_build_tables(t->seed, t->base0, (size_t)t->N, (size_t)t->S, t->order, d.D, d.samples,
-                      d.Dbits, g_stream);
-    if (t->fut == FUT_WHT) {     // gather layout of the WHT kernel, computed once from the samples
-        std::vector<int32_t> hs((size_t)t->S), slot_sample, slot_out;
-        SKB_CUDA(cudaMemcpyAsync(hs.data(), d.samples, hs.size() * sizeof(int32_t),
-                                 cudaMemcpyDeviceToHost, g_stream));
+    double *D = nullptr; int32_t *samples = nullptr, *ss = nullptr, *so = nullptr; uint32_t *Dbits = nullptr;
+    try {
+        SKB_CUDA(cudaMalloc(&D, (size_t)t->N * sizeof(double)));
+        SKB_CUDA(cudaMalloc(&samples, (size_t)t->S * sizeof(int32_t)));
+        SKB_CUDA(cudaMalloc(&Dbits, ((size_t)t->N / 32 + 1) * sizeof(uint32_t)));
+        fjlt_build_tables(t->seed, t->base0, (size_t)t->N, (size_t)t->S, t->order, D, samples, Dbits, g_stream);
         SKB_CUDA(cudaStreamSynchronize(g_stream));
-        fjlt_build_wht_slots(hs.data(), hs.size(), slot_sample, slot_out);
-        SKB_CUDA(cudaMalloc(&d.wht_slot_sample, slot_sample.size() * sizeof(int32_t) + 16));
-        SKB_CUDA(cudaMalloc(&d.wht_slot_out, slot_out.size() * sizeof(int32_t) + 16));
-        SKB_CUDA(cudaMemcpy(d.wht_slot_sample, slot_sample.data(), slot_sample.size() * sizeof(int32_t),
-                            cudaMemcpyHostToDevice));
-        SKB_CUDA(cudaMemcpy(d.wht_slot_out, slot_out.data(), slot_out.size() * sizeof(int32_t),
-                            cudaMemcpyHostToDevice));
-    }
+        if (t->fut == FUT_WHT) {     // gather layout of the WHT kernel, computed once from the samples
+            std::vector<int32_t> hs((size_t)t->S), slot_sample, slot_out;
+            SKB_CUDA(cudaMemcpy(hs.data(), samples, hs.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+            fjlt_build_wht_slots(hs.data(), hs.size(), slot_sample, slot_out);
+            SKB_CUDA(cudaMalloc(&ss, slot_sample.size() * sizeof(int32_t) + 16));
+            SKB_CUDA(cudaMalloc(&so, slot_out.size() * sizeof(int32_t) + 16));
+            SKB_CUDA(cudaMemcpy(ss, slot_sample.data(), slot_sample.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+            SKB_CUDA(cudaMemcpy(so, slot_out.data(), slot_out.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        }
+    } catch (...) { cudaFree(D); cudaFree(samples); cudaFree(Dbits); cudaFree(ss); cudaFree(so); throw; }
+    d.samples = samples; d.Dbits = Dbits; d.wht_slot_sample = ss; d.wht_slot_out = so; d.D = D;
 }
 
 static DenseParams dense_params(const sl_sketch_transform_t *t) {

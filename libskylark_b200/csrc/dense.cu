@@ -1742,7 +1742,9 @@ static constexpr size_t NOALLOC_PANEL_DOUBLES = (size_t)4 << 20;        // 32 Mi
 static __device__ __align__(256) double g_noalloc_panel[NOALLOC_PANEL_DOUBLES];
 
 // In host code `g_noalloc_panel` is only a handle for the runtime, not a device address;
-// the address each device gave the array is looked up once per device and kept here.
+// the address each device gave the array is looked up once per device and kept here.  Two host
+// threads making their first call on a device together both look it up and store the same
+// value, so the cache needs no lock.
 static double *g_noalloc_panel_addr[64] = {nullptr};
 
 static double *noalloc_panel_for_current_device() {
@@ -1840,6 +1842,22 @@ int sl_dense_sketch_apply_noalloc(int seed, uint64_t counter_base, int dist, dou
         const int64_t a_rows = dim == 1 ? n : m, sa_rows = dim == 1 ? s : m;
         if (lda < a_rows || ldsa < sa_rows)
             throw skb::error(skb::SKB_ERR_INVALID_PARAM, "sl_dense_sketch_apply_noalloc: leading dimension too small");
+        // The built-in array that is used is the CURRENT device's; the operands must live there
+        // too (a query, not an allocation).
+        {
+            int cur = 0;
+            SKB_CUDA(cudaGetDevice(&cur));
+            const void *ptrs[2] = {A_dev, SA_dev};
+            for (const void *q : ptrs) {
+                cudaPointerAttributes at;
+                if (cudaPointerGetAttributes(&at, q) != cudaSuccess) { cudaGetLastError(); continue; }
+                if (at.type == cudaMemoryTypeDevice && at.device != cur)
+                    throw skb::error(skb::SKB_ERR_INVALID_USAGE,
+                                     "sl_dense_sketch_apply_noalloc: A_dev / SA_dev belong to device " +
+                                     std::to_string(at.device) + " but the current device is " +
+                                     std::to_string(cur) + "; make the operands' device current first");
+            }
+        }
         skb::DenseParams p;
         p.seed = seed; p.base = counter_base; p.dist = dist; p.scale = scale;
         p.N = (size_t)n; p.S = (size_t)s;

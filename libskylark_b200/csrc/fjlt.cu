@@ -355,20 +355,30 @@ void fjlt_build_wht_slots(const int32_t *samples, size_t S, std::vector<int32_t>
     }
 }
 
-// Tiled transpose: T[k + j*N] = X[k*ldx + j]  (rows layout -> contiguous columns)
+// Tiled transpose: T[k + j*N] = X[k*ldx + j]  (rows layout -> contiguous columns).  The long
+// extent (N / 32 tiles) rides in grid.x; grid.y is capped and strides over the column tiles.
 __global__ void k_transpose_to_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
                                     double *__restrict__ T) {
     __shared__ double tile[32][33];
-    size_t j0 = (size_t)blockIdx.x * 32, k0 = (size_t)blockIdx.y * 32;
-    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
-        size_t k = k0 + r, j = j0 + threadIdx.x;
-        tile[r][threadIdx.x] = (k < N && j < m) ? X[k * ldx + j] : 0.0;
+    const size_t k0 = (size_t)blockIdx.x * 32;
+    for (size_t j0 = (size_t)blockIdx.y * 32; j0 < m; j0 += (size_t)gridDim.y * 32) {
+        for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+            size_t k = k0 + r, j = j0 + threadIdx.x;
+            tile[r][threadIdx.x] = (k < N && j < m) ? X[k * ldx + j] : 0.0;
+        }
+        __syncthreads();
+        for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+            size_t j = j0 + r, k = k0 + threadIdx.x;
+            if (k < N && j < m) T[k + j * N] = tile[threadIdx.x][r];
+        }
+        __syncthreads();
     }
-    __syncthreads();
-    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
-        size_t j = j0 + r, k = k0 + threadIdx.x;
-        if (k < N && j < m) T[k + j * N] = tile[threadIdx.x][r];
-    }
+}
+static void launch_transpose_to_cols(const double *X, size_t ldx, size_t N, size_t m, double *T,
+                                     cudaStream_t st) {
+    const size_t ty = (m + 31) / 32;
+    dim3 grid((unsigned)((N + 31) / 32), (unsigned)(ty < 65535 ? ty : 65535));
+    k_transpose_to_cols<<<grid, dim3(32, 8), 0, st>>>(X, ldx, N, m, T);
 }
 
 
@@ -867,6 +877,7 @@ static size_t dct_batch_cols(size_t N, size_t m) {
     size_t b = (mb << 20) / (N * sizeof(double));
     if (b < 1) b = 1;
     if (b > m) b = m;
+    if (b > 65535) b = 65535;      // a batch rides in grid.y
     return b;
 }
 
@@ -916,8 +927,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
             double *T = reinterpret_cast<double *>(ws);
             ws += ((N * m * sizeof(double) + 255) / 256) * 256;
             LaunchScope ls(KC_FJLT, st);
-            dim3 grid((unsigned)((m + 31) / 32), (unsigned)((N + 31) / 32));
-            k_transpose_to_cols<<<grid, dim3(32, 8), 0, st>>>(X, ldx, N, m, T);
+            launch_transpose_to_cols(X, ldx, N, m, T, st);
             SKB_CUDA(cudaGetLastError());
             Xc = T; ldc = N;
         }
@@ -1039,8 +1049,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
             double *T = reinterpret_cast<double *>(ws);
             ws += (nloc * m * sizeof(double) + 255) / 256 * 256;
             LaunchScope ls(KC_FJLT, st);
-            dim3 grid((unsigned)((m + 31) / 32), (unsigned)((nloc + 31) / 32));
-            k_transpose_to_cols<<<grid, dim3(32, 8), 0, st>>>(X, ldx, nloc, m, T);
+            launch_transpose_to_cols(X, ldx, nloc, m, T, st);
             SKB_CUDA(cudaGetLastError());
             Xc = T; ldc = nloc;
         }

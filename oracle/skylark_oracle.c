@@ -540,6 +540,14 @@ void sko_fjlt_gather(const double *TA, size_t N, size_t w, const uint64_t *sampl
             SA[i + j * ldsa] = scale * TA[samples[i] + j * N];
 }
 
+void sko_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int sko_num_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

@@ -35,7 +35,7 @@ def test_numpy_both_orders_both_dims(sk, oracle, T, shape):
 
 def test_many_panels_and_shards(sk, oracle):
     import torch
-    n, s, d = 20000, 48, 72      # panel cap 8192 rows -> 3 panels
+    n, s, d = 20000, 48, 72      # one panel (cap 32768 rows); several panels: next test
     c, oc = _ctx(sk, oracle, 5, 12345)
     S, O = sk.JLT(n, s, c), oracle.JLT(n, s, oc)
     A = torch.randn(n, d, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(1))
@@ -52,6 +52,31 @@ def test_many_panels_and_shards(sk, oracle):
     B = torch.randn(n, d, dtype=torch.float64, device="cuda")
     lhs = S.apply(A + 0.5 * B, None, 0)
     assert rel_fro(lhs.cpu().numpy(), (SA + 0.5 * S.apply(B, None, 0)).cpu().numpy()) < 1e-13
+
+
+@pytest.mark.parametrize("shape", [(70000, 48, 72), (20000, 4096, 64)])
+def test_benchmarked_multi_panel_device_path(sk, oracle, shape):
+    """The path bench.py times: device tensors, several generated panels (cap 32768 rows, or
+    256 MiB: 8192 rows at s = 4096 as in config C2), double-buffered on the forked side
+    streams, not accumulating.  Both operand layouts, twice in a row (buffers are reused)."""
+    import torch
+    n, s, d = shape
+    c, oc = _ctx(sk, oracle, 5, 999)
+    S, O = sk.JLT(n, s, c), oracle.JLT(n, s, oc)
+    A = torch.randn(n, d, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(2))
+    want = O.apply(A.cpu().numpy(), "columnwise")
+    SA = torch.empty(s, d, dtype=torch.float64, device="cuda")
+    for _ in range(2):
+        SA.fill_(float("nan"))
+        S.apply(A, SA, "columnwise")
+        assert rel_fro(SA.cpu().numpy(), want) < TOL64
+    Af = A.t().contiguous().t()                       # column-major operand
+    SAf = torch.empty(d, s, dtype=torch.float64, device="cuda").t()
+    S.apply(Af, SAf, "columnwise")
+    assert rel_fro(SAf.cpu().numpy(), want) < TOL64
+    half = (n // 2) // 16 * 16 + 8                    # shard boundary inside a panel, odd offset/8
+    parts = S.apply_shard(A[:half], None, 0, 0) + S.apply_shard(A[half:], None, 0, half)
+    assert rel_fro(parts.cpu().numpy(), want) < TOL64
 
 
 def test_tile_mode_direct_store(sk, oracle):

@@ -99,3 +99,48 @@ def test_wht_row_shards_add_up(sk, oracle):
     Sd = sk.FJLT(n, s, lib.Context(5))                                    # DCT mode cannot
     with pytest.raises(errors.LowerLayerError):
         Sd.apply_shard(A[:32768], None, 0, 0)
+
+
+@pytest.mark.parametrize("fut", ["dct", "wht"])
+def test_fjlt_at_the_baseline_length(sk, oracle, fut):
+    """Config C3's N = 2^20 and s = 8192 on a few columns: the DCT runs its 2^19-point split
+    and the Walsh-Hadamard kernel walks 128 segments per column, as in the benchmark."""
+    import torch
+    from libskylark_b200 import lib
+    n, s, d = 2 ** 20, 8192, 4
+    lib.set_option("fjlt_fut", fut)
+    try:
+        S = sk.FJLT(n, s, lib.Context(123834))
+    finally:
+        lib.set_option("fjlt_fut", "dct")
+    O = oracle.FJLT(n, s, oracle.Context(123834))
+    A = torch.randn(d, n, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(4)).t()
+    want = O.apply(A.cpu().numpy(), "columnwise", fut=fut)
+    got = S.apply(A, None, "columnwise")
+    assert rel_fro(got.cpu().numpy(), want) < TOL
+    got_r = S.apply(A.contiguous(), None, "columnwise")          # row-major operand
+    assert rel_fro(got_r.cpu().numpy(), want) < TOL
+
+
+def test_fjlt_long_and_wide_shapes(sk, oracle):
+    """Shapes whose tile counts exceed the 65535 limit of a launch grid's y extent: a rows-layout
+    operand with N = 2^21 (65536 row tiles in the transpose) and N = 1024 with 70000 columns
+    (one batch of more than 65535 columns in the small-N DCT)."""
+    import torch
+    from libskylark_b200 import lib
+    for fut in ("dct", "wht"):
+        n, s, d = 2 ** 21, 64, 2
+        lib.set_option("fjlt_fut", fut)
+        try:
+            S = sk.FJLT(n, s, lib.Context(8))
+        finally:
+            lib.set_option("fjlt_fut", "dct")
+        O = oracle.FJLT(n, s, oracle.Context(8))
+        A = torch.randn(n, d, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(6))
+        got = S.apply(A, None, "columnwise")                     # row-major n x d: the transposing path
+        assert rel_fro(got.cpu().numpy(), O.apply(A.cpu().numpy(), "columnwise", fut=fut)) < TOL
+    n, s, d = 1024, 16, 70000
+    S, O = sk.FJLT(n, s, lib.Context(9)), oracle.FJLT(n, s, oracle.Context(9))
+    A = torch.randn(d, n, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(7)).t()
+    got = S.apply(A, None, "columnwise")
+    assert rel_fro(got.cpu().numpy(), O.apply(A.cpu().numpy(), "columnwise")) < TOL

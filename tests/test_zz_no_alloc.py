@@ -52,6 +52,35 @@ def test_matches_regular_entry_point_twice_in_a_row(sk):
     assert rel_fro(got.t().cpu().numpy(), want.cpu().numpy()) < 1e-11   # Cauchy tails: cf. test_gpu_dense
 
 
+def test_panel_reuse_inside_one_call_against_the_oracle(sk, oracle):
+    """s = 4096 leaves room for 1024 input rows in the built-in array, so n = 3000 makes the call
+    regenerate the panel three times in place; odd s and padded leading dimensions take the
+    8-byte copy variants and the strided clear.  Checked against the CPU oracle as well as the
+    regular entry point, and device memory in use must not move across a call."""
+    import torch
+    from libskylark_b200 import lib
+    gen = torch.Generator("cuda").manual_seed(11)
+    for (n, s, d, pad) in ((3000, 4096, 40, 0), (2500, 1023, 33, 5)):
+        J = sk.JLT(n, s, lib.Context(99, 77))
+        O = oracle.JLT(n, s, oracle.Context(99, 77))
+        A = torch.randn(n, d, dtype=torch.float64, device="cuda", generator=gen)
+        want = J.apply(A, None, "columnwise")
+        want_cpu = O.apply(A.cpu().numpy(), "columnwise")
+        buf = torch.full((s, d + pad), float("nan"), dtype=torch.float64, device="cuda")
+        got = buf[:, :d]                      # row-major s x d with row stride d + pad
+        torch.cuda.synchronize()
+        for call in range(2):
+            free0 = torch.cuda.mem_get_info()[0]
+            assert _noalloc(lib, 99, 77, 0, math.sqrt(1.0 / s), n, s, A, got, 2) == 0
+            torch.cuda.synchronize()
+            if call == 1:                     # the first call may load kernels; the second may not move anything
+                assert torch.cuda.mem_get_info()[0] == free0
+            assert rel_fro(got.cpu().numpy(), want.cpu().numpy()) < TOL, (n, s, call)
+            assert rel_fro(got.cpu().numpy(), want_cpu) < TOL, (n, s, call)
+        if pad:
+            assert bool(torch.isnan(buf[:, d:]).all())      # the padding is left alone
+
+
 def test_size_limit_is_refused_with_a_message(sk):
     import torch
     from libskylark_b200 import lib

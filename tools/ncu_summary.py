@@ -1,5 +1,8 @@
 """Compact text summary of an .ncu-rep (run where ncu is installed; no GPU needed).
-usage: python tools/ncu_summary.py report.ncu-rep [max_kernels]"""
+usage: python tools/ncu_summary.py report.ncu-rep [max_kernels]
+       python tools/ncu_summary.py --traffic report.ncu-rep     (updates profiles/dram_traffic.json:
+           per kernel name, dram__bytes_read.sum + dram__bytes_write.sum averaged over its launches
+           in the report -- what bench.py reports as roofline.traffic)"""
 import csv
 import subprocess
 import sys
@@ -20,7 +23,41 @@ WANT = [
 ]
 
 
+def to_bytes(v, unit):
+    x = float(v.replace(",", ""))
+    return x * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}.get(unit, 1.0)
+
+
+def traffic(rep):
+    import json
+    import os
+    import re
+    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    u = dict(zip(hdr, units))
+    acc = {}
+    for r in rows[2:]:
+        d = dict(zip(hdr, r))
+        name = re.split(r"[<(]", d.get("Kernel Name", "?"))[0].split("::")[-1].strip()
+        b = to_bytes(d["dram__bytes_read.sum"], u["dram__bytes_read.sum"]) + \
+            to_bytes(d["dram__bytes_write.sum"], u["dram__bytes_write.sum"])
+        acc.setdefault(name, []).append(b)
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "dram_traffic.json")
+    try:
+        cur = json.load(open(path))
+    except Exception:
+        cur = {}
+    for k, v in acc.items():
+        cur[k] = {"dram_bytes_per_launch": sum(v) / len(v), "launches_in_capture": len(v),
+                  "source": "ncu --set full, " + os.path.basename(rep)}
+    json.dump(cur, open(path, "w"), indent=1, sort_keys=True)
+    print(json.dumps({k: cur[k] for k in acc}, indent=1))
+
+
 def main():
+    if sys.argv[1] == "--traffic":
+        return traffic(sys.argv[2])
     rep = sys.argv[1]
     maxk = int(sys.argv[2]) if len(sys.argv) > 2 else 3
     out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
