@@ -58,6 +58,7 @@ def cpu_reference_sample(n_sample, repeats=1):
         o.lib().sko_set_num_threads(_host_cores())
     except Exception:
         pass
+    o.set_libm(False)       # timed as the reference would run here: this box's libm, not the checker's
     rng = np.random.default_rng(DATA_SEED)
     A = rng.standard_normal((n_sample, D_COLS))
     ctx = o.Context(SKETCH_SEED)
@@ -220,8 +221,9 @@ def cpu_other_configs():
     import scipy.sparse
     from oracle import oracle as o
     out = {}
+    o.set_libm(False)
     rng = np.random.default_rng(DATA_SEED)
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = _host_cores()
 
     def best(fn, reps=2):
         ts = []

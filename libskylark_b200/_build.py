@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.environ.get("SKB_SO") or os.path.join(HERE, "libcskylark_b200.so")   # SKB_SO: A/B builds
 SOURCES = ["capi.cu", "hash.cu", "dense.cu", "fjlt.cu"]
-HEADERS = ["rng.cuh", "skb_internal.h", os.path.join("..", "..", "include", "skylark_b200.h")]
+HEADERS = ["rng.cuh", "cr_math.cuh", "cr_tables.cuh", "skb_internal.h", os.path.join("..", "..", "include", "skylark_b200.h")]
 
 
 def _nvcc():
@@ -36,6 +36,8 @@ def build(force=False, verbose=False):
            "-Xcompiler", "-fPIC", "-shared", "-o", SO] + [os.path.join(CSRC, s) for s in SOURCES]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
+    if os.environ.get("SKB_NVCC_FLAGS"):        # A/B builds (with SKB_SO), e.g. -DSKB_LIBM_FAST
+        cmd[1:1] = os.environ["SKB_NVCC_FLAGS"].split()
     subprocess.check_call(cmd)
     return SO
 

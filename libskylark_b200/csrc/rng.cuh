@@ -129,6 +129,12 @@ __host__ __device__ __forceinline__ double boost_rademacher(MicroUrng &u, int or
 }
 
 #ifdef __CUDACC__
+}  // namespace skb
+#include "cr_math.cuh"
+namespace skb {
+// SKB_LIBM_FAST (compile-time, for A/B timing only): the previous generators -- libdevice log / tan
+// (1-2 ulp) and the 0.6-ulp cosine below -- instead of the nearly correctly rounded cr_math.cuh.
+
 // cos(x) for x in [0, 2*pi]: Cody-Waite reduction by pi/2 in 33-bit pieces (exact products,
 // with the extra rounds when x sits next to a multiple of pi/2) and the classic degree-13/14
 // minimax kernels evaluated on the (head, tail) pair -- about 0.6 ulp, against the 1-2 ulp of
@@ -193,21 +199,38 @@ __device__ __forceinline__ double cos_0_2pi(double x) {
 }
 
 // boost::random::normal_distribution (Box-Muller, cosine branch)
+// r1, r2 = the two uniform_01 draws, in draw order
+__device__ __forceinline__ double box_muller_cos(double r1, double r2) {
+#ifdef SKB_LIBM_FAST
+    double rho = sqrt(__dmul_rn(-2.0, log(__dsub_rn(1.0, r2))));
+    return __dmul_rn(rho, cos_0_2pi(__dmul_rn(2.0 * SKB_BOOST_PI, r1)));
+#else
+    double rho = sqrt(__dmul_rn(-2.0, log_cr(__dsub_rn(1.0, r2))));     // 1 - r2 in [2^-53, 1]
+    return __dmul_rn(rho, cos_cr_0_2pi(__dmul_rn(2.0 * SKB_BOOST_PI, r1)));
+#endif
+}
 __device__ __forceinline__ double boost_normal(MicroUrng &u) {
     double r1 = boost_u01(u);
     double r2 = boost_u01(u);
-    double rho = sqrt(__dmul_rn(-2.0, log(__dsub_rn(1.0, r2))));
-    return __dmul_rn(rho, cos_0_2pi(__dmul_rn(2.0 * SKB_BOOST_PI, r1)));
+    return box_muller_cos(r1, r2);
 }
 
 // boost::random::cauchy_distribution(0,1)
 __device__ __forceinline__ double boost_cauchy(MicroUrng &u) {
+#ifdef SKB_LIBM_FAST
     return tan(__dmul_rn(SKB_BOOST_PI, __dsub_rn(boost_u01(u), 0.5)));
+#else
+    return tan_cr_halfpi(__dmul_rn(SKB_BOOST_PI, __dsub_rn(boost_u01(u), 0.5)));
+#endif
 }
 
 // boost::random::exponential_distribution(1)
 __device__ __forceinline__ double boost_exponential(MicroUrng &u) {
+#ifdef SKB_LIBM_FAST
     return -log(__dsub_rn(1.0, boost_u01(u)));
+#else
+    return -log_cr(__dsub_rn(1.0, boost_u01(u)));
+#endif
 }
 
 // Fast path for the dense generators: both draws of block 0 taken directly; the
@@ -218,10 +241,7 @@ __device__ __forceinline__ double normal_at(uint64_t key, uint64_t idx) {
         MicroUrng u(key, idx);
         return boost_normal(u);
     }
-    double r1 = u64_to_u01_rn(b.y);
-    double r2 = u64_to_u01_rn(b.x);
-    double rho = sqrt(__dmul_rn(-2.0, log(__dsub_rn(1.0, r2))));
-    return __dmul_rn(rho, cos_0_2pi(__dmul_rn(2.0 * SKB_BOOST_PI, r1)));
+    return box_muller_cos(u64_to_u01_rn(b.y), u64_to_u01_rn(b.x));
 }
 
 __device__ __forceinline__ double cauchy_at(uint64_t key, uint64_t idx) {

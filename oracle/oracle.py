@@ -41,7 +41,7 @@ def build(force=False):
             and os.path.getmtime(_SO) >= os.path.getmtime(_SRC)):
         return _SO
     cmd = ["gcc", "-O2", "-fopenmp", "-ffp-contract=off", "-fPIC", "-shared",
-           "-o", _SO, _SRC, "-lm"]
+           "-o", _SO, _SRC, "-lquadmath", "-lm"]
     subprocess.check_call(cmd)
     return _SO
 
@@ -72,6 +72,15 @@ _int = ctypes.c_int
 
 def num_threads():
     return lib().sko_num_threads()
+
+
+def set_libm(correctly_rounded):
+    """True (default): log / cos / tan / pow inside the variates are correctly rounded, like the
+    libm of the reference's era (see skylark_oracle.c); False: this box's glibc, as the timed CPU
+    baseline uses.  Returns the previous setting."""
+    prev = bool(lib().sko_get_libm())
+    lib().sko_set_libm(1 if correctly_rounded else 0)
+    return prev
 
 
 # ---------------------------------------------------------------------------

@@ -141,23 +141,69 @@ static inline double boost_rademacher(urng_t *u, int order) {
 
 #define BOOST_PI 3.14159265358979323846
 
+/* ------------------------------------------------------------------------ */
+/* The C library behind Boost's distributions.                              */
+/* Boost.Random calls std::log / std::cos / std::tan / std::pow.  The libm  */
+/* the reference was built against at its pinned versions (glibc <= 2.27:   */
+/* the IBM Accurate Mathematical Library) rounds these functions correctly; */
+/* the glibc on this box (2.39) is within 0.52 ulp but not correctly        */
+/* rounded.  Mode 1 (default) therefore evaluates them in extended          */
+/* precision and rounds once: x87 long double first and, when that result   */
+/* sits too close to a rounding boundary to decide, __float128.  Mode 0     */
+/* calls this box's libm directly (what the reference would cost here: the  */
+/* timed CPU baseline uses it).                                             */
+/* ------------------------------------------------------------------------ */
+#include <quadmath.h>
+static int g_libm_cr = 1;
+void sko_set_libm(int correctly_rounded) { g_libm_cr = correctly_rounded ? 1 : 0; }
+int sko_get_libm(void) { return g_libm_cr; }
+
+static inline int ld_ambiguous(long double v) {
+    union { long double ld; struct { uint64_t m; uint16_t se; } p; } u;
+    u.ld = v;
+    int low = (int)(u.p.m & 0x7FF);            /* the 11 bits below a double's last place */
+    int dist = low - 0x400;
+    if (dist < 0) dist = -dist;
+    return dist <= 16;                         /* libm's long double routines: a few ulp_ld */
+}
+static inline double m_log(double x) {
+    if (!g_libm_cr) return log(x);
+    long double v = logl((long double)x);
+    return ld_ambiguous(v) ? (double)logq((__float128)x) : (double)v;
+}
+static inline double m_cos(double x) {
+    if (!g_libm_cr) return cos(x);
+    long double v = cosl((long double)x);
+    return ld_ambiguous(v) ? (double)cosq((__float128)x) : (double)v;
+}
+static inline double m_tan(double x) {
+    if (!g_libm_cr) return tan(x);
+    long double v = tanl((long double)x);
+    return ld_ambiguous(v) ? (double)tanq((__float128)x) : (double)v;
+}
+static inline double m_pow(double x, double y) {
+    if (!g_libm_cr) return pow(x, y);
+    long double v = powl((long double)x, (long double)y);
+    return ld_ambiguous(v) ? (double)powq((__float128)x, (__float128)y) : (double)v;
+}
+
 /* boost::random::normal_distribution<double> (<= 1.63): Box-Muller, always the
  * cosine branch because randgen.hpp:113 clones a reset distribution. */
 static inline double boost_normal(urng_t *u) {
     double r1 = boost_u01(u);
     double r2 = boost_u01(u);
-    double rho = sqrt(-2.0 * log(1.0 - r2));
-    return rho * cos(2.0 * BOOST_PI * r1);
+    double rho = sqrt(-2.0 * m_log(1.0 - r2));
+    return rho * m_cos(2.0 * BOOST_PI * r1);
 }
 
 /* boost::random::cauchy_distribution<double>(0,1) */
 static inline double boost_cauchy(urng_t *u) {
-    return tan(BOOST_PI * (boost_u01(u) - 0.5));
+    return m_tan(BOOST_PI * (boost_u01(u) - 0.5));
 }
 
 /* boost::random::exponential_distribution<double>(1) (<= 1.63) */
 static inline double boost_exponential(urng_t *u) {
-    return -1.0 * log(1.0 - boost_u01(u));
+    return -1.0 * m_log(1.0 - boost_u01(u));
 }
 
 /* boost::random::uniform_real_distribution<double>(a,b) */
@@ -258,7 +304,7 @@ void sko_wzt_values(int seed, uint64_t val_base, uint64_t pm_base, size_t count,
         double e = boost_exponential(&u);
         urng_init(&u, seed, pm_base + i);
         double pm = boost_rademacher(&u, order);
-        out[i] = pm * pow(1.0 / e, 1.0 / p);
+        out[i] = pm * m_pow(1.0 / e, 1.0 / p);
     }
 }
 

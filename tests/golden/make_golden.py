@@ -21,7 +21,10 @@ def hexs(a):
 
 
 def main():
-    g = {"note": "derived from oracle/skylark_oracle.c; parity unpinned (no reference vectors exist)"}
+    g = {"note": "derived from oracle/skylark_oracle.c; parity unpinned (no reference vectors exist)",
+         "libm": "log / cos / tan / pow inside the variates correctly rounded (oracle libm mode 1: the "
+                 "behaviour of the reference era's glibc <= 2.27), not this box's glibc"}
+    o.set_libm(True)
     g["threefry2x64_20_published"] = [
         {"ctr": ["0" * 16, "0" * 16], "key": ["0" * 16, "0" * 16],
          "out": ["c2b6e3a8c2c69865", "6f81ed42f350084d"]},

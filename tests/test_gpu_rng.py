@@ -59,9 +59,9 @@ def test_golden_transform_sequence(sk):
         assert t.row_value().tolist() == g["cwt_row_value"]
         assert m.row_idx().tolist() == g["mmt_row_idx"]
         assert ulp_diff(m.row_value(), [float.fromhex(x) for x in g["mmt_row_value"]]).max() <= 2
-        assert ulp_diff(w.row_value(), [float.fromhex(x) for x in g["wzt_row_value"]]).max() <= 4
+        assert ulp_diff(w.row_value(), [float.fromhex(x) for x in g["wzt_row_value"]]).max() <= 2
         got = j.export_dense().ravel(order="F")
-        assert ulp_diff(got, [float.fromhex(x) for x in g["jlt_S"]]).max() <= 4
+        assert ulp_diff(got, [float.fromhex(x) for x in g["jlt_S"]]).max() <= 2
         assert r.shifts().tolist() == [float.fromhex(x) for x in g["rft_shifts"]]
         assert f.diagonal().tolist() == g["fjlt_D"]
         assert f.samples().tolist() == g["fjlt_samples"]
@@ -79,7 +79,7 @@ def test_mmt_wzt_values(sk, oracle):
         ow = oracle.WZT(n, s, p, oracle.Context(6))
         assert np.array_equal(w.row_idx(), ow.row_idx.astype(np.int64))
         assert np.array_equal(np.sign(w.row_value()), np.sign(ow.row_value))
-        assert ulp_diff(w.row_value(), ow.row_value).max() <= 4   # log, divide and pow chained
+        assert ulp_diff(w.row_value(), ow.row_value).max() <= 2   # the exponential is exact now; pow is CUDA's (<= 2 ulp)
 
 
 def test_dense_entries_within_2ulp(sk, oracle):
@@ -88,22 +88,29 @@ def test_dense_entries_within_2ulp(sk, oracle):
     j = sk.JLT(n, s, lib.Context(123834, 17))
     oj = oracle.JLT(n, s, oracle.Context(123834, 17))
     d = ulp_diff(j.export_dense(), oj.realize())
-    # Target (BASELINE.json): 2 ulp.  Measured on B200 over 2e6 Gaussians with the in-house
-    # 0.6-ulp cosine (rng.cuh: cos_0_2pi): 97.5 % bit-identical to the glibc-based oracle,
-    # 99.987 % within 2 ulp, 0.013 % at 3 ulp, one sample at 5.  The rest comes from log():
-    # libdevice's (1 ulp) and glibc's (0.52 ulp) are both faithful, neither correctly rounded.
-    assert (d <= 2).mean() >= 0.9995 and d.max() <= 6, (float((d <= 2).mean()), int(d.max()))
+    # Bar (BASELINE.json north_star): Gaussian / Cauchy variates within 2 ulp.  The oracle rounds
+    # log / cos / tan correctly, as the libm of the reference's era did (skylark_oracle.c, libm
+    # mode 1); the device functions (cr_math.cuh) are correctly rounded except within ~2^-14 ulp
+    # of a rounding boundary, so nearly every entry is bit-identical and none is further than 2.
+    assert d.max() <= 2 and (d == 0).mean() >= 0.9995, (float((d == 0).mean()), int(d.max()))
+    # the same against this box's glibc (0.52-ulp log / cos, not correctly rounded): still <= 3
+    prev = oracle.set_libm(False)
+    try:
+        dn = ulp_diff(j.export_dense(), oracle.JLT(n, s, oracle.Context(123834, 17)).realize())
+    finally:
+        oracle.set_libm(prev)
+    assert dn.max() <= 3 and (dn <= 2).mean() >= 0.99999, (float((dn <= 2).mean()), int(dn.max()))
     # sub-block addressing S[i0:i0+h, j0:j0+w]
     assert np.array_equal(j.export_dense(7, 11, 20, 30), j.export_dense()[7:27, 11:41])
     c = sk.CT(n, s, 2.0, lib.Context(9))
     oc = oracle.CT(n, s, 2.0, oracle.Context(9))
     d = ulp_diff(c.export_dense(), oc.realize())
-    assert (d <= 2).mean() >= 0.9999 and d.max() <= 4, (float((d <= 2).mean()), int(d.max()))
+    assert d.max() <= 2 and (d == 0).mean() >= 0.9995, (float((d == 0).mean()), int(d.max()))
     r = sk.GaussianRFT(64, 128, 3.0, lib.Context(4))
     orr = oracle.GaussianRFT(64, 128, 3.0, oracle.Context(4))
     assert np.array_equal(r.shifts(), orr.shifts)
     assert np.array_equal(r.scales(), orr.scales)
-    assert ulp_diff(r.export_dense(), orr.realize()).max() <= 6
+    assert ulp_diff(r.export_dense(), orr.realize()).max() <= 2
 
 
 def test_fjlt_tables_and_overlap(sk, oracle):
