@@ -367,13 +367,18 @@ def other_configs(torch, lib, sketch, hbm_gbs, fp64_peak):
 
 def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
     """BASELINE.json configs 3-5 on `world` GPUs (all ranks run this in lockstep; device time via
-    CUDA events, max over ranks).  C3: strong scaling of the fixed 2^20 x 2048 problem, row
-    shards + all-reduce of the 134 MB sketch.  C4: 1.25e6 rows per rank of a (1.25e6*world) x 1e5
-    CSC matrix + reduce-scatter of the 16 GB dense partial.  C5: 5e5 points per rank, no
-    collective."""
-    from libskylark_b200.dist import reduce_partial
+    CUDA events, max over ranks).  C3: strong scaling of the fixed 2^20 x 2048 problem -- Walsh-
+    Hadamard mode on row shards with the reduction overlapped block by block, DCT mode (what the
+    reference computes) through the reference's rows -> columns all-to-all and on column shards.
+    C4: 1.25e6 rows per rank of a (1.25e6*world) x 1e5 CSC matrix + reduce-scatter of the 16 GB
+    dense partial, or a sparse exchange, or column shards.  C5: 5e5 points per rank, no collective.
+    Every exchanged result is checked OUTSIDE the timed region against a single-GPU recompute of a
+    column slice on rank 0 ("distributed == local", tests/unit/DenseSketchApplyElementalTest.cpp:28-106);
+    the relative Frobenius error is printed as `check_rel_fro` and must be < 1e-12."""
+    from libskylark_b200 import dist as sd
     dev = "cuda"
     out = {}
+    TOL = 1e-12
 
     def timed(fn, reps):
         fn()
@@ -389,28 +394,115 @@ def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
             dist.barrier()
         return statistics.median(ts)
 
-    # ---- C3 (Walsh-Hadamard mode; the DCT does not split over row shards)
+    def rank0_time(fn, reps):
+        """single-GPU time of the whole problem on rank 0 (the others wait): the T1 of a speed-up"""
+        ms = 0.0
+        if rank == 0:
+            fn(); torch.cuda.synchronize()
+            ts = []
+            for _ in range(reps):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+                ts.append(e0.elapsed_time(e1))
+            ms = statistics.median(ts)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.broadcast(t, 0)
+        return float(t.item())
+
+    def bcast_check(v):
+        t = torch.tensor([v if v is not None else -1.0], dtype=torch.float64, device=dev)
+        dist.broadcast(t, 0)
+        v = float(t.item())
+        if not (0 <= v < TOL):
+            raise RuntimeError("multi-GPU result differs from the single-GPU recompute: %g" % v)
+        return v
+
+    def rel(a, b):
+        return float((a - b).norm() / b.norm())
+
+    def guarded(name, fn):
+        try:
+            out[name] = fn()
+        except Exception as e:      # keep the bench line if one leg fails
+            out[name] = {"error": repr(e)[:300]}
+        torch.cuda.empty_cache()
+        dist.barrier()
+
+    # ---- C3: fixed 2^20 x 2048 problem, every rank generates the SAME matrix and keeps its rows
     n, d, s = 2 ** 20, 2048, 8192
-    if n % (8192 * world) == 0:
+    CHK = 8                                             # columns recomputed on one GPU
+    nloc = n // world
+
+    def c3_data():
+        g = torch.Generator(device=dev).manual_seed(DATA_SEED + 3)
+        full = torch.randn(d, n, dtype=torch.float64, device=dev, generator=g)     # column-major n x d
+        shard = full[:, rank * nloc:(rank + 1) * nloc].contiguous().t()             # rows of this rank
+        chk = full[:CHK].contiguous().t()                                           # n x CHK, all rows
+        return full, shard, chk
+
+    def c3_wht():
+        if n % (8192 * world):
+            return {"skipped": "needs 8192-aligned row shards"}
         lib.set_option("fjlt_fut", "wht")
         try:
             S = sketch.FJLT(n, s, lib.Context(SKETCH_SEED))
         finally:
             lib.set_option("fjlt_fut", "dct")
-        nloc = n // world
-        A = torch.randn(d, nloc, dtype=torch.float64, device=dev).t()       # column-major shard
-        SA = torch.empty(d, s, dtype=torch.float64, device=dev).t()
-
-        def c3():
-            S.apply_shard(A, SA, "columnwise", rank * nloc)
-            reduce_partial(SA, None, "allreduce")
-        ms = timed(c3, 3)
-        gbs = (n * d * 8 + s * d * 8) / (ms * 1e-3) / 1e9
-        out["c3_fjlt_wht"] = {"workload": "C3: FJLT(wht) fp64 2^20x2048 -> 8192 row-sharded over %d GPUs, "
-                              "all-reduce of the 134 MB sketch (strong scaling)" % world,
-                              "ms": ms, "value": gbs, "unit": "GB/s", "scaling": "strong"}
-        del A, SA, S
+        full, A, chk = c3_data()
+        t1 = rank0_time(lambda: S.apply(full.t(), None, "columnwise"), 3)
+        del full
         torch.cuda.empty_cache()
+        SA = torch.empty(d, s, dtype=torch.float64, device=dev).t()
+        res = {}
+        for key, red in (("allreduce", "allreduce"), ("reduce_scatter", "reduce_scatter")):
+            ms = timed(lambda: sd.apply_distributed_overlapped(S, A, SA, "columnwise", rank * nloc,
+                                                               reduce=red, blocks=4), 5)
+            got = sd.apply_distributed_overlapped(S, A, SA, "columnwise", rank * nloc, reduce=red, blocks=4)
+            err = None
+            if rank == 0:       # allreduce: SA whole; reduce_scatter: rank 0 owns the first d/(4*world) columns of block 0
+                want = S.apply(chk, None, "columnwise")
+                err = rel(got[:, :CHK], want)
+            res[key] = {"ms": ms, "check_rel_fro": bcast_check(err)}
+        ms_plain = timed(lambda: sd.apply_distributed(S, A, SA, "columnwise", rank * nloc, reduce="allreduce"), 3)
+        best = min(res["allreduce"]["ms"], res["reduce_scatter"]["ms"])
+        return {"workload": "C3: FJLT(wht) fp64 2^20x2048 -> 8192 row-sharded over %d GPUs (strong scaling); "
+                            "kernel of column block b+1 overlapped with the NCCL reduction of block b" % world,
+                "ms": res["allreduce"]["ms"], "ms_reduce_scatter": res["reduce_scatter"]["ms"],
+                "ms_unoverlapped_allreduce": ms_plain, "ms_one_gpu_same_run": t1,
+                "speedup_vs_one_gpu": t1 / res["allreduce"]["ms"],
+                "speedup_vs_one_gpu_reduce_scatter": t1 / res["reduce_scatter"]["ms"],
+                "scaling_efficiency": t1 / res["allreduce"]["ms"] / world,
+                "check_rel_fro": max(res["allreduce"]["check_rel_fro"], res["reduce_scatter"]["check_rel_fro"]),
+                "value": (n * d * 8 + s * d * 8) / (best * 1e-3) / 1e9, "unit": "GB/s", "scaling": "strong"}
+
+    def c3_dct():
+        S = sketch.FJLT(n, s, lib.Context(SKETCH_SEED))
+        full, A, chk = c3_data()
+        t1 = rank0_time(lambda: S.apply(full.t(), None, "columnwise"), 3)
+        dloc = d // world
+        Acols = full[rank * dloc:(rank + 1) * dloc].contiguous().t()                # n x d/world, all rows
+        del full
+        torch.cuda.empty_cache()
+        # (i) the reference's route: rows -> columns all-to-all, local transform, all-gather
+        ms_a2a = timed(lambda: sd.fjlt_apply_row_sharded(S, A, gather=True), 3)
+        got = sd.fjlt_apply_row_sharded(S, A, gather=True)
+        err = rel(got[:, :CHK], S.apply(chk, None, "columnwise")) if rank == 0 else None
+        e1 = bcast_check(err)
+        # (ii) the data already column-sharded: no exchange before the transform; all-gather after
+        ms_col = timed(lambda: sd.gather_columns(S.apply(Acols, None, "columnwise"), d), 3)
+        got = sd.gather_columns(S.apply(Acols, None, "columnwise"), d)
+        err = rel(got[:, :CHK], S.apply(chk, None, "columnwise")) if rank == 0 else None
+        e2 = bcast_check(err)
+        return {"workload": "C3: FJLT(dct, the reference's transform) fp64 2^20x2048 -> 8192 over %d GPUs (strong "
+                            "scaling): row shards re-sharded to columns by all-to-all (FJLT_Elemental.hpp:149-150), "
+                            "local DCT, all-gather; and the same from column shards" % world,
+                "ms": ms_a2a, "ms_column_sharded": ms_col, "ms_one_gpu_same_run": t1,
+                "speedup_vs_one_gpu": t1 / ms_a2a, "speedup_vs_one_gpu_column_sharded": t1 / ms_col,
+                "check_rel_fro": max(e1, e2),
+                "value": (n * d * 8 + s * d * 8) / (ms_a2a * 1e-3) / 1e9, "unit": "GB/s", "scaling": "strong"}
+
+    guarded("c3_fjlt_wht", c3_wht)
+    guarded("c3_fjlt_dct", c3_dct)
 
     # ---- C4
     n_loc, d, s, nnz_col = 1_250_000, 100_000, 20_000, 1250
@@ -421,48 +513,82 @@ def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
         values = torch.randn(d * nnz_col, dtype=torch.float64, device=dev, generator=g)
         A = lib.DeviceCSC(indptr, indices, values, (n_loc, d))
         S = sketch.CWT(n_loc * world, s, lib.Context(SKETCH_SEED))
-        SA = torch.empty(d, s, dtype=torch.float64, device=dev).t()          # column-major s x d
-        kernel_ms = []
 
-        def c4():
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            S.apply_shard(A, SA, "columnwise", rank * n_loc)
-            e1.record()
-            res = reduce_partial(SA, None, "reduce_scatter")     # each rank keeps d/world columns
-            torch.cuda.synchronize()
-            kernel_ms.append(e0.elapsed_time(e1))
-            return res
-        ms = timed(c4, 2)
-        nbytes = world * (d * nnz_col * 12 + (d + 1) * 4 + s * d * 8)
-        out["c4_cwt_csc"] = {"workload": "C4: CWT CSC %dx100000, %.2e nnz -> 20000 row-sharded over %d GPUs, "
-                             "reduce-scatter of the 16 GB partials" % (n_loc * world, 1.25e8 * world, world),
-                             "ms": ms, "kernel_ms_rank0": statistics.median(kernel_ms),
-                             "value": nbytes / (ms * 1e-3) / 1e9, "unit": "GB/s (all GPUs, kernel bytes / "
-                             "end-to-end time incl. collective)", "scaling": "weak"}
-        del SA
-        torch.cuda.empty_cache()
-        # the same sketch with sparse partials: column-block all-to-all of ~1.5 GB per GPU instead of
-        # the 16 GB dense reduce-scatter; every rank ends with its d/world columns as CSC
-        from libskylark_b200.dist import apply_distributed_sparse
-        try:
-            def c4s():
-                res = apply_distributed_sparse(S, A, rank * n_loc, None)
+        def c4_slice_reference():
+            """columns [0, CHK) of the whole matrix gathered on every rank (global row ids), sketched
+            by ONE GPU: what rank 0 compares its share of the exchanged result with"""
+            k = CHK * nnz_col
+            idx = [torch.empty(k, dtype=torch.int32, device=dev) for _ in range(world)]
+            val = [torch.empty(k, dtype=torch.float64, device=dev) for _ in range(world)]
+            dist.all_gather(idx, indices[:k].contiguous())
+            dist.all_gather(val, values[:k].contiguous())
+            if rank != 0:
+                return None
+            cols = []
+            for c in range(CHK):
+                cols.append((torch.cat([idx[r][c * nnz_col:(c + 1) * nnz_col] + r * n_loc for r in range(world)]),
+                             torch.cat([val[r][c * nnz_col:(c + 1) * nnz_col] for r in range(world)])))
+            ip = (torch.arange(CHK + 1, device=dev, dtype=torch.int64) * nnz_col * world).to(torch.int32)
+            Ac = lib.DeviceCSC(ip, torch.cat([c[0] for c in cols]), torch.cat([c[1] for c in cols]),
+                               (n_loc * world, CHK))
+            SAc = torch.empty(CHK, s, dtype=torch.float64, device=dev).t()
+            S.apply(Ac, SAc, "columnwise")
+            return SAc
+
+        def c4_dense():
+            SA = torch.empty(d, s, dtype=torch.float64, device=dev).t()          # column-major s x d
+            kernel_ms = []
+
+            def step():
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                S.apply_shard(A, SA, "columnwise", rank * n_loc)
+                e1.record()
+                res = sd.reduce_partial(SA, None, "reduce_scatter")     # each rank keeps d/world columns
+                torch.cuda.synchronize()
+                kernel_ms.append(e0.elapsed_time(e1))
+                return res
+            ms = timed(step, 2)
+            got = step()
+            want = c4_slice_reference()
+            err = rel(got[:, :CHK], want) if rank == 0 else None
+            nbytes = world * (d * nnz_col * 12 + (d + 1) * 4 + s * d * 8)
+            return {"workload": "C4: CWT CSC %dx100000, %.2e nnz -> 20000 row-sharded over %d GPUs, "
+                                "reduce-scatter of the 16 GB partials" % (n_loc * world, 1.25e8 * world, world),
+                    "ms": ms, "kernel_ms_rank0": statistics.median(kernel_ms), "check_rel_fro": bcast_check(err),
+                    "value": nbytes / (ms * 1e-3) / 1e9, "unit": "GB/s (all GPUs, kernel bytes / "
+                    "end-to-end time incl. collective)", "scaling": "weak"}
+
+        def c4_sparse():
+            def step():
+                res = sd.apply_distributed_sparse(S, A, rank * n_loc, None)
                 torch.cuda.synchronize()
                 return res
-            ms = timed(c4s, 2)
-            out["c4_cwt_csc_sparse_exchange"] = {
-                "workload": "C4: same matrix, sparse partial sketches (CSC -> CSC), column-block all-to-all, "
-                            "merge on the device; result = d/world columns per GPU as CSC",
-                "ms": ms, "value": world * (d * nnz_col * 12 + (d + 1) * 4) / (ms * 1e-3) / 1e9,
-                "unit": "GB/s (all GPUs, input bytes / end-to-end time incl. exchange and merge)", "scaling": "weak"}
-        except Exception as e:      # keep the bench line if this optional leg fails
-            out["c4_cwt_csc_sparse_exchange"] = {"error": repr(e)[:300]}
+            ms = timed(step, 2)
+            res, (c0, nc) = step()
+            want = c4_slice_reference()
+            err = None
+            if rank == 0:
+                ip = res.indptr[:CHK + 1].to(torch.int64)
+                dense = torch.zeros(CHK, s, dtype=torch.float64, device=dev)
+                colid = torch.repeat_interleave(torch.arange(CHK, device=dev), ip[1:] - ip[:-1])
+                e = int(ip[-1])
+                dense[colid, res.indices[:e].to(torch.int64)] = res.values[:e]
+                err = rel(dense.t(), want)
+            return {"workload": "C4: same matrix, sparse partial sketches (CSC -> CSC), column-block all-to-all, "
+                                "merge on the device; result = d/world columns per GPU as CSC",
+                    "ms": ms, "check_rel_fro": bcast_check(err),
+                    "value": world * (d * nnz_col * 12 + (d + 1) * 4) / (ms * 1e-3) / 1e9,
+                    "unit": "GB/s (all GPUs, input bytes / end-to-end time incl. exchange and merge)", "scaling": "weak"}
+
+        guarded("c4_cwt_csc", c4_dense)
+        guarded("c4_cwt_csc_sparse_exchange", c4_sparse)
         del A, S, indptr, indices, values
         torch.cuda.empty_cache()
-        # the partition that needs no exchange at all: shard the COLUMNS of A (every GPU holds all
-        # 1e7 rows of d/world columns, the same 1.25e8 nnz) -> each GPU owns its columns of SA outright
-        try:
+
+        def c4_columns():
+            # the partition that needs no exchange at all: shard the COLUMNS of A (every GPU holds all
+            # 1e7 rows of d/world columns, the same 1.25e8 nnz) -> each GPU owns its columns of SA outright
             dc, nnz_c = d // world, nnz_col * world
             n_all = n_loc * world
             g = torch.Generator(device=dev).manual_seed(DATA_SEED + 100 + rank)
@@ -473,27 +599,30 @@ def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
             S = sketch.CWT(n_all, s, lib.Context(SKETCH_SEED))
             SA = torch.empty(dc, s, dtype=torch.float64, device=dev).t()
             ms = timed(lambda: S.apply(A, SA, "columnwise"), 3)
-            out["c4_cwt_csc_column_sharded"] = {
-                "workload": "C4: same 1e7 x 1e5 matrix, COLUMNS sharded over %d GPUs (all rows of %d columns each): "
-                            "no collective, each GPU owns its %d columns of SA (dense)" % (world, dc, dc),
-                "ms": ms, "value": world * (dc * nnz_c * 12 + (dc + 1) * 4 + s * dc * 8) / (ms * 1e-3) / 1e9,
-                "unit": "GB/s (all GPUs)", "scaling": "strong"}
-            del A, S, SA, indptr, indices, values
-        except Exception as e:
-            out["c4_cwt_csc_column_sharded"] = {"error": repr(e)[:300]}
-        torch.cuda.empty_cache()
+            return {"workload": "C4: same 1e7 x 1e5 matrix, COLUMNS sharded over %d GPUs (all rows of %d columns each): "
+                                "no collective, each GPU owns its %d columns of SA (dense)" % (world, dc, dc),
+                    "ms": ms, "value": world * (dc * nnz_c * 12 + (dc + 1) * 4 + s * dc * 8) / (ms * 1e-3) / 1e9,
+                    "unit": "GB/s (all GPUs)", "scaling": "strong"}
+        guarded("c4_cwt_csc_column_sharded", c4_columns)
 
     # ---- C5
-    m, n, s = 500_000, 784, 16384
-    S = sketch.GaussianRFT(n, s, 10.0, context=lib.Context(SKETCH_SEED))
-    A = torch.rand(m, n, dtype=torch.float32, device=dev)
-    SA = torch.empty(m, s, dtype=torch.float32, device=dev)
-    ms = timed(lambda: S.apply(A, SA, "rowwise"), 2)
-    out["c5_rft"] = {"workload": "C5: GaussianRFT fp32 %dx784 -> 16384 rowwise, %d points per GPU, no collective"
-                     % (m * world, m), "ms": ms, "value": 2.0 * m * world * n * s / (ms * 1e-3) / 1e12,
-                     "unit": "TFLOP/s", "scaling": "weak"}
-    del A, SA, S
-    torch.cuda.empty_cache()
+    def c5():
+        m, n, s = 500_000, 784, 16384
+        S = sketch.GaussianRFT(n, s, 10.0, context=lib.Context(SKETCH_SEED))
+        A = torch.rand(m, n, dtype=torch.float32, device=dev)
+        SA = torch.empty(m, s, dtype=torch.float32, device=dev)
+        ms = timed(lambda: S.apply(A, SA, "rowwise"), 2)
+        # no exchange to check; the rows of every rank against the FP64 path of the same transform
+        want = S.apply(A[:256].double(), None, "rowwise")
+        err = rel(SA[:256].double(), want)
+        t = torch.tensor([err], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if not float(t.item()) < 1e-5:
+            raise RuntimeError("C5 fp32 features differ from the fp64 path: %g" % float(t.item()))
+        return {"workload": "C5: GaussianRFT fp32 %dx784 -> 16384 rowwise, %d points per GPU, no collective"
+                            % (m * world, m), "ms": ms, "check_rel_fro_vs_fp64_path": float(t.item()),
+                "value": 2.0 * m * world * n * s / (ms * 1e-3) / 1e12, "unit": "TFLOP/s", "scaling": "weak"}
+    guarded("c5_rft", c5)
     return out
 
 
@@ -606,7 +735,24 @@ def run_ours(args):
     L.sl_host_free_pinned(hSA)
 
     multi = None
+    main_check = None
     if world > 1:
+        # "distributed == local": columns [0, 8) of the all-reduced sketch against ONE GPU sketching
+        # the same columns of the whole (world * 1e6)-row matrix (outside the timed region)
+        step()
+        sl = A[:, :8].contiguous()
+        allsl = torch.empty(world * N_ROWS, 8, dtype=torch.float64, device="cuda")
+        dist.all_gather_into_tensor(allsl, sl)
+        err = -1.0
+        if rank == 0:
+            want = S.apply(allsl, None, "columnwise")
+            err = float((SA[:, :8] - want).norm() / want.norm())
+        t = torch.tensor([err], dtype=torch.float64, device="cuda")
+        dist.broadcast(t, 0)
+        main_check = float(t.item())
+        if not (0 <= main_check < 1e-12):
+            raise SystemExit("bench.py: the all-reduced sketch differs from the single-GPU recompute: %g" % main_check)
+        del allsl, sl
         del A, SA
         torch.cuda.empty_cache()
         try:
@@ -659,6 +805,8 @@ def run_ours(args):
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
                     "path": "sl_apply_sketch_transform_shard on pinned HOST buffers (C ABI)"},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline}
+    if main_check is not None:
+        line["check_rel_fro_vs_one_gpu"] = main_check
     if cpu is not None:
         line["cpu_baseline"] = {"value": cpu["tflops"], "unit": UNIT, "cores": cpu["cores"],
                                 "kind": "port", "sample": cpu["sample"], "seconds": cpu["seconds"]}

@@ -152,6 +152,7 @@ struct DevState {
     double *shifts = nullptr, *scales = nullptr;
     double *D = nullptr; int32_t *samples = nullptr; uint32_t *Dbits = nullptr;
     int32_t *wht_slot_sample = nullptr, *wht_slot_out = nullptr;
+    void *dct_plan = nullptr;
     void *ws = nullptr; size_t ws_bytes = 0;
 };
 
@@ -172,7 +173,7 @@ struct sl_sketch_transform_t {
             DevState &d = kv.second;
             cudaFree(d.bucket); cudaFree(d.value); cudaFree(d.shifts); cudaFree(d.scales);
             cudaFree(d.D); cudaFree(d.samples); cudaFree(d.Dbits); cudaFree(d.wht_slot_sample);
-            cudaFree(d.wht_slot_out); cudaFree(d.ws);
+            cudaFree(d.wht_slot_out); cudaFree(d.dct_plan); cudaFree(d.ws);
             for (auto &p : d.plans) hash_free_plan(&p.second);
             if (prev >= 0) cudaSetDevice(prev);
         }
@@ -265,11 +266,19 @@ static void ensure_rft_tables(sl_sketch_transform_t *t, DevState &d) {
 static void ensure_fjlt_tables(sl_sketch_transform_t *t, DevState &d) {
     if (d.D) return;
     double *D = nullptr; int32_t *samples = nullptr, *ss = nullptr, *so = nullptr; uint32_t *Dbits = nullptr;
+    void *plan = nullptr;
     try {
         SKB_CUDA(cudaMalloc(&D, (size_t)t->N * sizeof(double)));
         SKB_CUDA(cudaMalloc(&samples, (size_t)t->S * sizeof(int32_t)));
         SKB_CUDA(cudaMalloc(&Dbits, ((size_t)t->N / 32 + 1) * sizeof(uint32_t)));
         fjlt_build_tables(t->seed, t->base0, (size_t)t->N, (size_t)t->S, t->order, D, samples, Dbits, g_stream);
+        if (t->fut == FUT_DCT) {
+            const size_t pb = fjlt_dct_plan_bytes((size_t)t->N, (size_t)t->S);
+            if (pb) {
+                SKB_CUDA(cudaMalloc(&plan, pb));
+                fjlt_dct_plan_build((size_t)t->N, (size_t)t->S, samples, plan, g_stream);
+            }
+        }
         SKB_CUDA(cudaStreamSynchronize(g_stream));
         if (t->fut == FUT_WHT) {     // gather layout of the WHT kernel, computed once from the samples
             std::vector<int32_t> hs((size_t)t->S), slot_sample, slot_out;
@@ -280,8 +289,8 @@ static void ensure_fjlt_tables(sl_sketch_transform_t *t, DevState &d) {
             SKB_CUDA(cudaMemcpy(ss, slot_sample.data(), slot_sample.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
             SKB_CUDA(cudaMemcpy(so, slot_out.data(), slot_out.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
         }
-    } catch (...) { cudaFree(D); cudaFree(samples); cudaFree(Dbits); cudaFree(ss); cudaFree(so); throw; }
-    d.samples = samples; d.Dbits = Dbits; d.wht_slot_sample = ss; d.wht_slot_out = so; d.D = D;
+    } catch (...) { cudaFree(D); cudaFree(samples); cudaFree(Dbits); cudaFree(ss); cudaFree(so); cudaFree(plan); throw; }
+    d.samples = samples; d.Dbits = Dbits; d.wht_slot_sample = ss; d.wht_slot_out = so; d.dct_plan = plan; d.D = D;
 }
 
 static DenseParams dense_params(const sl_sketch_transform_t *t) {
@@ -465,7 +474,7 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
     fjlt_apply(t->fut, layout_rows, (const double *)A->data, (size_t)A->ld, (size_t)t->N,
                (size_t)other, d.D, d.Dbits, d.samples, (size_t)t->S, d.wht_slot_sample, d.wht_slot_out,
                (double *)SA->data, (size_t)SA->ld,
-               d.ws, d.ws_bytes, st, (size_t)offset, (size_t)sk);
+               d.ws, d.ws_bytes, st, (size_t)offset, (size_t)sk, d.dct_plan);
 }
 
 // Hands a freshly computed device CSC to the wrapper SA: kept on the device for device wrappers,
@@ -944,6 +953,12 @@ int sl_set_option(const char *key, const char *value) {
         if (strcmp(value, "dct") == 0) g_fjlt_fut = FUT_DCT;
         else if (strcmp(value, "wht") == 0) g_fjlt_fut = FUT_WHT;
         else throw error(SKB_ERR_INVALID_PARAM, "fjlt_fut must be dct or wht");
+    } else if (strcmp(key, "sm_reserve") == 0) {
+        // SMs the persistent FJLT kernels leave free (so that a collective running beside them,
+        // dist.apply_distributed_overlapped, finds room for its CTAs); 0 = use the whole GPU
+        const int v = atoi(value);
+        if (v < 0 || v > 100) throw error(SKB_ERR_INVALID_PARAM, "sm_reserve must be in [0, 100]");
+        fjlt_set_sm_reserve(v);
     } else throw error(SKB_ERR_INVALID_PARAM, std::string("unknown option ") + key);
     SL_CATCH
 }

@@ -19,6 +19,10 @@
 
 namespace skb {
 
+static int g_sm_reserve = 0;
+void fjlt_set_sm_reserve(int sms) { g_sm_reserve = sms; }
+static unsigned fjlt_sms() { return (unsigned)(148 - (g_sm_reserve < 140 ? g_sm_reserve : 140)); }
+
 __global__ void k_fjlt_tables(uint64_t key, uint64_t base, size_t N, size_t S, int order,
                               double *__restrict__ D, int32_t *__restrict__ samples,
                               uint32_t *__restrict__ Dbits) {
@@ -608,20 +612,14 @@ k_dct_pass2(DctPlan pl, cplx *__restrict__ H) {
 // pass), so a 1024-point transform is 3 passes (16 * 16 * 4) instead of 5 radix-4 ones, with
 // 16 independent loads, twiddles and stores per thread in flight.
 // ---------------------------------------------------------------------------
-// one spare element after every 16, one more after every 256 (sequences of a CTA start on different banks)
-__device__ __forceinline__ int pad16(int i) { return i + (i >> 4) + (i >> 8); }
 #ifndef SKB_FFT_PPT
 #define SKB_FFT_PPT 16          // points a thread holds per pass (16: radix-16 passes, 8: radix-8)
 #endif
 #ifndef SKB_FFT_MINB
 #define SKB_FFT_MINB 2
 #endif
-#ifndef SKB_FFT_TWPOW
-#define SKB_FFT_TWPOW 1         // twiddles of a butterfly as powers of one table entry
-#endif
 constexpr int FFT_PPT = SKB_FFT_PPT;
 constexpr size_t FFT_POINTS = 4096, FFT_THREADS = FFT_POINTS / FFT_PPT;
-constexpr size_t FFT_SMEM = (FFT_POINTS + (FFT_POINTS >> 4) + (FFT_POINTS >> 8) + 16) * sizeof(cplx);
 
 __device__ __forceinline__ cplx ldg_cplx(const cplx *p) {
     double2 v = __ldg(reinterpret_cast<const double2 *>(p));
@@ -684,172 +682,6 @@ template <> __device__ __forceinline__ void butterfly<16>(cplx *a) {
     for (int i = 0; i < 16; i++) a[i] = x[i];
 }
 
-template <int R>
-__device__ __forceinline__ void inplace_pass(cplx *buf, int L, int Ns, const cplx *__restrict__ W) {
-    constexpr int U = FFT_PPT / R;       // butterflies per thread
-    const int per = L / R, pshift = 31 - __clz(per), step = L / (Ns * R);
-    cplx a[U][R];
-    int dbase[U];
-#pragma unroll
-    for (int uu = 0; uu < U; uu++) {
-        const int u = (int)threadIdx.x + uu * (int)FFT_THREADS;
-        const int g = u >> pshift, j = u & (per - 1), k = j & (Ns - 1);
-        const int sbase = g * L + j;
-#pragma unroll
-        for (int t = 0; t < R; t++) a[uu][t] = buf[pad16(sbase + t * per)];
-        if (Ns > 1) {
-#if SKB_FFT_TWPOW
-            // one table read per butterfly; the other R-2 twiddles are its powers (product tree of
-            // depth <= 4, a few ulp): the FP64 pipe is idle here, the load latency is not
-            cplx wp[R];
-            wp[1] = ldg_cplx(W + k * step);
-#pragma unroll
-            for (int t = 2; t < R; t++) wp[t] = (t & 1) ? cmul(wp[t - 1], wp[1]) : cmul(wp[t / 2], wp[t / 2]);
-#pragma unroll
-            for (int t = 1; t < R; t++) a[uu][t] = cmul(a[uu][t], wp[t]);
-#else
-#pragma unroll
-            for (int t = 1; t < R; t++) a[uu][t] = cmul(a[uu][t], ldg_cplx(W + t * k * step));
-#endif
-        }
-        dbase[uu] = g * L + (j - k) * R + k;
-    }
-    __syncthreads();                     // every input is in registers: the buffer may be overwritten
-#pragma unroll
-    for (int uu = 0; uu < U; uu++) {
-        butterfly<R>(a[uu]);
-#pragma unroll
-        for (int q = 0; q < R; q++) buf[pad16(dbase[uu] + q * Ns)] = a[uu][q];
-    }
-    __syncthreads();
-}
-
-// In-place FFT of 4096 / L sequences of length L (16 <= L <= 4096, power of two); W = W_L table.
-__device__ __forceinline__ void smem_fft16(cplx *buf, int L, const cplx *__restrict__ W) {
-    int Ns = 1;
-    for (; L / Ns >= FFT_PPT; Ns *= FFT_PPT) inplace_pass<FFT_PPT>(buf, L, Ns, W);
-    const int rem = L / Ns;
-    if (FFT_PPT > 8 && rem == 8) inplace_pass<(FFT_PPT > 8 ? 8 : 2)>(buf, L, Ns, W);
-    else if (rem == 4) inplace_pass<4>(buf, L, Ns, W);
-    else if (rem == 2) inplace_pass<2>(buf, L, Ns, W);
-}
-
-// pass 1 (register-blocked engine): grid (N1 / G, columns in batch), G = 4096 / N2 sequences
-// per CTA.  The Makhoul permutation puts z[n] = (x[4n], x[4n+2]) and its mirror
-// z[N'-1-n] = (x[4n+3], x[4n+1]) in the same 32-byte sector, and the mirror of sequence n1,
-// position n2 is sequence N1-1-n1, position N2-1-n2 -- so a CTA takes G/2 sequences and their
-// G/2 mirrors and every sector it touches is used whole (one 4-double read per pair of points).
-template <bool AL32>
-__global__ void __launch_bounds__(FFT_THREADS, SKB_FFT_MINB)
-k_dct_pass1_r16(const double *__restrict__ X, size_t ldx, size_t col0, DctPlan pl,
-                const uint32_t *__restrict__ Dbits, double inscale, cplx *__restrict__ H) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    cplx *buf = reinterpret_cast<cplx *>(smem_raw);
-    const int N2 = (int)pl.N2, N1 = (int)pl.N1, G = (int)(FFT_POINTS / pl.N2), gshift = 31 - __clz(G);
-    const int Gh = G >> 1, a = (int)blockIdx.x * Gh;
-    const double *col = X + (col0 + blockIdx.y) * ldx;
-    cplx *Hc = H + (size_t)blockIdx.y * pl.Np;
-    auto seq = [&](int g) { return g < Gh ? a + g : N1 - 1 - a - (g - Gh); };   // sequence id of slot g
-    constexpr int PAIRS = (int)(FFT_POINTS / 2 / FFT_THREADS);      // 8 pairs of points per thread
-#pragma unroll
-    for (int b4 = 0; b4 < PAIRS / 4; b4++) {
-        double x[4][4]; uint32_t w[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const int p = (int)threadIdx.x + (b4 * 4 + u) * (int)FFT_THREADS;
-            const int g = p & (G - 1), n2 = p >> gshift;                // n2 < N2/2: the lower half
-            const unsigned q = 4u * (unsigned)(seq(g) + N1 * n2);       // < N <= 2^25
-            w[u] = __ldg(Dbits + (q >> 5)) >> (q & 31);
-            if (AL32) {
-                double2 lo = ldg_stream2(col + q), hi = ldg_stream2(col + q + 2);
-                x[u][0] = lo.x; x[u][1] = lo.y; x[u][2] = hi.x; x[u][3] = hi.y;
-            } else {
-#pragma unroll
-                for (int e = 0; e < 4; e++) x[u][e] = ldg_stream1(col + q + e);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const int p = (int)threadIdx.x + (b4 * 4 + u) * (int)FFT_THREADS;
-            const int g = p & (G - 1), n2 = p >> gshift;
-            double sx[4];
-#pragma unroll
-            for (int e = 0; e < 4; e++) sx[e] = __dmul_rn((w[u] >> e) & 1 ? -inscale : inscale, x[u][e]);
-            cplx z, zm;
-            z.x = sx[0]; z.y = sx[2];            // z[n]
-            zm.x = sx[3]; zm.y = sx[1];          // z[N'-1-n]
-            buf[pad16(g * N2 + n2)] = z;
-            buf[pad16((g ^ Gh) * N2 + (N2 - 1 - n2))] = zm;
-        }
-    }
-    __syncthreads();
-    smem_fft16(buf, N2, pl.W1);
-    // twiddle W_N'^(n1*k2): k2 advances by a fixed step per iteration, so the factor is refreshed
-    // from the tables every fourth point and advanced by one multiplication in between
-    const size_t lo_mask = ((size_t)1 << pl.lo_bits) - 1;
-    const int g = (int)threadIdx.x & (G - 1), n1 = seq(g);
-    const int k2_0 = (int)threadIdx.x >> gshift, dk = (int)FFT_THREADS >> gshift;
-    auto table_tw = [&](size_t e) {
-        e &= pl.Np - 1;
-        return cmul(ldg_cplx(pl.Thi + (e >> pl.lo_bits)), ldg_cplx(pl.Tlo + (e & lo_mask)));
-    };
-    const cplx wstep = table_tw((size_t)n1 * (size_t)dk);
-#pragma unroll
-    for (int i4 = 0; i4 < FFT_PPT / 4; i4++) {
-        cplx tw = table_tw((size_t)n1 * (size_t)(k2_0 + i4 * 4 * dk));
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const int k2 = k2_0 + (i4 * 4 + u) * dk;
-            Hc[(size_t)k2 * N1 + n1] = cmul(buf[pad16(g * N2 + k2)], tw);
-            tw = cmul(tw, wstep);
-        }
-    }
-}
-
-// pass 2 (register-blocked engine): grid (N2 / G, columns in batch), G = 4096 / N1 contiguous rows per CTA,
-// keeping only the bins the samples need (see DctPlan::need)
-__global__ void __launch_bounds__(FFT_THREADS, SKB_FFT_MINB)
-k_dct_pass2_r16_sel(DctPlan pl, const cplx *__restrict__ H) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    cplx *buf = reinterpret_cast<cplx *>(smem_raw);
-    const size_t base = (size_t)blockIdx.x * FFT_POINTS;
-    const cplx *rows = H + (size_t)blockIdx.y * pl.Np + base;
-#pragma unroll
-    for (int it = 0; it < FFT_PPT; it++) {
-        const int idx = (int)threadIdx.x + it * (int)FFT_THREADS;
-        buf[pad16(idx)] = rows[idx];
-    }
-    __syncthreads();
-    smem_fft16(buf, (int)pl.N1, pl.W2);
-    cplx *zc = pl.Zc + (size_t)blockIdx.y * pl.zc_ld;
-#pragma unroll
-    for (int it = 0; it < FFT_PPT; it++) {
-        const int idx = (int)threadIdx.x + it * (int)FFT_THREADS;
-        const size_t p = base + idx;
-        const uint32_t w = __ldg(pl.need + (p >> 5));
-        if ((w >> (p & 31)) & 1u)
-            zc[__ldg(pl.rank + (p >> 5)) + __popc(w & ((1u << (p & 31)) - 1u))] = buf[pad16(idx)];
-    }
-}
-
-__global__ void k_dct_post_sel(DctPlan pl, const int32_t *__restrict__ samples,
-                               size_t S, size_t col0, size_t ncols, double outscale,
-                               double *__restrict__ OUT, size_t oi, size_t oj) {
-    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= S * ncols) return;
-    const size_t i = t % S, c = t / S;
-    const size_t k = (size_t)samples[i], kp = k & (pl.Np - 1), km = (pl.Np - kp) & (pl.Np - 1);
-    const cplx *Z = pl.Zc + c * pl.zc_ld;
-    const cplx za = Z[dct_rank_of(pl, dct_pos(pl, kp))];
-    const cplx zb = Z[dct_rank_of(pl, dct_pos(pl, km))];
-    cplx E, O;
-    E.x = 0.5 * (za.x + zb.x); E.y = 0.5 * (za.y - zb.y);
-    O.x = 0.5 * (za.y + zb.y); O.y = -0.5 * (za.x - zb.x);
-    cplx V = cadd(E, cmul(pl.post[2 * i], O));
-    cplx Yc = cmul(pl.post[2 * i + 1], V);
-    OUT[i * oi + (col0 + c) * oj] = outscale * (2.0 * Yc.x);
-}
-
 // sampled bins -> DCT values -> OUT
 __global__ void k_dct_post(DctPlan pl, const cplx *__restrict__ H, const int32_t *__restrict__ samples,
                            size_t S, size_t col0, size_t ncols, double outscale,
@@ -867,6 +699,571 @@ __global__ void k_dct_post(DctPlan pl, const cplx *__restrict__ H, const int32_t
     cplx V = cadd(E, cmul(pl.post[2 * i], O));
     cplx Yc = cmul(pl.post[2 * i + 1], V);
     OUT[i * oi + (col0 + c) * oj] = outscale * (2.0 * Yc.x);
+}
+
+
+// ---------------------------------------------------------------------------
+// K8, fused form: ONE persistent launch per apply does pass 1, pass 2 and the sampled post-pass
+// of every column, with the intermediate H of a column handed from pass 1 to pass 2 through a
+// ring of DCT_NSLOT column slots (32 MB at N = 2^20) that stays in the 126 MB L2 -- HBM sees each
+// input element once and the s*d result once.
+//
+// Work items are numbered so that dependencies always point backwards: stage s holds the pass-1
+// tiles of column s, the pass-2 tiles of column s - LAG (alternating, so HBM-bound and
+// compute-bound tiles share the SMs) and the post item of column s - 2 LAG.  CTAs take items in
+// order from a global counter; an item that needs another one to have finished (pass 2: all
+// pass-1 tiles of its column; pass 1: the ring slot's previous user; post: all pass-2 tiles) spins
+// on a per-column counter that only ever depends on lower-numbered items, which are already
+// running or done -- no co-residency assumption, no deadlock.
+//
+// Inside a tile the first and last radix passes are fused with the global traffic: pass 2 loads
+// its rows straight into butterfly registers and hands its last-pass outputs to the selection
+// (only the bins the samples need are kept); pass 1 multiplies its last-pass outputs by the
+// inter-pass twiddle in registers and stores them with the sequence index varying across lanes,
+// i.e. in 256-byte runs of H.
+// ---------------------------------------------------------------------------
+// Pass 2 of a column runs `lag` stages behind its pass 1, the post-pass `lag` stages behind pass 2;
+// the rings hold lag + 2 columns of H and lag + 14 columns of kept bins.  lag is chosen per launch so
+// that a dependency is at least one full round of resident CTAs old when it is needed.
+static constexpr int DCT_POST_CHUNK = 1024;                      // samples per post item
+constexpr size_t FFT_SMEM2 = (FFT_POINTS + (FFT_POINTS >> 4) + 64) * sizeof(cplx);
+// Shared-memory twiddle tables of the fused kernel, filled once per (persistent) CTA -- every
+// dependency wait ends in a fence that drops the L1, so tables read through L1 would miss on every
+// tile.  Per pass kind a compact table of 16 + 256 butterfly twiddles; the inter-pass factors
+// W_N'^e = Thi[e >> 10] * Tlo[e & 1023] when both tables fit (N <= 2^21).
+constexpr int TW_COMPACT = 16 + 256, TT_SMEM_MAX = 2048;
+constexpr size_t FFT_SMEM2_TW = 2 * TW_COMPACT * sizeof(cplx);
+// W: table of W_L^m, m < L.  tw[k] = W_L^(k L / 256), k < 16 (middle pass, L >= 512);
+// tw[16 + j] = W_L^j, j < L / R_last (last pass)
+__device__ __forceinline__ void fused_twiddles(cplx *tw, const cplx *__restrict__ W, int L) {
+    int Ns = 16;
+    if (L / Ns > 16) {
+        if (threadIdx.x < 16) tw[threadIdx.x] = ldg_cplx(W + (int)threadIdx.x * (L >> 8));
+        Ns = 256;
+    }
+    for (int j = threadIdx.x; j < Ns; j += blockDim.x) tw[16 + j] = ldg_cplx(W + j);
+}
+
+struct DctFused {
+    const double *X; size_t ldx; size_t m;
+    DctPlan pl;
+    const uint32_t *Dbits; const int32_t *samples; size_t S;
+    double inscale, outscale;
+    cplx *H;                 // ring: DCT_NSLOT * Np
+    cplx *Zc;                // ring: DCT_NZ * zc_ld
+    const int32_t *pidx;     // per sample: position of Z[k'] and of Z[N'-k'] in a column's kept bins
+    unsigned *ctr;           // [0] item counter | ready1[m] | done2[m] | postdone[m]
+    double *OUT; size_t oi, oj;
+    unsigned T;              // tiles per column per pass = Np / 4096
+    unsigned PB;             // post items per column
+    unsigned TPI;            // tiles per pass-1 / pass-2 item
+    unsigned lag, nslot, nz; // see above
+    int tt_smem;             // inter-pass twiddle tables (Tlo, Thi) fit in shared memory
+    unsigned pf_dist;        // L2 prefetch distance in pass-1 tiles
+    int dbg;                 // SKB_DCT_DBG bits (timing experiments): 1 skip pass-2 work, 2 skip pass-1 work, 4 skip post
+};
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned ld_relaxed_u32(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// One thread polls and fences; the barrier extends the ordering to the CTA.  What other SMs wrote is
+// read through L2 only (ld.cg), so no L1 line can be stale.
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+__device__ __forceinline__ void red_release_add(unsigned *p, unsigned v) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// `seen` = a value of *p polled earlier by thread 0 (0 if none)
+__device__ __forceinline__ void wait_counter(const unsigned *p, unsigned target, unsigned seen = 0) {
+    if (threadIdx.x == 0) {
+        while (seen < target) { seen = ld_relaxed_u32(p); if (seen < target) __nanosleep(40); }
+        fence_acq_rel_gpu();
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ void signal_counter(unsigned *p) {
+    __syncthreads();
+    if (threadIdx.x == 0) { __threadfence(); atomicAdd(p, 1u); }
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void stg_cplx_hint(cplx *p, cplx v, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.v2.f64 [%0], {%1, %2}, %3;" ::"l"(p), "d"(v.x), "d"(v.y), "l"(pol) : "memory");
+}
+__device__ __forceinline__ cplx ldcg_cplx_hint(const cplx *p, uint64_t pol) {      // L2 only: H is written by other SMs
+    cplx v;
+    asm volatile("ld.global.cg.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;" : "=d"(v.x), "=d"(v.y) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ double2 ldg_stream2_hint(const double *p, uint64_t pol) {
+    double2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;"
+                 : "=d"(v.x), "=d"(v.y) : "l"(p), "l"(pol));
+    return v;
+}
+
+// shared-memory index of point i: a spare element after every 16; then either one per 256 (rows
+// walked with the position varying across lanes) or one per sequence (pass 1, whose last pass
+// walks the SEQUENCE index across lanes)
+template <bool SEQPAD> __device__ __forceinline__ int padx(int i, int lshift) {
+    return i + (i >> 4) + (SEQPAD ? (i >> lshift) : (i >> 8));
+}
+
+// twiddles of one radix-R butterfly of a pass with sub-length Ns: powers of W_L^(k * step)
+template <int R> __device__ __forceinline__ void twiddle_inputs(cplx *a, const cplx *W, int kstep) {
+    cplx wp[R];
+    wp[1] = W[kstep];
+#pragma unroll
+    for (int t = 2; t < R; t++) wp[t] = (t & 1) ? cmul(wp[t - 1], wp[1]) : cmul(wp[t / 2], wp[t / 2]);
+#pragma unroll
+    for (int t = 1; t < R; t++) a[t] = cmul(a[t], wp[t]);
+}
+
+// middle pass, in place in shared memory (all reads, barrier, all writes, barrier)
+template <int R, bool SEQPAD>
+__device__ __forceinline__ void mid_pass(cplx *buf, int L, int lshift, int Ns, const cplx *W) {
+    constexpr int U = FFT_PPT / R;
+    const int per = L / R, pshift = 31 - __clz(per);
+    cplx a[U][R];
+    int dbase[U];
+#pragma unroll
+    for (int uu = 0; uu < U; uu++) {
+        const int u = (int)threadIdx.x + uu * (int)FFT_THREADS;
+        const int g = u >> pshift, j = u & (per - 1), k = j & (Ns - 1);
+#pragma unroll
+        for (int t = 0; t < R; t++) a[uu][t] = buf[padx<SEQPAD>(g * L + j + t * per, lshift)];
+        twiddle_inputs<R>(a[uu], W, k);           // compact table: entry k = W_L^(k * step)
+        dbase[uu] = g * L + (j - k) * R + k;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int uu = 0; uu < U; uu++) {
+        butterfly<R>(a[uu]);
+#pragma unroll
+        for (int q = 0; q < R; q++) buf[padx<SEQPAD>(dbase[uu] + q * Ns, lshift)] = a[uu][q];
+    }
+    __syncthreads();
+}
+
+// last pass (Ns * R == L): outputs go to sink(g, k, value), k = natural-order index inside
+// sequence g.  GFAST: the sequence index varies fastest across lanes.
+template <int R, bool SEQPAD, bool GFAST, class Sink>
+__device__ __forceinline__ void last_pass(const cplx *buf, int L, int lshift, const cplx *W, Sink sink) {
+    constexpr int U = FFT_PPT / R;
+    const int Ns = L / R, nshift = 31 - __clz(Ns), gshift = 12 - lshift;     // G = 4096 / L sequences
+#pragma unroll
+    for (int uu = 0; uu < U; uu++) {
+        const int u = (int)threadIdx.x + uu * (int)FFT_THREADS;
+        const int g = GFAST ? (u & ((1 << gshift) - 1)) : (u >> nshift);
+        const int j = GFAST ? (u >> gshift) : (u & (Ns - 1));
+        cplx a[R];
+#pragma unroll
+        for (int t = 0; t < R; t++) a[t] = buf[padx<SEQPAD>(g * L + j + t * Ns, lshift)];
+        twiddle_inputs<R>(a, W, j);                 // step = 1
+        butterfly<R>(a);
+        sink(g, j, Ns, a);
+    }
+}
+
+template <bool SEQPAD, bool GFAST, class Sink>
+__device__ __forceinline__ void fft_tail(cplx *buf, int L, int lshift, const cplx *W, Sink sink,
+                                         const unsigned *slot_free, unsigned slot_free_target, unsigned slot_seen) {
+    // after the first radix-16 pass (Ns = 16): at most one middle radix-16 pass (L >= 512), then the
+    // last pass.  W is the compact shared-memory table of fused_twiddles(): 16 entries for the
+    // middle pass, then the last pass's.
+    int Ns = 16;
+    if (L / Ns > 16) { mid_pass<16, SEQPAD>(buf, L, lshift, Ns, W); Ns *= 16; }
+    W += 16;
+    // the ring slot the last pass stores into must have been released by its previous user: checked
+    // here, at the latest possible point, where it has long been the case
+    if (slot_free) {         // write-after-read: ordered by the control dependency and the barrier, no fence
+        if (threadIdx.x == 0)
+            while (slot_seen < slot_free_target) { __nanosleep(20); slot_seen = ld_relaxed_u32(slot_free); }
+        __syncthreads();
+    }
+    const int rem = L / Ns;
+    if (rem == 16) last_pass<16, SEQPAD, GFAST>(buf, L, lshift, W, sink);
+    else if (rem == 8) last_pass<8, SEQPAD, GFAST>(buf, L, lshift, W, sink);
+    else if (rem == 4) last_pass<4, SEQPAD, GFAST>(buf, L, lshift, W, sink);
+    else last_pass<2, SEQPAD, GFAST>(buf, L, lshift, W, sink);
+}
+
+template <bool AL32>
+__device__ __forceinline__ void dct_tile_pass1(const DctFused &a, cplx *buf, size_t c, unsigned tile,
+                                               uint64_t pol_first, uint64_t pol_last,
+                                               const unsigned *slot_free, unsigned slot_free_target, unsigned slot_seen,
+                                               const cplx *tw, const cplx *tt) {
+    const DctPlan &pl = a.pl;
+    const int N2 = (int)pl.N2, N1 = (int)pl.N1, lshift = 31 - __clz(N2);
+    const int G = (int)(FFT_POINTS / pl.N2), gshift = 12 - lshift, Gh = G >> 1, a0 = (int)tile * Gh;
+    const double *col = a.X + c * a.ldx;
+    cplx *Hc = a.H + (c % a.nslot) * pl.Np;
+    auto seq = [&](int g) { return g < Gh ? a0 + g : N1 - 1 - a0 - (g - Gh); };
+    constexpr int PAIRS = (int)(FFT_POINTS / 2 / FFT_THREADS);
+#pragma unroll
+    for (int b4 = 0; b4 < PAIRS / 4; b4++) {
+        double x[4][4]; uint32_t w[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int p = (int)threadIdx.x + (b4 * 4 + u) * (int)FFT_THREADS;
+            const int g = p & (G - 1), n2 = p >> gshift;                // n2 < N2/2: the lower half
+            const unsigned q = 4u * (unsigned)(seq(g) + N1 * n2);
+            w[u] = __ldg(a.Dbits + (q >> 5)) >> (q & 31);
+            if (AL32) {
+                double2 lo = ldg_stream2_hint(col + q, pol_first), hi = ldg_stream2_hint(col + q + 2, pol_first);
+                x[u][0] = lo.x; x[u][1] = lo.y; x[u][2] = hi.x; x[u][3] = hi.y;
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; e++) x[u][e] = ldg_stream1(col + q + e);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int p = (int)threadIdx.x + (b4 * 4 + u) * (int)FFT_THREADS;
+            const int g = p & (G - 1), n2 = p >> gshift;
+            double sx[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) sx[e] = __dmul_rn((w[u] >> e) & 1 ? -a.inscale : a.inscale, x[u][e]);
+            cplx z, zm;
+            z.x = sx[0]; z.y = sx[2];            // z[n]
+            zm.x = sx[3]; zm.y = sx[1];          // z[N'-1-n]
+            buf[padx<true>(g * N2 + n2, lshift)] = z;
+            buf[padx<true>((g ^ Gh) * N2 + (N2 - 1 - n2), lshift)] = zm;
+        }
+    }
+    __syncthreads();
+    {   // first radix-16 pass (Ns = 1), in place
+        const int per = N2 >> 4, pshift = 31 - __clz(per);
+        const int u = (int)threadIdx.x, g = u >> pshift, j = u & (per - 1);
+        cplx v[16];
+#pragma unroll
+        for (int t = 0; t < 16; t++) v[t] = buf[padx<true>(g * N2 + j + t * per, lshift)];
+        __syncthreads();
+        butterfly<16>(v);
+#pragma unroll
+        for (int q = 0; q < 16; q++) buf[padx<true>(g * N2 + j * 16 + q, lshift)] = v[q];
+        __syncthreads();
+    }
+    const size_t lo_mask = ((size_t)1 << pl.lo_bits) - 1;
+    auto table_tw = [&](size_t e) {
+        e &= pl.Np - 1;
+        if (a.tt_smem) return cmul(tt[((size_t)1 << pl.lo_bits) + (e >> pl.lo_bits)], tt[e & lo_mask]);
+        return cmul(ldg_cplx(pl.Thi + (e >> pl.lo_bits)), ldg_cplx(pl.Tlo + (e & lo_mask)));
+    };
+    // last-pass outputs k2 = j + q*Ns of sequence g: times W_N'^(n1*k2), stored at H[k2*N1 + n1]
+    auto sink = [&](int g, int j, int Ns, auto &v) {
+        constexpr int R = (int)(sizeof(v) / sizeof(cplx));
+        const size_t n1 = (size_t)seq(g);
+        const cplx wstep = table_tw(n1 * (size_t)Ns);
+        cplx tw = table_tw(n1 * (size_t)j);
+#pragma unroll
+        for (int q = 0; q < R; q++) {
+            if (q && (q & 7) == 0) tw = table_tw(n1 * (size_t)(j + q * Ns));     // bound the error of the running product
+            stg_cplx_hint(Hc + (size_t)(j + q * Ns) * (size_t)N1 + n1, cmul(v[q], tw), pol_last);
+            tw = cmul(tw, wstep);
+        }
+    };
+    fft_tail<true, true>(buf, N2, lshift, tw, sink, slot_free, slot_free_target, slot_seen);
+}
+
+__device__ __forceinline__ void dct_tile_pass2(const DctFused &a, cplx *buf, size_t c, unsigned tile, uint64_t pol_last,
+                                               const unsigned *slot_free, unsigned slot_free_target, unsigned slot_seen,
+                                               const cplx *tw, uint32_t *s_need, uint32_t *s_rank) {
+    const DctPlan &pl = a.pl;
+    const int L = (int)pl.N1, lshift = 31 - __clz(L);
+    const size_t base = (size_t)tile * FFT_POINTS;
+    const cplx *rows = a.H + (c % a.nslot) * pl.Np + base;
+    if (threadIdx.x < FFT_POINTS / 32) {     // which of the tile's bins the samples need, and their ranks
+        s_need[threadIdx.x] = __ldg(pl.need + (base >> 5) + threadIdx.x);
+        s_rank[threadIdx.x] = __ldg(pl.rank + (base >> 5) + threadIdx.x);
+    }
+    {   // first radix-16 pass straight from global memory (rows are contiguous)
+        const int per = L >> 4, pshift = 31 - __clz(per);
+        const int u = (int)threadIdx.x, g = u >> pshift, j = u & (per - 1);
+        cplx v[16];
+#pragma unroll
+        for (int t = 0; t < 16; t++) v[t] = ldcg_cplx_hint(rows + g * L + j + t * per, pol_last);
+        butterfly<16>(v);
+#pragma unroll
+        for (int q = 0; q < 16; q++) buf[padx<false>(g * L + j * 16 + q, lshift)] = v[q];
+        __syncthreads();
+    }
+    cplx *zc = a.Zc + (c % a.nz) * pl.zc_ld;
+    auto sink = [&](int g, int j, int Ns, auto &v) {
+        constexpr int R = (int)(sizeof(v) / sizeof(cplx));
+#pragma unroll
+        for (int q = 0; q < R; q++) {
+            const int p = g * L + j + q * Ns;                      // position inside the tile
+            const uint32_t w = s_need[p >> 5];
+            if ((w >> (p & 31)) & 1u)
+                zc[s_rank[p >> 5] + __popc(w & ((1u << (p & 31)) - 1u))] = v[q];
+        }
+    };
+    fft_tail<false, false>(buf, L, lshift, tw, sink, slot_free, slot_free_target, slot_seen);
+}
+
+__device__ __forceinline__ void dct_post_chunk(const DctFused &a, size_t c, unsigned chunk) {
+    const DctPlan &pl = a.pl;
+    const cplx *Z = a.Zc + (c % a.nz) * pl.zc_ld;
+    const size_t i0 = (size_t)chunk * DCT_POST_CHUNK, i1 = i0 + DCT_POST_CHUNK < a.S ? i0 + DCT_POST_CHUNK : a.S;
+    for (size_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+        const int2 pq = __ldg(reinterpret_cast<const int2 *>(a.pidx) + i);
+        const double2 ra = __ldcg(reinterpret_cast<const double2 *>(Z + pq.x));
+        const double2 rb = __ldcg(reinterpret_cast<const double2 *>(Z + pq.y));
+        cplx E, O;
+        E.x = 0.5 * (ra.x + rb.x); E.y = 0.5 * (ra.y - rb.y);
+        O.x = 0.5 * (ra.y + rb.y); O.y = -0.5 * (ra.x - rb.x);
+        cplx V = cadd(E, cmul(ldg_cplx(pl.post + 2 * i), O));
+        cplx Yc = cmul(ldg_cplx(pl.post + 2 * i + 1), V);
+        a.OUT[i * a.oi + c * a.oj] = a.outscale * (2.0 * Yc.x);
+    }
+}
+
+template <bool AL32>
+__global__ void __launch_bounds__(FFT_THREADS, SKB_FFT_MINB)
+k_dct_fused(const DctFused a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cplx *buf = reinterpret_cast<cplx *>(smem_raw);
+    __shared__ unsigned s_item[2];
+    __shared__ uint32_t s_need[FFT_POINTS / 32], s_rank[FFT_POINTS / 32];
+    // an item is TPI consecutive tiles of one pass of one column (or one chunk of the post-pass);
+    // the per-column counters count items
+    const unsigned TPI = a.TPI, TI = a.T / TPI, PB = a.PB, per_stage = 2 * TI + PB;
+    const unsigned long long total = (unsigned long long)(a.m + 2 * a.lag) * per_stage;
+    unsigned *ready1 = a.ctr + 1, *done2 = ready1 + a.m, *postdone = done2 + a.m;
+    const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
+    cplx *tw1 = reinterpret_cast<cplx *>(smem_raw + FFT_SMEM2), *tw2 = tw1 + TW_COMPACT, *tt = tw2 + TW_COMPACT;
+    fused_twiddles(tw1, a.pl.W1, (int)a.pl.N2);
+    fused_twiddles(tw2, a.pl.W2, (int)a.pl.N1);
+    if (a.tt_smem) {
+        const int nlo = 1 << a.pl.lo_bits, nhi = (int)(a.pl.Np >> a.pl.lo_bits);
+        for (int i = threadIdx.x; i < nlo; i += blockDim.x) tt[i] = ldg_cplx(a.pl.Tlo + i);
+        for (int i = threadIdx.x; i < nhi; i += blockDim.x) tt[nlo + i] = ldg_cplx(a.pl.Thi + i);
+    }
+    if (threadIdx.x == 0) s_item[0] = atomicAdd(a.ctr, 1u);
+    __syncthreads();
+    for (int par = 0;; par ^= 1) {
+        const unsigned item = s_item[par];
+        if (item >= total) break;
+        // the next item is fetched while this one is worked on (items are still handed out in order)
+        // duties are spread over three warps so that their memory round trips overlap: thread 0 polls
+        // dependencies, thread 32 publishes completions, thread 64 fetches items
+        unsigned nxt = 0;
+        if (threadIdx.x == 64) nxt = atomicAdd(a.ctr, 1u);
+        const size_t stage = item / per_stage;
+        const unsigned r = item % per_stage;
+        unsigned *done = nullptr;                  // counter this item bumps when its stores are out
+        if (r >= 2 * TI) {
+            if (stage >= 2 * a.lag && stage - (2 * a.lag) < a.m) {
+                const size_t c = stage - (2 * a.lag);
+                wait_counter(done2 + c, TI);
+                if (!(a.dbg & 4)) dct_post_chunk(a, c, r - 2 * TI);
+                done = postdone + c;
+            }
+        } else if ((r & 1) == 0) {
+            if (stage < a.m) {
+                const size_t c = stage;
+                const unsigned *sf = c >= a.nslot ? done2 + (c - a.nslot) : nullptr;      // H ring slot free
+                unsigned seen = (sf && threadIdx.x == 0) ? ld_relaxed_u32(sf) : 0u;            // polled early, needed late
+                if (AL32 && !(a.dbg & 8)) {
+                    // pull the input of the pass-1 tiles that run about one round of CTAs later into L2
+                    const int N2 = (int)a.pl.N2, N1 = (int)a.pl.N1, Gh = (int)(FFT_POINTS / a.pl.N2) >> 1;
+                    for (unsigned sub = 0; sub < TPI; sub++) {
+                        const unsigned long long q = (unsigned long long)stage * a.T + (r >> 1) * TPI + sub + a.pf_dist;
+                        const size_t cpf = (size_t)(q / a.T);
+                        if (cpf >= a.m) break;
+                        const int a0 = (int)(q % a.T) * Gh;
+                        const double *colp = a.X + cpf * a.ldx;
+                        for (int i = threadIdx.x; i < N2; i += blockDim.x) {        // N2/2 positions x 2 runs
+                            const int n2 = i >> 1, first = (i & 1) ? N1 - a0 - Gh : a0;
+                            const double *src = colp + 4 * ((size_t)first + (size_t)N1 * n2);
+                            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(Gh * 32));
+                        }
+                    }
+                }
+                for (unsigned sub = 0; sub < TPI; sub++) {
+                    if (sub) __syncthreads();      // the previous tile's last pass has left the buffer
+                    if (!(a.dbg & 2))
+                        dct_tile_pass1<AL32>(a, buf, c, (r >> 1) * TPI + sub, pol_first, pol_last,
+                                             sub == 0 ? sf : nullptr, TI, seen, tw1, tt);
+                }
+                done = ready1 + c;
+            }
+        } else {
+            if (stage >= a.lag && stage - a.lag < a.m) {
+                const size_t c = stage - a.lag;
+                const unsigned *sf = c >= a.nz ? postdone + (c - a.nz) : nullptr;         // kept-bin ring slot free
+                unsigned seen = (sf && threadIdx.x == 0) ? ld_relaxed_u32(sf) : 0u;
+                wait_counter(ready1 + c, TI);
+                for (unsigned sub = 0; sub < TPI; sub++) {
+                    if (sub) __syncthreads();
+                    if (!(a.dbg & 1))
+                        dct_tile_pass2(a, buf, c, (r >> 1) * TPI + sub, pol_last, sub == 0 ? sf : nullptr, PB, seen,
+                                       tw2, s_need, s_rank);
+                }
+                done = done2 + c;
+            }
+        }
+        if (threadIdx.x == 64) s_item[par ^ 1] = nxt;
+        __syncthreads();                           // stores are issued, the tile buffer is free, s_item[par ^ 1] is set
+        if (done && threadIdx.x == 32) red_release_add(done, 1u);       // cumulative over the barrier; off the others' path
+    }
+}
+
+// split N' = N1 * N2 of the fused form: 128-point strided FFTs (pass 1: 32 sequences per tile, 256-byte
+// runs) and rows of up to 4096 points (pass 2: one tile per row)
+static bool dct_fused_ok(size_t N) { return N >= 8192 && (N & (N - 1)) == 0 && N <= ((size_t)1 << 24); }
+static void dct_fused_split(size_t N, size_t *N1, size_t *N2) {
+    const size_t Np = N / 2;
+    size_t n2 = 128;
+    {   // debug knob: log2 of the strided (pass 1) FFT length
+        static const char *e = getenv("SKB_DCT_N2LOG");
+        if (e && atoi(e) >= 7 && atoi(e) <= 11) n2 = (size_t)1 << atoi(e);
+    }
+    while (Np / n2 > FFT_POINTS) n2 *= 2;
+    while (Np / n2 < 32 && n2 > 128) n2 /= 2;
+    *N2 = n2; *N1 = Np / n2;
+}
+
+static bool dct_legacy_forced() {
+    static const bool v = getenv("SKB_DCT_LEGACY") != nullptr;      // A/B: the per-batch two-kernel form
+    return v;
+}
+static size_t align256(size_t x) { return (x + 255) / 256 * 256; }
+
+// Tables of the fused form: they depend on (N, S, samples) only, so a transform builds them once
+// per device (fjlt_dct_plan_build) and every apply reuses them.
+static DctPlan dct_plan_layout(size_t N, size_t S, void *buf) {
+    DctPlan pl;
+    pl.N = N; pl.Np = N / 2;
+    dct_fused_split(N, &pl.N1, &pl.N2);
+    pl.lo_bits = 10;
+    pl.G1 = pl.G2 = 0;
+    char *p = reinterpret_cast<char *>(buf);
+    auto take = [&](size_t bytes) { char *r = p; p += align256(bytes); return r; };
+    pl.W1 = reinterpret_cast<cplx *>(take(pl.N2 * sizeof(cplx)));
+    pl.W2 = reinterpret_cast<cplx *>(take(pl.N1 * sizeof(cplx)));
+    pl.Tlo = reinterpret_cast<cplx *>(take(((size_t)1 << pl.lo_bits) * sizeof(cplx)));
+    pl.Thi = reinterpret_cast<cplx *>(take(((pl.Np >> pl.lo_bits) + 1) * sizeof(cplx)));
+    pl.post = reinterpret_cast<cplx *>(take(2 * S * sizeof(cplx)));
+    pl.need = reinterpret_cast<uint32_t *>(take((pl.Np / 32 + 64) * sizeof(uint32_t)));
+    pl.rank = reinterpret_cast<uint32_t *>(take((pl.Np / 32 + 64) * sizeof(uint32_t)));
+    pl.Zc = nullptr; pl.zc_ld = 2 * S;
+    pl.G2 = (size_t)(take(2 * S * sizeof(int32_t)) - reinterpret_cast<char *>(buf));   // offset of pidx
+    pl.G1 = (size_t)(p - reinterpret_cast<char *>(buf));     // bytes used (host side only)
+    return pl;
+}
+__global__ void k_dct_pidx(DctPlan pl, const int32_t *__restrict__ samples, size_t S, int32_t *__restrict__ pidx) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S) return;
+    const size_t k = (size_t)samples[t], kp = k & (pl.Np - 1), km = (pl.Np - kp) & (pl.Np - 1);
+    pidx[2 * t] = (int32_t)dct_rank_of(pl, dct_pos(pl, kp));
+    pidx[2 * t + 1] = (int32_t)dct_rank_of(pl, dct_pos(pl, km));
+}
+size_t fjlt_dct_plan_bytes(size_t N, size_t S) {
+    if (!dct_fused_ok(N) || dct_legacy_forced()) return 0;
+    return dct_plan_layout(N, S, nullptr).G1;
+}
+void fjlt_dct_plan_build(size_t N, size_t S, const int32_t *samples, void *buf, cudaStream_t st) {
+    DctPlan pl = dct_plan_layout(N, S, buf);
+    size_t nt = pl.N2 > S ? pl.N2 : S;
+    if (nt < pl.N1) nt = pl.N1;
+    if (nt < 1024) nt = 1024;
+    if (nt < (pl.Np >> pl.lo_bits) + 1) nt = (pl.Np >> pl.lo_bits) + 1;
+    {
+        LaunchScope ls(KC_TABLES, st);
+        k_dct_tables<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(pl, samples, S);
+        SKB_CUDA(cudaGetLastError());
+    }
+    SKB_CUDA(cudaMemsetAsync(pl.need, 0, (pl.Np / 32 + 64) * sizeof(uint32_t), st));
+    {
+        LaunchScope ls(KC_TABLES, st);
+        k_dct_mark<<<(unsigned)((S + 255) / 256), 256, 0, st>>>(pl, samples, S);
+        SKB_CUDA(cudaGetLastError());
+    }
+    {
+        LaunchScope ls(KC_TABLES, st);
+        k_dct_rank<<<1, 1024, 0, st>>>(pl);
+        SKB_CUDA(cudaGetLastError());
+    }
+    {
+        LaunchScope ls(KC_TABLES, st);
+        k_dct_pidx<<<(unsigned)((S + 255) / 256), 256, 0, st>>>(
+            pl, samples, S, reinterpret_cast<int32_t *>(reinterpret_cast<char *>(buf) + pl.G2));
+        SKB_CUDA(cudaGetLastError());
+    }
+}
+static unsigned dct_fused_tpi(size_t N) {
+    static const char *e = getenv("SKB_DCT_TPI");
+    unsigned tpi = e ? (unsigned)atoi(e) : 1u;
+    const unsigned T = (unsigned)(N / 2 / FFT_POINTS);
+    if (tpi < 1) tpi = 1;
+    while (tpi > 1 && T % tpi) tpi--;
+    return tpi;
+}
+static unsigned dct_fused_lag(size_t N, size_t S) {
+    static const char *e = getenv("SKB_DCT_LAG");
+    if (e && atoi(e) > 0) return (unsigned)atoi(e);
+    const unsigned long long per_stage = 2ULL * (N / 2 / FFT_POINTS / dct_fused_tpi(N)) + (S + DCT_POST_CHUNK - 1) / DCT_POST_CHUNK;
+    const unsigned long long slots = 148ULL * SKB_FFT_MINB;
+    unsigned long long lag = (slots + per_stage - 1) / per_stage + 1;
+    if (lag < 2) lag = 2;
+    // keep the H ring inside L2 where the sizes allow (a longer ring only costs residency, not correctness)
+    const unsigned long long cap = ((unsigned long long)48 << 20) / ((N / 2) * sizeof(cplx));
+    if (lag + 2 > cap && cap >= 4) lag = cap - 2;
+    return (unsigned)lag;
+}
+static size_t dct_fused_ws_bytes(size_t N, size_t m, size_t S) {
+    const size_t lag = dct_fused_lag(N, S);
+    return align256((lag + 2) * (N / 2) * sizeof(cplx)) + align256((lag + 14) * 2 * S * sizeof(cplx)) +
+           align256((1 + 3 * m) * sizeof(unsigned));
+}
+// columns [c0, c0 + mc) of Xc through the fused kernel
+static void dct_fused_launch(const double *Xc, size_t ldc, size_t N, size_t mc, const uint32_t *Dbits,
+                             const int32_t *samples, size_t S, const void *plan, char *ws, double *OUT,
+                             size_t oi, size_t oj, cudaStream_t st) {
+    DctFused a;
+    a.X = Xc; a.ldx = ldc; a.m = mc;
+    a.pl = dct_plan_layout(N, S, const_cast<void *>(plan));
+    a.Dbits = Dbits; a.samples = samples; a.S = S;
+    a.inscale = 1.0 / sqrt(2.0 * (double)N); a.outscale = sqrt((double)N / (double)S);
+    a.lag = dct_fused_lag(N, S); a.nslot = a.lag + 2; a.nz = a.lag + 14;
+    a.H = reinterpret_cast<cplx *>(ws); ws += align256(a.nslot * (N / 2) * sizeof(cplx));
+    a.Zc = reinterpret_cast<cplx *>(ws); ws += align256(a.nz * 2 * S * sizeof(cplx));
+    a.pidx = reinterpret_cast<const int32_t *>(reinterpret_cast<const char *>(plan) + a.pl.G2);
+    a.PB = (unsigned)((S + DCT_POST_CHUNK - 1) / DCT_POST_CHUNK);
+    a.TPI = dct_fused_tpi(N);
+    a.ctr = reinterpret_cast<unsigned *>(ws);
+    a.OUT = OUT; a.oi = oi; a.oj = oj;
+    a.T = (unsigned)(a.pl.Np / FFT_POINTS);
+    { static const char *e = getenv("SKB_DCT_DBG"); a.dbg = e ? atoi(e) : 0; }
+    SKB_CUDA(cudaMemsetAsync(a.ctr, 0, (1 + 3 * mc) * sizeof(unsigned), st));
+    const bool al32 = (ldc % 4 == 0) && ((uintptr_t)Xc % 32 == 0);
+    auto kern = al32 ? k_dct_fused<true> : k_dct_fused<false>;
+    const size_t ntt = ((size_t)1 << a.pl.lo_bits) + (a.pl.Np >> a.pl.lo_bits);
+    a.tt_smem = ntt <= (size_t)TT_SMEM_MAX ? 1 : 0;
+    const size_t smem = FFT_SMEM2 + FFT_SMEM2_TW + (a.tt_smem ? ntt * sizeof(cplx) : 0);
+    { static const char *e = getenv("SKB_DCT_PF"); a.pf_dist = e ? (unsigned)atoi(e) : 148u; }
+    SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned long long items = (unsigned long long)(mc + 2 * a.lag) * (2ULL * (a.T / a.TPI) + a.PB);
+    const unsigned long long slots = (unsigned long long)fjlt_sms() * SKB_FFT_MINB;
+    LaunchScope ls(KC_FJLT, st);
+    kern<<<(unsigned)(items < slots ? items : slots), FFT_THREADS, smem, st>>>(a);
+    SKB_CUDA(cudaGetLastError());
 }
 
 static bool dct_fast_ok(size_t N) { return N >= 1024 && (N & (N - 1)) == 0 && N <= ((size_t)1 << 25); }
@@ -891,6 +1288,8 @@ static size_t dct_sel_bytes(size_t N, size_t S, size_t B) {     // need bitmap, 
 static bool wht_fast_ok(size_t N) { return N >= (size_t)WSEG && (N & (N - 1)) == 0 && N <= ((size_t)1 << 28); }
 
 size_t fjlt_workspace_bytes(size_t N, size_t m, int fut, bool layout_rows, size_t S) {
+    if (fut == FUT_DCT && dct_fused_ok(N) && !dct_legacy_forced())
+        return (layout_rows ? align256(N * m * sizeof(double)) : 0) + dct_fused_ws_bytes(N, m, S) + 1024;
     if (fut == FUT_DCT && dct_fast_ok(N))
         return (layout_rows ? N * m * sizeof(double) : 0) + dct_batch_cols(N, m) * N * sizeof(double) +
                dct_table_bytes(N, S) + dct_sel_bytes(N, S, dct_batch_cols(N, m)) + 1024;
@@ -909,7 +1308,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
                 const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
                 const int32_t *wht_slot_sample, const int32_t *wht_slot_out,
                 double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
-                cudaStream_t st, size_t offset, size_t nloc) {
+                cudaStream_t st, size_t offset, size_t nloc, const void *dct_plan) {
     if (S == 0 || m == 0) return;
     if (nloc != N && !fjlt_shard_ok(fut, N, offset, nloc))
         throw error(SKB_ERR_INVALID_USAGE,
@@ -930,6 +1329,18 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
             launch_transpose_to_cols(X, ldx, N, m, T, st);
             SKB_CUDA(cudaGetLastError());
             Xc = T; ldc = N;
+        }
+        const size_t oi_ = layout_rows ? ldo : 1, oj_ = layout_rows ? 1 : ldo;
+        if (dct_plan && dct_fused_ok(N) && !dct_legacy_forced()) {
+            // keep the 32-bit item counter of one launch far from wrapping
+            const size_t tiles = N / 2 / FFT_POINTS,
+                         cmax = ((size_t)1 << 30) / (2 * tiles + (S + DCT_POST_CHUNK - 1) / DCT_POST_CHUNK);
+            for (size_t c0 = 0; c0 < m; c0 += cmax) {
+                const size_t mc = m - c0 < cmax ? m - c0 : cmax;
+                dct_fused_launch(Xc + c0 * ldc, ldc, N, mc, Dbits, samples, S, dct_plan, ws, OUT + c0 * oj_,
+                                 oi_, oj_, st);
+            }
+            return;
         }
         DctPlan pl;
         pl.N = N; pl.Np = N / 2;
@@ -982,46 +1393,8 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         // one radix-4 unit per thread per pass where possible (latency hiding by occupancy)
         auto threads_for = [](size_t units) { size_t t = 128; while (t < units && t < 1024) t *= 2; return (unsigned)t; };
         const unsigned thr1 = threads_for(pl.G1 * pl.N2 / 4), thr2 = threads_for(pl.G2 * pl.N1 / 4);
-        // register-blocked radix-16 engine when a CTA's 4096 points hold whole sequences
-        const bool r16 = pl.N1 >= (size_t)FFT_PPT && pl.N2 >= (size_t)FFT_PPT && pl.N1 <= FFT_POINTS && pl.N2 <= FFT_POINTS / 2 &&
-                         pl.N1 * pl.N2 >= FFT_POINTS;
-        if (r16) {
-            SKB_CUDA(cudaFuncSetAttribute(k_dct_pass1_r16<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFT_SMEM));
-            SKB_CUDA(cudaFuncSetAttribute(k_dct_pass1_r16<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFT_SMEM));
-            SKB_CUDA(cudaFuncSetAttribute(k_dct_pass2_r16_sel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FFT_SMEM));
-            SKB_CUDA(cudaMemsetAsync(pl.need, 0, (pl.Np / 32) * sizeof(uint32_t), st));
-            {
-                LaunchScope ls(KC_FJLT, st);
-                k_dct_mark<<<(unsigned)((S + 255) / 256), 256, 0, st>>>(pl, samples, S);
-            }
-            {
-                LaunchScope ls(KC_FJLT, st);
-                k_dct_rank<<<1, 1024, 0, st>>>(pl);
-            }
-        }
         for (size_t c0 = 0; c0 < m; c0 += B) {
             const size_t nb = m - c0 < B ? m - c0 : B;
-            if (r16) {
-                {
-                    LaunchScope ls(KC_FJLT, st);
-                    const bool al32 = (ldc % 4 == 0) && ((uintptr_t)Xc % 32 == 0);
-                    auto k1 = al32 ? k_dct_pass1_r16<true> : k_dct_pass1_r16<false>;
-                    k1<<<dim3((unsigned)(pl.N1 * pl.N2 / FFT_POINTS), (unsigned)nb),
-                         FFT_THREADS, FFT_SMEM, st>>>(Xc, ldc, c0, pl, Dbits, inscale, H);
-                }
-                {
-                    LaunchScope ls(KC_FJLT, st);
-                    k_dct_pass2_r16_sel<<<dim3((unsigned)(pl.N1 * pl.N2 / FFT_POINTS), (unsigned)nb),
-                                          FFT_THREADS, FFT_SMEM, st>>>(pl, H);
-                }
-                {
-                    LaunchScope ls(KC_FJLT, st);
-                    k_dct_post_sel<<<(unsigned)((S * nb + 255) / 256), 256, 0, st>>>(
-                        pl, samples, S, c0, nb, outscale, OUT, oi, oj);
-                }
-                SKB_CUDA(cudaGetLastError());
-                continue;
-            } else {
             {
                 LaunchScope ls(KC_FJLT, st);
                 k_dct_pass1<<<dim3((unsigned)(pl.N1 / pl.G1), (unsigned)nb), thr1, smem1, st>>>(
@@ -1030,7 +1403,6 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
             {
                 LaunchScope ls(KC_FJLT, st);
                 k_dct_pass2<<<dim3((unsigned)(pl.N2 / pl.G2), (unsigned)nb), thr2, smem2, st>>>(pl, H);
-            }
             }
             {
                 LaunchScope ls(KC_FJLT, st);
@@ -1066,7 +1438,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         const bool al16 = (ldc % 2 == 0) && ((uintptr_t)Xc % 16 == 0);
         auto kern = al16 ? k_fjlt_wht_cols<true> : k_fjlt_wht_cols<false>;
         SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        unsigned grid = (unsigned)(m < 148 ? m : 148);
+        unsigned grid = (unsigned)(m < fjlt_sms() ? m : fjlt_sms());
         const size_t per_pass = (size_t)WG_THREADS * WSPT;               // 8192 samples per pass
         for (size_t s0 = 0, p = 0; s0 < S; s0 += per_pass, p++) {
             LaunchScope ls(KC_FJLT, st);

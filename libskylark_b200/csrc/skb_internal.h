@@ -145,8 +145,14 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
                 const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
                 const int32_t *wht_slot_sample, const int32_t *wht_slot_out,
                 double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
-                cudaStream_t st, size_t offset, size_t nloc);   // X holds rows [offset, offset+nloc)
+                cudaStream_t st, size_t offset, size_t nloc,    // X holds rows [offset, offset+nloc)
+                const void *dct_plan = nullptr);                // prebuilt tables of the fused DCT form
+// Per-transform tables of the fused DCT-II kernel (twiddles, post factors, the bitmap of needed
+// bins and its ranks): bytes (0 when N is outside the fused form's range) and the build.
+size_t fjlt_dct_plan_bytes(size_t N, size_t S);
+void fjlt_dct_plan_build(size_t N, size_t S, const int32_t *samples, void *buf, cudaStream_t st);
 bool fjlt_shard_ok(int fut, size_t N, size_t offset, size_t nloc);
+void fjlt_set_sm_reserve(int sms);      // SMs the persistent FJLT kernels leave free
 // Host-side layout of the sampled gather of the WHT kernel (see fjlt.cu).
 void fjlt_build_wht_slots(const int32_t *samples, size_t S, std::vector<int32_t> &slot_sample,
                           std::vector<int32_t> &slot_out);

@@ -144,3 +144,147 @@ def apply_distributed_sparse(S, A_local, index_offset=0, group=None):
     ip, ix, vv, (c0, nc) = exchange_sparse_partials(part.indptr, part.indices, part.values, group)
     merged = lib.DeviceCSC(ip, ix, vv, (S.getsketchdim(), nc), "csc")
     return sketch.coalesce(merged), (c0, nc)
+
+
+# ---------------------------------------------------------------------------
+# Overlapped exchange, FJLT in DCT mode on row shards
+# ---------------------------------------------------------------------------
+def _block_edges(extent, blocks, multiple):
+    """Cuts range(extent) in at most `blocks` pieces whose sizes are multiples of `multiple`
+    (the last one takes the remainder, which must itself be a multiple)."""
+    unit = max(1, int(multiple))
+    if extent % unit:
+        raise ValueError("extent %d is not a multiple of %d" % (extent, unit))
+    nunits = extent // unit
+    blocks = max(1, min(int(blocks), nunits))
+    per, rem = divmod(nunits, blocks)
+    edges = [0]
+    for b in range(blocks):
+        edges.append(edges[-1] + (per + (1 if b < rem else 0)) * unit)
+    return edges
+
+
+def apply_distributed_overlapped(S, A_local, SA=None, dim=0, index_offset=0, group=None,
+                                 reduce="allreduce", blocks=4, sm_reserve=16):
+    """apply_distributed with the exchange hidden behind the kernels: the NON-sketched dimension
+    is cut in `blocks` blocks; the sketch of block b+1 runs on the current stream while NCCL
+    reduces block b on its own stream (what SURVEY 2.3 / hash_transform_Elemental.hpp:557-561
+    do in one step at the end).  `sm_reserve` SMs are left free by the persistent FJLT kernels
+    so that the collective's CTAs can be resident next to them.
+
+    Needs device tensors whose blocks are contiguous: column-major operands for dim 0,
+    row-major for dim 1 (anything else falls back to apply_distributed).  With
+    reduce="reduce_scatter" every block is scattered on its own, so a rank ends up owning the
+    r-th 1/world of EVERY block (block-cyclic), returned concatenated in block order."""
+    import torch
+    import torch.distributed as dist
+    dim = S._normdim(dim)
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+    ok = isinstance(A_local, torch.Tensor) and A_local.is_cuda and A_local.dim() == 2 and reduce in (
+        "allreduce", "reduce_scatter")
+    if ok:
+        col_major = A_local.stride(0) == 1 and A_local.shape[0] > 1
+        ok = (dim == 0 and col_major) or (dim == 1 and not col_major and A_local.stride(1) == 1)
+    if not ok or world == 1 or blocks <= 1:
+        return apply_distributed(S, A_local, SA, dim, index_offset, group, reduce)
+    from . import lib
+    s, other = S.getsketchdim(), A_local.shape[1 - dim]
+    if SA is None:
+        SA = (torch.empty(other, s, dtype=A_local.dtype, device=A_local.device).t() if dim == 0
+              else torch.empty(other, s, dtype=A_local.dtype, device=A_local.device))
+    edges = _block_edges(other, blocks, world if reduce == "reduce_scatter" else 1)
+    works, outs = [], []
+    lib.set_option("sm_reserve", int(sm_reserve))
+    try:
+        for b0, b1 in zip(edges, edges[1:]):
+            Ab = A_local[:, b0:b1] if dim == 0 else A_local[b0:b1, :]
+            SAb = SA[:, b0:b1] if dim == 0 else SA[b0:b1, :]
+            S.apply_shard(Ab, SAb, dim, index_offset)
+            slab = SAb.t() if dim == 0 else SAb            # contiguous (b1 - b0) x s
+            if reduce == "allreduce":
+                works.append(dist.all_reduce(slab, op=dist.ReduceOp.SUM, group=group, async_op=True))
+            else:
+                out = torch.empty((slab.shape[0] // world, s), dtype=slab.dtype, device=slab.device)
+                works.append(dist.reduce_scatter_tensor(out, slab, op=dist.ReduceOp.SUM, group=group,
+                                                        async_op=True))
+                outs.append(out)
+    finally:
+        lib.set_option("sm_reserve", 0)
+    for w in works:
+        w.wait()
+    if reduce == "allreduce":
+        return SA
+    res = torch.cat(outs, dim=0)
+    return res.t() if dim == 0 else res
+
+
+def reshard_rows_to_columns(A_local, n_total, group=None):
+    """[VC,*] -> [*,VC] of sketch/FJLT_Elemental.hpp:149-150 as one all-to-all: every rank passes
+    its contiguous block of ROWS (shard_range(n_total, rank, world)) of an n_total x d matrix and
+    receives all rows of its block of COLUMNS (shard_range(d, rank, world)).  Returns the
+    column-major n_total x d_local tensor (a transposed view of contiguous storage) and
+    (first_column, columns)."""
+    import torch
+    import torch.distributed as dist
+    d = A_local.shape[1]
+    if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return A_local, (0, d)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    r0, nloc = shard_range(n_total, rank, world)
+    if A_local.shape[0] != nloc:
+        raise ValueError("rank %d must hold rows [%d, %d) of the matrix" % (rank, r0, r0 + nloc))
+    send = A_local.t().contiguous()                      # (d, nloc): column blocks are row slabs
+    c0, dloc = shard_range(d, rank, world)
+    rows = [shard_range(n_total, q, world)[1] for q in range(world)]
+    cols = [shard_range(d, q, world)[1] for q in range(world)]
+    recv = torch.empty(dloc * n_total, dtype=A_local.dtype, device=A_local.device)
+    dist.all_to_all_single(recv, send.view(-1), output_split_sizes=[dloc * rq for rq in rows],
+                           input_split_sizes=[cq * nloc for cq in cols], group=group)
+    out = torch.empty(dloc, n_total, dtype=A_local.dtype, device=A_local.device)
+    pos = 0
+    for q in range(world):                               # source q sent (dloc, rows[q])
+        off = shard_range(n_total, q, world)[0]
+        out[:, off:off + rows[q]] = recv[pos:pos + dloc * rows[q]].view(dloc, rows[q])
+        pos += dloc * rows[q]
+    return out.t(), (c0, dloc)
+
+
+def gather_columns(SA_local, d_total, group=None):
+    """[*,VC] -> [*,*] (sketch/FJLT_Elemental.hpp:168): every rank holds the s x d_local sketch of
+    its column block (column-major); returns the replicated s x d_total sketch (column-major)."""
+    import torch
+    import torch.distributed as dist
+    if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return SA_local
+    world = dist.get_world_size(group)
+    s = SA_local.shape[0]
+    slab = SA_local.t().contiguous()                     # (d_local, s)
+    cols = [shard_range(d_total, q, world)[1] for q in range(world)]
+    out = torch.empty(d_total, s, dtype=slab.dtype, device=slab.device)
+    if len(set(cols)) == 1:
+        dist.all_gather_into_tensor(out, slab, group=group)
+    else:           # uneven blocks: pad to the widest, gather, drop the padding
+        cmax = max(cols)
+        padded = torch.zeros(cmax, s, dtype=slab.dtype, device=slab.device)
+        padded[:slab.shape[0]] = slab
+        allp = torch.empty(world * cmax, s, dtype=slab.dtype, device=slab.device)
+        dist.all_gather_into_tensor(allp, padded, group=group)
+        pos = 0
+        for q in range(world):
+            out[pos:pos + cols[q]] = allp[q * cmax:q * cmax + cols[q]]
+            pos += cols[q]
+    return out.t()
+
+
+def fjlt_apply_row_sharded(S, A_local, group=None, gather=True):
+    """Columnwise FJLT of a row-sharded matrix the way the reference does it
+    (sketch/FJLT_Elemental.hpp:144-169): re-shard rows -> columns, transform and sample whole
+    columns locally, gather.  Works in both FUT modes (the DCT has no other way to use row
+    shards); in the Walsh-Hadamard mode apply_distributed_overlapped moves s*d instead of n*d.
+    Returns the replicated s x d sketch, or (s x d_local sketch, (first_column, columns)) with
+    gather=False."""
+    A_cols, (c0, dloc) = reshard_rows_to_columns(A_local, S.getindim(), group)
+    SA_loc = S.apply(A_cols, None, 0)
+    if not gather:
+        return SA_loc, (c0, dloc)
+    return gather_columns(SA_loc, A_local.shape[1], group)

@@ -103,3 +103,40 @@ def test_sparse_partials_exchange_world2(tmp_path):
     port = _free_port()
     mp.spawn(_sparse_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert os.path.exists(tmp_path / "ok0") and os.path.exists(tmp_path / "ok1")
+
+
+def _reshard_worker(rank, world, port, out_dir):
+    """FJLT of a row-sharded matrix the reference's way (FJLT_Elemental.hpp:144-169): rows ->
+    columns all-to-all, whole columns transformed locally (here by the oracle: the product has no
+    CPU path), all-gather.  Uneven row and column blocks on purpose."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from libskylark_b200.dist import gather_columns, reshard_rows_to_columns, shard_range, _block_edges
+    from oracle import oracle as o
+    n, d, s = 37, 7, 5
+    A = np.random.default_rng(3).standard_normal((n, d))
+    f = o.FJLT(n, s, o.Context(19))
+    full = f.apply(A, "columnwise")
+    off, cnt = shard_range(n, rank, world)
+    for local in (torch.from_numpy(A[off:off + cnt].copy()),                      # row-major shard
+                  torch.from_numpy(np.ascontiguousarray(A[off:off + cnt].T)).t()):  # column-major shard
+        cols, (c0, dc) = reshard_rows_to_columns(local, n, None)
+        assert (c0, dc) == shard_range(d, rank, world) and tuple(cols.shape) == (n, dc)
+        np.testing.assert_array_equal(cols.numpy(), A[:, c0:c0 + dc])
+        part = f.apply(cols.numpy(), "columnwise")
+        got = gather_columns(torch.from_numpy(np.ascontiguousarray(part.T)).t(), d, None)
+        np.testing.assert_allclose(got.numpy(), full, rtol=1e-13, atol=1e-13)
+    assert _block_edges(24, 4, 2) == [0, 6, 12, 18, 24] and _block_edges(10, 4, 1) == [0, 3, 6, 8, 10]
+    assert _block_edges(6, 8, 2) == [0, 2, 4, 6]
+    with pytest.raises(ValueError):
+        _block_edges(7, 2, 2)
+    dist.barrier()
+    dist.destroy_process_group()
+    open(os.path.join(out_dir, "ok%d" % rank), "w").write("ok")
+
+
+def test_fjlt_rows_to_columns_reshard_world2(tmp_path):
+    port = _free_port()
+    mp.spawn(_reshard_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    assert os.path.exists(tmp_path / "ok0") and os.path.exists(tmp_path / "ok1")
