@@ -90,10 +90,11 @@ def main():
     res, (c0, nc) = sd.apply_distributed_sparse(C, Ad, off2)
     got = scipy.sparse.csc_matrix((res.values.cpu().numpy(), res.indices.cpu().numpy(), res.indptr.cpu().numpy()), shape=(ss, nc))
     w = want[:, c0:c0 + nc].tocsc(); w.sort_indices(); got.sort_indices()
-    same = (got.indptr.tolist() == w.indptr.tolist() and got.indices.tolist() == w.indices.tolist()
-            and np.array_equal(got.data, w.data))
-    checks["CWT sparse exchange bit-identical"] = 0.0 if same else 1.0
-
+    # same stored pattern; values to rounding (every rank adds its own rows first, so a slot's sum
+    # is associated differently from the single left-to-right chain)
+    same = got.indptr.tolist() == w.indptr.tolist() and got.indices.tolist() == w.indices.tolist()
+    checks["CWT sparse exchange: pattern identical"] = 0.0 if same else 1.0
+    checks["CWT sparse exchange: values"] = float(np.linalg.norm(got.data - w.data) / np.linalg.norm(w.data)) if same else 1.0
     bad = {k: v for k, v in checks.items() if not v < 1e-12}
     for k, v in checks.items():
         print("rank %d  %-50s %.3e" % (rank, k, v), flush=True)
