@@ -49,7 +49,9 @@ int sl_create_context(int seed, void *comm_ignored, sl_context_t **ctxt);
 int sl_free_context(sl_context_t *ctxt);
 
 /* capi/sketchc.hpp:21-23, capi/csketch.cpp:379-545.  Variadic tail: CT `double C`;
- * WZT `double p`; GaussianRFT / LaplacianRFT `double sigma`.  Unknown type -> 111. */
+ * WZT `double p`; GaussianRFT / LaplacianRFT `double sigma`; UST `int replace` (the reference has
+ * UST_t, sketch/UST_data.hpp:19-115, but does not register it in its C API: an extension, with
+ * ("UST","Matrix","Matrix") advertised by sl_supported_sketch_transforms).  Unknown type -> 111. */
 int sl_create_sketch_transform(sl_context_t *ctxt, char *type, int n, int s,
                                sl_sketch_transform_t **sketch, ...);
 /* capi/sketchc.hpp:29-30 */
@@ -127,7 +129,7 @@ int sl_set_option(const char *key, const char *value);
 
 /* Generated tables, copied to host memory (tests compare them bit for bit):
  * what = "row_idx" (int64, hash), "row_value" (double, hash), "D" (double, FJLT),
- * "samples" (int64, FJLT), "shifts" (double, RFT), "scales" (double, RFT);
+ * "samples" (int64, FJLT and UST), "shifts" (double, RFT), "scales" (double, RFT);
  * elements [first, first+count). */
 int sl_sketch_export(sl_sketch_transform_t *S, const char *what, int64_t first, int64_t count,
                      void *host_out);

@@ -144,7 +144,7 @@ struct SpOwned {
     ~SpOwned() { release_device(); }
 };
 
-enum TType { T_JLT, T_CT, T_CWT, T_MMT, T_WZT, T_GRFT, T_LRFT, T_FJLT };
+enum TType { T_JLT, T_CT, T_CWT, T_MMT, T_WZT, T_GRFT, T_LRFT, T_FJLT, T_UST };
 
 struct DevState {
     int32_t *bucket = nullptr; double *value = nullptr;
@@ -186,7 +186,7 @@ struct sl_sketch_transform_t {
 static bool str2type(const char *s, TType *t) {   // capi/csketch.cpp:48-67 (sketch subset)
     static const struct { const char *n; TType t; } tab[] = {
         {"JLT", T_JLT}, {"CT", T_CT}, {"CWT", T_CWT}, {"MMT", T_MMT}, {"WZT", T_WZT},
-        {"GaussianRFT", T_GRFT}, {"LaplacianRFT", T_LRFT}, {"FJLT", T_FJLT}};
+        {"GaussianRFT", T_GRFT}, {"LaplacianRFT", T_LRFT}, {"FJLT", T_FJLT}, {"UST", T_UST}};
     for (auto &e : tab) if (strcmp(s, e.n) == 0) { *t = e.t; return true; }
     return false;
 }
@@ -217,6 +217,10 @@ static sl_sketch_transform_t *make_transform(TType type, const char *name, int n
         t->base0 = ctx.allocate(N * S); t->base1 = ctx.allocate(S); break;
     case T_FJLT:                      // FJLT_data.hpp:79-86 + RFUT_data.hpp:27-31 (overlap kept)
         t->base0 = ctx.counter; ctx.allocate(S); break;
+    case T_UST:                       // UST_data.hpp:81-102: param != 0 = with replacement
+        if (param == 0.0 && s > n)
+            throw error(SKB_ERR_INVALID_PARAM, "UST without replacement needs s <= n");
+        t->base0 = ctx.allocate(param != 0.0 ? S : N); break;
     }
     return t.release();
 }
@@ -291,6 +295,57 @@ static void ensure_fjlt_tables(sl_sketch_transform_t *t, DevState &d) {
         }
     } catch (...) { cudaFree(D); cudaFree(samples); cudaFree(Dbits); cudaFree(ss); cudaFree(so); cudaFree(plan); throw; }
     d.samples = samples; d.Dbits = Dbits; d.wht_slot_sample = ss; d.wht_slot_out = so; d.dct_plan = plan; d.D = D;
+}
+
+// UST_data_t::build (sketch/UST_data.hpp:81-102).  With replacement: samples[i] =
+// uniform_int(0, N-1) at stream index base + i.  Without: the inside-out shuffle
+//   for i in [0, N): j = uniform_int<int>(0, i) at stream index base + i; work[i] = work[j]; work[j] = i
+// whose first S entries are the samples -- a sequential recurrence, so it runs on the host once per
+// transform (integer arithmetic only: identical on host and device) and the S indices are copied.
+static void ensure_ust_tables(sl_sketch_transform_t *t, DevState &d) {
+    if (d.samples) return;
+    std::vector<int32_t> smp((size_t)t->S);
+    const uint64_t key = seed_to_key(t->seed);
+    if (t->param != 0.0) {
+        for (int i = 0; i < t->S; i++) {
+            MicroUrng u(key, t->base0 + (uint64_t)i);
+            smp[(size_t)i] = (int32_t)boost_uniform_int(u, (uint64_t)t->N - 1);
+        }
+    } else {
+        std::vector<int32_t> work((size_t)t->N);
+        for (int i = 0; i < t->N; i++) {
+            MicroUrng u(key, t->base0 + (uint64_t)i);
+            const int j = (int)boost_uniform_int(u, (uint64_t)i);
+            work[(size_t)i] = work[(size_t)j];
+            work[(size_t)j] = i;
+        }
+        for (int i = 0; i < t->S; i++) smp[(size_t)i] = work[(size_t)i];
+    }
+    int32_t *samples = nullptr;
+    try {
+        SKB_CUDA(cudaMalloc(&samples, smp.size() * sizeof(int32_t) + 16));
+        SKB_CUDA(cudaMemcpy(samples, smp.data(), smp.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    } catch (...) { cudaFree(samples); throw; }
+    d.samples = samples;
+}
+
+// UST_t::apply (sketch/UST_Elemental.hpp: sa[j*ldsa + i] = a[j*lda + samples[i]] columnwise,
+// sa[j*ldsa + i] = a[samples[j]*lda + i] rowwise).  X holds sketched indices [offset, offset+nloc);
+// samples outside that range give zeros, so the partial results of a partition add up.
+// layout_rows: X[k*ldx + j], OUT[i*ldo + j]  (contiguous rows are copied whole);
+// otherwise:   X[k + j*ldx], OUT[i + j*ldo].
+__global__ void k_ust_gather(const double *__restrict__ X, size_t ldx, size_t m, const int32_t *__restrict__ samples,
+                             size_t S, int64_t offset, int64_t nloc, double *__restrict__ OUT, size_t ldo,
+                             int layout_rows) {
+    const size_t total = S * m;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        size_t i, j;
+        if (layout_rows) { i = t / m; j = t - i * m; } else { j = t / S; i = t - j * S; }
+        const int64_t k = (int64_t)samples[i] - offset;
+        const bool in = k >= 0 && k < nloc;
+        const double v = in ? (layout_rows ? X[(size_t)k * ldx + j] : X[(size_t)k + j * ldx]) : 0.0;
+        if (layout_rows) OUT[i * ldo + j] = v; else OUT[i + j * ldo] = v;
+    }
 }
 
 static DenseParams dense_params(const sl_sketch_transform_t *t) {
@@ -410,7 +465,7 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
         throw error(SKB_ERR_INVALID_USAGE, "apply: accumulation is implemented for JLT/CT only");
     if (A->kind == MK_SPARSE) {
         if (t->is_dense() || t->is_rft()) { apply_dense_on_sparse(t, A, SA, dim, offset, shard); return; }
-        if (!t->is_hash()) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: FJLT takes dense operands only");
+        if (!t->is_hash()) throw error(SKB_ERR_UNSUPPORTED_BASE, "apply: FJLT and UST take dense operands only");
         ensure_hash_tables(t, d);
         const int32_t *b = d.bucket + offset; const double *v = d.value + offset;
         if (colwise)
@@ -459,6 +514,19 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
         ensure_ws(d, need);
         dense_apply(p, layout_rows, f32, A->data, (size_t)A->ld, (size_t)other, (size_t)offset,
                     (size_t)sk, SA->data, (size_t)SA->ld, epi, d.ws, d.ws_bytes, st, accumulate);
+        return;
+    }
+    if (t->type == T_UST) {
+        ensure_ust_tables(t, d);
+        const size_t total = (size_t)t->S * (size_t)other;
+        if (total == 0) return;
+        size_t blocks = (total + 255) / 256;
+        if (blocks > (size_t)148 * 32) blocks = (size_t)148 * 32;
+        LaunchScope ls(KC_MISC, st);
+        k_ust_gather<<<(unsigned)blocks, 256, 0, st>>>((const double *)A->data, (size_t)A->ld, (size_t)other, d.samples,
+                                                       (size_t)t->S, offset, sk, (double *)SA->data, (size_t)SA->ld,
+                                                       layout_rows ? 1 : 0);
+        SKB_CUDA(cudaGetLastError());
         return;
     }
     // FJLT.  Row shards are possible in the Walsh-Hadamard mode only (H_N = H_P (x) H_{N/P}:
@@ -744,7 +812,7 @@ char *sl_supported_sketch_transforms(void) {
     static char s[] =
         "(\"JLT\",\"Matrix\",\"Matrix\") (\"JLT\",\"SparseMatrix\",\"Matrix\") "
         "(\"CT\",\"Matrix\",\"Matrix\") (\"CT\",\"SparseMatrix\",\"Matrix\") "
-        "(\"FJLT\",\"Matrix\",\"Matrix\") "
+        "(\"FJLT\",\"Matrix\",\"Matrix\") (\"UST\",\"Matrix\",\"Matrix\") "
         "(\"CWT\",\"Matrix\",\"Matrix\") (\"CWT\",\"SparseMatrix\",\"Matrix\") "
         "(\"CWT\",\"SparseMatrix\",\"SparseMatrix\") "
         "(\"MMT\",\"Matrix\",\"Matrix\") (\"MMT\",\"SparseMatrix\",\"Matrix\") "
@@ -794,6 +862,11 @@ int sl_create_sketch_transform(sl_context_t *ctxt, char *type_, int n, int s,
         va_start(argp, sketch);
         p1 = va_arg(argp, double);
         va_end(argp);
+    } else if (type == T_UST) {       // `int replace` (UST_data_t::params_t, sketch/UST_data.hpp:27-33)
+        va_list argp;
+        va_start(argp, sketch);
+        p1 = va_arg(argp, int) ? 1.0 : 0.0;
+        va_end(argp);
     }
     SL_TRY
     if (!ctxt) throw error(SKB_ERR_INVALID_PARAM, "null context");
@@ -808,6 +881,7 @@ int sl_serialize_sketch_transform(const sl_sketch_transform_t *t, char **data) {
     if (t->type == T_CT) { snprintf(buf, sizeof buf, ",\n    \"C\": \"%.17g\"", t->param); extra = buf; }
     if (t->type == T_WZT) { snprintf(buf, sizeof buf, ",\n    \"P\": \"%.17g\"", t->param); extra = buf; }
     if (t->is_rft()) { snprintf(buf, sizeof buf, ",\n    \"sigma\": \"%.17g\"", t->param); extra = buf; }
+    if (t->type == T_UST) extra = std::string(",\n    \"replace\": \"") + (t->param != 0.0 ? "true" : "false") + "\"";
     snprintf(buf, sizeof buf,
              "{\n    \"skylark_object_type\": \"sketch\",\n    \"sketch_type\": \"%s\",\n"
              "    \"skylark_version\": \"0.20\",\n    \"N\": \"%d\",\n    \"S\": \"%d\",\n"
@@ -839,6 +913,7 @@ int sl_deserialize_sketch_transform(const char *data, sl_sketch_transform_t **sk
     if (type == T_CT) p1 = strtod(json_get(kv, "C").c_str(), nullptr);
     if (type == T_WZT) p1 = strtod(json_get(kv, "P").c_str(), nullptr);
     if (type == T_GRFT || type == T_LRFT) p1 = strtod(json_get(kv, "sigma").c_str(), nullptr);
+    if (type == T_UST) { const std::string &r = json_get(kv, "replace"); p1 = (r == "true" || r == "1") ? 1.0 : 0.0; }
     *sketch = make_transform(type, name.c_str(), n, s, p1, ctx);   // replays the RNG (CWT_data.hpp:48-52)
     SL_CATCH
 }
@@ -988,6 +1063,7 @@ int sl_sketch_export(sl_sketch_transform_t *t, const char *what, int64_t first, 
     else if (strcmp(what, "row_value") == 0 && t->is_hash()) { ensure_hash_tables(t, d); copy_f64(d.value, t->N); }
     else if (strcmp(what, "D") == 0 && t->type == T_FJLT) { ensure_fjlt_tables(t, d); copy_f64(d.D, t->N); }
     else if (strcmp(what, "samples") == 0 && t->type == T_FJLT) { ensure_fjlt_tables(t, d); copy_i32_as_i64(d.samples, t->S); }
+    else if (strcmp(what, "samples") == 0 && t->type == T_UST) { ensure_ust_tables(t, d); copy_i32_as_i64(d.samples, t->S); }
     else if (strcmp(what, "shifts") == 0 && t->is_rft()) { ensure_rft_tables(t, d); copy_f64(d.shifts, t->S); }
     else if (strcmp(what, "scales") == 0 && t->is_rft()) { ensure_rft_tables(t, d); copy_f64(d.scales, t->S); }
     else throw error(SKB_ERR_INVALID_PARAM, std::string("sl_sketch_export: no table '") + what + "' for " + t->name);

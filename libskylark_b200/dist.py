@@ -165,7 +165,7 @@ def _block_edges(extent, blocks, multiple):
 
 
 def apply_distributed_overlapped(S, A_local, SA=None, dim=0, index_offset=0, group=None,
-                                 reduce="allreduce", blocks=4, sm_reserve=16):
+                                 reduce="allreduce", blocks=4, sm_reserve=8):
     """apply_distributed with the exchange hidden behind the kernels: the NON-sketched dimension
     is cut in `blocks` blocks; the sketch of block b+1 runs on the current stream while NCCL
     reduces block b on its own stream (what SURVEY 2.3 / hash_transform_Elemental.hpp:557-561
@@ -192,7 +192,21 @@ def apply_distributed_overlapped(S, A_local, SA=None, dim=0, index_offset=0, gro
     if SA is None:
         SA = (torch.empty(other, s, dtype=A_local.dtype, device=A_local.device).t() if dim == 0
               else torch.empty(other, s, dtype=A_local.dtype, device=A_local.device))
-    edges = _block_edges(other, blocks, world if reduce == "reduce_scatter" else 1)
+    # the persistent FJLT kernels take one column per CTA and round: blocks that are whole rounds of
+    # the CTAs left after the reservation lose nothing to a ragged last round
+    unit = world if reduce == "reduce_scatter" else 1
+    ctas = 148 - int(sm_reserve)
+    if other % unit == 0 and other >= 2 * ctas:
+        rounds = -(-other // ctas)                       # ceil
+        per = max(1, rounds // blocks)
+        step = per * ctas // unit * unit
+        if step > 0 and other - (blocks - 1) * step >= step:
+            first = other - (blocks - 1) * step          # the ragged (largest) block goes first:
+            edges = [0] + [first + b * step for b in range(blocks)]   # the last reduction is a short one
+        else:
+            edges = _block_edges(other, blocks, unit)
+    else:
+        edges = _block_edges(other, blocks, unit)
     works, outs = [], []
     lib.set_option("sm_reserve", int(sm_reserve))
     try:

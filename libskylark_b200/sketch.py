@@ -89,7 +89,8 @@ class _SketchTransform(object):
             sketch_transform = c_void_p()
             ctx = lib.ctxt_obj if context is None else context._obj
             lib.callsl("sl_create_sketch_transform", ctx, ttype, int(n), int(s),
-                       byref(sketch_transform), *[c_double(float(p)) for p in params])
+                       byref(sketch_transform),
+                       *[ctypes.c_int(int(p)) if isinstance(p, bool) else c_double(float(p)) for p in params])
         self._obj = sketch_transform
 
     def _baseinit(self, ttype, n, s, defouttype, forceppy):
@@ -279,6 +280,20 @@ class FJLT(_SketchTransform):
         return self._export("samples", self._s, numpy.int64)
 
 
+class UST(_SketchTransform):
+    """Uniform sampling transform: SA = A[samples, :] (columnwise) with `s` indices drawn uniformly
+    from range(n), with or without replacement (sketch/UST_data.hpp:81-102, UST_Elemental.hpp).
+    The reference's Python layer only has the numpy-random `URST`; this is its C++ UST_t, whose
+    samples come from the context's counter stream."""
+
+    def __init__(self, n, s, replace=True, defouttype=None, forceppy=False, sketch_transform=None, context=None):
+        self._replace = bool(replace)
+        super().__init__("UST", n, s, defouttype, forceppy, sketch_transform, context, params=(bool(replace),))
+
+    def samples(self):
+        return self._export("samples", self._s, numpy.int64)
+
+
 class _HashTransform(_SketchTransform):
     def row_idx(self):
         return self._export("row_idx", self._n, numpy.int64)
@@ -358,7 +373,7 @@ FastMaternRFT = _outside_hot_path("FastMaternRFT", "sketch.py:743-772")
 ExpSemigroupRLT = _outside_hot_path("ExpSemigroupRLT", "sketch.py:774-800")
 ExpSemigroupQRLT = _outside_hot_path("ExpSemigroupQRLT", "sketch.py:802-827")
 PPT = _outside_hot_path("PPT", "sketch.py:829-881")
-URST = _outside_hot_path("URST", "sketch.py:883-904, pure Python in the reference")
+URST = UST      # sketch.py:883-904 is a numpy.random sampler; here it is the C++ UST_t
 NURST = _outside_hot_path("NURST", "sketch.py:906-931, pure Python in the reference")
 
 # Additional names (sketch.py:962-970); FastJLT = JLT is the reference's own aliasing.
@@ -377,6 +392,7 @@ _map_csketch_type_to_cfun = {
     "JLT": lambda sd, obj: JLT(int(sd["N"]), int(sd["S"]), None, False, obj),
     "CT": lambda sd, obj: CT(int(sd["N"]), int(sd["S"]), float(sd["C"]), None, False, obj),
     "FJLT": lambda sd, obj: FJLT(int(sd["N"]), int(sd["S"]), None, False, obj),
+    "UST": lambda sd, obj: UST(int(sd["N"]), int(sd["S"]), str(sd["replace"]) in ("true", "1", "True"), None, False, obj),
     "CWT": lambda sd, obj: CWT(int(sd["N"]), int(sd["S"]), None, False, obj),
     "MMT": lambda sd, obj: MMT(int(sd["N"]), int(sd["S"]), None, False, obj),
     "WZT": lambda sd, obj: WZT(int(sd["N"]), int(sd["S"]), float(sd["P"]), None, False, obj),

@@ -457,3 +457,29 @@ class FJLT(_Transform):
             TA = wht((scale * self.D)[:, None] * A)
         out = math.sqrt(float(N) / float(self.S))
         return out * TA[self.samples.astype(np.int64), :]
+
+
+class UST(_Transform):
+    """sketch/UST_data.hpp:81-102 (samples) and sketch/UST_Elemental.hpp (apply): uniform row /
+    column sampling, with replacement (S draws of uniform_int(0, N-1)) or without (inside-out
+    shuffle over N single draws uniform_int<int>(0, i), first S entries)."""
+    sketch_type = "UST"
+
+    def __init__(self, N, S, replace, context):
+        super().__init__(N, S, context)
+        self.replace = bool(replace)
+        seed = context.seed
+        if self.replace:
+            self.base = context.allocate(S)
+            self.samples = uniform_int(seed, self.base, S, N - 1).astype(np.int64)
+        else:
+            self.base = context.allocate(N)
+            self.samples = np.empty(S, dtype=np.int64)
+            lib().sko_ust_noreplace(_int(seed), _u64(self.base), _sz(N), _sz(S), _p(self.samples))
+
+    def _extra(self):
+        return {"replace": "true" if self.replace else "false"}
+
+    def apply(self, A, dim="columnwise"):
+        A = np.asarray(A)
+        return A[self.samples, :] if dim in (0, "columnwise") else A[:, self.samples]

@@ -287,6 +287,22 @@ void sko_uniform_real(int seed, uint64_t base, size_t count, double a, double b,
     }
 }
 
+/* UST_data_t::build without replacement (sketch/UST_data.hpp:89-98): inside-out shuffle,
+ * i-th draw = context.random_value(uniform_int_distribution<int>(0, i)) at stream index base + i
+ * (base/context.hpp:131-136); the first S entries of the shuffled range are the samples. */
+void sko_ust_noreplace(int seed, uint64_t base, size_t N, size_t S, int64_t *out) {
+    int64_t *work = (int64_t *)malloc((N ? N : 1) * sizeof(int64_t));
+    for (size_t i = 0; i < N; i++) {
+        urng_t u;
+        urng_init(&u, seed, base + i);
+        size_t j = (size_t)boost_uniform_int(&u, (uint64_t)i);
+        work[i] = work[j];
+        work[j] = (int64_t)i;
+    }
+    for (size_t i = 0; i < S; i++) out[i] = work[i];
+    free(work);
+}
+
 /* context_t::random_int via random_array_t (base/randgen.hpp:171-187) */
 int sko_random_int(int seed, uint64_t base) {
     urng_t u;

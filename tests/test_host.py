@@ -102,9 +102,25 @@ def test_error_codes(sk):
 def test_reference_names_outside_the_path_fail_clearly(sk):
     from libskylark_b200 import errors
     for name in ("SJLT", "SparseJLT", "PPT", "TensorSketch", "FastGaussianRFT", "Fastfood", "MaternRFT",
-                 "URST", "UniformSampler", "NURST", "GaussianQRFT", "ExpSemigroupRLT"):
+                 "NURST", "GaussianQRFT", "ExpSemigroupRLT"):
         with pytest.raises(errors.UnsupportedError, match="outside the GPU sketch-apply path"):
             getattr(sk, name)(10, 5)
+
+
+def test_ust_counters_and_json_on_the_host(sk):
+    # UST_data.hpp:81-102 / SURVEY App. B: c+S with replacement, c+N without (no device needed
+    # until the samples are asked for)
+    from libskylark_b200 import lib
+    c = lib.Context(9, 100)
+    u = sk.UST(50, 7, True, context=c)
+    assert c.counter == 107 and sk.URST is sk.UST and sk.UniformSampler is sk.UST
+    v = sk.UST(50, 7, False, context=c)
+    assert c.counter == 157
+    d = v.serialize()
+    assert d["sketch_type"] == "UST" and d["replace"] == "false" and d["creation_context"]["counter"] == "107"
+    assert u.serialize()["replace"] == "true"
+    w = sk.deserialize_sketch(d)
+    assert w.serialize() == d
 
 
 def test_adapter_checks(sk):
