@@ -726,22 +726,26 @@ __global__ void k_dct_post(DctPlan pl, const cplx *__restrict__ H, const int32_t
 // the rings hold lag + 2 columns of H and lag + 14 columns of kept bins.  lag is chosen per launch so
 // that a dependency is at least one full round of resident CTAs old when it is needed.
 static constexpr int DCT_POST_CHUNK = 1024;                      // samples per post item
-constexpr size_t FFT_SMEM2 = (FFT_POINTS + (FFT_POINTS >> 4) + 64) * sizeof(cplx);
+constexpr int FFT_PPT_LOG = FFT_PPT == 16 ? 4 : 3;
+static_assert(FFT_PPT == 16 || FFT_PPT == 8, "fused DCT: 16 or 8 points per thread");
+constexpr size_t FFT_SMEM2 = (FFT_POINTS + (FFT_POINTS >> FFT_PPT_LOG) + 64) * sizeof(cplx);
 // Shared-memory twiddle tables of the fused kernel, filled once per (persistent) CTA -- every
 // dependency wait ends in a fence that drops the L1, so tables read through L1 would miss on every
 // tile.  Per pass kind a compact table of 16 + 256 butterfly twiddles; the inter-pass factors
 // W_N'^e = Thi[e >> 10] * Tlo[e & 1023] when both tables fit (N <= 2^21).
-constexpr int TW_COMPACT = 16 + 256, TT_SMEM_MAX = 2048;
+constexpr int TW_COMPACT = FFT_PPT == 16 ? 16 + 256 : 8 + 64 + 512;
+constexpr int TT_SMEM_MAX = FFT_PPT == 16 ? 2048 : 0;     // with 8 points per thread the buffers take the room
 constexpr size_t FFT_SMEM2_TW = 2 * TW_COMPACT * sizeof(cplx);
-// W: table of W_L^m, m < L.  tw[k] = W_L^(k L / 256), k < 16 (middle pass, L >= 512);
-// tw[16 + j] = W_L^j, j < L / R_last (last pass)
+// W: table of W_L^m, m < L.  One region per twiddled pass, in pass order: a middle pass with
+// sub-length Ns holds W_L^(k L / (Ns R)), k < Ns (R = FFT_PPT); the last pass W_L^j, j < L / R_last.
 __device__ __forceinline__ void fused_twiddles(cplx *tw, const cplx *__restrict__ W, int L) {
-    int Ns = 16;
-    if (L / Ns > 16) {
-        if (threadIdx.x < 16) tw[threadIdx.x] = ldg_cplx(W + (int)threadIdx.x * (L >> 8));
-        Ns = 256;
+    int Ns = FFT_PPT, off = 0;
+    while (L / Ns > FFT_PPT) {
+        const int step = L / (Ns * FFT_PPT);
+        for (int k = threadIdx.x; k < Ns; k += blockDim.x) tw[off + k] = ldg_cplx(W + k * step);
+        off += Ns; Ns *= FFT_PPT;
     }
-    for (int j = threadIdx.x; j < Ns; j += blockDim.x) tw[16 + j] = ldg_cplx(W + j);
+    for (int j = threadIdx.x; j < Ns; j += blockDim.x) tw[off + j] = ldg_cplx(W + j);
 }
 
 struct DctFused {
@@ -816,11 +820,11 @@ __device__ __forceinline__ double2 ldg_stream2_hint(const double *p, uint64_t po
     return v;
 }
 
-// shared-memory index of point i: a spare element after every 16; then either one per 256 (rows
+// shared-memory index of point i: a spare element after every FFT_PPT; then either one per 256 (rows
 // walked with the position varying across lanes) or one per sequence (pass 1, whose last pass
 // walks the SEQUENCE index across lanes)
 template <bool SEQPAD> __device__ __forceinline__ int padx(int i, int lshift) {
-    return i + (i >> 4) + (SEQPAD ? (i >> lshift) : (i >> 8));
+    return i + (i >> FFT_PPT_LOG) + (SEQPAD ? (i >> lshift) : (FFT_PPT == 16 ? (i >> 8) : 0));
 }
 
 // twiddles of one radix-R butterfly of a pass with sub-length Ns: powers of W_L^(k * step)
@@ -885,9 +889,8 @@ __device__ __forceinline__ void fft_tail(cplx *buf, int L, int lshift, const cpl
     // after the first radix-16 pass (Ns = 16): at most one middle radix-16 pass (L >= 512), then the
     // last pass.  W is the compact shared-memory table of fused_twiddles(): 16 entries for the
     // middle pass, then the last pass's.
-    int Ns = 16;
-    if (L / Ns > 16) { mid_pass<16, SEQPAD>(buf, L, lshift, Ns, W); Ns *= 16; }
-    W += 16;
+    int Ns = FFT_PPT;
+    while (L / Ns > FFT_PPT) { mid_pass<FFT_PPT, SEQPAD>(buf, L, lshift, Ns, W); W += Ns; Ns *= FFT_PPT; }
     // the ring slot the last pass stores into must have been released by its previous user: checked
     // here, at the latest possible point, where it has long been the case
     if (slot_free) {         // write-after-read: ordered by the control dependency and the barrier, no fence
@@ -896,7 +899,7 @@ __device__ __forceinline__ void fft_tail(cplx *buf, int L, int lshift, const cpl
         __syncthreads();
     }
     const int rem = L / Ns;
-    if (rem == 16) last_pass<16, SEQPAD, GFAST>(buf, L, lshift, W, sink);
+    if (FFT_PPT == 16 && rem == 16) last_pass<FFT_PPT, SEQPAD, GFAST>(buf, L, lshift, W, sink);
     else if (rem == 8) last_pass<8, SEQPAD, GFAST>(buf, L, lshift, W, sink);
     else if (rem == 4) last_pass<4, SEQPAD, GFAST>(buf, L, lshift, W, sink);
     else last_pass<2, SEQPAD, GFAST>(buf, L, lshift, W, sink);
@@ -946,16 +949,16 @@ __device__ __forceinline__ void dct_tile_pass1(const DctFused &a, cplx *buf, siz
         }
     }
     __syncthreads();
-    {   // first radix-16 pass (Ns = 1), in place
-        const int per = N2 >> 4, pshift = 31 - __clz(per);
+    {   // first pass (radix FFT_PPT, Ns = 1), in place
+        const int per = N2 >> FFT_PPT_LOG, pshift = 31 - __clz(per);
         const int u = (int)threadIdx.x, g = u >> pshift, j = u & (per - 1);
-        cplx v[16];
+        cplx v[FFT_PPT];
 #pragma unroll
-        for (int t = 0; t < 16; t++) v[t] = buf[padx<true>(g * N2 + j + t * per, lshift)];
+        for (int t = 0; t < FFT_PPT; t++) v[t] = buf[padx<true>(g * N2 + j + t * per, lshift)];
         __syncthreads();
-        butterfly<16>(v);
+        butterfly<FFT_PPT>(v);
 #pragma unroll
-        for (int q = 0; q < 16; q++) buf[padx<true>(g * N2 + j * 16 + q, lshift)] = v[q];
+        for (int q = 0; q < FFT_PPT; q++) buf[padx<true>(g * N2 + j * FFT_PPT + q, lshift)] = v[q];
         __syncthreads();
     }
     const size_t lo_mask = ((size_t)1 << pl.lo_bits) - 1;
@@ -991,15 +994,15 @@ __device__ __forceinline__ void dct_tile_pass2(const DctFused &a, cplx *buf, siz
         s_need[threadIdx.x] = __ldg(pl.need + (base >> 5) + threadIdx.x);
         s_rank[threadIdx.x] = __ldg(pl.rank + (base >> 5) + threadIdx.x);
     }
-    {   // first radix-16 pass straight from global memory (rows are contiguous)
-        const int per = L >> 4, pshift = 31 - __clz(per);
+    {   // first pass (radix FFT_PPT) straight from global memory (rows are contiguous)
+        const int per = L >> FFT_PPT_LOG, pshift = 31 - __clz(per);
         const int u = (int)threadIdx.x, g = u >> pshift, j = u & (per - 1);
-        cplx v[16];
+        cplx v[FFT_PPT];
 #pragma unroll
-        for (int t = 0; t < 16; t++) v[t] = ldcg_cplx_hint(rows + g * L + j + t * per, pol_last);
-        butterfly<16>(v);
+        for (int t = 0; t < FFT_PPT; t++) v[t] = ldcg_cplx_hint(rows + g * L + j + t * per, pol_last);
+        butterfly<FFT_PPT>(v);
 #pragma unroll
-        for (int q = 0; q < 16; q++) buf[padx<false>(g * L + j * 16 + q, lshift)] = v[q];
+        for (int q = 0; q < FFT_PPT; q++) buf[padx<false>(g * L + j * FFT_PPT + q, lshift)] = v[q];
         __syncthreads();
     }
     cplx *zc = a.Zc + (c % a.nz) * pl.zc_ld;
