@@ -352,7 +352,32 @@ def other_configs(torch, lib, sketch, hbm_gbs, fp64_peak):
                 "ms": ms, "value": tf, "unit": "TFLOP/s", "frac_of_3xtf32_tcgen05_peak": tf / tf32_eff_peak,
                 "ratio_to_measured_fp64_gemm": tf / fp64_peak}
 
+    def c1_host():
+        # the reference's own calling convention: numpy operands through sl_apply_sketch_transform,
+        # host <-> device copies inside the call (pageable host memory, staging from the pool)
+        import numpy as np
+        n, d, s = 100_000, 500, 2000
+        A = np.random.default_rng(DATA_SEED).standard_normal((n, d))
+        SA = np.empty((s, d))
+        S = sketch.CWT(n, s, lib.Context(SKETCH_SEED))
+        S.apply(A, SA, "columnwise")
+        ts = []
+        for _ in range(5):
+            t0 = time.perf_counter(); S.apply(A, SA, "columnwise"); ts.append(time.perf_counter() - t0)
+        ms = statistics.median(ts) * 1e3
+        At = torch.from_numpy(A)
+        dA = torch.empty_like(At, device=dev)
+        cs = []
+        for _ in range(5):
+            torch.cuda.synchronize(); t0 = time.perf_counter(); dA.copy_(At); torch.cuda.synchronize()
+            cs.append(time.perf_counter() - t0)
+        copy_ms = statistics.median(cs) * 1e3
+        return {"workload": "C1 end to end on HOST numpy operands (400 MB in, 8 MB out) through sl_apply_sketch_transform",
+                "ms": ms, "h2d_copy_alone_ms": copy_ms, "ratio_to_copy": ms / copy_ms,
+                "value": (n * d * 8 + s * d * 8) / (ms * 1e-3) / 1e9, "unit": "GB/s"}
+
     guarded("c1_cwt_rowmajor", lambda: c1("C"))
+    guarded("c1_cwt_host_operands", c1_host)
     guarded("c1_cwt_colmajor", lambda: c1("F"))
     guarded("c3_fjlt_wht", lambda: c3("wht", 2048))
     guarded("c3_fjlt_dct", lambda: c3("dct", 2048))

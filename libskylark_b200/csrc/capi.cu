@@ -700,43 +700,50 @@ static void apply_any(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA,
         apply_host_dense_pipelined(t, A, SA, dim, offset, shard, device);
         return;
     }
+    // Staging buffers come from a grow-only pool per device: a host-operand apply costs its copies
+    // and its kernels, not four cudaMalloc / cudaFree round trips (each a device synchronisation).
     sl_matrix_t dA = *A, dSA = *SA;
     dA.on_device = dSA.on_device = true; dA.device = dSA.device = device;
-    void *bufs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    struct Slot { void *p = nullptr; size_t cap = 0; };
+    static Slot pool[64][4];
+    if (device < 0 || device >= 64) throw error(SKB_ERR_GENERIC, "device index out of range");
+    auto stage = [&](int slot, size_t bytes) -> void * {
+        Slot &sl = pool[device][slot];
+        if (sl.cap < bytes || !sl.p) {
+            SKB_CUDA(cudaStreamSynchronize(st));
+            cudaFree(sl.p); sl.p = nullptr; sl.cap = 0;
+            const size_t want = bytes + bytes / 8 + 256;       // some headroom for the next, slightly larger call
+            SKB_CUDA(cudaMalloc(&sl.p, want));
+            sl.cap = want;
+        }
+        return sl.p;
+    };
     try {
         const size_t esz = A->dtype == SL_DTYPE_F32 ? 4 : 8;
         if (A->kind == MK_DENSE) {
             size_t bytes = (size_t)A->ld * (size_t)A->n * esz;
-            SKB_CUDA(cudaMalloc(&bufs[0], bytes ? bytes : 16));
-            SKB_CUDA(cudaMemcpyAsync(bufs[0], A->data, bytes, cudaMemcpyHostToDevice, st));
-            dA.data = bufs[0];
+            dA.data = stage(0, bytes);
+            SKB_CUDA(cudaMemcpyAsync(dA.data, A->data, bytes, cudaMemcpyHostToDevice, st));
         } else {
             size_t pb = (size_t)(A->n + 1) * 4, ib = (size_t)A->nnz * 4, vb = (size_t)A->nnz * 8;
-            SKB_CUDA(cudaMalloc(&bufs[0], pb));
-            SKB_CUDA(cudaMalloc(&bufs[1], ib ? ib : 16));
-            SKB_CUDA(cudaMalloc(&bufs[2], vb ? vb : 16));
-            SKB_CUDA(cudaMemcpyAsync(bufs[0], A->indptr, pb, cudaMemcpyHostToDevice, st));
-            SKB_CUDA(cudaMemcpyAsync(bufs[1], A->indices, ib, cudaMemcpyHostToDevice, st));
-            SKB_CUDA(cudaMemcpyAsync(bufs[2], A->values, vb, cudaMemcpyHostToDevice, st));
-            dA.indptr = (int32_t *)bufs[0]; dA.indices = (int32_t *)bufs[1]; dA.values = (double *)bufs[2];
+            dA.indptr = (int32_t *)stage(0, pb); dA.indices = (int32_t *)stage(1, ib); dA.values = (double *)stage(2, vb);
+            SKB_CUDA(cudaMemcpyAsync(dA.indptr, A->indptr, pb, cudaMemcpyHostToDevice, st));
+            SKB_CUDA(cudaMemcpyAsync(dA.indices, A->indices, ib, cudaMemcpyHostToDevice, st));
+            SKB_CUDA(cudaMemcpyAsync(dA.values, A->values, vb, cudaMemcpyHostToDevice, st));
         }
         if (SA->kind == MK_SPARSE) {
             apply_sparse_out(t, &dA, SA, dim, offset, shard, device);
-            for (void *b : bufs) cudaFree(b);
             return;
         }
         size_t obytes = (size_t)SA->ld * (size_t)SA->n * (SA->dtype == SL_DTYPE_F32 ? 4 : 8);
-        SKB_CUDA(cudaMalloc(&bufs[3], obytes ? obytes : 16));
-        dSA.data = bufs[3];
+        dSA.data = stage(3, obytes);
         apply_device(t, &dA, &dSA, dim, offset, shard, false);
-        SKB_CUDA(cudaMemcpyAsync(SA->data, bufs[3], obytes, cudaMemcpyDeviceToHost, st));
+        SKB_CUDA(cudaMemcpyAsync(SA->data, dSA.data, obytes, cudaMemcpyDeviceToHost, st));
         SKB_CUDA(cudaStreamSynchronize(st));
     } catch (...) {
         cudaStreamSynchronize(st);
-        for (void *b : bufs) cudaFree(b);
         throw;
     }
-    for (void *b : bufs) cudaFree(b);
 }
 
 // ---------------------------------------------------------------------------

@@ -1290,15 +1290,27 @@ static size_t dct_sel_bytes(size_t N, size_t S, size_t B) {     // need bitmap, 
 
 static bool wht_fast_ok(size_t N) { return N >= (size_t)WSEG && (N & (N - 1)) == 0 && N <= ((size_t)1 << 28); }
 
+// Rows layout (every sketched index owns a contiguous row, e.g. a row-major n x d array sketched
+// columnwise): the column kernels are fed through a transposed copy of a BLOCK of columns at a
+// time (the reference also transposes for this direction, RFUT_Elemental.hpp:74-90), so the scratch
+// is bounded (<= 4 GiB) instead of a second copy of the operand.
+static size_t rows_block_cols(size_t rows, size_t m) {
+    size_t cb = ((size_t)4 << 30) / (rows * sizeof(double));
+    if (cb > 592) cb = 592;          // four rounds of the persistent kernels' CTAs
+    if (cb < 1) cb = 1;
+    return cb < m ? cb : m;
+}
 size_t fjlt_workspace_bytes(size_t N, size_t m, int fut, bool layout_rows, size_t S) {
+    const size_t mb = layout_rows ? rows_block_cols(N, m) : m;      // columns in flight
+    const size_t tr = layout_rows ? align256(N * mb * sizeof(double)) : 0;
     if (fut == FUT_DCT && dct_fused_ok(N) && !dct_legacy_forced())
-        return (layout_rows ? align256(N * m * sizeof(double)) : 0) + dct_fused_ws_bytes(N, m, S) + 1024;
+        return tr + dct_fused_ws_bytes(N, mb, S) + 1024;
     if (fut == FUT_DCT && dct_fast_ok(N))
-        return (layout_rows ? N * m * sizeof(double) : 0) + dct_batch_cols(N, m) * N * sizeof(double) +
-               dct_table_bytes(N, S) + dct_sel_bytes(N, S, dct_batch_cols(N, m)) + 1024;
+        return tr + dct_batch_cols(N, mb) * N * sizeof(double) +
+               dct_table_bytes(N, S) + dct_sel_bytes(N, S, dct_batch_cols(N, mb)) + 1024;
     if (fut == FUT_DCT) return 4 * N * sizeof(double) + 256;
-    if (fut == FUT_WHT && wht_fast_ok(N))         // sign words (+ transposed copy)
-        return (layout_rows ? (N * m * sizeof(double) + 255) / 256 * 256 : 0) + N / 8 + 256;
+    if (fut == FUT_WHT && wht_fast_ok(N))         // sign words (+ transposed block)
+        return tr + N / 8 + 256;
     return 256;
 }
 
@@ -1307,11 +1319,51 @@ bool fjlt_shard_ok(int fut, size_t N, size_t offset, size_t nloc) {
            offset % WSEG == 0 && nloc % WSEG == 0 && nloc > 0;
 }
 
+static void fjlt_apply_impl(int fut, bool layout_rows, const double *X, size_t ldx, size_t N, size_t m,
+                            const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
+                            const int32_t *wht_slot_sample, const int32_t *wht_slot_out,
+                            double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
+                            cudaStream_t st, size_t offset, size_t nloc, const void *dct_plan,
+                            bool out_rows);
+
 void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N, size_t m,
                 const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
                 const int32_t *wht_slot_sample, const int32_t *wht_slot_out,
                 double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
                 cudaStream_t st, size_t offset, size_t nloc, const void *dct_plan) {
+    if (S == 0 || m == 0) return;
+    if (workspace_bytes < fjlt_workspace_bytes(N, m, fut, layout_rows, S))
+        throw error(SKB_ERR_ALLOC, "fjlt apply: workspace too small");
+    const bool fast = (fut == FUT_DCT && dct_fast_ok(N)) || (fut == FUT_WHT && wht_fast_ok(N));
+    if (layout_rows && fast) {
+        // block of columns -> contiguous columns in scratch -> column kernel writing rows-layout output
+        const size_t rows = fut == FUT_WHT ? nloc : N, cb = rows_block_cols(N, m);
+        double *T = reinterpret_cast<double *>(workspace);
+        char *rest = reinterpret_cast<char *>(workspace) + align256(N * cb * sizeof(double));
+        const size_t rest_bytes = workspace_bytes - align256(N * cb * sizeof(double));
+        for (size_t c0 = 0; c0 < m; c0 += cb) {
+            const size_t mc = m - c0 < cb ? m - c0 : cb;
+            {
+                LaunchScope ls(KC_FJLT, st);
+                launch_transpose_to_cols(X + c0, ldx, rows, mc, T, st);
+                SKB_CUDA(cudaGetLastError());
+            }
+            fjlt_apply_impl(fut, false, T, rows, N, mc, D, Dbits, samples, S, wht_slot_sample, wht_slot_out,
+                            OUT + c0, ldo, rest, rest_bytes, st, offset, nloc, dct_plan, true);
+        }
+        return;
+    }
+    fjlt_apply_impl(fut, layout_rows, X, ldx, N, m, D, Dbits, samples, S, wht_slot_sample, wht_slot_out, OUT, ldo,
+                    workspace, workspace_bytes, st, offset, nloc, dct_plan, layout_rows);
+}
+
+// out_rows: OUT[i*ldo + j] (else OUT[i + j*ldo]); layout_rows is only seen by the general-N path here
+static void fjlt_apply_impl(int fut, bool layout_rows, const double *X, size_t ldx, size_t N, size_t m,
+                            const double *D, const uint32_t *Dbits, const int32_t *samples, size_t S,
+                            const int32_t *wht_slot_sample, const int32_t *wht_slot_out,
+                            double *OUT, size_t ldo, void *workspace, size_t workspace_bytes,
+                            cudaStream_t st, size_t offset, size_t nloc, const void *dct_plan,
+                            bool out_rows) {
     if (S == 0 || m == 0) return;
     if (nloc != N && !fjlt_shard_ok(fut, N, offset, nloc))
         throw error(SKB_ERR_INVALID_USAGE,
@@ -1319,21 +1371,11 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
                     "of two >= 8192, and shard offset and length that are multiples of 8192");
     if (fut == FUT_WHT && (N & (N - 1)) != 0)
         throw error(SKB_ERR_INVALID_PARAM, "FJLT (WHT mode): N must be a power of two");
-    if (workspace_bytes < fjlt_workspace_bytes(N, m, fut, layout_rows, S))
-        throw error(SKB_ERR_ALLOC, "fjlt apply: workspace too small");
     if (fut == FUT_DCT && dct_fast_ok(N)) {
         char *ws = reinterpret_cast<char *>(workspace);
         const double *Xc = X;
         size_t ldc = ldx;
-        if (layout_rows) {      // the reference also transposes for this direction
-            double *T = reinterpret_cast<double *>(ws);
-            ws += ((N * m * sizeof(double) + 255) / 256) * 256;
-            LaunchScope ls(KC_FJLT, st);
-            launch_transpose_to_cols(X, ldx, N, m, T, st);
-            SKB_CUDA(cudaGetLastError());
-            Xc = T; ldc = N;
-        }
-        const size_t oi_ = layout_rows ? ldo : 1, oj_ = layout_rows ? 1 : ldo;
+        const size_t oi_ = out_rows ? ldo : 1, oj_ = out_rows ? 1 : ldo;
         if (dct_plan && dct_fused_ok(N) && !dct_legacy_forced()) {
             // keep the 32-bit item counter of one launch far from wrapping
             const size_t tiles = N / 2 / FFT_POINTS,
@@ -1391,7 +1433,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
             k_dct_tables<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(pl, samples, S);
             SKB_CUDA(cudaGetLastError());
         }
-        const size_t oi = layout_rows ? ldo : 1, oj = layout_rows ? 1 : ldo;
+        const size_t oi = oi_, oj = oj_;
         const double inscale = 1.0 / sqrt(2.0 * (double)N), outscale = sqrt((double)N / (double)S);
         // one radix-4 unit per thread per pass where possible (latency hiding by occupancy)
         auto threads_for = [](size_t units) { size_t t = 128; while (t < units && t < 1024) t *= 2; return (unsigned)t; };
@@ -1420,14 +1462,6 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
         const double *Xc = X;
         size_t ldc = ldx;
         char *ws = reinterpret_cast<char *>(workspace);
-        if (layout_rows) {      // the reference also transposes for this direction
-            double *T = reinterpret_cast<double *>(ws);
-            ws += (nloc * m * sizeof(double) + 255) / 256 * 256;
-            LaunchScope ls(KC_FJLT, st);
-            launch_transpose_to_cols(X, ldx, nloc, m, T, st);
-            SKB_CUDA(cudaGetLastError());
-            Xc = T; ldc = nloc;
-        }
         uint64_t *Dwht = reinterpret_cast<uint64_t *>(ws);      // N/64 words, rebuilt per apply (~2 us)
         {
             LaunchScope ls(KC_FJLT, st);
@@ -1435,7 +1469,7 @@ void fjlt_apply(int fut, bool layout_rows, const double *X, size_t ldx, size_t N
             k_wht_sign_words<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(Dbits, nwords, Dwht);
             SKB_CUDA(cudaGetLastError());
         }
-        const size_t oi = layout_rows ? ldo : 1, oj = layout_rows ? 1 : ldo;
+        const size_t oi = out_rows ? ldo : 1, oj = out_rows ? 1 : ldo;
         const double inscale = 1.0 / sqrt((double)N), outscale = sqrt((double)N / (double)S);
         const size_t smem = (size_t)WSMEM_BYTES;
         const bool al16 = (ldc % 2 == 0) && ((uintptr_t)Xc % 16 == 0);
