@@ -39,7 +39,7 @@ def traffic(rep):
     acc = {}
     for r in rows[2:]:
         d = dict(zip(hdr, r))
-        name = re.split(r"[<(]", d.get("Kernel Name", "?"))[0].split("::")[-1].strip()
+        name = re.split(r"[<(]", d.get("Kernel Name", "?"))[0].split("::")[-1].strip().split()[-1]
         b = to_bytes(d["dram__bytes_read.sum"], u["dram__bytes_read.sum"]) + \
             to_bytes(d["dram__bytes_write.sum"], u["dram__bytes_write.sum"])
         acc.setdefault(name, []).append(b)
