@@ -149,6 +149,7 @@ enum TType { T_JLT, T_CT, T_CWT, T_MMT, T_WZT, T_GRFT, T_LRFT, T_FJLT, T_UST };
 struct DevState {
     int32_t *bucket = nullptr; double *value = nullptr;
     std::map<std::pair<size_t, size_t>, HashPlan> plans;
+    std::map<std::pair<size_t, size_t>, HashColsPlan> cplans;
     double *shifts = nullptr, *scales = nullptr;
     double *D = nullptr; int32_t *samples = nullptr; uint32_t *Dbits = nullptr;
     int32_t *wht_slot_sample = nullptr, *wht_slot_out = nullptr;
@@ -175,6 +176,7 @@ struct sl_sketch_transform_t {
             cudaFree(d.D); cudaFree(d.samples); cudaFree(d.Dbits); cudaFree(d.wht_slot_sample);
             cudaFree(d.wht_slot_out); cudaFree(d.dct_plan); cudaFree(d.ws);
             for (auto &p : d.plans) hash_free_plan(&p.second);
+            for (auto &p : d.cplans) hash_free_cols_plan(&p.second);
             if (prev >= 0) cudaSetDevice(prev);
         }
     }
@@ -489,9 +491,24 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
             hash_apply_rows((const double *)A->data, (size_t)A->ld, (size_t)other, it->second,
                             d.value + offset, (double *)SA->data, (size_t)SA->ld, t->S, st);
         } else {
-            hash_apply_cols((const double *)A->data, (size_t)A->ld, (size_t)sk, (size_t)other,
-                            d.bucket + offset, d.value + offset, (double *)SA->data,
-                            (size_t)SA->ld, t->S, st);
+            // strided layout: the atomics-free planned kernel when the shape allows, for operands
+            // large enough to pay for building the plan once (host side, O(n))
+            bool done = false;
+            if ((size_t)sk * (size_t)other >= ((size_t)1 << 20) && t->S <= 23552) {
+                auto key = std::make_pair((size_t)offset, (size_t)sk);
+                auto it = d.cplans.find(key);
+                if (it == d.cplans.end()) {
+                    HashColsPlan plan;
+                    hash_build_cols_plan(d.bucket + offset, d.value + offset, (size_t)sk, t->S, &plan, st);
+                    it = d.cplans.emplace(key, plan).first;
+                }
+                done = hash_apply_cols_planned((const double *)A->data, (size_t)A->ld, (size_t)sk, (size_t)other,
+                                               it->second, (double *)SA->data, (size_t)SA->ld, t->S, st);
+            }
+            if (!done)
+                hash_apply_cols((const double *)A->data, (size_t)A->ld, (size_t)sk, (size_t)other,
+                                d.bucket + offset, d.value + offset, (double *)SA->data,
+                                (size_t)SA->ld, t->S, st);
         }
         return;
     }

@@ -386,6 +386,211 @@ void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int3
 }
 
 // ---------------------------------------------------------------------------
+// K2p: strided layout without atomics (see HashColsPlan).  A CTA owns CG columns and a range of
+// index tiles.  Tiles of 2048 indices x CG columns are staged in shared memory by cp.async
+// (coalesced 16-byte pieces, double buffered, with an L2 prefetch a few tiles ahead); warp w then
+// walks the rounds the plan queued for it: lane l takes the entry of a bucket only it owns, reads
+// the CG values of that index from the tile and does load-add-store on its accumulators.  Rows of
+// a bucket are added in ascending order (the reference's rounding sequence,
+// hash_transform_Elemental.hpp:83-100), the accumulators are written out once.
+// ---------------------------------------------------------------------------
+constexpr int HC_K = 2048, HC_W = 8, HC_THREADS = HC_W * 32, HC_NBUF = 2, HC_PF = 4, HC_B = 8;
+constexpr uint32_t HC_EMPTY = 0xFFFFFFFFu;
+
+void hash_free_cols_plan(HashColsPlan *plan) {
+    cudaFree(plan->entries); cudaFree(plan->vals); cudaFree(plan->off);
+    *plan = HashColsPlan();
+}
+
+void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, int S, HashColsPlan *plan,
+                          cudaStream_t st) {
+    hash_free_cols_plan(plan);
+    plan->n = n; plan->S = S;
+    plan->SW = (((S + HC_W - 1) / HC_W) + 31) / 32 * 32;
+    plan->ntiles = (int)((n + HC_K - 1) / HC_K);
+    if (n == 0) return;
+    std::vector<int32_t> hb(n); std::vector<double> hv(n);
+    SKB_CUDA(cudaMemcpyAsync(hb.data(), bucket, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    SKB_CUDA(cudaMemcpyAsync(hv.data(), value, n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    SKB_CUDA(cudaStreamSynchronize(st));
+    bool signs = true;
+    for (size_t k = 0; k < n && signs; k++) signs = hv[k] == 1.0 || hv[k] == -1.0;
+    std::vector<uint32_t> entries, off((size_t)plan->ntiles * HC_W + 1);
+    std::vector<double> vals;
+    entries.reserve(n * 2);
+    if (!signs) vals.reserve(n * 2);
+    std::vector<uint32_t> q[HC_W][32];
+    size_t rounds = 0;
+    for (int t = 0; t < plan->ntiles; t++) {
+        const size_t k0 = (size_t)t * HC_K, k1 = std::min(n, k0 + HC_K);
+        for (int w = 0; w < HC_W; w++) for (int l = 0; l < 32; l++) q[w][l].clear();
+        for (size_t k = k0; k < k1; k++) {
+            const int h = hb[k], w = h / plan->SW, l = (h - w * plan->SW) & 31;
+            q[w][l].push_back((uint32_t)(k - k0));
+        }
+        for (int w = 0; w < HC_W; w++) {
+            off[(size_t)t * HC_W + w] = (uint32_t)rounds;
+            size_t nr = 0;
+            for (int l = 0; l < 32; l++) nr = std::max(nr, q[w][l].size());
+            for (size_t r = 0; r < nr; r++)
+                for (int l = 0; l < 32; l++) {
+                    if (r < q[w][l].size()) {
+                        const uint32_t kk = q[w][l][r];
+                        const size_t k = k0 + kk;
+                        uint32_t e = kk | ((uint32_t)hb[k] << 11);
+                        if (signs && hv[k] < 0) e |= 0x80000000u;
+                        entries.push_back(e);
+                        if (!signs) vals.push_back(hv[k]);
+                    } else {
+                        entries.push_back(HC_EMPTY);
+                        if (!signs) vals.push_back(0.0);
+                    }
+                }
+            rounds += nr;
+        }
+    }
+    off[(size_t)plan->ntiles * HC_W] = (uint32_t)rounds;
+    try {
+        SKB_CUDA(cudaMalloc(&plan->entries, entries.size() * sizeof(uint32_t) + 256));
+        SKB_CUDA(cudaMalloc(&plan->off, off.size() * sizeof(uint32_t)));
+        SKB_CUDA(cudaMemcpy(plan->entries, entries.data(), entries.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        SKB_CUDA(cudaMemcpy(plan->off, off.data(), off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        if (!signs) {
+            SKB_CUDA(cudaMalloc(&plan->vals, vals.size() * sizeof(double) + 256));
+            SKB_CUDA(cudaMemcpy(plan->vals, vals.data(), vals.size() * sizeof(double), cudaMemcpyHostToDevice));
+        }
+    } catch (...) { hash_free_cols_plan(plan); throw; }
+}
+
+template <int CG, bool SIGN>
+__global__ void __launch_bounds__(HC_THREADS, CG == 4 ? 1 : 2)
+k_hash_cols_plan(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
+                 const uint32_t *__restrict__ entries, const double *__restrict__ vals,
+                 const uint32_t *__restrict__ off, int ntiles, int tiles_per_split,
+                 double *__restrict__ OUT, size_t ldo, int S, int SP, int ksplit) {
+    extern __shared__ __align__(16) double hc_smem[];
+    double *acc = hc_smem;                                  // [CG][SP]
+    double *tiles = hc_smem + (size_t)CG * SP;              // [HC_NBUF][CG][HC_K]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t j0 = (size_t)blockIdx.x * CG;
+    const int ncol = (int)min((size_t)CG, m - j0);
+    const int t0 = blockIdx.y * tiles_per_split, t1 = min(ntiles, t0 + tiles_per_split);
+    for (int i = tid; i < CG * SP; i += HC_THREADS) acc[i] = 0.0;
+    auto issue = [&](int t, int buf) {
+        const size_t k0 = (size_t)t * HC_K;
+        const int len = (int)min((size_t)HC_K, n - k0);
+        for (int idx = tid; idx < CG * (HC_K / 2); idx += HC_THREADS) {
+            const int c = idx / (HC_K / 2), p2 = (idx - c * (HC_K / 2)) * 2;
+            if (c < ncol && p2 < len) {
+                const double *src = X + k0 + p2 + (j0 + c) * ldx;
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(tiles + ((size_t)(buf * CG + c) * HC_K + p2));
+                if (p2 + 1 < len) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+                else asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (tid < ncol) {                                   // keep L2 a few tiles ahead of the staging loads
+            const size_t kp = (size_t)(t + HC_PF) * HC_K;
+            if (t + HC_PF < t1 && kp + HC_K <= n)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(X + kp + (j0 + tid) * ldx), "r"(HC_K * 8));
+        }
+    };
+    if (t0 < t1) issue(t0, 0);
+    for (int t = t0; t < t1; t++) {
+        const int buf = (t - t0) & 1;
+        if (t + 1 < t1) {
+            issue(t + 1, buf ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();
+        const double *tile = tiles + (size_t)buf * CG * HC_K;
+        const uint32_t r0 = __ldg(off + (size_t)t * HC_W + warp), r1 = __ldg(off + (size_t)t * HC_W + warp + 1);
+        // entries come from L2: a batch of HC_B rounds is in flight while the previous one is applied
+        uint32_t eb[HC_B]; double vb[HC_B];
+        auto fetch = [&](uint32_t r, uint32_t (&e)[HC_B], double (&v)[HC_B]) {
+#pragma unroll
+            for (int i = 0; i < HC_B; i++) {
+                e[i] = r + i < r1 ? __ldg(entries + (size_t)(r + i) * 32 + lane) : HC_EMPTY;
+                v[i] = (!SIGN && r + i < r1) ? __ldg(vals + (size_t)(r + i) * 32 + lane) : 0.0;
+            }
+        };
+        fetch(r0, eb, vb);
+        for (uint32_t r = r0; r < r1; r += HC_B) {
+            uint32_t en[HC_B]; double vn[HC_B];
+            fetch(r + HC_B, en, vn);
+#pragma unroll
+            for (int i = 0; i < HC_B; i++) {
+                const uint32_t e = eb[i];
+                if (e != HC_EMPTY) {
+                    const int k = (int)(e & (HC_K - 1)), h = (int)((e >> 11) & 0xFFFFu);
+                    double x[CG], a[CG];
+#pragma unroll
+                    for (int c = 0; c < CG; c++) x[c] = c < ncol ? tile[c * HC_K + k] : 0.0;
+#pragma unroll
+                    for (int c = 0; c < CG; c++) a[c] = acc[c * SP + h];
+#pragma unroll
+                    for (int c = 0; c < CG; c++) {          // product, then sum: the reference's rounding
+                        const double p = SIGN ? ((e >> 31) ? -x[c] : x[c]) : __dmul_rn(vb[i], x[c]);
+                        a[c] = __dadd_rn(a[c], p);
+                    }
+#pragma unroll
+                    for (int c = 0; c < CG; c++) acc[c * SP + h] = a[c];
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < HC_B; i++) { eb[i] = en[i]; vb[i] = vn[i]; }
+        }
+        __syncthreads();                                    // the buffer is refilled two tiles later
+    }
+    __syncthreads();
+    for (int i = tid; i < S * ncol; i += HC_THREADS) {
+        const int c = i / S, h = i - c * S;
+        const double a = acc[c * SP + h];
+        double *o = OUT + h + (j0 + c) * ldo;
+        if (ksplit == 1) *o = a;
+        else if (a != 0.0) atomicAdd(o, a);
+    }
+}
+
+bool hash_apply_cols_planned(const double *X, size_t ldx, size_t n, size_t m, const HashColsPlan &plan,
+                             double *OUT, size_t ldo, int S, cudaStream_t st) {
+    static const bool off_env = getenv("SKB_DEBUG_NO_COLS_PLAN") != nullptr;
+    if (off_env || m == 0 || n == 0 || plan.n != n || plan.S != S || !plan.entries) return false;
+    if (S > 32767 || (ldx & 1) || ((uintptr_t)X & 15)) return false;
+    const int SP = plan.SW * HC_W;
+    auto smem_for = [&](int cg) { return ((size_t)cg * SP + (size_t)HC_NBUF * cg * HC_K) * sizeof(double); };
+    // two columns per CTA and two CTAs per SM (one's barriers and staging overlap the other's rounds)
+    // when that still fills the GPU: measured 0.172 ms against 0.209 ms with four columns at C1
+    int CG = (m + 1) / 2 >= 148 && smem_for(2) <= 108 * 1024 ? 2 : 4;
+    { static const char *e = getenv("SKB_HC_CG"); if (e && (atoi(e) == 1 || atoi(e) == 2 || atoi(e) == 4)) CG = atoi(e); }
+    while (CG > 1 && smem_for(CG) > 216 * 1024) CG >>= 1;
+    if (smem_for(CG) > 216 * 1024) return false;
+    const unsigned gx = (unsigned)((m + CG - 1) / CG);
+    int ksplit = 1;
+    while ((long long)gx * ksplit < 120 && plan.ntiles / (ksplit * 2) >= 4) ksplit *= 2;
+    const int tps = (plan.ntiles + ksplit - 1) / ksplit;
+    if (ksplit > 1) zero_matrix(OUT, ldo, (size_t)S, m, st);
+    const bool sign = plan.vals == nullptr;
+    const size_t smem = smem_for(CG);
+    LaunchScope ls(KC_HASH, st);
+#define SKB_HC_LAUNCH(CGV, SG)                                                                               \
+    do {                                                                                                    \
+        auto kern = k_hash_cols_plan<CGV, SG>;                                                              \
+        SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
+        kern<<<dim3(gx, (unsigned)ksplit), HC_THREADS, smem, st>>>(X, ldx, n, m, plan.entries, plan.vals,   \
+                                                                   plan.off, plan.ntiles, tps, OUT, ldo, S, SP, ksplit); \
+    } while (0)
+    if (CG == 4) { if (sign) SKB_HC_LAUNCH(4, true); else SKB_HC_LAUNCH(4, false); }
+    else if (CG == 2) { if (sign) SKB_HC_LAUNCH(2, true); else SKB_HC_LAUNCH(2, false); }
+    else { if (sign) SKB_HC_LAUNCH(1, true); else SKB_HC_LAUNCH(1, false); }
+#undef SKB_HC_LAUNCH
+    SKB_CUDA(cudaGetLastError());
+    return true;
+}
+
+// ---------------------------------------------------------------------------
 // K3: CSC input, sketch over rows.  Persistent CTAs; each column is accumulated in
 // a shared S-vector (shared atomics), then written as one coalesced dense column
 // while the accumulator is re-zeroed.

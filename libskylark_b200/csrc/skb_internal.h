@@ -81,6 +81,23 @@ void hash_apply_rows(const double *X, size_t ldx, size_t m, const HashPlan &plan
 // OUT[h(k) + j*ldo] += v(k) * X[k + j*ldx], j < m   (input index k strided by 1 inside a column)
 void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int32_t *bucket,
                      const double *value, double *OUT, size_t ldo, int S, cudaStream_t st);
+// Plan of the strided layout (K2): sketched indices are cut in tiles of 2048; inside a tile every
+// index is queued at the (warp, lane) that OWNS its bucket (warp = bucket / SW, lane = bucket % 32),
+// so a CTA accumulates in shared memory with plain loads and stores -- no atomics.  Built on the
+// host once per (transform, shard) from the bucket / value tables.
+struct HashColsPlan {
+    uint32_t *entries = nullptr;   // rounds of 32 packed entries: k in tile | bucket << 11 | sign << 31
+    double *vals = nullptr;        // value per entry; null when every value is +-1 (sign bit used)
+    uint32_t *off = nullptr;       // first round of (tile, warp), ntiles * 8 + 1 entries
+    int ntiles = 0, S = 0, SW = 0;
+    size_t n = 0;
+};
+void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, int S, HashColsPlan *plan,
+                          cudaStream_t st);
+void hash_free_cols_plan(HashColsPlan *plan);
+// false = shape or alignment outside the planned kernel's range (caller falls back to hash_apply_cols)
+bool hash_apply_cols_planned(const double *X, size_t ldx, size_t n, size_t m, const HashColsPlan &plan,
+                             double *OUT, size_t ldo, int S, cudaStream_t st);
 // CSC input (rows are the sketched index): OUT[h(row) + col*ldo] += v(row)*val
 void hash_apply_csc_columnwise(const int32_t *indptr, const int32_t *indices,
                                const double *values, size_t ncols, const int32_t *bucket,

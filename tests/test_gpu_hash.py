@@ -323,3 +323,32 @@ def test_serialized_sketch_replays_identically(sk, oracle):
     F = sk.FJLT(4096, 100, c)
     F2 = pickle.loads(pickle.dumps(F))
     assert np.array_equal(F2.samples(), F.samples()) and np.array_equal(F2.diagonal(), F.diagonal())
+
+
+@pytest.mark.parametrize("T,shape", [("CWT", (100000, 500, 2000)), ("CWT", (30001, 70, 513)), ("MMT", (40000, 37, 5000)),
+                                     ("WZT", (50000, 26, 20000)), ("CWT", (4097, 300, 64))])
+def test_strided_layout_planned_kernel(sk, oracle, T, shape):
+    """Column-major operands (the reference-native Elemental layout, hash_transform_Elemental.hpp:83-100)
+    large enough for the atomics-free kernel: buckets owned by lanes, tiles staged in shared memory.
+    C1's shape, 4 / 2 / 1 columns per CTA (by S), ragged column groups, odd n, valued transforms;
+    CWT sums follow the reference's order, so the result is bit-identical to the oracle's."""
+    import torch
+    n, d, s = shape
+    S, O = _pair(sk, oracle, T, n, s, seed=4711)
+    g = torch.Generator("cuda").manual_seed(3)
+    A = torch.randn(d, n, dtype=torch.float64, device="cuda", generator=g).t()        # column-major n x d
+    want = O.apply(A.cpu().numpy(), "columnwise")
+    SA = torch.full((d, s), float("nan"), dtype=torch.float64, device="cuda").t()
+    for _ in range(2):
+        S.apply(A, SA, "columnwise")
+        got = SA.cpu().numpy()
+        assert rel_fro(got, want) < TOL
+    if T == "CWT" and d >= 480:                             # one index range per CTA: the reference's summation order
+        assert np.array_equal(got, want)
+    # rowwise on a row-major operand is the same kernel (the transposed view)
+    B = A.t().contiguous()                                  # d x n row-major
+    assert rel_fro(S.apply(B, None, "rowwise").cpu().numpy(), want.T) < TOL
+    # row shards with global indices (own plans per shard), one of them at an odd offset
+    cut = (n // 3) | 1
+    parts = S.apply_shard(A[:cut], None, 0, 0) + S.apply_shard(A[cut:], None, 0, cut)
+    assert rel_fro(parts.cpu().numpy(), want) < TOL
