@@ -96,6 +96,9 @@ void sl_print_exception_trace(void);
 int sl_create_context_at(int seed, uint64_t counter, sl_context_t **ctxt);
 int sl_context_get_seed(sl_context_t *ctxt, int *seed);
 int sl_context_get_counter(sl_context_t *ctxt, uint64_t *counter);
+/* context_t::allocate_random_samples_array's bookkeeping (base/context.hpp:94-101): reserves `size`
+ * stream indices, returns the first; 108 when the stream would be exhausted. */
+int sl_context_allocate(sl_context_t *ctxt, uint64_t size, uint64_t *base);
 
 #define SL_DTYPE_F64 0
 #define SL_DTYPE_F32 1
@@ -141,6 +144,13 @@ int sl_sketch_export_dense(sl_sketch_transform_t *S, int64_t i0, int64_t j0, int
  * (base/randgen.hpp:109-114), generated on the device. */
 int sl_rng_export_raw(int seed, uint64_t base, int64_t count, uint64_t *first,
                       uint64_t *second);
+
+/* Variates of stream indices [base, base+count), generated on the device with the semantics of
+ * base/randgen.hpp:98-115 + Boost.Random: kind 0 = Rademacher
+ * (utility/distributions.hpp:40-52, current boost_order), 1 = normal(0,1), 2 = cauchy(0,1),
+ * 3 = uniform_real(a, b), 4 = uniform_int(0, a) (as doubles).  Used by the composite transforms of the Python layer (Fastfood, PPT),
+ * whose tables are several such arrays (sketch/FRFT_data.hpp:91-120, sketch/PPT_data.hpp:83-99). */
+int sl_rng_export(int kind, int seed, uint64_t base, int64_t count, double a, double b, double *host_out);
 
 /* Launch accounting.  Classes: 0 tables, 1 hash apply, 2 dense panel generation,
  * 3 dense GEMM, 4 FJLT, 5 misc.  With timing enabled every launch is bracketed by CUDA

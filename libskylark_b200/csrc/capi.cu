@@ -872,6 +872,12 @@ int sl_create_context_at(int seed, uint64_t counter, sl_context_t **ctxt) {
 int sl_free_context(sl_context_t *ctxt) { delete ctxt; return 0; }
 int sl_context_get_seed(sl_context_t *ctxt, int *seed) { *seed = ctxt->seed; return 0; }
 int sl_context_get_counter(sl_context_t *ctxt, uint64_t *counter) { *counter = ctxt->counter; return 0; }
+int sl_context_allocate(sl_context_t *ctxt, uint64_t size, uint64_t *base) {
+    SL_TRY
+    if (!ctxt || !base) throw error(SKB_ERR_INVALID_PARAM, "null argument");
+    *base = ctxt->allocate(size);
+    SL_CATCH
+}
 
 int sl_create_sketch_transform(sl_context_t *ctxt, char *type_, int n, int s,
                                sl_sketch_transform_t **sketch, ...) {
@@ -1115,6 +1121,21 @@ int sl_sketch_export_dense(sl_sketch_transform_t *t, int64_t i0, int64_t j0, int
 
 }  // extern "C"
 
+// variates of stream indices [base, base + count) for the composite transforms of the Python layer
+__global__ void k_rng_export(int kind, uint64_t key, uint64_t base, size_t count, double a, double b, int order,
+                             double *out) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    MicroUrng u(key, base + t);
+    double v;
+    if (kind == 0) v = boost_rademacher(u, order);
+    else if (kind == 1) v = boost_normal(u);
+    else if (kind == 2) v = boost_cauchy(u);
+    else if (kind == 3) v = boost_uniform_real(u, a, b);
+    else v = (double)boost_uniform_int(u, (uint64_t)a);       // kind 4: uniform_int(0, a), a < 2^53
+    out[t] = v;
+}
+
 __global__ void k_raw_draws(uint64_t key, uint64_t base, size_t count, uint64_t *first, uint64_t *second) {
     size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= count) return;
@@ -1141,6 +1162,27 @@ int sl_rng_export_raw(int seed, uint64_t base, int64_t count, uint64_t *first, u
         SKB_CUDA(cudaGetLastError());
         SKB_CUDA(cudaMemcpyAsync(first, buf, (size_t)count * 8, cudaMemcpyDeviceToHost, g_stream));
         SKB_CUDA(cudaMemcpyAsync(second, buf + count, (size_t)count * 8, cudaMemcpyDeviceToHost, g_stream));
+        SKB_CUDA(cudaStreamSynchronize(g_stream));
+    } catch (...) { cudaFree(buf); throw; }
+    cudaFree(buf);
+    SL_CATCH
+}
+
+int sl_rng_export(int kind, int seed, uint64_t base, int64_t count, double a, double b, double *host_out) {
+    SL_TRY
+    require_device();
+    if (count < 0 || kind < 0 || kind > 4) throw error(SKB_ERR_INVALID_PARAM, "sl_rng_export: bad argument");
+    if (count == 0) return 0;
+    double *buf = nullptr;
+    SKB_CUDA(cudaMalloc(&buf, (size_t)count * 8));
+    try {
+        {
+            LaunchScope ls(KC_TABLES, g_stream);
+            k_rng_export<<<(unsigned)((count + 255) / 256), 256, 0, g_stream>>>(kind, seed_to_key(seed), base, (size_t)count,
+                                                                               a, b, g_boost_order, buf);
+        }
+        SKB_CUDA(cudaGetLastError());
+        SKB_CUDA(cudaMemcpyAsync(host_out, buf, (size_t)count * 8, cudaMemcpyDeviceToHost, g_stream));
         SKB_CUDA(cudaStreamSynchronize(g_stream));
     } catch (...) { cudaFree(buf); throw; }
     cudaFree(buf);

@@ -57,7 +57,7 @@ def _load():
                  "sl_apply_sketch_transform_shard", "sl_set_option", "sl_sketch_export",
                  "sl_sketch_export_dense", "sl_rng_export_raw", "sl_profile_enable",
                  "sl_profile_reset", "sl_profile_read", "sl_host_alloc_pinned",
-                 "sl_host_free_pinned", "sl_device_count"):
+                 "sl_host_free_pinned", "sl_device_count", "sl_rng_export", "sl_context_allocate"):
         getattr(L, name).restype = c_int
     L.sl_strerror.restype = c_char_p
     L.sl_supported_sketch_transforms.restype = c_char_p
@@ -76,6 +76,8 @@ def _load():
     L.sl_sketch_export.argtypes = (c_void_p, c_char_p, c_int64, c_int64, c_void_p)
     L.sl_sketch_export_dense.argtypes = (c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p)
     L.sl_rng_export_raw.argtypes = (c_int, c_uint64, c_int64, c_void_p, c_void_p)
+    L.sl_rng_export.argtypes = (c_int, c_int, c_uint64, c_int64, c_double, c_double, c_void_p)
+    L.sl_context_allocate.argtypes = (c_void_p, c_uint64, c_void_p)
     L.sl_set_stream.argtypes = (c_void_p,)
     L.sl_host_alloc_pinned.argtypes = (c_size_t, c_void_p)
     L.sl_host_free_pinned.argtypes = (c_void_p,)
@@ -155,6 +157,43 @@ class Context:
         v = c_uint64()
         callsl("sl_context_get_counter", self._obj, byref(v))
         return v.value
+
+    def allocate(self, size):
+        """Reserve `size` stream indices (base/context.hpp:94-101); returns the first."""
+        v = c_uint64()
+        callsl("sl_context_allocate", self._obj, c_uint64(int(size)), byref(v))
+        return v.value
+
+
+class _GlobalContext(object):
+    """The reference's single global context (lib.py:80) behind the Context interface."""
+
+    @property
+    def _obj(self):
+        return ctxt_obj
+
+    seed = Context.seed
+    counter = Context.counter
+    allocate = Context.allocate
+
+
+def rng_export(kind, seed, base, count, a=0.0, b=0.0):
+    """Variates of stream indices [base, base + count) generated on the device (sl_rng_export):
+    kind "rademacher" | "normal" | "cauchy" | "uniform_real" (a, b) | "uniform_int" (0..a)."""
+    code = {"rademacher": 0, "normal": 1, "cauchy": 2, "uniform_real": 3, "uniform_int": 4}[kind]
+    out = numpy.empty(int(count), dtype=numpy.float64)
+    callsl("sl_rng_export", c_int(code), c_int(int(seed)), c_uint64(int(base)), ctypes.c_int64(int(count)),
+           c_double(float(a)), c_double(float(b)), out.ctypes.data_as(c_void_p))
+    return out
+
+
+def rng_export_raw(seed, base, count):
+    """First and second 64-bit draw of every stream index in [base, base + count)."""
+    first = numpy.empty(int(count), dtype=numpy.uint64)
+    second = numpy.empty(int(count), dtype=numpy.uint64)
+    callsl("sl_rng_export_raw", c_int(int(seed)), c_uint64(int(base)), ctypes.c_int64(int(count)),
+           first.ctypes.data_as(c_void_p), second.ctypes.data_as(c_void_p))
+    return first, second
 
 
 def global_counter():

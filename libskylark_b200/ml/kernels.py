@@ -97,9 +97,27 @@ class Laplacian(Kernel):
         return sketch.LaplacianRFT(self._d, s, self._sigma, defouttype, **kwargs)
 
 
+class Polynomial(Kernel):
+    """k(x, y) = (gamma x^T y + c)^q (ml/kernels.hpp polynomial_t); rft = TensorSketch (kernels.py:163-199)."""
+
+    def __init__(self, d, q=3, c=0, gamma=1):
+        if c < 0:
+            raise ValueError("kernel paramter must be >= 0")
+        if type(q) is not int:
+            raise errors.InvalidParamterError("exponent must be integer")
+        super().__init__(d)
+        self._q, self._c, self._gamma = q, c, gamma
+
+    def _gram(self, torch, X, Y):
+        return (self._gamma * (X @ Y.t()) + self._c) ** self._q
+
+    def rft(self, s, subtype=None, defouttype=None, **kwargs):
+        return sketch.PPT(self._d, s, self._q, self._c, self._gamma, defouttype, **kwargs)
+
+
 def kernel(kerneltype, *args):
     """Factory (kernels.py:13-38)."""
-    table = {"linear": Linear, "gaussian": Gaussian, "laplacian": Laplacian}
+    table = {"linear": Linear, "gaussian": Gaussian, "laplacian": Laplacian, "polynomial": Polynomial}
     if not isinstance(kerneltype, str):
         raise ValueError("kerneltype must be a string")
     try:

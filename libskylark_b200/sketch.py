@@ -17,6 +17,7 @@ Additions over the reference (all optional, existing calls keep their meaning):
 """
 import ctypes
 import json
+import math
 from ctypes import byref, c_char_p, c_double, c_void_p
 
 import numpy
@@ -352,6 +353,176 @@ class LaplacianRFT(_RFT):
                          params=(sigma,))
 
 
+# ---------------------------------------------------------------------------
+# Composite transforms: their random tables come from the context's counter
+# stream through the C ABI (bit for bit the reference's), their CountSketches run on the hash
+# kernels, and the FFT / DCT steps go through torch.fft (cuFFT) -- library code, as FFTW is in the
+# reference.  Device tensors in, device tensors out; numpy operands are copied over.
+# ---------------------------------------------------------------------------
+def _torch():
+    import torch
+    return torch
+
+
+def _to_device_f64(A):
+    torch = _torch()
+    if isinstance(A, torch.Tensor):
+        if not A.is_cuda or A.dtype != torch.float64:
+            raise errors.UnsupportedError("composite transforms take float64 CUDA tensors or numpy arrays")
+        return A, True
+    return torch.from_numpy(numpy.ascontiguousarray(A, dtype=numpy.float64)).cuda(), False
+
+
+def _dct2_unnormalized(X):
+    """FFTW REDFT10 along dim 0: Y_k = 2 sum_n x_n cos(pi (n + 1/2) k / N) (utility/fft/fftw_futs.h:117-126),
+    by Makhoul's even/odd reordering and one complex FFT of length N."""
+    torch = _torch()
+    N = X.shape[0]
+    v = torch.cat([X[0::2], X[1::2].flip(0)], dim=0)
+    V = torch.fft.fft(v, dim=0)
+    k = torch.arange(N, device=X.device, dtype=torch.float64)
+    w = torch.polar(torch.ones_like(k), -math.pi * k / (2.0 * N))
+    return 2.0 * (V * w.reshape((N,) + (1,) * (X.dim() - 1))).real
+
+
+class _Composite(object):
+    def _ctx(self, context):
+        return context if context is not None else lib._GlobalContext()
+
+    def getindim(self):
+        return self._n
+
+    def getsketchdim(self):
+        return self._s
+
+    def __mul__(self, A):
+        return self.apply(A, None, dim=0)
+
+    def __truediv__(self, A):
+        return self.apply(A, None, dim=1)
+
+    def _finish(self, out, SA, was_device, dim):
+        """out: s x m (one column per data vector).  Hands back what the caller's operands call for."""
+        res = out if dim == 0 else out.t()
+        if SA is not None:
+            if isinstance(SA, _torch().Tensor):
+                SA.copy_(res)
+            else:
+                SA[...] = res.cpu().numpy()
+            return SA
+        return res.contiguous() if was_device else res.cpu().numpy()
+
+
+class FastGaussianRFT(_Composite):
+    """Fastfood features of the Gaussian kernel (sketch/FRFT_data.hpp:19-160, FRFT_Elemental.hpp:70-135;
+    sketch.py:679-741).  Per block of N features: scale * cos(Sm .* DCT(G .* Perm(DCT(B .* x))) + shifts),
+    DCT = the unnormalised DCT-II of the FFTW build, B Rademacher, G Gaussian, Perm a Fisher-Yates
+    shuffle, Sm = 1 / (sigma sqrt(N)); tables drawn in the reference's order (shifts, B, G, P)."""
+
+    def __init__(self, n, s, sigma=1.0, defouttype=None, forceppy=False, sketch_transform=None, context=None):
+        defouttype, context = _split_context(defouttype, context)
+        if forceppy:
+            raise errors.UnsupportedError("forceppy: this package has no pure-Python / CPU implementation")
+        torch = _torch()
+        self._n, self._s, self._sigma = int(n), int(s), float(sigma)
+        ctx = self._ctx(context)
+        N, S = self._n, self._s
+        nb = 1 + (S - 1) // N                                    # numblks, block size NB = N (FFTW build)
+        seed = ctx.seed
+        self._creation = (seed, ctx.counter)
+        two_pi = 2.0 * 3.141592653589793238462643383279502884      # boost::math::constants::pi
+        shifts = lib.rng_export("uniform_real", seed, ctx.allocate(S), S, 0.0, two_pi)
+        B = lib.rng_export("rademacher", seed, ctx.allocate(nb * N), nb * N)
+        G = lib.rng_export("normal", seed, ctx.allocate(nb * N), nb * N)
+        praw = lib.rng_export_raw(seed, ctx.allocate(nb * (N - 1)), nb * (N - 1))[0]
+        scal = math.sqrt(N) * (1.0 / math.sqrt(2.0 * N))         # sqrt(NB) * fut.scale()
+        perms = numpy.empty((nb, N), dtype=numpy.int64)
+        for i in range(nb):                                      # FRFT_data.hpp:111-114 + the swap loop of apply
+            arr = list(range(N))
+            for l in range(N - 1):
+                idx1 = N - 1 - l
+                idx2 = int(praw[i * (N - 1) + l] % numpy.uint64(idx1 + 1))
+                arr[idx1], arr[idx2] = arr[idx2], arr[idx1]
+            perms[i] = arr
+        dev = "cuda"
+        self._B = torch.from_numpy(B.reshape(nb, N)).to(dev)
+        self._G = torch.from_numpy((scal * G).reshape(nb, N)).to(dev)
+        self._Sm = scal * (1.0 / (self._sigma * math.sqrt(N)))
+        self._perm = torch.from_numpy(perms).to(dev)
+        self._shifts = torch.from_numpy(shifts).to(dev)
+        self._scale = math.sqrt(2.0 / S)
+        self._nb = nb
+
+    def apply(self, A, SA=None, dim=0):
+        torch = _torch()
+        dim = _SketchTransform._normdim(dim)
+        X, was_device = _to_device_f64(A)
+        X = X if dim == 0 else X.t()                             # N x m, one data vector per column
+        if X.shape[0] != self._n:
+            raise errors.DimensionMistmatchError("Sketched dimension is incorrect (input)")
+        N, S = self._n, self._s
+        out = torch.empty(S, X.shape[1], dtype=torch.float64, device=X.device)
+        for i in range(self._nb):
+            s0, e0 = i * N, min((i + 1) * N, S)
+            W = _dct2_unnormalized(X * self._B[i][:, None])
+            W = W[self._perm[i]]
+            W = _dct2_unnormalized(W * self._G[i][:, None])
+            W = W * self._Sm
+            out[s0:e0] = self._scale * torch.cos(W[:e0 - s0] + self._shifts[s0:e0, None])
+        return self._finish(out, SA, was_device, dim)
+
+    def serialize(self):
+        return {"skylark_object_type": "sketch", "sketch_type": "FastGaussianRFT", "skylark_version": "0.20",
+                "N": str(self._n), "S": str(self._s), "sigma": repr(self._sigma),
+                "creation_context": {"skylark_object_type": "context", "skylark_version": "0.20",
+                                     "seed": str(self._creation[0]), "counter": str(self._creation[1])}}
+
+
+class PPT(_Composite):
+    """Pham-Pagh TensorSketch of the polynomial kernel (gamma x^T y + c)^q (sketch/PPT_data.hpp:19-105,
+    PPT_Elemental.hpp:140-185; sketch.py:829-881): q CountSketches of sqrt(gamma) x, each with
+    sqrt(c) * (+-1) added at one random position, multiplied in the Fourier domain, transformed back."""
+
+    def __init__(self, n, s, q=3, c=0.0, gamma=1.0, defouttype=None, forceppy=False, sketch_transform=None,
+                 context=None):
+        defouttype, context = _split_context(defouttype, context)
+        if forceppy:
+            raise errors.UnsupportedError("forceppy: this package has no pure-Python / CPU implementation")
+        if c < 0:
+            raise ValueError("kernel parameter must be >= 0")
+        self._n, self._s, self._q, self._c, self._gamma = int(n), int(s), int(q), float(c), float(gamma)
+        ctx = self._ctx(context)
+        seed = ctx.seed
+        self._creation = (seed, ctx.counter)
+        passed = context                                         # None = the global context, as CWT expects
+        self._cwts = [CWT(self._n, self._s, context=passed) for _ in range(self._q)]     # PPT_data.hpp:85-88
+        self._hash_idx = lib.rng_export("uniform_int", seed, ctx.allocate(self._q), self._q, self._s - 1).astype(numpy.int64)
+        self._hash_val = lib.rng_export("rademacher", seed, ctx.allocate(self._q), self._q)
+
+    def apply(self, A, SA=None, dim=0):
+        torch = _torch()
+        dim = _SketchTransform._normdim(dim)
+        X, was_device = _to_device_f64(A)
+        X = X if dim == 0 else X.t()
+        if X.shape[0] != self._n:
+            raise errors.DimensionMistmatchError("Sketched dimension is incorrect (input)")
+        Xc = X.t().contiguous().t() if X.stride(0) != 1 else X   # column-major operand for the hash kernels
+        P = None
+        for i, cw in enumerate(self._cwts):
+            W = cw.apply(Xc, None, "columnwise") * math.sqrt(self._gamma)
+            W[self._hash_idx[i], :] += math.sqrt(self._c) * self._hash_val[i]
+            FW = torch.fft.rfft(W, dim=0)
+            P = FW if P is None else P * FW
+        out = torch.fft.irfft(P, n=self._s, dim=0)               # FFTW's c2r is unscaled; the reference divides by S
+        return self._finish(out, SA, was_device, dim)
+
+    def serialize(self):
+        return {"skylark_object_type": "sketch", "sketch_type": "PPT", "skylark_version": "0.20",
+                "N": str(self._n), "S": str(self._s), "q": str(self._q), "c": repr(self._c), "gamma": repr(self._gamma),
+                "creation_context": {"skylark_object_type": "context", "skylark_version": "0.20",
+                                     "seed": str(self._creation[0]), "counter": str(self._creation[1])}}
+
+
 def _outside_hot_path(name, where):
     """Reference transforms that are not part of the accelerated path keep their names, so that
     code importing them fails with a clear message instead of an AttributeError."""
@@ -368,11 +539,9 @@ SJLT = _outside_hot_path("SJLT", "sketch.py:303-338, pure Python in the referenc
 MaternRFT = _outside_hot_path("MaternRFT", "sketch.py:592-619")
 GaussianQRFT = _outside_hot_path("GaussianQRFT", "sketch.py:621-648")
 LaplacianQRFT = _outside_hot_path("LaplacianQRFT", "sketch.py:650-677")
-FastGaussianRFT = _outside_hot_path("FastGaussianRFT", "sketch.py:679-741")
 FastMaternRFT = _outside_hot_path("FastMaternRFT", "sketch.py:743-772")
 ExpSemigroupRLT = _outside_hot_path("ExpSemigroupRLT", "sketch.py:774-800")
 ExpSemigroupQRLT = _outside_hot_path("ExpSemigroupQRLT", "sketch.py:802-827")
-PPT = _outside_hot_path("PPT", "sketch.py:829-881")
 URST = UST      # sketch.py:883-904 is a numpy.random sampler; here it is the C++ UST_t
 NURST = _outside_hot_path("NURST", "sketch.py:906-931, pure Python in the reference")
 

@@ -483,3 +483,72 @@ class UST(_Transform):
     def apply(self, A, dim="columnwise"):
         A = np.asarray(A)
         return A[self.samples, :] if dim in (0, "columnwise") else A[:, self.samples]
+
+
+class FastGaussianRFT(_Transform):
+    """Fastfood: sketch/FRFT_data.hpp:91-120 (tables: shifts, B, G, P in that order; P reduced modulo
+    j+1 for the Fisher-Yates swaps), FastGaussianRFT_data_t::build (:190-196, Sm = 1/(sigma sqrt(N))),
+    and the columnwise apply of sketch/FRFT_Elemental.hpp:70-135 with the FFTW DCT (block size N)."""
+    sketch_type = "FastGaussianRFT"
+
+    def __init__(self, N, S, sigma, context, order=BOOST_160):
+        super().__init__(N, S, context)
+        self.sigma = float(sigma)
+        seed = context.seed
+        nb = 1 + (S - 1) // N
+        pi = 3.141592653589793238462643383279502884
+        self.shifts = uniform_real(seed, context.allocate(S), S, 0.0, 2 * pi)
+        self.B = rademacher(seed, context.allocate(nb * N), nb * N, order)
+        self.G = normal(seed, context.allocate(nb * N), nb * N)
+        praw, _ = raw_draws(seed, context.allocate(nb * (N - 1)), nb * (N - 1))
+        self.P = np.array([int(praw[i * (N - 1) + l]) % (N - l) for i in range(nb) for l in range(N - 1)],
+                          dtype=np.int64)
+        self.nb, self.scale = nb, math.sqrt(2.0 / S)
+        self.Sm = np.full(nb * N, 1.0 / (self.sigma * math.sqrt(N)))
+
+    def apply(self, A, dim="columnwise"):
+        import scipy.fft
+        A = np.asarray(A, dtype=np.float64)
+        X = A if dim in (0, "columnwise") else A.T
+        N, S = self.N, self.S
+        scal = math.sqrt(N) * (1.0 / math.sqrt(2.0 * N))
+        out = np.empty((S, X.shape[1]))
+        for c in range(X.shape[1]):
+            ac = X[:, c]
+            for i in range(self.nb):
+                s0, e0 = i * N, min((i + 1) * N, S)
+                w = self.B[i * N:(i + 1) * N] * ac
+                w = scipy.fft.dct(w, type=2)
+                for l in range(N - 1):
+                    i1, i2 = N - 1 - l, self.P[i * (N - 1) + l]
+                    w[i1], w[i2] = w[i2], w[i1]
+                w = (scal * self.G[i * N:(i + 1) * N]) * w
+                w = scipy.fft.dct(w, type=2)
+                w = (scal * self.Sm[i * N:(i + 1) * N]) * w
+                out[s0:e0, c] = self.scale * np.cos(w[:e0 - s0] + self.shifts[s0:e0])
+        return out if dim in (0, "columnwise") else out.T
+
+
+class PPT(_Transform):
+    """TensorSketch: sketch/PPT_data.hpp:83-99 (q CWTs, then q hash positions, then q signs) and the
+    apply of sketch/PPT_Elemental.hpp:140-185 (r2c FFT of every CountSketch, product, c2r / S)."""
+    sketch_type = "PPT"
+
+    def __init__(self, N, S, q, c, gamma, context, order=BOOST_160):
+        super().__init__(N, S, context)
+        self.q, self.c, self.gamma = int(q), float(c), float(gamma)
+        self.cwts = [CWT(N, S, context, order) for _ in range(self.q)]
+        seed = context.seed
+        self.hash_idx = uniform_int(seed, context.allocate(self.q), self.q, S - 1).astype(np.int64)
+        self.hash_val = rademacher(seed, context.allocate(self.q), self.q, order)
+
+    def apply(self, A, dim="columnwise"):
+        A = np.asarray(A, dtype=np.float64)
+        X = A if dim in (0, "columnwise") else A.T
+        P = np.ones((self.S // 2 + 1, X.shape[1]), dtype=np.complex128)
+        for i, cw in enumerate(self.cwts):
+            W = cw.apply(X, "columnwise") * math.sqrt(self.gamma)
+            W[self.hash_idx[i], :] += math.sqrt(self.c) * self.hash_val[i]
+            P *= np.fft.rfft(W, axis=0)
+        out = np.fft.irfft(P, n=self.S, axis=0)
+        return out if dim in (0, "columnwise") else out.T

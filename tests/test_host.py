@@ -101,8 +101,7 @@ def test_error_codes(sk):
 
 def test_reference_names_outside_the_path_fail_clearly(sk):
     from libskylark_b200 import errors
-    for name in ("SJLT", "SparseJLT", "PPT", "TensorSketch", "FastGaussianRFT", "Fastfood", "MaternRFT",
-                 "NURST", "GaussianQRFT", "ExpSemigroupRLT"):
+    for name in ("SJLT", "SparseJLT", "MaternRFT", "FastMaternRFT", "NURST", "GaussianQRFT", "ExpSemigroupRLT"):
         with pytest.raises(errors.UnsupportedError, match="outside the GPU sketch-apply path"):
             getattr(sk, name)(10, 5)
 
