@@ -516,10 +516,23 @@ def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
                 graph_ms[key] = None
                 graph_ms[key + "_error"] = repr(e)[:160]
                 torch.cuda.synchronize()
+        fused_ms = None
+        try:        # the reduce-scatter fused into the kernel (peer stores), result = s x d/world per rank
+            fn = lambda: sd.fjlt_wht_fused_reduce_scatter(S, A, rank * nloc)
+            fused_ms = timed(fn, 5)
+            got = fn()
+            err = rel(got[:, :CHK], S.apply(chk, None, "columnwise")) if rank == 0 else None
+            bcast_check(err)
+        except Exception as e:
+            graph_ms["fused_error"] = repr(e)[:200]
+            fused_ms = None
+            torch.cuda.synchronize()
         variants = {"overlapped all-reduce (4 column blocks)": res["allreduce"]["ms"],
                     "overlapped reduce-scatter (4 column blocks)": res["reduce_scatter"]["ms"],
                     "one kernel, then one all-reduce": ms_plain,
                     "one kernel, then one reduce-scatter": ms_plain_rs}
+        if fused_ms:
+            variants["reduce-scatter fused into the kernel (peer stores)"] = fused_ms
         if graph_ms.get("allreduce"):
             variants["overlapped all-reduce, CUDA graph"] = graph_ms["allreduce"]
         if graph_ms.get("reduce_scatter"):

@@ -126,6 +126,18 @@ int sl_apply_sketch_transform_shard(sl_sketch_transform_t *S, char *input_type, 
                                     char *output_type, void *SA, int dim,
                                     int64_t index_offset);
 
+/* Row-sharded FJLT (Walsh-Hadamard mode) with the reduce-scatter fused into the kernel -- what
+ * sketch/FJLT_Elemental.hpp:144-169 does with two redistributions, for a group of GPUs that can store
+ * into each other's memory.  A: this rank's rows [index_offset, ...) of the n x d matrix (device,
+ * column-major, d a multiple of `world`).  peer_ptrs_dev: DEVICE array of `world` pointers, entry r =
+ * the staging buffer of rank r as mapped into this process, each world * (d/world) * s doubles laid out
+ * [source rank][local column][sample].  The kernel writes the partial sketch of column j into slab `rank`
+ * of the buffer of rank j / (d/world) (plain stores over NVLink, no TMA); after all ranks' kernels have
+ * finished (a group barrier, the caller's job) every rank adds its `world` slabs.  scratch_dev: 148 * s
+ * doubles of local device memory.  Needs an even s <= 8192.  dist.fjlt_wht_fused_reduce_scatter drives it. */
+int sl_fjlt_apply_shard_peer(sl_sketch_transform_t *S, void *A, int64_t index_offset, void *peer_ptrs_dev,
+                             int world, int rank, void *scratch_dev);
+
 /* Options: "boost_order" = "160" (default; Boost >= 1.57 Rademacher draw order) | "155";
  * "fjlt_fut" = "dct" (default; what the reference computes) | "wht". */
 int sl_set_option(const char *key, const char *value);

@@ -1168,6 +1168,32 @@ int sl_rng_export_raw(int seed, uint64_t base, int64_t count, uint64_t *first, u
     SL_CATCH
 }
 
+// See include/skylark_b200.h.
+int sl_fjlt_apply_shard_peer(sl_sketch_transform_t *S, void *A_, int64_t index_offset, void *peer_ptrs_dev,
+                             int world, int rank, void *scratch_dev) {
+    SL_TRY
+    require_device();
+    if (!S || !A_ || !peer_ptrs_dev || !scratch_dev || world < 1 || rank < 0 || rank >= world)
+        throw error(SKB_ERR_INVALID_PARAM, "sl_fjlt_apply_shard_peer: bad argument");
+    sl_matrix_t *A = as_matrix(A_);
+    if (S->type != T_FJLT || S->fut != FUT_WHT || A->kind != MK_DENSE || !A->on_device || A->dtype != SL_DTYPE_F64)
+        throw error(SKB_ERR_UNSUPPORTED_BASE, "sl_fjlt_apply_shard_peer: needs an FJLT in Walsh-Hadamard mode and a "
+                                              "float64 device matrix");
+    if (A->n % world != 0)
+        throw error(SKB_ERR_INVALID_PARAM, "sl_fjlt_apply_shard_peer: the number of columns must be a multiple of the group size");
+    DeviceGuard g(A->device);
+    // a dummy SA wrapper of the right shape: the kernel sends its columns to the owners instead
+    sl_matrix_t SA = *A;
+    SA.m = S->S; SA.n = A->n; SA.ld = S->S; SA.data = scratch_dev;
+    fjlt_set_peer_out(reinterpret_cast<double *const *>(peer_ptrs_dev), reinterpret_cast<double *>(scratch_dev),
+                      (int)(A->n / world), rank, S->S);
+    try {
+        apply_device(S, A, &SA, SL_COLUMNWISE, index_offset, true, false);
+    } catch (...) { fjlt_set_peer_out(nullptr, nullptr, 0, 0, 0); throw; }
+    fjlt_set_peer_out(nullptr, nullptr, 0, 0, 0);
+    SL_CATCH
+}
+
 int sl_rng_export(int kind, int seed, uint64_t base, int64_t count, double a, double b, double *host_out) {
     SL_TRY
     require_device();

@@ -19,6 +19,22 @@
 
 namespace skb {
 
+// Fused reduce-scatter of a row-sharded sketch (multi-GPU): instead of its own OUT, the WHT kernel
+// sends the finished column j of this rank's partial sketch to the GPU that owns column j, into slab
+// `rank` of that GPU's staging buffer (plain stores to peer memory over NVLink).  The gather warps
+// first assemble the column in a local scratch line (their per-sample stores are scattered), then
+// copy it out in coalesced 16-byte pieces.  ptrs == nullptr: single-GPU behaviour.
+struct WhtPeerOut {
+    double *const *ptrs;     // device array: staging buffer of every rank, [world][cols_per_owner][S]
+    double *scratch;         // (number of CTAs) * S doubles, local
+    int cols_per_owner, rank;
+    int S;
+};
+static thread_local WhtPeerOut g_wht_peer = {nullptr, nullptr, 0, 0, 0};     // set around one apply
+void fjlt_set_peer_out(double *const *ptrs, double *scratch, int cols_per_owner, int rank, int S) {
+    g_wht_peer.ptrs = ptrs; g_wht_peer.scratch = scratch; g_wht_peer.cols_per_owner = cols_per_owner;
+    g_wht_peer.rank = rank; g_wht_peer.S = S;
+}
 static int g_sm_reserve = 0;
 void fjlt_set_sm_reserve(int sms) { g_sm_reserve = sms; }
 static unsigned fjlt_sms() { return (unsigned)(148 - (g_sm_reserve < 140 ? g_sm_reserve : 140)); }
@@ -122,7 +138,7 @@ static constexpr int WSMEM_BYTES = WNBUF * WBUF_BYTES + WG_THREADS * WSPT * 4;
 // named barriers: FULL one id per ring buffer; EMPTY one id per (ring buffer, butterfly group
 // that will refill it) -- with a shared id the other group, running ahead, could complete the
 // barrier in place of the group it was meant for; INNER one per butterfly group
-enum { WBAR_FULL = 1, WBAR_EMPTY = 4, WBAR_INNER = 10 };
+enum { WBAR_FULL = 1, WBAR_EMPTY = 4, WBAR_INNER = 10, WBAR_OUT = 12 };
 static constexpr int WREG_B = 168, WREG_G = 88;      // 256*168 + 256*88 = the whole register file
 #ifndef SKB_WHT_PF
 #define SKB_WHT_PF 4                 // L2 prefetch distance in segments (0 = off)
@@ -192,7 +208,7 @@ __global__ void __launch_bounds__(WTHREADS, 1)
 k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
                 const uint64_t *__restrict__ Dwht, const int32_t *__restrict__ slot_sample,
                 const int32_t *__restrict__ slot_out, size_t seg0, double inscale, double outscale,
-                double *__restrict__ OUT, size_t oi, size_t oj) {
+                double *__restrict__ OUT, size_t oi, size_t oj, WhtPeerOut peer) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const unsigned sbase = (unsigned)__cvta_generic_to_shared(smem_raw);
     const int tid = threadIdx.x;
@@ -315,10 +331,28 @@ k_fjlt_wht_cols(const double *__restrict__ X, size_t ldx, size_t N, size_t m,
                 if (it + WNBUF < total)           // item it+3 (other parity) refills this buffer
                     bar_arrive(WBAR_EMPTY + 2 * b + (int)((it + 1) & 1), WB_THREADS + WG_THREADS);
             }
+            if (peer.ptrs == nullptr) {
 #pragma unroll
-            for (int q = 0; q < WSPT; q++) {
-                const int i = slot_out[q * WG_THREADS + g];
-                if (i >= 0) OUT[(size_t)i * oi + j * oj] = scale * acc[q];
+                for (int q = 0; q < WSPT; q++) {
+                    const int i = slot_out[q * WG_THREADS + g];
+                    if (i >= 0) OUT[(size_t)i * oi + j * oj] = scale * acc[q];
+                }
+            } else {
+                double *loc = peer.scratch + (size_t)blockIdx.x * peer.S;
+#pragma unroll
+                for (int q = 0; q < WSPT; q++) {
+                    const int i = slot_out[q * WG_THREADS + g];
+                    if (i >= 0) loc[i] = scale * acc[q];
+                }
+                bar_sync(WBAR_OUT, WG_THREADS);                 // the column is complete in the scratch line
+                double *dst = peer.ptrs[j / peer.cols_per_owner] +
+                              ((size_t)peer.rank * peer.cols_per_owner + (j % peer.cols_per_owner)) * (size_t)peer.S;
+                for (int r = g * 2; r + 1 < peer.S; r += WG_THREADS * 2) {
+                    const double2 v = __ldcg(reinterpret_cast<const double2 *>(loc + r));
+                    *reinterpret_cast<double2 *>(dst + r) = v;
+                }
+                if ((peer.S & 1) && g == 0) dst[peer.S - 1] = __ldcg(loc + peer.S - 1);
+                bar_sync(WBAR_OUT, WG_THREADS);                 // before the next column reuses the line
             }
         }
     }
@@ -1476,12 +1510,14 @@ static void fjlt_apply_impl(int fut, bool layout_rows, const double *X, size_t l
         auto kern = al16 ? k_fjlt_wht_cols<true> : k_fjlt_wht_cols<false>;
         SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         unsigned grid = (unsigned)(m < fjlt_sms() ? m : fjlt_sms());
+        if (g_wht_peer.ptrs && (S > (size_t)WG_THREADS * WSPT || out_rows || (S & 1) || ((uintptr_t)g_wht_peer.scratch & 15)))
+            throw error(SKB_ERR_INVALID_USAGE, "FJLT peer output: needs an even s <= 8192 and column-major operands");
         const size_t per_pass = (size_t)WG_THREADS * WSPT;               // 8192 samples per pass
         for (size_t s0 = 0, p = 0; s0 < S; s0 += per_pass, p++) {
             LaunchScope ls(KC_FJLT, st);
             kern<<<grid, WTHREADS, smem, st>>>(Xc, ldc, nloc, m, Dwht, wht_slot_sample + p * per_pass,
                                                wht_slot_out + p * per_pass, offset >> WSEG_LOG,
-                                               inscale, outscale, OUT, oi, oj);
+                                               inscale, outscale, OUT, oi, oj, g_wht_peer);
             SKB_CUDA(cudaGetLastError());
         }
         return;

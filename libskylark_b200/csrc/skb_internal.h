@@ -170,6 +170,8 @@ size_t fjlt_dct_plan_bytes(size_t N, size_t S);
 void fjlt_dct_plan_build(size_t N, size_t S, const int32_t *samples, void *buf, cudaStream_t st);
 bool fjlt_shard_ok(int fut, size_t N, size_t offset, size_t nloc);
 void fjlt_set_sm_reserve(int sms);      // SMs the persistent FJLT kernels leave free
+// Peer-output mode of the WHT kernel for the calling thread's next applies (nullptr = off); see fjlt.cu.
+void fjlt_set_peer_out(double *const *ptrs, double *scratch, int cols_per_owner, int rank, int S);
 // Host-side layout of the sampled gather of the WHT kernel (see fjlt.cu).
 void fjlt_build_wht_slots(const int32_t *samples, size_t S, std::vector<int32_t> &slot_sample,
                           std::vector<int32_t> &slot_out);

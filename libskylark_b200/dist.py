@@ -302,3 +302,53 @@ def fjlt_apply_row_sharded(S, A_local, group=None, gather=True):
     if not gather:
         return SA_loc, (c0, dloc)
     return gather_columns(SA_loc, A_local.shape[1], group)
+
+
+# ---------------------------------------------------------------------------
+# FJLT (Walsh-Hadamard mode) on row shards with the reduce-scatter fused into the kernel
+# ---------------------------------------------------------------------------
+_fused_state = {}
+
+
+def fjlt_wht_fused_reduce_scatter(S, A_local, index_offset, group=None):
+    """Columnwise FJLT (fjlt_fut = wht) of a row-sharded matrix in ONE kernel per rank: every rank
+    sketches its rows (A_local: n_loc x d CUDA tensor, column-major) and the kernel itself sends each
+    finished column of its partial sketch to the GPU that owns that column (stores into peer memory
+    over NVLink, torch symmetric memory for the mapping) -- no separate collective.  After a group
+    barrier each rank adds the `world` slabs it received.  Returns this rank's s x (d / world) slice
+    of the sketch (column-major), columns [rank * d / world, ...).  Needs d % world == 0 and an even
+    s <= 8192; the reference reaches the same result through two redistributions
+    (sketch/FJLT_Elemental.hpp:144-169)."""
+    import ctypes
+    import torch
+    import torch.distributed as dist
+    import torch.distributed._symmetric_memory as symm
+    from . import lib
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    s, d = S.getsketchdim(), A_local.shape[1]
+    if d % world:
+        raise ValueError("the number of columns (%d) must be a multiple of the group size (%d)" % (d, world))
+    if not (A_local.is_cuda and A_local.dtype == torch.float64 and A_local.stride(0) == 1):
+        raise ValueError("A_local must be a column-major float64 CUDA tensor")
+    cpo = d // world
+    pg = group if group is not None else dist.group.WORLD
+    key = (id(pg), s, d, A_local.device.index)
+    st = _fused_state.get(key)
+    if st is None:
+        stage = symm.empty((world, cpo, s), dtype=torch.float64, device=A_local.device)
+        hdl = symm.rendezvous(stage, pg.group_name)
+        scratch = torch.empty(148 * s, dtype=torch.float64, device=A_local.device)
+        st = _fused_state[key] = (stage, hdl, scratch)
+    stage, hdl, scratch = st
+    A = lib.adapt(A_local)
+    lib.set_stream_from_torch()
+    hdl.barrier(channel=0)                       # every rank has finished reading its previous slabs
+    Aobj = A.ptr()
+    try:
+        lib.callsl("sl_fjlt_apply_shard_peer", S._obj, Aobj, ctypes.c_int64(int(index_offset)),
+                   ctypes.c_void_p(int(hdl.buffer_ptrs_dev)), ctypes.c_int(world), ctypes.c_int(rank),
+                   ctypes.c_void_p(scratch.data_ptr()))
+    finally:
+        A.ptrcleaner()
+    hdl.barrier(channel=0)                       # every rank's columns have arrived
+    return stage.sum(dim=0).t()                  # (d/world, s) storage = column-major s x d/world

@@ -66,6 +66,16 @@ def main():
                       for b0, b1 in zip(edges, edges[1:])], dim=1)
     checks["FJLT-WHT overlapped reduce_scatter"] = rel(got, mine)
 
+    try:        # reduce-scatter fused into the kernel (stores into peer memory)
+        got = sd.fjlt_wht_fused_reduce_scatter(F, Ac[off:off + cnt], off)
+        cpo = d // world
+        for _ in range(2):      # twice: the staging slabs are reused
+            got = sd.fjlt_wht_fused_reduce_scatter(F, Ac[off:off + cnt], off)
+        checks["FJLT-WHT fused peer-store reduce-scatter"] = rel(got, full[:, rank * cpo:(rank + 1) * cpo])
+    except Exception as e:
+        print("rank %d fused peer path failed: %r" % (rank, e), flush=True)
+        checks["FJLT-WHT fused peer-store reduce-scatter"] = 1.0
+
     # --- FJLT, DCT mode (what the reference computes): rows -> columns all-to-all, gather
     Fd = sketch.FJLT(n, s, lib.Context(78))
     full = Fd.apply(Ac, None, 0)
