@@ -494,9 +494,12 @@ def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
         # the overlapped forms again as CUDA graphs: at ~1 ms per step the host cannot enqueue four
         # kernels and four collectives fast enough, a replayed graph can
         graph_ms = {}
-        for key, red in (("allreduce", "allreduce"), ("reduce_scatter", "reduce_scatter")):
+        for key, red in (("allreduce", "allreduce"), ("reduce_scatter", "reduce_scatter"), ("plain_rs", "reduce_scatter")):
             try:
-                fn = lambda: sd.apply_distributed_overlapped(S, A, SA, "columnwise", rank * nloc, reduce=red, blocks=4)
+                if key == "plain_rs":
+                    fn = lambda: sd.apply_distributed(S, A, SA, "columnwise", rank * nloc, reduce="reduce_scatter")
+                else:
+                    fn = lambda: sd.apply_distributed_overlapped(S, A, SA, "columnwise", rank * nloc, reduce=red, blocks=4)
                 side = torch.cuda.Stream()
                 side.wait_stream(torch.cuda.current_stream())
                 with torch.cuda.stream(side):
@@ -537,6 +540,8 @@ def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
             variants["overlapped all-reduce, CUDA graph"] = graph_ms["allreduce"]
         if graph_ms.get("reduce_scatter"):
             variants["overlapped reduce-scatter, CUDA graph"] = graph_ms["reduce_scatter"]
+        if graph_ms.get("plain_rs"):
+            variants["one kernel, then one reduce-scatter, CUDA graph"] = graph_ms["plain_rs"]
         best = min(variants.values())
         return {"workload": "C3: FJLT(wht) fp64 2^20x2048 -> 8192 row-sharded over %d GPUs (strong scaling); "
                             "kernel of column block b+1 overlapped with the NCCL reduction of block b" % world,

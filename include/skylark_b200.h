@@ -214,6 +214,13 @@ int sl_device_count(int *count);
  * A with entries of equal (row, column) added in storage order and the rows of every column
  * sorted -- the merge step after ranks have exchanged sparse partial sketches. */
 int sl_sp_matrix_coalesce(void *A, void *SA);
+/* The same merge straight from the receive buffers of an all-to-all, without re-ordering them first:
+ * the partial sketches of `nseg` ranks lie one after the other (rank-major); entries of column j sent by
+ * rank r are indices/values[vptr[r * n_cols + j] .. vptr[r * n_cols + j + 1]) (device arrays, vptr has
+ * nseg * n_cols + 1 entries).  SA (device sparse wrapper) receives the n_rows x n_cols sum; equal
+ * (row, column) entries are added in rank order.  109 when a merged column has more than 10240 entries. */
+int sl_sp_merge_segments(const int32_t *vptr_dev, const int32_t *indices_dev, const double *values_dev, int nseg,
+                         int64_t n_rows, int64_t n_cols, int64_t nnz, void *SA);
 
 #ifdef __cplusplus
 }

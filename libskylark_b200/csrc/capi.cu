@@ -1265,6 +1265,27 @@ int sl_sp_matrix_coalesce(void *A_, void *SA_) {
     attach_sparse_result(SA, oi, ox, ov, onnz, A->m, A->n, A->device);
     SL_CATCH
 }
+// See include/skylark_b200.h.
+int sl_sp_merge_segments(const int32_t *vptr_dev, const int32_t *indices_dev, const double *values_dev, int nseg,
+                         int64_t n_rows, int64_t n_cols, int64_t nnz, void *SA_) {
+    SL_TRY
+    require_device();
+    sl_matrix_t *SA = as_matrix(SA_);
+    if (SA->kind != MK_SPARSE || !SA->on_device)
+        throw error(SKB_ERR_INVALID_USAGE, "sl_sp_merge_segments: SA must be a device sparse matrix");
+    if (!vptr_dev || nseg < 1 || n_rows < 0 || n_cols < 0 || nnz < 0)
+        throw error(SKB_ERR_INVALID_PARAM, "sl_sp_merge_segments: bad argument");
+    DeviceGuard g(SA->device);
+    static std::map<int, std::pair<void *, size_t>> ws_per_dev;      // grow-only scratch per device
+    auto &ws = ws_per_dev[SA->device];
+    int32_t *oi = nullptr, *ox = nullptr; double *ov = nullptr; size_t onnz = 0;
+    if (!hash_merge_segments(vptr_dev, indices_dev, values_dev, nseg, (size_t)n_cols, (size_t)n_rows, (size_t)nnz,
+                             &oi, &ox, &ov, &onnz, &ws.first, &ws.second, g_stream))
+        throw error(SKB_ERR_UNSUPPORTED_BASE, "sl_sp_merge_segments: a merged column exceeds 10240 entries (or the "
+                                              "input is empty); re-order and use sl_sp_matrix_coalesce");
+    attach_sparse_result(SA, oi, ox, ov, onnz, n_rows, n_cols, SA->device);
+    SL_CATCH
+}
 int sl_device_count(int *count) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }

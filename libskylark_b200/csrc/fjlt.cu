@@ -653,7 +653,12 @@ k_dct_pass2(DctPlan pl, cplx *__restrict__ H) {
 #define SKB_FFT_MINB 2
 #endif
 constexpr int FFT_PPT = SKB_FFT_PPT;
-constexpr size_t FFT_POINTS = 4096, FFT_THREADS = FFT_POINTS / FFT_PPT;
+#ifndef SKB_FFT_POINTS
+#define SKB_FFT_POINTS 4096     // complex points a CTA transforms at a time (4096 or 2048)
+#endif
+constexpr size_t FFT_POINTS = SKB_FFT_POINTS, FFT_THREADS = FFT_POINTS / FFT_PPT;
+constexpr int FFT_POINTS_LOG = FFT_POINTS == 4096 ? 12 : 11;
+static_assert(FFT_POINTS == 4096 || FFT_POINTS == 2048, "tile of 4096 or 2048 points");
 
 __device__ __forceinline__ cplx ldg_cplx(const cplx *p) {
     double2 v = __ldg(reinterpret_cast<const double2 *>(p));
@@ -768,7 +773,7 @@ constexpr size_t FFT_SMEM2 = (FFT_POINTS + (FFT_POINTS >> FFT_PPT_LOG) + 64) * s
 // tile.  Per pass kind a compact table of 16 + 256 butterfly twiddles; the inter-pass factors
 // W_N'^e = Thi[e >> 10] * Tlo[e & 1023] when both tables fit (N <= 2^21).
 constexpr int TW_COMPACT = FFT_PPT == 16 ? 16 + 256 : 8 + 64 + 512;
-constexpr int TT_SMEM_MAX = FFT_PPT == 16 ? 2048 : 0;     // with 8 points per thread the buffers take the room
+constexpr int TT_SMEM_MAX = (FFT_PPT == 16 && FFT_POINTS == 4096) ? 2048 : 0;     // otherwise the buffers take the room
 constexpr size_t FFT_SMEM2_TW = 2 * TW_COMPACT * sizeof(cplx);
 // W: table of W_L^m, m < L.  One region per twiddled pass, in pass order: a middle pass with
 // sub-length Ns holds W_L^(k L / (Ns R)), k < Ns (R = FFT_PPT); the last pass W_L^j, j < L / R_last.
@@ -902,7 +907,7 @@ __device__ __forceinline__ void mid_pass(cplx *buf, int L, int lshift, int Ns, c
 template <int R, bool SEQPAD, bool GFAST, class Sink>
 __device__ __forceinline__ void last_pass(const cplx *buf, int L, int lshift, const cplx *W, Sink sink) {
     constexpr int U = FFT_PPT / R;
-    const int Ns = L / R, nshift = 31 - __clz(Ns), gshift = 12 - lshift;     // G = 4096 / L sequences
+    const int Ns = L / R, nshift = 31 - __clz(Ns), gshift = FFT_POINTS_LOG - lshift;     // G = FFT_POINTS / L sequences
 #pragma unroll
     for (int uu = 0; uu < U; uu++) {
         const int u = (int)threadIdx.x + uu * (int)FFT_THREADS;
@@ -946,7 +951,7 @@ __device__ __forceinline__ void dct_tile_pass1(const DctFused &a, cplx *buf, siz
                                                const cplx *tw, const cplx *tt) {
     const DctPlan &pl = a.pl;
     const int N2 = (int)pl.N2, N1 = (int)pl.N1, lshift = 31 - __clz(N2);
-    const int G = (int)(FFT_POINTS / pl.N2), gshift = 12 - lshift, Gh = G >> 1, a0 = (int)tile * Gh;
+    const int G = (int)(FFT_POINTS / pl.N2), gshift = FFT_POINTS_LOG - lshift, Gh = G >> 1, a0 = (int)tile * Gh;
     const double *col = a.X + c * a.ldx;
     cplx *Hc = a.H + (c % a.nslot) * pl.Np;
     auto seq = [&](int g) { return g < Gh ? a0 + g : N1 - 1 - a0 - (g - Gh); };
@@ -1024,9 +1029,9 @@ __device__ __forceinline__ void dct_tile_pass2(const DctFused &a, cplx *buf, siz
     const int L = (int)pl.N1, lshift = 31 - __clz(L);
     const size_t base = (size_t)tile * FFT_POINTS;
     const cplx *rows = a.H + (c % a.nslot) * pl.Np + base;
-    if (threadIdx.x < FFT_POINTS / 32) {     // which of the tile's bins the samples need, and their ranks
-        s_need[threadIdx.x] = __ldg(pl.need + (base >> 5) + threadIdx.x);
-        s_rank[threadIdx.x] = __ldg(pl.rank + (base >> 5) + threadIdx.x);
+    for (int i = threadIdx.x; i < (int)(FFT_POINTS / 32); i += blockDim.x) {     // which of the tile's bins the samples need, and their ranks
+        s_need[i] = __ldg(pl.need + (base >> 5) + i);
+        s_rank[i] = __ldg(pl.rank + (base >> 5) + i);
     }
     {   // first pass (radix FFT_PPT) straight from global memory (rows are contiguous)
         const int per = L >> FFT_PPT_LOG, pshift = 31 - __clz(per);

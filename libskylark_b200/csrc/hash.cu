@@ -18,6 +18,7 @@
 //   * the strided layout and CSC input accumulate in shared memory per output
 //     column and dump coalesced columns.
 #include <algorithm>
+#include <map>
 #include <cstdlib>
 #include <cub/block/block_radix_sort.cuh>
 #include <cub/block/block_scan.cuh>
@@ -842,12 +843,18 @@ struct SpcTypes {
     static constexpr size_t smem_bytes = tmp_bytes + (size_t)CAP * 8 + ((size_t)CAP + 4) * 4;
 };
 
-template <int THREADS, int ITEMS>
+// SEG: the entries of column `col` are not one contiguous run but the concatenation of `nseg`
+// runs [vptr[s * ncols + col], vptr[s * ncols + col + 1]) -- the layout in which the partial
+// sketches of nseg ranks arrive from an all-to-all (rank-major) -- taken in segment order; rows are
+// their own buckets and values are taken as they are (a merge, not a sketch).
+template <int THREADS, int ITEMS, bool SEG>
 __global__ void __launch_bounds__(THREADS)
 k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ indices,
               const double *__restrict__ values, int ncols, const int32_t *__restrict__ bucket,
               const double *__restrict__ value, int pos_bits, int key_bits,
-              int32_t *__restrict__ tmp_idx, double *__restrict__ tmp_val, int32_t *__restrict__ cnt) {
+              int32_t *__restrict__ tmp_idx, double *__restrict__ tmp_val, int32_t *__restrict__ cnt,
+              const int32_t *__restrict__ vptr, int nseg) {
+    __shared__ int seg_pos[65], seg_src[64];
     using T = SpcTypes<THREADS, ITEMS>;
     constexpr int CAP = T::CAP;
     extern __shared__ __align__(16) unsigned char spc_smem[];
@@ -857,15 +864,35 @@ k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ in
     const uint32_t pmask = (1u << pos_bits) - 1u;
     for (int col = blockIdx.x; col < ncols; col += gridDim.x) {
         const int c0 = indptr[col], cn = indptr[col + 1] - c0;
+        if (SEG) {
+            if (threadIdx.x == 0) {
+                int p = 0;
+                for (int sg = 0; sg < nseg; sg++) {
+                    const int b = vptr[(size_t)sg * ncols + col];
+                    seg_pos[sg] = p; seg_src[sg] = b;
+                    p += vptr[(size_t)sg * ncols + col + 1] - b;
+                }
+                seg_pos[nseg] = p;
+            }
+            __syncthreads();
+        }
         uint32_t keys[ITEMS];
+        int sg = 0;
 #pragma unroll
         for (int t = 0; t < ITEMS; t++) {                // blocked: thread holds ITEMS consecutive entries
             const int i = threadIdx.x * ITEMS + t;
             keys[t] = 0xffffffffu;
             if (i < cn) {
-                const int row = indices[c0 + i];
-                keys[t] = ((uint32_t)bucket[row] << pos_bits) | (uint32_t)i;
-                svals[i] = __dmul_rn(values[c0 + i], value[row]);
+                if (SEG) {
+                    while (i >= seg_pos[sg + 1]) sg++;
+                    const int src = seg_src[sg] + (i - seg_pos[sg]);
+                    keys[t] = ((uint32_t)indices[src] << pos_bits) | (uint32_t)i;
+                    svals[i] = values[src];
+                } else {
+                    const int row = indices[c0 + i];
+                    keys[t] = ((uint32_t)bucket[row] << pos_bits) | (uint32_t)i;
+                    svals[i] = __dmul_rn(values[c0 + i], value[row]);
+                }
             }
         }
         // the radix sort is stable and the entries start in column order, so only the bucket
@@ -905,16 +932,17 @@ k_sp_col_sort(const int32_t *__restrict__ indptr, const int32_t *__restrict__ in
 template <int THREADS, int ITEMS>
 static void launch_sp_col_sort(const int32_t *indptr, const int32_t *indices, const double *values,
                                int ncols, const int32_t *bucket, const double *value, int pos_bits,
-                               int key_bits, int32_t *tmp_idx, double *tmp_val, int32_t *cnt, cudaStream_t st) {
+                               int key_bits, int32_t *tmp_idx, double *tmp_val, int32_t *cnt, cudaStream_t st,
+                               const int32_t *vptr = nullptr, int nseg = 0) {
     using T = SpcTypes<THREADS, ITEMS>;
-    auto kern = k_sp_col_sort<THREADS, ITEMS>;
+    auto kern = vptr ? k_sp_col_sort<THREADS, ITEMS, true> : k_sp_col_sort<THREADS, ITEMS, false>;
     SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::smem_bytes));
     size_t per_sm = (size_t)(220 * 1024) / T::smem_bytes;
     if (per_sm * THREADS > 2048) per_sm = 2048 / THREADS;
     if (per_sm < 1) per_sm = 1;
     const unsigned grid = (unsigned)std::min<size_t>((size_t)ncols, 148 * per_sm);
     kern<<<grid, THREADS, T::smem_bytes, st>>>(indptr, indices, values, ncols, bucket, value, pos_bits,
-                                               key_bits, tmp_idx, tmp_val, cnt);
+                                               key_bits, tmp_idx, tmp_val, cnt, vptr, nseg);
     SKB_CUDA(cudaGetLastError());
 }
 
@@ -946,9 +974,10 @@ static bool sparse_columnwise_fast(const int32_t *indptr, const int32_t *indices
                                    size_t ncols, size_t nnz, const int32_t *bucket, const double *value,
                                    int S, int32_t **out_indptr, int32_t **out_indices,
                                    double **out_values, size_t *out_nnz, void **ws, size_t *ws_bytes,
-                                   cudaStream_t st) {
+                                   cudaStream_t st, const int32_t *vptr = nullptr, int nseg = 0) {
     static const bool off = getenv("SKB_DEBUG_SP_GENERIC") != nullptr;
-    if (off || nnz == 0 || ncols == 0 || nnz / ncols < 256) return false;   // short columns: the global sort wins
+    if (nnz == 0 || ncols == 0) return false;
+    if (!vptr && (off || nnz / ncols < 256)) return false;   // short columns: the global sort wins
     auto al = [](size_t b) { return (b + 255) / 256 * 256; };
     size_t scan_bytes = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (int32_t *)nullptr, (int32_t *)nullptr, (int)ncols + 1, st);
@@ -985,11 +1014,11 @@ static bool sparse_columnwise_fast(const int32_t *indptr, const int32_t *indices
     {
         LaunchScope ls(KC_HASH, st);
         const int kb = pos_bits + bucket_bits, nc = (int)ncols;
-        if (cap == 512) launch_sp_col_sort<256, 2>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st);
-        else if (cap == 1024) launch_sp_col_sort<256, 4>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st);
-        else if (cap == 2048) launch_sp_col_sort<256, 8>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st);
-        else if (cap == 5120) launch_sp_col_sort<512, 10>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st);
-        else launch_sp_col_sort<512, 20>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st);
+        if (cap == 512) launch_sp_col_sort<256, 2>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st, vptr, nseg);
+        else if (cap == 1024) launch_sp_col_sort<256, 4>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st, vptr, nseg);
+        else if (cap == 2048) launch_sp_col_sort<256, 8>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st, vptr, nseg);
+        else if (cap == 5120) launch_sp_col_sort<512, 10>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st, vptr, nseg);
+        else launch_sp_col_sort<512, 20>(indptr, indices, values, nc, bucket, value, pos_bits, kb, tmp_idx, tmp_val, cnt, st, vptr, nseg);
     }
     {
         LaunchScope ls(KC_HASH, st);
@@ -1008,6 +1037,48 @@ static bool sparse_columnwise_fast(const int32_t *indptr, const int32_t *indices
     }
     *out_nnz = (size_t)nout;
     return true;
+}
+
+__global__ void k_seg_col_counts(const int32_t *__restrict__ vptr, int nseg, int ncols, int32_t *__restrict__ cnt) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j > ncols) return;
+    int c = 0;
+    if (j < ncols)
+        for (int sg = 0; sg < nseg; sg++) c += vptr[(size_t)sg * ncols + j + 1] - vptr[(size_t)sg * ncols + j];
+    cnt[j] = c;
+}
+
+// Merge of nseg rank-major CSC pieces (see k_sp_col_sort<.., SEG>): entries of equal (row, column)
+// are added in segment order, rows of every column come out sorted.  colbase: caller-provided scratch
+// of ncols + 1 ints.  Returns false when a merged column exceeds the shared-memory sort's capacity.
+bool hash_merge_segments(const int32_t *vptr, const int32_t *indices, const double *values, int nseg,
+                         size_t ncols, size_t nrows, size_t nnz, int32_t **out_indptr, int32_t **out_indices,
+                         double **out_values, size_t *out_nnz, void **ws, size_t *ws_bytes, cudaStream_t st) {
+    *out_indptr = nullptr; *out_indices = nullptr; *out_values = nullptr; *out_nnz = 0;
+    if (nseg < 1 || nseg > 64 || nnz > 0x7fffffffULL || ncols > 0x7ffffffeULL)
+        throw error(SKB_ERR_INVALID_PARAM, "sparse merge: bad sizes");
+    static std::map<int, std::pair<int32_t *, size_t>> base_per_dev;
+    int dev = 0;
+    SKB_CUDA(cudaGetDevice(&dev));
+    auto &cb = base_per_dev[dev];
+    size_t scan_bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (int32_t *)nullptr, (int32_t *)nullptr, (int)ncols + 1, st);
+    const size_t need = (ncols + 1) * 2 * sizeof(int32_t) + scan_bytes + 512;
+    if (cb.second < need) {
+        SKB_CUDA(cudaStreamSynchronize(st));
+        cudaFree(cb.first); cb.first = nullptr; cb.second = 0;
+        SKB_CUDA(cudaMalloc(&cb.first, need));
+        cb.second = need;
+    }
+    int32_t *cnt = cb.first, *colbase = cb.first + (ncols + 1);
+    void *scan_tmp = colbase + (ncols + 1);
+    {
+        LaunchScope ls(KC_HASH, st);
+        k_seg_col_counts<<<(unsigned)((ncols + 1 + 255) / 256), 256, 0, st>>>(vptr, nseg, (int)ncols, cnt);
+        SKB_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, cnt, colbase, (int)ncols + 1, st));
+    }
+    return sparse_columnwise_fast(colbase, indices, values, ncols, nnz, nullptr, nullptr, (int)nrows, out_indptr,
+                                  out_indices, out_values, out_nnz, ws, ws_bytes, st, vptr, nseg);
 }
 
 void hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices, const double *values,

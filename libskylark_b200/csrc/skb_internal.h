@@ -120,6 +120,12 @@ void hash_apply_csc_sparse(const int32_t *indptr, const int32_t *indices, const 
                            int32_t **out_indptr, int32_t **out_indices, double **out_values,
                            size_t *out_nnz, void **ws, size_t *ws_bytes, cudaStream_t st);
 void hash_sparse_free(void *p, cudaStream_t st);
+// Merge of nseg rank-major CSC pieces: column j = concatenation over s of entries
+// [vptr[s*ncols + j], vptr[s*ncols + j + 1]); equal (row, column) entries are added in segment
+// order, rows come out sorted.  false = a merged column is too long for the shared-memory sort.
+bool hash_merge_segments(const int32_t *vptr, const int32_t *indices, const double *values, int nseg,
+                         size_t ncols, size_t nrows, size_t nnz, int32_t **out_indptr, int32_t **out_indices,
+                         double **out_values, size_t *out_nnz, void **ws, size_t *ws_bytes, cudaStream_t st);
 
 // ---- dense transforms (dense.cu) -------------------------------------------
 enum DenseDist { DD_NORMAL = 0, DD_CAUCHY = 1 };

@@ -81,7 +81,7 @@ def apply_distributed(S, A_local, SA=None, dim=0, index_offset=0, group=None,
     return reduce_partial(SA, group, reduce, dst)
 
 
-def exchange_sparse_partials(indptr, indices, values, group=None):
+def exchange_sparse_partials(indptr, indices, values, group=None, reorder=True):
     """Column-block all-to-all of sparse partial sketches (the sparse form of the reduce-scatter
     above).  Every rank passes its partial s x d sketch as CSC tensors (int32 indptr/indices,
     float64 values; CUDA with NCCL, CPU with gloo).  Rank r receives, for its block of columns
@@ -115,6 +115,12 @@ def exchange_sparse_partials(indptr, indices, values, group=None):
                            input_split_sizes=send_entries, group=group)
     dist.all_to_all_single(rval, values.contiguous(), output_split_sizes=recv_entries,
                            input_split_sizes=send_entries, group=group)
+    if not reorder:
+        # leave the pieces as they arrived (rank-major) and describe them: entries of column j from
+        # rank r are [vptr[r * ncols + j], vptr[r * ncols + j + 1]) -- what sl_sp_merge_segments reads
+        vptr = torch.zeros(world * ncols + 1, dtype=torch.int32, device=dev)
+        vptr[1:] = torch.cumsum(recv_counts, 0, dtype=torch.int32) if total < 2 ** 31 else 0
+        return vptr, ridx, rval, (col0, ncols)
     # received order is (rank, column); wanted order is (column, rank)
     per_col = C.sum(dim=0)
     out_indptr = torch.zeros(ncols + 1, dtype=torch.int64, device=dev)
@@ -138,12 +144,47 @@ def apply_distributed_sparse(S, A_local, index_offset=0, group=None):
     Returns (lib.DeviceCSC of shape s x columns_of_this_rank, (first_column, columns)).  For
     sketches much sparser than s x d this moves nnz*12 bytes instead of the s*d*8 bytes of the
     dense reduce-scatter (config C4: 1.5 GB instead of 16 GB per GPU)."""
+    import torch
     from . import lib, sketch
     part = S.apply_shard(A_local, lib.DeviceCSC.empty((S.getsketchdim(), A_local.shape[1]), "csc",
                                                        A_local.values.device), 0, index_offset)
+    import torch.distributed as dist
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+    if world > 1 and part.values.is_cuda:
+        # merge straight from the receive buffers (no re-ordering pass); falls back when a merged
+        # column is too long for the shared-memory sort
+        vptr, ix, vv, (c0, nc) = exchange_sparse_partials(part.indptr, part.indices, part.values, group,
+                                                          reorder=False)
+        try:
+            return sketch.merge_segments(vptr, ix, vv, world, (S.getsketchdim(), nc)), (c0, nc)
+        except Exception:
+            flat = (vptr[1:] - vptr[:-1]).to(torch.int64).view(world, nc)
+            ip, ix, vv = _reorder_segments(flat, ix, vv)
+            return sketch.coalesce(lib.DeviceCSC(ip, ix, vv, (S.getsketchdim(), nc), "csc")), (c0, nc)
     ip, ix, vv, (c0, nc) = exchange_sparse_partials(part.indptr, part.indices, part.values, group)
     merged = lib.DeviceCSC(ip, ix, vv, (S.getsketchdim(), nc), "csc")
     return sketch.coalesce(merged), (c0, nc)
+
+
+def _reorder_segments(C, ridx, rval):
+    """(rank, column)-ordered entries -> CSC with every column's entries in rank order."""
+    import torch
+    dev = ridx.device
+    world, ncols = C.shape
+    total = int(ridx.numel())
+    per_col = C.sum(dim=0)
+    out_indptr = torch.zeros(ncols + 1, dtype=torch.int64, device=dev)
+    out_indptr[1:] = torch.cumsum(per_col, 0)
+    flat = C.reshape(-1)
+    src_start = torch.cumsum(flat, 0) - flat
+    dst_start = (out_indptr[:-1].unsqueeze(0) + torch.cumsum(C, 0) - C).reshape(-1)
+    seg = torch.repeat_interleave(torch.arange(flat.numel(), device=dev), flat)
+    dest = dst_start[seg] + (torch.arange(total, device=dev) - src_start[seg])
+    oidx = torch.empty_like(ridx)
+    oval = torch.empty_like(rval)
+    oidx[dest] = ridx
+    oval[dest] = rval
+    return out_indptr.to(torch.int32), oidx, oval
 
 
 # ---------------------------------------------------------------------------
@@ -335,19 +376,25 @@ def fjlt_wht_fused_reduce_scatter(S, A_local, index_offset, group=None):
     key = (id(pg), s, d, A_local.device.index)
     st = _fused_state.get(key)
     if st is None:
-        stage = symm.empty((world, cpo, s), dtype=torch.float64, device=A_local.device)
-        hdl = symm.rendezvous(stage, pg.group_name)
+        # two staging sets used alternately: a rank may start writing set k % 2 of step k as soon as it
+        # has passed the barrier of step k - 1, by which time every owner has finished adding its slabs
+        # of step k - 2 (stream order) -- one barrier per step instead of two
+        sets = []
+        for _ in range(2):
+            stage = symm.empty((world, cpo, s), dtype=torch.float64, device=A_local.device)
+            sets.append((stage, symm.rendezvous(stage, pg.group_name)))
         scratch = torch.empty(148 * s, dtype=torch.float64, device=A_local.device)
-        st = _fused_state[key] = (stage, hdl, scratch)
-    stage, hdl, scratch = st
+        sets[0][1].barrier(channel=0)
+        st = _fused_state[key] = {"sets": sets, "scratch": scratch, "step": 0}
+    stage, hdl = st["sets"][st["step"] & 1]
+    st["step"] += 1
     A = lib.adapt(A_local)
     lib.set_stream_from_torch()
-    hdl.barrier(channel=0)                       # every rank has finished reading its previous slabs
     Aobj = A.ptr()
     try:
         lib.callsl("sl_fjlt_apply_shard_peer", S._obj, Aobj, ctypes.c_int64(int(index_offset)),
                    ctypes.c_void_p(int(hdl.buffer_ptrs_dev)), ctypes.c_int(world), ctypes.c_int(rank),
-                   ctypes.c_void_p(scratch.data_ptr()))
+                   ctypes.c_void_p(st["scratch"].data_ptr()))
     finally:
         A.ptrcleaner()
     hdl.barrier(channel=0)                       # every rank's columns have arrived

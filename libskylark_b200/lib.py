@@ -58,7 +58,7 @@ def _load():
                  "sl_sketch_export_dense", "sl_rng_export_raw", "sl_profile_enable",
                  "sl_profile_reset", "sl_profile_read", "sl_host_alloc_pinned",
                  "sl_host_free_pinned", "sl_device_count", "sl_rng_export", "sl_context_allocate",
-                 "sl_fjlt_apply_shard_peer"):
+                 "sl_fjlt_apply_shard_peer", "sl_sp_merge_segments", "sl_sp_matrix_coalesce"):
         getattr(L, name).restype = c_int
     L.sl_strerror.restype = c_char_p
     L.sl_supported_sketch_transforms.restype = c_char_p
@@ -79,6 +79,7 @@ def _load():
     L.sl_rng_export_raw.argtypes = (c_int, c_uint64, c_int64, c_void_p, c_void_p)
     L.sl_rng_export.argtypes = (c_int, c_int, c_uint64, c_int64, c_double, c_double, c_void_p)
     L.sl_context_allocate.argtypes = (c_void_p, c_uint64, c_void_p)
+    L.sl_sp_merge_segments.argtypes = (c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p)
     L.sl_fjlt_apply_shard_peer.argtypes = (c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int, c_void_p)
     L.sl_set_stream.argtypes = (c_void_p,)
     L.sl_host_alloc_pinned.argtypes = (c_size_t, c_void_p)

@@ -62,6 +62,22 @@ def coalesce(A):
     return out
 
 
+def merge_segments(vptr, indices, values, nseg, shape):
+    """Adds `nseg` rank-major CSC pieces as they arrive from an all-to-all (sl_sp_merge_segments;
+    see dist.exchange_sparse_partials(reorder=False)).  Returns a lib.DeviceCSC of `shape`."""
+    out = lib.DeviceCSC.empty(shape, "csc", values.device)
+    o = lib.DeviceCSCAdapter(out)
+    lib.set_stream_from_torch()
+    op = o.ptr()
+    try:
+        lib.callsl("sl_sp_merge_segments", c_void_p(vptr.data_ptr()), c_void_p(indices.data_ptr()),
+                   c_void_p(values.data_ptr()), ctypes.c_int(int(nseg)), ctypes.c_int64(int(shape[0])),
+                   ctypes.c_int64(int(shape[1])), ctypes.c_int64(int(indices.numel())), op)
+    finally:
+        o.ptrcleaner()
+    return out
+
+
 def deserialize_sketch(sketch_dict):
     """Rebuild a transform from `.serialize()` output (sketch.py:33-42)."""
     sketch_transform = c_void_p()

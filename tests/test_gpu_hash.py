@@ -352,3 +352,33 @@ def test_strided_layout_planned_kernel(sk, oracle, T, shape):
     cut = (n // 3) | 1
     parts = S.apply_shard(A[:cut], None, 0, 0) + S.apply_shard(A[cut:], None, 0, cut)
     assert rel_fro(parts.cpu().numpy(), want) < TOL
+
+
+@pytest.mark.parametrize("nseg,shape", [(3, (500, 40)), (8, (20000, 64)), (2, (7, 3))])
+def test_device_merge_segments(sk, nseg, shape):
+    """sl_sp_merge_segments: rank-major CSC pieces (the receive buffers of the sparse exchange) added
+    without re-ordering them; pattern and values against scipy's sum of the pieces."""
+    import scipy.sparse
+    import torch
+    m, n = shape
+    rng = np.random.default_rng(5)
+    dens = min(0.5, 600.0 / m)
+    pieces = [scipy.sparse.random(m, n, dens, format="csc", random_state=int(rng.integers(1 << 30)), dtype=np.float64)
+              for _ in range(nseg)]
+    for p in pieces:
+        p.sort_indices()
+    want = sum(pieces[1:], pieces[0]).tocsc()
+    want.sort_indices()
+    idx = np.concatenate([p.indices for p in pieces]).astype(np.int32)
+    val = np.concatenate([p.data for p in pieces])
+    vptr = np.zeros(nseg * n + 1, dtype=np.int32)
+    vptr[1:] = np.cumsum(np.concatenate([np.diff(p.indptr) for p in pieces]))
+    got = sk.merge_segments(torch.from_numpy(vptr).cuda(), torch.from_numpy(idx).cuda(), torch.from_numpy(val).cuda(),
+                            nseg, (m, n)).to_scipy()
+    got.sort_indices()
+    # entries that cancel to zero stay stored, as in the sketch itself: compare as dense plus pattern superset
+    assert np.allclose(got.toarray(), want.toarray(), rtol=1e-13, atol=1e-13)
+    assert got.indptr[-1] >= want.indptr[-1] and np.all(np.diff(got.indptr) >= 0)
+    for j in range(n):
+        rows = got.indices[got.indptr[j]:got.indptr[j + 1]]
+        assert np.all(np.diff(rows) > 0)                    # sorted, merged (no duplicates)
