@@ -526,6 +526,27 @@ def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
             got = fn()
             err = rel(got[:, :CHK], S.apply(chk, None, "columnwise")) if rank == 0 else None
             bcast_check(err)
+            # as a CUDA graph of TWO steps (the two staging sets alternate, so a graph must hold both)
+            try:
+                side = torch.cuda.Stream()
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    fn(); fn()
+                torch.cuda.current_stream().wait_stream(side)
+                torch.cuda.synchronize(); dist.barrier()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    fn()
+                    keep = fn()
+                graph_ms["fused"] = timed(g.replay, 5) / 2.0
+                g.replay()
+                torch.cuda.synchronize()
+                err = rel(keep[:, :CHK], S.apply(chk, None, "columnwise")) if rank == 0 else None
+                bcast_check(err)
+                del g, keep
+            except Exception as e:
+                graph_ms["fused_graph_error"] = repr(e)[:160]
+                torch.cuda.synchronize()
         except Exception as e:
             graph_ms["fused_error"] = repr(e)[:200]
             fused_ms = None
@@ -540,6 +561,8 @@ def multi_gpu_configs(torch, dist, lib, sketch, rank, world, hbm_gbs):
             variants["overlapped all-reduce, CUDA graph"] = graph_ms["allreduce"]
         if graph_ms.get("reduce_scatter"):
             variants["overlapped reduce-scatter, CUDA graph"] = graph_ms["reduce_scatter"]
+        if graph_ms.get("fused"):
+            variants["reduce-scatter fused into the kernel, CUDA graph of two steps"] = graph_ms["fused"]
         if graph_ms.get("plain_rs"):
             variants["one kernel, then one reduce-scatter, CUDA graph"] = graph_ms["plain_rs"]
         best = min(variants.values())
