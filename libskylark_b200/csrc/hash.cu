@@ -12,11 +12,16 @@
 //     C-ordered "columnwise" sketch takes), rows are grouped by bucket once per
 //     transform (stable radix sort) so that the apply is a gather-side segmented
 //     sum: each warp streams <=32 whole rows of one bucket with 128-bit loads and
-//     writes one 64-column slice of one output row.  No atomics unless a bucket is
-//     longer than 32 rows, and rows inside a bucket are added in ascending order
-//     with separate multiply and add, i.e. the reference's own rounding sequence.
-//   * the strided layout and CSC input accumulate in shared memory per output
-//     column and dump coalesced columns.
+//     writes one 64-column slice of one output row.  Rows inside a chunk are added in
+//     ascending order with separate multiply and add, i.e. the reference's own rounding
+//     sequence; a bucket of <= 32 rows is one chunk and is stored plainly (bit-identical to
+//     the reference loop, identical from run to run).  A longer bucket spans several chunks
+//     whose sums meet in red.f64: the result is then correct to rounding but its low bits
+//     depend on the order in which the atomics land -- the same holds for the strided kernels
+//     when the index is split over CTAs (ksplit > 1), for the CSC rowwise kernel and for the
+//     stream-K flush of the dense GEMM.  Tests compare those with a tolerance, not bitwise.
+//   * the strided layout accumulates in shared memory without atomics (lane-owned buckets,
+//     K2p) and the CSC input per output column (shared atomics), both dump coalesced columns.
 #include <algorithm>
 #include <map>
 #include <cstdlib>
