@@ -452,6 +452,7 @@ struct DctPlan {
     // Zc = per column the needed bins in position order (stride zc_ld)
     uint32_t *need, *rank;
     cplx *Zc; size_t zc_ld;
+    uint32_t *pmask;          // fused engine: per (pass-2 tile, thread) the needed last-pass outputs
 };
 
 __device__ __forceinline__ size_t dct_pos(const DctPlan &pl, size_t k) {     // bin k -> position in H
@@ -795,6 +796,7 @@ struct DctFused {
     cplx *H;                 // ring: DCT_NSLOT * Np
     cplx *Zc;                // ring: DCT_NZ * zc_ld
     const int32_t *pidx;     // per sample: position of Z[k'] and of Z[N'-k'] in a column's kept bins
+    const uint32_t *pmask;   // per (pass-2 tile, thread): which of its last-pass outputs are needed
     unsigned *ctr;           // [0] item counter | ready1[m] | done2[m] | postdone[m]
     double *OUT; size_t oi, oj;
     unsigned T;              // tiles per column per pass = Np / 4096
@@ -877,6 +879,16 @@ template <int R> __device__ __forceinline__ void twiddle_inputs(cplx *a, const c
 }
 
 // middle pass, in place in shared memory (all reads, barrier, all writes, barrier)
+#ifdef SKB_K8_NOADD
+constexpr bool K8_ADD = false;
+#else
+constexpr bool K8_ADD = true;
+#endif
+#ifdef SKB_K8_NOPMASK
+constexpr bool K8_PMASK = false;
+#else
+constexpr bool K8_PMASK = true;
+#endif
 template <int R, bool SEQPAD>
 __device__ __forceinline__ void mid_pass(cplx *buf, int L, int lshift, int Ns, const cplx *W) {
     constexpr int U = FFT_PPT / R;
@@ -896,8 +908,16 @@ __device__ __forceinline__ void mid_pass(cplx *buf, int L, int lshift, int Ns, c
 #pragma unroll
     for (int uu = 0; uu < U; uu++) {
         butterfly<R>(a[uu]);
+        if (K8_ADD && FFT_PPT == 16) {
+            // the middle pass has Ns = 16: dbase + 16 q moves one more padding element per step, and
+            // padx is additive there (no carry out of the low 8 bits, same sequence)
+            cplx *dst = buf + padx<SEQPAD>(dbase[uu], lshift);
 #pragma unroll
-        for (int q = 0; q < R; q++) buf[padx<SEQPAD>(dbase[uu] + q * Ns, lshift)] = a[uu][q];
+            for (int q = 0; q < R; q++) dst[q * 17] = a[uu][q];
+        } else {
+#pragma unroll
+            for (int q = 0; q < R; q++) buf[padx<SEQPAD>(dbase[uu] + q * Ns, lshift)] = a[uu][q];
+        }
     }
     __syncthreads();
 }
@@ -914,11 +934,19 @@ __device__ __forceinline__ void last_pass(const cplx *buf, int L, int lshift, co
         const int g = GFAST ? (u & ((1 << gshift) - 1)) : (u >> nshift);
         const int j = GFAST ? (u >> gshift) : (u & (Ns - 1));
         cplx a[R];
+        if (K8_ADD && FFT_PPT == 16) {
+            // Ns is 16 or 256 here, and padx is additive in t along that stride
+            const cplx *src = buf + padx<SEQPAD>(g * L + j, lshift);
+            const int c = Ns + (Ns >> 4) + ((!SEQPAD && Ns == 256) ? 1 : 0);
 #pragma unroll
-        for (int t = 0; t < R; t++) a[t] = buf[padx<SEQPAD>(g * L + j + t * Ns, lshift)];
+            for (int t = 0; t < R; t++) a[t] = src[t * c];
+        } else {
+#pragma unroll
+            for (int t = 0; t < R; t++) a[t] = buf[padx<SEQPAD>(g * L + j + t * Ns, lshift)];
+        }
         twiddle_inputs<R>(a, W, j);                 // step = 1
         butterfly<R>(a);
-        sink(g, j, Ns, a);
+        sink(g, j, Ns, a, uu);
     }
 }
 
@@ -997,7 +1025,11 @@ __device__ __forceinline__ void dct_tile_pass1(const DctFused &a, cplx *buf, siz
         __syncthreads();
         butterfly<FFT_PPT>(v);
 #pragma unroll
-        for (int q = 0; q < FFT_PPT; q++) buf[padx<true>(g * N2 + j * FFT_PPT + q, lshift)] = v[q];
+        {
+            cplx *dst = buf + padx<true>(g * N2 + j * FFT_PPT, lshift);      // FFT_PPT consecutive slots
+#pragma unroll
+            for (int q = 0; q < FFT_PPT; q++) dst[q] = v[q];
+        }
         __syncthreads();
     }
     const size_t lo_mask = ((size_t)1 << pl.lo_bits) - 1;
@@ -1007,15 +1039,18 @@ __device__ __forceinline__ void dct_tile_pass1(const DctFused &a, cplx *buf, siz
         return cmul(ldg_cplx(pl.Thi + (e >> pl.lo_bits)), ldg_cplx(pl.Tlo + (e & lo_mask)));
     };
     // last-pass outputs k2 = j + q*Ns of sequence g: times W_N'^(n1*k2), stored at H[k2*N1 + n1]
-    auto sink = [&](int g, int j, int Ns, auto &v) {
+    auto sink = [&](int g, int j, int Ns, auto &v, int) {
         constexpr int R = (int)(sizeof(v) / sizeof(cplx));
         const size_t n1 = (size_t)seq(g);
         const cplx wstep = table_tw(n1 * (size_t)Ns);
         cplx tw = table_tw(n1 * (size_t)j);
+        cplx *dst = Hc + (size_t)j * (size_t)N1 + n1;
+        const size_t dstep = (size_t)Ns * (size_t)N1;
 #pragma unroll
         for (int q = 0; q < R; q++) {
             if (q && (q & 7) == 0) tw = table_tw(n1 * (size_t)(j + q * Ns));     // bound the error of the running product
-            stg_cplx_hint(Hc + (size_t)(j + q * Ns) * (size_t)N1 + n1, cmul(v[q], tw), pol_last);
+            stg_cplx_hint(dst, cmul(v[q], tw), pol_last);
+            dst += dstep;
             tw = cmul(tw, wstep);
         }
     };
@@ -1041,18 +1076,29 @@ __device__ __forceinline__ void dct_tile_pass2(const DctFused &a, cplx *buf, siz
         for (int t = 0; t < FFT_PPT; t++) v[t] = ldcg_cplx_hint(rows + g * L + j + t * per, pol_last);
         butterfly<FFT_PPT>(v);
 #pragma unroll
-        for (int q = 0; q < FFT_PPT; q++) buf[padx<false>(g * L + j * FFT_PPT + q, lshift)] = v[q];
+        {
+            cplx *dst = buf + padx<false>(g * L + j * FFT_PPT, lshift);
+#pragma unroll
+            for (int q = 0; q < FFT_PPT; q++) dst[q] = v[q];
+        }
         __syncthreads();
     }
     cplx *zc = a.Zc + (c % a.nz) * pl.zc_ld;
-    auto sink = [&](int g, int j, int Ns, auto &v) {
+    // which of this thread's FFT_PPT last-pass outputs the samples need: one precomputed word per
+    // (tile, thread) -- most threads hold none (the samples touch ~3 % of the bins) and skip the lot
+    const uint32_t mine = __ldg(a.pmask + (size_t)tile * FFT_THREADS + threadIdx.x);
+    auto sink = [&](int g, int j, int Ns, auto &v, int uu) {
         constexpr int R = (int)(sizeof(v) / sizeof(cplx));
+        const uint32_t m = K8_PMASK ? ((mine >> (uu * R)) & ((1u << R) - 1u)) : 0xffffu;
+        if (m == 0) return;
 #pragma unroll
         for (int q = 0; q < R; q++) {
-            const int p = g * L + j + q * Ns;                      // position inside the tile
-            const uint32_t w = s_need[p >> 5];
-            if ((w >> (p & 31)) & 1u)
-                zc[s_rank[p >> 5] + __popc(w & ((1u << (p & 31)) - 1u))] = v[q];
+            if ((m >> q) & 1u) {
+                const int p = g * L + j + q * Ns;                  // position inside the tile
+                const uint32_t w = s_need[p >> 5];
+                if (K8_PMASK || ((w >> (p & 31)) & 1u))
+                    zc[s_rank[p >> 5] + __popc(w & ((1u << (p & 31)) - 1u))] = v[q];
+            }
         }
     };
     fft_tail<false, false>(buf, L, lshift, tw, sink, slot_free, slot_free_target, slot_seen);
@@ -1206,8 +1252,31 @@ static DctPlan dct_plan_layout(size_t N, size_t S, void *buf) {
     pl.rank = reinterpret_cast<uint32_t *>(take((pl.Np / 32 + 64) * sizeof(uint32_t)));
     pl.Zc = nullptr; pl.zc_ld = 2 * S;
     pl.G2 = (size_t)(take(2 * S * sizeof(int32_t)) - reinterpret_cast<char *>(buf));   // offset of pidx
+    pl.pmask = reinterpret_cast<uint32_t *>(take((pl.Np / FFT_POINTS) * FFT_THREADS * sizeof(uint32_t)));
     pl.G1 = (size_t)(p - reinterpret_cast<char *>(buf));     // bytes used (host side only)
     return pl;
+}
+// bit (uu * R + q) of pmask[tile * FFT_THREADS + tid] = 1 iff the bin that last_pass<R, .., GFAST = false>
+// hands to its sink as (unit uu, output q) of thread tid in pass-2 tile `tile` is needed by a sample
+__global__ void k_dct_pmask(DctPlan pl, uint32_t *__restrict__ pmask) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t ntiles = pl.Np / FFT_POINTS;
+    if (t >= ntiles * FFT_THREADS) return;
+    const int tid = (int)(t % FFT_THREADS);
+    const size_t base = (t / FFT_THREADS) * FFT_POINTS;
+    const int L = (int)pl.N1;
+    int Ns = FFT_PPT;
+    while (L / Ns > FFT_PPT) Ns *= FFT_PPT;
+    const int R = L / Ns, U = FFT_PPT / R, nshift = 31 - __clz(Ns);
+    uint32_t m = 0;
+    for (int uu = 0; uu < U; uu++) {
+        const int u = tid + uu * (int)FFT_THREADS, g = u >> nshift, j = u & (Ns - 1);
+        for (int q = 0; q < R; q++) {
+            const size_t p = base + (size_t)(g * L + j + q * Ns);
+            if ((pl.need[p >> 5] >> (p & 31)) & 1u) m |= 1u << (uu * R + q);
+        }
+    }
+    pmask[t] = m;
 }
 __global__ void k_dct_pidx(DctPlan pl, const int32_t *__restrict__ samples, size_t S, int32_t *__restrict__ pidx) {
     size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1240,6 +1309,12 @@ void fjlt_dct_plan_build(size_t N, size_t S, const int32_t *samples, void *buf, 
     {
         LaunchScope ls(KC_TABLES, st);
         k_dct_rank<<<1, 1024, 0, st>>>(pl);
+        SKB_CUDA(cudaGetLastError());
+    }
+    {
+        LaunchScope ls(KC_TABLES, st);
+        const size_t nt2 = (pl.Np / FFT_POINTS) * FFT_THREADS;
+        k_dct_pmask<<<(unsigned)((nt2 + 255) / 256), 256, 0, st>>>(pl, pl.pmask);
         SKB_CUDA(cudaGetLastError());
     }
     {
@@ -1287,6 +1362,7 @@ static void dct_fused_launch(const double *Xc, size_t ldc, size_t N, size_t mc, 
     a.H = reinterpret_cast<cplx *>(ws); ws += align256(a.nslot * (N / 2) * sizeof(cplx));
     a.Zc = reinterpret_cast<cplx *>(ws); ws += align256(a.nz * 2 * S * sizeof(cplx));
     a.pidx = reinterpret_cast<const int32_t *>(reinterpret_cast<const char *>(plan) + a.pl.G2);
+    a.pmask = a.pl.pmask;
     a.PB = (unsigned)((S + DCT_POST_CHUNK - 1) / DCT_POST_CHUNK);
     a.TPI = dct_fused_tpi(N);
     a.ctr = reinterpret_cast<unsigned *>(ws);
