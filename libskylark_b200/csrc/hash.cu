@@ -395,13 +395,14 @@ void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int3
 // K2p: strided layout without atomics (see HashColsPlan).  A CTA owns CG columns and a range of
 // index tiles.  Tiles of 2048 indices x CG columns are staged in shared memory by cp.async
 // (coalesced 16-byte pieces, double buffered, with an L2 prefetch a few tiles ahead); warp w then
-// walks the rounds the plan queued for it: lane l takes the entry of a bucket only it owns, reads
+// walks the rounds the plan queued for it (one contiguous stream per warp, read a few batches ahead
+// across tile boundaries): lane l takes the entry of a bucket only it owns, reads
 // the CG values of that index from the tile and does load-add-store on its accumulators.  Rows of
 // a bucket are added in ascending order (the reference's rounding sequence,
 // hash_transform_Elemental.hpp:83-100), the accumulators are written out once.
 // ---------------------------------------------------------------------------
-constexpr int HC_K = 2048, HC_W = 8, HC_THREADS = HC_W * 32, HC_NBUF = 2, HC_PF = 4, HC_B = 8;
-constexpr uint32_t HC_EMPTY = 0xFFFFFFFFu;
+constexpr int HC_K = 2048, HC_W = 8, HC_THREADS = HC_W * 32, HC_NBUF = 2, HC_PF = 4;
+constexpr int HC_B = 4, HC_Q = 4;      // rounds per batch; batches of plan entries in flight per warp
 
 void hash_free_cols_plan(HashColsPlan *plan) {
     cudaFree(plan->entries); cudaFree(plan->vals); cudaFree(plan->off);
@@ -421,41 +422,61 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
     SKB_CUDA(cudaStreamSynchronize(st));
     bool signs = true;
     for (size_t k = 0; k < n && signs; k++) signs = hv[k] == 1.0 || hv[k] == -1.0;
-    std::vector<uint32_t> entries, off((size_t)plan->ntiles * HC_W + 1);
-    std::vector<double> vals;
-    entries.reserve(n * 2);
-    if (!signs) vals.reserve(n * 2);
+    // Warp-major: the rounds of warp w for tiles 0, 1, ... follow each other, every (warp, tile) run
+    // padded with empty rounds to whole batches of HC_B, so a warp reads ONE contiguous stream and its
+    // prefetch runs across tile boundaries.  off[w * (ntiles + 1) + t] = first round of (w, t).
+    const size_t nt = (size_t)plan->ntiles;
+    std::vector<std::vector<uint32_t>> we(HC_W);
+    std::vector<std::vector<double>> wv(HC_W);
+    std::vector<uint32_t> off((size_t)HC_W * (nt + 1));
+    std::vector<size_t> wr(HC_W, 0);
     std::vector<uint32_t> q[HC_W][32];
-    size_t rounds = 0;
-    for (int t = 0; t < plan->ntiles; t++) {
-        const size_t k0 = (size_t)t * HC_K, k1 = std::min(n, k0 + HC_K);
+    // an empty slot adds element 0 of the tile into a spare accumulator of its lane (bucket SW / 32,
+    // never written out): the round needs no branch
+    const uint32_t empty = (uint32_t)(plan->SW / 32) << 16;
+    for (size_t t = 0; t < nt; t++) {
+        const size_t k0 = t * HC_K, k1 = std::min(n, k0 + HC_K);
         for (int w = 0; w < HC_W; w++) for (int l = 0; l < 32; l++) q[w][l].clear();
         for (size_t k = k0; k < k1; k++) {
             const int h = hb[k], w = h / plan->SW, l = (h - w * plan->SW) & 31;
             q[w][l].push_back((uint32_t)(k - k0));
         }
         for (int w = 0; w < HC_W; w++) {
-            off[(size_t)t * HC_W + w] = (uint32_t)rounds;
+            off[(size_t)w * (nt + 1) + t] = (uint32_t)wr[w];         // made absolute below
             size_t nr = 0;
             for (int l = 0; l < 32; l++) nr = std::max(nr, q[w][l].size());
+            nr = (nr + HC_B - 1) / HC_B * HC_B;
             for (size_t r = 0; r < nr; r++)
                 for (int l = 0; l < 32; l++) {
                     if (r < q[w][l].size()) {
                         const uint32_t kk = q[w][l][r];
                         const size_t k = k0 + kk;
-                        uint32_t e = kk | ((uint32_t)hb[k] << 11);
+                        const uint32_t b = (uint32_t)(hb[k] - w * plan->SW) >> 5;     // bucket of the lane
+                        uint32_t e = (kk << 3) | (b << 16);
                         if (signs && hv[k] < 0) e |= 0x80000000u;
-                        entries.push_back(e);
-                        if (!signs) vals.push_back(hv[k]);
+                        we[w].push_back(e);
+                        if (!signs) wv[w].push_back(hv[k]);
                     } else {
-                        entries.push_back(HC_EMPTY);
-                        if (!signs) vals.push_back(0.0);
+                        we[w].push_back(empty);
+                        if (!signs) wv[w].push_back(0.0);
                     }
                 }
-            rounds += nr;
+            wr[w] += nr;
         }
     }
-    off[(size_t)plan->ntiles * HC_W] = (uint32_t)rounds;
+    std::vector<uint32_t> entries;
+    std::vector<double> vals;
+    size_t base = 0;
+    for (int w = 0; w < HC_W; w++) {
+        for (size_t t = 0; t < nt; t++) off[(size_t)w * (nt + 1) + t] += (uint32_t)base;
+        off[(size_t)w * (nt + 1) + nt] = (uint32_t)(base + wr[w]);
+        entries.insert(entries.end(), we[w].begin(), we[w].end());
+        if (!signs) vals.insert(vals.end(), wv[w].begin(), wv[w].end());
+        base += wr[w];
+    }
+    // the prefetch reads HC_Q batches past the round it works on
+    entries.insert(entries.end(), (size_t)HC_Q * HC_B * 32, empty);
+    if (!signs) vals.insert(vals.end(), (size_t)HC_Q * HC_B * 32, 0.0);
     try {
         SKB_CUDA(cudaMalloc(&plan->entries, entries.size() * sizeof(uint32_t) + 256));
         SKB_CUDA(cudaMalloc(&plan->off, off.size() * sizeof(uint32_t)));
@@ -468,30 +489,58 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
     } catch (...) { hash_free_cols_plan(plan); throw; }
 }
 
+__device__ __forceinline__ double hc_lds(unsigned a) {
+    double v; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v;
+}
+__device__ __forceinline__ void hc_sts(unsigned a, double v) {
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory");
+}
+// accumulators: [CG][HC_W][SW + 32] -- the buckets of warp w, then one spare per lane
+__host__ __device__ inline int hc_acc_stride(int SW) { return HC_W * (SW + 32); }
+
 template <int CG, bool SIGN>
 __global__ void __launch_bounds__(HC_THREADS, CG == 4 ? 1 : 2)
 k_hash_cols_plan(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
                  const uint32_t *__restrict__ entries, const double *__restrict__ vals,
                  const uint32_t *__restrict__ off, int ntiles, int tiles_per_split,
-                 double *__restrict__ OUT, size_t ldo, int S, int SP, int ksplit) {
+                 double *__restrict__ OUT, size_t ldo, int S, int SW, int ksplit, int dbg) {
     extern __shared__ __align__(16) double hc_smem[];
-    double *acc = hc_smem;                                  // [CG][SP]
-    double *tiles = hc_smem + (size_t)CG * SP;              // [HC_NBUF][CG][HC_K]
+    const int SPp = hc_acc_stride(SW);
+    double *acc = hc_smem;                                  // [CG][SPp]
+    double *tiles = hc_smem + (size_t)CG * SPp;             // [HC_NBUF][CG][HC_K]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t j0 = (size_t)blockIdx.x * CG;
     const int ncol = (int)min((size_t)CG, m - j0);
     const int t0 = blockIdx.y * tiles_per_split, t1 = min(ntiles, t0 + tiles_per_split);
-    for (int i = tid; i < CG * SP; i += HC_THREADS) acc[i] = 0.0;
+    // columns past the last one are never staged: whatever their buffers hold goes into accumulators
+    // that are not written out; start those from zeros all the same
+    for (int i = tid; i < CG * SPp + HC_NBUF * CG * HC_K; i += HC_THREADS) hc_smem[i] = 0.0;
+    __syncthreads();
     auto issue = [&](int t, int buf) {
         const size_t k0 = (size_t)t * HC_K;
         const int len = (int)min((size_t)HC_K, n - k0);
-        for (int idx = tid; idx < CG * (HC_K / 2); idx += HC_THREADS) {
-            const int c = idx / (HC_K / 2), p2 = (idx - c * (HC_K / 2)) * 2;
-            if (c < ncol && p2 < len) {
-                const double *src = X + k0 + p2 + (j0 + c) * ldx;
-                const unsigned dst = (unsigned)__cvta_generic_to_shared(tiles + ((size_t)(buf * CG + c) * HC_K + p2));
-                if (p2 + 1 < len) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-                else asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+        if (dbg & 1) { asm volatile("cp.async.commit_group;" ::: "memory"); return; }
+        if (len == HC_K) {                                  // whole tile: 4 pieces of 16 bytes per thread and column
+#pragma unroll
+            for (int c = 0; c < CG; c++) {
+                if (c < ncol) {
+                    const double *src = X + k0 + (j0 + c) * ldx + tid * 2;
+                    const unsigned dst = (unsigned)__cvta_generic_to_shared(tiles + ((size_t)(buf * CG + c) * HC_K + tid * 2));
+#pragma unroll
+                    for (int i = 0; i < HC_K / (2 * HC_THREADS); i++)
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + i * HC_THREADS * 16),
+                                     "l"(src + i * HC_THREADS * 2) : "memory");
+                }
+            }
+        } else {
+            for (int idx = tid; idx < CG * (HC_K / 2); idx += HC_THREADS) {
+                const int c = idx / (HC_K / 2), p2 = (idx - c * (HC_K / 2)) * 2;
+                if (c < ncol && p2 < len) {
+                    const double *src = X + k0 + p2 + (j0 + c) * ldx;
+                    const unsigned dst = (unsigned)__cvta_generic_to_shared(tiles + ((size_t)(buf * CG + c) * HC_K + p2));
+                    if (p2 + 1 < len) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+                    else asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+                }
             }
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
@@ -501,59 +550,86 @@ k_hash_cols_plan(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
                 asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(X + kp + (j0 + tid) * ldx), "r"(HC_K * 8));
         }
     };
-    if (t0 < t1) issue(t0, 0);
-    for (int t = t0; t < t1; t++) {
-        const int buf = (t - t0) & 1;
-        if (t + 1 < t1) {
-            issue(t + 1, buf ^ 1);
-            asm volatile("cp.async.wait_group 1;" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
+    // this warp's stream of plan entries: HC_Q batches of HC_B rounds ahead of the round being applied,
+    // across tile boundaries (the entries come from L2, ~1 us away)
+    const uint32_t *woff = off + (size_t)warp * (ntiles + 1);
+    uint32_t r = t0 < t1 ? __ldg(woff + t0) : 0u;
+    uint32_t rnext = t0 < t1 ? __ldg(woff + t0 + 1) : 0u;
+    uint32_t eq[HC_Q][HC_B]; double vq[HC_Q][HC_B];
+    const uint32_t *ep = entries + (size_t)r * 32 + lane;   // next batch to fetch
+    const double *vp = vals + (size_t)r * 32 + lane;
+    auto fetch = [&](uint32_t (&e)[HC_B], double (&v)[HC_B]) {
+#pragma unroll
+        for (int i = 0; i < HC_B; i++) {
+            e[i] = __ldg(ep + i * 32);
+            v[i] = SIGN ? 0.0 : __ldg(vp + i * 32);
         }
-        __syncthreads();
-        const double *tile = tiles + (size_t)buf * CG * HC_K;
-        const uint32_t r0 = __ldg(off + (size_t)t * HC_W + warp), r1 = __ldg(off + (size_t)t * HC_W + warp + 1);
-        // entries come from L2: a batch of HC_B rounds is in flight while the previous one is applied
-        uint32_t eb[HC_B]; double vb[HC_B];
-        auto fetch = [&](uint32_t r, uint32_t (&e)[HC_B], double (&v)[HC_B]) {
+        ep += HC_B * 32; vp += HC_B * 32;
+    };
+    if (t0 < t1) {
+        issue(t0, 0);
 #pragma unroll
-            for (int i = 0; i < HC_B; i++) {
-                e[i] = r + i < r1 ? __ldg(entries + (size_t)(r + i) * 32 + lane) : HC_EMPTY;
-                v[i] = (!SIGN && r + i < r1) ? __ldg(vals + (size_t)(r + i) * 32 + lane) : 0.0;
+        for (int qi = 0; qi < HC_Q; qi++) fetch(eq[qi], vq[qi]);
+    }
+    // The queue is indexed statically (slot s of an HC_Q-way unrolled loop), never shifted: a register
+    // move of a slot whose load is still in flight would wait for it.  A tile may end at any slot, so
+    // the hand-over to the next tile (one barrier per tile per warp) sits inside every slot.
+    const unsigned accb = (unsigned)__cvta_generic_to_shared(acc + warp * (SW + 32) + lane);   // + bucket * 256 bytes
+    const unsigned tiles_s = (unsigned)__cvta_generic_to_shared(tiles);
+    int t = t0 - 1;
+    uint32_t rend = r;
+    unsigned tile = tiles_s;
+    bool live = t0 < t1;
+    while (live) {
+#pragma unroll
+        for (int s = 0; s < HC_Q; s++) {
+            while (live && r == rend) {                     // this warp has finished tile t
+                if (++t == t1) { live = false; break; }
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+                asm volatile("bar.sync 0;" ::: "memory");   // tile t has landed; every warp is done with tile t - 1
+                const int buf = (t - t0) & 1;
+                if (t + 1 < t1) issue(t + 1, buf ^ 1);
+                rend = rnext;
+                if (t + 1 < t1) rnext = __ldg(woff + t + 2);        // needed one tile from now
+                tile = tiles_s + (unsigned)buf * (CG * HC_K * 8);
             }
-        };
-        fetch(r0, eb, vb);
-        for (uint32_t r = r0; r < r1; r += HC_B) {
-            uint32_t en[HC_B]; double vn[HC_B];
-            fetch(r + HC_B, en, vn);
+            if (!live) break;
+            if (dbg & 2) { r = rend; continue; }
+            // all tile reads of the batch first (the tile is read-only), then round by round: two
+            // rounds of a lane may hit the same bucket
+            unsigned aa[HC_B];
+            double x[HC_B][CG];
 #pragma unroll
             for (int i = 0; i < HC_B; i++) {
-                const uint32_t e = eb[i];
-                if (e != HC_EMPTY) {
-                    const int k = (int)(e & (HC_K - 1)), h = (int)((e >> 11) & 0xFFFFu);
-                    double x[CG], a[CG];
+                const uint32_t e = eq[s][i];
+                const unsigned xa = tile + (e & 0x3FF8u);                       // index k of the tile, column 0
+                aa[i] = accb + __byte_perm(e, 0u, 0x4424u);                     // this lane's bucket (e >> 16) & 255
 #pragma unroll
-                    for (int c = 0; c < CG; c++) x[c] = c < ncol ? tile[c * HC_K + k] : 0.0;
+                for (int c = 0; c < CG; c++) x[i][c] = hc_lds(xa + c * (HC_K * 8));
+            }
 #pragma unroll
-                    for (int c = 0; c < CG; c++) a[c] = acc[c * SP + h];
+            for (int i = 0; i < HC_B; i++) {
+                const uint32_t e = eq[s][i];
+                double a[CG];
 #pragma unroll
-                    for (int c = 0; c < CG; c++) {          // product, then sum: the reference's rounding
-                        const double p = SIGN ? ((e >> 31) ? -x[c] : x[c]) : __dmul_rn(vb[i], x[c]);
-                        a[c] = __dadd_rn(a[c], p);
-                    }
+                for (int c = 0; c < CG; c++) a[c] = hc_lds(aa[i] + c * SPp * 8);
 #pragma unroll
-                    for (int c = 0; c < CG; c++) acc[c * SP + h] = a[c];
+                for (int c = 0; c < CG; c++) {              // product, then sum: the reference's rounding
+                    const double p = SIGN ? __hiloint2double(__double2hiint(x[i][c]) ^ (int)(e & 0x80000000u), __double2loint(x[i][c]))
+                                          : __dmul_rn(vq[s][i], x[i][c]);
+                    a[c] = __dadd_rn(a[c], p);
                 }
-            }
 #pragma unroll
-            for (int i = 0; i < HC_B; i++) { eb[i] = en[i]; vb[i] = vn[i]; }
+                for (int c = 0; c < CG; c++) hc_sts(aa[i] + c * SPp * 8, a[c]);
+            }
+            fetch(eq[s], vq[s]);
+            r += HC_B;
         }
-        __syncthreads();                                    // the buffer is refilled two tiles later
     }
     __syncthreads();
     for (int i = tid; i < S * ncol; i += HC_THREADS) {
-        const int c = i / S, h = i - c * S;
-        const double a = acc[c * SP + h];
+        const int c = i / S, h = i - c * S, w = h / SW;
+        const double a = acc[c * SPp + w * (SW + 32) + (h - w * SW)];
         double *o = OUT + h + (j0 + c) * ldo;
         if (ksplit == 1) *o = a;
         else if (a != 0.0) atomicAdd(o, a);
@@ -565,8 +641,9 @@ bool hash_apply_cols_planned(const double *X, size_t ldx, size_t n, size_t m, co
     static const bool off_env = getenv("SKB_DEBUG_NO_COLS_PLAN") != nullptr;
     if (off_env || m == 0 || n == 0 || plan.n != n || plan.S != S || !plan.entries) return false;
     if (S > 32767 || (ldx & 1) || ((uintptr_t)X & 15)) return false;
-    const int SP = plan.SW * HC_W;
-    auto smem_for = [&](int cg) { return ((size_t)cg * SP + (size_t)HC_NBUF * cg * HC_K) * sizeof(double); };
+    if (plan.SW / 32 > 255) return false;                   // the bucket field of an entry is 8 bits
+    const int SPp = hc_acc_stride(plan.SW);
+    auto smem_for = [&](int cg) { return ((size_t)cg * SPp + (size_t)HC_NBUF * cg * HC_K) * sizeof(double); };
     // two columns per CTA and two CTAs per SM (one's barriers and staging overlap the other's rounds)
     // when that still fills the GPU: measured 0.172 ms against 0.209 ms with four columns at C1
     int CG = (m + 1) / 2 >= 148 && smem_for(2) <= 108 * 1024 ? 2 : 4;
@@ -580,17 +657,19 @@ bool hash_apply_cols_planned(const double *X, size_t ldx, size_t n, size_t m, co
     if (ksplit > 1) zero_matrix(OUT, ldo, (size_t)S, m, st);
     const bool sign = plan.vals == nullptr;
     const size_t smem = smem_for(CG);
+    static const int dbg = getenv("SKB_HC_DBG") ? atoi(getenv("SKB_HC_DBG")) : 0;    // timing experiments only
     LaunchScope ls(KC_HASH, st);
 #define SKB_HC_LAUNCH(CGV, SG)                                                                               \
     do {                                                                                                    \
         auto kern = k_hash_cols_plan<CGV, SG>;                                                              \
         SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
         kern<<<dim3(gx, (unsigned)ksplit), HC_THREADS, smem, st>>>(X, ldx, n, m, plan.entries, plan.vals,   \
-                                                                   plan.off, plan.ntiles, tps, OUT, ldo, S, SP, ksplit); \
+                                                                   plan.off, plan.ntiles, tps, OUT, ldo, S, plan.SW, ksplit, dbg); \
     } while (0)
     if (CG == 4) { if (sign) SKB_HC_LAUNCH(4, true); else SKB_HC_LAUNCH(4, false); }
     else if (CG == 2) { if (sign) SKB_HC_LAUNCH(2, true); else SKB_HC_LAUNCH(2, false); }
     else { if (sign) SKB_HC_LAUNCH(1, true); else SKB_HC_LAUNCH(1, false); }
+#undef SKB_HC_LAUNCH
 #undef SKB_HC_LAUNCH
     SKB_CUDA(cudaGetLastError());
     return true;

@@ -86,9 +86,9 @@ void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int3
 // so a CTA accumulates in shared memory with plain loads and stores -- no atomics.  Built on the
 // host once per (transform, shard) from the bucket / value tables.
 struct HashColsPlan {
-    uint32_t *entries = nullptr;   // rounds of 32 packed entries: k in tile | bucket << 11 | sign << 31
+    uint32_t *entries = nullptr;   // rounds of 32 packed entries: k in tile << 3 | bucket of the lane << 16 | sign << 31
     double *vals = nullptr;        // value per entry; null when every value is +-1 (sign bit used)
-    uint32_t *off = nullptr;       // first round of (tile, warp), ntiles * 8 + 1 entries
+    uint32_t *off = nullptr;       // first round of (warp, tile): 8 * (ntiles + 1) entries, warp-major streams
     int ntiles = 0, S = 0, SW = 0;
     size_t n = 0;
 };
