@@ -443,6 +443,39 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
         }
         for (int w = 0; w < HC_W; w++) {
             off[(size_t)w * (nt + 1) + t] = (uint32_t)wr[w];         // made absolute below
+            // A lane may take the rows of DIFFERENT buckets in any order (each bucket still sees its
+            // rows ascending).  Use that freedom against bank conflicts of the tile reads: round by
+            // round, every lane of a half warp picks the pending row whose bank pair (k mod 16) is
+            // the least used so far in that half warp's round.
+            {
+                const int nb = std::max(1, plan->SW / 32);
+                std::vector<std::vector<uint32_t>> fifo((size_t)32 * nb);
+                std::vector<size_t> head((size_t)32 * nb, 0);
+                size_t longest = 0;
+                for (int l = 0; l < 32; l++) {
+                    for (uint32_t kk : q[w][l]) fifo[(size_t)l * nb + (size_t)((hb[k0 + kk] - w * plan->SW) >> 5)].push_back(kk);
+                    longest = std::max(longest, q[w][l].size());
+                    q[w][l].clear();
+                }
+                for (size_t r = 0; r < longest; r++)
+                    for (int half = 0; half < 2; half++) {
+                        int used[16] = {0};
+                        for (int l = half * 16; l < half * 16 + 16; l++) {
+                            int best = -1; int bu = 0; size_t brem = 0;
+                            for (int b = 0; b < nb; b++) {
+                                const size_t f = (size_t)l * nb + b, rem = fifo[f].size() - head[f];
+                                if (!rem) continue;
+                                const int u = used[fifo[f][head[f]] & 15];
+                                if (best < 0 || u < bu || (u == bu && rem > brem)) { best = b; bu = u; brem = rem; }
+                            }
+                            if (best < 0) continue;
+                            const size_t f = (size_t)l * nb + best;
+                            const uint32_t kk = fifo[f][head[f]++];
+                            used[kk & 15]++;
+                            q[w][l].push_back(kk);
+                        }
+                    }
+            }
             size_t nr = 0;
             for (int l = 0; l < 32; l++) nr = std::max(nr, q[w][l].size());
             nr = (nr + HC_B - 1) / HC_B * HC_B;
