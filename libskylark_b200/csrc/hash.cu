@@ -394,15 +394,25 @@ void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int3
 // ---------------------------------------------------------------------------
 // K2p: strided layout without atomics (see HashColsPlan).  A CTA owns CG columns and a range of
 // index tiles.  Tiles of 2048 indices x CG columns are staged in shared memory by cp.async
-// (coalesced 16-byte pieces, double buffered, with an L2 prefetch a few tiles ahead); warp w then
-// walks the rounds the plan queued for it (one contiguous stream per warp, read a few batches ahead
-// across tile boundaries): lane l takes the entry of a bucket only it owns, reads
-// the CG values of that index from the tile and does load-add-store on its accumulators.  Rows of
-// a bucket are added in ascending order (the reference's rounding sequence,
-// hash_transform_Elemental.hpp:83-100), the accumulators are written out once.
+// (coalesced 16-byte pieces, double buffered, with an L2 prefetch a few tiles ahead).  Warp w owns
+// the buckets [w * SW, (w + 1) * SW) and walks the rounds the plan queued for it (one contiguous
+// stream per warp, read ahead across tile boundaries): in a round every lane takes a row of a
+// DIFFERENT bucket, reads the CG values of that index from the tile and does load-add-store on the
+// bucket's accumulators.  The plan also arranges each half warp of a round on 16 different bank pairs
+// for both accesses, so a round costs 6 * CG shared-memory wavefronts.  Rows of a bucket are added
+// in ascending order (the reference's rounding sequence, hash_transform_Elemental.hpp:83-100), the
+// accumulators are written out once.
+// History at C1 (100k x 500 -> 2000, column-major): 0.216 ms with shared-memory atomics; 0.172 ms
+// with lane-owned buckets (44 % of the lane slots busy); 0.117 ms in this form.  What did NOT help:
+// several batches of entry loads in flight per warp (waiting on the oldest also waits for the
+// newer ones that share its scoreboard), and denser rounds without the bank-pair matching (as many
+// wavefronts as before, in fewer instructions).
 // ---------------------------------------------------------------------------
 constexpr int HC_K = 2048, HC_W = 8, HC_THREADS = HC_W * 32, HC_NBUF = 2, HC_PF = 4;
-constexpr int HC_B = 4, HC_Q = 4;      // rounds per batch; batches of plan entries in flight per warp
+#ifndef SKB_HC_NB
+#define SKB_HC_NB 8
+#endif
+constexpr int HC_B = 2, HC_NB = SKB_HC_NB;      // rounds applied together; rounds per register set of plan entries      // rounds per batch; batches of plan entries in flight per warp
 
 void hash_free_cols_plan(HashColsPlan *plan) {
     cudaFree(plan->entries); cudaFree(plan->vals); cudaFree(plan->off);
@@ -430,69 +440,88 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
     std::vector<std::vector<double>> wv(HC_W);
     std::vector<uint32_t> off((size_t)HC_W * (nt + 1));
     std::vector<size_t> wr(HC_W, 0);
-    std::vector<uint32_t> q[HC_W][32];
-    // an empty slot adds element 0 of the tile into a spare accumulator of its lane (bucket SW / 32,
-    // never written out): the round needs no branch
-    const uint32_t empty = (uint32_t)(plan->SW / 32) << 16;
+    // A warp owns the SW buckets [w * SW, (w + 1) * SW); ANY lane may take any of its rows, as long as
+    // the 32 rows of a round go to 32 different buckets (plain load-add-store, no atomics) and a bucket
+    // sees its rows in ascending order.  Rounds are filled from the buckets with the most rows left
+    // (that needs max(ceil(rows / 32), longest bucket) rounds, the minimum), and each half warp -- one
+    // shared-memory wavefront of 8-byte accesses -- gets 16 different accumulator bank pairs
+    // (bucket mod 16) where the rows allow it, then different tile bank pairs (k mod 16).
+    // An empty slot adds element 0 of the tile into a spare accumulator of its lane (bucket SW + lane,
+    // never written out): the round needs no branch.
+    const int SW = plan->SW;
+    std::vector<std::vector<uint32_t>> fifo((size_t)HC_W * SW);
+    std::vector<uint32_t> head((size_t)SW), cand;
     for (size_t t = 0; t < nt; t++) {
         const size_t k0 = t * HC_K, k1 = std::min(n, k0 + HC_K);
-        for (int w = 0; w < HC_W; w++) for (int l = 0; l < 32; l++) q[w][l].clear();
-        for (size_t k = k0; k < k1; k++) {
-            const int h = hb[k], w = h / plan->SW, l = (h - w * plan->SW) & 31;
-            q[w][l].push_back((uint32_t)(k - k0));
-        }
+        for (auto &f : fifo) f.clear();
+        for (size_t k = k0; k < k1; k++) fifo[(size_t)hb[k]].push_back((uint32_t)(k - k0));   // hb < S <= HC_W * SW
         for (int w = 0; w < HC_W; w++) {
             off[(size_t)w * (nt + 1) + t] = (uint32_t)wr[w];         // made absolute below
-            // A lane may take the rows of DIFFERENT buckets in any order (each bucket still sees its
-            // rows ascending).  Use that freedom against bank conflicts of the tile reads: round by
-            // round, every lane of a half warp picks the pending row whose bank pair (k mod 16) is
-            // the least used so far in that half warp's round.
-            {
-                const int nb = std::max(1, plan->SW / 32);
-                std::vector<std::vector<uint32_t>> fifo((size_t)32 * nb);
-                std::vector<size_t> head((size_t)32 * nb, 0);
-                size_t longest = 0;
-                for (int l = 0; l < 32; l++) {
-                    for (uint32_t kk : q[w][l]) fifo[(size_t)l * nb + (size_t)((hb[k0 + kk] - w * plan->SW) >> 5)].push_back(kk);
-                    longest = std::max(longest, q[w][l].size());
-                    q[w][l].clear();
+            std::vector<uint32_t> *fw = fifo.data() + (size_t)w * SW;
+            size_t left = 0;
+            for (int bk = 0; bk < SW; bk++) { head[bk] = 0; left += fw[bk].size(); }
+            size_t nr = 0;
+            int degA[16] = {0}, degX[16] = {0};           // rows left per accumulator / tile bank pair
+            for (int bk = 0; bk < SW; bk++)
+                for (uint32_t kk : fw[bk]) { degA[bk & 15]++; degX[kk & 15]++; }
+            while (left) {
+                // one round = two half warps; a half warp takes rows with 16 different accumulator bank
+                // pairs AND 16 different tile bank pairs (a matching between the two), so each of its
+                // six shared-memory accesses is one wavefront.  Rows whose bank pairs have the most
+                // rows left go first -- those pairs decide how many rounds the tile needs.
+                cand.clear();
+                for (int bk = 0; bk < SW; bk++) if (head[bk] < fw[bk].size()) cand.push_back((uint32_t)bk);
+                std::stable_sort(cand.begin(), cand.end(), [&](uint32_t x, uint32_t y) {
+                    const int px = std::max(degA[x & 15], degX[fw[x][head[x]] & 15]);
+                    const int py = std::max(degA[y & 15], degX[fw[y][head[y]] & 15]);
+                    if (px != py) return px > py;
+                    return fw[x].size() - head[x] > fw[y].size() - head[y];
+                });
+                int slot_b[32]; uint32_t slot_k[32];
+                for (int l = 0; l < 32; l++) slot_b[l] = -1;
+                int fill[2] = {0, 0};
+                bool acc_used[2][16] = {{false}}, x_used[2][16] = {{false}};
+                for (uint32_t bk : cand) {
+                    if (fill[0] + fill[1] == 32) break;
+                    const uint32_t kk = fw[bk][head[bk]];
+                    const int c = (int)(bk & 15), xc = (int)(kk & 15);
+                    int h = -1;
+                    for (int hh = 0; hh < 2 && h < 0; hh++) {
+                        const int g = fill[0] <= fill[1] ? hh : 1 - hh;            // emptier half first
+                        if (fill[g] < 16 && !acc_used[g][c] && !x_used[g][xc]) h = g;
+                    }
+                    if (h < 0) continue;
+                    head[bk]++; left--; degA[c]--; degX[xc]--;
+                    slot_b[h * 16 + fill[h]] = (int)bk; slot_k[h * 16 + fill[h]] = kk;
+                    fill[h]++; acc_used[h][c] = true; x_used[h][xc] = true;
                 }
-                for (size_t r = 0; r < longest; r++)
-                    for (int half = 0; half < 2; half++) {
-                        int used[16] = {0};
-                        for (int l = half * 16; l < half * 16 + 16; l++) {
-                            int best = -1; int bu = 0; size_t brem = 0;
-                            for (int b = 0; b < nb; b++) {
-                                const size_t f = (size_t)l * nb + b, rem = fifo[f].size() - head[f];
-                                if (!rem) continue;
-                                const int u = used[fifo[f][head[f]] & 15];
-                                if (best < 0 || u < bu || (u == bu && rem > brem)) { best = b; bu = u; brem = rem; }
-                            }
-                            if (best < 0) continue;
-                            const size_t f = (size_t)l * nb + best;
-                            const uint32_t kk = fifo[f][head[f]++];
-                            used[kk & 15]++;
-                            q[w][l].push_back(kk);
+                for (int h = 0; h < 2; h++) {
+                    // idle lanes: the tile element of a busy lane of the half (same address = broadcast),
+                    // or element 0, and a spare accumulator on a bank pair the half does not use
+                    const uint32_t kfill = fill[h] ? slot_k[h * 16] : 0u;
+                    int c = 0;
+                    for (int i = 0; i < 16; i++) {
+                        const int l = h * 16 + i;
+                        if (slot_b[l] >= 0) {
+                            const size_t k = k0 + slot_k[l];
+                            uint32_t e = (slot_k[l] << 3) | ((uint32_t)slot_b[l] << 16);
+                            if (signs && hv[k] < 0) e |= 0x80000000u;
+                            we[w].push_back(e);
+                            if (!signs) wv[w].push_back(hv[k]);
+                        } else {
+                            while (acc_used[h][c]) c++;
+                            we[w].push_back((kfill << 3) | ((uint32_t)(SW + h * 16 + c) << 16));
+                            if (!signs) wv[w].push_back(0.0);
+                            c++;
                         }
                     }
+                }
+                nr++;
             }
-            size_t nr = 0;
-            for (int l = 0; l < 32; l++) nr = std::max(nr, q[w][l].size());
-            nr = (nr + HC_B - 1) / HC_B * HC_B;
-            for (size_t r = 0; r < nr; r++)
+            for (; nr % HC_B; nr++)
                 for (int l = 0; l < 32; l++) {
-                    if (r < q[w][l].size()) {
-                        const uint32_t kk = q[w][l][r];
-                        const size_t k = k0 + kk;
-                        const uint32_t b = (uint32_t)(hb[k] - w * plan->SW) >> 5;     // bucket of the lane
-                        uint32_t e = (kk << 3) | (b << 16);
-                        if (signs && hv[k] < 0) e |= 0x80000000u;
-                        we[w].push_back(e);
-                        if (!signs) wv[w].push_back(hv[k]);
-                    } else {
-                        we[w].push_back(empty);
-                        if (!signs) wv[w].push_back(0.0);
-                    }
+                    we[w].push_back((uint32_t)(SW + l) << 16);
+                    if (!signs) wv[w].push_back(0.0);
                 }
             wr[w] += nr;
         }
@@ -508,8 +537,9 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
         base += wr[w];
     }
     // the prefetch reads HC_Q batches past the round it works on
-    entries.insert(entries.end(), (size_t)HC_Q * HC_B * 32, empty);
-    if (!signs) vals.insert(vals.end(), (size_t)HC_Q * HC_B * 32, 0.0);
+    for (int z = 0; z < 2 * HC_NB; z++)                     // the prefetch runs two sets past the last round
+        for (int l = 0; l < 32; l++) entries.push_back((uint32_t)(plan->SW + l) << 16);
+    if (!signs) vals.insert(vals.end(), (size_t)2 * HC_NB * 32, 0.0);
     try {
         SKB_CUDA(cudaMalloc(&plan->entries, entries.size() * sizeof(uint32_t) + 256));
         SKB_CUDA(cudaMalloc(&plan->off, off.size() * sizeof(uint32_t)));
@@ -583,81 +613,103 @@ k_hash_cols_plan(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
                 asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(X + kp + (j0 + tid) * ldx), "r"(HC_K * 8));
         }
     };
-    // this warp's stream of plan entries: HC_Q batches of HC_B rounds ahead of the round being applied,
-    // across tile boundaries (the entries come from L2, ~1 us away)
-    const uint32_t *woff = off + (size_t)warp * (ntiles + 1);
-    uint32_t r = t0 < t1 ? __ldg(woff + t0) : 0u;
-    uint32_t rnext = t0 < t1 ? __ldg(woff + t0 + 1) : 0u;
-    uint32_t eq[HC_Q][HC_B]; double vq[HC_Q][HC_B];
-    const uint32_t *ep = entries + (size_t)r * 32 + lane;   // next batch to fetch
-    const double *vp = vals + (size_t)r * 32 + lane;
-    auto fetch = [&](uint32_t (&e)[HC_B], double (&v)[HC_B]) {
-#pragma unroll
-        for (int i = 0; i < HC_B; i++) {
-            e[i] = __ldg(ep + i * 32);
-            v[i] = SIGN ? 0.0 : __ldg(vp + i * 32);
-        }
-        ep += HC_B * 32; vp += HC_B * 32;
-    };
-    if (t0 < t1) {
-        issue(t0, 0);
-#pragma unroll
-        for (int qi = 0; qi < HC_Q; qi++) fetch(eq[qi], vq[qi]);
+    // the round offsets of this warp's tiles come through a 64-entry ring in shared memory, refilled
+    // 32 tiles ahead (a tile can be shorter than the L2 latency of a load issued when it starts)
+    const uint32_t *woff = off + (size_t)warp * (ntiles + 1) + t0;
+    volatile uint32_t *ring = reinterpret_cast<uint32_t *>(tiles + (size_t)HC_NBUF * CG * HC_K) + warp * 64;
+    const int nti = t1 - t0;                                // offsets 0 .. nti are this CTA's
+    if (nti > 0) {
+        if (lane <= nti) ring[lane] = __ldg(woff + lane);
+        if (lane + 32 <= nti) ring[lane + 32] = __ldg(woff + lane + 32);
     }
-    // The queue is indexed statically (slot s of an HC_Q-way unrolled loop), never shifted: a register
-    // move of a slot whose load is still in flight would wait for it.  A tile may end at any slot, so
-    // the hand-over to the next tile (one barrier per tile per warp) sits inside every slot.
-    const unsigned accb = (unsigned)__cvta_generic_to_shared(acc + warp * (SW + 32) + lane);   // + bucket * 256 bytes
+    __syncwarp();
+    uint32_t r = nti > 0 ? ring[0] : 0u;
+    // Plan entries come from L2 behind the tile traffic, more than a microsecond away.  Two register
+    // sets of HC_NB rounds: while one is applied the other is in flight.  A set is refilled only AFTER
+    // the first entry of the other set has been waited for (the refill addresses depend on it): the
+    // hardware tracks loads with a handful of scoreboards, and waiting on an old load while newer ones
+    // share its scoreboard would wait for those as well -- a queue of several batches in flight
+    // measured no better than one.
+    uint32_t ea[HC_NB], eb[HC_NB]; double va[HC_NB], vb[HC_NB];
+    const uint32_t *ep = entries + (size_t)r * 32 + lane;   // next set to fetch
+    const double *vp = vals + (size_t)r * 32 + lane;
+    auto fetch = [&](uint32_t (&e)[HC_NB], double (&v)[HC_NB], uint32_t dep) {
+        const uint32_t *ep_ = ep + dep; const double *vp_ = vp + dep;
+#pragma unroll
+        for (int i = 0; i < HC_NB; i++) {
+            if (dbg & 4) e[i] = (((unsigned)(size_t)ep_ * 2654435761u + (unsigned)lane * 40503u + (unsigned)i * 977u) & 0x3FF8u) | (((unsigned)lane * 7u + (unsigned)i) & 0xffu) << 16;
+            else e[i] = __ldg(ep_ + i * 32);
+            v[i] = SIGN ? 0.0 : __ldg(vp_ + i * 32);
+        }
+        ep += HC_NB * 32; vp += HC_NB * 32;
+    };
+    const unsigned accb = (unsigned)__cvta_generic_to_shared(acc + warp * (SW + 32));   // + bucket of the warp * 8 bytes
     const unsigned tiles_s = (unsigned)__cvta_generic_to_shared(tiles);
     int t = t0 - 1;
     uint32_t rend = r;
     unsigned tile = tiles_s;
-    bool live = t0 < t1;
-    while (live) {
+    bool live = nti > 0;
+    if (live) {
+        issue(t0, 0);
+        fetch(ea, va, 0u);
+    }
+    // applies the HC_NB rounds of one set; a tile may end after any pair of rounds, so the hand-over to
+    // the next tile (one barrier per tile per warp) sits in front of every pair
+    auto apply_set = [&](uint32_t (&e_)[HC_NB], double (&v_)[HC_NB]) {
 #pragma unroll
-        for (int s = 0; s < HC_Q; s++) {
+        for (int g = 0; g < HC_NB; g += HC_B) {
             while (live && r == rend) {                     // this warp has finished tile t
                 if (++t == t1) { live = false; break; }
                 asm volatile("cp.async.wait_group 0;" ::: "memory");
                 asm volatile("bar.sync 0;" ::: "memory");   // tile t has landed; every warp is done with tile t - 1
                 const int buf = (t - t0) & 1;
                 if (t + 1 < t1) issue(t + 1, buf ^ 1);
-                rend = rnext;
-                if (t + 1 < t1) rnext = __ldg(woff + t + 2);        // needed one tile from now
+                const int ti = t - t0;
+                if (ti > 0 && (ti & 31) == 0 && ti + 32 + lane <= nti)
+                    ring[(ti + 32 + lane) & 63] = __ldg(woff + ti + 32 + lane);
+                __syncwarp();
+                rend = ring[(ti + 1) & 63];
                 tile = tiles_s + (unsigned)buf * (CG * HC_K * 8);
             }
-            if (!live) break;
+            if (!live) return;
             if (dbg & 2) { r = rend; continue; }
-            // all tile reads of the batch first (the tile is read-only), then round by round: two
-            // rounds of a lane may hit the same bucket
+            // all tile reads of the group first (the tile is read-only), then round by round: two
+            // rounds may hit the same bucket
             unsigned aa[HC_B];
             double x[HC_B][CG];
 #pragma unroll
             for (int i = 0; i < HC_B; i++) {
-                const uint32_t e = eq[s][i];
+                const uint32_t e = e_[g + i];
                 const unsigned xa = tile + (e & 0x3FF8u);                       // index k of the tile, column 0
-                aa[i] = accb + __byte_perm(e, 0u, 0x4424u);                     // this lane's bucket (e >> 16) & 255
+                aa[i] = accb + ((e >> 13) & 0xFFF8u);                           // bucket of the warp: (e >> 16) & 0x1fff
 #pragma unroll
                 for (int c = 0; c < CG; c++) x[i][c] = hc_lds(xa + c * (HC_K * 8));
             }
 #pragma unroll
             for (int i = 0; i < HC_B; i++) {
-                const uint32_t e = eq[s][i];
+                const uint32_t e = e_[g + i];
                 double a[CG];
 #pragma unroll
                 for (int c = 0; c < CG; c++) a[c] = hc_lds(aa[i] + c * SPp * 8);
 #pragma unroll
                 for (int c = 0; c < CG; c++) {              // product, then sum: the reference's rounding
                     const double p = SIGN ? __hiloint2double(__double2hiint(x[i][c]) ^ (int)(e & 0x80000000u), __double2loint(x[i][c]))
-                                          : __dmul_rn(vq[s][i], x[i][c]);
+                                          : __dmul_rn(v_[g + i], x[i][c]);
                     a[c] = __dadd_rn(a[c], p);
                 }
 #pragma unroll
                 for (int c = 0; c < CG; c++) hc_sts(aa[i] + c * SPp * 8, a[c]);
+                __syncwarp();               // the next round's lanes may read what other lanes stored here
             }
-            fetch(eq[s], vq[s]);
             r += HC_B;
         }
+    };
+    while (live) {
+        fetch(eb, vb, ea[0] & 0x4000u);     // bits 14..15 of an entry are zero: a data dependence, not an offset
+        apply_set(ea, va);
+        if (!live) break;
+        fetch(ea, va, eb[0] & 0x4000u);
+        apply_set(eb, vb);
     }
     __syncthreads();
     for (int i = tid; i < S * ncol; i += HC_THREADS) {
@@ -674,9 +726,8 @@ bool hash_apply_cols_planned(const double *X, size_t ldx, size_t n, size_t m, co
     static const bool off_env = getenv("SKB_DEBUG_NO_COLS_PLAN") != nullptr;
     if (off_env || m == 0 || n == 0 || plan.n != n || plan.S != S || !plan.entries) return false;
     if (S > 32767 || (ldx & 1) || ((uintptr_t)X & 15)) return false;
-    if (plan.SW / 32 > 255) return false;                   // the bucket field of an entry is 8 bits
     const int SPp = hc_acc_stride(plan.SW);
-    auto smem_for = [&](int cg) { return ((size_t)cg * SPp + (size_t)HC_NBUF * cg * HC_K) * sizeof(double); };
+    auto smem_for = [&](int cg) { return ((size_t)cg * SPp + (size_t)HC_NBUF * cg * HC_K) * sizeof(double) + HC_W * 64 * sizeof(uint32_t); };
     // two columns per CTA and two CTAs per SM (one's barriers and staging overlap the other's rounds)
     // when that still fills the GPU: measured 0.172 ms against 0.209 ms with four columns at C1
     int CG = (m + 1) / 2 >= 148 && smem_for(2) <= 108 * 1024 ? 2 : 4;
@@ -690,7 +741,8 @@ bool hash_apply_cols_planned(const double *X, size_t ldx, size_t n, size_t m, co
     if (ksplit > 1) zero_matrix(OUT, ldo, (size_t)S, m, st);
     const bool sign = plan.vals == nullptr;
     const size_t smem = smem_for(CG);
-    static const int dbg = getenv("SKB_HC_DBG") ? atoi(getenv("SKB_HC_DBG")) : 0;    // timing experiments only
+    // timing experiments only (results are wrong): 1 = no tile staging, 2 = no rounds, 4 = made-up entries
+    static const int dbg = getenv("SKB_HC_DBG") ? atoi(getenv("SKB_HC_DBG")) : 0;
     LaunchScope ls(KC_HASH, st);
 #define SKB_HC_LAUNCH(CGV, SG)                                                                               \
     do {                                                                                                    \

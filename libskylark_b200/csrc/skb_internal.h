@@ -81,12 +81,13 @@ void hash_apply_rows(const double *X, size_t ldx, size_t m, const HashPlan &plan
 // OUT[h(k) + j*ldo] += v(k) * X[k + j*ldx], j < m   (input index k strided by 1 inside a column)
 void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int32_t *bucket,
                      const double *value, double *OUT, size_t ldo, int S, cudaStream_t st);
-// Plan of the strided layout (K2): sketched indices are cut in tiles of 2048; inside a tile every
-// index is queued at the (warp, lane) that OWNS its bucket (warp = bucket / SW, lane = bucket % 32),
-// so a CTA accumulates in shared memory with plain loads and stores -- no atomics.  Built on the
-// host once per (transform, shard) from the bucket / value tables.
+// Plan of the strided layout (K2): sketched indices are cut in tiles of 2048; inside a tile the rows
+// of warp w's buckets (w = bucket / SW) are arranged in rounds of 32 rows with 32 different buckets,
+// each half warp on 16 different shared-memory bank pairs for the accumulators and for the tile, so
+// a CTA accumulates in shared memory with plain loads and stores -- no atomics.  Built on the host
+// once per (transform, shard) from the bucket / value tables.
 struct HashColsPlan {
-    uint32_t *entries = nullptr;   // rounds of 32 packed entries: k in tile << 3 | bucket of the lane << 16 | sign << 31
+    uint32_t *entries = nullptr;   // rounds of 32 packed entries: k in tile << 3 | bucket in the warp's range << 16 | sign << 31
     double *vals = nullptr;        // value per entry; null when every value is +-1 (sign bit used)
     uint32_t *off = nullptr;       // first round of (warp, tile): 8 * (ntiles + 1) entries, warp-major streams
     int ntiles = 0, S = 0, SW = 0;
