@@ -394,7 +394,7 @@ void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int3
 // ---------------------------------------------------------------------------
 // K2p: strided layout without atomics (see HashColsPlan).  A CTA owns CG columns and a range of
 // index tiles.  Tiles of 2048 indices x CG columns are staged in shared memory by cp.async
-// (coalesced 16-byte pieces, double buffered, with an L2 prefetch a few tiles ahead).  Warp w owns
+// (coalesced 16-byte pieces, double buffered).  Warp w owns
 // the buckets [w * SW, (w + 1) * SW) and walks the rounds the plan queued for it (one contiguous
 // stream per warp, read ahead across tile boundaries): in a round every lane takes a row of a
 // DIFFERENT bucket, reads the CG values of that index from the tile and does load-add-store on the
@@ -403,12 +403,15 @@ void hash_apply_cols(const double *X, size_t ldx, size_t n, size_t m, const int3
 // in ascending order (the reference's rounding sequence, hash_transform_Elemental.hpp:83-100), the
 // accumulators are written out once.
 // History at C1 (100k x 500 -> 2000, column-major): 0.216 ms with shared-memory atomics; 0.172 ms
-// with lane-owned buckets (44 % of the lane slots busy); 0.117 ms in this form.  What did NOT help:
+// with lane-owned buckets (44 % of the lane slots busy); 0.109 ms in this form.  What did NOT help:
 // several batches of entry loads in flight per warp (waiting on the oldest also waits for the
 // newer ones that share its scoreboard), and denser rounds without the bank-pair matching (as many
 // wavefronts as before, in fewer instructions).
 // ---------------------------------------------------------------------------
-constexpr int HC_K = 2048, HC_W = 8, HC_THREADS = HC_W * 32, HC_NBUF = 2, HC_PF = 4;
+#ifndef SKB_HC_PF
+#define SKB_HC_PF 0          // L2 prefetch distance in tiles (0 = none: measured 0.109 ms at C1, 4: 0.113, 8: 0.127)
+#endif
+constexpr int HC_K = 2048, HC_W = 8, HC_THREADS = HC_W * 32, HC_NBUF = 2, HC_PF = SKB_HC_PF;
 #ifndef SKB_HC_NB
 #define SKB_HC_NB 8
 #endif
@@ -451,6 +454,7 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
     const int SW = plan->SW;
     std::vector<std::vector<uint32_t>> fifo((size_t)HC_W * SW);
     std::vector<uint32_t> head((size_t)SW), cand;
+    std::vector<char> in_group((size_t)SW);
     for (size_t t = 0; t < nt; t++) {
         const size_t k0 = t * HC_K, k1 = std::min(n, k0 + HC_K);
         for (auto &f : fifo) f.clear();
@@ -469,8 +473,11 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
                 // pairs AND 16 different tile bank pairs (a matching between the two), so each of its
                 // six shared-memory accesses is one wavefront.  Rows whose bank pairs have the most
                 // rows left go first -- those pairs decide how many rounds the tile needs.
+                // (the HC_B rounds the kernel applies together also keep to different buckets: it reads
+                // all their accumulators before it stores any)
+                if (nr % HC_B == 0) std::fill(in_group.begin(), in_group.end(), 0);
                 cand.clear();
-                for (int bk = 0; bk < SW; bk++) if (head[bk] < fw[bk].size()) cand.push_back((uint32_t)bk);
+                for (int bk = 0; bk < SW; bk++) if (head[bk] < fw[bk].size() && !in_group[bk]) cand.push_back((uint32_t)bk);
                 std::stable_sort(cand.begin(), cand.end(), [&](uint32_t x, uint32_t y) {
                     const int px = std::max(degA[x & 15], degX[fw[x][head[x]] & 15]);
                     const int py = std::max(degA[y & 15], degX[fw[y][head[y]] & 15]);
@@ -491,7 +498,7 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
                         if (fill[g] < 16 && !acc_used[g][c] && !x_used[g][xc]) h = g;
                     }
                     if (h < 0) continue;
-                    head[bk]++; left--; degA[c]--; degX[xc]--;
+                    head[bk]++; left--; degA[c]--; degX[xc]--; in_group[bk] = 1;
                     slot_b[h * 16 + fill[h]] = (int)bk; slot_k[h * 16 + fill[h]] = kk;
                     fill[h]++; acc_used[h][c] = true; x_used[h][xc] = true;
                 }
@@ -607,7 +614,7 @@ k_hash_cols_plan(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
             }
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
-        if (tid < ncol) {                                   // keep L2 a few tiles ahead of the staging loads
+        if (HC_PF > 0 && tid < ncol) {                      // keep L2 a few tiles ahead of the staging loads
             const size_t kp = (size_t)(t + HC_PF) * HC_K;
             if (t + HC_PF < t1 && kp + HC_K <= n)
                 asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(X + kp + (j0 + tid) * ldx), "r"(HC_K * 8));
@@ -673,10 +680,10 @@ k_hash_cols_plan(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
             }
             if (!live) return;
             if (dbg & 2) { r = rend; continue; }
-            // all tile reads of the group first (the tile is read-only), then round by round: two
-            // rounds may hit the same bucket
+            // the plan keeps the HC_B * 32 rows of a group on different buckets: all loads, then the
+            // adds, then all stores
             unsigned aa[HC_B];
-            double x[HC_B][CG];
+            double x[HC_B][CG], a[HC_B][CG];
 #pragma unroll
             for (int i = 0; i < HC_B; i++) {
                 const uint32_t e = e_[g + i];
@@ -684,23 +691,24 @@ k_hash_cols_plan(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
                 aa[i] = accb + ((e >> 13) & 0xFFF8u);                           // bucket of the warp: (e >> 16) & 0x1fff
 #pragma unroll
                 for (int c = 0; c < CG; c++) x[i][c] = hc_lds(xa + c * (HC_K * 8));
+#pragma unroll
+                for (int c = 0; c < CG; c++) a[i][c] = hc_lds(aa[i] + c * SPp * 8);
             }
 #pragma unroll
             for (int i = 0; i < HC_B; i++) {
                 const uint32_t e = e_[g + i];
-                double a[CG];
-#pragma unroll
-                for (int c = 0; c < CG; c++) a[c] = hc_lds(aa[i] + c * SPp * 8);
 #pragma unroll
                 for (int c = 0; c < CG; c++) {              // product, then sum: the reference's rounding
                     const double p = SIGN ? __hiloint2double(__double2hiint(x[i][c]) ^ (int)(e & 0x80000000u), __double2loint(x[i][c]))
                                           : __dmul_rn(v_[g + i], x[i][c]);
-                    a[c] = __dadd_rn(a[c], p);
+                    a[i][c] = __dadd_rn(a[i][c], p);
                 }
-#pragma unroll
-                for (int c = 0; c < CG; c++) hc_sts(aa[i] + c * SPp * 8, a[c]);
-                __syncwarp();               // the next round's lanes may read what other lanes stored here
             }
+#pragma unroll
+            for (int i = 0; i < HC_B; i++)
+#pragma unroll
+                for (int c = 0; c < CG; c++) hc_sts(aa[i] + c * SPp * 8, a[i][c]);
+            __syncwarp();                   // the next group's lanes may read what other lanes stored here
             r += HC_B;
         }
     };
