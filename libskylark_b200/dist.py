@@ -11,6 +11,8 @@ dense_transform_Elemental_coldist_star.hpp:228).  Here the partition is contiguo
 the sum is an NCCL collective over NVLink.  Rowwise sketches of column-sharded data (feature
 maps over sharded data points) need no collective: call `apply` on each rank.
 """
+import os
+
 import numpy
 
 
@@ -137,6 +139,87 @@ def exchange_sparse_partials(indptr, indices, values, group=None, reorder=True):
     return out_indptr.to(torch.int32), oidx, oval, (col0, ncols)
 
 
+def exchange_merge_pipelined(indptr, indices, values, nrows, group=None, nblocks=4):
+    """exchange_sparse_partials(reorder=False) + sketch.merge_segments, cut in `nblocks` rounds: round
+    q moves, for every destination, the q-th slice of that destination's columns.  All rounds are
+    queued on NCCL at once (one count exchange and one host read of the split sizes for all of
+    them; grouped send/recv straight from slices of the partial, no packing copy), and the merge
+    kernel of round q runs while round q + 1 is on the wire.  Returns (lib.DeviceCSC of shape
+    nrows x columns_of_this_rank, (first_column, columns)).  CUDA + NCCL only."""
+    import torch
+    import torch.distributed as dist
+    from . import lib, sketch
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = indptr.device
+    dbg = os.environ.get("SKB_DIST_DEBUG") and rank == 0
+    if dbg:
+        import time
+        marks = []
+
+        def mark(tag):
+            ev = torch.cuda.Event(enable_timing=True); ev.record()
+            marks.append((tag, time.perf_counter(), ev))
+        mark("start")
+    d = indptr.numel() - 1
+    blocks = [shard_range(d, r, world) for r in range(world)]
+    col0, ncols = blocks[rank]
+    # column edges of (destination r, round q): edge[r][q] .. edge[r][q + 1]
+    edge = [[b0 + (bn * q) // nblocks for q in range(nblocks + 1)] for (b0, bn) in blocks]
+    my = [e - col0 for e in edge[rank]]                                # this rank's slices, local columns
+    ip = indptr.to(torch.int64)
+    counts = (ip[1:] - ip[:-1]).to(torch.int32).contiguous()            # entries per column
+    recv_counts = torch.empty(world * ncols, dtype=torch.int32, device=dev)
+    dist.all_to_all_single(recv_counts, counts, output_split_sizes=[ncols] * world,
+                           input_split_sizes=[b[1] for b in blocks], group=group)
+    C = recv_counts.view(world, ncols)                                  # C[s, j]: entries of column j from rank s
+    flat_edges = torch.tensor([e for r in range(world) for e in edge[r]], device=dev)
+    Ccum = torch.zeros(world, ncols + 1, dtype=torch.int64, device=dev)
+    Ccum[:, 1:] = torch.cumsum(C, 1)
+    my_t = torch.tensor(my, device=dev)
+    # ONE host read: send offsets at every (r, q) edge, receive sizes of every (source, round)
+    host = torch.cat([ip[flat_edges], (Ccum[:, my_t[1:]] - Ccum[:, my_t[:-1]]).reshape(-1)]).tolist()
+    send_off = [host[r * (nblocks + 1):(r + 1) * (nblocks + 1)] for r in range(world)]
+    recv_n = host[world * (nblocks + 1):]                               # [source][round]
+    if dbg:
+        mark("sizes on host")
+    works, bufs = [], []
+    for q in range(nblocks):
+        n_from = [int(recv_n[sr * nblocks + q]) for sr in range(world)]
+        tot = sum(n_from)
+        ridx = torch.empty(tot, dtype=indices.dtype, device=dev)
+        rval = torch.empty(tot, dtype=values.dtype, device=dev)
+        o_idx = list(torch.split(ridx, n_from)); o_val = list(torch.split(rval, n_from))
+        i_idx = [indices[int(send_off[r][q]):int(send_off[r][q + 1])] for r in range(world)]
+        i_val = [values[int(send_off[r][q]):int(send_off[r][q + 1])] for r in range(world)]
+        w1 = dist.all_to_all(o_idx, i_idx, group=group, async_op=True)
+        w2 = dist.all_to_all(o_val, i_val, group=group, async_op=True)
+        works.append((w1, w2)); bufs.append((ridx, rval))
+    if dbg:
+        mark("rounds queued")
+    parts = []
+    for q in range(nblocks):
+        works[q][0].wait(); works[q][1].wait()
+        if dbg:
+            mark("round %d arrived" % q)
+        ncq = my[q + 1] - my[q]
+        vptr = torch.zeros(world * ncq + 1, dtype=torch.int32, device=dev)
+        vptr[1:] = torch.cumsum(C[:, my[q]:my[q + 1]].reshape(-1), 0, dtype=torch.int32)
+        parts.append(sketch.merge_segments(vptr, bufs[q][0], bufs[q][1], world, (nrows, ncq)))
+        if dbg:
+            mark("round %d merged" % q)
+    sizes = torch.tensor([0] + [int(p_.indices.numel()) for p_ in parts]).cumsum(0).tolist()
+    out_ip = torch.cat([parts[0].indptr.to(torch.int64)] +
+                       [parts[q].indptr[1:].to(torch.int64) + sizes[q] for q in range(1, nblocks)]).to(torch.int32)
+    merged = lib.DeviceCSC(out_ip, torch.cat([p_.indices for p_ in parts]), torch.cat([p_.values for p_ in parts]),
+                           (nrows, ncols), "csc")
+    if dbg:
+        mark("joined")
+        torch.cuda.synchronize()
+        print("  ".join("%s host %.2f gpu %.2f |" % (t, (h - marks[0][1]) * 1e3, marks[0][2].elapsed_time(e))
+                        for (t, h, e) in marks[1:]), flush=True)
+    return merged, (col0, ncols)
+
+
 def apply_distributed_sparse(S, A_local, index_offset=0, group=None):
     """Columnwise CWT/MMT/WZT of a row-sharded device CSC matrix with a SPARSE exchange: every
     rank sketches its rows into a sparse partial (lib.DeviceCSC, format "csc"), the partials
@@ -150,6 +233,13 @@ def apply_distributed_sparse(S, A_local, index_offset=0, group=None):
                                                        A_local.values.device), 0, index_offset)
     import torch.distributed as dist
     world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+    nblk = int(os.environ.get("SKB_SPARSE_PIPE", "4"))
+    if world > 1 and part.values.is_cuda and nblk > 1 and A_local.shape[1] >= world * nblk * 64 \
+            and part.values.numel() < 2 ** 31:
+        try:
+            return exchange_merge_pipelined(part.indptr, part.indices, part.values, S.getsketchdim(), group, nblk)
+        except lib.errors.LowerLayerError:
+            pass                          # a merged column too long for the shared-memory sort: below
     if world > 1 and part.values.is_cuda:
         # merge straight from the receive buffers (no re-ordering pass); falls back when a merged
         # column is too long for the shared-memory sort
