@@ -105,6 +105,24 @@ def main():
     same = got.indptr.tolist() == w.indptr.tolist() and got.indices.tolist() == w.indices.tolist()
     checks["CWT sparse exchange: pattern identical"] = 0.0 if same else 1.0
     checks["CWT sparse exchange: values"] = float(np.linalg.norm(got.data - w.data) / np.linalg.norm(w.data)) if same else 1.0
+    # --- the same through the pipelined rounds (enough columns for dist.exchange_merge_pipelined):
+    # entry for entry what the one-shot exchange gives
+    ds2 = 320 * world
+    Asp2 = scipy.sparse.random(ns, ds2, 0.02, format="csc", random_state=10, dtype=np.float64)
+    sh2 = Asp2[off2:off2 + cnt2].tocsc()
+    Ad2 = lib.DeviceCSC(torch.from_numpy(sh2.indptr.astype(np.int32)).to(dev), torch.from_numpy(sh2.indices.astype(np.int32)).to(dev),
+                        torch.from_numpy(sh2.data).to(dev), (cnt2, ds2))
+    os.environ["SKB_SPARSE_PIPE"] = "1"
+    one, (c0, nc) = sd.apply_distributed_sparse(C, Ad2, off2)
+    os.environ["SKB_SPARSE_PIPE"] = "4"
+    pip, (c0p, ncp) = sd.apply_distributed_sparse(C, Ad2, off2)
+    os.environ.pop("SKB_SPARSE_PIPE")
+    ident = (c0, nc) == (c0p, ncp) and torch.equal(one.indptr, pip.indptr) and torch.equal(one.indices, pip.indices) \
+        and torch.equal(one.values, pip.values)
+    checks["CWT sparse exchange in rounds == one shot (bitwise)"] = 0.0 if ident else 1.0
+    want2 = o.CWT(ns, ss, o.Context(41)).apply_csc_sparse(Asp2, "columnwise")[:, c0:c0 + nc].tocsc()
+    got2 = scipy.sparse.csc_matrix((pip.values.cpu().numpy(), pip.indices.cpu().numpy(), pip.indptr.cpu().numpy()), shape=(ss, nc))
+    checks["CWT sparse exchange in rounds vs oracle"] = float(abs(got2 - want2).max()) / float(abs(want2).max())
     bad = {k: v for k, v in checks.items() if not v < 1e-12}
     for k, v in checks.items():
         print("rank %d  %-50s %.3e" % (rank, k, v), flush=True)
