@@ -791,6 +791,7 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
     int hC[PRE]; double wC[PRE], xC[PRE];          // current column: bucket, table value, entry
     int rN[PRE]; double xN[PRE];                   // next column: row index, entry
     int q0 = 0, q1 = 0;                            // column after next: its indptr pair
+    int e0 = 0, e1 = 0, t0 = 0, t1 = 0;            // the same pair, carried along with the column's stages
     auto load_ptr = [&](size_t col) {
         q0 = q1 = 0;
         if (col < ncols) { q0 = indptr[col]; q1 = indptr[col + 1]; }
@@ -802,6 +803,7 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
             rN[i] = -1; xN[i] = 0.0;
             if (p < q1) { rN[i] = indices[p]; xN[i] = values[p]; }
         }
+        e0 = q0; e1 = q1;
     };
     auto load_tables = [&]() {                     // uses rN/xN, fills hC/wC/xC
 #pragma unroll
@@ -809,6 +811,7 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
             hC[i] = -1; wC[i] = 0.0; xC[i] = xN[i];
             if (rN[i] >= 0) { hC[i] = bucket[rN[i]]; wC[i] = value[rN[i]]; }
         }
+        t0 = e0; t1 = e1;
     };
     // prologue: column c fully staged, column c+stride at the entry stage, c+2*stride at indptr
     load_ptr(blockIdx.x); load_entries(); load_tables();
@@ -818,8 +821,9 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
 #pragma unroll
         for (int i = 0; i < PRE; i++)
             if (hC[i] >= 0) atomicAdd(&acc[hC[i]], __dmul_rn(wC[i], xC[i]));
-        {   // columns with more than PRE * blockDim nonzeros
-            const int p0 = indptr[col], p1 = indptr[col + 1];
+        {   // columns with more than PRE * blockDim nonzeros (p0, p1 arrived three columns ago: a
+            // fresh indptr load here would put an L2 round trip on every column's critical path)
+            const int p0 = t0, p1 = t1;
             for (int p = p0 + PRE * (int)blockDim.x + (int)threadIdx.x; p < p1; p += blockDim.x) {
                 const int row = indices[p];
                 atomicAdd(&acc[bucket[row]], __dmul_rn(value[row], values[p]));
