@@ -847,6 +847,117 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
     }
 }
 
+__device__ __forceinline__ uint64_t hc_policy_evict_last() {
+    uint64_t pol; asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol)); return pol;
+}
+__device__ __forceinline__ uint64_t hc_policy_evict_first() {
+    uint64_t pol; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol)); return pol;
+}
+__device__ __forceinline__ int ldg_i32_hint(const int32_t *p, uint64_t pol) {
+    int v; asm volatile("ld.global.nc.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol)); return v;
+}
+__device__ __forceinline__ double ldg_f64_hint(const double *p, uint64_t pol) {
+    double v; asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol)); return v;
+}
+// K3, bulk-store form.  Measured on the C4 shard: the loads + shared-memory sums of all columns take
+// 1.5 ms, writing the 16 GB takes 2.1 - 2.6 ms (the write ceiling is 7.5 TB/s; 148 CTAs streaming whole
+// columns reach 6.0 - 6.4, tools/colwrite_bw.cu), and a kernel with one S-vector per SM that dumps a
+// column and then starts the next pays the SUM (3.7 ms, whether 512 threads store from registers or
+// one bulk copy does).  Here a CTA holds only a SLICE of the S-vector (S / NH slots) and walks the NH
+// slices of its column one after the other: sum the nonzeros whose bucket falls in the slice (they
+// stay in registers for all slices, so nothing is gathered twice), hand the slice to the copy engine
+// (cp.async.bulk.global.shared::cta: no registers, no LSU queue), wait until the engine has READ it,
+// re-zero the slots it touched.  Several such CTAs share an SM, so one's copy streams while the
+// others sum.  L2 hints keep the 15 MB bucket / value tables resident under the 16 GB write stream
+// (output and nonzeros evict-first, tables evict-last): without them 3.9 ms, with them 3.4 at NH = 2
+// in one CTA per SM.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+k_hash_csc_colwise_bulk(const int32_t *__restrict__ indptr, const int32_t *__restrict__ indices,
+                        const double *__restrict__ values, size_t ncols,
+                        const int32_t *__restrict__ bucket, const double *__restrict__ value,
+                        double *__restrict__ OUT, size_t ldo, int S, int NH, int dbg) {
+    extern __shared__ __align__(16) double acc[];   // [S / NH]; (S / NH) % 2 == 0, columns 16-byte aligned
+    const int H = S / NH;
+    for (int i = threadIdx.x; i < H; i += THREADS) acc[i] = 0.0;
+    __syncthreads();
+    constexpr int PRE = 2048 / THREADS;             // nonzeros per thread held in registers
+    const size_t stride = gridDim.x;
+    const unsigned acc_s = (unsigned)__cvta_generic_to_shared(acc);
+    const uint64_t pol_first = hc_policy_evict_first(), pol_last = hc_policy_evict_last();
+    int hC[PRE]; double wC[PRE], xC[PRE];
+    int rN[PRE]; double xN[PRE];
+    int q0 = 0, q1 = 0, e0 = 0, e1 = 0, t0 = 0, t1 = 0;
+    auto load_ptr = [&](size_t col) {
+        q0 = q1 = 0;
+        if (col < ncols) { q0 = indptr[col]; q1 = indptr[col + 1]; }
+    };
+    auto load_entries = [&]() {
+#pragma unroll
+        for (int i = 0; i < PRE; i++) {
+            const int p = q0 + (int)threadIdx.x + i * THREADS;
+            rN[i] = -1; xN[i] = 0.0;
+            if (p < q1) { rN[i] = ldg_i32_hint(indices + p, pol_first); xN[i] = ldg_f64_hint(values + p, pol_first); }
+        }
+        e0 = q0; e1 = q1;
+    };
+    auto load_tables = [&]() {
+#pragma unroll
+        for (int i = 0; i < PRE; i++) {
+            hC[i] = -1; wC[i] = 0.0; xC[i] = xN[i];
+            if (rN[i] >= 0) { hC[i] = ldg_i32_hint(bucket + rN[i], pol_last); wC[i] = ldg_f64_hint(value + rN[i], pol_last); }
+        }
+        t0 = e0; t1 = e1;
+    };
+    load_ptr(blockIdx.x); load_entries(); load_tables();
+    load_ptr(blockIdx.x + stride); load_entries();
+    load_ptr(blockIdx.x + 2 * stride);
+    int hP[PRE];                       // buckets whose slots are still set in the buffer (previous slice)
+#pragma unroll
+    for (int i = 0; i < PRE; i++) hP[i] = -1;
+    int pp0 = 0, pp1 = 0, plo = 0;     // the same for nonzeros beyond the registers: their range and slice
+    for (size_t col = blockIdx.x; col < ncols; col += stride) {
+        const int p0 = t0, p1 = t1;
+        int hN[PRE]; double vN[PRE];
+#pragma unroll
+        for (int i = 0; i < PRE; i++) { hN[i] = hC[i]; vN[i] = __dmul_rn(wC[i], xC[i]); }
+        load_tables();                 // column col + stride   (this column's registers are copied above)
+        load_entries();                // column col + 2*stride
+        load_ptr(col + 3 * stride);
+        for (int sl = 0; sl < NH; sl++) {
+            const int lo = sl * H, hi = lo + H;
+            // the engine has read the previous slice out of the buffer
+            if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncthreads();
+#pragma unroll
+            for (int i = 0; i < PRE; i++) if (hP[i] >= plo && hP[i] < plo + H) acc[hP[i] - plo] = 0.0;
+            for (int p = pp0 + PRE * THREADS + (int)threadIdx.x; p < pp1; p += THREADS) {
+                const int h = bucket[indices[p]];
+                if (h >= plo && h < plo + H) acc[h - plo] = 0.0;
+            }
+            __syncthreads();           // the buffer is all zeros again
+#pragma unroll
+            for (int i = 0; i < PRE; i++)
+                if (hN[i] >= lo && hN[i] < hi && !(dbg & 2)) atomicAdd(&acc[hN[i] - lo], vN[i]);
+            for (int p = p0 + PRE * THREADS + (int)threadIdx.x; p < p1; p += THREADS) {
+                const int row = indices[p], h = bucket[row];
+                if (h >= lo && h < hi) atomicAdd(&acc[h - lo], __dmul_rn(value[row], values[p]));
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // the sums, for the copy engine
+            __syncthreads();
+            if (threadIdx.x == 0 && !(dbg & 1)) {
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(OUT + col * ldo + lo),
+                             "r"(acc_s), "r"(H * 8), "l"(pol_first) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+#pragma unroll
+            for (int i = 0; i < PRE; i++) hP[i] = hN[i];
+            pp0 = p0; pp1 = p1; plo = lo;
+        }
+    }
+    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 __global__ void k_hash_csc_colwise_global(const int32_t *__restrict__ indptr,
                                           const int32_t *__restrict__ indices,
                                           const double *__restrict__ values, size_t ncols,
@@ -875,6 +986,36 @@ void hash_apply_csc_columnwise(const int32_t *indptr, const int32_t *indices,
     if (force_global < 0) force_global = getenv("SKB_DEBUG_CSC_GLOBAL") ? 1 : 0;
     if (smem <= 220 * 1024 && !force_global) {
         const bool vec2 = (ldo % 2 == 0) && ((uintptr_t)OUT % 16 == 0);
+        static const bool no_bulk = getenv("SKB_CSC_DUMP") != nullptr;         // A/B: the register dump
+        const bool bulk = vec2 && S % 4 == 0 && !no_bulk;
+        static const int dbg = getenv("SKB_CSC_DBG") ? atoi(getenv("SKB_CSC_DBG")) : 0;   // timing experiments only
+        if (bulk) {
+            // slices per column / threads per CTA: SKB_CSC_NH, SKB_CSC_THREADS (tuning)
+            static const int nh_env = getenv("SKB_CSC_NH") ? atoi(getenv("SKB_CSC_NH")) : 0;
+            static const int th_env = getenv("SKB_CSC_THREADS") ? atoi(getenv("SKB_CSC_THREADS")) : 0;
+            int NH = nh_env > 0 ? nh_env : 2;
+            while (NH > 1 && (S % (2 * NH) != 0)) NH--;
+            const int threads = th_env == 512 ? 512 : 256;     // measured at the C4 shard: 3.30 ms (256) / 3.81 (512) at NH = 2
+            const size_t sl_bytes = (size_t)(S / NH) * sizeof(double);
+            int per_sm = (int)((220 * 1024) / (sl_bytes + 1024));
+            const int cap = threads == 256 ? 8 : 2;          // register file: 62 registers x threads
+            if (per_sm > cap) per_sm = cap;
+            if (per_sm < 1) per_sm = 1;
+            size_t grid = (size_t)148 * per_sm;
+            if (grid > ncols) grid = ncols;
+            LaunchScope ls(KC_HASH, st);
+            if (threads == 256) {
+                SKB_CUDA(cudaFuncSetAttribute(k_hash_csc_colwise_bulk<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sl_bytes));
+                k_hash_csc_colwise_bulk<256><<<(unsigned)grid, 256, sl_bytes, st>>>(indptr, indices, values, ncols, bucket, value,
+                                                                                    OUT, ldo, S, NH, dbg);
+            } else {
+                SKB_CUDA(cudaFuncSetAttribute(k_hash_csc_colwise_bulk<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sl_bytes));
+                k_hash_csc_colwise_bulk<512><<<(unsigned)grid, 512, sl_bytes, st>>>(indptr, indices, values, ncols, bucket, value,
+                                                                                    OUT, ldo, S, NH, dbg);
+            }
+            SKB_CUDA(cudaGetLastError());
+            return;
+        }
         auto kern = vec2 ? k_hash_csc_colwise_smem<true> : k_hash_csc_colwise_smem<false>;
         SKB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int per_sm = smem <= 100 * 1024 ? 2 : 1;
