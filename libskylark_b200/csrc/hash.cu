@@ -559,6 +559,21 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
     } catch (...) { hash_free_cols_plan(plan); throw; }
 }
 
+__device__ __forceinline__ uint64_t hc_policy_evict_last() {
+    uint64_t pol; asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol)); return pol;
+}
+__device__ __forceinline__ uint64_t hc_policy_evict_first() {
+    uint64_t pol; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol)); return pol;
+}
+__device__ __forceinline__ int ldg_i32_hint(const int32_t *p, uint64_t pol) {
+    int v; asm volatile("ld.global.nc.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol)); return v;
+}
+__device__ __forceinline__ double ldg_f64_hint(const double *p, uint64_t pol) {
+    double v; asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol)); return v;
+}
+__device__ __forceinline__ unsigned ldg_u32_hint(const uint32_t *p, uint64_t pol) {
+    unsigned v; asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol)); return v;
+}
 __device__ __forceinline__ double hc_lds(unsigned a) {
     double v; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v;
 }
@@ -586,6 +601,8 @@ k_hash_cols_plan(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
     // that are not written out; start those from zeros all the same
     for (int i = tid; i < CG * SPp + HC_NBUF * CG * HC_K; i += HC_THREADS) hc_smem[i] = 0.0;
     __syncthreads();
+    // the plan entries are re-read by every CTA while the operand streams through L2: ask for them to stay
+    const uint64_t pol_last = hc_policy_evict_last();
     auto issue = [&](int t, int buf) {
         const size_t k0 = (size_t)t * HC_K;
         const int len = (int)min((size_t)HC_K, n - k0);
@@ -645,7 +662,7 @@ k_hash_cols_plan(const double *__restrict__ X, size_t ldx, size_t n, size_t m,
 #pragma unroll
         for (int i = 0; i < HC_NB; i++) {
             if (dbg & 4) e[i] = (((unsigned)(size_t)ep_ * 2654435761u + (unsigned)lane * 40503u + (unsigned)i * 977u) & 0x3FF8u) | (((unsigned)lane * 7u + (unsigned)i) & 0xffu) << 16;
-            else e[i] = __ldg(ep_ + i * 32);
+            else e[i] = ldg_u32_hint(ep_ + i * 32, pol_last);
             v[i] = SIGN ? 0.0 : __ldg(vp_ + i * 32);
         }
         ep += HC_NB * 32; vp += HC_NB * 32;
@@ -847,18 +864,6 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
     }
 }
 
-__device__ __forceinline__ uint64_t hc_policy_evict_last() {
-    uint64_t pol; asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol)); return pol;
-}
-__device__ __forceinline__ uint64_t hc_policy_evict_first() {
-    uint64_t pol; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol)); return pol;
-}
-__device__ __forceinline__ int ldg_i32_hint(const int32_t *p, uint64_t pol) {
-    int v; asm volatile("ld.global.nc.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol)); return v;
-}
-__device__ __forceinline__ double ldg_f64_hint(const double *p, uint64_t pol) {
-    double v; asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol)); return v;
-}
 // K3, bulk-store form.  Measured on the C4 shard: the loads + shared-memory sums of all columns take
 // 1.5 ms, writing the 16 GB takes 2.1 - 2.6 ms (the write ceiling is 7.5 TB/s; 148 CTAs streaming whole
 // columns reach 6.0 - 6.4, tools/colwrite_bw.cu), and a kernel with one S-vector per SM that dumps a
