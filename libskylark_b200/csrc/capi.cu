@@ -472,7 +472,7 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
         const int32_t *b = d.bucket + offset; const double *v = d.value + offset;
         if (colwise)
             hash_apply_csc_columnwise(A->indptr, A->indices, A->values, (size_t)A->n, b, v,
-                                      (double *)SA->data, (size_t)SA->ld, t->S, st);
+                                      (double *)SA->data, (size_t)SA->ld, t->S, st, (size_t)A->nnz);
         else
             hash_apply_csc_rowwise(A->indptr, A->indices, A->values, (size_t)A->m, (size_t)A->n, b,
                                    v, (double *)SA->data, (size_t)SA->ld, t->S, st);

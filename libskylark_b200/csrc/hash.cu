@@ -984,7 +984,7 @@ __global__ void k_hash_csc_colwise_global(const int32_t *__restrict__ indptr,
 void hash_apply_csc_columnwise(const int32_t *indptr, const int32_t *indices,
                                const double *values, size_t ncols, const int32_t *bucket,
                                const double *value, double *OUT, size_t ldo, int S,
-                               cudaStream_t st) {
+                               cudaStream_t st, size_t nnz_hint) {
     if (ncols == 0) return;
     size_t smem = (size_t)S * sizeof(double);
     static int force_global = -1;
@@ -992,7 +992,10 @@ void hash_apply_csc_columnwise(const int32_t *indptr, const int32_t *indices,
     if (smem <= 220 * 1024 && !force_global) {
         const bool vec2 = (ldo % 2 == 0) && ((uintptr_t)OUT % 16 == 0);
         static const bool no_bulk = getenv("SKB_CSC_DUMP") != nullptr;         // A/B: the register dump
-        const bool bulk = vec2 && S % 4 == 0 && !no_bulk;
+        // the bulk form keeps a column's nonzeros in registers (2048 per CTA) across its slices; longer
+        // columns would be gathered once per slice and once more to re-zero: those keep the dump form
+        // (C4 column-sharded, 10000 nonzeros per column: 3.2 ms against 7.1)
+        const bool bulk = vec2 && S % 4 == 0 && !no_bulk && nnz_hint > 0 && nnz_hint / ncols <= 1536;
         static const int dbg = getenv("SKB_CSC_DBG") ? atoi(getenv("SKB_CSC_DBG")) : 0;   // timing experiments only
         if (bulk) {
             // slices per column / threads per CTA: SKB_CSC_NH, SKB_CSC_THREADS (tuning)

@@ -87,6 +87,29 @@ def test_scipy_sparse_input(sk, oracle, T, fmt):
     assert np.count_nonzero(S.apply(E, np.empty((s, 5), order=order), 0)) == 0
 
 
+@pytest.mark.parametrize("T", ["CWT", "MMT"])
+@pytest.mark.parametrize("case", ["few long columns", "all columns long"])
+def test_csc_to_dense_long_columns(sk, oracle, T, case):
+    """CSC -> dense with columns beyond the 2048 nonzeros a CTA of the bulk-store kernel holds in
+    registers (its overflow loops), and with long columns throughout (the register-dump kernel, picked by
+    the average column length); s % 4 == 0 and a column-major result, as both kernels need."""
+    n, s = 12000, 128
+    rng = np.random.default_rng(5)
+    lens = [60] * 30 + [3000, 5000, 2049] if case == "few long columns" else [2600] * 7
+    cols = [np.sort(rng.choice(n, size=L, replace=False)) for L in lens]
+    indptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    A = scipy.sparse.csc_matrix((rng.standard_normal(indptr[-1]), np.concatenate(cols).astype(np.int32), indptr),
+                                shape=(n, len(lens)))
+    S, O = _pair(sk, oracle, T, n, s)
+    want = O.apply(A.toarray(), "columnwise")
+    got = S.apply(A, np.empty((s, len(lens)), order="F"), "columnwise")
+    assert rel_fro(got, want) < TOL
+    # a second apply starts from clean shared accumulators (sums of a slot are taken with shared-memory
+    # atomics, so the two results agree to rounding, not bitwise)
+    got2 = S.apply(A, np.empty((s, len(lens)), order="F"), "columnwise")
+    assert rel_fro(got2, want) < TOL
+
+
 def _canon(M):
     M = scipy.sparse.csc_matrix(M).copy()
     M.sort_indices()
