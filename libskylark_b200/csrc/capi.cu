@@ -494,7 +494,7 @@ static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const s
             // strided layout: the atomics-free planned kernel when the shape allows, for operands
             // large enough to pay for building the plan once (host side, O(n))
             bool done = false;
-            if ((size_t)sk * (size_t)other >= ((size_t)1 << 20) && t->S <= 23552) {
+            if ((size_t)sk * (size_t)other >= ((size_t)1 << 20) && t->S >= 256 && t->S <= 23552) {
                 auto key = std::make_pair((size_t)offset, (size_t)sk);
                 auto it = d.cplans.find(key);
                 if (it == d.cplans.end()) {

@@ -750,7 +750,10 @@ bool hash_apply_cols_planned(const double *X, size_t ldx, size_t n, size_t m, co
                              double *OUT, size_t ldo, int S, cudaStream_t st) {
     static const bool off_env = getenv("SKB_DEBUG_NO_COLS_PLAN") != nullptr;
     if (off_env || m == 0 || n == 0 || plan.n != n || plan.S != S || !plan.entries) return false;
-    if (S > 32767 || (ldx & 1) || ((uintptr_t)X & 15)) return false;
+    // fewer than 32 buckets per warp leave warps (S < 256: 8 warps x 32 buckets) without work while the
+    // others serialise on their few buckets: the shared-atomics kernel is faster there (measured at
+    // 100k x 500: S = 32: 0.26 ms against 0.46; 64: 0.22 / 0.27; 256: equal; 1000: 0.175 / 0.113)
+    if (S < 256 || S > 32767 || (ldx & 1) || ((uintptr_t)X & 15)) return false;
     const int SPp = hc_acc_stride(plan.SW);
     auto smem_for = [&](int cg) { return ((size_t)cg * SPp + (size_t)HC_NBUF * cg * HC_K) * sizeof(double) + HC_W * 64 * sizeof(uint32_t); };
     // two columns per CTA and two CTAs per SM (one's barriers and staging overlap the other's rounds)

@@ -349,11 +349,12 @@ def test_serialized_sketch_replays_identically(sk, oracle):
 
 
 @pytest.mark.parametrize("T,shape", [("CWT", (100000, 500, 2000)), ("CWT", (30001, 70, 513)), ("MMT", (40000, 37, 5000)),
-                                     ("WZT", (50000, 26, 20000)), ("CWT", (4097, 300, 64))])
+                                     ("WZT", (50000, 26, 20000)), ("CWT", (4097, 300, 256)), ("CWT", (4097, 300, 64))])
 def test_strided_layout_planned_kernel(sk, oracle, T, shape):
     """Column-major operands (the reference-native Elemental layout, hash_transform_Elemental.hpp:83-100)
-    large enough for the atomics-free kernel: buckets owned by lanes, tiles staged in shared memory.
-    C1's shape, 4 / 2 / 1 columns per CTA (by S), ragged column groups, odd n, valued transforms;
+    large enough for the atomics-free kernel: buckets owned by warps, rounds matched to bank pairs, tiles
+    staged in shared memory.  C1's shape, 4 / 2 / 1 columns per CTA (by S), ragged column groups, odd n,
+    valued transforms, the smallest S the kernel takes (256) and one below it (the shared-atomics kernel);
     CWT sums follow the reference's order, so the result is bit-identical to the oracle's."""
     import torch
     n, d, s = shape

@@ -1,7 +1,7 @@
 import torch, statistics, sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from libskylark_b200 import lib, sketch
-n,d,s=100000,500,2000
+n,d,s=100000,500,int(os.environ.get("C1_S","2000"))
 A=torch.randn(d,n,dtype=torch.float64,device="cuda").t()
 flush=torch.empty(256<<20,dtype=torch.uint8,device="cuda")
 S=sketch.CWT(n,s,lib.Context(123834))
