@@ -455,19 +455,31 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
     std::vector<std::vector<uint32_t>> fifo((size_t)HC_W * SW);
     std::vector<uint32_t> head((size_t)SW), cand;
     std::vector<char> in_group((size_t)SW);
+    // a tile touches at most 2048 of the HC_W * SW buckets: only those are visited (the cost of a plan
+    // stays O(n log) whatever S is)
+    std::vector<int> touched;
+    std::vector<std::vector<uint32_t>> live(HC_W);         // per warp: its buckets with rows in this tile
     for (size_t t = 0; t < nt; t++) {
         const size_t k0 = t * HC_K, k1 = std::min(n, k0 + HC_K);
-        for (auto &f : fifo) f.clear();
-        for (size_t k = k0; k < k1; k++) fifo[(size_t)hb[k]].push_back((uint32_t)(k - k0));   // hb < S <= HC_W * SW
+        for (int h : touched) fifo[(size_t)h].clear();
+        touched.clear();
+        for (int w = 0; w < HC_W; w++) live[w].clear();
+        for (size_t k = k0; k < k1; k++) {                  // hb < S <= HC_W * SW
+            const int h = hb[k];
+            if (fifo[(size_t)h].empty()) { touched.push_back(h); live[h / SW].push_back((uint32_t)(h % SW)); }
+            fifo[(size_t)h].push_back((uint32_t)(k - k0));
+        }
         for (int w = 0; w < HC_W; w++) {
             off[(size_t)w * (nt + 1) + t] = (uint32_t)wr[w];         // made absolute below
             std::vector<uint32_t> *fw = fifo.data() + (size_t)w * SW;
+            std::sort(live[w].begin(), live[w].end());              // bucket order: ties below resolve as before
             size_t left = 0;
-            for (int bk = 0; bk < SW; bk++) { head[bk] = 0; left += fw[bk].size(); }
             size_t nr = 0;
             int degA[16] = {0}, degX[16] = {0};           // rows left per accumulator / tile bank pair
-            for (int bk = 0; bk < SW; bk++)
+            for (uint32_t bk : live[w]) {
+                head[bk] = 0; left += fw[bk].size(); in_group[bk] = 0;
                 for (uint32_t kk : fw[bk]) { degA[bk & 15]++; degX[kk & 15]++; }
+            }
             while (left) {
                 // one round = two half warps; a half warp takes rows with 16 different accumulator bank
                 // pairs AND 16 different tile bank pairs (a matching between the two), so each of its
@@ -475,9 +487,9 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
                 // rows left go first -- those pairs decide how many rounds the tile needs.
                 // (the HC_B rounds the kernel applies together also keep to different buckets: it reads
                 // all their accumulators before it stores any)
-                if (nr % HC_B == 0) std::fill(in_group.begin(), in_group.end(), 0);
+                if (nr % HC_B == 0) for (uint32_t bk : live[w]) in_group[bk] = 0;
                 cand.clear();
-                for (int bk = 0; bk < SW; bk++) if (head[bk] < fw[bk].size() && !in_group[bk]) cand.push_back((uint32_t)bk);
+                for (uint32_t bk : live[w]) if (head[bk] < fw[bk].size() && !in_group[bk]) cand.push_back(bk);
                 std::stable_sort(cand.begin(), cand.end(), [&](uint32_t x, uint32_t y) {
                     const int px = std::max(degA[x & 15], degX[fw[x][head[x]] & 15]);
                     const int py = std::max(degA[y & 15], degX[fw[y][head[y]] & 15]);
