@@ -6,13 +6,16 @@
 // (de)serialisation that replays the RNG, the error-code convention of
 // base/exception.hpp:9-24.  All arithmetic runs on the GPU; there is no CPU fallback.
 #include <cmath>
+#include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/skylark_b200.h"
@@ -692,6 +695,111 @@ static void apply_host_dense_pipelined(sl_sketch_transform_t *t, sl_matrix_t *A,
     SKB_CUDA(cudaStreamSynchronize(st));
 }
 
+// ---------------------------------------------------------------------------
+// Host -> device copy of a PAGEABLE buffer (numpy arrays, what the reference's callers pass).  One
+// cudaMemcpyAsync from pageable memory runs at the driver's single-threaded staging rate (11.6 GB/s
+// measured on the C1 operand).  Here a few worker threads copy 32 MiB chunks into a ring of pinned
+// buffers and every chunk goes out as its own asynchronous copy, so the host-side memcpy of chunk
+// c + 1 overlaps the transfer of chunk c.  Stream-ordered like cudaMemcpyAsync; the caller's buffer
+// has been read completely when the function returns.  SKB_COPY_THREADS = 0 restores the plain copy.
+// ---------------------------------------------------------------------------
+namespace {
+struct CopyPool {
+    struct Task { char *dst; const char *src; size_t n; };
+    std::vector<std::thread> workers;
+    std::mutex mu;
+    std::condition_variable cv, done_cv;
+    std::vector<Task> q;
+    size_t pending = 0;
+    explicit CopyPool(int n) {
+        for (int i = 0; i < n; i++)
+            workers.emplace_back([this] {
+                for (;;) {
+                    Task t;
+                    {
+                        std::unique_lock<std::mutex> lk(mu);
+                        cv.wait(lk, [this] { return !q.empty(); });
+                        t = q.back(); q.pop_back();
+                    }
+                    memcpy(t.dst, t.src, t.n);
+                    {
+                        std::lock_guard<std::mutex> lk(mu);
+                        if (--pending == 0) done_cv.notify_all();
+                    }
+                }
+            });
+        for (auto &w : workers) w.detach();        // the pool lives as long as the process
+    }
+    void copy(char *dst, const char *src, size_t n) {        // returns when all of [src, src + n) is in dst
+        const size_t parts = workers.size(), piece = ((n + parts - 1) / parts + 4095) / 4096 * 4096;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            for (size_t o = 0; o < n; o += piece) { q.push_back({dst + o, src + o, std::min(piece, n - o)}); pending++; }
+        }
+        cv.notify_all();
+        std::unique_lock<std::mutex> lk(mu);
+        done_cv.wait(lk, [this] { return pending == 0; });
+    }
+};
+struct PinnedRing {
+    static constexpr int NBUF = 3;
+    static constexpr size_t CHUNK = (size_t)32 << 20;
+    char *buf[NBUF] = {nullptr, nullptr, nullptr};
+    cudaEvent_t sent[NBUF] = {nullptr, nullptr, nullptr};
+    bool in_flight[NBUF] = {false, false, false};
+};
+}  // namespace
+
+static int copy_threads() {
+    static int n = -1;
+    if (n < 0) {
+        const char *e = getenv("SKB_COPY_THREADS");
+        const unsigned hw = std::thread::hardware_concurrency();
+        n = (e && *e) ? atoi(e) : (int)std::min(8u, std::max(2u, hw / 2));
+        if (n < 0) n = 0;
+        if (n > 32) n = 32;
+    }
+    return n;
+}
+
+static void h2d_from_pageable(void *dst_dev, const void *src_host, size_t bytes, int device, cudaStream_t st) {
+    bool pageable = true;                         // pinned / registered memory goes out directly at PCIe speed
+    {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, src_host) == cudaSuccess) pageable = at.type == cudaMemoryTypeUnregistered;
+        else cudaGetLastError();
+    }
+    if (!pageable || copy_threads() < 2 || bytes < 2 * PinnedRing::CHUNK || device < 0 || device >= 64) {
+        SKB_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, st));
+        return;
+    }
+    static CopyPool *pool = new CopyPool(copy_threads());     // never destroyed: no join at exit
+    static PinnedRing rings[64];
+    PinnedRing &r = rings[device];
+    if (!r.buf[0]) {
+        for (int b = 0; b < PinnedRing::NBUF; b++) {
+            if (cudaHostAlloc((void **)&r.buf[b], PinnedRing::CHUNK, cudaHostAllocDefault) != cudaSuccess) {
+                cudaGetLastError();
+                for (int z = 0; z < b; z++) { cudaFreeHost(r.buf[z]); r.buf[z] = nullptr; }
+                r.buf[0] = nullptr;
+                SKB_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, st));
+                return;
+            }
+            SKB_CUDA(cudaEventCreateWithFlags(&r.sent[b], cudaEventDisableTiming));
+        }
+    }
+    size_t c = 0;
+    for (size_t o = 0; o < bytes; o += PinnedRing::CHUNK, c++) {
+        const int b = (int)(c % PinnedRing::NBUF);
+        const size_t n = std::min(PinnedRing::CHUNK, bytes - o);
+        if (r.in_flight[b]) SKB_CUDA(cudaEventSynchronize(r.sent[b]));     // its last transfer has left the buffer
+        pool->copy(r.buf[b], (const char *)src_host + o, n);
+        SKB_CUDA(cudaMemcpyAsync((char *)dst_dev + o, r.buf[b], n, cudaMemcpyHostToDevice, st));
+        SKB_CUDA(cudaEventRecord(r.sent[b], st));
+        r.in_flight[b] = true;
+    }
+}
+
 // Host operands: stage through device memory (copies inside the call, synchronous).
 static void apply_any(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA, int dim,
                       int64_t offset, bool shard) {
@@ -740,13 +848,13 @@ static void apply_any(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA,
         if (A->kind == MK_DENSE) {
             size_t bytes = (size_t)A->ld * (size_t)A->n * esz;
             dA.data = stage(0, bytes);
-            SKB_CUDA(cudaMemcpyAsync(dA.data, A->data, bytes, cudaMemcpyHostToDevice, st));
+            h2d_from_pageable(dA.data, A->data, bytes, device, st);
         } else {
             size_t pb = (size_t)(A->n + 1) * 4, ib = (size_t)A->nnz * 4, vb = (size_t)A->nnz * 8;
             dA.indptr = (int32_t *)stage(0, pb); dA.indices = (int32_t *)stage(1, ib); dA.values = (double *)stage(2, vb);
             SKB_CUDA(cudaMemcpyAsync(dA.indptr, A->indptr, pb, cudaMemcpyHostToDevice, st));
-            SKB_CUDA(cudaMemcpyAsync(dA.indices, A->indices, ib, cudaMemcpyHostToDevice, st));
-            SKB_CUDA(cudaMemcpyAsync(dA.values, A->values, vb, cudaMemcpyHostToDevice, st));
+            h2d_from_pageable(dA.indices, A->indices, ib, device, st);
+            h2d_from_pageable(dA.values, A->values, vb, device, st);
         }
         if (SA->kind == MK_SPARSE) {
             apply_sparse_out(t, &dA, SA, dim, offset, shard, device);
