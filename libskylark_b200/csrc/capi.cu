@@ -362,6 +362,164 @@ static DenseParams dense_params(const sl_sketch_transform_t *t) {
 }
 
 // ---------------------------------------------------------------------------
+// Host -> device copy of a PAGEABLE buffer (numpy arrays, what the reference's callers pass).  One
+// cudaMemcpyAsync from pageable memory runs at the driver's single-threaded staging rate (11.6 GB/s
+// measured on the C1 operand).  Here a few worker threads copy 32 MiB chunks into a ring of pinned
+// buffers and every chunk goes out as its own asynchronous copy, so the host-side memcpy of chunk
+// c + 1 overlaps the transfer of chunk c.  Stream-ordered like cudaMemcpyAsync; the caller's buffer
+// has been read completely when the function returns.  SKB_COPY_THREADS = 0 restores the plain copy.
+// ---------------------------------------------------------------------------
+namespace {
+struct CopyPool {
+    struct Task { char *dst; const char *src; size_t n; };
+    std::vector<std::thread> workers;
+    std::mutex mu;
+    std::condition_variable cv, done_cv;
+    std::vector<Task> q;
+    size_t pending = 0;
+    explicit CopyPool(int n) {
+        for (int i = 0; i < n; i++)
+            workers.emplace_back([this] {
+                for (;;) {
+                    Task t;
+                    {
+                        std::unique_lock<std::mutex> lk(mu);
+                        cv.wait(lk, [this] { return !q.empty(); });
+                        t = q.back(); q.pop_back();
+                    }
+                    memcpy(t.dst, t.src, t.n);
+                    {
+                        std::lock_guard<std::mutex> lk(mu);
+                        if (--pending == 0) done_cv.notify_all();
+                    }
+                }
+            });
+        for (auto &w : workers) w.detach();        // the pool lives as long as the process
+    }
+    void run(const std::vector<Task> &tasks) {               // returns when every task has been copied
+        if (tasks.empty()) return;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            for (const Task &t : tasks) { q.push_back(t); pending++; }
+        }
+        cv.notify_all();
+        std::unique_lock<std::mutex> lk(mu);
+        done_cv.wait(lk, [this] { return pending == 0; });
+    }
+    void copy(char *dst, const char *src, size_t n) {        // returns when all of [src, src + n) is in dst
+        const size_t parts = workers.size(), piece = ((n + parts - 1) / parts + 4095) / 4096 * 4096;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            for (size_t o = 0; o < n; o += piece) { q.push_back({dst + o, src + o, std::min(piece, n - o)}); pending++; }
+        }
+        cv.notify_all();
+        std::unique_lock<std::mutex> lk(mu);
+        done_cv.wait(lk, [this] { return pending == 0; });
+    }
+};
+struct PinnedRing {
+    static constexpr int NBUF = 3;
+    static constexpr size_t CHUNK = (size_t)32 << 20;
+    char *buf[NBUF] = {nullptr, nullptr, nullptr};
+    cudaEvent_t sent[NBUF] = {nullptr, nullptr, nullptr};
+    bool in_flight[NBUF] = {false, false, false};
+};
+}  // namespace
+
+static int copy_threads() {
+    static int n = -1;
+    if (n < 0) {
+        const char *e = getenv("SKB_COPY_THREADS");
+        const unsigned hw = std::thread::hardware_concurrency();
+        n = (e && *e) ? atoi(e) : (int)std::min(8u, std::max(2u, hw / 2));
+        if (n < 0) n = 0;
+        if (n > 32) n = 32;
+    }
+    return n;
+}
+
+static bool host_pointer_is_pageable(const void *p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) == cudaSuccess) return at.type == cudaMemoryTypeUnregistered;
+    cudaGetLastError();
+    return true;
+}
+static CopyPool *copy_pool() {
+    static CopyPool *pool = new CopyPool(copy_threads());     // never destroyed: no join at exit
+    return pool;
+}
+static PinnedRing *pinned_ring(int device) {                  // nullptr: no pinned memory to be had
+    static PinnedRing rings[64];
+    PinnedRing &r = rings[device];
+    if (!r.buf[0]) {
+        for (int b = 0; b < PinnedRing::NBUF; b++) {
+            if (cudaHostAlloc((void **)&r.buf[b], PinnedRing::CHUNK, cudaHostAllocDefault) != cudaSuccess) {
+                cudaGetLastError();
+                for (int z = 0; z < b; z++) { cudaFreeHost(r.buf[z]); r.buf[z] = nullptr; }
+                r.buf[0] = nullptr;
+                return nullptr;
+            }
+            SKB_CUDA(cudaEventCreateWithFlags(&r.sent[b], cudaEventDisableTiming));
+        }
+    }
+    return &r;
+}
+// `height` pieces of `width` bytes, `spitch` apart in pageable host memory, packed on the device
+// (what cudaMemcpy2DAsync with dpitch == width does)
+static void h2d_2d_from_pageable(void *dst_dev, const void *src_host, size_t spitch, size_t width, size_t height,
+                                 int device, cudaStream_t st) {
+    PinnedRing *r = nullptr;
+    if (host_pointer_is_pageable(src_host) && copy_threads() >= 2 && width * height >= 2 * PinnedRing::CHUNK &&
+        width <= PinnedRing::CHUNK && device >= 0 && device < 64)
+        r = pinned_ring(device);
+    if (!r) {
+        SKB_CUDA(cudaMemcpy2DAsync(dst_dev, width, src_host, spitch, width, height, cudaMemcpyHostToDevice, st));
+        return;
+    }
+    const size_t per = std::max<size_t>(1, PinnedRing::CHUNK / width);       // pieces per chunk
+    std::vector<CopyPool::Task> tasks;
+    size_t c = 0;
+    for (size_t h0 = 0; h0 < height; h0 += per, c++) {
+        const int b = (int)(c % PinnedRing::NBUF);
+        const size_t nh = std::min(per, height - h0);
+        if (r->in_flight[b]) SKB_CUDA(cudaEventSynchronize(r->sent[b]));
+        tasks.clear();
+        // pieces of at least 1 MiB per task: whole pieces grouped, or one piece cut
+        const size_t group = std::max<size_t>(1, ((size_t)1 << 20) / width);
+        for (size_t i = 0; i < nh; i += group)
+            for (size_t j = i; j < std::min(nh, i + group); j++)
+                tasks.push_back({r->buf[b] + j * width, (const char *)src_host + (h0 + j) * spitch, width});
+        copy_pool()->run(tasks);
+        SKB_CUDA(cudaMemcpyAsync((char *)dst_dev + h0 * width, r->buf[b], nh * width, cudaMemcpyHostToDevice, st));
+        SKB_CUDA(cudaEventRecord(r->sent[b], st));
+        r->in_flight[b] = true;
+    }
+}
+
+static void h2d_from_pageable(void *dst_dev, const void *src_host, size_t bytes, int device, cudaStream_t st) {
+    PinnedRing *rp = nullptr;        // pinned / registered memory goes out directly at PCIe speed
+    if (host_pointer_is_pageable(src_host) && copy_threads() >= 2 && bytes >= 2 * PinnedRing::CHUNK &&
+        device >= 0 && device < 64)
+        rp = pinned_ring(device);
+    if (!rp) {
+        SKB_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, st));
+        return;
+    }
+    PinnedRing &r = *rp;
+    CopyPool *pool = copy_pool();
+    size_t c = 0;
+    for (size_t o = 0; o < bytes; o += PinnedRing::CHUNK, c++) {
+        const int b = (int)(c % PinnedRing::NBUF);
+        const size_t n = std::min(PinnedRing::CHUNK, bytes - o);
+        if (r.in_flight[b]) SKB_CUDA(cudaEventSynchronize(r.sent[b]));     // its last transfer has left the buffer
+        pool->copy(r.buf[b], (const char *)src_host + o, n);
+        SKB_CUDA(cudaMemcpyAsync((char *)dst_dev + o, r.buf[b], n, cudaMemcpyHostToDevice, st));
+        SKB_CUDA(cudaEventRecord(r.sent[b], st));
+        r.in_flight[b] = true;
+    }
+}
+
+// ---------------------------------------------------------------------------
 // apply on device-resident operands
 // ---------------------------------------------------------------------------
 static void apply_device(sl_sketch_transform_t *t, const sl_matrix_t *A, const sl_matrix_t *SA,
@@ -678,13 +836,12 @@ static void apply_host_dense_pipelined(sl_sketch_transform_t *t, sl_matrix_t *A,
         dA.on_device = true; dA.device = device; dA.data = h.buf[b];
         if (colwise) {     // A is sk x other column-major: rows [k0, k0+kc) of every column
             dA.m = kc; dA.n = other; dA.ld = kc;
-            SKB_CUDA(cudaMemcpy2DAsync(h.buf[b], (size_t)kc * 8, (const double *)A->data + k0,
-                                       (size_t)A->ld * 8, (size_t)kc * 8, (size_t)other,
-                                       cudaMemcpyHostToDevice, h.copy));
+            h2d_2d_from_pageable(h.buf[b], (const double *)A->data + k0, (size_t)A->ld * 8, (size_t)kc * 8,
+                                 (size_t)other, device, h.copy);
         } else {           // A is other x sk column-major: columns [k0, k0+kc) are contiguous
             dA.m = other; dA.n = kc; dA.ld = A->ld;
-            SKB_CUDA(cudaMemcpyAsync(h.buf[b], (const double *)A->data + (size_t)k0 * A->ld,
-                                     (size_t)kc * (size_t)A->ld * 8, cudaMemcpyHostToDevice, h.copy));
+            h2d_from_pageable(h.buf[b], (const double *)A->data + (size_t)k0 * A->ld,
+                              (size_t)kc * (size_t)A->ld * 8, device, h.copy);
         }
         SKB_CUDA(cudaEventRecord(h.copied[b], h.copy));
         SKB_CUDA(cudaStreamWaitEvent(st, h.copied[b], 0));
@@ -693,111 +850,6 @@ static void apply_host_dense_pipelined(sl_sketch_transform_t *t, sl_matrix_t *A,
     }
     SKB_CUDA(cudaMemcpyAsync(SA->data, h.out, obytes, cudaMemcpyDeviceToHost, st));
     SKB_CUDA(cudaStreamSynchronize(st));
-}
-
-// ---------------------------------------------------------------------------
-// Host -> device copy of a PAGEABLE buffer (numpy arrays, what the reference's callers pass).  One
-// cudaMemcpyAsync from pageable memory runs at the driver's single-threaded staging rate (11.6 GB/s
-// measured on the C1 operand).  Here a few worker threads copy 32 MiB chunks into a ring of pinned
-// buffers and every chunk goes out as its own asynchronous copy, so the host-side memcpy of chunk
-// c + 1 overlaps the transfer of chunk c.  Stream-ordered like cudaMemcpyAsync; the caller's buffer
-// has been read completely when the function returns.  SKB_COPY_THREADS = 0 restores the plain copy.
-// ---------------------------------------------------------------------------
-namespace {
-struct CopyPool {
-    struct Task { char *dst; const char *src; size_t n; };
-    std::vector<std::thread> workers;
-    std::mutex mu;
-    std::condition_variable cv, done_cv;
-    std::vector<Task> q;
-    size_t pending = 0;
-    explicit CopyPool(int n) {
-        for (int i = 0; i < n; i++)
-            workers.emplace_back([this] {
-                for (;;) {
-                    Task t;
-                    {
-                        std::unique_lock<std::mutex> lk(mu);
-                        cv.wait(lk, [this] { return !q.empty(); });
-                        t = q.back(); q.pop_back();
-                    }
-                    memcpy(t.dst, t.src, t.n);
-                    {
-                        std::lock_guard<std::mutex> lk(mu);
-                        if (--pending == 0) done_cv.notify_all();
-                    }
-                }
-            });
-        for (auto &w : workers) w.detach();        // the pool lives as long as the process
-    }
-    void copy(char *dst, const char *src, size_t n) {        // returns when all of [src, src + n) is in dst
-        const size_t parts = workers.size(), piece = ((n + parts - 1) / parts + 4095) / 4096 * 4096;
-        {
-            std::lock_guard<std::mutex> lk(mu);
-            for (size_t o = 0; o < n; o += piece) { q.push_back({dst + o, src + o, std::min(piece, n - o)}); pending++; }
-        }
-        cv.notify_all();
-        std::unique_lock<std::mutex> lk(mu);
-        done_cv.wait(lk, [this] { return pending == 0; });
-    }
-};
-struct PinnedRing {
-    static constexpr int NBUF = 3;
-    static constexpr size_t CHUNK = (size_t)32 << 20;
-    char *buf[NBUF] = {nullptr, nullptr, nullptr};
-    cudaEvent_t sent[NBUF] = {nullptr, nullptr, nullptr};
-    bool in_flight[NBUF] = {false, false, false};
-};
-}  // namespace
-
-static int copy_threads() {
-    static int n = -1;
-    if (n < 0) {
-        const char *e = getenv("SKB_COPY_THREADS");
-        const unsigned hw = std::thread::hardware_concurrency();
-        n = (e && *e) ? atoi(e) : (int)std::min(8u, std::max(2u, hw / 2));
-        if (n < 0) n = 0;
-        if (n > 32) n = 32;
-    }
-    return n;
-}
-
-static void h2d_from_pageable(void *dst_dev, const void *src_host, size_t bytes, int device, cudaStream_t st) {
-    bool pageable = true;                         // pinned / registered memory goes out directly at PCIe speed
-    {
-        cudaPointerAttributes at;
-        if (cudaPointerGetAttributes(&at, src_host) == cudaSuccess) pageable = at.type == cudaMemoryTypeUnregistered;
-        else cudaGetLastError();
-    }
-    if (!pageable || copy_threads() < 2 || bytes < 2 * PinnedRing::CHUNK || device < 0 || device >= 64) {
-        SKB_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, st));
-        return;
-    }
-    static CopyPool *pool = new CopyPool(copy_threads());     // never destroyed: no join at exit
-    static PinnedRing rings[64];
-    PinnedRing &r = rings[device];
-    if (!r.buf[0]) {
-        for (int b = 0; b < PinnedRing::NBUF; b++) {
-            if (cudaHostAlloc((void **)&r.buf[b], PinnedRing::CHUNK, cudaHostAllocDefault) != cudaSuccess) {
-                cudaGetLastError();
-                for (int z = 0; z < b; z++) { cudaFreeHost(r.buf[z]); r.buf[z] = nullptr; }
-                r.buf[0] = nullptr;
-                SKB_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, st));
-                return;
-            }
-            SKB_CUDA(cudaEventCreateWithFlags(&r.sent[b], cudaEventDisableTiming));
-        }
-    }
-    size_t c = 0;
-    for (size_t o = 0; o < bytes; o += PinnedRing::CHUNK, c++) {
-        const int b = (int)(c % PinnedRing::NBUF);
-        const size_t n = std::min(PinnedRing::CHUNK, bytes - o);
-        if (r.in_flight[b]) SKB_CUDA(cudaEventSynchronize(r.sent[b]));     // its last transfer has left the buffer
-        pool->copy(r.buf[b], (const char *)src_host + o, n);
-        SKB_CUDA(cudaMemcpyAsync((char *)dst_dev + o, r.buf[b], n, cudaMemcpyHostToDevice, st));
-        SKB_CUDA(cudaEventRecord(r.sent[b], st));
-        r.in_flight[b] = true;
-    }
 }
 
 // Host operands: stage through device memory (copies inside the call, synchronous).
