@@ -519,6 +519,41 @@ static void h2d_from_pageable(void *dst_dev, const void *src_host, size_t bytes,
     }
 }
 
+// The mirror image for results (feature maps return far more than they take: 500k x 16384 floats from
+// 500k x 784): chunks come back into the pinned ring and the worker threads move chunk c into the
+// caller's pageable buffer while chunk c + 1 is on the wire.  Synchronous: the result is in dst_host
+// when the function returns.
+static void d2h_to_pageable(void *dst_host, const void *src_dev, size_t bytes, int device, cudaStream_t st) {
+    PinnedRing *rp = nullptr;
+    if (host_pointer_is_pageable(dst_host) && copy_threads() >= 2 && bytes >= 2 * PinnedRing::CHUNK &&
+        device >= 0 && device < 64)
+        rp = pinned_ring(device);
+    if (!rp) {
+        SKB_CUDA(cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, st));
+        SKB_CUDA(cudaStreamSynchronize(st));
+        return;
+    }
+    PinnedRing &r = *rp;
+    CopyPool *pool = copy_pool();
+    for (int b = 0; b < PinnedRing::NBUF; b++)
+        if (r.in_flight[b]) { SKB_CUDA(cudaEventSynchronize(r.sent[b])); r.in_flight[b] = false; }
+    const size_t nchunks = (bytes + PinnedRing::CHUNK - 1) / PinnedRing::CHUNK;
+    auto issue = [&](size_t c) {
+        const int b = (int)(c % PinnedRing::NBUF);
+        const size_t o = c * PinnedRing::CHUNK, n = std::min(PinnedRing::CHUNK, bytes - o);
+        SKB_CUDA(cudaMemcpyAsync(r.buf[b], (const char *)src_dev + o, n, cudaMemcpyDeviceToHost, st));
+        SKB_CUDA(cudaEventRecord(r.sent[b], st));
+    };
+    for (size_t c = 0; c < nchunks && c + 1 < (size_t)PinnedRing::NBUF; c++) issue(c);     // NBUF - 1 chunks ahead
+    for (size_t c = 0; c < nchunks; c++) {
+        const int b = (int)(c % PinnedRing::NBUF);
+        if (c + PinnedRing::NBUF - 1 < nchunks) issue(c + PinnedRing::NBUF - 1);           // into the buffer drained last turn
+        const size_t o = c * PinnedRing::CHUNK, n = std::min(PinnedRing::CHUNK, bytes - o);
+        SKB_CUDA(cudaEventSynchronize(r.sent[b]));
+        pool->copy((char *)dst_host + o, r.buf[b], n);
+    }
+}
+
 // ---------------------------------------------------------------------------
 // apply on device-resident operands
 // ---------------------------------------------------------------------------
@@ -915,8 +950,7 @@ static void apply_any(sl_sketch_transform_t *t, sl_matrix_t *A, sl_matrix_t *SA,
         size_t obytes = (size_t)SA->ld * (size_t)SA->n * (SA->dtype == SL_DTYPE_F32 ? 4 : 8);
         dSA.data = stage(3, obytes);
         apply_device(t, &dA, &dSA, dim, offset, shard, false);
-        SKB_CUDA(cudaMemcpyAsync(SA->data, dSA.data, obytes, cudaMemcpyDeviceToHost, st));
-        SKB_CUDA(cudaStreamSynchronize(st));
+        d2h_to_pageable(SA->data, dSA.data, obytes, device, st);
     } catch (...) {
         cudaStreamSynchronize(st);
         throw;
