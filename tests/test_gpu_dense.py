@@ -155,6 +155,22 @@ def test_large_host_arrays_take_the_pipelined_path(sk, oracle):
     assert rel_fro(part, want) < TOL64
 
 
+def test_large_pageable_operands_and_results(sk, oracle):
+    """Host arrays above 64 MiB on the generic path (hash transforms, feature maps): the operand goes to
+    the device, and the result comes back, in chunks through pinned memory filled by worker threads."""
+    c, oc = _ctx(sk, oracle, 78)
+    n, s, d = 60000, 64, 200                                     # 96 MB in
+    A = np.random.default_rng(10).standard_normal((n, d))
+    S, O = sk.CWT(n, s, c), oracle.CWT(n, s, oc)
+    want = O.apply(A, "columnwise")
+    assert rel_fro(S.apply(np.asfortranarray(A), None, "columnwise"), want) < TOL64
+    assert rel_fro(S.apply(A.copy(), None, "columnwise"), want) < TOL64
+    m, k, f = 45000, 40, 256                                     # 92 MB out
+    X = np.random.default_rng(11).random((m, k))
+    R, Ro = sk.GaussianRFT(k, f, 3.0, context=c), oracle.GaussianRFT(k, f, 3.0, oc)
+    assert rel_fro(R.apply(X, None, "rowwise"), Ro.apply(X, "rowwise")) < TOL64
+
+
 def test_edge_shapes(sk, oracle):
     c, oc = _ctx(sk, oracle, 3)
     J, OJ = sk.JLT(37, 1, c), oracle.JLT(37, 1, oc)              # one sketch row
