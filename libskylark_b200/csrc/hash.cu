@@ -78,7 +78,10 @@ void hash_build_tables(int seed, uint64_t idx_base, uint64_t val_base, uint64_t 
 // ---------------------------------------------------------------------------
 // Plan: rows grouped by bucket, cut in chunks of <= CHUNK rows
 // ---------------------------------------------------------------------------
-static constexpr int CHUNK = 32;
+#ifndef SKB_K1_CHUNK
+#define SKB_K1_CHUNK 32
+#endif
+static constexpr int CHUNK = SKB_K1_CHUNK;       // rows of one bucket a warp takes: 32 or 64
 
 __global__ void k_iota(int32_t *a, size_t n) {
     size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -228,6 +231,8 @@ k_hash_rows(const double *__restrict__ X, size_t ldx, int m,
 
     int myrow = 0; double myval = 0.0;
     if (lane < cnt) { myrow = rows[beg + lane]; myval = value[myrow]; }
+    int myrow1 = 0; double myval1 = 0.0;           // rows 32..63 of the chunk (CHUNK == 64)
+    if (CHUNK > 32 && lane + 32 < cnt) { myrow1 = rows[beg + 32 + lane]; myval1 = value[myrow1]; }
 
     constexpr int TILE = 32 * VEC;
     const int col = tile * TILE + lane * VEC;
@@ -240,8 +245,8 @@ k_hash_rows(const double *__restrict__ X, size_t ldx, int m,
         double2 x[U]; double v[U];
 #pragma unroll
         for (int i = 0; i < U; i++) {
-            int k = __shfl_sync(0xffffffffu, myrow, (r + i) & 31);
-            v[i] = __shfl_sync(0xffffffffu, myval, (r + i) & 31);
+            int k = __shfl_sync(0xffffffffu, (CHUNK > 32 && r >= 32) ? myrow1 : myrow, (r + i) & 31);
+            v[i] = __shfl_sync(0xffffffffu, (CHUNK > 32 && r >= 32) ? myval1 : myval, (r + i) & 31);
             x[i].x = 0.0; x[i].y = 0.0;
             if (active && r + i < cnt) {
                 const double *p = xcol + (size_t)k * ldx;
