@@ -63,7 +63,11 @@ int sl_free_sketch_transform(sl_sketch_transform_t *S);
 /* capi/sketchc.hpp:53-56, capi/csketch.cpp:614-1958.  input_type/output_type are
  * "Matrix" or "SparseMatrix"; A/SA come from the sl_wrap_* functions; dim is
  * SL_COLUMNWISE (SA = S*A) or SL_ROWWISE (SA = A*S^T).  An unsupported combination
- * returns 109 (the reference silently returns 0, capi/csketch.cpp:1957). */
+ * returns 109 (the reference silently returns 0, capi/csketch.cpp:1957).
+ * Host buffers (the reference's only kind) are copied to the device and the result back inside the
+ * call, which returns when SA is complete.  Pageable buffers above 64 MiB are staged through pinned
+ * memory by a few worker threads of the library (SKB_COPY_THREADS, default min(8, cores / 2); 0 = one
+ * plain cudaMemcpyAsync); the threads only read A and write SA, and only during the call. */
 int sl_apply_sketch_transform(sl_sketch_transform_t *S, char *input_type, void *A,
                               char *output_type, void *SA, int dim);
 
