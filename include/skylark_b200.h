@@ -143,7 +143,9 @@ int sl_fjlt_apply_shard_peer(sl_sketch_transform_t *S, void *A, int64_t index_of
                              int world, int rank, void *scratch_dev);
 
 /* Options: "boost_order" = "160" (default; Boost >= 1.57 Rademacher draw order) | "155";
- * "fjlt_fut" = "dct" (default; what the reference computes) | "wht". */
+ * "fjlt_fut" = "dct" (default; what the reference computes) | "wht";
+ * "sm_reserve" = SMs the persistent FJLT kernels leave free for a collective running beside them (0..100);
+ * "csc_form" = "dump" (default) | "bulk": kernel form of the CSC -> dense hash sketch (same results). */
 int sl_set_option(const char *key, const char *value);
 
 /* Generated tables, copied to host memory (tests compare them bit for bit):

@@ -1258,6 +1258,12 @@ int sl_set_option(const char *key, const char *value) {
         const int v = atoi(value);
         if (v < 0 || v > 100) throw error(SKB_ERR_INVALID_PARAM, "sm_reserve must be in [0, 100]");
         fjlt_set_sm_reserve(v);
+    } else if (strcmp(key, "csc_form") == 0) {
+        // kernel form of the CSC -> dense hash sketch: "dump" (default) or "bulk" (slices of the
+        // accumulator through the copy engine; same speed at C4, kept selectable for A/B and tests)
+        if (strcmp(value, "dump") == 0) hash_set_csc_form(0);
+        else if (strcmp(value, "bulk") == 0) hash_set_csc_form(1);
+        else throw error(SKB_ERR_INVALID_PARAM, "csc_form must be dump or bulk");
     } else throw error(SKB_ERR_INVALID_PARAM, std::string("unknown option ") + key);
     SL_CATCH
 }

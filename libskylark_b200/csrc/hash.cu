@@ -819,6 +819,9 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
     extern __shared__ double acc[];   // [S]
     for (int i = threadIdx.x; i < S; i += blockDim.x) acc[i] = 0.0;
     __syncthreads();
+    // output and nonzeros stream through L2 once (evict-first); the bucket / value tables are gathered at
+    // random by every column and are asked to stay (see k_hash_csc_colwise_bulk)
+    const uint64_t pol_first = hc_policy_evict_first(), pol_last = hc_policy_evict_last();
     // Three-deep software pipeline over the columns this CTA owns.  A nonzero needs three
     // dependent trips to L2/HBM (indptr -> index/value -> bucket/value tables); each trip of a
     // LATER column is issued before the current column's dense S-vector is written out and its
@@ -838,7 +841,7 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
         for (int i = 0; i < PRE; i++) {
             const int p = q0 + (int)threadIdx.x + i * (int)blockDim.x;
             rN[i] = -1; xN[i] = 0.0;
-            if (p < q1) { rN[i] = indices[p]; xN[i] = values[p]; }
+            if (p < q1) { rN[i] = ldg_i32_hint(indices + p, pol_first); xN[i] = ldg_f64_hint(values + p, pol_first); }
         }
         e0 = q0; e1 = q1;
     };
@@ -846,7 +849,7 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
 #pragma unroll
         for (int i = 0; i < PRE; i++) {
             hC[i] = -1; wC[i] = 0.0; xC[i] = xN[i];
-            if (rN[i] >= 0) { hC[i] = bucket[rN[i]]; wC[i] = value[rN[i]]; }
+            if (rN[i] >= 0) { hC[i] = ldg_i32_hint(bucket + rN[i], pol_last); wC[i] = ldg_f64_hint(value + rN[i], pol_last); }
         }
         t0 = e0; t1 = e1;
     };
@@ -862,8 +865,9 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
             // fresh indptr load here would put an L2 round trip on every column's critical path)
             const int p0 = t0, p1 = t1;
             for (int p = p0 + PRE * (int)blockDim.x + (int)threadIdx.x; p < p1; p += blockDim.x) {
-                const int row = indices[p];
-                atomicAdd(&acc[bucket[row]], __dmul_rn(value[row], values[p]));
+                const int row = ldg_i32_hint(indices + p, pol_first);
+                atomicAdd(&acc[ldg_i32_hint(bucket + row, pol_last)],
+                          __dmul_rn(ldg_f64_hint(value + row, pol_last), ldg_f64_hint(values + p, pol_first)));
             }
         }
         load_tables();                 // column col + stride   (rows arrived an iteration ago)
@@ -875,7 +879,7 @@ k_hash_csc_colwise_smem(const int32_t *__restrict__ indptr, const int32_t *__res
             double2 *o2 = reinterpret_cast<double2 *>(o);
             double2 *a2 = reinterpret_cast<double2 *>(acc);
             const double2 z = make_double2(0.0, 0.0);
-            for (int i = threadIdx.x; i < S / 2; i += blockDim.x) { o2[i] = a2[i]; a2[i] = z; }
+            for (int i = threadIdx.x; i < S / 2; i += blockDim.x) { __stcs(o2 + i, a2[i]); a2[i] = z; }
             if ((S & 1) && threadIdx.x == 0) { o[S - 1] = acc[S - 1]; acc[S - 1] = 0.0; }
         } else {
             for (int i = threadIdx.x; i < S; i += blockDim.x) { o[i] = acc[i]; acc[i] = 0.0; }
@@ -1001,6 +1005,9 @@ __global__ void k_hash_csc_colwise_global(const int32_t *__restrict__ indptr,
     }
 }
 
+static int g_csc_bulk = -1;              // -1: environment (SKB_CSC_BULK), else sl_set_option("csc_form")
+void hash_set_csc_form(int bulk) { g_csc_bulk = bulk ? 1 : 0; }
+
 void hash_apply_csc_columnwise(const int32_t *indptr, const int32_t *indices,
                                const double *values, size_t ncols, const int32_t *bucket,
                                const double *value, double *OUT, size_t ldo, int S,
@@ -1011,11 +1018,13 @@ void hash_apply_csc_columnwise(const int32_t *indptr, const int32_t *indices,
     if (force_global < 0) force_global = getenv("SKB_DEBUG_CSC_GLOBAL") ? 1 : 0;
     if (smem <= 220 * 1024 && !force_global) {
         const bool vec2 = (ldo % 2 == 0) && ((uintptr_t)OUT % 16 == 0);
-        static const bool no_bulk = getenv("SKB_CSC_DUMP") != nullptr;         // A/B: the register dump
-        // the bulk form keeps a column's nonzeros in registers (2048 per CTA) across its slices; longer
-        // columns would be gathered once per slice and once more to re-zero: those keep the dump form
-        // (C4 column-sharded, 10000 nonzeros per column: 3.2 ms against 7.1)
-        const bool bulk = vec2 && S % 4 == 0 && !no_bulk && nnz_hint > 0 && nnz_hint / ncols <= 1536;
+        // Both forms carry the L2 hints that matter (3.70 -> 3.3 ms at the C4 shard); with them the plain
+        // register dump (3.26 ms, any column length) and the bulk-store slices (3.30 ms, columns of up to
+        // 2048 nonzeros kept in registers) measure the same, so the simpler one is the default and
+        // sl_set_option("csc_form", "bulk") / SKB_CSC_BULK=1 selects the other.
+        static const bool env_bulk = getenv("SKB_CSC_BULK") != nullptr;
+        const bool want_bulk = g_csc_bulk < 0 ? env_bulk : g_csc_bulk == 1;
+        const bool bulk = want_bulk && vec2 && S % 4 == 0 && nnz_hint > 0 && nnz_hint / ncols <= 1536;
         static const int dbg = getenv("SKB_CSC_DBG") ? atoi(getenv("SKB_CSC_DBG")) : 0;   // timing experiments only
         if (bulk) {
             // slices per column / threads per CTA: SKB_CSC_NH, SKB_CSC_THREADS (tuning)

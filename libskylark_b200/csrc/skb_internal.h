@@ -104,6 +104,7 @@ void hash_apply_csc_columnwise(const int32_t *indptr, const int32_t *indices,
                                const double *values, size_t ncols, const int32_t *bucket,
                                const double *value, double *OUT, size_t ldo, int S,
                                cudaStream_t st, size_t nnz_hint = 0);      // nnz of the operand: picks the kernel form
+void hash_set_csc_form(int bulk);        // 0: register dump (default), 1: bulk-store slices
 // CSC input (columns are the sketched index): OUT[row + h(col)*ldo] += v(col)*val
 void hash_apply_csc_rowwise(const int32_t *indptr, const int32_t *indices,
                             const double *values, size_t nrows, size_t ncols,

@@ -90,9 +90,10 @@ def test_scipy_sparse_input(sk, oracle, T, fmt):
 @pytest.mark.parametrize("T", ["CWT", "MMT"])
 @pytest.mark.parametrize("case", ["few long columns", "all columns long"])
 def test_csc_to_dense_long_columns(sk, oracle, T, case):
-    """CSC -> dense with columns beyond the 2048 nonzeros a CTA of the bulk-store kernel holds in
-    registers (its overflow loops), and with long columns throughout (the register-dump kernel, picked by
-    the average column length); s % 4 == 0 and a column-major result, as both kernels need."""
+    """CSC -> dense in both kernel forms: the register dump (default) and the bulk-store slices, the latter
+    with columns beyond the 2048 nonzeros its CTA holds in registers (overflow loops) and, when columns are
+    long throughout, falling back to the dump by the average column length; s % 4 == 0 and a column-major
+    result, as the bulk form needs."""
     n, s = 12000, 128
     rng = np.random.default_rng(5)
     lens = [60] * 30 + [3000, 5000, 2049] if case == "few long columns" else [2600] * 7
@@ -104,6 +105,13 @@ def test_csc_to_dense_long_columns(sk, oracle, T, case):
     want = O.apply(A.toarray(), "columnwise")
     got = S.apply(A, np.empty((s, len(lens)), order="F"), "columnwise")
     assert rel_fro(got, want) < TOL
+    from libskylark_b200 import lib
+    lib.set_option("csc_form", "bulk")                   # the slices-through-the-copy-engine form
+    try:
+        for _ in range(2):                               # twice: the slice buffers are left clean
+            assert rel_fro(S.apply(A, np.empty((s, len(lens)), order="F"), "columnwise"), want) < TOL
+    finally:
+        lib.set_option("csc_form", "dump")
     # a second apply starts from clean shared accumulators (sums of a slot are taken with shared-memory
     # atomics, so the two results agree to rounding, not bitwise)
     got2 = S.apply(A, np.empty((s, len(lens)), order="F"), "columnwise")
