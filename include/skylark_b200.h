@@ -148,6 +148,14 @@ int sl_fjlt_apply_shard_peer(sl_sketch_transform_t *S, void *A, int64_t index_of
  * "csc_form" = "dump" (default) | "bulk": kernel form of the CSC -> dense hash sketch (same results). */
 int sl_set_option(const char *key, const char *value);
 
+/* Testing hook, host arithmetic only (no device needed): the plan of the strided hash kernel for the given
+ * bucket / value tables (n entries, s buckets).  entries = rounds of 32 packed words
+ * (index in its tile of 2048 << 3 | bucket inside the warp's range << 16 | sign << 31), one stream per warp
+ * (8 warps), off[w * (ntiles + 1) + t] = first round of warp w in tile t; bucket_width = buckets per warp.
+ * Both arrays are malloc'ed; the caller frees them. */
+int sl_debug_hash_cols_plan(const int32_t *bucket, const double *value, int64_t n, int s, uint32_t **entries,
+                            int64_t *n_entries, uint32_t **off, int64_t *n_off, int *bucket_width);
+
 /* Generated tables, copied to host memory (tests compare them bit for bit):
  * what = "row_idx" (int64, hash), "row_value" (double, hash), "D" (double, FJLT),
  * "samples" (int64, FJLT and UST), "shifts" (double, RFT), "scales" (double, RFT);

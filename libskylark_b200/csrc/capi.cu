@@ -1268,6 +1268,25 @@ int sl_set_option(const char *key, const char *value) {
     SL_CATCH
 }
 
+int sl_debug_hash_cols_plan(const int32_t *bucket, const double *value, int64_t n, int s, uint32_t **entries,
+                            int64_t *n_entries, uint32_t **off, int64_t *n_off, int *bucket_width) {
+    SL_TRY
+    if (!bucket || !value || n < 0 || s < 1 || !entries || !n_entries || !off || !n_off || !bucket_width)
+        throw error(SKB_ERR_INVALID_PARAM, "sl_debug_hash_cols_plan: bad argument");
+    std::vector<uint32_t> e, o;
+    std::vector<double> v;
+    bool signs = true;
+    hash_schedule_cols_plan(bucket, value, (size_t)n, s, e, v, o, &signs);
+    *entries = (uint32_t *)malloc(e.size() * sizeof(uint32_t) + 1);
+    *off = (uint32_t *)malloc(o.size() * sizeof(uint32_t) + 1);
+    if (!*entries || !*off) { free(*entries); free(*off); throw error(SKB_ERR_ALLOC, "out of host memory"); }
+    memcpy(*entries, e.data(), e.size() * sizeof(uint32_t));
+    memcpy(*off, o.data(), o.size() * sizeof(uint32_t));
+    *n_entries = (int64_t)e.size(); *n_off = (int64_t)o.size();
+    *bucket_width = hash_cols_plan_bucket_width(s);
+    SL_CATCH
+}
+
 int sl_sketch_export(sl_sketch_transform_t *t, const char *what, int64_t first, int64_t count,
                      void *host_out) {
     SL_TRY

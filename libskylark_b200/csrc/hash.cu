@@ -427,26 +427,25 @@ void hash_free_cols_plan(HashColsPlan *plan) {
     *plan = HashColsPlan();
 }
 
-void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, int S, HashColsPlan *plan,
-                          cudaStream_t st) {
-    hash_free_cols_plan(plan);
-    plan->n = n; plan->S = S;
-    plan->SW = (((S + HC_W - 1) / HC_W) + 31) / 32 * 32;
-    plan->ntiles = (int)((n + HC_K - 1) / HC_K);
-    if (n == 0) return;
-    std::vector<int32_t> hb(n); std::vector<double> hv(n);
-    SKB_CUDA(cudaMemcpyAsync(hb.data(), bucket, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-    SKB_CUDA(cudaMemcpyAsync(hv.data(), value, n * sizeof(double), cudaMemcpyDeviceToHost, st));
-    SKB_CUDA(cudaStreamSynchronize(st));
+int hash_cols_plan_bucket_width(int S) { return (((S + HC_W - 1) / HC_W) + 31) / 32 * 32; }
+
+// The plan itself: host arithmetic only (no CUDA), so the CPU test-suite can check its invariants
+// (tests/test_host.py through sl_debug_hash_cols_plan).
+void hash_schedule_cols_plan(const int32_t *hb, const double *hv, size_t n, int S, std::vector<uint32_t> &entries,
+                             std::vector<double> &vals, std::vector<uint32_t> &off, bool *signs_out) {
+    const int SW = hash_cols_plan_bucket_width(S);
+    const int ntiles = (int)((n + HC_K - 1) / HC_K);
     bool signs = true;
     for (size_t k = 0; k < n && signs; k++) signs = hv[k] == 1.0 || hv[k] == -1.0;
+    *signs_out = signs;
+    entries.clear(); vals.clear();
     // Warp-major: the rounds of warp w for tiles 0, 1, ... follow each other, every (warp, tile) run
     // padded with empty rounds to whole batches of HC_B, so a warp reads ONE contiguous stream and its
     // prefetch runs across tile boundaries.  off[w * (ntiles + 1) + t] = first round of (w, t).
-    const size_t nt = (size_t)plan->ntiles;
+    const size_t nt = (size_t)ntiles;
     std::vector<std::vector<uint32_t>> we(HC_W);
     std::vector<std::vector<double>> wv(HC_W);
-    std::vector<uint32_t> off((size_t)HC_W * (nt + 1));
+    off.assign((size_t)HC_W * (nt + 1), 0u);
     std::vector<size_t> wr(HC_W, 0);
     // A warp owns the SW buckets [w * SW, (w + 1) * SW); ANY lane may take any of its rows, as long as
     // the 32 rows of a round go to 32 different buckets (plain load-add-store, no atomics) and a bucket
@@ -456,7 +455,6 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
     // (bucket mod 16) where the rows allow it, then different tile bank pairs (k mod 16).
     // An empty slot adds element 0 of the tile into a spare accumulator of its lane (bucket SW + lane,
     // never written out): the round needs no branch.
-    const int SW = plan->SW;
     std::vector<std::vector<uint32_t>> fifo((size_t)HC_W * SW);
     std::vector<uint32_t> head((size_t)SW), cand;
     std::vector<char> in_group((size_t)SW);
@@ -550,8 +548,6 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
             wr[w] += nr;
         }
     }
-    std::vector<uint32_t> entries;
-    std::vector<double> vals;
     size_t base = 0;
     for (int w = 0; w < HC_W; w++) {
         for (size_t t = 0; t < nt; t++) off[(size_t)w * (nt + 1) + t] += (uint32_t)base;
@@ -562,8 +558,25 @@ void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, 
     }
     // the prefetch reads HC_Q batches past the round it works on
     for (int z = 0; z < 2 * HC_NB; z++)                     // the prefetch runs two sets past the last round
-        for (int l = 0; l < 32; l++) entries.push_back((uint32_t)(plan->SW + l) << 16);
+        for (int l = 0; l < 32; l++) entries.push_back((uint32_t)(SW + l) << 16);
     if (!signs) vals.insert(vals.end(), (size_t)2 * HC_NB * 32, 0.0);
+}
+
+void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, int S, HashColsPlan *plan,
+                          cudaStream_t st) {
+    hash_free_cols_plan(plan);
+    plan->n = n; plan->S = S;
+    plan->SW = hash_cols_plan_bucket_width(S);
+    plan->ntiles = (int)((n + HC_K - 1) / HC_K);
+    if (n == 0) return;
+    std::vector<int32_t> hb(n); std::vector<double> hv(n);
+    SKB_CUDA(cudaMemcpyAsync(hb.data(), bucket, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    SKB_CUDA(cudaMemcpyAsync(hv.data(), value, n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    SKB_CUDA(cudaStreamSynchronize(st));
+    std::vector<uint32_t> entries, off;
+    std::vector<double> vals;
+    bool signs = true;
+    hash_schedule_cols_plan(hb.data(), hv.data(), n, S, entries, vals, off, &signs);
     try {
         SKB_CUDA(cudaMalloc(&plan->entries, entries.size() * sizeof(uint32_t) + 256));
         SKB_CUDA(cudaMalloc(&plan->off, off.size() * sizeof(uint32_t)));

@@ -96,6 +96,12 @@ struct HashColsPlan {
 void hash_build_cols_plan(const int32_t *bucket, const double *value, size_t n, int S, HashColsPlan *plan,
                           cudaStream_t st);
 void hash_free_cols_plan(HashColsPlan *plan);
+// the host-only part of the plan (no CUDA): rounds of 32 packed entries per warp, warp-major, and the
+// first round of every (warp, tile)
+int hash_cols_plan_bucket_width(int S);
+void hash_schedule_cols_plan(const int32_t *bucket_host, const double *value_host, size_t n, int S,
+                             std::vector<uint32_t> &entries, std::vector<double> &vals, std::vector<uint32_t> &off,
+                             bool *all_signs);
 // false = shape or alignment outside the planned kernel's range (caller falls back to hash_apply_cols)
 bool hash_apply_cols_planned(const double *X, size_t ldx, size_t n, size_t m, const HashColsPlan &plan,
                              double *OUT, size_t ldo, int S, cudaStream_t st);

@@ -169,3 +169,74 @@ def test_shard_range():
         assert parts[0][0] == 0 and sum(c for _, c in parts) == n
         for (o1, c1), (o2, _) in zip(parts, parts[1:]):
             assert o1 + c1 == o2
+
+
+@pytest.mark.parametrize("n,s,valued", [(5000, 256, False), (9001, 2000, False), (4096, 513, True), (300, 20000, False)])
+def test_strided_hash_plan_invariants(n, s, valued):
+    """The host-built plan of the atomics-free strided hash kernel (hash.cu: hash_schedule_cols_plan), checked
+    without a device: every index appears exactly once, in its own tile and in the stream of the warp that
+    owns its bucket; the 32 rows of a round -- and of the two rounds the kernel applies together -- go to
+    different buckets (plain load-add-store is then race-free); a bucket sees its rows in ascending order
+    (the reference's summation order, hash_transform_Elemental.hpp:83-100); idle slots point at the spare
+    accumulators; and each half warp of a round sits on 16 different shared-memory bank pairs for the
+    accumulators (a performance property, asserted because the kernel's 6-wavefront round depends on it)."""
+    from libskylark_b200 import _build
+    L = ctypes.CDLL(_build.SO)
+    rng = np.random.default_rng(n + s)
+    bucket = rng.integers(0, s, size=n, dtype=np.int32)
+    value = (rng.standard_normal(n) if valued else rng.choice([-1.0, 1.0], size=n)).astype(np.float64)
+    ent, off = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint32)()
+    n_ent, n_off, sw = ctypes.c_int64(), ctypes.c_int64(), ctypes.c_int()
+    L.sl_debug_hash_cols_plan.argtypes = (ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int,
+                                          ctypes.POINTER(ctypes.POINTER(ctypes.c_uint32)), ctypes.POINTER(ctypes.c_int64),
+                                          ctypes.POINTER(ctypes.POINTER(ctypes.c_uint32)), ctypes.POINTER(ctypes.c_int64),
+                                          ctypes.POINTER(ctypes.c_int))
+    rc = L.sl_debug_hash_cols_plan(bucket.ctypes.data, value.ctypes.data, n, s, ctypes.byref(ent), ctypes.byref(n_ent),
+                                   ctypes.byref(off), ctypes.byref(n_off), ctypes.byref(sw))
+    assert rc == 0
+    libc = ctypes.CDLL(None)
+    libc.free.argtypes = (ctypes.c_void_p,)
+    try:
+        E = np.ctypeslib.as_array(ent, shape=(n_ent.value,)).copy().reshape(-1, 32)
+        O = np.ctypeslib.as_array(off, shape=(n_off.value,)).copy()
+    finally:
+        libc.free(ent); libc.free(off)
+    SW, W, K = sw.value, 8, 2048
+    assert SW % 32 == 0 and W * SW >= s
+    ntiles = (n + K - 1) // K
+    O = O.reshape(W, ntiles + 1)
+    assert E.shape[0] >= int(O[-1, -1]) + 2                      # the kernel's prefetch may run past the last round
+    seen = np.zeros(n, dtype=np.int64)
+    last_row = {}
+    for w in range(W):
+        assert np.all(np.diff(O[w]) >= 0) and np.all(np.diff(O[w]) % 2 == 0)       # whole pairs of rounds
+        if w:
+            assert O[w, 0] == O[w - 1, -1]                                         # streams follow each other
+        for t in range(ntiles):
+            rounds = E[O[w, t]:O[w, t + 1]]
+            for r0 in range(0, len(rounds), 2):
+                pair_buckets = []
+                for r in rounds[r0:r0 + 2]:
+                    k = (r >> 3) & 0x7FF
+                    b = (r >> 16) & 0x1FFF
+                    real = b < SW
+                    assert np.all(b[~real] >= SW) and np.all(b[~real] < SW + 32)        # spare accumulators
+                    g = t * K + k[real].astype(np.int64)                                # global index
+                    assert np.all(g < n)
+                    assert np.array_equal(bucket[g], w * SW + b[real].astype(np.int64))  # right warp, right bucket
+                    sign = (r[real] >> 31).astype(bool)
+                    if not valued:
+                        assert np.array_equal(sign, value[g] < 0)
+                    seen[g] += 1
+                    assert len(set(b[real].tolist())) == int(real.sum())                # 32 different buckets
+                    pair_buckets += b[real].tolist()
+                    for half in (slice(0, 16), slice(16, 32)):                          # one wavefront per half warp
+                        assert len(set((b[half] % 16).tolist())) == 16
+                        kk = k[half][real[half]]
+                        assert len(set((kk % 16).tolist())) == len(kk)
+                    for gi, bi in zip(g.tolist(), b[real].tolist()):                    # ascending rows per bucket
+                        key = (w, bi)
+                        assert last_row.get(key, -1) < gi
+                        last_row[key] = gi
+                assert len(set(pair_buckets)) == len(pair_buckets)                      # the pair applied together
+    assert np.all(seen == 1)
